@@ -1,0 +1,227 @@
+"""Host-side mirror of the reference's interface for the PIC hot path.
+
+`PicContext` owns one C-ABI context (one rank == one GPU) and exposes the four
+hot entries under the reference's own subroutine names
+(`update_eb_fields_half`, `push_particles`, `current_finish`,
+`update_eb_fields_final`; epoch3d/src/epoch3d.F90:208-246) plus the setters that
+replace reading `MODULE shared_data` globals.  Python is harness glue only: all
+arithmetic happens behind the ABI.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+
+# boundary codes (constants.F90:56-71)
+BC = dict(periodic=1, other=2, simple_laser=3, simple_outflow=4, open=5, dump=6,
+          zero_gradient=7, clamp=8, reflect=9, conduct=10, thermal=11,
+          cpml_laser=12, cpml_outflow=13, mixed=14, heat_bath=15)
+SHAPES = dict(tophat=0, triangle=1, bspline3=2)
+PNG = {0: 2, 1: 3, 2: 4}  # constants.F90:472-485
+FIELD_NAMES = ("ex", "ey", "ez", "bx", "by", "bz", "jx", "jy", "jz")
+
+
+class EpochError(RuntimeError):
+    pass
+
+
+def _i32(a):
+    return (C.c_int32 * len(a))(*[int(x) for x in a])
+
+
+def _f64(a):
+    return (C.c_double * len(a))(*[float(x) for x in a])
+
+
+def _pad3(a, fill):
+    a = list(a)
+    return a + [fill] * (3 - len(a))
+
+
+class PicContext:
+    def __init__(self, ndims, shape="triangle", abi=None, device=0, rank=0, nproc=1,
+                 nprocdir=(1, 1, 1), coords=(0, 0, 0), nccl_id=None):
+        self.abi = abi if abi is not None else _abi.product()
+        self.ndims = int(ndims)
+        self.shape = SHAPES[shape] if isinstance(shape, str) else int(shape)
+        self.ng = PNG[self.shape] + 2
+        self.nvar = self.ndims + 4
+        self._ctx = C.c_void_p()
+        idbuf = None
+        if nccl_id is not None:
+            idbuf = C.create_string_buffer(bytes(nccl_id), 128)
+        rc = self.abi.create(C.byref(self._ctx), self.ndims, self.shape, device, rank, nproc,
+                             _i32(_pad3(nprocdir, 1)), _i32(_pad3(coords, 0)), idbuf)
+        if rc != 0:
+            raise EpochError(f"create failed rc={rc}: {self.abi.last_error(None)}")
+        self.n = None
+        self.nspecies = 0
+
+    # -- plumbing ---------------------------------------------------------
+    def _ck(self, rc):
+        if rc != 0:
+            msg = self.abi.last_error(self._ctx)
+            raise EpochError(f"rc={rc}: {msg.decode() if msg else ''}")
+
+    def close(self):
+        if self._ctx:
+            self.abi.destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- setters ----------------------------------------------------------
+    def set_grid(self, n_local, d, grid_min_local, min_local, max_local, min_global, max_global,
+                 n_global=None, n_global_min=None, cpml_thickness=0):
+        nd = self.ndims
+        self.n = tuple(int(x) for x in n_local[:nd])
+        self.d = tuple(float(x) for x in d[:nd])
+        n_global = n_global if n_global is not None else n_local
+        n_global_min = n_global_min if n_global_min is not None else [1] * nd
+        self._ck(self.abi.set_grid(self._ctx, _i32(_pad3(n_local, 1)), _i32(_pad3(n_global, 1)),
+                                   _i32(_pad3(n_global_min, 1)), _f64(_pad3(d, 1.0)),
+                                   _f64(_pad3(grid_min_local, 0.0)), _f64(_pad3(min_local, 0.0)),
+                                   _f64(_pad3(max_local, 0.0)), _f64(_pad3(min_global, 0.0)),
+                                   _f64(_pad3(max_global, 0.0)), cpml_thickness))
+        self.field_shape = tuple(x + 2 * self.ng for x in self.n)  # Fortran order (x fastest)
+
+    def set_time(self, dt, time, step=0):
+        self._ck(self.abi.set_time(self._ctx, dt, time, step))
+
+    def set_field_bcs(self, bcs):
+        bcs = [BC[b] if isinstance(b, str) else int(b) for b in bcs]
+        self._ck(self.abi.set_field_bcs(self._ctx, _i32((bcs + [1] * 6)[:6])))
+
+    def set_solver(self, field_order=2, maxwell_solver=0, coeffs=None):
+        self._ck(self.abi.set_solver(self._ctx, field_order, maxwell_solver,
+                                     _f64(coeffs if coeffs is not None else [0.0] * 15)))
+
+    def set_species(self, isp, charge, mass, weight=1.0, immobile=False, zero_current=False,
+                    species_type=0, bcs=None):
+        nd = self.ndims
+        bcs = bcs if bcs is not None else ["periodic"] * (2 * nd)
+        bcs = [BC[b] if isinstance(b, str) else int(b) for b in bcs]
+        self._ck(self.abi.set_species(self._ctx, isp, charge, mass, weight, int(immobile),
+                                      int(zero_current), species_type, _i32((bcs + [1] * 6)[:6])))
+        self.nspecies = max(self.nspecies, isp + 1)
+
+    # -- particles (partlist wire format: pos(ndims), p(3), weight) ---------
+    def upload_particles(self, isp, packed, append=False):
+        packed = np.ascontiguousarray(packed, dtype=np.float64).reshape(-1, self.nvar)
+        fn = self.abi.append_particles if append else self.abi.upload_particles
+        self._ck(fn(self._ctx, isp, packed.shape[0], packed.ctypes.data_as(C.c_void_p), self.nvar))
+
+    def particle_count(self, isp):
+        n = C.c_int64()
+        self._ck(self.abi.particle_count(self._ctx, isp, C.byref(n)))
+        return n.value
+
+    def download_particles(self, isp):
+        n = self.particle_count(isp)
+        out = np.empty((n, self.nvar), dtype=np.float64)
+        got = C.c_int64()
+        self._ck(self.abi.download_particles(self._ctx, isp, 0, n, out.ctypes.data_as(C.c_void_p),
+                                             self.nvar, C.byref(got)))
+        return out[:got.value]
+
+    # -- fields (Fortran-shaped with ghosts; returned as numpy arrays indexed
+    #    [k, j, i] i.e. C order of the column-major reference array) ---------
+    def _np_shape(self):
+        return tuple(reversed(self.field_shape))
+
+    def upload_fields(self, **fields):
+        ptrs = []
+        keep = []
+        for name in FIELD_NAMES:
+            a = fields.get(name)
+            if a is None:
+                ptrs.append(None)
+            else:
+                a = np.ascontiguousarray(a, dtype=np.float64)
+                assert a.size == int(np.prod(self.field_shape)), (name, a.shape, self.field_shape)
+                keep.append(a)
+                ptrs.append(a.ctypes.data_as(C.c_void_p))
+        self._ck(self.abi.upload_fields(self._ctx, *ptrs))
+
+    def download_fields(self, names=FIELD_NAMES):
+        out = {}
+        ptrs = []
+        for name in FIELD_NAMES:
+            if name in names:
+                out[name] = np.empty(self._np_shape(), dtype=np.float64)
+                ptrs.append(out[name].ctypes.data_as(C.c_void_p))
+            else:
+                ptrs.append(None)
+        self._ck(self.abi.download_fields(self._ctx, *ptrs))
+        return out
+
+    def interior(self, a):
+        ng = self.ng
+        return a[tuple(slice(ng, -ng) for _ in range(self.ndims))]
+
+    # -- lasers -------------------------------------------------------------
+    def set_laser(self, boundary, lid, amp, pol_angle=0.0, t_start=0.0, t_end=1e300,
+                  profile=None, phase=None):
+        keep = []
+
+        def ptr(a):
+            if a is None:
+                return None
+            a = np.ascontiguousarray(a, dtype=np.float64)
+            keep.append(a)
+            return a.ctypes.data_as(C.c_void_p)
+        self._ck(self.abi.set_laser(self._ctx, boundary, lid, amp, pol_angle, t_start, t_end,
+                                    ptr(profile), ptr(phase)))
+
+    def set_laser_step(self, boundary, lid, t_env, integral_phase):
+        self._ck(self.abi.set_laser_step(self._ctx, boundary, lid, t_env, integral_phase))
+
+    # -- the reference's entry points -----------------------------------------
+    def update_eb_fields_half(self):
+        self._ck(self.abi.update_eb_fields_half(self._ctx))
+
+    def push_particles(self):
+        self._ck(self.abi.push_particles(self._ctx))
+
+    def current_finish(self):
+        self._ck(self.abi.current_finish(self._ctx))
+
+    def update_eb_fields_final(self):
+        self._ck(self.abi.update_eb_fields_final(self._ctx))
+
+    def particle_bcs(self):
+        self._ck(self.abi.particle_bcs(self._ctx))
+
+    def efield_bcs(self):
+        self._ck(self.abi.efield_bcs(self._ctx))
+
+    def bfield_final_bcs(self):
+        self._ck(self.abi.bfield_final_bcs(self._ctx))
+
+    # -- diagnostics ----------------------------------------------------------
+    def energy(self):
+        fe = C.c_double()
+        ps = (C.c_double * max(1, self.nspecies))()
+        self._ck(self.abi.energy(self._ctx, C.byref(fe), ps))
+        return fe.value, list(ps)[:self.nspecies]
+
+    def charge_residual(self):
+        a, b = C.c_double(), C.c_double()
+        self._ck(self.abi.charge_residual(self._ctx, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def set_option(self, key, value):
+        self._ck(self.abi.set_option(self._ctx, key.encode(), str(value).encode()))
+
+    def sync(self):
+        self._ck(self.abi.sync(self._ctx))
+
+    def timer(self, phase, reset=False):
+        ms, n = C.c_double(), C.c_int64()
+        self._ck(self.abi.timer(self._ctx, phase.encode(), int(reset), C.byref(ms), C.byref(n)))
+        return ms.value, n.value

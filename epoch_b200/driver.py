@@ -1,0 +1,232 @@
+"""Mirror of PROGRAM pic's control flow around the hot path.
+
+Reproduces, for a single deck-like description, what the Fortran driver does
+between `read_deck` and the end of the main loop as far as the hot path is
+concerned: grid setup (housekeeping/setup.F90:174-231), time-step selection
+(`set_dt`, setup.F90:700-767; 1D :566-620; 2D analogue), the initial boundary
+calls (epoch3d.F90:141-158), and the per-step sequence with its time
+bookkeeping (epoch3d.F90:184-249).  The arithmetic of the
+hot path itself is behind `PicContext` (C ABI); this file is host logic only and
+is shared by the tests (driving oracle and CUDA library alike) and by bench.py.
+"""
+import math
+
+import numpy as np
+
+from .context import BC, PicContext, SHAPES, PNG
+from . import decomp
+
+# constants.F90:144-151
+PI = 3.141592653589793238462643383279503
+Q0 = 1.602176565e-19
+M0 = 9.10938291e-31
+C = 2.99792458e8
+KB = 1.3806488e-23
+EPS0 = 8.854187817620389850536563031710750e-12
+C_TINY = 1e-300
+
+
+def gauss(x, x0, w):
+    """evaluator_blocks.F90:1009-1012"""
+    return np.exp(-((x - x0) / w) ** 2)
+
+
+class LaserSpec:
+    """deck `laser` block (deck_laser_block.f90): amplitude, omega, envelope."""
+
+    def __init__(self, boundary, lid=1, intensity_w_cm2=None, amp=None, lambda_=None, omega=None,
+                 pol_angle=0.0, t_start=0.0, t_end=None, t_profile=None, profile=None, phase=None):
+        self.boundary = boundary  # 1..6
+        self.id = lid
+        if amp is None:
+            # deck_laser_block.f90:135-139
+            amp = math.sqrt(intensity_w_cm2 / (C * EPS0 / 2.0)) * 100.0
+        self.amp = amp
+        self.omega = omega if omega is not None else 2.0 * PI * C / lambda_  # laser.f90:325-328
+        self.pol_angle = pol_angle
+        self.t_start = t_start
+        self.t_end = t_end
+        self.t_profile = t_profile  # callable(time) or None (=1)
+        self.profile = profile      # callable(*tangential coordinate arrays) or None
+        self.phase = phase
+
+
+class SpeciesSpec:
+    def __init__(self, name, charge, mass, bcs=None, zero_current=False, immobile=False,
+                 density=0.0, temperature=(0.0, 0.0, 0.0)):
+        self.name, self.charge, self.mass = name, charge, mass
+        self.bcs, self.zero_current, self.immobile = bcs, zero_current, immobile
+        self.density = density            # for set_plasma_frequency_dt only
+        self.temperature = temperature
+
+
+class Simulation:
+    def __init__(self, ndims, n_global, mins, maxs, shape="triangle", bc_field=None, species=(),
+                 lasers=(), dt_multiplier=0.95, field_order=2, t_end=None, abi=None, device=0,
+                 rank=0, nproc=1, nprocdir=(1, 1, 1), nccl_id=None, dt=None):
+        self.ndims = nd = ndims
+        self.shape = SHAPES[shape] if isinstance(shape, str) else shape
+        self.n_global = tuple(n_global[:nd])
+        self.mins, self.maxs = tuple(mins[:nd]), tuple(maxs[:nd])
+        self.bc_field = [BC[b] if isinstance(b, str) else b for b in
+                         (bc_field or ["periodic"] * (2 * nd))]
+        self.species, self.lasers = list(species), list(lasers)
+        self.field_order = field_order
+        self.t_end = t_end
+        self.rank, self.nproc = rank, nproc
+        self.nprocdir = tuple(nprocdir)
+        self.coords = decomp.rank_to_coords(rank, self.nprocdir)
+        # setup_grid: setup.F90:174-231
+        self.length = [self.maxs[d] - self.mins[d] for d in range(nd)]
+        self.d = [self.length[d] / float(self.n_global[d]) for d in range(nd)]
+        self.grid_min = [self.mins[d] + self.d[d] / 2.0 for d in range(nd)]
+        # split_domain: near-even split (mpi_routines.F90:44-270)
+        self.cell_min, self.cell_max = [], []
+        for d in range(nd):
+            lo, hi = decomp.cell_range(self.n_global[d], self.nprocdir[d], self.coords[d])
+            self.cell_min.append(lo)
+            self.cell_max.append(hi)
+        self.n_local = [self.cell_max[d] - self.cell_min[d] + 1 for d in range(nd)]
+        # setup_grid_x: utilities.f90:343-373 (x_global(ix) = x_grid_min + (ix-1)*dx)
+        self.grid_min_local = [self.grid_min[d] + (self.cell_min[d] - 1) * self.d[d] for d in range(nd)]
+        grid_max_local = [self.grid_min[d] + (self.cell_max[d] - 1) * self.d[d] for d in range(nd)]
+        self.min_local = [self.grid_min_local[d] + (0 - 0.5) * self.d[d] for d in range(nd)]
+        self.max_local = [grid_max_local[d] - (0 - 0.5) * self.d[d] for d in range(nd)]
+
+        self.ctx = PicContext(nd, self.shape, abi=abi, device=device, rank=rank, nproc=nproc,
+                              nprocdir=self.nprocdir, coords=self.coords, nccl_id=nccl_id)
+        self.ctx.set_grid(self.n_local, self.d, self.grid_min_local, self.min_local, self.max_local,
+                          self.mins, self.maxs, n_global=self.n_global, n_global_min=self.cell_min)
+        self.ctx.set_field_bcs(self.bc_field)
+        self.ctx.set_solver(field_order, 0)
+        for i, sp in enumerate(self.species):
+            self.ctx.set_species(i, sp.charge, sp.mass, 1.0, sp.immobile, sp.zero_current, 0, sp.bcs)
+        self.dt_multiplier = dt_multiplier
+        self.dt = dt if dt is not None else self.set_dt()
+        self.time = 0.0
+        self.step = 0
+        self._setup_lasers()
+        self._started = False
+
+    # -- set_dt -----------------------------------------------------------------
+    def set_dt(self):
+        nd, d = self.ndims, self.d
+        cfl = {2: 1.0, 4: 6.0 / 7.0, 6: 120.0 / 149.0}[self.field_order]  # fields.f90:34-49
+        if nd == 1:
+            solver = d[0] / C
+        elif nd == 2:
+            solver = d[0] * d[1] / math.sqrt(d[0] ** 2 + d[1] ** 2) / C
+        else:
+            solver = d[0] * d[1] * d[2] / math.sqrt((d[0] * d[1]) ** 2 + (d[1] * d[2]) ** 2
+                                                   + (d[2] * d[0]) ** 2) / C
+        dt = cfl * solver
+        bcs = [self._norm_field_bc(b) for b in self.bc_field]
+        any_open = any(b in (BC["simple_laser"], BC["simple_outflow"]) for b in bcs)
+        if any_open:
+            dt = min(dt, solver)
+        # set_plasma_frequency_dt (setup.F90:640-696; 1D :514-563)
+        min_dt = 1000000.0
+        k_max = 2.0 * PI / d[0]
+        for sp in self.species:
+            omega2 = Q0 ** 2 / sp.mass / EPS0 * sp.density + 3.0 * k_max ** 2 * KB / sp.mass * max(sp.temperature)
+            if omega2 > C_TINY:
+                min_dt = min(min_dt, 2.0 * PI / math.sqrt(omega2))
+        dt_plasma = min_dt / 2.0
+        if dt_plasma > C_TINY:
+            dt = min(dt, dt_plasma)
+        # set_laser_dt (laser.f90:452-505)
+        if self.lasers:
+            dt_laser = min(2.0 * PI / L.omega for L in self.lasers) / 2.0
+            if dt_laser > C_TINY:
+                dt = min(dt, dt_laser)
+        return self.dt_multiplier * dt
+
+    @staticmethod
+    def _norm_field_bc(b):
+        # setup_boundaries, boundary.F90:45-58
+        if b == BC["other"] or b == BC["reflect"]:
+            return BC["clamp"]
+        if b == BC["open"]:
+            return BC["simple_outflow"]
+        return b
+
+    # -- lasers -----------------------------------------------------------------
+    def _tangential_coords(self, boundary):
+        """cell-centre coordinates over indices 0..n of the tangential dims, as
+        evaluated by laser_update_profile (laser.f90:232-268) on this rank."""
+        a = (boundary - 1) // 2
+        axes = [d for d in range(self.ndims) if d != a]
+        lines = [self.grid_min_local[d] + (np.arange(0, self.n_local[d] + 1) - 1) * self.d[d] for d in axes]
+        if not lines:
+            return []
+        if len(lines) == 1:
+            return [lines[0]]
+        g0, g1 = np.meshgrid(lines[0], lines[1], indexing="ij")  # [i, j]
+        return [g0, g1]
+
+    def _setup_lasers(self):
+        for L in self.lasers:
+            a = (L.boundary - 1) // 2
+            on_bnd = self.coords[a] == (0 if (L.boundary - 1) % 2 == 0 else self.nprocdir[a] - 1)
+            L.active = on_bnd
+            if not on_bnd:
+                continue
+            coords = self._tangential_coords(L.boundary)
+
+            def plane(fn):
+                if fn is None:
+                    return None
+                v = np.asarray(fn(*coords), dtype=np.float64) if coords else np.asarray([fn()], dtype=np.float64)
+                if coords:
+                    v = np.broadcast_to(v, coords[0].shape)
+                # storage: lower axis fastest
+                return np.ascontiguousarray(v.T if v.ndim == 2 else v)
+            t_end = L.t_end if L.t_end is not None else (self.t_end if self.t_end is not None else 1e300)
+            self.ctx.set_laser(L.boundary, L.id, L.amp, L.pol_angle, L.t_start, t_end,
+                               plane(L.profile), plane(L.phase))
+
+    def _laser_step(self):
+        # update_laser_omegas + laser_time_profile (laser.f90:207-226,334-346)
+        for L in self.lasers:
+            if not L.active:
+                continue
+            t_env = 1.0 if L.t_profile is None else float(L.t_profile(self.time))
+            self.ctx.set_laser_step(L.boundary, L.id, t_env, L.omega * self.time)
+
+    # -- PROGRAM pic ------------------------------------------------------------
+    def start(self):
+        """epoch3d.F90:141-158: particle_bcs; efield_bcs; half-dt bfield_final_bcs."""
+        ctx = self.ctx
+        ctx.set_time(self.dt, self.time, self.step)
+        ctx.particle_bcs()
+        ctx.efield_bcs()
+        dt_store = self.dt
+        self.time = self.time + dt_store / 2.0
+        ctx.set_time(dt_store / 2.0, self.time, self.step)
+        self._laser_step()
+        ctx.bfield_final_bcs()
+        ctx.set_time(dt_store, self.time, self.step)
+        self._started = True
+
+    def finished(self):
+        return self.t_end is not None and self.time >= self.t_end
+
+    def step_once(self, output=None, push=True):
+        """One iteration of the main DO loop (epoch3d.F90:184-249).  `output` is
+        called where output_routines is (time = (n+1)*dt, fields at n+1/2)."""
+        if not self._started:
+            self.start()
+        ctx = self.ctx
+        ctx.set_time(self.dt, self.time, self.step)
+        ctx.update_eb_fields_half()
+        if push and self.species:
+            ctx.push_particles()
+            ctx.current_finish()
+        self.step += 1
+        self.time = self.time + self.dt / 2.0
+        if output is not None:
+            output(self)
+        self.time = self.time + self.dt / 2.0
+        ctx.set_time(self.dt, self.time, self.step)
+        self._laser_step()
+        ctx.update_eb_fields_final()

@@ -1,0 +1,187 @@
+/*
+ * epoch_b200.h -- C ABI of the B200-native EPOCH PIC hot path.
+ *
+ * This is the drop-in boundary.  EPOCH (Fortran 90 + MPI) has no FFI today: the
+ * "interface" of its per-timestep core is four argument-less module procedures
+ * acting on MODULE shared_data globals, called from PROGRAM pic:
+ *
+ *     update_eb_fields_half    epoch3d/src/fields.f90:819    (call epoch3d.F90:208)
+ *     push_particles           epoch3d/src/particles.F90:28  (call epoch3d.F90:213)
+ *     current_finish           epoch3d/src/housekeeping/current_smooth.F90:29 (call epoch3d.F90:235)
+ *     update_eb_fields_final   epoch3d/src/fields.f90:851    (call epoch3d.F90:246)
+ *
+ * Each entry below names the reference item it replaces.  The Fortran side binds
+ * these with ISO_C_BINDING (see fortran/epoch_b200_iface.F90).
+ *
+ * Conventions
+ *  - every function returns 0 on success, <0 on error (EB200_E_*); the message
+ *    is available from eb200_last_error().  Nothing throws across the ABI.
+ *  - all reals are IEEE fp64 (EPOCH's REAL(num), constants.F90:24), SI units.
+ *  - grid arrays are Fortran shaped *including ghosts*: (1-ng:nx+ng [,1-ng:ny+ng
+ *    [,1-ng:nz+ng]]), column major (x fastest); ng = 4/5/6 for tophat/triangle/
+ *    bspline3 (constants.F90:472-492).  Dimensions that do not exist in a 1D/2D
+ *    build are simply absent from the array (as in epoch1d / epoch2d).
+ *  - packed particles use the partlist wire format (housekeeping/partlist.F90:
+ *    411-553): nvar consecutive doubles per particle = pos(ndims), p(3), weight.
+ *  - one context per MPI rank == one GPU.  A context is thread-compatible, not
+ *    thread-safe.  Hot entries enqueue work on a context-private CUDA stream and
+ *    may return before completion; eb200_sync()/download/energy synchronise.
+ *
+ * The same declarations are re-used (with prefix orc_) by the CPU oracle in
+ * oracle/, which is TEST INFRASTRUCTURE ONLY.
+ */
+#ifndef EPOCH_B200_H
+#define EPOCH_B200_H
+
+#include <stdint.h>
+
+#ifndef EB200_NAME
+#define EB200_NAME(x) eb200_##x
+#endif
+#ifndef EB200_CTX
+#define EB200_CTX eb200_ctx
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct EB200_CTX EB200_CTX;
+
+/* error classes */
+enum {
+  EB200_OK = 0,
+  EB200_E_ARG = -1,      /* bad argument / unsupported option          */
+  EB200_E_STATE = -2,    /* call sequence error (grid not set, ...)     */
+  EB200_E_CUDA = -3,     /* CUDA runtime failure                        */
+  EB200_E_NCCL = -4,     /* NCCL failure / NCCL not loadable            */
+  EB200_E_NOMEM = -5,    /* out of device (or host) memory              */
+  EB200_E_UNSUPPORTED = -6 /* reference feature outside the hot path    */
+};
+
+/* particle shapes: compile-time #ifdefs in the reference (Makefile:186-207) */
+enum { EB200_SHAPE_TOPHAT = 0, EB200_SHAPE_TRIANGLE = 1, EB200_SHAPE_BSPLINE3 = 2 };
+
+/* boundary codes, identical to constants.F90:56-71 */
+enum {
+  EB200_BC_PERIODIC = 1, EB200_BC_OTHER = 2, EB200_BC_SIMPLE_LASER = 3,
+  EB200_BC_SIMPLE_OUTFLOW = 4, EB200_BC_OPEN = 5, EB200_BC_DUMP = 6,
+  EB200_BC_ZERO_GRADIENT = 7, EB200_BC_CLAMP = 8, EB200_BC_REFLECT = 9,
+  EB200_BC_CONDUCT = 10, EB200_BC_THERMAL = 11, EB200_BC_CPML_LASER = 12,
+  EB200_BC_CPML_OUTFLOW = 13, EB200_BC_MIXED = 14, EB200_BC_HEAT_BATH = 15
+};
+/* boundary location codes 1..6 = x_min,x_max,y_min,y_max,z_min,z_max (constants.F90:74-79) */
+
+/* ---- lifecycle -------------------------------------------------------------
+ * Replaces the allocation half of mpi_initialise (housekeeping/mpi_routines.F90:
+ * 393-593) and setup_communicator (:274-389).  nprocdir/coords describe the
+ * Cartesian process grid (x,y,z); nccl_unique_id is 128 bytes obtained from
+ * eb200_nccl_unique_id() on rank 0 and broadcast by the host (MPI_BCAST); it may
+ * be NULL when nproc == 1. */
+int32_t EB200_NAME(create)(EB200_CTX** out, int32_t ndims, int32_t shape,
+                           int32_t device_ordinal, int32_t rank, int32_t nproc,
+                           const int32_t nprocdir[3], const int32_t coords[3],
+                           const void* nccl_unique_id);
+int32_t EB200_NAME(nccl_unique_id)(void* out128);
+int32_t EB200_NAME(destroy)(EB200_CTX*);
+
+/* ---- grid / time -----------------------------------------------------------
+ * Mirrors the scalars of shared_data.F90:453,508-523 set by setup_grid
+ * (housekeeping/setup.F90:174-231) and setup_grid_x (utilities.f90:343-373).
+ * n_global_min is the 1-based global index of local cell 1.  grid_min_local is
+ * the centre of local cell 1 (x_grid_min_local); min_local/max_local are the
+ * particle-ownership bounds (x_min_local, x_max_local); min_global/max_global
+ * are x_min/x_max of the deck.  Call again after a re-decomposition. */
+int32_t EB200_NAME(set_grid)(EB200_CTX*, const int32_t n_local[3], const int32_t n_global[3],
+                             const int32_t n_global_min[3], const double d[3],
+                             const double grid_min_local[3], const double min_local[3],
+                             const double max_local[3], const double min_global[3],
+                             const double max_global[3], int32_t cpml_thickness);
+/* dt, time and step as the reference's globals hold them at the next hot call
+ * (epoch3d.F90:153-159,241-246). */
+int32_t EB200_NAME(set_time)(EB200_CTX*, double dt, double time, int32_t step);
+/* bc_field(1:6) after setup_boundaries normalisation is applied internally
+ * (boundary.F90:30-75). */
+int32_t EB200_NAME(set_field_bcs)(EB200_CTX*, const int32_t bc_field[6]);
+/* set_field_order / set_maxwell_solver (fields.f90:34-179).  coeffs = alphax,
+ * alphay,alphaz, betaxy,betaxz,betayx,betayz,betazx,betazy, gammax,gammay,gammaz,
+ * deltax,deltay,deltaz; ignored for maxwell_solver == 0 (Yee). */
+int32_t EB200_NAME(set_solver)(EB200_CTX*, int32_t field_order, int32_t maxwell_solver,
+                               const double coeffs[15]);
+
+/* ---- species / particles ---------------------------------------------------
+ * TYPE particle_species scalars used by the push (shared_data.F90:184-263). */
+int32_t EB200_NAME(set_species)(EB200_CTX*, int32_t ispecies, double charge, double mass,
+                                double species_weight, int32_t immobile, int32_t zero_current,
+                                int32_t species_type, const int32_t bc_particle[6]);
+/* list -> device import (replaces walking attached_list; wire format of
+ * pack_particle, partlist.F90:411-473).  upload replaces the species' particles,
+ * append adds to them (chunked uploads, injectors, window insert_particles). */
+int32_t EB200_NAME(upload_particles)(EB200_CTX*, int32_t ispecies, int64_t n,
+                                     const double* packed, int32_t nvar);
+int32_t EB200_NAME(append_particles)(EB200_CTX*, int32_t ispecies, int64_t n,
+                                     const double* packed, int32_t nvar);
+int32_t EB200_NAME(particle_count)(EB200_CTX*, int32_t ispecies, int64_t* n);
+/* device -> list export (unpack_particle, partlist.F90:477-553); first = offset
+ * of the first particle to copy so the host can stream in chunks. */
+int32_t EB200_NAME(download_particles)(EB200_CTX*, int32_t ispecies, int64_t first,
+                                       int64_t capacity, double* packed, int32_t nvar,
+                                       int64_t* n_out);
+
+/* ---- fields ----------------------------------------------------------------
+ * ex..jz of shared_data.F90:461 (allocated mpi_routines.F90:531-540).  NULL
+ * pointers are skipped. */
+int32_t EB200_NAME(upload_fields)(EB200_CTX*, const double* ex, const double* ey, const double* ez,
+                                  const double* bx, const double* by, const double* bz,
+                                  const double* jx, const double* jy, const double* jz);
+int32_t EB200_NAME(download_fields)(EB200_CTX*, double* ex, double* ey, double* ez,
+                                    double* bx, double* by, double* bz,
+                                    double* jx, double* jy, double* jz);
+
+/* ---- laser / outflow boundaries ----------------------------------------------
+ * TYPE laser_block (shared_data.F90) as used by outflow_bcs_* (laser.f90:509-973).
+ * profile/phase are the boundary planes over indices 0..n of the tangential
+ * dimensions, x-fastest, i.e. (ny+1)*(nz+1) doubles for an x boundary in 3D,
+ * (ny+1) in 2D, 1 in 1D; NULL = 1.0 / 0.0.  The host evaluates the deck's time
+ * profile and phase integral each step (laser.f90:207-226,334-346) and passes
+ * them through set_laser_step. */
+int32_t EB200_NAME(set_laser)(EB200_CTX*, int32_t boundary, int32_t id, double amp,
+                              double pol_angle, double t_start, double t_end,
+                              const double* profile, const double* phase);
+int32_t EB200_NAME(set_laser_step)(EB200_CTX*, int32_t boundary, int32_t id, double t_env,
+                                   double integral_phase);
+
+/* ---- the four hot entries --------------------------------------------------*/
+int32_t EB200_NAME(update_eb_fields_half)(EB200_CTX*);   /* fields.f90:819-847   */
+int32_t EB200_NAME(push_particles)(EB200_CTX*);          /* particles.F90:28-614 incl. particle_bcs */
+int32_t EB200_NAME(current_finish)(EB200_CTX*);          /* current_smooth.F90:29-45 */
+int32_t EB200_NAME(update_eb_fields_final)(EB200_CTX*);  /* fields.f90:851-872   */
+/* initial boundary calls of PROGRAM pic (epoch3d.F90:141-142,157) */
+int32_t EB200_NAME(particle_bcs)(EB200_CTX*);            /* boundary.F90:1316    */
+int32_t EB200_NAME(efield_bcs)(EB200_CTX*);              /* boundary.F90:1148    */
+int32_t EB200_NAME(bfield_final_bcs)(EB200_CTX*);        /* boundary.F90:1267    */
+
+/* ---- diagnostics -----------------------------------------------------------
+ * calc_total_energy_sum (io/calc_df.F90:1190-1288): local (this rank) sums; the
+ * host MPI_REDUCEs them as the reference does. */
+int32_t EB200_NAME(energy)(EB200_CTX*, double* field_energy,
+                           double* particle_energy_per_species);
+/* max |div E - rho/eps0| and max |rho/eps0| over interior cells, rho deposited
+ * with the normalised weights of calc_charge_density (calc_df.F90:439-519). */
+int32_t EB200_NAME(charge_residual)(EB200_CTX*, double* max_abs_residual,
+                                    double* max_abs_rho_over_eps0);
+/* options: "deterministic_deposit"="0|1", "push_kernel"="auto|baseline|tiled",
+ * "sort_every"="<n>" */
+int32_t EB200_NAME(set_option)(EB200_CTX*, const char* key, const char* value);
+int32_t EB200_NAME(sync)(EB200_CTX*);
+/* milliseconds of device time spent in the named phase since the last call with
+ * reset != 0 ("push", "sort", "fields", "halo", "bcs"); CUDA-event based. */
+int32_t EB200_NAME(timer)(EB200_CTX*, const char* phase, int32_t reset, double* ms,
+                          int64_t* launches);
+const char* EB200_NAME(last_error)(EB200_CTX*);
+const char* EB200_NAME(version)(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EPOCH_B200_H */

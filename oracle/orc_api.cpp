@@ -1,0 +1,264 @@
+// oracle/orc_api.cpp -- CPU ORACLE (test infrastructure only): the same C ABI as
+// include/epoch_b200.h with prefix orc_, so the parity tests drive oracle and
+// product through one harness.  Single rank only (nproc must be 1 per context;
+// multi-rank tests exchange halos themselves through orc_field_ptr).
+#define EB200_NAME(x) orc_##x
+#define EB200_CTX orc_ctx
+#include "../include/epoch_b200.h"
+#include "orc_state.hpp"
+#include <algorithm>
+#include <new>
+
+struct orc_ctx { orc::State s; };
+using namespace orc;
+
+static thread_local std::string g_err;
+static int32_t fail(orc_ctx* c, int32_t code, const std::string& m) {
+  if (c) c->s.err = m;
+  g_err = m;
+  return code;
+}
+
+extern "C" {
+
+int32_t orc_create(orc_ctx** out, int32_t ndims, int32_t shape, int32_t, int32_t rank,
+                   int32_t nproc, const int32_t nprocdir[3], const int32_t coords[3], const void*) {
+  if (!out || ndims < 1 || ndims > 3 || shape < 0 || shape > 2) return fail(nullptr, EB200_E_ARG, "bad ndims/shape");
+  orc_ctx* c = new (std::nothrow) orc_ctx();
+  if (!c) return EB200_E_NOMEM;
+  State& s = c->s;
+  s.ndims = ndims; s.shape = shape; s.rank = rank; s.nproc = nproc;
+  for (int d = 0; d < 3; ++d) {
+    s.nprocdir[d] = nprocdir ? nprocdir[d] : 1;
+    s.coords[d] = coords ? coords[d] : 0;
+    s.min_bnd[d] = s.coords[d] == 0;
+    s.max_bnd[d] = s.coords[d] == s.nprocdir[d] - 1;
+  }
+  // constants.F90:472-492
+  if (shape == 2) { s.sf_min = -2; s.sf_max = 2; s.png = 4; }
+  else if (shape == 0) { s.sf_min = 0; s.sf_max = 1; s.png = 2; }
+  else { s.sf_min = -1; s.sf_max = 1; s.png = 3; }
+  s.ng = s.png + 2;
+  *out = c;
+  return 0;
+}
+int32_t orc_nccl_unique_id(void* out128) { if (out128) std::memset(out128, 0, 128); return 0; }
+int32_t orc_destroy(orc_ctx* c) { delete c; return 0; }
+
+int32_t orc_set_grid(orc_ctx* c, const int32_t n_local[3], const int32_t n_global[3],
+                     const int32_t n_global_min[3], const double d[3], const double grid_min_local[3],
+                     const double min_local[3], const double max_local[3], const double min_global[3],
+                     const double max_global[3], int32_t cpml_thickness) {
+  if (!c) return EB200_E_ARG;
+  State& s = c->s;
+  if (cpml_thickness != 0) return fail(c, EB200_E_UNSUPPORTED, "CPML not supported");
+  int64_t stride = 1;
+  for (int k = 0; k < 3; ++k) {
+    const bool ex = k < s.ndims;
+    s.n[k] = ex ? n_local[k] : 1;
+    s.nglob[k] = ex ? n_global[k] : 1;
+    s.nglob_min[k] = ex ? n_global_min[k] : 1;
+    s.ngd[k] = ex ? s.ng : 0;
+    s.d[k] = ex ? d[k] : 1.0;
+    s.grid_min_local[k] = ex ? grid_min_local[k] : 0.0;
+    s.min_local[k] = ex ? min_local[k] : 0.0;
+    s.max_local[k] = ex ? max_local[k] : 0.0;
+    s.gmin[k] = ex ? min_global[k] : 0.0;
+    s.gmax[k] = ex ? max_global[k] : 0.0;
+    if (s.n[k] < 1) return fail(c, EB200_E_ARG, "n_local < 1");
+    s.st[k] = stride;
+    stride *= (int64_t)(s.n[k] + 2 * s.ngd[k]);
+  }
+  s.total = stride;
+  s.cpml_thickness = cpml_thickness;
+  for (int f = 0; f < NFIELD; ++f) s.f[f].assign((size_t)s.total, 0.0);
+  s.grid_set = true;
+  return 0;
+}
+
+int32_t orc_set_time(orc_ctx* c, double dt, double time, int32_t step) {
+  if (!c) return EB200_E_ARG;
+  c->s.dt = dt; c->s.time = time; c->s.step = step;
+  return 0;
+}
+
+int32_t orc_set_field_bcs(orc_ctx* c, const int32_t bc_field[6]) {
+  if (!c) return EB200_E_ARG;
+  State& s = c->s;
+  // setup_boundaries, boundary.F90:30-59
+  for (int i = 0; i < 6; ++i) {
+    int bc = i < 2 * s.ndims ? bc_field[i] : BC_PERIODIC;
+    s.add_laser[i] = false;
+    if (bc == BC_OTHER) bc = BC_CLAMP;
+    if (bc == BC_CPML_LASER || bc == BC_CPML_OUTFLOW) return fail(c, EB200_E_UNSUPPORTED, "CPML not supported");
+    if (bc == BC_SIMPLE_LASER) s.add_laser[i] = true;
+    if (bc == BC_REFLECT) bc = BC_CLAMP;
+    if (bc == BC_OPEN) bc = BC_SIMPLE_OUTFLOW;
+    s.bc_field[i] = bc;
+  }
+  return 0;
+}
+
+int32_t orc_set_solver(orc_ctx* c, int32_t field_order, int32_t maxwell_solver, const double coeffs[15]) {
+  if (!c) return EB200_E_ARG;
+  if (field_order != 2 && field_order != 4 && field_order != 6) return fail(c, EB200_E_ARG, "field_order");
+  if (maxwell_solver != 0) return fail(c, EB200_E_UNSUPPORTED, "only the Yee solver is supported");
+  c->s.field_order = field_order; c->s.maxwell_solver = maxwell_solver;
+  if (coeffs) std::copy(coeffs, coeffs + 15, c->s.coeffs);
+  return 0;
+}
+
+int32_t orc_set_species(orc_ctx* c, int32_t isp, double charge, double mass, double weight,
+                        int32_t immobile, int32_t zero_current, int32_t species_type,
+                        const int32_t bc_particle[6]) {
+  if (!c || isp < 0 || isp > 1023) return EB200_E_ARG;
+  State& s = c->s;
+  if ((size_t)isp >= s.species.size()) s.species.resize(isp + 1);
+  Species& sp = s.species[isp];
+  sp.defined = true; sp.charge = charge; sp.mass = mass; sp.weight = weight;
+  sp.immobile = immobile; sp.zero_current = zero_current; sp.species_type = species_type;
+  for (int i = 0; i < 6; ++i) {
+    int bc = (bc_particle && i < 2 * s.ndims) ? bc_particle[i] : BC_PERIODIC;
+    // setup_particle_boundary, boundary.F90:98-140
+    if (bc == BC_OTHER || bc == BC_CONDUCT) bc = BC_REFLECT;
+    if (bc == BC_SIMPLE_LASER || bc == BC_SIMPLE_OUTFLOW || bc == BC_CPML_LASER || bc == BC_CPML_OUTFLOW) bc = BC_OPEN;
+    if (bc == BC_THERMAL || bc == BC_HEAT_BATH) return fail(c, EB200_E_UNSUPPORTED, "thermal particle BCs not supported");
+    if (bc != BC_PERIODIC && bc != BC_REFLECT && bc != BC_OPEN) return fail(c, EB200_E_ARG, "bad particle BC");
+    sp.bc[i] = bc;
+  }
+  for (const Species& o : s.species)
+    if (o.defined)
+      for (int i = 0; i < 6; ++i)
+        if (o.bc[i] != sp.bc[i]) return fail(c, EB200_E_UNSUPPORTED, "mixed per-species particle BCs not supported");
+  return 0;
+}
+
+static int32_t add_particles(orc_ctx* c, int32_t isp, int64_t n, const double* packed, int32_t nvar, bool replace) {
+  if (!c || isp < 0 || (size_t)isp >= c->s.species.size() || !c->s.species[isp].defined) return fail(c, EB200_E_ARG, "species not set");
+  State& s = c->s;
+  if (nvar != s.ndims + 4) return fail(c, EB200_E_ARG, "nvar must be ndims+4");
+  if (n < 0 || (n > 0 && !packed)) return EB200_E_ARG;
+  Species& sp = s.species[isp];
+  if (replace) { for (int d = 0; d < 3; ++d) { sp.pos[d].clear(); sp.p[d].clear(); } sp.w.clear(); }
+  for (int64_t i = 0; i < n; ++i) {
+    const double* q = packed + i * nvar;
+    for (int d = 0; d < s.ndims; ++d) sp.pos[d].push_back(q[d]);
+    for (int d = 0; d < 3; ++d) sp.p[d].push_back(q[s.ndims + d]);
+    sp.w.push_back(q[s.ndims + 3]);
+  }
+  return 0;
+}
+int32_t orc_upload_particles(orc_ctx* c, int32_t isp, int64_t n, const double* packed, int32_t nvar) {
+  return add_particles(c, isp, n, packed, nvar, true);
+}
+int32_t orc_append_particles(orc_ctx* c, int32_t isp, int64_t n, const double* packed, int32_t nvar) {
+  return add_particles(c, isp, n, packed, nvar, false);
+}
+int32_t orc_particle_count(orc_ctx* c, int32_t isp, int64_t* n) {
+  if (!c || !n || isp < 0 || (size_t)isp >= c->s.species.size()) return EB200_E_ARG;
+  *n = (int64_t)c->s.species[isp].count();
+  return 0;
+}
+int32_t orc_download_particles(orc_ctx* c, int32_t isp, int64_t first, int64_t capacity, double* packed,
+                               int32_t nvar, int64_t* n_out) {
+  if (!c || isp < 0 || (size_t)isp >= c->s.species.size()) return EB200_E_ARG;
+  State& s = c->s;
+  if (nvar != s.ndims + 4) return fail(c, EB200_E_ARG, "nvar must be ndims+4");
+  const Species& sp = s.species[isp];
+  int64_t n = std::max<int64_t>(0, std::min<int64_t>((int64_t)sp.count() - first, capacity));
+  for (int64_t i = 0; i < n; ++i) {
+    double* q = packed + i * nvar;
+    for (int d = 0; d < s.ndims; ++d) q[d] = sp.pos[d][first + i];
+    for (int d = 0; d < 3; ++d) q[s.ndims + d] = sp.p[d][first + i];
+    q[s.ndims + 3] = sp.w[first + i];
+  }
+  if (n_out) *n_out = n;
+  return 0;
+}
+
+int32_t orc_upload_fields(orc_ctx* c, const double* ex, const double* ey, const double* ez, const double* bx,
+                          const double* by, const double* bz, const double* jx, const double* jy, const double* jz) {
+  if (!c || !c->s.grid_set) return fail(c, EB200_E_STATE, "grid not set");
+  const double* src[NFIELD] = {ex, ey, ez, bx, by, bz, jx, jy, jz};
+  for (int f = 0; f < NFIELD; ++f)
+    if (src[f]) std::copy(src[f], src[f] + c->s.total, c->s.f[f].begin());
+  return 0;
+}
+int32_t orc_download_fields(orc_ctx* c, double* ex, double* ey, double* ez, double* bx, double* by, double* bz,
+                            double* jx, double* jy, double* jz) {
+  if (!c || !c->s.grid_set) return fail(c, EB200_E_STATE, "grid not set");
+  double* dst[NFIELD] = {ex, ey, ez, bx, by, bz, jx, jy, jz};
+  for (int f = 0; f < NFIELD; ++f)
+    if (dst[f]) std::copy(c->s.f[f].begin(), c->s.f[f].end(), dst[f]);
+  return 0;
+}
+// oracle-only: direct pointer to a field array (multi-rank CPU tests)
+double* orc_field_ptr(orc_ctx* c, int32_t comp) {
+  if (!c || comp < 0 || comp >= NFIELD) return nullptr;
+  return c->s.f[comp].data();
+}
+
+static size_t plane_size(const State& s, int boundary) {
+  const int a = boundary / 2;
+  size_t n = 1;
+  for (int d = 0; d < s.ndims; ++d) if (d != a) n *= (size_t)(s.n[d] + 1);
+  return n;
+}
+int32_t orc_set_laser(orc_ctx* c, int32_t boundary, int32_t id, double amp, double pol, double t_start,
+                      double t_end, const double* profile, const double* phase) {
+  if (!c || !c->s.grid_set) return fail(c, EB200_E_STATE, "grid not set");
+  State& s = c->s;
+  if (boundary < 1 || boundary > 2 * s.ndims) return fail(c, EB200_E_ARG, "bad boundary");
+  const int b = boundary - 1;
+  Laser* L = nullptr;
+  for (Laser& l : s.lasers[b]) if (l.id == id) L = &l;
+  if (!L) { s.lasers[b].emplace_back(); L = &s.lasers[b].back(); L->id = id; }
+  L->amp = amp; L->pol = pol; L->t_start = t_start; L->t_end = t_end;
+  const size_t n = plane_size(s, b);
+  if (profile) L->profile.assign(profile, profile + n); else L->profile.clear();
+  if (phase) L->phase.assign(phase, phase + n); else L->phase.clear();
+  return 0;
+}
+int32_t orc_set_laser_step(orc_ctx* c, int32_t boundary, int32_t id, double t_env, double integral_phase) {
+  if (!c || boundary < 1 || boundary > 6) return EB200_E_ARG;
+  for (Laser& l : c->s.lasers[boundary - 1])
+    if (l.id == id) { l.t_env = t_env; l.integral_phase = integral_phase; return 0; }
+  return fail(c, EB200_E_ARG, "laser id not set");
+}
+
+#define HOT(name, call)                                                         \
+  int32_t orc_##name(orc_ctx* c) {                                              \
+    if (!c || !c->s.grid_set) return fail(c, EB200_E_STATE, "grid not set");    \
+    if (c->s.dt <= 0) return fail(c, EB200_E_STATE, "dt not set");              \
+    call(c->s);                                                                 \
+    return 0;                                                                   \
+  }
+HOT(update_eb_fields_half, update_eb_fields_half)
+HOT(push_particles, push_particles)
+HOT(current_finish, current_finish)
+HOT(update_eb_fields_final, update_eb_fields_final)
+HOT(particle_bcs, particle_bcs)
+HOT(efield_bcs, efield_bcs)
+HOT(bfield_final_bcs, bfield_final_bcs)
+
+int32_t orc_energy(orc_ctx* c, double* fe, double* per_species) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  energy(c->s, fe, per_species);
+  return 0;
+}
+int32_t orc_charge_residual(orc_ctx* c, double* max_res, double* max_rho) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  charge_residual(c->s, max_res, max_rho);
+  return 0;
+}
+int32_t orc_set_option(orc_ctx*, const char*, const char*) { return 0; }
+int32_t orc_sync(orc_ctx*) { return 0; }
+int32_t orc_timer(orc_ctx*, const char*, int32_t, double* ms, int64_t* launches) {
+  if (ms) *ms = 0;
+  if (launches) *launches = 0;
+  return 0;
+}
+const char* orc_last_error(orc_ctx* c) { return c ? c->s.err.c_str() : g_err.c_str(); }
+const char* orc_version(void) { return "epoch-oracle-cpu 0.1 (test infrastructure)"; }
+
+}  // extern "C"

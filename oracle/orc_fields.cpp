@@ -1,0 +1,422 @@
+// oracle/orc_fields.cpp -- CPU ORACLE (test infrastructure only).
+// Restates epochNd/src/fields.f90 (update_e_field, update_b_field,
+// update_eb_fields_half/final), the field parts of epochNd/src/boundary.F90
+// (field_bc, field_clamp_zero, field_zero_gradient, efield_bcs, bfield_bcs,
+// bfield_final_bcs, processor_summation_bcs) and outflow_bcs_* of laser.f90.
+#include "orc_state.hpp"
+
+namespace orc {
+
+// stagger(dir, comp): setup.F90:134-144
+static inline bool stagger(int dir, int comp) {
+  switch (comp) {
+    case EX: case JX: return dir == 0;
+    case EY: case JY: return dir == 1;
+    case EZ: case JZ: return dir == 2;
+    case BX: return dir != 0;
+    case BY: return dir != 1;
+    case BZ: return dir != 2;
+  }
+  return false;
+}
+
+// visit every line along `axis` (all positions of the other dims, ghosts included);
+// fn(base) where element with Fortran index c along axis is base + (c+ng-1)*stride
+template <class F>
+static void for_each_line(const State& s, int axis, F fn) {
+  int a1 = (axis + 1) % 3, a2 = (axis + 2) % 3;
+  int e1 = s.n[a1] + 2 * s.ngd[a1], e2 = s.n[a2] + 2 * s.ngd[a2];
+  for (int q = 0; q < e2; ++q)
+    for (int p = 0; p < e1; ++p) fn((int64_t)p * s.st[a1] + (int64_t)q * s.st[a2]);
+}
+
+void set_half_step_scalars(State& s) {
+  // fields.f90:821-830
+  s.hdt = 0.5 * s.dt;
+  for (int d = 0; d < 3; ++d) {
+    s.hdtd[d] = s.hdt / s.d[d];
+    s.cn[d] = s.hdtd[d] * (C * C);
+  }
+  s.fac = s.hdt / EPS0;
+}
+
+// fields.f90:183-424 (non-CPML branches; 1D epoch1d/src/fields.f90:76, 2D epoch2d:104)
+void update_e_field(State& s) {
+  const int nd = s.ndims;
+  double* ex = s.f[EX].data(); double* ey = s.f[EY].data(); double* ez = s.f[EZ].data();
+  const double* bx = s.f[BX].data(); const double* by = s.f[BY].data(); const double* bz = s.f[BZ].data();
+  const double* jx = s.f[JX].data(); const double* jy = s.f[JY].data(); const double* jz = s.f[JZ].data();
+  const int64_t sx = s.st[0], sy = s.st[1], sz = s.st[2];
+  const double fac = s.fac;
+  double c1 = 1, c2 = 0, c3 = 0;
+  if (s.field_order == 4) { c1 = 9.0 / 8.0; c2 = -1.0 / 24.0; }
+  else if (s.field_order == 6) { c1 = 75.0 / 64.0; c2 = -25.0 / 384.0; c3 = 3.0 / 640.0; }
+  const int ord = s.field_order;
+  const double cx1 = ord == 2 ? s.cn[0] : c1 * s.cn[0], cx2 = c2 * s.cn[0], cx3 = c3 * s.cn[0];
+  const double cy1 = ord == 2 ? s.cn[1] : c1 * s.cn[1], cy2 = c2 * s.cn[1], cy3 = c3 * s.cn[1];
+  const double cz1 = ord == 2 ? s.cn[2] : c1 * s.cn[2], cz2 = c2 * s.cn[2], cz3 = c3 * s.cn[2];
+  for (int iz = s.lo0(2); iz <= s.hi(2); ++iz)
+    for (int iy = s.lo0(1); iy <= s.hi(1); ++iy)
+      for (int ix = 0; ix <= s.n[0]; ++ix) {
+        const int64_t i = s.idx(ix, iy, iz);
+        // the reference evaluates left to right: e + A - B - fac*j
+        double vx = ex[i], vy = ey[i], vz = ez[i];
+        // ex: + cy*(d_y bz) - cz*(d_z by)
+        if (nd >= 2) {
+          vx = vx + cy1 * (bz[i] - bz[i - sy]);
+          if (ord >= 4) vx = vx + cy2 * (bz[i + sy] - bz[i - 2 * sy]);
+          if (ord >= 6) vx = vx + cy3 * (bz[i + 2 * sy] - bz[i - 3 * sy]);
+        }
+        if (nd >= 3) {
+          vx = vx - cz1 * (by[i] - by[i - sz]);
+          if (ord >= 4) vx = vx - cz2 * (by[i + sz] - by[i - 2 * sz]);
+          if (ord >= 6) vx = vx - cz3 * (by[i + 2 * sz] - by[i - 3 * sz]);
+        }
+        vx = vx - fac * jx[i];
+        // ey: + cz*(d_z bx) - cx*(d_x bz)
+        if (nd >= 3) {
+          vy = vy + cz1 * (bx[i] - bx[i - sz]);
+          if (ord >= 4) vy = vy + cz2 * (bx[i + sz] - bx[i - 2 * sz]);
+          if (ord >= 6) vy = vy + cz3 * (bx[i + 2 * sz] - bx[i - 3 * sz]);
+        }
+        vy = vy - cx1 * (bz[i] - bz[i - sx]);
+        if (ord >= 4) vy = vy - cx2 * (bz[i + sx] - bz[i - 2 * sx]);
+        if (ord >= 6) vy = vy - cx3 * (bz[i + 2 * sx] - bz[i - 3 * sx]);
+        vy = vy - fac * jy[i];
+        // ez: + cx*(d_x by) - cy*(d_y bx)
+        vz = vz + cx1 * (by[i] - by[i - sx]);
+        if (ord >= 4) vz = vz + cx2 * (by[i + sx] - by[i - 2 * sx]);
+        if (ord >= 6) vz = vz + cx3 * (by[i + 2 * sx] - by[i - 3 * sx]);
+        if (nd >= 2) {
+          vz = vz - cy1 * (bx[i] - bx[i - sy]);
+          if (ord >= 4) vz = vz - cy2 * (bx[i + sy] - bx[i - 2 * sy]);
+          if (ord >= 6) vz = vz - cy3 * (bx[i + 2 * sy] - bx[i - 3 * sy]);
+        }
+        vz = vz - fac * jz[i];
+        ex[i] = vx; ey[i] = vy; ez[i] = vz;
+      }
+}
+
+// fields.f90:428-815 (Yee branches :637-654, orders 4/6 :734-812)
+void update_b_field(State& s) {
+  const int nd = s.ndims;
+  const double* ex = s.f[EX].data(); const double* ey = s.f[EY].data(); const double* ez = s.f[EZ].data();
+  double* bx = s.f[BX].data(); double* by = s.f[BY].data(); double* bz = s.f[BZ].data();
+  const int64_t sx = s.st[0], sy = s.st[1], sz = s.st[2];
+  double c1 = 1, c2 = 0, c3 = 0;
+  if (s.field_order == 4) { c1 = 9.0 / 8.0; c2 = -1.0 / 24.0; }
+  else if (s.field_order == 6) { c1 = 75.0 / 64.0; c2 = -25.0 / 384.0; c3 = 3.0 / 640.0; }
+  const int ord = s.field_order;
+  const double cx1 = ord == 2 ? s.hdtd[0] : c1 * s.hdtd[0], cx2 = c2 * s.hdtd[0], cx3 = c3 * s.hdtd[0];
+  const double cy1 = ord == 2 ? s.hdtd[1] : c1 * s.hdtd[1], cy2 = c2 * s.hdtd[1], cy3 = c3 * s.hdtd[1];
+  const double cz1 = ord == 2 ? s.hdtd[2] : c1 * s.hdtd[2], cz2 = c2 * s.hdtd[2], cz3 = c3 * s.hdtd[2];
+  for (int iz = s.lo0(2); iz <= s.hi(2); ++iz)
+    for (int iy = s.lo0(1); iy <= s.hi(1); ++iy)
+      for (int ix = 0; ix <= s.n[0]; ++ix) {
+        const int64_t i = s.idx(ix, iy, iz);
+        double vx = bx[i], vy = by[i], vz = bz[i];
+        // bx: - cy*(d_y ez) + cz*(d_z ey)
+        if (nd >= 2) {
+          vx = vx - cy1 * (ez[i + sy] - ez[i]);
+          if (ord >= 4) vx = vx - cy2 * (ez[i + 2 * sy] - ez[i - sy]);
+          if (ord >= 6) vx = vx - cy3 * (ez[i + 3 * sy] - ez[i - 2 * sy]);
+        }
+        if (nd >= 3) {
+          vx = vx + cz1 * (ey[i + sz] - ey[i]);
+          if (ord >= 4) vx = vx + cz2 * (ey[i + 2 * sz] - ey[i - sz]);
+          if (ord >= 6) vx = vx + cz3 * (ey[i + 3 * sz] - ey[i - 2 * sz]);
+        }
+        // by: - cz*(d_z ex) + cx*(d_x ez)
+        if (nd >= 3) {
+          vy = vy - cz1 * (ex[i + sz] - ex[i]);
+          if (ord >= 4) vy = vy - cz2 * (ex[i + 2 * sz] - ex[i - sz]);
+          if (ord >= 6) vy = vy - cz3 * (ex[i + 3 * sz] - ex[i - 2 * sz]);
+        }
+        vy = vy + cx1 * (ez[i + sx] - ez[i]);
+        if (ord >= 4) vy = vy + cx2 * (ez[i + 2 * sx] - ez[i - sx]);
+        if (ord >= 6) vy = vy + cx3 * (ez[i + 3 * sx] - ez[i - 2 * sx]);
+        // bz: - cx*(d_x ey) + cy*(d_y ex)
+        vz = vz - cx1 * (ey[i + sx] - ey[i]);
+        if (ord >= 4) vz = vz - cx2 * (ey[i + 2 * sx] - ey[i - sx]);
+        if (ord >= 6) vz = vz - cx3 * (ey[i + 3 * sx] - ey[i - 2 * sx]);
+        if (nd >= 2) {
+          vz = vz + cy1 * (ex[i + sy] - ex[i]);
+          if (ord >= 4) vz = vz + cy2 * (ex[i + 2 * sy] - ex[i - sy]);
+          if (ord >= 6) vz = vz + cy3 * (ex[i + 3 * sy] - ex[i - 2 * sy]);
+        }
+        bx[i] = vx; by[i] = vy; bz[i] = vz;
+      }
+}
+
+// boundary.F90:145-152,321-468 do_field_mpi_with_lengths, single-rank form: the
+// x_min neighbour of a periodic rank is itself, so A(nx+1:nx+ng) <- A(1:ng) and
+// A(1-ng:0) <- A(nx+1-ng:nx); x then y then z over FULL extents of the other dims;
+// on a non-periodic physical boundary the ghost cells are left untouched.
+void field_bc(State& s, int comp) {
+  double* a = s.f[comp].data();
+  const int ng = s.ng;
+  for (int ax = 0; ax < s.ndims; ++ax) {
+    const int nn = s.n[ax];
+    const int64_t sa = s.st[ax];
+    const bool per_max = s.bc_field[2 * ax + 1] == BC_PERIODIC;
+    const bool per_min = s.bc_field[2 * ax] == BC_PERIODIC;
+    for_each_line(s, ax, [&](int64_t base) {
+      if (per_max)
+        for (int i = 1; i <= ng; ++i) a[base + (nn + i + ng - 1) * sa] = a[base + (i + ng - 1) * sa];
+      if (per_min)
+        for (int i = 1; i <= ng; ++i) a[base + (i - ng + ng - 1) * sa] = a[base + (nn + i - ng + ng - 1) * sa];
+    });
+  }
+}
+
+// boundary.F90:623-698
+static void field_zero_gradient(State& s, int comp, int boundary /*0..5*/) {
+  if (s.bc_field[boundary] == BC_PERIODIC) return;
+  const int ax = boundary / 2;
+  if (ax >= s.ndims) return;
+  const bool is_max = boundary & 1;
+  if (is_max ? !s.max_bnd[ax] : !s.min_bnd[ax]) return;
+  double* a = s.f[comp].data();
+  const int ng = s.ng, nn = s.n[ax];
+  const int64_t sa = s.st[ax];
+  const bool stg = stagger(ax, comp);
+  for_each_line(s, ax, [&](int64_t base) {
+    auto A = [&](int c) -> double& { return a[base + (int64_t)(c + ng - 1) * sa]; };
+    if (!is_max) {
+      if (stg) for (int i = 1; i <= ng - 1; ++i) A(i - ng) = A(ng - i);
+      else for (int i = 1; i <= ng; ++i) A(i - ng) = A(ng + 1 - i);
+    } else {
+      if (stg) for (int i = 1; i <= ng - 1; ++i) A(nn + i) = A(nn - i);
+      else for (int i = 1; i <= ng; ++i) A(nn + i) = A(nn + 1 - i);
+    }
+  });
+}
+
+// boundary.F90:702-783
+static void field_clamp_zero(State& s, int comp, int boundary) {
+  if (s.bc_field[boundary] == BC_PERIODIC) return;
+  const int ax = boundary / 2;
+  if (ax >= s.ndims) return;
+  const bool is_max = boundary & 1;
+  if (is_max ? !s.max_bnd[ax] : !s.min_bnd[ax]) return;
+  double* a = s.f[comp].data();
+  const int ng = s.ng, nn = s.n[ax];
+  const int64_t sa = s.st[ax];
+  const bool stg = stagger(ax, comp);
+  for_each_line(s, ax, [&](int64_t base) {
+    auto A = [&](int c) -> double& { return a[base + (int64_t)(c + ng - 1) * sa]; };
+    if (!is_max) {
+      if (stg) { for (int i = 1; i <= ng - 1; ++i) A(i - ng) = -A(ng - i); A(0) = 0.0; }
+      else for (int i = 1; i <= ng; ++i) A(i - ng) = -A(ng + 1 - i);
+    } else {
+      if (stg) { A(nn) = 0.0; for (int i = 1; i <= ng - 1; ++i) A(nn + i) = -A(nn - i); }
+      else for (int i = 1; i <= ng; ++i) A(nn + i) = -A(nn + 1 - i);
+    }
+  });
+}
+
+// boundary.F90:1148-1202
+void efield_bcs(State& s) {
+  field_bc(s, EX); field_bc(s, EY); field_bc(s, EZ);
+  for (int ax = 0; ax < s.ndims; ++ax)
+    for (int side = 0; side < 2; ++side) {
+      const int b = 2 * ax + side;
+      if (s.bc_field[b] == BC_CONDUCT)
+        for (int c = 0; c < 3; ++c) {
+          if (c == ax) field_clamp_zero(s, EX + c, b);
+          else field_zero_gradient(s, EX + c, b);
+        }
+    }
+  for (int b = 0; b < 2 * s.ndims; ++b) {
+    const int bc = s.bc_field[b];
+    if (bc == BC_CLAMP || bc == BC_SIMPLE_LASER || bc == BC_SIMPLE_OUTFLOW)
+      for (int c = 0; c < 3; ++c) field_clamp_zero(s, EX + c, b);
+    if (bc == BC_ZERO_GRADIENT || bc == BC_CPML_LASER || bc == BC_CPML_OUTFLOW)
+      for (int c = 0; c < 3; ++c) field_zero_gradient(s, EX + c, b);
+  }
+}
+
+// boundary.F90:1206-1263
+void bfield_bcs(State& s, bool mpi_only) {
+  field_bc(s, BX); field_bc(s, BY); field_bc(s, BZ);
+  if (mpi_only) return;
+  for (int ax = 0; ax < s.ndims; ++ax)
+    for (int side = 0; side < 2; ++side) {
+      const int b = 2 * ax + side;
+      if (s.bc_field[b] == BC_CONDUCT)
+        for (int c = 0; c < 3; ++c) {
+          if (c == ax) field_zero_gradient(s, BX + c, b);
+          else field_clamp_zero(s, BX + c, b);
+        }
+    }
+  for (int b = 0; b < 2 * s.ndims; ++b) {
+    const int bc = s.bc_field[b];
+    if (bc == BC_CLAMP || bc == BC_SIMPLE_LASER || bc == BC_SIMPLE_OUTFLOW)
+      for (int c = 0; c < 3; ++c) field_clamp_zero(s, BX + c, b);
+    if (bc == BC_ZERO_GRADIENT || bc == BC_CPML_LASER || bc == BC_CPML_OUTFLOW)
+      for (int c = 0; c < 3; ++c) field_zero_gradient(s, BX + c, b);
+  }
+}
+
+// laser.f90:509-973 outflow_bcs_{x,y,z}_{min,max} (1D epoch1d/src/laser.f90:303,
+// 2D epoch2d/src/laser.f90:411).  The six routines are cyclic permutations of one
+// another: normal axis a, tangential t1=a+1, t2=a+2.  External boundary fields
+// (ex_x_min ... from the deck's `fields` block) are zero here.
+static void outflow_bcs(State& s, int boundary) {
+  const int a = boundary / 2, t1 = (a + 1) % 3, t2 = (a + 2) % 3;
+  const bool is_max = boundary & 1;
+  const int lp = is_max ? s.n[a] : 1;
+  const double dtc2 = s.dt * (C * C);
+  const double la = dtc2 / s.d[a];
+  const double l1 = t1 < s.ndims ? dtc2 / s.d[t1] : 0.0;
+  const double l2 = t2 < s.ndims ? dtc2 / s.d[t2] : 0.0;
+  const double sum = 1.0 / (la + C), diff = la - C, dt_eps = s.dt / EPS0;
+  double* Ba = s.f[BX + a].data(); double* B1 = s.f[BX + t1].data(); double* B2 = s.f[BX + t2].data();
+  const double* E1 = s.f[EX + t1].data(); const double* E2 = s.f[EX + t2].data();
+  const double* J1 = s.f[JX + t1].data(); const double* J2 = s.f[JX + t2].data();
+  // plane index ranges 0..n over existing tangential dims; plane storage is
+  // x-fastest in (lower axis, higher axis) order like the reference's (0:ny,0:nz)
+  const int lo_axis = t1 < t2 ? t1 : t2, hi_axis = t1 < t2 ? t2 : t1;
+  const int nlo = lo_axis < s.ndims ? s.n[lo_axis] + 1 : 1;
+  const int nhi = hi_axis < s.ndims ? s.n[hi_axis] + 1 : 1;
+  const int64_t sa = s.st[a];
+  for (int q = 0; q < nhi; ++q)
+    for (int p = 0; p < nlo; ++p) {
+      int c[3];
+      c[a] = lp;
+      c[lo_axis] = lo_axis < s.ndims ? p : 1;
+      c[hi_axis] = hi_axis < s.ndims ? q : 1;
+      const int64_t i = s.idx(c[0], c[1], c[2]);
+      double source1 = 0.0, source2 = 0.0;
+      if (s.add_laser[boundary]) {
+        for (const Laser& L : s.lasers[boundary]) {
+          if (s.time >= L.t_start && s.time <= L.t_end) {
+            const size_t k = (size_t)q * nlo + p;
+            const double prof = L.profile.empty() ? 1.0 : L.profile[k];
+            const double ph = L.phase.empty() ? 0.0 : L.phase[k];
+            const double t_env = L.t_env * L.amp;
+            const double base = t_env * prof * std::sin(L.integral_phase + ph);
+            source1 = source1 + base * std::cos(L.pol);
+            source2 = source2 + base * std::sin(L.pol);
+          }
+        }
+      }
+      if (!is_max) {
+        Ba[i - sa] = 0.0;  // bx(laserpos-1) = bx_x_min
+        double v2 = 4.0 * source1 + 2.0 * (0.0 + C * 0.0) - 2.0 * E1[i];
+        if (t2 < s.ndims) v2 = v2 - l2 * (Ba[i] - Ba[i - s.st[t2]]);
+        v2 = v2 + dt_eps * J1[i] + diff * B2[i];
+        B2[i - sa] = sum * v2;
+        double v1 = -4.0 * source2 - 2.0 * (0.0 - C * 0.0) + 2.0 * E2[i];
+        if (t1 < s.ndims) v1 = v1 - l1 * (Ba[i] - Ba[i - s.st[t1]]);
+        v1 = v1 - dt_eps * J2[i] + diff * B1[i];
+        B1[i - sa] = sum * v1;
+      } else {
+        Ba[i + sa] = 0.0;  // bx(laserpos+1) = bx_x_max
+        double v2 = -4.0 * source1 - 2.0 * (0.0 - C * 0.0) + 2.0 * E1[i];
+        if (t2 < s.ndims) v2 = v2 + l2 * (Ba[i] - Ba[i - s.st[t2]]);
+        v2 = v2 - dt_eps * J1[i] + diff * B2[i - sa];
+        B2[i] = sum * v2;
+        double v1 = 4.0 * source2 + 2.0 * (0.0 + C * 0.0) - 2.0 * E2[i];
+        if (t1 < s.ndims) v1 = v1 + l1 * (Ba[i] - Ba[i - s.st[t1]]);
+        v1 = v1 + dt_eps * J2[i] + diff * B1[i - sa];
+        B1[i] = sum * v1;
+      }
+    }
+}
+
+// boundary.F90:1267-1312
+void bfield_final_bcs(State& s) {
+  bfield_bcs(s, false);
+  for (int b = 0; b < 2 * s.ndims; ++b) {
+    const int ax = b / 2;
+    const bool on_bnd = (b & 1) ? s.max_bnd[ax] : s.min_bnd[ax];
+    if (!on_bnd) continue;
+    if (s.add_laser[b] || s.bc_field[b] == BC_SIMPLE_OUTFLOW) outflow_bcs(s, b);
+  }
+  bfield_bcs(s, true);
+}
+
+// fields.f90:819-847
+void update_eb_fields_half(State& s) {
+  set_half_step_scalars(s);
+  update_e_field(s);
+  efield_bcs(s);
+  update_b_field(s);
+  bfield_bcs(s, true);
+}
+
+// fields.f90:851-872
+void update_eb_fields_final(State& s) {
+  set_half_step_scalars(s);
+  update_b_field(s);
+  bfield_final_bcs(s);
+  update_e_field(s);
+  efield_bcs(s);
+}
+
+// bc_allspecies (deck_species_block.F90:231-245): common particle BC or mixed
+static int bc_allspecies(const State& s, int b) {
+  int bc = -1;
+  for (const Species& sp : s.species) {
+    if (!sp.defined) continue;
+    if (bc == -1) bc = sp.bc[b];
+    else if (bc != sp.bc[b]) return BC_MIXED;
+  }
+  return bc == -1 ? BC_PERIODIC : bc;
+}
+
+// boundary.F90:787-919 particle_reflection_bcs + :923-1084 particle_periodic_bcs
+static void processor_summation_bcs(State& s, int comp, int flip_dir /*0..2*/) {
+  double* a = s.f[comp].data();
+  const int ng = s.ng;
+  // reflection first
+  for (int ax = 0; ax < s.ndims; ++ax) {
+    const int nn = s.n[ax];
+    const int64_t sa = s.st[ax];
+    const bool rmin = s.min_bnd[ax] && bc_allspecies(s, 2 * ax) == BC_REFLECT;
+    const bool rmax = s.max_bnd[ax] && bc_allspecies(s, 2 * ax + 1) == BC_REFLECT;
+    if (!rmin && !rmax) continue;
+    for_each_line(s, ax, [&](int64_t base) {
+      auto A = [&](int c) -> double& { return a[base + (int64_t)(c + ng - 1) * sa]; };
+      if (rmin) {
+        if (flip_dir == ax) for (int i = 1; i <= ng - 1; ++i) { A(i) = A(i) - A(-i); A(-i) = 0.0; }
+        else for (int i = 1; i <= ng - 1; ++i) { A(i) = A(i) + A(1 - i); A(1 - i) = 0.0; }
+      }
+      if (rmax) {
+        if (flip_dir == ax) for (int i = 1; i <= ng; ++i) { A(nn - i) = A(nn - i) - A(nn + i); A(nn + i) = 0.0; }
+        else for (int i = 1; i <= ng; ++i) { A(nn + 1 - i) = A(nn + 1 - i) + A(nn + i); A(nn + i) = 0.0; }
+      }
+    });
+  }
+  // periodic / subdomain sums, x then y then z (single rank: neighbour is self if
+  // the species boundary is periodic, else MPI_PROC_NULL -> temp stays 0)
+  for (int ax = 0; ax < s.ndims; ++ax) {
+    const int nn = s.n[ax];
+    const int64_t sa = s.st[ax];
+    const bool pmin = !(s.min_bnd[ax] && bc_allspecies(s, 2 * ax) != BC_PERIODIC);
+    const bool pmax = !(s.max_bnd[ax] && bc_allspecies(s, 2 * ax + 1) != BC_PERIODIC);
+    std::vector<double> temp(ng);
+    for_each_line(s, ax, [&](int64_t base) {
+      auto A = [&](int c) -> double& { return a[base + (int64_t)(c + ng - 1) * sa]; };
+      // send A(nn+1:nn+ng) to +1 neighbour, receive from -1 neighbour, add to A(1:ng)
+      // single rank: receive own slab iff both the send (+1) and recv (-1) sides exist
+      if (pmax && pmin) {
+        for (int i = 1; i <= ng; ++i) temp[i - 1] = A(nn + i);
+        for (int i = 1; i <= ng; ++i) A(i) = A(i) + temp[i - 1];
+        for (int i = 1; i <= ng; ++i) temp[i - 1] = A(i - ng);
+        for (int i = 1; i <= ng; ++i) A(nn - ng + i) = A(nn - ng + i) + temp[i - 1];
+      }
+    });
+  }
+}
+
+// housekeeping/current_smooth.F90:29-45 (smoothing and current correction off)
+void current_finish(State& s) {
+  processor_summation_bcs(s, JX, 0);
+  processor_summation_bcs(s, JY, 1);
+  processor_summation_bcs(s, JZ, 2);
+  field_bc(s, JX); field_bc(s, JY); field_bc(s, JZ);
+}
+
+}  // namespace orc
