@@ -1,0 +1,409 @@
+// capi.cu -- the C ABI of include/epoch_b200.h (extern "C", plain pointers and
+// sizes).  One context per rank == per GPU; all work is enqueued on the context's
+// private stream.  There is no CPU fallback: without a CUDA device every entry
+// that touches data fails with EB200_E_CUDA.
+#include "ctx.cuh"
+#include <cstring>
+#include <cstdlib>
+#include <new>
+
+static thread_local std::string g_last_error;
+
+namespace eb {
+
+int32_t fail(eb200_ctx* c, int32_t code, const std::string& msg) {
+  if (c) c->err = msg;
+  g_last_error = msg;
+  return code;
+}
+
+ScopedPhase::ScopedPhase(eb200_ctx* c_, const char* n) : c(c_), name(n) {
+  if (!c->timers_on) return;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  cudaEventRecord(e0, c->stream);
+  launches0 = c->launches;
+}
+ScopedPhase::~ScopedPhase() {
+  if (!e0) return;
+  cudaEventRecord(e1, c->stream);
+  PhaseTimer& t = c->timers[name];
+  t.ev.emplace_back(e0, e1);
+  t.launches += c->launches - launches0;
+}
+
+static void free_species(SpeciesD& sp) {
+  for (int k = 0; k < 7; ++k) if (sp.a[k]) { cudaFree(sp.a[k]); sp.a[k] = nullptr; }
+  if (sp.key) cudaFree(sp.key);
+  if (sp.dest) cudaFree(sp.dest);
+  sp.key = sp.dest = nullptr; sp.n = sp.cap = 0;
+}
+
+}  // namespace eb
+using namespace eb;
+
+#define CHECK_CTX(c) do { if (!(c)) return fail(nullptr, EB200_E_ARG, "null context"); cudaSetDevice((c)->device); } while (0)
+#define NEED_GRID(c) do { if (!(c)->grid_set) return fail((c), EB200_E_STATE, "set_grid has not been called"); } while (0)
+#define NEED_DT(c) do { if (!((c)->dt > 0)) return fail((c), EB200_E_STATE, "set_time has not been called (dt <= 0)"); } while (0)
+
+extern "C" {
+
+int32_t eb200_create(eb200_ctx** out, int32_t ndims, int32_t shape, int32_t device, int32_t rank,
+                     int32_t nproc, const int32_t nprocdir[3], const int32_t coords[3], const void* nccl_id) {
+  if (!out) return fail(nullptr, EB200_E_ARG, "out is null");
+  *out = nullptr;
+  if (ndims < 1 || ndims > 3) return fail(nullptr, EB200_E_ARG, "ndims must be 1, 2 or 3");
+  if (shape < 0 || shape > 2) return fail(nullptr, EB200_E_ARG, "shape must be 0 (tophat), 1 (triangle) or 2 (bspline3)");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(nullptr, EB200_E_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e) + " (this library has no CPU path)");
+  if (device < 0 || device >= ndev) return fail(nullptr, EB200_E_ARG, "bad device ordinal");
+  eb200_ctx* c = new (std::nothrow) eb200_ctx();
+  if (!c) return fail(nullptr, EB200_E_NOMEM, "host allocation failed");
+  c->ndims = ndims; c->shape = shape; c->device = device; c->rank = rank; c->nproc = nproc < 1 ? 1 : nproc;
+  int np = 1;
+  for (int d = 0; d < 3; ++d) {
+    c->nprocdir[d] = (nprocdir && d < ndims) ? nprocdir[d] : 1;
+    c->coords[d] = (coords && d < ndims) ? coords[d] : 0;
+    if (c->nprocdir[d] < 1 || c->coords[d] < 0 || c->coords[d] >= c->nprocdir[d]) { delete c; return fail(nullptr, EB200_E_ARG, "bad nprocdir/coords"); }
+    np *= c->nprocdir[d];
+    c->min_bnd[d] = c->coords[d] == 0;
+    c->max_bnd[d] = c->coords[d] == c->nprocdir[d] - 1;
+  }
+  if (np != c->nproc) { delete c; return fail(nullptr, EB200_E_ARG, "product of nprocdir != nproc"); }
+  // neighbours of the (nprocz,nprocy,nprocx) Cartesian communicator, always with
+  // wrap-around; the call sites decide whether a wrap link is used
+  for (int d = 0; d < 3; ++d) {
+    int cl[3] = {c->coords[0], c->coords[1], c->coords[2]}, ch[3] = {c->coords[0], c->coords[1], c->coords[2]};
+    cl[d] = (cl[d] - 1 + c->nprocdir[d]) % c->nprocdir[d];
+    ch[d] = (ch[d] + 1) % c->nprocdir[d];
+    c->nbr_lo[d] = (cl[2] * c->nprocdir[1] + cl[1]) * c->nprocdir[0] + cl[0];
+    c->nbr_hi[d] = (ch[2] * c->nprocdir[1] + ch[1]) * c->nprocdir[0] + ch[0];
+  }
+  // constants.F90:472-492
+  if (shape == 2) { c->sf_min = -2; c->sf_max = 2; c->png = 4; }
+  else if (shape == 0) { c->sf_min = 0; c->sf_max = 1; c->png = 2; }
+  else { c->sf_min = -1; c->sf_max = 1; c->png = 3; }
+  c->ng = c->png + 2;
+  cudaSetDevice(device);
+  if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaMalloc(&c->d_counters, 64 * sizeof(unsigned long long)) != cudaSuccess ||
+      cudaMallocHost(&c->h_counters, 64 * sizeof(unsigned long long)) != cudaSuccess ||
+      cudaMalloc(&c->d_red, 64 * sizeof(double)) != cudaSuccess ||
+      cudaMallocHost(&c->h_red, 64 * sizeof(double)) != cudaSuccess) {
+    std::string m = cudaGetErrorString(cudaGetLastError());
+    delete c;
+    return fail(nullptr, EB200_E_CUDA, "context setup failed: " + m);
+  }
+  const char* t = getenv("EB200_TIMERS");
+  c->timers_on = t && t[0] == '1';
+  int32_t rc = comm_init(c, nccl_id);
+  if (rc != 0) { std::string m = c->err; eb200_destroy(c); return fail(nullptr, rc, m); }
+  *out = c;
+  return 0;
+}
+
+int32_t eb200_nccl_unique_id(void* out128) {
+  if (!out128) return fail(nullptr, EB200_E_ARG, "null");
+  return nccl_unique_id(out128);
+}
+
+int32_t eb200_destroy(eb200_ctx* c) {
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  comm_destroy(c);
+  for (SpeciesD& sp : c->species) free_species(sp);
+  for (int b = 0; b < 6; ++b) for (Laser& L : c->lasers[b]) { if (L.profile) cudaFree(L.profile); if (L.phase) cudaFree(L.phase); }
+  void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->cell_start, c->cub_tmp, c->halo_send, c->halo_recv,
+                  c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  if (c->h_counters) cudaFreeHost(c->h_counters);
+  if (c->h_red) cudaFreeHost(c->h_red);
+  for (auto& kv : c->timers) for (auto& ev : kv.second.ev) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return 0;
+}
+
+int32_t eb200_set_grid(eb200_ctx* c, const int32_t n_local[3], const int32_t n_global[3], const int32_t n_global_min[3],
+                       const double d[3], const double grid_min_local[3], const double min_local[3],
+                       const double max_local[3], const double min_global[3], const double max_global[3],
+                       int32_t cpml_thickness) {
+  CHECK_CTX(c);
+  if (!n_local || !d || !grid_min_local || !min_local || !max_local || !min_global || !max_global)
+    return fail(c, EB200_E_ARG, "null argument");
+  if (cpml_thickness != 0) return fail(c, EB200_E_UNSUPPORTED, "CPML boundaries are outside the hot path (SURVEY 8f-2)");
+  GridP& g = c->g;
+  g.ndims = c->ndims; g.shape = c->shape; g.ng = c->ng;
+  long long stride = 1, ncell = 1;
+  for (int k = 0; k < 3; ++k) {
+    const bool ex = k < c->ndims;
+    g.n[k] = ex ? n_local[k] : 1;
+    if (g.n[k] < 1) return fail(c, EB200_E_ARG, "n_local < 1");
+    if (ex && d[k] <= 0) return fail(c, EB200_E_ARG, "cell size <= 0");
+    c->nglob[k] = ex && n_global ? n_global[k] : g.n[k];
+    c->nglob_min[k] = ex && n_global_min ? n_global_min[k] : 1;
+    g.ngd[k] = ex ? c->ng : 0;
+    g.d[k] = ex ? d[k] : 1.0; g.id[k] = 1.0 / g.d[k];
+    g.gml[k] = ex ? grid_min_local[k] : 0.0;
+    g.min_local[k] = ex ? min_local[k] : 0.0; g.max_local[k] = ex ? max_local[k] : 0.0;
+    g.gmin[k] = ex ? min_global[k] : 0.0; g.gmax[k] = ex ? max_global[k] : 0.0;
+    g.st[k] = stride;
+    stride *= (long long)(g.n[k] + 2 * g.ngd[k]);
+    g.kn[k] = ex ? g.n[k] + 2 * KM : 1;
+    ncell *= g.kn[k];
+  }
+  if (ncell >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "local grid too large for 32-bit cell keys");
+  g.total = stride; g.ncell_ext = ncell;
+  if (c->fbase) { cudaStreamSynchronize(c->stream); cudaFree(c->fbase); c->fbase = nullptr; }
+  if (c->rho) { cudaFree(c->rho); c->rho = nullptr; }
+  if (c->res_ref) { cudaFree(c->res_ref); c->res_ref = nullptr; }
+  EB_CUDA(c, cudaMalloc(&c->fbase, (size_t)NFIELD * g.total * sizeof(double)));
+  EB_CUDA(c, cudaMemsetAsync(c->fbase, 0, (size_t)NFIELD * g.total * sizeof(double), c->stream));
+  for (int f = 0; f < NFIELD; ++f) c->f.f[f] = c->fbase + (size_t)f * g.total;
+  for (SpeciesD& sp : c->species) sp.sorted = false;
+  c->grid_set = true;
+  return 0;
+}
+
+int32_t eb200_set_time(eb200_ctx* c, double dt, double time, int32_t step) {
+  CHECK_CTX(c);
+  if (!(dt > 0)) return fail(c, EB200_E_ARG, "dt must be > 0");
+  if (dt != c->dt) for (SpeciesD& sp : c->species) sp.sorted = false;   // sort keys depend on dt
+  c->dt = dt; c->time = time; c->step = step;
+  return 0;
+}
+
+int32_t eb200_set_field_bcs(eb200_ctx* c, const int32_t bc_field[6]) {
+  CHECK_CTX(c);
+  if (!bc_field) return fail(c, EB200_E_ARG, "null");
+  // setup_boundaries, boundary.F90:30-59
+  for (int i = 0; i < 6; ++i) {
+    int bc = i < 2 * c->ndims ? bc_field[i] : EB200_BC_PERIODIC;
+    c->add_laser[i] = false;
+    if (bc == EB200_BC_OTHER) bc = EB200_BC_CLAMP;
+    if (bc == EB200_BC_CPML_LASER || bc == EB200_BC_CPML_OUTFLOW)
+      return fail(c, EB200_E_UNSUPPORTED, "CPML boundaries are outside the hot path (SURVEY 8f-2)");
+    if (bc == EB200_BC_SIMPLE_LASER) c->add_laser[i] = true;
+    if (bc == EB200_BC_REFLECT) bc = EB200_BC_CLAMP;
+    if (bc == EB200_BC_OPEN) bc = EB200_BC_SIMPLE_OUTFLOW;
+    if (bc != EB200_BC_PERIODIC && bc != EB200_BC_CLAMP && bc != EB200_BC_SIMPLE_LASER && bc != EB200_BC_SIMPLE_OUTFLOW &&
+        bc != EB200_BC_ZERO_GRADIENT && bc != EB200_BC_CONDUCT)
+      return fail(c, EB200_E_ARG, "unrecognised field boundary code");
+    c->bc_field[i] = bc;
+  }
+  for (int d = 0; d < c->ndims; ++d)
+    if ((c->bc_field[2 * d] == EB200_BC_PERIODIC) != (c->bc_field[2 * d + 1] == EB200_BC_PERIODIC))
+      return fail(c, EB200_E_ARG, "periodic field boundaries must come in min/max pairs");
+  return 0;
+}
+
+int32_t eb200_set_solver(eb200_ctx* c, int32_t field_order, int32_t maxwell_solver, const double coeffs[15]) {
+  CHECK_CTX(c);
+  if (field_order != 2 && field_order != 4 && field_order != 6) return fail(c, EB200_E_ARG, "field_order must be 2, 4 or 6");
+  if (maxwell_solver != 0) return fail(c, EB200_E_UNSUPPORTED, "extended-stencil Maxwell solvers are not built yet (SURVEY 8f-4)");
+  if (field_order / 2 > c->ng) return fail(c, EB200_E_ARG, "field_order needs more ghost cells");
+  c->field_order = field_order; c->maxwell_solver = maxwell_solver;
+  if (coeffs) std::memcpy(c->coeffs, coeffs, 15 * sizeof(double));
+  return 0;
+}
+
+int32_t eb200_set_species(eb200_ctx* c, int32_t isp, double charge, double mass, double weight, int32_t immobile,
+                          int32_t zero_current, int32_t species_type, const int32_t bc_particle[6]) {
+  CHECK_CTX(c);
+  if (isp < 0 || isp > 62) return fail(c, EB200_E_ARG, "species index out of range (0..62)");
+  if (!(mass > 0) && species_type != 1) return fail(c, EB200_E_ARG, "mass must be > 0");
+  if ((size_t)isp >= c->species.size()) c->species.resize(isp + 1);
+  SpeciesD& sp = c->species[isp];
+  int bcs[6];
+  for (int i = 0; i < 6; ++i) {
+    int bc = (bc_particle && i < 2 * c->ndims) ? bc_particle[i] : EB200_BC_PERIODIC;
+    // setup_particle_boundary, boundary.F90:98-140
+    if (bc == EB200_BC_OTHER || bc == EB200_BC_CONDUCT) bc = EB200_BC_REFLECT;
+    if (bc == EB200_BC_SIMPLE_LASER || bc == EB200_BC_SIMPLE_OUTFLOW || bc == EB200_BC_CPML_LASER || bc == EB200_BC_CPML_OUTFLOW) bc = EB200_BC_OPEN;
+    if (bc == EB200_BC_THERMAL || bc == EB200_BC_HEAT_BATH)
+      return fail(c, EB200_E_UNSUPPORTED, "thermal / heat-bath particle boundaries need the host RNG and stay on the host");
+    if (bc != EB200_BC_PERIODIC && bc != EB200_BC_REFLECT && bc != EB200_BC_OPEN) return fail(c, EB200_E_ARG, "unrecognised particle boundary code");
+    bcs[i] = bc;
+  }
+  for (int d = 0; d < c->ndims; ++d)
+    if ((bcs[2 * d] == EB200_BC_PERIODIC) != (bcs[2 * d + 1] == EB200_BC_PERIODIC))
+      return fail(c, EB200_E_ARG, "periodic particle boundaries must come in min/max pairs");
+  for (size_t o = 0; o < c->species.size(); ++o)
+    if (c->species[o].defined && (int)o != isp)
+      for (int i = 0; i < 6; ++i)
+        if (c->species[o].bc[i] != bcs[i])
+          return fail(c, EB200_E_UNSUPPORTED, "per-species (mixed) particle boundaries are not supported (boundary.F90:1130-1136)");
+  sp.defined = true; sp.charge = charge; sp.mass = mass; sp.weight = weight;
+  sp.immobile = immobile; sp.zero_current = zero_current; sp.species_type = species_type;
+  for (int i = 0; i < 6; ++i) sp.bc[i] = bcs[i];
+  sp.sorted = false;
+  return 0;
+}
+
+static int32_t check_species(eb200_ctx* c, int32_t isp, int32_t nvar) {
+  if (isp < 0 || (size_t)isp >= c->species.size() || !c->species[isp].defined) return fail(c, EB200_E_ARG, "species not defined");
+  if (nvar != c->ndims + 4) return fail(c, EB200_E_ARG, "nvar must be ndims+4 (pos, p(3), weight): optional per-particle fields are not on this path");
+  return 0;
+}
+int32_t eb200_upload_particles(eb200_ctx* c, int32_t isp, int64_t n, const double* packed, int32_t nvar) {
+  CHECK_CTX(c); NEED_GRID(c);
+  EB_TRY(check_species(c, isp, nvar));
+  if (n < 0 || (n > 0 && !packed)) return fail(c, EB200_E_ARG, "bad particle buffer");
+  return add_particles(c, isp, n, packed, nvar, true);
+}
+int32_t eb200_append_particles(eb200_ctx* c, int32_t isp, int64_t n, const double* packed, int32_t nvar) {
+  CHECK_CTX(c); NEED_GRID(c);
+  EB_TRY(check_species(c, isp, nvar));
+  if (n < 0 || (n > 0 && !packed)) return fail(c, EB200_E_ARG, "bad particle buffer");
+  return add_particles(c, isp, n, packed, nvar, false);
+}
+int32_t eb200_particle_count(eb200_ctx* c, int32_t isp, int64_t* n) {
+  CHECK_CTX(c);
+  if (!n || isp < 0 || (size_t)isp >= c->species.size()) return fail(c, EB200_E_ARG, "bad argument");
+  *n = c->species[isp].n;
+  return 0;
+}
+int32_t eb200_download_particles(eb200_ctx* c, int32_t isp, int64_t first, int64_t capacity, double* packed,
+                                 int32_t nvar, int64_t* n_out) {
+  CHECK_CTX(c);
+  EB_TRY(check_species(c, isp, nvar));
+  if (first < 0 || capacity < 0 || (capacity > 0 && !packed)) return fail(c, EB200_E_ARG, "bad particle buffer");
+  long long got = 0;
+  EB_TRY(get_particles(c, isp, first, capacity, packed, nvar, &got));
+  if (n_out) *n_out = got;
+  return 0;
+}
+
+int32_t eb200_upload_fields(eb200_ctx* c, const double* ex, const double* ey, const double* ez, const double* bx,
+                            const double* by, const double* bz, const double* jx, const double* jy, const double* jz) {
+  CHECK_CTX(c); NEED_GRID(c);
+  const double* src[NFIELD] = {ex, ey, ez, bx, by, bz, jx, jy, jz};
+  for (int f = 0; f < NFIELD; ++f)
+    if (src[f]) EB_CUDA(c, cudaMemcpyAsync(c->f.f[f], src[f], (size_t)c->g.total * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));   // host buffers are not retained past the call
+  return 0;
+}
+int32_t eb200_download_fields(eb200_ctx* c, double* ex, double* ey, double* ez, double* bx, double* by, double* bz,
+                              double* jx, double* jy, double* jz) {
+  CHECK_CTX(c); NEED_GRID(c);
+  double* dst[NFIELD] = {ex, ey, ez, bx, by, bz, jx, jy, jz};
+  for (int f = 0; f < NFIELD; ++f)
+    if (dst[f]) EB_CUDA(c, cudaMemcpyAsync(dst[f], c->f.f[f], (size_t)c->g.total * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int32_t eb200_set_laser(eb200_ctx* c, int32_t boundary, int32_t id, double amp, double pol_angle, double t_start,
+                        double t_end, const double* profile, const double* phase) {
+  CHECK_CTX(c); NEED_GRID(c);
+  if (boundary < 1 || boundary > 2 * c->ndims) return fail(c, EB200_E_ARG, "boundary must be 1..2*ndims");
+  const int b = boundary - 1, a = b / 2;
+  size_t plane = 1;
+  for (int d = 0; d < c->ndims; ++d) if (d != a) plane *= (size_t)(c->g.n[d] + 1);
+  Laser* L = nullptr;
+  for (Laser& l : c->lasers[b]) if (l.id == id) L = &l;
+  if (!L) { c->lasers[b].emplace_back(); L = &c->lasers[b].back(); L->id = id; }
+  L->amp = amp; L->pol = pol_angle; L->t_start = t_start; L->t_end = t_end; L->plane = plane;
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (L->profile) { cudaFree(L->profile); L->profile = nullptr; }
+  if (L->phase) { cudaFree(L->phase); L->phase = nullptr; }
+  if (profile) {
+    EB_CUDA(c, cudaMalloc(&L->profile, plane * sizeof(double)));
+    EB_CUDA(c, cudaMemcpy(L->profile, profile, plane * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  if (phase) {
+    EB_CUDA(c, cudaMalloc(&L->phase, plane * sizeof(double)));
+    EB_CUDA(c, cudaMemcpy(L->phase, phase, plane * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  return 0;
+}
+int32_t eb200_set_laser_step(eb200_ctx* c, int32_t boundary, int32_t id, double t_env, double integral_phase) {
+  CHECK_CTX(c);
+  if (boundary < 1 || boundary > 6) return fail(c, EB200_E_ARG, "bad boundary");
+  for (Laser& l : c->lasers[boundary - 1])
+    if (l.id == id) { l.t_env = t_env; l.integral_phase = integral_phase; return 0; }
+  return fail(c, EB200_E_ARG, "laser id has not been set on this boundary");
+}
+
+int32_t eb200_update_eb_fields_half(eb200_ctx* c) {
+  CHECK_CTX(c); NEED_GRID(c); NEED_DT(c);
+  // fields.f90:819-847
+  EB_TRY(update_e_field(c));
+  EB_TRY(efield_bcs(c));
+  EB_TRY(update_b_field(c));
+  return bfield_bcs(c, true);
+}
+int32_t eb200_update_eb_fields_final(eb200_ctx* c) {
+  CHECK_CTX(c); NEED_GRID(c); NEED_DT(c);
+  // fields.f90:851-872
+  EB_TRY(update_b_field(c));
+  EB_TRY(bfield_final_bcs(c));
+  EB_TRY(update_e_field(c));
+  return efield_bcs(c);
+}
+int32_t eb200_push_particles(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); NEED_DT(c); return push_particles(c); }
+int32_t eb200_current_finish(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); return current_finish(c); }
+int32_t eb200_particle_bcs(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); NEED_DT(c); return particle_bcs(c); }
+int32_t eb200_efield_bcs(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); return efield_bcs(c); }
+int32_t eb200_bfield_final_bcs(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); NEED_DT(c); return bfield_final_bcs(c); }
+
+int32_t eb200_energy(eb200_ctx* c, double* fe, double* per_species) { CHECK_CTX(c); NEED_GRID(c); return energy(c, fe, per_species); }
+int32_t eb200_charge_residual(eb200_ctx* c, double* max_res, double* max_rho) {
+  CHECK_CTX(c); NEED_GRID(c); NEED_DT(c);
+  return charge_residual(c, max_res, max_rho, false);
+}
+
+int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
+  CHECK_CTX(c);
+  if (!key || !value) return fail(c, EB200_E_ARG, "null");
+  const std::string k(key), v(value);
+  if (k == "capture_charge_reference") { NEED_GRID(c); NEED_DT(c); double a, b; return charge_residual(c, &a, &b, true); }
+  if (k == "push_kernel") {
+    if (v == "auto") c->push_kernel = 0; else if (v == "baseline") c->push_kernel = 1; else if (v == "tiled") c->push_kernel = 2;
+    else return fail(c, EB200_E_ARG, "push_kernel: auto|baseline|tiled");
+    return 0;
+  }
+  if (k == "deterministic_deposit") { c->deterministic = atoi(value) != 0; return 0; }
+  if (k == "sort_every") { c->sort_every = atoi(value) < 1 ? 1 : atoi(value); return 0; }
+  if (k == "timers") { c->timers_on = atoi(value) != 0; return 0; }
+  if (k == "mig_capacity") { c->mig_min_particles = atoll(value); return 0; }
+  return fail(c, EB200_E_ARG, "unknown option " + k);
+}
+
+int32_t eb200_sync(eb200_ctx* c) {
+  CHECK_CTX(c);
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int32_t eb200_timer(eb200_ctx* c, const char* phase, int32_t reset, double* ms, int64_t* launches) {
+  CHECK_CTX(c);
+  if (!phase) return fail(c, EB200_E_ARG, "null");
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  const std::string k(phase);
+  if (k == "launches") {   // total kernels launched by this context
+    if (ms) *ms = 0;
+    if (launches) *launches = c->launches;
+    if (reset) c->launches = 0;
+    return 0;
+  }
+  PhaseTimer& t = c->timers[k];
+  for (auto& ev : t.ev) {
+    float f = 0;
+    cudaEventElapsedTime(&f, ev.first, ev.second);
+    t.ms += f;
+    cudaEventDestroy(ev.first); cudaEventDestroy(ev.second);
+  }
+  t.ev.clear();
+  if (ms) *ms = t.ms;
+  if (launches) *launches = t.launches;
+  if (reset) { t.ms = 0; t.launches = 0; }
+  return 0;
+}
+
+const char* eb200_last_error(eb200_ctx* c) { return c ? c->err.c_str() : g_last_error.c_str(); }
+const char* eb200_version(void) { return "epoch_b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,176 @@
+// ctx.cuh -- context, device parameter blocks and helpers shared by all kernels.
+// B200-native (sm_100a) implementation of EPOCH's PIC hot path; see DESIGN.md.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include <map>
+#include "../../include/epoch_b200.h"
+
+namespace eb {
+
+// constants.F90:144-151 (CODATA-2010 era literals, as the reference)
+constexpr double PI = 3.141592653589793238462643383279503;
+constexpr double C0 = 2.99792458e8;
+constexpr double EPS0 = 8.854187817620389850536563031710750e-12;
+
+enum { EX = 0, EY, EZ, BX, BY, BZ, JX, JY, JZ, NFIELD };
+enum { SHAPE_TOPHAT = 0, SHAPE_TRIANGLE = 1, SHAPE_BSPLINE3 = 2 };
+
+// Grid description passed by value to kernels.  Arrays are Fortran shaped with
+// ghosts, x fastest; dims that do not exist have n=1, ngd=0.
+struct GridP {
+  int ndims, shape, ng;
+  int n[3];
+  int ngd[3];
+  long long st[3];
+  long long total;
+  double d[3], id[3];
+  double gml[3];          // x_grid_min_local (centre of local cell 1)
+  double min_local[3], max_local[3];
+  double gmin[3], gmax[3];
+  // extended cell grid used for sort keys: cells (1-KM .. n+KM) per existing dim
+  int kn[3];              // extended extents
+  long long ncell_ext;
+  __host__ __device__ inline long long idx(int i, int j, int k) const {
+    return (long long)(i + ngd[0] - 1) * st[0] + (long long)(j + ngd[1] - 1) * st[1] +
+           (long long)(k + ngd[2] - 1) * st[2];
+  }
+};
+constexpr int KM = 3;                    // key-grid margin in cells
+constexpr uint32_t KEY_INVALID = 0xFFFFFFFFu;
+
+struct FieldP { double* f[NFIELD]; };
+
+// per-species device storage: structure of arrays, fp64
+struct SpeciesD {
+  bool defined = false;
+  double charge = 0, mass = 0, weight = 0;
+  int immobile = 0, zero_current = 0, species_type = 0;
+  int bc[6] = {1, 1, 1, 1, 1, 1};
+  long long n = 0;          // live particles (valid after the last compaction)
+  long long cap = 0;        // allocated slots per attribute
+  double* a[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // x,y,z,px,py,pz,w
+  uint32_t* key = nullptr;  // sort key per slot
+  uint32_t* dest = nullptr; // destination index per slot
+  bool sorted = false;      // keys/cell_start valid for the current positions
+};
+
+struct Laser {
+  int id = 0;
+  double amp = 0, pol = 0, t_start = 0, t_end = 0, t_env = 0, integral_phase = 0;
+  double* profile = nullptr;   // device planes (or null)
+  double* phase = nullptr;
+  size_t plane = 0;
+};
+
+struct PhaseTimer {
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev;
+  double ms = 0;
+  long long launches = 0;
+};
+
+struct Nccl;  // comm.cu
+
+}  // namespace eb
+
+struct eb200_ctx {
+  int ndims = 3, shape = 1, device = 0;
+  int rank = 0, nproc = 1, nprocdir[3] = {1, 1, 1}, coords[3] = {0, 0, 0};
+  bool min_bnd[3] = {true, true, true}, max_bnd[3] = {true, true, true};
+  int nbr_lo[3] = {-1, -1, -1}, nbr_hi[3] = {-1, -1, -1};  // cartesian neighbours (rank or -1)
+  int sf_min = -1, sf_max = 1, png = 3, ng = 5;
+  bool grid_set = false;
+  eb::GridP g;
+  int nglob[3] = {1, 1, 1}, nglob_min[3] = {1, 1, 1};
+  double dt = 0, time = 0;
+  int step = 0;
+  int bc_field[6] = {1, 1, 1, 1, 1, 1};
+  bool add_laser[6] = {false, false, false, false, false, false};
+  int field_order = 2, maxwell_solver = 0;
+  double coeffs[15] = {0};
+  double* fbase = nullptr;     // 9 * total doubles
+  eb::FieldP f;
+  std::vector<eb::SpeciesD> species;
+  std::vector<eb::Laser> lasers[6];
+  cudaStream_t stream = nullptr;
+  std::string err;
+  // scratch
+  double* attr_scratch = nullptr; long long attr_scratch_cap = 0;   // one attribute array for the sort ping-pong
+  uint32_t* cell_count = nullptr;   // ncell_ext + 2 (last bucket = invalid)
+  uint32_t* cell_start = nullptr;   // ncell_ext + 2
+  long long cell_cap = 0;
+  void* cub_tmp = nullptr; size_t cub_tmp_bytes = 0;
+  double* halo_send = nullptr; double* halo_recv = nullptr; size_t halo_bytes = 0;
+  double* mig_send[2] = {nullptr, nullptr}; double* mig_recv[2] = {nullptr, nullptr};
+  long long mig_cap = 0;
+  long long mig_min_particles = 1 << 16;   // option mig_capacity
+  unsigned long long* d_counters = nullptr;   // small device scalar block (64 x u64)
+  unsigned long long* h_counters = nullptr;   // pinned mirror
+  double* d_red = nullptr;                    // reductions (64 doubles)
+  double* h_red = nullptr;
+  double* res_ref = nullptr;                  // captured charge residual
+  double* rho = nullptr;
+  // options
+  int push_kernel = 0;          // 0 auto, 1 baseline, 2 tiled
+  int deterministic = 0;
+  int sort_every = 1;
+  bool timers_on = false;
+  std::map<std::string, eb::PhaseTimer> timers;
+  long long launches = 0;       // kernels launched (for gpu_launches accounting)
+  eb::Nccl* nccl = nullptr;
+};
+
+namespace eb {
+
+int32_t fail(eb200_ctx* c, int32_t code, const std::string& msg);
+#define EB_CUDA(c, call)                                                                 \
+  do {                                                                                   \
+    cudaError_t e__ = (call);                                                            \
+    if (e__ != cudaSuccess)                                                              \
+      return eb::fail((c), e__ == cudaErrorMemoryAllocation ? EB200_E_NOMEM : EB200_E_CUDA, \
+                      std::string(#call) + ": " + cudaGetErrorString(e__));              \
+  } while (0)
+#define EB_TRY(call)                 \
+  do {                               \
+    int32_t rc__ = (call);           \
+    if (rc__ != 0) return rc__;      \
+  } while (0)
+
+struct ScopedPhase {
+  eb200_ctx* c; const char* name; cudaEvent_t e0 = nullptr, e1 = nullptr; long long launches0 = 0;
+  ScopedPhase(eb200_ctx* c_, const char* n);
+  ~ScopedPhase();
+};
+
+// fdtd.cu
+int32_t update_e_field(eb200_ctx* c);
+int32_t update_b_field(eb200_ctx* c);
+// bcs.cu
+int32_t field_bc(eb200_ctx* c, int first_comp, int ncomp);       // halo exchange of ncomp consecutive components
+int32_t efield_bcs(eb200_ctx* c);
+int32_t bfield_bcs(eb200_ctx* c, bool mpi_only);
+int32_t bfield_final_bcs(eb200_ctx* c);
+int32_t current_finish(eb200_ctx* c);
+int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir);  // processor_summation_bcs on one array
+// comm.cu
+int32_t nccl_unique_id(void* out128);
+int32_t comm_init(eb200_ctx* c, const void* id);
+void comm_destroy(eb200_ctx* c);
+// exchange `count` doubles with the low/high neighbours along an axis: send_lo goes to nbr_lo and
+// recv_hi comes from nbr_hi (first call), etc.  Null neighbours are skipped.
+int32_t comm_sendrecv(eb200_ctx* c, const double* send, int dst, double* recv, int src, size_t count);
+int32_t comm_sendrecv_v(eb200_ctx* c, const double* send, int dst, size_t nsend, double* recv, int src, size_t nrecv);
+// particles.cu
+int32_t push_particles(eb200_ctx* c);
+int32_t particle_bcs(eb200_ctx* c);
+int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need);
+int32_t add_particles(eb200_ctx* c, int isp, long long n, const double* packed, int nvar, bool replace);
+int32_t get_particles(eb200_ctx* c, int isp, long long first, long long cap, double* packed, int nvar, long long* n_out);
+int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots);
+// reduce.cu
+int32_t energy(eb200_ctx* c, double* fe, double* per_species);
+int32_t charge_residual(eb200_ctx* c, double* max_res, double* max_rho, bool capture);
+
+}  // namespace eb

@@ -1,0 +1,473 @@
+// particles.cu -- particle container (cell-sorted structure of arrays, fp64),
+// push_particles orchestration, per-step counting sort, particle boundary
+// conditions and migration.  Replaces the linked-list container and wire format of
+// housekeeping/partlist.F90 (:353-553,:808-862), push_particles' driver part
+// (particles.F90:147-212,609-612) and particle_bcs (boundary.F90:1316-1972).
+#include "push_common.cuh"
+#include <cub/device/device_scan.cuh>
+#include <algorithm>
+
+namespace eb {
+
+int32_t launch_push_baseline(eb200_ctx* c, const SpeciesD& sp, const PushP& p);   // push_baseline.cu
+int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled);  // push_tiled.cu
+
+// ---------------------------------------------------------------------------------
+// storage
+// ---------------------------------------------------------------------------------
+template <class T>
+static int32_t regrow(eb200_ctx* c, T*& ptr, long long old_n, long long new_cap) {
+  T* np = nullptr;
+  EB_CUDA(c, cudaMalloc(&np, (size_t)new_cap * sizeof(T)));
+  if (ptr && old_n > 0) EB_CUDA(c, cudaMemcpyAsync(np, ptr, (size_t)old_n * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
+  if (ptr) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(ptr); }
+  ptr = np;
+  return 0;
+}
+
+int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need) {
+  if (need <= sp.cap) return 0;
+  long long ncap = std::max<long long>(need + need / 32 + 1024, 4096);
+  const int nattr = c->ndims + 4;
+  // attributes live in a[0..ndims-1] (pos), a[3..5] (p), a[6] (w)
+  for (int k = 0; k < 7; ++k) {
+    if (k < 3 && k >= c->ndims) continue;
+    EB_TRY(regrow(c, sp.a[k], sp.n, ncap));
+  }
+  (void)nattr;
+  EB_TRY(regrow(c, sp.key, sp.n, ncap));
+  EB_TRY(regrow(c, sp.dest, 0, ncap));
+  sp.cap = ncap;
+  return 0;
+}
+
+// AoS (partlist wire format) <-> SoA
+__global__ void k_unpack_aos(const double* __restrict__ packed, int nd, long long n, long long off,
+                             double* x, double* y, double* z, double* px, double* py, double* pz, double* w,
+                             uint32_t* key) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double* q = packed + i * (nd + 4);
+  x[off + i] = q[0];
+  if (nd >= 2) y[off + i] = q[1];
+  if (nd >= 3) z[off + i] = q[2];
+  px[off + i] = q[nd]; py[off + i] = q[nd + 1]; pz[off + i] = q[nd + 2];
+  w[off + i] = q[nd + 3];
+  key[off + i] = 0;
+}
+__global__ void k_pack_aos(double* __restrict__ packed, int nd, long long n, long long off,
+                           const double* x, const double* y, const double* z, const double* px,
+                           const double* py, const double* pz, const double* w) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double* q = packed + i * (nd + 4);
+  q[0] = x[off + i];
+  if (nd >= 2) q[1] = y[off + i];
+  if (nd >= 3) q[2] = z[off + i];
+  q[nd] = px[off + i]; q[nd + 1] = py[off + i]; q[nd + 2] = pz[off + i];
+  q[nd + 3] = w[off + i];
+}
+
+static int32_t ensure_stage(eb200_ctx* c, long long doubles) {
+  if (c->mig_cap >= doubles) return 0;
+  for (int s = 0; s < 2; ++s) {
+    if (c->mig_send[s]) cudaFree(c->mig_send[s]);
+    if (c->mig_recv[s]) cudaFree(c->mig_recv[s]);
+    c->mig_send[s] = c->mig_recv[s] = nullptr;
+  }
+  c->mig_cap = 0;
+  for (int s = 0; s < 2; ++s) {
+    EB_CUDA(c, cudaMalloc(&c->mig_send[s], (size_t)doubles * sizeof(double)));
+    EB_CUDA(c, cudaMalloc(&c->mig_recv[s], (size_t)doubles * sizeof(double)));
+  }
+  c->mig_cap = doubles;
+  return 0;
+}
+
+int32_t add_particles(eb200_ctx* c, int isp, long long n, const double* packed, int nvar, bool replace) {
+  SpeciesD& sp = c->species[isp];
+  if (replace) sp.n = 0;
+  if (n == 0) { sp.sorted = false; return 0; }
+  EB_TRY(species_reserve(c, sp, sp.n + n));
+  const long long chunk = std::min<long long>(n, 4LL << 20);   // <= 4M particles per staging copy
+  EB_TRY(ensure_stage(c, std::max<long long>(chunk * nvar, 1 << 16)));
+  for (long long done = 0; done < n; done += chunk) {
+    const long long m = std::min(chunk, n - done);
+    EB_CUDA(c, cudaMemcpyAsync(c->mig_recv[0], packed + done * nvar, (size_t)m * nvar * sizeof(double),
+                               cudaMemcpyHostToDevice, c->stream));
+    k_unpack_aos<<<(unsigned)((m + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[0], c->ndims, m, sp.n + done,
+        sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
+    c->launches++;
+    // the staging buffer is reused by the next chunk
+    EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  sp.n += n;
+  sp.sorted = false;
+  return 0;
+}
+
+int32_t get_particles(eb200_ctx* c, int isp, long long first, long long cap, double* packed, int nvar, long long* n_out) {
+  SpeciesD& sp = c->species[isp];
+  const long long n = std::max<long long>(0, std::min(sp.n - first, cap));
+  const long long chunk = std::min<long long>(std::max<long long>(n, 1), 4LL << 20);
+  EB_TRY(ensure_stage(c, std::max<long long>(chunk * nvar, 1 << 16)));
+  for (long long done = 0; done < n; done += chunk) {
+    const long long m = std::min(chunk, n - done);
+    k_pack_aos<<<(unsigned)((m + 255) / 256), 256, 0, c->stream>>>(c->mig_send[0], c->ndims, m, first + done,
+        sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6]);
+    c->launches++;
+    EB_CUDA(c, cudaMemcpyAsync(packed + done * nvar, c->mig_send[0], (size_t)m * nvar * sizeof(double),
+                               cudaMemcpyDeviceToHost, c->stream));
+    EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  if (n_out) *n_out = n;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------
+// per-step counting sort by the cell the NEXT push will gather from
+// ---------------------------------------------------------------------------------
+// key = extended-grid linear index of (cell_x1, cell_y1, cell_z1) evaluated exactly
+// as the push does (half drift with the stored momentum, particles.F90:242-291).
+template <int ND, int SHAPE>
+__global__ void k_keys(GridP g, PushP p, const double* __restrict__ X, const double* __restrict__ Y,
+                       const double* __restrict__ Z, const double* __restrict__ PX,
+                       const double* __restrict__ PY, const double* __restrict__ PZ, uint32_t* key) {
+  const long long ip = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (ip >= p.n) return;
+  if (key[ip] == KEY_INVALID) return;
+  const double* POS[3] = {X, Y, Z};
+  const double ux = PX[ip] * p.ipart_mc, uy = PY[ip] * p.ipart_mc, uz = PZ[ip] * p.ipart_mc;
+  const double root = p.dtco2 / sqrt(ux * ux + uy * uy + uz * uz + 1.0);
+  const double u0[3] = {ux, uy, uz};
+  uint32_t k = 0, mul = 1;
+#pragma unroll
+  for (int d = 0; d < ND; ++d) {
+    const double px = (POS[d][ip] - p.gml[d]) + u0[d] * root;
+    const double cr = SHAPE == SHAPE_TOPHAT ? px * p.idx[d] - 0.5 : px * p.idx[d];
+    double frac;
+    int cell = cell_round(cr, frac);          // 1-based
+    int e = cell - (1 - KM);
+    e = e < 0 ? 0 : (e >= g.kn[d] ? g.kn[d] - 1 : e);
+    k += mul * (uint32_t)e;
+    mul *= (uint32_t)g.kn[d];
+  }
+  key[ip] = k;
+}
+
+// warp-aggregated histogram / rank: sorted input => few distinct keys per warp
+__global__ void k_hist(const uint32_t* __restrict__ key, long long n, uint32_t* count, uint32_t nbucket) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool act = i < n;
+  const unsigned am = __ballot_sync(0xffffffffu, act);
+  if (!act) return;
+  uint32_t k = key[i];
+  if (k == KEY_INVALID) k = nbucket - 1;
+  const unsigned peers = __match_any_sync(am, k);
+  const int leader = __ffs(peers) - 1;
+  if ((threadIdx.x & 31) == leader) atomicAdd(count + k, (uint32_t)__popc(peers));
+}
+__global__ void k_dest(const uint32_t* __restrict__ key, long long n, const uint32_t* __restrict__ start,
+                       uint32_t* cursor, uint32_t* dest, uint32_t nbucket) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool act = i < n;
+  const unsigned am = __ballot_sync(0xffffffffu, act);
+  if (!act) return;
+  uint32_t k = key[i];
+  if (k == KEY_INVALID) k = nbucket - 1;
+  const unsigned peers = __match_any_sync(am, k);
+  const int lane = threadIdx.x & 31;
+  const int leader = __ffs(peers) - 1;
+  uint32_t base = 0;
+  if (lane == leader) base = atomicAdd(cursor + k, (uint32_t)__popc(peers));
+  base = __shfl_sync(peers, base, leader);
+  dest[i] = start[k] + base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+}
+__global__ void k_permute(const double* __restrict__ src, double* __restrict__ dst,
+                          const uint32_t* __restrict__ dest, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[dest[i]] = src[i];
+}
+__global__ void k_fill_u32(uint32_t* a, long long n, uint32_t v) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) a[i] = v;
+}
+
+static PushP make_push_params(eb200_ctx* c, const SpeciesD& sp, long long n) {
+  PushP p;
+  const int nd = c->ndims;
+  const double fac = shape_fac(c->shape, nd);
+  p.n = n;
+  for (int d = 0; d < 3; ++d) { p.idx[d] = 1.0 / c->g.d[d]; p.gml[d] = c->g.gml[d]; }
+  const double idt = 1.0 / c->dt;
+  p.dto2 = c->dt / 2.0;
+  p.dtco2 = C0 * p.dto2;
+  const double dtfac = 0.5 * c->dt * fac;
+  p.q = sp.charge;
+  p.part_mc = C0 * sp.mass;
+  p.ipart_mc = 1.0 / p.part_mc;
+  p.cmratio = p.q * dtfac * p.ipart_mc;
+  p.ccmratio = C0 * p.cmratio;
+  if (nd == 3) { p.fc[0] = idt * p.idx[1] * p.idx[2] * fac; p.fc[1] = idt * p.idx[0] * p.idx[2] * fac; p.fc[2] = idt * p.idx[0] * p.idx[1] * fac; }
+  else if (nd == 2) { p.fc[0] = idt * p.idx[1] * fac; p.fc[1] = idt * p.idx[0] * fac; p.fc[2] = p.idx[0] * p.idx[1] * fac; }
+  else { p.fc[0] = idt * fac; p.fc[1] = p.idx[0] * fac; p.fc[2] = 0.0; }
+  p.zero_current = sp.zero_current;
+  return p;
+}
+
+static int32_t ensure_cells(eb200_ctx* c) {
+  const long long need = c->g.ncell_ext + 2;
+  if (c->cell_cap >= need) return 0;
+  if (c->cell_count) cudaFree(c->cell_count);
+  if (c->cell_start) cudaFree(c->cell_start);
+  c->cell_count = c->cell_start = nullptr; c->cell_cap = 0;
+  EB_CUDA(c, cudaMalloc(&c->cell_count, (size_t)need * sizeof(uint32_t)));
+  EB_CUDA(c, cudaMalloc(&c->cell_start, (size_t)need * sizeof(uint32_t)));
+  c->cell_cap = need;
+  return 0;
+}
+
+// sort slots [0, n_slots) of a species; dead slots (key == KEY_INVALID) go last
+// and are dropped.  `need_count`: read the live count back (it can only change
+// when particles were removed or appended).
+int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
+  ScopedPhase ph(c, "sort");
+  if (n_slots == 0) { sp.n = 0; sp.sorted = true; return 0; }
+  if (n_slots >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "more than 2^32 particles per species per GPU");
+  EB_TRY(ensure_cells(c));
+  const uint32_t nbucket = (uint32_t)(c->g.ncell_ext + 1);   // last = invalid
+  const int B = 256;
+  const unsigned gp = (unsigned)((n_slots + B - 1) / B);
+  PushP p = make_push_params(c, sp, n_slots);
+#define LK(ND, SH)                                                                               \
+  if (c->ndims == ND && c->shape == SH)                                                          \
+    k_keys<ND, SH><<<gp, B, 0, c->stream>>>(c->g, p, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.key);
+  LK(1, 0) LK(1, 1) LK(1, 2) LK(2, 0) LK(2, 1) LK(2, 2) LK(3, 0) LK(3, 1) LK(3, 2)
+#undef LK
+  EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
+  k_hist<<<gp, B, 0, c->stream>>>(sp.key, n_slots, c->cell_count, nbucket);
+  size_t tmp = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tmp, c->cell_count, c->cell_start, (int)(nbucket + 1), c->stream);
+  if (tmp > c->cub_tmp_bytes) {
+    if (c->cub_tmp) cudaFree(c->cub_tmp);
+    c->cub_tmp = nullptr; c->cub_tmp_bytes = 0;
+    EB_CUDA(c, cudaMalloc(&c->cub_tmp, tmp));
+    c->cub_tmp_bytes = tmp;
+  }
+  cub::DeviceScan::ExclusiveSum(c->cub_tmp, tmp, c->cell_count, c->cell_start, (int)(nbucket + 1), c->stream);
+  EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
+  k_dest<<<gp, B, 0, c->stream>>>(sp.key, n_slots, c->cell_start, c->cell_count, sp.dest, nbucket);
+  c->launches += 5;
+  // scatter each attribute through one spare array; the spare rotates
+  if (c->attr_scratch_cap < sp.cap) {
+    if (c->attr_scratch) cudaFree(c->attr_scratch);
+    c->attr_scratch = nullptr; c->attr_scratch_cap = 0;
+    EB_CUDA(c, cudaMalloc(&c->attr_scratch, (size_t)sp.cap * sizeof(double)));
+    c->attr_scratch_cap = sp.cap;
+  }
+  for (int k = 0; k < 7; ++k) {
+    if (k < 3 && k >= c->ndims) continue;
+    if (c->attr_scratch_cap != sp.cap) {
+      // spare and attribute must be interchangeable: same capacity
+      if (c->attr_scratch) cudaFree(c->attr_scratch);
+      c->attr_scratch = nullptr; c->attr_scratch_cap = 0;
+      EB_CUDA(c, cudaMalloc(&c->attr_scratch, (size_t)sp.cap * sizeof(double)));
+      c->attr_scratch_cap = sp.cap;
+    }
+    k_permute<<<gp, B, 0, c->stream>>>(sp.a[k], c->attr_scratch, sp.dest, n_slots);
+    std::swap(sp.a[k], c->attr_scratch);
+    c->launches++;
+  }
+  // live count = start of the invalid bucket
+  EB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->cell_start + (nbucket - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  sp.n = (long long)(*(uint32_t*)c->h_counters);
+  // keys of the live range are now implied by cell_start; reset them to "valid"
+  k_fill_u32<<<(unsigned)((n_slots + B - 1) / B), B, 0, c->stream>>>(sp.key, n_slots, 0u);
+  c->launches++;
+  sp.sorted = true;
+  EB_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------
+// particle boundary conditions (one axis at a time: x, then y, then z)
+// ---------------------------------------------------------------------------------
+struct BcP {
+  int axis, min_bnd, max_bnd, bc_min, bc_max, multi;   // multi: nprocdir[axis] > 1
+  double min_local, max_local, gmin, gmax, min_outer, max_outer, shift;
+};
+// flags: dest[i] = 0 stay, 1 send to low neighbour, 2 send to high neighbour
+__global__ void k_particle_bc(BcP b, long long n, double* __restrict__ pos, double* __restrict__ mom,
+                              uint32_t* key, uint32_t* flag, unsigned long long* counters) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (key[i] == KEY_INVALID) { if (b.multi) flag[i] = 0; return; }
+  const double part_pos = pos[i];
+  int xbd = 0;
+  bool out = false;
+  if (part_pos < b.min_local) {
+    xbd = -1;
+    if (b.min_bnd) {
+      xbd = 0;
+      if (b.bc_min == EB200_BC_REFLECT) { pos[i] = 2.0 * b.gmin - part_pos; mom[i] = -mom[i]; }
+      else if (b.bc_min == EB200_BC_PERIODIC) { xbd = -1; pos[i] = part_pos + b.shift; }
+      if (part_pos < b.min_outer && b.bc_min != EB200_BC_PERIODIC) out = true;
+    }
+  }
+  if (part_pos >= b.max_local) {
+    xbd = 1;
+    if (b.max_bnd) {
+      xbd = 0;
+      if (b.bc_max == EB200_BC_REFLECT) { pos[i] = 2.0 * b.gmax - part_pos; mom[i] = -mom[i]; }
+      else if (b.bc_max == EB200_BC_PERIODIC) { xbd = 1; pos[i] = part_pos - b.shift; }
+      if (part_pos >= b.max_outer && b.bc_max != EB200_BC_PERIODIC) out = true;
+    }
+  }
+  if (out) { key[i] = KEY_INVALID; atomicAdd(counters + 2, 1ULL); xbd = 0; }
+  if (b.multi) {
+    flag[i] = xbd < 0 ? 1u : (xbd > 0 ? 2u : 0u);
+    if (xbd != 0) atomicAdd(counters + (xbd < 0 ? 0 : 1), 1ULL);
+  }
+}
+// pack flagged particles into the per-side AoS send buffers and free their slots
+__global__ void k_pack_leavers(long long n, int nd, const double* x, const double* y, const double* z,
+                               const double* px, const double* py, const double* pz, const double* w,
+                               uint32_t* key, const uint32_t* flag, unsigned long long* cursors,
+                               double* send_lo, double* send_hi) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t f = flag[i];
+  if (f == 0) return;
+  const unsigned long long slot = atomicAdd(cursors + (f == 1 ? 3 : 4), 1ULL);
+  double* q = (f == 1 ? send_lo : send_hi) + slot * (nd + 4);
+  q[0] = x[i];
+  if (nd >= 2) q[1] = y[i];
+  if (nd >= 3) q[2] = z[i];
+  q[nd] = px[i]; q[nd + 1] = py[i]; q[nd + 2] = pz[i]; q[nd + 3] = w[i];
+  key[i] = KEY_INVALID;
+}
+
+static int32_t read_counters(eb200_ctx* c, int n) {
+  EB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+// applies particle_bcs to slots [0, n_slots) of one species; returns the new slot
+// count (arrivals are appended) and whether the live count may have changed
+static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool& changed) {
+  const GridP& g = c->g;
+  const int nvar = c->ndims + 4;
+  for (int ax = 0; ax < c->ndims; ++ax) {
+    BcP b;
+    b.axis = ax; b.min_bnd = c->min_bnd[ax]; b.max_bnd = c->max_bnd[ax];
+    b.bc_min = sp.bc[2 * ax]; b.bc_max = sp.bc[2 * ax + 1];
+    b.multi = c->nprocdir[ax] > 1;
+    b.min_local = g.min_local[ax]; b.max_local = g.max_local[ax];
+    b.gmin = g.gmin[ax]; b.gmax = g.gmax[ax];
+    const double boundary_shift = g.d[ax] * (double)((1 + c->png + 0) / 2);   // boundary.F90:1336-1338
+    b.min_outer = b.gmin - boundary_shift; b.max_outer = b.gmax + boundary_shift;
+    b.shift = (b.gmax - b.gmin);                                             // x_shift, cpml_thickness = 0
+    const bool open_here = (b.min_bnd && b.bc_min == EB200_BC_OPEN) || (b.max_bnd && b.bc_max == EB200_BC_OPEN);
+    if (n_slots > 0 || b.multi) {
+      if (b.multi || open_here) EB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
+      if (n_slots > 0) {
+        k_particle_bc<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(b, n_slots, sp.a[ax], sp.a[3 + ax],
+            sp.key, sp.dest, c->d_counters);
+        c->launches++;
+      }
+    }
+    if (open_here) changed = true;
+    if (!b.multi) continue;
+    changed = true;
+    EB_TRY(read_counters(c, 3));
+    const long long nlo = (long long)c->h_counters[0], nhi = (long long)c->h_counters[1];
+    EB_TRY(ensure_stage(c, std::max<long long>(std::max<long long>(4 * std::max(nlo, nhi), c->mig_min_particles) * nvar, 1 << 16)));
+    if (nlo + nhi > 0) {
+      k_pack_leavers<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(n_slots, c->ndims, sp.a[0], sp.a[1], sp.a[2],
+          sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key, sp.dest, c->d_counters, c->mig_send[0], c->mig_send[1]);
+      c->launches++;
+    }
+    // exchange counts (as doubles, exact below 2^53), then payloads; low side first.
+    // A particle leaves through a physical boundary only if that boundary is periodic
+    // (xbd is reset to 0 otherwise), so the wrap-around neighbours are always valid.
+    const int lo = c->nbr_lo[ax], hi = c->nbr_hi[ax];
+    double* cnt = c->d_red;     // [0] my->lo, [1] my->hi, [2] from hi, [3] from lo
+    const double hc[2] = {(double)nlo, (double)nhi};
+    EB_CUDA(c, cudaMemcpyAsync(cnt, hc, 2 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    EB_CUDA(c, cudaMemsetAsync(cnt + 2, 0, 2 * sizeof(double), c->stream));
+    EB_TRY(comm_sendrecv(c, cnt + 0, lo, cnt + 2, hi, 1));
+    EB_TRY(comm_sendrecv(c, cnt + 1, hi, cnt + 3, lo, 1));
+    EB_CUDA(c, cudaMemcpyAsync(c->h_red, cnt, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    EB_CUDA(c, cudaStreamSynchronize(c->stream));
+    const long long from_hi = (long long)c->h_red[2], from_lo = (long long)c->h_red[3];
+    // receive buffers are sized after the counts are known (send buffers were sized
+    // before packing and are separate allocations, so growing here would lose them)
+    if (std::max(from_hi, from_lo) * nvar > c->mig_cap)
+      return fail(c, EB200_E_NOMEM, "migration receive buffer too small; raise option mig_capacity");
+    // lo-bound leavers travel to `lo`; what arrives from `hi` are hi's lo-bound leavers
+    EB_TRY(comm_sendrecv_v(c, c->mig_send[0], nlo > 0 ? lo : -1, (size_t)nlo * nvar,
+                           c->mig_recv[0], from_hi > 0 ? hi : -1, (size_t)from_hi * nvar));
+    EB_TRY(comm_sendrecv_v(c, c->mig_send[1], nhi > 0 ? hi : -1, (size_t)nhi * nvar,
+                           c->mig_recv[1], from_lo > 0 ? lo : -1, (size_t)from_lo * nvar));
+    const long long arrivals = from_hi + from_lo;
+    if (arrivals > 0) {
+      const long long keep_n = sp.n;
+      sp.n = n_slots;                       // regrow copies [0, sp.n)
+      EB_TRY(species_reserve(c, sp, n_slots + arrivals));
+      sp.n = keep_n;
+      if (from_hi > 0) {
+        k_unpack_aos<<<(unsigned)((from_hi + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[0], c->ndims, from_hi, n_slots,
+            sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
+        n_slots += from_hi; c->launches++;
+      }
+      if (from_lo > 0) {
+        k_unpack_aos<<<(unsigned)((from_lo + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[1], c->ndims, from_lo, n_slots,
+            sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
+        n_slots += from_lo; c->launches++;
+      }
+    }
+  }
+  EB_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+int32_t particle_bcs(eb200_ctx* c) {
+  for (SpeciesD& sp : c->species) {
+    if (!sp.defined) continue;
+    long long n_slots = sp.n;
+    bool changed = false;
+    {
+      ScopedPhase ph(c, "bcs");
+      EB_TRY(species_bcs(c, sp, n_slots, changed));
+    }
+    EB_TRY(sort_species(c, sp, n_slots));
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------
+// push_particles (particles.F90:28-614)
+// ---------------------------------------------------------------------------------
+int32_t push_particles(eb200_ctx* c) {
+  // jx = jy = jz = 0 (particles.F90:147-149): one memset over the 3 contiguous arrays
+  {
+    ScopedPhase ph(c, "push");
+    EB_CUDA(c, cudaMemsetAsync(c->f.f[JX], 0, (size_t)3 * c->g.total * sizeof(double), c->stream));
+  }
+  for (SpeciesD& sp : c->species) {
+    if (!sp.defined || sp.immobile || sp.species_type == 1) continue;
+    if (!sp.sorted) EB_TRY(sort_species(c, sp, sp.n));
+    if (sp.n == 0) continue;
+    ScopedPhase ph(c, "push");
+    PushP p = make_push_params(c, sp, sp.n);
+    bool handled = false;
+    if (c->push_kernel != 1) EB_TRY(launch_push_tiled(c, sp, p, &handled));
+    if (!handled) EB_TRY(launch_push_baseline(c, sp, p));
+  }
+  // current_bcs(species) is a no-op without mixed per-species BCs (boundary.F90:1130-1136)
+  return particle_bcs(c);
+}
+
+}  // namespace eb

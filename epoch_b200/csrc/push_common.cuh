@@ -1,0 +1,88 @@
+// push_common.cuh -- device helpers shared by the push+deposit kernels.
+// Arithmetic follows epochNd/src/particles.F90 and include/*/{gx,hx_dcell}.inc
+// (SURVEY Appendix A.3-A.5).
+#pragma once
+#include "ctx.cuh"
+
+namespace eb {
+
+template <int SHAPE> struct Sh;
+template <> struct Sh<SHAPE_TOPHAT>   { static constexpr int NW = 2, SFMIN = 0; };
+template <> struct Sh<SHAPE_TRIANGLE> { static constexpr int NW = 3, SFMIN = -1; };
+template <> struct Sh<SHAPE_BSPLINE3> { static constexpr int NW = 5, SFMIN = -2; };
+
+// un-normalised 1-D weights W_s(f), slots SFMIN..SFMIN+NW-1
+template <int SHAPE>
+__device__ __forceinline__ void shape_weights(double f, double* w) {
+  if (SHAPE == SHAPE_TOPHAT) {            // tophat/gx.inc:3-4
+    w[0] = 0.5 + f;
+    w[1] = 0.5 - f;
+  } else if (SHAPE == SHAPE_TRIANGLE) {   // triangle/gx.inc:1-4
+    const double cf2 = f * f;
+    w[0] = 0.25 + cf2 + f;
+    w[1] = 1.5 - 2.0 * cf2;
+    w[2] = 0.25 + cf2 - f;
+  } else {                                // bspline3/gx.inc:3-10
+    const double cf2 = f * f;
+    double a = 0.5 + f; a = a * a;
+    w[0] = a * a;
+    w[1] = 4.75 + 11.0 * f + 4.0 * cf2 * (1.5 - f - cf2);
+    w[2] = 14.375 + 6.0 * cf2 * (cf2 - 2.5);
+    w[3] = 4.75 - 11.0 * f + 4.0 * cf2 * (1.5 + f - cf2);
+    double b = 0.5 - f; b = b * b;
+    w[4] = b * b;
+  }
+}
+
+// per-launch constants of push_particles (particles.F90:153-212)
+struct PushP {
+  long long n;
+  double idx[3];
+  double gml[3];
+  double dto2, dtco2;
+  double cmratio, ccmratio, part_mc, ipart_mc, q;
+  double fc[3];          // idtyz,idtxz,idtxy (3D) | idty,idtx,idxy (2D) | idtf,idxf,- (1D), without weight
+  int zero_current;
+};
+
+__host__ inline double shape_fac(int shape, int nd) {   // particles.F90:128-136
+  double fac = 1.0;
+  if (shape == SHAPE_BSPLINE3) for (int d = 0; d < nd; ++d) fac *= (1.0 / 24.0);
+  else if (shape == SHAPE_TRIANGLE) for (int d = 0; d < nd; ++d) fac *= 0.5;
+  return fac;
+}
+
+// nearest-node cell and fraction: cell = FLOOR(r+0.5); frac = cell - r; cell+1
+__device__ __forceinline__ int cell_round(double r, double& frac) {
+  const double fl = floor(r + 0.5);
+  frac = fl - r;
+  return (int)fl + 1;
+}
+// staggered cell: cell = FLOOR(r); frac = cell - r + 0.5; cell+1
+__device__ __forceinline__ int cell_floor(double r, double& frac) {
+  const double fl = floor(r);
+  frac = fl - r + 0.5;
+  return (int)fl + 1;
+}
+
+// Boris rotation (particles.F90:347-394); u is updated in place
+__device__ __forceinline__ void boris(double& ux, double& uy, double& uz, double ex, double ey, double ez,
+                                      double bx, double by, double bz, double cmratio, double ccmratio) {
+  const double uxm = ux + cmratio * ex, uym = uy + cmratio * ey, uzm = uz + cmratio * ez;
+  const double gamma_rel = sqrt(uxm * uxm + uym * uym + uzm * uzm + 1.0);
+  const double root = ccmratio / gamma_rel;
+  const double taux = bx * root, tauy = by * root, tauz = bz * root;
+  const double taux2 = taux * taux, tauy2 = tauy * tauy, tauz2 = tauz * tauz;
+  const double tau = 1.0 / (1.0 + taux2 + tauy2 + tauz2);
+  const double uxp = ((1.0 + taux2 - tauy2 - tauz2) * uxm
+      + 2.0 * ((taux * tauy + tauz) * uym + (taux * tauz - tauy) * uzm)) * tau;
+  const double uyp = ((1.0 - taux2 + tauy2 - tauz2) * uym
+      + 2.0 * ((tauy * tauz + taux) * uzm + (tauy * taux - tauz) * uxm)) * tau;
+  const double uzp = ((1.0 - taux2 - tauy2 + tauz2) * uzm
+      + 2.0 * ((tauz * taux + tauy) * uxm + (tauz * tauy - taux) * uym)) * tau;
+  ux = uxp + cmratio * ex;
+  uy = uyp + cmratio * ey;
+  uz = uzp + cmratio * ez;
+}
+
+}  // namespace eb

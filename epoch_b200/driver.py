@@ -211,7 +211,7 @@ class Simulation:
     def finished(self):
         return self.t_end is not None and self.time >= self.t_end
 
-    def step_once(self, output=None, push=True):
+    def step_once(self, output=None, push=True, after_half=None):
         """One iteration of the main DO loop (epoch3d.F90:184-249).  `output` is
         called where output_routines is (time = (n+1)*dt, fields at n+1/2)."""
         if not self._started:
@@ -219,6 +219,9 @@ class Simulation:
         ctx = self.ctx
         ctx.set_time(self.dt, self.time, self.step)
         ctx.update_eb_fields_half()
+        if after_half is not None:
+            # E, B at t+dt/2 and particles at x(t): div E = rho(x + half drift)/eps0 here
+            after_half(self)
         if push and self.species:
             ctx.push_particles()
             ctx.current_finish()

@@ -248,10 +248,16 @@ int32_t orc_energy(orc_ctx* c, double* fe, double* per_species) {
 }
 int32_t orc_charge_residual(orc_ctx* c, double* max_res, double* max_rho) {
   if (!c || !c->s.grid_set) return EB200_E_STATE;
-  charge_residual(c->s, max_res, max_rho);
+  charge_residual(c->s, max_res, max_rho, false);
   return 0;
 }
-int32_t orc_set_option(orc_ctx*, const char*, const char*) { return 0; }
+int32_t orc_set_option(orc_ctx* c, const char* key, const char*) {
+  if (c && key && std::string(key) == "capture_charge_reference") {
+    double a, b;
+    charge_residual(c->s, &a, &b, true);
+  }
+  return 0;
+}
 int32_t orc_sync(orc_ctx*) { return 0; }
 int32_t orc_timer(orc_ctx*, const char*, int32_t, double* ms, int64_t* launches) {
   if (ms) *ms = 0;

@@ -85,6 +85,7 @@ struct State {
   std::vector<Species> species;
   std::vector<Laser> lasers[6];
   std::string err;
+  std::vector<double> res_ref;   // captured div E - rho/eps0 (option capture_charge_reference)
 
   // linear index of Fortran (i,j,k) (1-based interior); missing dims use index 1
   inline int64_t idx(int i, int j, int k) const {
@@ -111,6 +112,6 @@ void current_finish(State& s);
 void push_particles(State& s);
 void particle_bcs(State& s);
 void energy(const State& s, double* field_energy, double* per_species);
-void charge_residual(const State& s, double* max_res, double* max_rho);
+void charge_residual(State& s, double* max_res, double* max_rho, bool capture);
 
 }  // namespace orc

@@ -1,0 +1,216 @@
+"""-m gpu: parity of the CUDA path (through the C ABI) against the CPU oracle on
+identical seeded decks, against the reference's golden sums, and through
+size-independent invariants.  Tolerances: fp64, 1e-12 relative (positions relative
+to the domain length, grid quantities norm-wise), as BASELINE.json's north_star
+states; golden sums at the reference's own np.isclose tolerance."""
+import numpy as np
+import pytest
+
+from helpers import make_plasma, SHAPE_NAMES, ALL9, FIELDS6, match_particles, relerr
+from test_oracle import (laser_1d, laser_2d, laser_3d, run_laser_deck, check_golden, GOLD_1D,
+                         GOLD_2D, GOLD_3D, femto)
+from epoch_b200.driver import Simulation, SpeciesSpec, Q0, M0, C
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+
+
+def compare_fields(a, b, names, tol=TOL):
+    fa, fb = a.ctx.download_fields(names), b.ctx.download_fields(names)
+    for k in names:
+        assert relerr(fa[k], fb[k]) < tol, (k, relerr(fa[k], fb[k]))
+
+
+def compare_particles(gpu, orc, tol=TOL):
+    for isp in range(len(gpu.species)):
+        A, B = gpu.ctx.download_particles(isp), orc.ctx.download_particles(isp)
+        assert A.shape == B.shape, (A.shape, B.shape)
+        if len(A) == 0:
+            continue
+        A, B = match_particles(A, B)
+        nd = gpu.ndims
+        assert np.array_equal(A[:, -1], B[:, -1])
+        for d in range(nd):
+            assert np.max(np.abs(A[:, d] - B[:, d])) / gpu.length[d] < tol, ("pos", d)
+        pscale = np.max(np.abs(B[:, nd:nd + 3]))
+        assert np.max(np.abs(A[:, nd:nd + 3] - B[:, nd:nd + 3])) / pscale < tol, "momentum"
+
+
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("order", [2, 4, 6])
+def test_field_half_steps(product_abi, oracle_abi, ndims, order):
+    n = [40, 24, 20]
+    sims = [make_plasma(a, ndims, "triangle", n, seed=5, ppc=1, field_order=order, two_species=False)
+            for a in (product_abi, oracle_abi)]
+    for s in sims:
+        rng = np.random.default_rng(9)
+        shp = s.ctx._np_shape()
+        s.ctx.upload_fields(**{k: rng.normal(0, 1e6, shp) for k in ("jx", "jy", "jz")})
+        s.ctx.set_time(s.dt, 0.5 * s.dt, 0)
+        s.ctx.update_eb_fields_half()
+        s.ctx.update_eb_fields_final()
+    compare_fields(sims[0], sims[1], FIELDS6)
+
+
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_push_deposit_one_step(product_abi, oracle_abi, ndims, shape):
+    """push_particles + current_finish on random relativistic particles in random
+    fields (every particle crosses cells with probability ~1/2 per axis)."""
+    n = [24, 12, 10]
+    sims = [make_plasma(a, ndims, shape, n, seed=11, ppc=5, u_th=1.0) for a in (product_abi, oracle_abi)]
+    for s in sims:
+        s.ctx.set_time(s.dt, 0.5 * s.dt, 0)
+        s.ctx.push_particles()
+        s.ctx.current_finish()
+    compare_particles(*sims)
+    compare_fields(sims[0], sims[1], ("jx", "jy", "jz"))
+
+
+@pytest.mark.parametrize("ndims,shape", [(1, "triangle"), (2, "triangle"), (3, "triangle"), (3, "tophat"), (2, "bspline3")])
+def test_full_steps_energy_and_charge(product_abi, oracle_abi, ndims, shape):
+    """10 full PIC steps: fields, particles, energy history and the Gauss-law
+    invariant agree with the oracle; charge is conserved to rounding."""
+    n = [32, 16, 12]
+    sims = [make_plasma(a, ndims, shape, n, seed=21, ppc=4, u_th=0.2, e_amp=1e9, b_amp=3.0)
+            for a in (product_abi, oracle_abi)]
+    hist = [[], []]
+    for k, s in enumerate(sims):
+        def hook(sim, k=k):
+            if sim.step == 0:
+                sim.ctx.set_option("capture_charge_reference", "1")
+            hist[k].append(sim.ctx.energy() + sim.ctx.charge_residual())
+        for _ in range(10):
+            s.step_once(after_half=hook)
+    compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
+    compare_particles(sims[0], sims[1], tol=1e-10)
+    for (fe_g, pe_g, res_g, rho_g), (fe_o, pe_o, res_o, rho_o) in zip(*hist):
+        assert abs(fe_g - fe_o) <= 1e-11 * abs(fe_o)
+        assert np.allclose(pe_g, pe_o, rtol=1e-11, atol=0)
+        assert res_g <= 5e-12 * rho_g      # charge conservation at machine precision
+
+
+@pytest.mark.parametrize("deck,comp,snap,gold", [(laser_1d, "ey", 8 * femto, GOLD_1D),
+                                               (laser_2d, "ey", 25 * femto, GOLD_2D),
+                                               (laser_3d, "ex", 25 * femto, GOLD_3D)])
+def test_laser_goldens_on_gpu(product_abi, deck, comp, snap, gold):
+    """The reference's own test_laser assertions, run through the CUDA path."""
+    check_golden(run_laser_deck(deck(product_abi), comp, snap), gold)
+
+
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("pbc,fbc", [("reflect", "conduct"), ("open", "clamp"), ("open", "zero_gradient"), ("reflect", "open")])
+def test_boundaries(product_abi, oracle_abi, ndims, pbc, fbc):
+    """Non-periodic x (and, in 3D, z) boundaries: reflecting and open particles,
+    conducting / clamped / zero-gradient / outflow fields; other axes periodic."""
+    n = [20, 12, 10]
+    bc_field = [fbc, fbc] + ["periodic"] * (2 * (ndims - 1))
+    bcs = [pbc, pbc] + ["periodic"] * (2 * (ndims - 1))
+    if ndims == 3:
+        bc_field[4:6] = [fbc, fbc]
+        bcs[4:6] = [pbc, pbc]
+    sims = [make_plasma(a, ndims, "triangle", n, seed=31, ppc=4, u_th=1.0, bc_field=bc_field, bcs=bcs)
+            for a in (product_abi, oracle_abi)]
+    for s in sims:
+        for _ in range(6):
+            s.step_once()
+    assert sims[0].ctx.particle_count(0) == sims[1].ctx.particle_count(0)
+    if pbc == "open":
+        assert sims[0].ctx.particle_count(0) < len(sims[0].loads[0])   # some particles really left
+    compare_particles(sims[0], sims[1], tol=1e-10)
+    compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
+
+
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_cell_edge_particles(product_abi, oracle_abi, shape):
+    """Particles exactly on k*dx and (k+1/2)*dx with zero momentum: FLOOR(x+0.5)
+    / FLOOR(x) conventions."""
+    sims = []
+    for a in (product_abi, oracle_abi):
+        sp = SpeciesSpec("electron", -Q0, M0)
+        s = Simulation(2, [16, 16], [0.0, 0.0], [16e-6, 16e-6], shape=shape, species=[sp], abi=a)
+        k = np.arange(32)
+        P = np.zeros((64, 6))
+        P[:32, 0] = 0.5e-6 * k
+        P[:32, 1] = 0.5e-6 * ((k * 7) % 32)
+        P[32:, 0] = 0.5e-6 * ((k * 5) % 32)
+        P[32:, 1] = 0.5e-6 * k
+        P[:, 0:2] = np.minimum(P[:, 0:2], 16e-6 * (1 - 1e-16))
+        P[32:, 2] = 1e-3 * M0 * C
+        P[:, 5] = 1.0 + np.arange(64)
+        rng = np.random.default_rng(2)
+        shp = s.ctx._np_shape()
+        s.ctx.upload_fields(**{f: rng.normal(0, 1e8 if f[0] == "e" else 0.3, shp) for f in FIELDS6})
+        s.ctx.upload_particles(0, P)
+        s.ctx.set_time(s.dt, 0.5 * s.dt, 0)
+        s.ctx.push_particles()
+        s.ctx.current_finish()
+        sims.append(s)
+    compare_particles(*sims)
+    compare_fields(sims[0], sims[1], ("jx", "jy", "jz"))
+
+
+def test_empty_and_ragged(product_abi, oracle_abi):
+    """No particles at all; one empty and one populated species; zero-current and
+    immobile species."""
+    for a in (product_abi,):
+        sp = [SpeciesSpec("e", -Q0, M0), SpeciesSpec("p", Q0, 1836 * M0), SpeciesSpec("tracer", -Q0, M0, zero_current=True),
+              SpeciesSpec("fixed", Q0, 1836 * M0, immobile=True)]
+        s = Simulation(3, [8, 8, 8], [0.0] * 3, [8e-6] * 3, species=sp, abi=a)
+        for _ in range(2):
+            s.step_once()
+        assert s.ctx.particle_count(0) == 0
+        j = s.ctx.download_fields(("jx",))["jx"]
+        assert not j.any()
+    sims = []
+    for a in (product_abi, oracle_abi):
+        s = Simulation(3, [8, 8, 8], [0.0] * 3, [8e-6] * 3, species=sp, abi=a)
+        rng = np.random.default_rng(4)
+        P = np.empty((37, 7))
+        P[:, 0:3] = rng.uniform(0, 8e-6, (37, 3))
+        P[:, 3:6] = rng.normal(0, 0.5, (37, 3)) * M0 * C
+        P[:, 6] = 1e10 * (1 + np.arange(37))
+        s.ctx.upload_particles(1, P * np.array([1, 1, 1, 1836, 1836, 1836, 1]))
+        s.ctx.upload_particles(2, P)
+        s.ctx.upload_particles(3, P)
+        for _ in range(3):
+            s.step_once()
+        sims.append(s)
+    compare_particles(*sims)
+    compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
+    # immobile species untouched, tracer moved but deposited nothing on its own
+    fixed = sims[0].ctx.download_particles(3)
+    assert np.array_equal(np.sort(fixed[:, 0]), np.sort(P[:, 0]))
+
+
+def test_upload_download_roundtrip(product_abi):
+    s = make_plasma(product_abi, 3, "triangle", [6, 5, 4], seed=1, ppc=7)
+    for isp in range(2):
+        Q = s.ctx.download_particles(isp)
+        A, B = match_particles(Q, s.loads[isp])
+        assert np.array_equal(A, B)     # bit exact
+    f = s.ctx.download_fields(FIELDS6)
+    for k in FIELDS6:
+        assert np.array_equal(f[k], s.init_fields[k])
+    # chunked append
+    P = s.loads[0]
+    s.ctx.upload_particles(0, P[:10])
+    s.ctx.upload_particles(0, P[10:], append=True)
+    A, B = match_particles(s.ctx.download_particles(0), P)
+    assert np.array_equal(A, B)
+
+
+def test_error_behaviour(product_abi):
+    from epoch_b200 import PicContext, EpochError
+    c = PicContext(2, "triangle", abi=product_abi)
+    with pytest.raises(EpochError):
+        c.update_eb_fields_half()           # grid not set
+    c.set_grid([8, 8], [1e-6, 1e-6], [0.5e-6] * 2, [0.0] * 2, [8e-6] * 2, [0.0] * 2, [8e-6] * 2)
+    with pytest.raises(EpochError):
+        c.push_particles()                  # dt not set
+    with pytest.raises(EpochError):
+        c.set_field_bcs(["cpml_laser", "periodic", "periodic", "periodic"])
+    with pytest.raises(EpochError):
+        c.set_species(0, -Q0, M0, bcs=["thermal", "thermal", "periodic", "periodic"])
+    with pytest.raises(EpochError):
+        c.upload_particles(0, np.zeros((1, 6)))   # species not defined
