@@ -144,7 +144,7 @@ __global__ void k_keys(GridP g, PushP p, const double* __restrict__ X, const dou
 #pragma unroll
   for (int d = 0; d < ND; ++d) {
     const double px = (POS[d][ip] - p.gml[d]) + u0[d] * root;
-    const double cr = SHAPE == SHAPE_TOPHAT ? px * p.idx[d] - 0.5 : px * p.idx[d];
+    const double cr = cell_coord<SHAPE>(px, p.idx[d]);
     double frac;
     int cell = cell_round(cr, frac);          // 1-based
     int e = cell - (1 - KM);

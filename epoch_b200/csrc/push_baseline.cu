@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(128) k_push_baseline(GridP g, FieldP F, PushP 
   double wg[3][NW], wh[3][NW];
 #pragma unroll
   for (int d = 0; d < ND; ++d) {
-    const double cr = SHAPE == SHAPE_TOPHAT ? px[d] * p.idx[d] - 0.5 : px[d] * p.idx[d];
+    const double cr = cell_coord<SHAPE>(px[d], p.idx[d]);
     double frac;
     cell1[d] = cell_round(cr, frac);
     shape_weights<SHAPE>(frac, wg[d]);
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(128) k_push_baseline(GridP g, FieldP F, PushP 
 #pragma unroll
   for (int d = 0; d < ND; ++d) {
     px[d] = px[d] + delta[d];
-    const double cr = SHAPE == SHAPE_TOPHAT ? px[d] * p.idx[d] - 0.5 : px[d] * p.idx[d];
+    const double cr = cell_coord<SHAPE>(px[d], p.idx[d]);
     double frac;
     const int cell3 = cell_round(cr, frac);
     const int dcell = cell3 - cell1[d];

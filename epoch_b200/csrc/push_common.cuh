@@ -52,6 +52,13 @@ __host__ inline double shape_fac(int shape, int nd) {   // particles.F90:128-136
   return fac;
 }
 
+// cell coordinate x*idx [-0.5 tophat] (particles.F90:270-291), rounded as the reference
+// rounds it (two roundings, no FMA contraction) so that FLOOR lands in the same cell
+template <int SHAPE>
+__device__ __forceinline__ double cell_coord(double px, double idx) {
+  const double r = __dmul_rn(px, idx);
+  return SHAPE == SHAPE_TOPHAT ? __dadd_rn(r, -0.5) : r;
+}
 // nearest-node cell and fraction: cell = FLOOR(r+0.5); frac = cell - r; cell+1
 __device__ __forceinline__ int cell_round(double r, double& frac) {
   const double fl = floor(r + 0.5);

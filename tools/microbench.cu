@@ -61,6 +61,53 @@ __global__ void k_lds(double* out, int iters, int pattern) {
   }
   out[blockIdx.x*blockDim.x+threadIdx.x]=acc;
 }
+// DMMA m8n8k4 fp64 tensor-core MMA: 8 independent accumulator tiles per warp
+__global__ void k_dmma(double* out, int iters) {
+  double c[8][2];
+#pragma unroll
+  for (int t=0;t<8;++t){ c[t][0]=threadIdx.x*1e-3+t; c[t][1]=1.0+t; }
+  double a = 1.0 + threadIdx.x*1e-9, b = 1e-9*threadIdx.x;
+  for (int i=0;i<iters;++i){
+#pragma unroll
+    for (int t=0;t<8;++t)
+      asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                   : "+d"(c[t][0]), "+d"(c[t][1]) : "d"(a), "d"(b));
+  }
+  double s=0;
+#pragma unroll
+  for (int t=0;t<8;++t) s+=c[t][0]+c[t][1];
+  out[blockIdx.x*blockDim.x+threadIdx.x]=s;
+}
+// mixed: DFMA stream and DMMA stream in the same warp (do they share the fp64 pipe?)
+__global__ void k_mixed(double* out, int iters) {
+  double c[4][2];
+#pragma unroll
+  for (int t=0;t<4;++t){ c[t][0]=threadIdx.x*1e-3+t; c[t][1]=1.0+t; }
+  double a = 1.0 + threadIdx.x*1e-9, b = 1e-9*threadIdx.x;
+  double a0=threadIdx.x*1e-3, a1=a0+1, a2=a0+2, a3=a0+3, a4=a0+4, a5=a0+5, a6=a0+6, a7=a0+7;
+  const double bb=1.0000001, cc=1e-9;
+  for (int i=0;i<iters;++i){
+#pragma unroll
+    for (int t=0;t<4;++t)
+      asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                   : "+d"(c[t][0]), "+d"(c[t][1]) : "d"(a), "d"(b));
+    a0=a0*bb+cc; a1=a1*bb+cc; a2=a2*bb+cc; a3=a3*bb+cc; a4=a4*bb+cc; a5=a5*bb+cc; a6=a6*bb+cc; a7=a7*bb+cc;
+    a0=a0*bb+cc; a1=a1*bb+cc; a2=a2*bb+cc; a3=a3*bb+cc; a4=a4*bb+cc; a5=a5*bb+cc; a6=a6*bb+cc; a7=a7*bb+cc;
+  }
+  double s=a0+a1+a2+a3+a4+a5+a6+a7;
+#pragma unroll
+  for (int t=0;t<4;++t) s+=c[t][0]+c[t][1];
+  out[blockIdx.x*blockDim.x+threadIdx.x]=s;
+}
+// 64-bit warp shuffles
+__global__ void k_shfl(double* out, int iters) {
+  double v0=threadIdx.x, v1=v0+1, v2=v0+2, v3=v0+3;
+  for (int i=0;i<iters;++i){
+    v0 += __shfl_xor_sync(0xffffffffu, v0, 1); v1 += __shfl_xor_sync(0xffffffffu, v1, 2);
+    v2 += __shfl_xor_sync(0xffffffffu, v2, 4); v3 += __shfl_xor_sync(0xffffffffu, v3, 8);
+  }
+  out[blockIdx.x*blockDim.x+threadIdx.x]=v0+v1+v2+v3;
+}
 int main(){
   cudaDeviceProp pr; CK(cudaGetDeviceProperties(&pr,0));
   printf("device %s SMs %d\n", pr.name, pr.multiProcessorCount);
@@ -69,6 +116,13 @@ int main(){
   const int nb = pr.multiProcessorCount*8;
   { int it=20000; k_dfma<<<nb,256>>>(out,100); cudaEventRecord(e0); k_dfma<<<nb,256>>>(out,it); cudaEventRecord(e1); CK(cudaEventSynchronize(e1)); cudaEventElapsedTime(&ms,e0,e1);
     printf("DFMA: %.2f TFLOP/s fp64 (%.1f DFMA/clk/SM @1.9GHz-equiv)\n", 2.0*8*it*(double)nb*256/ms/1e9, 8.0*it*nb*256/(ms*1e-3)/pr.multiProcessorCount/1.9e9); }
+  { int it=20000; k_dmma<<<nb,256>>>(out,100); cudaEventRecord(e0); k_dmma<<<nb,256>>>(out,it); cudaEventRecord(e1); CK(cudaEventSynchronize(e1)); cudaEventElapsedTime(&ms,e0,e1);
+    const double nm = 8.0*it*(double)nb*8;   // warp-level MMAs
+    printf("DMMA m8n8k4: %.2f TFLOP/s fp64 (%.2f clk/MMA/SM @1.9GHz-equiv)\n", 2.0*256*nm/ms/1e9, (ms*1e-3)*1.9e9*pr.multiProcessorCount/nm); }
+  { int it=20000; k_mixed<<<nb,256>>>(out,100); cudaEventRecord(e0); k_mixed<<<nb,256>>>(out,it); cudaEventRecord(e1); CK(cudaEventSynchronize(e1)); cudaEventElapsedTime(&ms,e0,e1);
+    printf("mixed 4 DMMA + 16 DFMA per iter: %.3f ms; DFMA-only equiv would be %.2f TFLOP/s, DMMA part %.2f TFLOP/s\n", ms, 2.0*16*it*(double)nb*256/ms/1e9, 2.0*256*4.0*it*nb*8/ms/1e9); }
+  { int it=20000; k_shfl<<<nb,256>>>(out,100); cudaEventRecord(e0); k_shfl<<<nb,256>>>(out,it); cudaEventRecord(e1); CK(cudaEventSynchronize(e1)); cudaEventElapsedTime(&ms,e0,e1);
+    printf("SHFL.64+DADD: %.1f G lane-shuffles(64b)/s (%.2f warp-shfl64/clk/SM @1.9GHz)\n", 4.0*it*(double)nb*256/ms/1e6, 4.0*it*nb*8/(ms*1e-3)/pr.multiProcessorCount/1.9e9); }
   double* J; const long long big = 1LL<<27; CK(cudaMalloc(&J, big*8)); CK(cudaMemset(J,0,big*8));
   const char* pn[4]={"distinct-random","16-lane-groups","warp-uniform","coalesced"};
   for (int span_i=0; span_i<2; ++span_i) {
