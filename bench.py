@@ -1,0 +1,398 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the EPOCH PIC hot path on B200 (BASELINE.json metric).
+
+Workload (configs[2], the one the metric's target is quoted on): epoch3d uniform
+thermal plasma, 512^3 cells x 16 ppc electrons (neutralising background implied,
+deck_control_block.F90:519-526), periodic, triangle shape, fp64; n = 1e24 m^-3,
+T = 1 keV, dx = lambda_D / 2, dt = 0.95 x CFL.  Synthetic data: the
+particle load follows the reference loader's rule (16 particles per cell at
+x(ix) + (U - 1/2) dx, helper.F90:599-601; Maxwellian momenta sigma = sqrt(m kB T),
+particle_temperature.F90:397-409) with numpy's generator instead of KISS.
+
+A "step" is one iteration of PROGRAM pic's main loop as far as the hot path goes
+(epoch3d.F90:184-249): update_eb_fields_half, push_particles (push + deposit +
+particle_bcs + re-sort), current_finish, update_eb_fields_final -- all of it inside
+the timed region.  `value` = particles x steps / device time (CUDA events on the
+library's stream, max over ranks) with the state resident in HBM; `e2e` = the same
+through the C ABI from HOST buffers: upload of all particles and fields, K steps,
+download of all particles and fields, wall clock.
+
+N > 1 (torchrun): weak scaling, one 512^3 slab per GPU stacked along z, NCCL
+send/recv of field halos, current ghost sums and migrating particles.
+
+`--impl reference` times the CPU restatement of the reference (oracle/, built -O3)
+on all host cores, one independent periodic box per process.
+"""
+import argparse
+import json
+import math
+import multiprocessing as mp
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+Q0, M0, C0, KB, EPS0 = 1.602176565e-19, 9.10938291e-31, 2.99792458e8, 1.3806488e-23, 8.854187817620389850536563031710750e-12
+DENSITY = 1.0e24                   # m^-3
+T_KELVIN = 1.0e3 * Q0 / KB         # 1 keV
+PPC = 16
+ORACLE_FAST = os.path.join(ROOT, "oracle", "liborc_fast.so")
+
+
+def deck_geometry(cells):
+    lam_d = math.sqrt(EPS0 * KB * T_KELVIN / (DENSITY * Q0 * Q0))
+    dx = lam_d / 2.0
+    return dx, [c * dx for c in cells]
+
+
+def make_sim(abi, cells_global, rank=0, nproc=1, nccl_id=None, device=0):
+    from epoch_b200.driver import Simulation, SpeciesSpec
+    dx, length = deck_geometry(cells_global)
+    sp = SpeciesSpec("electron", -Q0, M0, density=DENSITY, temperature=(T_KELVIN,) * 3)
+    return Simulation(3, list(cells_global), [0.0, 0.0, 0.0], length, shape="triangle", species=[sp],
+                      abi=abi, device=device, rank=rank, nproc=nproc, nprocdir=(1, 1, nproc), nccl_id=nccl_id)
+
+
+def fill_particles(out, sim, seed, nthreads):
+    """Reference loader rule for a uniform plasma on this rank's cells, written
+    into `out` ((n_cells*PPC, 7) float64, partlist wire order x,y,z,px,py,pz,w)."""
+    nx, ny, nz = sim.n_local
+    dx = sim.d[0]
+    weight = DENSITY * dx ** 3 / PPC
+    sigma = math.sqrt(M0 * KB * T_KELVIN)
+    per_plane = nx * ny * PPC
+    cx = sim.grid_min_local[0] + np.arange(nx) * sim.d[0]
+    cy = sim.grid_min_local[1] + np.arange(ny) * sim.d[1]
+
+    def work(k0, k1):
+        for k in range(k0, k1):
+            rng = np.random.default_rng([seed, sim.rank, k])
+            P = out[k * per_plane:(k + 1) * per_plane]
+            u = rng.random((per_plane, 3))
+            u -= 0.5
+            cells = np.arange(nx * ny).repeat(PPC)
+            P[:, 0] = cx[cells % nx] + u[:, 0] * dx
+            P[:, 1] = cy[cells // nx] + u[:, 1] * dx
+            P[:, 2] = (sim.grid_min_local[2] + k * sim.d[2]) + u[:, 2] * dx
+            P[:, 3:6] = rng.standard_normal((per_plane, 3)) * sigma
+            P[:, 6] = weight
+    nthreads = max(1, min(nthreads, nz))
+    bounds = np.linspace(0, nz, nthreads + 1).astype(int)
+    ts = [threading.Thread(target=work, args=(bounds[i], bounds[i + 1])) for i in range(nthreads)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device=0):
+        self.proc = None
+        self.device = device
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------
+# CPU arm: the oracle port (CPU restatement of the reference), one independent
+# periodic box per process.  Only bench.py's cpu legs and tests/ may load oracle/.
+# ---------------------------------------------------------------------------
+def _cpu_worker(task):
+    cells, steps, warmup, seed = task
+    from epoch_b200 import _abi
+    abi = _abi.Abi(ORACLE_FAST, "orc_")
+    sim = make_sim(abi, (cells, cells, cells))
+    n = cells ** 3 * PPC
+    P = np.empty((n, 7))
+    fill_particles(P, sim, seed, 1)
+    sim.ctx.upload_particles(0, P)
+    for _ in range(warmup):
+        sim.step_once()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sim.step_once()
+    return n, time.perf_counter() - t0
+
+
+def cpu_arm(cores, cells, steps, warmup):
+    """particle-steps/s of the CPU port on `cores` processes (max-over-workers time)."""
+    if not os.path.exists(ORACLE_FAST):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(cores) as pool:
+        res = pool.map(_cpu_worker, [(cells, steps, warmup, 1000 + i) for i in range(cores)])
+    total = sum(r[0] for r in res) * steps
+    tmax = max(r[1] for r in res)
+    return total / tmax, tmax / steps
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = host_cores()
+    cells = args.cpu_cells
+    rate, s_per_step = cpu_arm(cores, cells, args.steps, args.warmup)
+    sample = (f"{cores} independent periodic boxes of {cells}^3 cells x {PPC} ppc "
+              f"({cores * cells ** 3 * PPC} particles), full step, {args.steps} steps after {args.warmup} warm-up")
+    line = {
+        "impl": "reference", "metric": "particle-steps/s (push+deposit, full PIC step)", "value": rate,
+        "unit": "particle-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": s_per_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, args.gpus),
+        "cpu_baseline": {"value": rate, "unit": "particle-steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": "particle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "CPU restatement of the reference (oracle/, g++ -O3 -march=x86-64-v3, no FMA contraction); "
+                "the Fortran reference cannot be built (no Fortran compiler, SDF submodule missing)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, n_gpus):
+    c = args.cells
+    return {"workload": f"epoch3d uniform thermal plasma {c}x{c}x{c * n_gpus} cells x {PPC} ppc electrons, periodic, "
+                        f"triangle shape, fp64 (BASELINE.json configs[2]; {c}^3 per GPU, slabs along z)",
+            "cells_per_gpu": [c, c, c], "ppc": PPC, "particles_per_gpu": c ** 3 * PPC,
+            "density_m3": DENSITY, "temperature_keV": 1.0, "dx_over_debye": 0.5, "dt_over_cfl": 0.95,
+            "l2_policy": "inputs larger than L2 (particle arrays %.1f GB per GPU)" % (c ** 3 * PPC * 56 / 1e9),
+            "parallelism": f"domain decomposition 1x1x{n_gpus} (slab along z)"}
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except OSError:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from epoch_b200 import _abi
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product library has no CPU path")
+    torch.cuda.set_device(local)
+    abi = _abi.product()
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        buf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            raw = (128 * __import__("ctypes").c_char)()
+            assert abi.nccl_unique_id(raw) == 0
+            buf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
+        dist.broadcast(buf, 0)
+        nccl_id = bytes(buf.cpu().numpy().tobytes())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    c = args.cells
+    cells_global = (c, c, c * world)
+    n_part = c ** 3 * PPC
+    t_setup = time.perf_counter()
+    sim = make_sim(abi, cells_global, rank, world, nccl_id, device=local)
+    # host copy of this rank's particle load (also the e2e leg's host buffer)
+    host = np.empty((n_part, 7))
+    fill_particles(host, sim, args.seed, host_cores() // max(1, world))
+    t_gen = time.perf_counter() - t_setup
+    sim.ctx.set_option("reserve", f"0:{n_part + n_part // 64 if world > 1 else n_part}")
+    sim.ctx.set_option("timers", 1)
+    sim.ctx.upload_particles(0, host)
+    sim.ctx.sync()
+    t_up = time.perf_counter() - t_setup - t_gen
+
+    for _ in range(args.warmup):
+        sim.step_once()
+    sim.ctx.sync()
+    for ph in ("push", "push_kernel", "sort", "fields", "halo", "bcs", "step"):
+        sim.ctx.timer(ph, reset=True)
+    l0 = sim.ctx.timer("launches")[1]
+    clocks = ClockSampler(local)
+    barrier(); torch.cuda.synchronize()
+    if rank == 0:
+        clocks.start()
+    sim.ctx.mark("step", 1)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        sim.step_once()
+    sim.ctx.mark("step", 0)
+    sim.ctx.sync()
+    wall = time.perf_counter() - t0
+    barrier(); torch.cuda.synchronize()
+    clk = clocks.stop() if rank == 0 else None
+    dev_ms = sim.ctx.timer("step")[0]
+    launches = sim.ctx.timer("launches")[1] - l0
+    ms = max_over_ranks(dev_ms)
+    phases = {ph: sim.ctx.timer(ph) for ph in ("push", "push_kernel", "sort", "fields", "halo", "bcs")}
+    n_live = sim.ctx.particle_count(0)
+    value = n_part * world * args.steps / (ms * 1e-3)
+
+    # roofline of the dominant kernel (push + deposit): algorithmic bytes per launch
+    # = 104 B per particle (read x,y,z,px,py,pz,w; write x,y,z,px,py,pz) + 72 B per
+    # cell (read 6 field components, write 3 current components)   [SURVEY 8d]
+    peaks, how = measured_peaks()
+    pk_ms, pk_launch = phases["push_kernel"]
+    roof = None
+    if pk_launch > 0 and pk_ms > 0:
+        n_launch = args.steps      # one species => one push launch per step
+        alg_bytes = 104.0 * n_live + 72.0 * c ** 3
+        ach = alg_bytes / (pk_ms / n_launch * 1e-3) / 1e9
+        roof = {"bound": "hbm", "kernel": "push+deposit (k_push_*)", "achieved": ach, "peak": peaks["hbm_gbs"],
+                "unit": "GB/s", "frac": ach / peaks["hbm_gbs"], "traffic": None, "peak_source": how,
+                "ms_per_launch": pk_ms / n_launch, "algorithmic_bytes_per_launch": alg_bytes,
+                "particle_steps_per_s_kernel_only": n_live / (pk_ms / n_launch * 1e-3),
+                "share_of_step": pk_ms / dev_ms}
+        tr = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tr):
+            try:
+                roof["traffic"] = json.load(open(tr)).get("push_bytes_per_particle", None)
+                if roof["traffic"] is not None:
+                    roof["traffic"] = roof["traffic"] * n_live
+            except Exception:
+                pass
+    fields_ms, fields_l = phases["fields"]
+    field_line = None
+    if fields_l > 0:
+        cells = (c + 1) ** 3
+        fb = (2 * 96.0 + 2 * 72.0) * cells * args.steps      # 2 E + 2 B half-steps per step
+        field_line = {"cell_updates_per_s": 4 * cells * args.steps / (fields_ms * 1e-3),
+                      "achieved_gbs": fb / (fields_ms * 1e-3) / 1e9,
+                      "frac_of_hbm": fb / (fields_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+    sim.ctx.close()
+    del sim
+
+    # e2e: same metric through the C ABI from host buffers (upload, K steps, download)
+    e2e = None
+    if not args.no_e2e:
+        barrier(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        sim2 = make_sim(abi, cells_global, rank, world, nccl_id, device=local)
+        sim2.ctx.set_option("reserve", f"0:{n_part + n_part // 64 if world > 1 else n_part}")
+        shp = sim2.ctx._np_shape()
+        fzero = np.zeros(shp)
+        sim2.ctx.upload_fields(ex=fzero, ey=fzero, ez=fzero, bx=fzero, by=fzero, bz=fzero)
+        sim2.ctx.upload_particles(0, host)
+        for _ in range(args.steps):
+            sim2.step_once()
+        got = sim2.ctx.download_particles(0, out=host)
+        fld = sim2.ctx.download_fields()
+        sim2.ctx.sync()
+        t_e2e = max_over_ranks(time.perf_counter() - t0)
+        h2d = host.nbytes + 6 * fzero.nbytes
+        d2h = got.nbytes + 9 * fzero.nbytes
+        e2e = {"value": n_part * world * args.steps / t_e2e, "unit": "particle-steps/s",
+               "h2d_bytes_per_step": h2d * world / args.steps, "d2h_bytes_per_step": d2h * world / args.steps,
+               "seconds": t_e2e, "steps_per_residency": args.steps,
+               "what": "eb200_create + upload_fields + upload_particles (pageable host numpy buffers) + K full steps "
+                       "+ download_particles + download_fields + sync, wall clock; the state lives on the device "
+                       "between steps, so the copies are amortised over K steps"}
+        del fld
+        sim2.ctx.close()
+    if rank != 0:
+        return
+    line = {
+        "metric": "particle-steps/s (push+deposit, full PIC step)", "value": value, "unit": "particle-steps/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, world), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
+        "roofline": roof, "fields": field_line,
+        "phases_ms_per_step": {k: v[0] / args.steps for k, v in phases.items()},
+        "wall_ms_per_step": wall * 1e3 / args.steps,
+        "setup_seconds": {"generate_host": t_gen, "upload": t_up},
+    }
+    if world == 1 and not args.no_cpu:
+        cores = host_cores()
+        rate, s_per = cpu_arm(cores, args.cpu_cells, 3, 1)
+        line["cpu_baseline"] = {"value": rate, "unit": "particle-steps/s", "cores": cores, "kind": "port",
+                                "sample": f"{cores} independent periodic boxes of {args.cpu_cells}^3 cells x {PPC} ppc, "
+                                          f"full step, 3 steps after 1 warm-up ({s_per:.2f} s/step)"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cells", type=int, default=512, help="cells per dimension per GPU")
+    ap.add_argument("--cpu-cells", type=int, default=64, help="cells per dimension per CPU process (cpu arm)")
+    ap.add_argument("--seed", type=int, default=12345)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -46,6 +46,7 @@ SIGNATURES = {
     "set_option": (i32, [c_ctx_p, C.c_char_p, C.c_char_p]),
     "sync": (i32, [c_ctx_p]),
     "timer": (i32, [c_ctx_p, C.c_char_p, i32, pf64, pi64]),
+    "mark": (i32, [c_ctx_p, C.c_char_p, i32]),
     "last_error": (C.c_char_p, [c_ctx_p]),
     "version": (C.c_char_p, []),
 }

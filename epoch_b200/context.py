@@ -121,9 +121,10 @@ class PicContext:
         self._ck(self.abi.particle_count(self._ctx, isp, C.byref(n)))
         return n.value
 
-    def download_particles(self, isp):
+    def download_particles(self, isp, out=None):
         n = self.particle_count(isp)
-        out = np.empty((n, self.nvar), dtype=np.float64)
+        if out is None or out.shape[0] < n:
+            out = np.empty((n, self.nvar), dtype=np.float64)
         got = C.c_int64()
         self._ck(self.abi.download_particles(self._ctx, isp, 0, n, out.ctypes.data_as(C.c_void_p),
                                              self.nvar, C.byref(got)))
@@ -220,6 +221,9 @@ class PicContext:
 
     def sync(self):
         self._ck(self.abi.sync(self._ctx))
+
+    def mark(self, phase, begin):
+        self._ck(self.abi.mark(self._ctx, phase.encode(), int(bool(begin))))
 
     def timer(self, phase, reset=False):
         ms, n = C.c_double(), C.c_int64()

@@ -368,6 +368,14 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
   if (k == "deterministic_deposit") { c->deterministic = atoi(value) != 0; return 0; }
   if (k == "sort_every") { c->sort_every = atoi(value) < 1 ? 1 : atoi(value); return 0; }
   if (k == "timers") { c->timers_on = atoi(value) != 0; return 0; }
+  if (k == "reserve") {   // "<species>:<particles>": allocate particle storage once, exactly (no regrow copies)
+    const size_t colon = v.find(':');
+    if (colon == std::string::npos) return fail(c, EB200_E_ARG, "reserve: <species>:<particles>");
+    const int isp = atoi(v.substr(0, colon).c_str());
+    const long long n = atoll(v.substr(colon + 1).c_str());
+    if (isp < 0 || (size_t)isp >= c->species.size() || !c->species[isp].defined || n < 0) return fail(c, EB200_E_ARG, "reserve: bad species or count");
+    return species_reserve(c, c->species[isp], n, true);
+  }
   if (k == "mig_capacity") { c->mig_min_particles = atoll(value); return 0; }
   return fail(c, EB200_E_ARG, "unknown option " + k);
 }
@@ -400,6 +408,26 @@ int32_t eb200_timer(eb200_ctx* c, const char* phase, int32_t reset, double* ms, 
   if (ms) *ms = t.ms;
   if (launches) *launches = t.launches;
   if (reset) { t.ms = 0; t.launches = 0; }
+  return 0;
+}
+
+int32_t eb200_mark(eb200_ctx* c, const char* phase, int32_t begin) {
+  CHECK_CTX(c);
+  if (!phase) return fail(c, EB200_E_ARG, "null");
+  PhaseTimer& t = c->timers[phase];
+  cudaEvent_t e = nullptr;
+  EB_CUDA(c, cudaEventCreate(&e));
+  EB_CUDA(c, cudaEventRecord(e, c->stream));
+  if (begin) {
+    if (c->open_marks.count(phase)) { cudaEventDestroy(c->open_marks[phase].first); }
+    c->open_marks[phase] = std::make_pair(e, c->launches);
+  } else {
+    auto it = c->open_marks.find(phase);
+    if (it == c->open_marks.end()) { cudaEventDestroy(e); return fail(c, EB200_E_STATE, "mark(end) without mark(begin)"); }
+    t.ev.emplace_back(it->second.first, e);
+    t.launches += c->launches - it->second.second;
+    c->open_marks.erase(it);
+  }
   return 0;
 }
 

@@ -118,6 +118,7 @@ struct eb200_ctx {
   int sort_every = 1;
   bool timers_on = false;
   std::map<std::string, eb::PhaseTimer> timers;
+  std::map<std::string, std::pair<cudaEvent_t, long long>> open_marks;
   long long launches = 0;       // kernels launched (for gpu_launches accounting)
   eb::Nccl* nccl = nullptr;
 };
@@ -165,7 +166,7 @@ int32_t comm_sendrecv_v(eb200_ctx* c, const double* send, int dst, size_t nsend,
 // particles.cu
 int32_t push_particles(eb200_ctx* c);
 int32_t particle_bcs(eb200_ctx* c);
-int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need);
+int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need, bool exact = false);
 int32_t add_particles(eb200_ctx* c, int isp, long long n, const double* packed, int nvar, bool replace);
 int32_t get_particles(eb200_ctx* c, int isp, long long first, long long cap, double* packed, int nvar, long long* n_out);
 int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots);

@@ -25,9 +25,9 @@ static int32_t regrow(eb200_ctx* c, T*& ptr, long long old_n, long long new_cap)
   return 0;
 }
 
-int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need) {
+int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need, bool exact) {
   if (need <= sp.cap) return 0;
-  long long ncap = std::max<long long>(need + need / 32 + 1024, 4096);
+  long long ncap = exact ? std::max<long long>(need, 1024) : std::max<long long>(need + need / 32 + 1024, 4096);
   const int nattr = c->ndims + 4;
   // attributes live in a[0..ndims-1] (pos), a[3..5] (p), a[6] (w)
   for (int k = 0; k < 7; ++k) {
@@ -463,6 +463,7 @@ int32_t push_particles(eb200_ctx* c) {
     ScopedPhase ph(c, "push");
     PushP p = make_push_params(c, sp, sp.n);
     bool handled = false;
+    ScopedPhase pk(c, "push_kernel");     // the kernel alone (roofline figure of bench.py)
     if (c->push_kernel != 1) EB_TRY(launch_push_tiled(c, sp, p, &handled));
     if (!handled) EB_TRY(launch_push_baseline(c, sp, p));
   }

@@ -178,6 +178,12 @@ int32_t EB200_NAME(sync)(EB200_CTX*);
  * reset != 0 ("push", "sort", "fields", "halo", "bcs"); CUDA-event based. */
 int32_t EB200_NAME(timer)(EB200_CTX*, const char* phase, int32_t reset, double* ms,
                           int64_t* launches);
+/* user bracket on the context's stream: mark(phase, 1) records a begin event,
+ * mark(phase, 0) the matching end event; the device time between them is added
+ * to `phase` and read back with timer().  Replaces timer_start/timer_stop of
+ * housekeeping/timer.f90:27-113 (wall clock there, CUDA events here).  Always on,
+ * independent of the "timers" option. */
+int32_t EB200_NAME(mark)(EB200_CTX*, const char* phase, int32_t begin);
 const char* EB200_NAME(last_error)(EB200_CTX*);
 const char* EB200_NAME(version)(void);
 

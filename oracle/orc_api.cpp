@@ -7,6 +7,8 @@
 #include "../include/epoch_b200.h"
 #include "orc_state.hpp"
 #include <algorithm>
+#include <chrono>
+#include <map>
 #include <new>
 
 struct orc_ctx { orc::State s; };
@@ -259,9 +261,22 @@ int32_t orc_set_option(orc_ctx* c, const char* key, const char*) {
   return 0;
 }
 int32_t orc_sync(orc_ctx*) { return 0; }
-int32_t orc_timer(orc_ctx*, const char*, int32_t, double* ms, int64_t* launches) {
-  if (ms) *ms = 0;
+// wall-clock brackets (housekeeping/timer.f90:27-113)
+static std::map<std::string, double> g_t_open, g_t_acc;
+static double now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+int32_t orc_mark(orc_ctx*, const char* phase, int32_t begin) {
+  if (!phase) return EB200_E_ARG;
+  if (begin) g_t_open[phase] = now_ms();
+  else if (g_t_open.count(phase)) { g_t_acc[phase] += now_ms() - g_t_open[phase]; g_t_open.erase(phase); }
+  return 0;
+}
+int32_t orc_timer(orc_ctx*, const char* phase, int32_t reset, double* ms, int64_t* launches) {
+  const std::string k(phase ? phase : "");
+  if (ms) *ms = g_t_acc.count(k) ? g_t_acc[k] : 0.0;
   if (launches) *launches = 0;
+  if (reset) g_t_acc.erase(k);
   return 0;
 }
 const char* orc_last_error(orc_ctx* c) { return c ? c->s.err.c_str() : g_err.c_str(); }
