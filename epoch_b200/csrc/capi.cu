@@ -35,6 +35,8 @@ static void free_species(SpeciesD& sp) {
   for (int k = 0; k < 7; ++k) if (sp.a[k]) { cudaFree(sp.a[k]); sp.a[k] = nullptr; }
   if (sp.key) cudaFree(sp.key);
   if (sp.dest) cudaFree(sp.dest);
+  if (sp.cell_start) cudaFree(sp.cell_start);
+  sp.cell_start = nullptr; sp.cell_cap = 0;
   sp.key = sp.dest = nullptr; sp.n = sp.cap = 0;
 }
 
@@ -88,6 +90,7 @@ int32_t eb200_create(eb200_ctx** out, int32_t ndims, int32_t shape, int32_t devi
   cudaSetDevice(device);
   if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
       cudaMalloc(&c->d_counters, 64 * sizeof(unsigned long long)) != cudaSuccess ||
+      cudaMemset(c->d_counters, 0, 64 * sizeof(unsigned long long)) != cudaSuccess ||
       cudaMallocHost(&c->h_counters, 64 * sizeof(unsigned long long)) != cudaSuccess ||
       cudaMalloc(&c->d_red, 64 * sizeof(double)) != cudaSuccess ||
       cudaMallocHost(&c->h_red, 64 * sizeof(double)) != cudaSuccess) {
@@ -115,7 +118,7 @@ int32_t eb200_destroy(eb200_ctx* c) {
   comm_destroy(c);
   for (SpeciesD& sp : c->species) free_species(sp);
   for (int b = 0; b < 6; ++b) for (Laser& L : c->lasers[b]) { if (L.profile) cudaFree(L.profile); if (L.phase) cudaFree(L.phase); }
-  void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->cell_start, c->cub_tmp, c->halo_send, c->halo_recv,
+  void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->cub_tmp, c->halo_send, c->halo_recv,
                   c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->h_counters) cudaFreeHost(c->h_counters);
@@ -152,8 +155,11 @@ int32_t eb200_set_grid(eb200_ctx* c, const int32_t n_local[3], const int32_t n_g
     g.st[k] = stride;
     stride *= (long long)(g.n[k] + 2 * g.ngd[k]);
     g.kn[k] = ex ? g.n[k] + 2 * KM : 1;
-    ncell *= g.kn[k];
+    g.tdim[k] = tile_dim(c->ndims, k);
+    g.ntile[k] = (g.kn[k] + g.tdim[k] - 1) / g.tdim[k];
+    ncell *= (long long)g.ntile[k] * g.tdim[k];
   }
+  g.cpt = g.tdim[0] * g.tdim[1] * g.tdim[2];
   if (ncell >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "local grid too large for 32-bit cell keys");
   g.total = stride; g.ncell_ext = ncell;
   if (c->fbase) { cudaStreamSynchronize(c->stream); cudaFree(c->fbase); c->fbase = nullptr; }
@@ -395,6 +401,13 @@ int32_t eb200_timer(eb200_ctx* c, const char* phase, int32_t reset, double* ms, 
     if (ms) *ms = 0;
     if (launches) *launches = c->launches;
     if (reset) c->launches = 0;
+    return 0;
+  }
+  if (k == "cell_mismatch") {   // particles whose sort key and push disagreed on the cell (must stay 0)
+    unsigned long long v = 0;
+    EB_CUDA(c, cudaMemcpy(&v, c->d_counters + 8, sizeof(v), cudaMemcpyDeviceToHost));
+    if (ms) *ms = 0;
+    if (launches) *launches = (int64_t)v;
     return 0;
   }
   PhaseTimer& t = c->timers[k];

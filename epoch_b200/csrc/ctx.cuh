@@ -30,15 +30,22 @@ struct GridP {
   double gml[3];          // x_grid_min_local (centre of local cell 1)
   double min_local[3], max_local[3];
   double gmin[3], gmax[3];
-  // extended cell grid used for sort keys: cells (1-KM .. n+KM) per existing dim
+  // extended cell grid used for sort keys: cells (1-KM .. n+KM) per existing dim,
+  // cut into tiles of tdim cells; a key is tile-major: tile * cpt + cell-in-tile
+  // (x fastest in both), so that the particles of a tile are contiguous
   int kn[3];              // extended extents
-  long long ncell_ext;
+  int tdim[3], ntile[3], cpt;
+  long long ncell_ext;    // number of key buckets = ntile[0]*ntile[1]*ntile[2]*cpt
   __host__ __device__ inline long long idx(int i, int j, int k) const {
     return (long long)(i + ngd[0] - 1) * st[0] + (long long)(j + ngd[1] - 1) * st[1] +
            (long long)(k + ngd[2] - 1) * st[2];
   }
 };
 constexpr int KM = 3;                    // key-grid margin in cells
+// tile shape of the cell sort / tiled push kernel per dimensionality
+__host__ __device__ constexpr int tile_dim(int nd, int d) {
+  return nd == 3 ? (d == 2 ? 4 : 8) : nd == 2 ? (d == 2 ? 1 : 16) : (d == 0 ? 256 : 1);
+}
 constexpr uint32_t KEY_INVALID = 0xFFFFFFFFu;
 
 struct FieldP { double* f[NFIELD]; };
@@ -54,6 +61,8 @@ struct SpeciesD {
   double* a[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // x,y,z,px,py,pz,w
   uint32_t* key = nullptr;  // sort key per slot
   uint32_t* dest = nullptr; // destination index per slot
+  uint32_t* cell_start = nullptr;   // per species: first particle of every key bucket (ncell_ext + 2)
+  long long cell_cap = 0;
   bool sorted = false;      // keys/cell_start valid for the current positions
 };
 
@@ -99,7 +108,6 @@ struct eb200_ctx {
   // scratch
   double* attr_scratch = nullptr; long long attr_scratch_cap = 0;   // one attribute array for the sort ping-pong
   uint32_t* cell_count = nullptr;   // ncell_ext + 2 (last bucket = invalid)
-  uint32_t* cell_start = nullptr;   // ncell_ext + 2
   long long cell_cap = 0;
   void* cub_tmp = nullptr; size_t cub_tmp_bytes = 0;
   double* halo_send = nullptr; double* halo_recv = nullptr; size_t halo_bytes = 0;

@@ -137,21 +137,17 @@ __global__ void k_keys(GridP g, PushP p, const double* __restrict__ X, const dou
   if (ip >= p.n) return;
   if (key[ip] == KEY_INVALID) return;
   const double* POS[3] = {X, Y, Z};
-  const double ux = PX[ip] * p.ipart_mc, uy = PY[ip] * p.ipart_mc, uz = PZ[ip] * p.ipart_mc;
-  const double root = p.dtco2 / sqrt(ux * ux + uy * uy + uz * uz + 1.0);
-  const double u0[3] = {ux, uy, uz};
-  uint32_t k = 0, mul = 1;
+  double pos[3] = {0, 0, 0}, px[3] = {0, 0, 0}, ux, uy, uz;
+#pragma unroll
+  for (int d = 0; d < ND; ++d) pos[d] = POS[d][ip];
+  half_drift<ND>(p, pos, PX[ip], PY[ip], PZ[ip], px, ux, uy, uz);
+  int cell[3] = {1, 1, 1};
 #pragma unroll
   for (int d = 0; d < ND; ++d) {
-    const double px = (POS[d][ip] - p.gml[d]) + u0[d] * root;
-    const double cr = cell_coord<SHAPE>(px, p.idx[d]);
     double frac;
-    int cell = cell_round(cr, frac);          // 1-based
-    int e = cell - (1 - KM);
-    e = e < 0 ? 0 : (e >= g.kn[d] ? g.kn[d] - 1 : e);
-    k += mul * (uint32_t)e;
-    mul *= (uint32_t)g.kn[d];
+    cell[d] = cell_round(cell_coord<SHAPE>(px[d], p.idx[d]), frac);   // 1-based
   }
+  const uint32_t k = cell_key<ND>(g, cell);
   key[ip] = k;
 }
 
@@ -215,15 +211,20 @@ static PushP make_push_params(eb200_ctx* c, const SpeciesD& sp, long long n) {
   return p;
 }
 
-static int32_t ensure_cells(eb200_ctx* c) {
+static int32_t ensure_cells(eb200_ctx* c, SpeciesD& sp) {
   const long long need = c->g.ncell_ext + 2;
-  if (c->cell_cap >= need) return 0;
-  if (c->cell_count) cudaFree(c->cell_count);
-  if (c->cell_start) cudaFree(c->cell_start);
-  c->cell_count = c->cell_start = nullptr; c->cell_cap = 0;
-  EB_CUDA(c, cudaMalloc(&c->cell_count, (size_t)need * sizeof(uint32_t)));
-  EB_CUDA(c, cudaMalloc(&c->cell_start, (size_t)need * sizeof(uint32_t)));
-  c->cell_cap = need;
+  if (c->cell_cap < need) {
+    if (c->cell_count) cudaFree(c->cell_count);
+    c->cell_count = nullptr; c->cell_cap = 0;
+    EB_CUDA(c, cudaMalloc(&c->cell_count, (size_t)need * sizeof(uint32_t)));
+    c->cell_cap = need;
+  }
+  if (sp.cell_cap < need) {
+    if (sp.cell_start) cudaFree(sp.cell_start);
+    sp.cell_start = nullptr; sp.cell_cap = 0;
+    EB_CUDA(c, cudaMalloc(&sp.cell_start, (size_t)need * sizeof(uint32_t)));
+    sp.cell_cap = need;
+  }
   return 0;
 }
 
@@ -234,7 +235,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
   ScopedPhase ph(c, "sort");
   if (n_slots == 0) { sp.n = 0; sp.sorted = true; return 0; }
   if (n_slots >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "more than 2^32 particles per species per GPU");
-  EB_TRY(ensure_cells(c));
+  EB_TRY(ensure_cells(c, sp));
   const uint32_t nbucket = (uint32_t)(c->g.ncell_ext + 1);   // last = invalid
   const int B = 256;
   const unsigned gp = (unsigned)((n_slots + B - 1) / B);
@@ -247,16 +248,16 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
   EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
   k_hist<<<gp, B, 0, c->stream>>>(sp.key, n_slots, c->cell_count, nbucket);
   size_t tmp = 0;
-  cub::DeviceScan::ExclusiveSum(nullptr, tmp, c->cell_count, c->cell_start, (int)(nbucket + 1), c->stream);
+  cub::DeviceScan::ExclusiveSum(nullptr, tmp, c->cell_count, sp.cell_start, (int)(nbucket + 1), c->stream);
   if (tmp > c->cub_tmp_bytes) {
     if (c->cub_tmp) cudaFree(c->cub_tmp);
     c->cub_tmp = nullptr; c->cub_tmp_bytes = 0;
     EB_CUDA(c, cudaMalloc(&c->cub_tmp, tmp));
     c->cub_tmp_bytes = tmp;
   }
-  cub::DeviceScan::ExclusiveSum(c->cub_tmp, tmp, c->cell_count, c->cell_start, (int)(nbucket + 1), c->stream);
+  cub::DeviceScan::ExclusiveSum(c->cub_tmp, tmp, c->cell_count, sp.cell_start, (int)(nbucket + 1), c->stream);
   EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
-  k_dest<<<gp, B, 0, c->stream>>>(sp.key, n_slots, c->cell_start, c->cell_count, sp.dest, nbucket);
+  k_dest<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket);
   c->launches += 5;
   // scatter each attribute through one spare array; the spare rotates
   if (c->attr_scratch_cap < sp.cap) {
@@ -279,7 +280,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
     c->launches++;
   }
   // live count = start of the invalid bucket
-  EB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->cell_start + (nbucket - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  EB_CUDA(c, cudaMemcpyAsync(c->h_counters, sp.cell_start + (nbucket - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
   EB_CUDA(c, cudaStreamSynchronize(c->stream));
   sp.n = (long long)(*(uint32_t*)c->h_counters);
   // keys of the live range are now implied by cell_start; reset them to "valid"

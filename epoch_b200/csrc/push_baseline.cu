@@ -45,17 +45,11 @@ __global__ void __launch_bounds__(128) k_push_baseline(GridP g, FieldP F, PushP 
   if (ip >= p.n) return;
   double* POS[3] = {X, Y, Z};
   const double part_weight = W[ip];
-  double px[3] = {0, 0, 0};
+  double px[3] = {0, 0, 0}, pos0[3] = {0, 0, 0};
 #pragma unroll
-  for (int d = 0; d < ND; ++d) px[d] = POS[d][ip] - p.gml[d];
-  double ux = PX[ip] * p.ipart_mc, uy = PY[ip] * p.ipart_mc, uz = PZ[ip] * p.ipart_mc;
-  double gamma_rel = sqrt(ux * ux + uy * uy + uz * uz + 1.0);
-  double root = p.dtco2 / gamma_rel;
-  {
-    const double u0[3] = {ux, uy, uz};
-#pragma unroll
-    for (int d = 0; d < ND; ++d) px[d] = px[d] + u0[d] * root;
-  }
+  for (int d = 0; d < ND; ++d) pos0[d] = POS[d][ip];
+  double ux, uy, uz, gamma_rel, root;
+  half_drift<ND>(p, pos0, PX[ip], PY[ip], PZ[ip], px, ux, uy, uz);
   int cell1[3] = {1, 1, 1}, cell2[3] = {1, 1, 1};
   double wg[3][NW], wh[3][NW];
 #pragma unroll

@@ -72,6 +72,36 @@ __device__ __forceinline__ int cell_floor(double r, double& frac) {
   return (int)fl + 1;
 }
 
+// half drift to t+dt/2 (particles.F90:242-257) with every rounding pinned by
+// intrinsics, so that the sort-key kernel and the push kernels place a particle in
+// the same cell bit for bit.  pos[] are absolute positions, out: px[] relative to
+// x_grid_min_local, u = p / (m c).
+template <int ND>
+__device__ __forceinline__ void half_drift(const PushP& p, const double* pos, double mx, double my, double mz,
+                                           double* px, double& ux, double& uy, double& uz) {
+  ux = __dmul_rn(mx, p.ipart_mc); uy = __dmul_rn(my, p.ipart_mc); uz = __dmul_rn(mz, p.ipart_mc);
+  const double g2 = __fma_rn(uz, uz, __fma_rn(uy, uy, __fma_rn(ux, ux, 1.0)));
+  const double root = __ddiv_rn(p.dtco2, __dsqrt_rn(g2));
+  const double u0[3] = {ux, uy, uz};
+#pragma unroll
+  for (int d = 0; d < ND; ++d) px[d] = __fma_rn(u0[d], root, __dadd_rn(pos[d], -p.gml[d]));
+}
+
+// tile-major sort key of the (1-based) cell triple, clamped into the extended grid
+template <int ND>
+__device__ __forceinline__ uint32_t cell_key(const GridP& g, const int* cell) {
+  uint32_t tile = 0, tmul = 1, loc = 0, lmul = 1;
+#pragma unroll
+  for (int d = 0; d < ND; ++d) {
+    int e = cell[d] - (1 - KM);
+    e = e < 0 ? 0 : (e >= g.kn[d] ? g.kn[d] - 1 : e);
+    const int td = tile_dim(ND, d);
+    tile += tmul * (uint32_t)(e / td); tmul *= (uint32_t)g.ntile[d];
+    loc += lmul * (uint32_t)(e % td); lmul *= (uint32_t)td;
+  }
+  return tile * (uint32_t)g.cpt + loc;
+}
+
 // Boris rotation (particles.F90:347-394); u is updated in place
 __device__ __forceinline__ void boris(double& ux, double& uy, double& uz, double ex, double ey, double ez,
                                       double bx, double by, double bz, double cmratio, double ccmratio) {

@@ -1,10 +1,521 @@
-// push_tiled.cu -- cell-sorted fast path for push + deposit (placeholder until the
-// tiled kernel lands; the dispatcher falls back to the general kernel).
+// push_tiled.cu -- tiled push + deposit for cell-sorted particles (2D/3D, tophat
+// and triangle shapes).  Replaces the per-particle loop of push_particles
+// (epoch3d/src/particles.F90:214-608, epoch2d :199-540).
+//
+// One CTA owns one tile of cells (3D 8x8x4, 2D 16x16; ctx.cuh tile_dim) whose
+// particles are contiguous because the sort key is tile-major.  Per tile:
+//   * E,B of the tile + gather halo are staged in shared memory once; J of the
+//     tile + deposit halo is accumulated in shared memory and flushed to HBM once
+//     (RED.ADD.F64 -- neighbouring tiles overlap in their halos).
+//   * The tile is walked in chunks of G = 64 consecutive cells.  Each chunk's
+//     particles are processed in sub-ranges of <= RCAP particles, in two phases:
+//       phase 1, thread per particle (coalesced, same-cell lanes -> broadcast
+//         shared loads): half drift, gather, Boris, drift, store; then the deposit
+//         inputs are left in shared memory as a compact record (fractions at
+//         t+dt/2 and t+3dt/2, cell shift, weight[, v_z]);
+//       phase 2, thread per (cell, current component): walks the records of its own
+//         cell and accumulates the component's contributions on the cell's
+//         NW^ND stencil box in REGISTERS -- no atomics, no shuffles: the reduction
+//         over the particles of a cell is a serial sum in one thread.
+//     A particle that changed cell (|dcell| = 1 on some axis) reaches one layer
+//     beyond the box; those few values are added by phase 2b, one warp per such
+//     particle, lane per (component, cell), with shared-memory atomics.
+//   * After the chunk the register boxes are added to the shared J tile with plain
+//     read-modify-writes: lanes of a warp are distinct cells of one component, and
+//     the two warps of a component take turns.
+// The Esirkepov sums are evaluated in factored form,
+//   Jx(i,j,k) = -fjx * cumsum_i(hx) * (gy(j) zf1(k) + hy(j) zf2(k)),   (cyclic)
+// which is the reference's running sum (particles.F90:522-563) with the common
+// factor taken out; the result differs from the reference order by rounding only.
 #include "push_common.cuh"
+
 namespace eb {
+
+namespace {
+
+constexpr int NT = 192;          // threads per CTA = 64 cells x 3 components in phase 2
+constexpr int G = 64;            // cells per chunk
+constexpr int RCAP = 512;        // particles per sub-range (record capacity)
+constexpr int RPAD = RCAP + RCAP / 16 + 1;   // swizzled record index r + (r >> 4)
+constexpr int NREC = 7;          // doubles per record
+
+template <int ND, int SHAPE>
+struct TL {
+  static constexpr int NW = Sh<SHAPE>::NW, SFM = Sh<SHAPE>::SFMIN;
+  static constexpr int TX = tile_dim(ND, 0), TY = tile_dim(ND, 1), TZ = tile_dim(ND, 2);
+  static constexpr int CPT = TX * TY * TZ;
+  // gather region: cells c0+SFM-1 .. c0+T-1+SFM+NW-1  (T + NW wide)
+  static constexpr int FX = TX + NW, FY = ND >= 2 ? TY + NW : 1, FZ = ND >= 3 ? TZ + NW : 1;
+  static constexpr int FN = FX * FY * FZ;
+  // deposit region: cells c0+SFM-1 .. c0+T-1+SFM+NW  (T + NW + 1 wide)
+  static constexpr int JX = TX + NW + 1, JY = ND >= 2 ? TY + NW + 1 : 1, JZ = ND >= 3 ? TZ + NW + 1 : 1;
+  static constexpr int JN = JX * JY * JZ;
+  static constexpr int NACC = ND == 3 ? NW * NW * NW : NW * NW;
+  static constexpr size_t SMEM = sizeof(double) * (6 * FN + 3 * JN + NREC * RPAD) + sizeof(int) * (RPAD + RCAP + G + 1 + 3);
+};
+
+__device__ __forceinline__ int swz(int r) { return r + (r >> 4); }
+
+// weights at t+3dt/2 expressed on the t+dt/2 stencil: box part hb[i] (slot SFM+i),
+// and the single slots one beyond the box on either side
+template <int SHAPE>
+__device__ __forceinline__ void axis_weights(double f1, double f3, int dc, double* g, double* hb, double& h_lo, double& h_hi) {
+  constexpr int NW = Sh<SHAPE>::NW;
+  double w3[NW];
+  shape_weights<SHAPE>(f1, g);
+  shape_weights<SHAPE>(f3, w3);
+  h_lo = dc < 0 ? w3[0] : 0.0;
+  h_hi = dc > 0 ? w3[NW - 1] : 0.0;
+#pragma unroll
+  for (int i = 0; i < NW; ++i) {
+    const double same = w3[i];
+    const double up = i >= 1 ? w3[i >= 1 ? i - 1 : 0] : 0.0;        // dc = +1: new weight index i-1
+    const double dn = i < NW - 1 ? w3[i < NW - 1 ? i + 1 : 0] : 0.0;   // dc = -1: new weight index i+1
+    const double nw = dc == 0 ? same : (dc > 0 ? up : dn);
+    hb[i] = nw - g[i];
+  }
+}
+
+}  // namespace
+
+namespace {
+
+// interpolation of one staged field component (include/*/e_part.inc, b_part.inc):
+// nested sums over x (innermost), y, z with the weights of the component's stagger
+template <int ND, int SHAPE>
+__device__ __forceinline__ double gather_tile(const double* __restrict__ f, const double* wx, const double* wy,
+                                              const double* wz, int bx, int by, int bz) {
+  using T = TL<ND, SHAPE>;
+  constexpr int NW = T::NW;
+  const double* b = f + ((ND >= 3 ? bz : 0) * T::FY + (ND >= 2 ? by : 0)) * T::FX + bx;
+  double accz = 0.0;
+#pragma unroll
+  for (int k = 0; k < (ND >= 3 ? NW : 1); ++k) {
+    double accy = 0.0;
+#pragma unroll
+    for (int j = 0; j < (ND >= 2 ? NW : 1); ++j) {
+      double accx = 0.0;
+#pragma unroll
+      for (int i = 0; i < NW; ++i) {
+        const double t = wx[i] * b[(k * T::FY + j) * T::FX + i];
+        accx = i == 0 ? t : accx + t;
+      }
+      if (ND >= 2) { const double t = wy[j] * accx; accy = j == 0 ? t : accy + t; }
+      else accy = accx;
+    }
+    if (ND >= 3) { const double t = wz[k] * accy; accz = k == 0 ? t : accz + t; }
+    else accz = accy;
+  }
+  return accz;
+}
+
+// 3D box accumulation of component A (cumsum axis A, product axes P = A+1, Q = A+2)
+template <int A, int NW>
+__device__ __forceinline__ void box3(double* acc, const double (*g)[NW], const double (*hb)[NW], const double* hlo,
+                                     double fj) {
+  constexpr int P = (A + 1) % 3, Q = (A + 2) % 3;
+  const double third = 1.0 / 3.0;
+  double ca[NW], qf1[NW], qf2[NW];
+  double c = hlo[A];
+#pragma unroll
+  for (int i = 0; i < NW; ++i) { c += hb[A][i]; ca[i] = fj * c; }
+#pragma unroll
+  for (int v = 0; v < NW; ++v) {
+    qf1[v] = g[Q][v] + 0.5 * hb[Q][v];
+    qf2[v] = third * hb[Q][v] + 0.5 * g[Q][v];
+  }
+#pragma unroll
+  for (int v = 0; v < NW; ++v)
+#pragma unroll
+    for (int u = 0; u < NW; ++u) {
+      const double w = g[P][u] * qf1[v] + hb[P][u] * qf2[v];
+#pragma unroll
+      for (int i = 0; i < NW; ++i) acc[(v * NW + u) * NW + i] += ca[i] * w;
+    }
+}
+
+// add the register box of component A to the shared J tile with plain read-modify-
+// writes.  The lanes of a warp are 32 distinct cells of ONE z-plane of the tile, so
+// for a fixed (dx, dy) the NW updates along z never collide between lanes; updates
+// with different (dx, dy) can (lane A's cell+1 is lane B's cell), so those steps are
+// ordered with __syncwarp() -- which also keeps the compiler from hoisting the
+// loads of a later step above the stores of an earlier one.
+template <int A, int NW, int JX, int JY>
+__device__ __forceinline__ void flush3(double* sj, const double* acc, const int* l) {
+  constexpr int P = (A + 1) % 3, Q = (A + 2) % 3;
+  double* b = sj + (l[0] + 1) + (l[1] + 1) * JX + (l[2] + 1) * JX * JY;
+#pragma unroll
+  for (int dy = 0; dy < NW; ++dy)
+#pragma unroll
+    for (int dx = 0; dx < NW; ++dx) {
+#pragma unroll
+      for (int dz = 0; dz < NW; ++dz) {
+        const int o[3] = {dx, dy, dz};
+        b[dx + dy * JX + dz * JX * JY] += acc[(o[Q] * NW + o[P]) * NW + o[A]];
+      }
+      __syncwarp();
+    }
+}
+
+template <int N>
+__device__ __forceinline__ double pick(const double* a, int t) {
+  double r = a[0];
+#pragma unroll
+  for (int i = 1; i < N; ++i) r = t == i ? a[i] : r;
+  return r;
+}
+
+}  // namespace
+
+namespace {
+
+struct PArr { double* x[3]; double* m[3]; const double* w; };
+
+// phase 1 for one particle: particles.F90:219-452 (gather stage, Boris, drift, store,
+// extra half drift); leaves the deposit inputs in the record arrays
+template <int ND, int SHAPE>
+__device__ __forceinline__ void push_one(const PushP& p, const PArr& a, long long ip, const int* c0,
+                                         const double* __restrict__ sF, double* __restrict__ sR, int* __restrict__ sD,
+                                         int* __restrict__ sM, int* __restrict__ sCnt, int r,
+                                         unsigned long long* counters) {
+  using T = TL<ND, SHAPE>;
+  constexpr int NW = T::NW;
+  double pos[3] = {0, 0, 0}, px[3] = {0, 0, 0}, ux, uy, uz;
+#pragma unroll
+  for (int d = 0; d < ND; ++d) pos[d] = a.x[d][ip];
+  const double part_weight = a.w[ip];
+  half_drift<ND>(p, pos, a.m[0][ip], a.m[1][ip], a.m[2][ip], px, ux, uy, uz);
+  int cell1[3] = {1, 1, 1}, l1[3] = {0, 0, 0}, l2[3] = {0, 0, 0};
+  double f1[3] = {0, 0, 0};
+  double wg[3][NW], wh[3][NW];
+  bool bad = false;
+#pragma unroll
+  for (int d = 0; d < ND; ++d) {
+    const double cr = cell_coord<SHAPE>(px[d], p.idx[d]);
+    cell1[d] = cell_round(cr, f1[d]);
+    shape_weights<SHAPE>(f1[d], wg[d]);
+    double f2;
+    const int cell2 = cell_floor(cr, f2);
+    shape_weights<SHAPE>(f2, wh[d]);
+    l1[d] = cell1[d] - c0[d];
+    l2[d] = cell2 - c0[d];
+    const int td = tile_dim(ND, d);
+    if ((unsigned)l1[d] >= (unsigned)td) { bad = true; l1[d] = l1[d] < 0 ? 0 : td - 1; l2[d] = l1[d]; }
+  }
+  if (bad) atomicAdd(counters + 8, 1ULL);   // key and push disagree on the cell: must never happen
+  // region index of weight slot i: g-type l1 + 1 + i, h-type l2 + 1 + i
+  const int gx = l1[0] + 1, gy = l1[1] + 1, gz = l1[2] + 1, hx = l2[0] + 1, hy = l2[1] + 1, hz = l2[2] + 1;
+  const double ex_part = gather_tile<ND, SHAPE>(sF + 0 * T::FN, wh[0], wg[1], wg[2], hx, gy, gz);
+  const double ey_part = gather_tile<ND, SHAPE>(sF + 1 * T::FN, wg[0], wh[1], wg[2], gx, hy, gz);
+  const double ez_part = gather_tile<ND, SHAPE>(sF + 2 * T::FN, wg[0], wg[1], wh[2], gx, gy, hz);
+  const double bx_part = gather_tile<ND, SHAPE>(sF + 3 * T::FN, wg[0], wh[1], wh[2], gx, hy, hz);
+  const double by_part = gather_tile<ND, SHAPE>(sF + 4 * T::FN, wh[0], wg[1], wh[2], hx, gy, hz);
+  const double bz_part = gather_tile<ND, SHAPE>(sF + 5 * T::FN, wh[0], wh[1], wg[2], hx, hy, gz);
+
+  boris(ux, uy, uz, ex_part, ey_part, ez_part, bx_part, by_part, bz_part, p.cmratio, p.ccmratio);
+
+  const double gamma_rel = sqrt(ux * ux + uy * uy + uz * uz + 1.0);
+  double delta[3] = {0, 0, 0}, part_vz = 0.0;
+  if (ND == 3) {
+    const double root = p.dtco2 / gamma_rel;
+    delta[0] = ux * root; delta[1] = uy * root; delta[2] = uz * root;
+  } else {
+    const double igamma = 1.0 / gamma_rel;
+    const double root = p.dtco2 * igamma;
+    delta[0] = ux * root; delta[1] = uy * root;
+    part_vz = uz * C0 * igamma;
+  }
+#pragma unroll
+  for (int d = 0; d < ND; ++d) {
+    px[d] = px[d] + delta[d];
+    a.x[d][ip] = px[d] + p.gml[d];
+  }
+  a.m[0][ip] = p.part_mc * ux; a.m[1][ip] = p.part_mc * uy; a.m[2][ip] = p.part_mc * uz;
+  if (p.zero_current) return;
+
+  int pack = 0;
+  const int rs = swz(r);
+#pragma unroll
+  for (int d = 0; d < ND; ++d) {
+    px[d] = px[d] + delta[d];
+    double f3;
+    const int cell3 = cell_round(cell_coord<SHAPE>(px[d], p.idx[d]), f3);
+    int dc = cell3 - cell1[d];
+    dc = dc < -1 ? -1 : (dc > 1 ? 1 : dc);          // |dcell| <= 1 by the CFL condition (particles.F90:506-507)
+    pack |= (dc + 1) << (2 * d);
+    sR[d * RPAD + rs] = f1[d];
+    sR[(ND + d) * RPAD + rs] = f3;
+  }
+  sR[2 * ND * RPAD + rs] = part_weight;
+  if (ND == 2) sR[(2 * ND + 1) * RPAD + rs] = part_vz;
+  const int lc = (l1[2] * T::TY + l1[1]) * T::TX + l1[0];
+  sD[rs] = pack | (lc << 8);
+  const int stay = ND == 3 ? 0x15 : 0x5;             // all dcell == 0
+  if (pack != stay) sM[atomicAdd(sCnt, 1)] = r;
+}
+
+}  // namespace
+
+namespace {
+
+// phase 2b: the warp adds the contributions of one cell-changing particle that fall
+// outside its home box (at most one layer per axis), lane per (component, cell)
+template <int ND, int SHAPE>
+__device__ __forceinline__ void mover_overflow(const PushP& p, const double* __restrict__ sR, const int* __restrict__ sD,
+                                               double* __restrict__ sJ, int r, int lane) {
+  using T = TL<ND, SHAPE>;
+  constexpr int NW = T::NW, NS = NW + 2;
+  const int rs = swz(r);
+  const int pk = sD[rs];
+  const int lc = pk >> 8;
+  const int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
+  const double w = sR[2 * ND * RPAD + rs];
+  // full-window arrays per axis: index t = 0 (slot below the box), 1..NW (box), NW+1 (slot above)
+  double g5[ND][NS], h5[ND][NS], c5[ND][NS];
+  int dc[ND], wd[ND], tlo[ND], tov[ND], ov[ND];
+#pragma unroll
+  for (int d = 0; d < ND; ++d) {
+    dc[d] = ((pk >> (2 * d)) & 3) - 1;
+    double g[NW], hb[NW], hlo, hhi;
+    axis_weights<SHAPE>(sR[d * RPAD + rs], sR[(ND + d) * RPAD + rs], dc[d], g, hb, hlo, hhi);
+    g5[d][0] = 0.0; g5[d][NS - 1] = 0.0; h5[d][0] = hlo; h5[d][NS - 1] = hhi;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) { g5[d][i + 1] = g[i]; h5[d][i + 1] = hb[i]; }
+    double c = 0.0;
+#pragma unroll
+    for (int t = 0; t < NS; ++t) { c += h5[d][t]; c5[d][t] = c; }
+    ov[d] = dc[d] != 0;
+    wd[d] = NW + ov[d];
+    tlo[d] = dc[d] < 0 ? 0 : 1;
+    tov[d] = dc[d] < 0 ? 0 : NW + 1;
+  }
+  const double third = 1.0 / 3.0;
+  int nov;
+  if (ND == 3) nov = ov[0] * wd[1] * wd[2] + NW * ov[1] * wd[2] + NW * NW * ov[2];
+  else nov = ov[0] * wd[1] + NW * ov[1];
+  for (int it = lane; it < 3 * nov; it += 32) {
+    const int comp = it / nov;
+    int q = it - comp * nov;
+    int t[3] = {1, 1, 1};
+    if (ND == 3) {
+      const int n0 = ov[0] * wd[1] * wd[2], n1 = NW * ov[1] * wd[2];
+      if (q < n0) { t[0] = tov[0]; t[1] = tlo[1] + q % wd[1]; t[2] = tlo[2] + q / wd[1]; }
+      else if (q < n0 + n1) { q -= n0; t[0] = 1 + q % NW; t[1] = tov[1]; t[2] = tlo[2] + q / NW; }
+      else { q -= n0 + n1; t[0] = 1 + q % NW; t[1] = 1 + (q / NW) % NW; t[2] = tov[2]; }
+    } else {
+      const int n0 = ov[0] * wd[1];
+      if (q < n0) { t[0] = tov[0]; t[1] = tlo[1] + q; }
+      else { q -= n0; t[0] = 1 + q; t[1] = tov[1]; }
+    }
+    double gv[ND], hv[ND], cv[ND];
+#pragma unroll
+    for (int d = 0; d < ND; ++d) {
+      gv[d] = pick<NS>(g5[d], t[d]); hv[d] = pick<NS>(h5[d], t[d]); cv[d] = pick<NS>(c5[d], t[d]);
+    }
+    double val;
+    if (ND == 3) {
+      // component A: -fj * C_A * (g_P * (g_Q + h_Q/2) + h_P * (h_Q/3 + g_Q/2)),  P = A+1, Q = A+2
+      const int A = comp, P = (comp + 1) % 3, Q = (comp + 2) % 3;
+      const double gA = comp == 0 ? cv[0] : (comp == 1 ? cv[1] : cv[2]);
+      const double gP = P == 0 ? gv[0] : (P == 1 ? gv[1] : gv[2]);
+      const double hP = P == 0 ? hv[0] : (P == 1 ? hv[1] : hv[2]);
+      const double gQ = Q == 0 ? gv[0] : (Q == 1 ? gv[1] : gv[2]);
+      const double hQ = Q == 0 ? hv[0] : (Q == 1 ? hv[1] : hv[2]);
+      const double fc = A == 0 ? p.fc[0] : (A == 1 ? p.fc[1] : p.fc[2]);
+      val = -(fc * w * p.q) * gA * (gP * (gQ + 0.5 * hQ) + hP * (third * hQ + 0.5 * gQ));
+    } else {
+      const double xf1 = gv[0] + 0.5 * hv[0];
+      const double yf1 = gv[1] + 0.5 * hv[1], yf2 = third * hv[1] + 0.5 * gv[1];
+      if (comp == 0) val = -(p.fc[0] * w * p.q) * cv[0] * yf1;
+      else if (comp == 1) val = -(p.fc[1] * w * p.q) * cv[1] * xf1;
+      else val = (p.fc[2] * w * p.q * sR[(2 * ND + 1) * RPAD + rs]) * (gv[0] * yf1 + hv[0] * yf2);
+    }
+    const int idx = ((ND >= 3 ? (l[2] + t[2]) : 0) * T::JY + (ND >= 2 ? (l[1] + t[1]) : 0)) * T::JX + l[0] + t[0];
+    atomicAdd(sJ + comp * T::JN + idx, val);
+  }
+}
+
+}  // namespace
+
+namespace {
+
+template <int ND, int SHAPE>
+__global__ void __launch_bounds__(NT, 2) k_push_tiled(GridP g, FieldP F, PushP p, PArr a,
+                                                      const uint32_t* __restrict__ cell_start,
+                                                      unsigned long long* counters) {
+  using T = TL<ND, SHAPE>;
+  constexpr int NW = T::NW, SFM = T::SFM;
+  extern __shared__ double smem[];
+  double* sF = smem;                       // [6][FN]   E,B of the tile + gather halo
+  double* sJ = sF + 6 * T::FN;             // [3][JN]   J of the tile + deposit halo
+  double* sR = sJ + 3 * T::JN;             // [NREC][RPAD] deposit records of the current sub-range
+  int* sD = (int*)(sR + NREC * RPAD);      // [RPAD]    cell shift pack | tile-local cell << 8
+  int* sM = sD + RPAD;                     // [RCAP]    records of particles that changed cell
+  uint32_t* sStart = (uint32_t*)(sM + RCAP);   // [G+1] particle offsets of the chunk's cells
+  int* sCnt = (int*)(sStart + G + 1);
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long tile = blockIdx.x;
+  const long long kbase = tile * T::CPT;
+  const uint32_t pb = cell_start[kbase], pe = cell_start[kbase + T::CPT];
+  if (pb == pe) return;
+  int tc[3];
+  tc[0] = (int)(tile % g.ntile[0]);
+  tc[1] = (int)((tile / g.ntile[0]) % g.ntile[1]);
+  tc[2] = (int)(tile / ((long long)g.ntile[0] * g.ntile[1]));
+  int c0[3], org[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    c0[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) : 1;   // Fortran coordinate of the tile's first cell
+    org[d] = d < ND ? c0[d] + SFM - 1 : 1;                     // ... of the first staged cell
+  }
+  // stage E,B (zero outside the allocated array)
+  for (int i = tid; i < 6 * T::FN; i += NT) {
+    const int comp = i / T::FN, r = i - comp * T::FN;
+    const int fx = r % T::FX, fy = (r / T::FX) % T::FY, fz = r / (T::FX * T::FY);
+    const int X = org[0] + fx, Y = org[1] + fy, Z = org[2] + fz;
+    const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
+                    Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
+    sF[i] = in ? __ldg(F.f[comp] + g.idx(X, Y, Z)) : 0.0;
+  }
+  for (int i = tid; i < 3 * T::JN; i += NT) sJ[i] = 0.0;
+
+  const int comp = warp >> 1;                 // phase 2 identity: component and cell of the chunk
+  const int ci = ((warp & 1) << 5) + lane;
+  double acc[T::NACC];
+
+  for (int ch = 0; ch < T::CPT / G; ++ch) {
+    __syncthreads();
+    if (tid <= G) sStart[tid] = cell_start[kbase + ch * G + tid];
+    __syncthreads();
+    const uint32_t cb = sStart[0], ce = sStart[G];
+    if (cb == ce) continue;
+#pragma unroll
+    for (int i = 0; i < T::NACC; ++i) acc[i] = 0.0;
+    const uint32_t my_b = sStart[ci], my_e = sStart[ci + 1];
+    const int lc = ch * G + ci;
+    const int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
+
+    for (uint32_t sb = cb; sb < ce; sb += RCAP) {
+      const uint32_t se = ce - sb > (uint32_t)RCAP ? sb + RCAP : ce;
+      if (tid == 0) sCnt[0] = 0;
+      __syncthreads();
+      // ---- phase 1: thread per particle ----
+      for (uint32_t q = sb + tid; q < se; q += NT)
+        push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, sR, sD, sM, sCnt, (int)(q - sb), counters);
+      __syncthreads();
+      if (!p.zero_current) {
+        // ---- phase 2: thread per (cell, component) over the cell's records ----
+        const uint32_t qb = my_b > sb ? my_b : sb, qe = my_e < se ? my_e : se;
+        for (uint32_t q = qb; q < qe; ++q) {
+          const int rs = swz((int)(q - sb));
+          const int pk = sD[rs];
+          double gw[ND][NW], hb[ND][NW], hlo[ND], hhi;
+#pragma unroll
+          for (int d = 0; d < ND; ++d)
+            axis_weights<SHAPE>(sR[d * RPAD + rs], sR[(ND + d) * RPAD + rs], ((pk >> (2 * d)) & 3) - 1, gw[d], hb[d], hlo[d], hhi);
+          const double wq = sR[2 * ND * RPAD + rs] * p.q;
+          if (ND == 3) {
+            if (comp == 0) box3<0, NW>(acc, gw, hb, hlo, -(p.fc[0] * wq));
+            else if (comp == 1) box3<1, NW>(acc, gw, hb, hlo, -(p.fc[1] * wq));
+            else box3<2, NW>(acc, gw, hb, hlo, -(p.fc[2] * wq));
+          } else {
+            const double third = 1.0 / 3.0;
+            if (comp == 0) {          // Jx = -fjx * cumsum_x(hx) * (gy + hy/2)
+              double c = hlo[0];
+#pragma unroll
+              for (int i = 0; i < NW; ++i) {
+                c += hb[0][i];
+                const double ca = -(p.fc[0] * wq) * c;
+#pragma unroll
+                for (int j = 0; j < NW; ++j) acc[j * NW + i] += ca * (gw[1][j] + 0.5 * hb[1][j]);
+              }
+            } else if (comp == 1) {   // Jy = -fjy * cumsum_y(hy) * (gx + hx/2)
+              double c = hlo[1];
+#pragma unroll
+              for (int j = 0; j < NW; ++j) {
+                c += hb[1][j];
+                const double ca = -(p.fc[1] * wq) * c;
+#pragma unroll
+                for (int i = 0; i < NW; ++i) acc[j * NW + i] += ca * (gw[0][i] + 0.5 * hb[0][i]);
+              }
+            } else {                  // Jz = fjz * (gx*(gy + hy/2) + hx*(hy/3 + gy/2))
+              const double fjz = p.fc[2] * wq * sR[(2 * ND + 1) * RPAD + rs];
+#pragma unroll
+              for (int j = 0; j < NW; ++j) {
+                const double yf1 = gw[1][j] + 0.5 * hb[1][j], yf2 = third * hb[1][j] + 0.5 * gw[1][j];
+#pragma unroll
+                for (int i = 0; i < NW; ++i) acc[j * NW + i] += fjz * (gw[0][i] * yf1 + hb[0][i] * yf2);
+              }
+            }
+          }
+        }
+        // ---- phase 2b: particles that changed cell, warp per particle ----
+        const int nm = sCnt[0];
+        for (int m = warp; m < nm; m += NT / 32) mover_overflow<ND, SHAPE>(p, sR, sD, sJ, sM[m], lane);
+      }
+      __syncthreads();
+    }
+    if (!p.zero_current) {
+      // ---- phase 3: register boxes -> shared J tile; the two warps of a component take turns ----
+      double* sj = sJ + comp * T::JN;
+      for (int turn = 0; turn < 2; ++turn) {
+        if ((warp & 1) == turn) {   // whole warp (empty cells add zeros): the steps inside are warp-synchronous
+          if (ND == 3) {
+            if (comp == 0) flush3<0, NW, T::JX, T::JY>(sj, acc, l);
+            else if (comp == 1) flush3<1, NW, T::JX, T::JY>(sj, acc, l);
+            else flush3<2, NW, T::JX, T::JY>(sj, acc, l);
+          } else {
+            double* b = sj + (l[1] + 1) * T::JX + l[0] + 1;
+#pragma unroll
+            for (int j = 0; j < NW; ++j)
+#pragma unroll
+              for (int i = 0; i < NW; ++i) { b[j * T::JX + i] += acc[j * NW + i]; __syncwarp(); }
+          }
+        }
+        __syncwarp();
+        if (turn == 0) asm volatile("bar.sync %0, %1;" ::"r"(1 + comp), "r"(64) : "memory");
+      }
+    }
+  }
+  __syncthreads();
+  // tile J -> HBM (neighbouring tiles overlap in the halo: RED.ADD.F64)
+  if (!p.zero_current) {
+    for (int i = tid; i < 3 * T::JN; i += NT) {
+      const double v = sJ[i];
+      if (v == 0.0) continue;
+      const int cj = i / T::JN, r = i - cj * T::JN;
+      const int jx = r % T::JX, jy = (r / T::JX) % T::JY, jz = r / (T::JX * T::JY);
+      const int X = org[0] + jx, Y = org[1] + jy, Z = org[2] + jz;
+      const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
+                      Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
+      if (in) atomicAdd(F.f[JX + cj] + g.idx(X, Y, Z), v);
+    }
+  }
+}
+
+}  // namespace
+
 int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled) {
-  (void)c; (void)sp; (void)p;
   *handled = false;
+  if (c->ndims < 2 || c->shape == SHAPE_BSPLINE3 || !sp.sorted) return 0;
+  PArr a;
+  for (int d = 0; d < 3; ++d) { a.x[d] = sp.a[d]; a.m[d] = sp.a[3 + d]; }
+  a.w = sp.a[6];
+  const long long ntiles = (long long)c->g.ntile[0] * c->g.ntile[1] * c->g.ntile[2];
+#define L(ND, SH)                                                                                       \
+  if (c->ndims == ND && c->shape == SH) {                                                               \
+    auto k = k_push_tiled<ND, SH>;                                                                      \
+    const size_t smem = TL<ND, SH>::SMEM;                                                               \
+    EB_CUDA(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
+    k<<<(unsigned)ntiles, NT, smem, c->stream>>>(c->g, c->f, p, a, sp.cell_start, c->d_counters);       \
+  }
+  L(2, 0) L(2, 1) L(3, 0) L(3, 1)
+#undef L
+  c->launches++;
+  EB_CUDA(c, cudaGetLastError());
+  *handled = true;
   return 0;
 }
+
 }  // namespace eb
