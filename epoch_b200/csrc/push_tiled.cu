@@ -34,10 +34,11 @@ namespace eb {
 namespace {
 
 constexpr int NT = 192;          // threads per CTA = 64 cells x 3 components in phase 2
-constexpr int G = 64;            // cells per chunk
+constexpr int G = 32;            // cells per chunk: 32 cells x 2 halves x 3 components = NT phase-2 threads
 constexpr int RCAP = 512;        // particles per sub-range (record capacity)
 constexpr int RPAD = RCAP + RCAP / 16 + 1;   // swizzled record index r + (r >> 4)
 constexpr int NREC = 7;          // doubles per record
+constexpr int MCAP = 1024;       // overflow work items per sub-range (more are deposited inline)
 
 template <int ND, int SHAPE>
 struct TL {
@@ -51,7 +52,7 @@ struct TL {
   static constexpr int JX = TX + NW + 1, JY = ND >= 2 ? TY + NW + 1 : 1, JZ = ND >= 3 ? TZ + NW + 1 : 1;
   static constexpr int JN = JX * JY * JZ;
   static constexpr int NACC = ND == 3 ? NW * NW * NW : NW * NW;
-  static constexpr size_t SMEM = sizeof(double) * (6 * FN + 3 * JN + NREC * RPAD) + sizeof(int) * (RPAD + RCAP + G + 1 + 3);
+  static constexpr size_t SMEM = sizeof(double) * (6 * FN + 3 * JN + NREC * RPAD) + sizeof(int) * (RPAD + MCAP + G + 1 + 3);
 };
 
 __device__ __forceinline__ int swz(int r) { return r + (r >> 4); }
@@ -135,26 +136,33 @@ __device__ __forceinline__ void box3(double* acc, const double (*g)[NW], const d
 }
 
 // add the register box of component A to the shared J tile with plain read-modify-
-// writes.  The lanes of a warp are 32 distinct cells of ONE z-plane of the tile, so
+// writes (even lanes; the odd lane of each pair has been folded in by shuffle).  The
+// writing lanes of a warp are 16 distinct cells of ONE z-plane of the tile, so
 // for a fixed (dx, dy) the NW updates along z never collide between lanes; updates
 // with different (dx, dy) can (lane A's cell+1 is lane B's cell), so those steps are
 // ordered with __syncwarp() -- which also keeps the compiler from hoisting the
 // loads of a later step above the stores of an earlier one.
 template <int A, int NW, int JX, int JY>
-__device__ __forceinline__ void flush3(double* sj, const double* acc, const int* l) {
+__device__ __forceinline__ void flush3(double* sj, const double* acc, const int* l, bool writer, int bar_id) {
   constexpr int P = (A + 1) % 3, Q = (A + 2) % 3;
   double* b = sj + (l[0] + 1) + (l[1] + 1) * JX + (l[2] + 1) * JX * JY;
 #pragma unroll
-  for (int dy = 0; dy < NW; ++dy)
+  for (int dy = 0; dy < NW; ++dy) {
 #pragma unroll
     for (int dx = 0; dx < NW; ++dx) {
+      if (writer) {
 #pragma unroll
-      for (int dz = 0; dz < NW; ++dz) {
-        const int o[3] = {dx, dy, dz};
-        b[dx + dy * JX + dz * JX * JY] += acc[(o[Q] * NW + o[P]) * NW + o[A]];
+        for (int dz = 0; dz < NW; ++dz) {
+          const int o[3] = {dx, dy, dz};
+          b[dx + dy * JX + dz * JX * JY] += acc[(o[Q] * NW + o[P]) * NW + o[A]];
+        }
       }
       __syncwarp();
     }
+    // the two warps of a component hold disjoint cell rows: at the same dy they touch disjoint
+    // J rows, so they only have to stay in step
+    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(64) : "memory");
+  }
 }
 
 template <int N>
@@ -169,6 +177,87 @@ __device__ __forceinline__ double pick(const double* a, int t) {
 
 namespace {
 
+// One overflow work item of a 3D particle that changed cell: current component A,
+// overflowing axis m.  The window cells outside the home box are split, per
+// component, by the first overflowing axis in the order (A, P, Q):
+//   m == A: cells one below the box along A (dcell = -1; above the box the running
+//           sum has returned to zero), any (u, v) of the P x Q window;
+//   m == P: u beyond the box, a inside it, any v of the Q window;
+//   m == Q: v beyond the box, a and u inside it.
+// Thread per item; the values go to the shared J tile with atomics.
+template <int SHAPE>
+__device__ __forceinline__ void mover_item3(const PushP& p, const double* __restrict__ sR, const int* __restrict__ sD,
+                                            double* __restrict__ sJ, int code) {
+  using T = TL<3, SHAPE>;
+  constexpr int NW = T::NW, NS = NW + 2;
+  const int r = code & 0xffff, A = (code >> 16) & 3, m = (code >> 18) & 3;
+  const int P = A == 2 ? 0 : A + 1, Q = P == 2 ? 0 : P + 1;
+  const int rs = swz(r);
+  const int pk = sD[rs];
+  const int lc = pk >> 8;
+  const int l0 = lc % T::TX, l1 = (lc / T::TX) % T::TY, l2 = lc / (T::TX * T::TY);
+  const int dcA = ((pk >> (2 * A)) & 3) - 1, dcP = ((pk >> (2 * P)) & 3) - 1, dcQ = ((pk >> (2 * Q)) & 3) - 1;
+  double gA[NW], hA[NW], gP[NW], hP[NW], gQ[NW], hQ[NW], loA, hiA, loP, hiP, loQ, hiQ;
+  axis_weights<SHAPE>(sR[A * RPAD + rs], sR[(3 + A) * RPAD + rs], dcA, gA, hA, loA, hiA);
+  axis_weights<SHAPE>(sR[P * RPAD + rs], sR[(3 + P) * RPAD + rs], dcP, gP, hP, loP, hiP);
+  axis_weights<SHAPE>(sR[Q * RPAD + rs], sR[(3 + Q) * RPAD + rs], dcQ, gQ, hQ, loQ, hiQ);
+  const double fj = -(p.fc[A] * sR[6 * RPAD + rs] * p.q);
+  const double third = 1.0 / 3.0;
+  const int stA = A == 0 ? 1 : (A == 1 ? T::JX : T::JX * T::JY);
+  const int stP = P == 0 ? 1 : (P == 1 ? T::JX : T::JX * T::JY);
+  const int stQ = Q == 0 ? 1 : (Q == 1 ? T::JX : T::JX * T::JY);
+  double* base = sJ + A * T::JN + l0 + l1 * T::JX + l2 * T::JX * T::JY;   // window index t = 0 <-> region index l
+  // full-window arrays along Q (t = 0 .. NW+1)
+  double q1[NS], q2[NS];
+  q1[0] = 0.5 * loQ; q2[0] = third * loQ; q1[NS - 1] = 0.5 * hiQ; q2[NS - 1] = third * hiQ;
+#pragma unroll
+  for (int v = 0; v < NW; ++v) { q1[v + 1] = gQ[v] + 0.5 * hQ[v]; q2[v + 1] = third * hQ[v] + 0.5 * gQ[v]; }
+  if (m == A) {
+    const double cov = fj * loA;
+    double g5[NS], h5[NS];
+    g5[0] = 0.0; g5[NS - 1] = 0.0; h5[0] = loP; h5[NS - 1] = hiP;
+#pragma unroll
+    for (int u = 0; u < NW; ++u) { g5[u + 1] = gP[u]; h5[u + 1] = hP[u]; }
+#pragma unroll
+    for (int v = 0; v < NS; ++v)
+#pragma unroll
+      for (int u = 0; u < NS; ++u) {
+        const double val = cov * (g5[u] * q1[v] + h5[u] * q2[v]);
+        if (val != 0.0) atomicAdd(base + u * stP + v * stQ, val);
+      }
+  } else {
+    double ca[NW];
+    double c = loA;
+#pragma unroll
+    for (int i = 0; i < NW; ++i) { c += hA[i]; ca[i] = fj * c; }
+    if (m == P) {
+      const int tu = dcP < 0 ? 0 : NW + 1;
+      const double hov = dcP < 0 ? loP : hiP;
+#pragma unroll
+      for (int v = 0; v < NS; ++v) {
+        const double w = hov * q2[v];
+        if (w != 0.0) {
+#pragma unroll
+          for (int i = 0; i < NW; ++i) atomicAdd(base + (1 + i) * stA + tu * stP + v * stQ, ca[i] * w);
+        }
+      }
+    } else {
+      const int tv = dcQ < 0 ? 0 : NW + 1;
+      const double hq = dcQ < 0 ? loQ : hiQ;
+#pragma unroll
+      for (int u = 0; u < NW; ++u) {
+        const double w = gP[u] * (0.5 * hq) + hP[u] * (third * hq);
+#pragma unroll
+        for (int i = 0; i < NW; ++i) atomicAdd(base + (1 + i) * stA + (1 + u) * stP + tv * stQ, ca[i] * w);
+      }
+    }
+  }
+}
+
+}  // namespace
+
+namespace {
+
 struct PArr { double* x[3]; double* m[3]; const double* w; };
 
 // phase 1 for one particle: particles.F90:219-452 (gather stage, Boris, drift, store,
@@ -176,7 +265,7 @@ struct PArr { double* x[3]; double* m[3]; const double* w; };
 template <int ND, int SHAPE>
 __device__ __forceinline__ void push_one(const PushP& p, const PArr& a, long long ip, const int* c0,
                                          const double* __restrict__ sF, double* __restrict__ sR, int* __restrict__ sD,
-                                         int* __restrict__ sM, int* __restrict__ sCnt, int r,
+                                         int* __restrict__ sM, int* __restrict__ sCnt, double* __restrict__ sJ, int r,
                                          unsigned long long* counters) {
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW;
@@ -251,7 +340,31 @@ __device__ __forceinline__ void push_one(const PushP& p, const PArr& a, long lon
   const int lc = (l1[2] * T::TY + l1[1]) * T::TX + l1[0];
   sD[rs] = pack | (lc << 8);
   const int stay = ND == 3 ? 0x15 : 0x5;             // all dcell == 0
-  if (pack != stay) sM[atomicAdd(sCnt, 1)] = r;
+  if (pack != stay) {
+    if (ND == 2) {
+      const int slot = atomicAdd(sCnt, 1);
+      if (slot < MCAP) sM[slot] = r;
+    } else {
+      // one work item per (component A, overflowing axis m); none for m == A with dcell = +1
+      int n = 0;
+#pragma unroll
+      for (int m = 0; m < 3; ++m) { const int dc = ((pack >> (2 * m)) & 3) - 1; n += dc == 0 ? 0 : (dc > 0 ? 2 : 3); }
+      int slot = atomicAdd(sCnt, n);
+#pragma unroll
+      for (int m = 0; m < 3; ++m) {
+        const int dc = ((pack >> (2 * m)) & 3) - 1;
+        if (dc == 0) continue;
+#pragma unroll
+        for (int A = 0; A < 3; ++A) {
+          if (A == m && dc > 0) continue;
+          const int code = r | (A << 16) | (m << 18);
+          if (slot < MCAP) sM[slot] = code;
+          else mover_item3<SHAPE>(p, sR, sD, sJ, code);    // list full: deposit right away
+          ++slot;
+        }
+      }
+    }
+  }
 }
 
 }  // namespace
@@ -350,8 +463,8 @@ __global__ void __launch_bounds__(NT, 2) k_push_tiled(GridP g, FieldP F, PushP p
   double* sJ = sF + 6 * T::FN;             // [3][JN]   J of the tile + deposit halo
   double* sR = sJ + 3 * T::JN;             // [NREC][RPAD] deposit records of the current sub-range
   int* sD = (int*)(sR + NREC * RPAD);      // [RPAD]    cell shift pack | tile-local cell << 8
-  int* sM = sD + RPAD;                     // [RCAP]    records of particles that changed cell
-  uint32_t* sStart = (uint32_t*)(sM + RCAP);   // [G+1] particle offsets of the chunk's cells
+  int* sM = sD + RPAD;                     // [MCAP]    overflow work items of particles that changed cell
+  uint32_t* sStart = (uint32_t*)(sM + MCAP);   // [G+1] particle offsets of the chunk's cells
   int* sCnt = (int*)(sStart + G + 1);
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -380,8 +493,11 @@ __global__ void __launch_bounds__(NT, 2) k_push_tiled(GridP g, FieldP F, PushP p
   }
   for (int i = tid; i < 3 * T::JN; i += NT) sJ[i] = 0.0;
 
-  const int comp = warp >> 1;                 // phase 2 identity: component and cell of the chunk
-  const int ci = ((warp & 1) << 5) + lane;
+  // phase 2 identity: component, cell of the chunk and which half of the cell's particles;
+  // the two lanes of a pair share a cell, the two warps of a component share a chunk
+  const int comp = warp >> 1;
+  const int ci = ((warp & 1) << 4) + (lane >> 1);
+  const int half = lane & 1;
   double acc[T::NACC];
 
   for (int ch = 0; ch < T::CPT / G; ++ch) {
@@ -402,12 +518,12 @@ __global__ void __launch_bounds__(NT, 2) k_push_tiled(GridP g, FieldP F, PushP p
       __syncthreads();
       // ---- phase 1: thread per particle ----
       for (uint32_t q = sb + tid; q < se; q += NT)
-        push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, sR, sD, sM, sCnt, (int)(q - sb), counters);
+        push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, sR, sD, sM, sCnt, sJ, (int)(q - sb), counters);
       __syncthreads();
       if (!p.zero_current) {
         // ---- phase 2: thread per (cell, component) over the cell's records ----
         const uint32_t qb = my_b > sb ? my_b : sb, qe = my_e < se ? my_e : se;
-        for (uint32_t q = qb; q < qe; ++q) {
+        for (uint32_t q = qb + half; q < qe; q += 2) {
           const int rs = swz((int)(q - sb));
           const int pk = sD[rs];
           double gw[ND][NW], hb[ND][NW], hlo[ND], hhi;
@@ -451,30 +567,36 @@ __global__ void __launch_bounds__(NT, 2) k_push_tiled(GridP g, FieldP F, PushP p
           }
         }
         // ---- phase 2b: particles that changed cell, warp per particle ----
-        const int nm = sCnt[0];
-        for (int m = warp; m < nm; m += NT / 32) mover_overflow<ND, SHAPE>(p, sR, sD, sJ, sM[m], lane);
+        const int nm = sCnt[0] < MCAP ? sCnt[0] : MCAP;
+        if (ND == 3) {
+          for (int m = tid; m < nm; m += NT) mover_item3<SHAPE>(p, sR, sD, sJ, sM[m]);
+        } else {
+          for (int m = warp; m < nm; m += NT / 32) mover_overflow<ND, SHAPE>(p, sR, sD, sJ, sM[m], lane);
+        }
       }
       __syncthreads();
     }
     if (!p.zero_current) {
-      // ---- phase 3: register boxes -> shared J tile; the two warps of a component take turns ----
+      // ---- phase 3: fold the odd lane of each pair into the even one, then register boxes ->
+      //      shared J tile, the two warps of a component in step ----
+#pragma unroll
+      for (int i = 0; i < T::NACC; ++i) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 1);
       double* sj = sJ + comp * T::JN;
-      for (int turn = 0; turn < 2; ++turn) {
-        if ((warp & 1) == turn) {   // whole warp (empty cells add zeros): the steps inside are warp-synchronous
-          if (ND == 3) {
-            if (comp == 0) flush3<0, NW, T::JX, T::JY>(sj, acc, l);
-            else if (comp == 1) flush3<1, NW, T::JX, T::JY>(sj, acc, l);
-            else flush3<2, NW, T::JX, T::JY>(sj, acc, l);
-          } else {
-            double* b = sj + (l[1] + 1) * T::JX + l[0] + 1;
+      if (ND == 3) {
+        if (comp == 0) flush3<0, NW, T::JX, T::JY>(sj, acc, l, half == 0, 1 + comp);
+        else if (comp == 1) flush3<1, NW, T::JX, T::JY>(sj, acc, l, half == 0, 1 + comp);
+        else flush3<2, NW, T::JX, T::JY>(sj, acc, l, half == 0, 1 + comp);
+      } else {
+        double* b = sj + (l[1] + 1) * T::JX + l[0] + 1;
 #pragma unroll
-            for (int j = 0; j < NW; ++j)
+        for (int j = 0; j < NW; ++j) {
 #pragma unroll
-              for (int i = 0; i < NW; ++i) { b[j * T::JX + i] += acc[j * NW + i]; __syncwarp(); }
+          for (int i = 0; i < NW; ++i) {
+            if (half == 0) b[j * T::JX + i] += acc[j * NW + i];
+            __syncwarp();
           }
+          asm volatile("bar.sync %0, %1;" ::"r"(1 + comp), "r"(64) : "memory");
         }
-        __syncwarp();
-        if (turn == 0) asm volatile("bar.sync %0, %1;" ::"r"(1 + comp), "r"(64) : "memory");
       }
     }
   }
