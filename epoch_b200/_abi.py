@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_HERE)
-PRODUCT_LIB = os.path.join(_HERE, "csrc", "libepoch_b200.so")
+PRODUCT_LIB = os.environ.get("EB200_LIB", os.path.join(_HERE, "csrc", "libepoch_b200.so"))
 
 c_ctx_p = C.c_void_p
 i32, i64, f64 = C.c_int32, C.c_int64, C.c_double

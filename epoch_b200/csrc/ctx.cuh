@@ -43,8 +43,13 @@ struct GridP {
 };
 constexpr int KM = 3;                    // key-grid margin in cells
 // tile shape of the cell sort / tiled push kernel per dimensionality
+#ifndef EB_T3X
+#define EB_T3X 8
+#define EB_T3Y 8
+#define EB_T3Z 4
+#endif
 __host__ __device__ constexpr int tile_dim(int nd, int d) {
-  return nd == 3 ? (d == 2 ? 4 : 8) : nd == 2 ? (d == 2 ? 1 : 16) : (d == 0 ? 256 : 1);
+  return nd == 3 ? (d == 0 ? EB_T3X : d == 1 ? EB_T3Y : EB_T3Z) : nd == 2 ? (d == 2 ? 1 : 16) : (d == 0 ? 256 : 1);
 }
 constexpr uint32_t KEY_INVALID = 0xFFFFFFFFu;
 

@@ -33,6 +33,9 @@ namespace eb {
 
 namespace {
 
+#ifndef EB_MINB
+#define EB_MINB 2
+#endif
 constexpr int NT = 192;          // threads per CTA = 64 cells x 3 components in phase 2
 constexpr int G = 32;            // cells per chunk: 32 cells x 2 halves x 3 components = NT phase-2 threads
 constexpr int RCAP = 512;        // particles per sub-range (record capacity)
@@ -453,7 +456,7 @@ __device__ __forceinline__ void mover_overflow(const PushP& p, const double* __r
 namespace {
 
 template <int ND, int SHAPE>
-__global__ void __launch_bounds__(NT, 2) k_push_tiled(GridP g, FieldP F, PushP p, PArr a,
+__global__ void __launch_bounds__(NT, EB_MINB) k_push_tiled(GridP g, FieldP F, PushP p, PArr a,
                                                       const uint32_t* __restrict__ cell_start,
                                                       unsigned long long* counters) {
   using T = TL<ND, SHAPE>;
