@@ -1,0 +1,178 @@
+! epoch_b200_hooks.F90 -- drop-in replacements, under the reference's own names,
+! for the four hot entries of PROGRAM pic (epoch3d/src/epoch3d.F90:208,213,235,246)
+! plus the lazy host <-> device synchronisation the rest of EPOCH needs.
+!
+! Usage in the reference tree (see INTEGRATION.md): add this file and
+! epoch_b200_iface.F90 to SRCFILES, link -lepoch_b200, and in epoch3d.F90 replace
+!     USE fields    -> USE epoch_b200_hooks, ONLY: update_eb_fields_half, update_eb_fields_final
+!     USE particles -> USE epoch_b200_hooks, ONLY: push_particles
+!     USE current_smooth -> USE epoch_b200_hooks, ONLY: current_finish
+! and call gpu_attach after mpi_initialise / set_dt, gpu_sync_to_host before anything
+! that reads particles or fields on the host (output_routines when a dump fires,
+! balance_workload, moving_window, restart), gpu_sync_to_device after anything that
+! wrote them.  A step with no dump / balance / window does no transfer at all.
+!
+! This file cannot be compiled in the authoring image (no Fortran compiler); it is
+! written against the reference's module variables by name and is reviewed, not built.
+MODULE epoch_b200_hooks
+
+  USE, INTRINSIC :: ISO_C_BINDING
+  USE epoch_b200_iface
+  USE shared_data          ! ex..bz, jx..jz, species_list, dt, time, step, nx.., x_grid_min_local.., bc_field, ...
+  USE partlist             ! pack_particle, unpack_particle, create_empty_partlist, add_particle_to_partlist
+  USE utilities            ! abort_code
+  IMPLICIT NONE
+
+  TYPE(C_PTR), SAVE :: gpu = C_NULL_PTR
+  LOGICAL, SAVE :: host_stale = .FALSE.      ! device copy is newer than the host copy
+  LOGICAL, SAVE :: device_stale = .TRUE.     ! host copy is newer than the device copy
+#ifdef PARTICLE_SHAPE_TOPHAT
+  INTEGER(C_INT32_T), PARAMETER :: gpu_shape = 0
+#elif defined(PARTICLE_SHAPE_BSPLINE3)
+  INTEGER(C_INT32_T), PARAMETER :: gpu_shape = 2
+#else
+  INTEGER(C_INT32_T), PARAMETER :: gpu_shape = 1
+#endif
+
+CONTAINS
+
+  SUBROUTINE gpu_check(rc)
+    ! reference convention: print and MPI_ABORT (housekeeping/utilities.f90:261-281)
+    INTEGER(C_INT32_T), INTENT(IN) :: rc
+    CHARACTER(KIND=C_CHAR), POINTER :: msg(:)
+    INTEGER :: i
+    IF (rc == 0) RETURN
+    CALL C_F_POINTER(eb200_last_error(gpu), msg, [512])
+    DO i = 1, 512
+      IF (msg(i) == C_NULL_CHAR) EXIT
+      WRITE(*, '(A)', ADVANCE='NO') msg(i)
+    END DO
+    WRITE(*,*)
+    CALL abort_code(c_err_terminate)
+  END SUBROUTINE gpu_check
+
+  SUBROUTINE gpu_attach
+    ! after mpi_initialise (mpi_routines.F90:393-593), setup_boundaries and set_dt
+    CHARACTER(KIND=C_CHAR), TARGET :: id(128)
+    INTEGER(C_INT32_T) :: nprocdir(3), crd(3), ndev, ispecies, bcp(6)
+    INTEGER :: ierr
+    IF (rank == 0) CALL gpu_check(eb200_nccl_unique_id(id))
+    CALL MPI_BCAST(id, 128, MPI_CHARACTER, 0, comm, ierr)
+    nprocdir = [nprocx, nprocy, nprocz]
+    crd = [x_coords, y_coords, z_coords]
+    ndev = 8                                         ! GPUs per node: one rank per GPU
+    CALL gpu_check(eb200_create(gpu, c_ndims, gpu_shape, MOD(rank, ndev), rank, nproc, nprocdir, crd, C_LOC(id)))
+    CALL gpu_set_grid
+    CALL gpu_check(eb200_set_field_bcs(gpu, INT(bc_field, C_INT32_T)))
+    CALL gpu_check(eb200_set_solver(gpu, field_order, maxwell_solver, &
+        [alphax, alphay, alphaz, betaxy, betaxz, betayx, betayz, betazx, betazy, &
+         gammax, gammay, gammaz, deltax, deltay, deltaz]))
+    DO ispecies = 1, n_species
+      bcp = INT(species_list(ispecies)%bc_particle, C_INT32_T)
+      CALL gpu_check(eb200_set_species(gpu, ispecies - 1, species_list(ispecies)%charge, &
+          species_list(ispecies)%mass, species_list(ispecies)%weight, &
+          MERGE(1, 0, species_list(ispecies)%immobile), MERGE(1, 0, species_list(ispecies)%zero_current), &
+          MERGE(1, 0, species_list(ispecies)%species_type == c_species_id_photon), bcp))
+    END DO
+    device_stale = .TRUE.
+  END SUBROUTINE gpu_attach
+
+  SUBROUTINE gpu_set_grid
+    ! call again after balance_workload / moving_window changed the local grid
+    CALL gpu_check(eb200_set_grid(gpu, [nx, ny, nz], [nx_global, ny_global, nz_global], &
+        [nx_global_min, ny_global_min, nz_global_min], [dx, dy, dz], &
+        [x_grid_min_local, y_grid_min_local, z_grid_min_local], &
+        [x_min_local, y_min_local, z_min_local], [x_max_local, y_max_local, z_max_local], &
+        [x_min, y_min, z_min], [x_max, y_max, z_max], cpml_thickness))
+  END SUBROUTINE gpu_set_grid
+
+  SUBROUTINE gpu_sync_to_device
+    ! host lists/arrays -> device (start of run, after restart_data, balance, window, injectors)
+    INTEGER :: ispecies
+    INTEGER(KIND=8) :: n, i
+    REAL(num), ALLOCATABLE, TARGET :: buf(:)
+    TYPE(particle), POINTER :: cur
+    IF (.NOT. device_stale) RETURN
+    CALL gpu_check(eb200_upload_fields(gpu, C_LOC(ex), C_LOC(ey), C_LOC(ez), C_LOC(bx), C_LOC(by), C_LOC(bz), &
+        C_LOC(jx), C_LOC(jy), C_LOC(jz)))
+    DO ispecies = 1, n_species
+      n = species_list(ispecies)%attached_list%count
+      ALLOCATE(buf(MAX(n, 1_8) * nvar))
+      cur => species_list(ispecies)%attached_list%head
+      DO i = 1, n
+        CALL pack_particle(buf((i - 1) * nvar + 1 : i * nvar), cur)      ! partlist.F90:411
+        cur => cur%next
+      END DO
+      CALL gpu_check(eb200_upload_particles(gpu, ispecies - 1, n, buf, nvar))
+      DEALLOCATE(buf)
+    END DO
+    device_stale = .FALSE.
+    host_stale = .FALSE.
+  END SUBROUTINE gpu_sync_to_device
+
+  SUBROUTINE gpu_sync_to_host
+    ! device -> host lists/arrays (before a dump, balance_workload, moving_window, finalise)
+    INTEGER :: ispecies
+    INTEGER(KIND=8) :: n, got, i
+    REAL(num), ALLOCATABLE, TARGET :: buf(:)
+    TYPE(particle), POINTER :: cur
+    IF (.NOT. host_stale) RETURN
+    CALL gpu_check(eb200_download_fields(gpu, C_LOC(ex), C_LOC(ey), C_LOC(ez), C_LOC(bx), C_LOC(by), C_LOC(bz), &
+        C_LOC(jx), C_LOC(jy), C_LOC(jz)))
+    DO ispecies = 1, n_species
+      CALL gpu_check(eb200_particle_count(gpu, ispecies - 1, n))
+      ALLOCATE(buf(MAX(n, 1_8) * nvar))
+      CALL gpu_check(eb200_download_particles(gpu, ispecies - 1, 0_8, n, buf, nvar, got))
+      CALL destroy_partlist(species_list(ispecies)%attached_list)
+      CALL create_empty_partlist(species_list(ispecies)%attached_list)
+      DO i = 1, got
+        CALL create_particle(cur)
+        CALL unpack_particle(buf((i - 1) * nvar + 1 : i * nvar), cur)    ! partlist.F90:477
+        CALL add_particle_to_partlist(species_list(ispecies)%attached_list, cur)
+      END DO
+      DEALLOCATE(buf)
+    END DO
+    host_stale = .FALSE.
+  END SUBROUTINE gpu_sync_to_host
+
+  SUBROUTINE gpu_laser_step
+    ! the host keeps evaluating the deck's time profiles (laser.f90:207-226,334-346)
+    TYPE(laser_block), POINTER :: current
+    INTEGER :: ib
+    CALL update_laser_omegas
+    DO ib = 1, 2 * c_ndims
+      current => laser_boundary_head(ib)       ! laser_x_min, laser_x_max, ... in the reference
+      DO WHILE (ASSOCIATED(current))
+        CALL gpu_check(eb200_set_laser_step(gpu, ib, current%id, laser_time_profile(current), &
+            current%current_integral_phase))
+        current => current%next
+      END DO
+    END DO
+  END SUBROUTINE gpu_laser_step
+
+  ! ---- the four hot entries, reference names and (absent) argument lists --------
+
+  SUBROUTINE update_eb_fields_half          ! fields.f90:819
+    CALL gpu_sync_to_device
+    CALL gpu_check(eb200_set_time(gpu, dt, time, step))
+    CALL gpu_check(eb200_update_eb_fields_half(gpu))
+    host_stale = .TRUE.
+  END SUBROUTINE update_eb_fields_half
+
+  SUBROUTINE push_particles                 ! particles.F90:28
+    CALL gpu_check(eb200_push_particles(gpu))
+    host_stale = .TRUE.
+  END SUBROUTINE push_particles
+
+  SUBROUTINE current_finish                 ! housekeeping/current_smooth.F90:29
+    CALL gpu_check(eb200_current_finish(gpu))
+  END SUBROUTINE current_finish
+
+  SUBROUTINE update_eb_fields_final         ! fields.f90:851
+    CALL gpu_check(eb200_set_time(gpu, dt, time, step))
+    CALL gpu_laser_step
+    CALL gpu_check(eb200_update_eb_fields_final(gpu))
+    host_stale = .TRUE.
+  END SUBROUTINE update_eb_fields_final
+
+END MODULE epoch_b200_hooks

@@ -1,0 +1,190 @@
+! epoch_b200_iface.F90 -- ISO_C_BINDING interfaces of include/epoch_b200.h.
+! One-to-one with the C declarations; the wrappers that carry the reference's
+! subroutine names live in epoch_b200_hooks.F90.  Pattern precedent in the
+! reference: housekeeping/terminal_controls.F90:22-29 (BIND(C, NAME='isatty')).
+! Compiled only where a Fortran compiler exists (none in the authoring image).
+MODULE epoch_b200_iface
+
+  USE, INTRINSIC :: ISO_C_BINDING
+  IMPLICIT NONE
+
+  INTERFACE
+    INTEGER(C_INT32_T) FUNCTION eb200_create(ctx, ndims, shape, device, rank, nproc, &
+        nprocdir, coords, nccl_id) BIND(C, NAME='eb200_create')
+      IMPORT
+      TYPE(C_PTR), INTENT(OUT) :: ctx
+      INTEGER(C_INT32_T), VALUE :: ndims, shape, device, rank, nproc
+      INTEGER(C_INT32_T), INTENT(IN) :: nprocdir(3), coords(3)
+      TYPE(C_PTR), VALUE :: nccl_id
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_nccl_unique_id(out128) BIND(C, NAME='eb200_nccl_unique_id')
+      IMPORT
+      CHARACTER(KIND=C_CHAR), INTENT(OUT) :: out128(128)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_destroy(ctx) BIND(C, NAME='eb200_destroy')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_grid(ctx, n_local, n_global, n_global_min, d, &
+        grid_min_local, min_local, max_local, min_global, max_global, cpml_thickness) &
+        BIND(C, NAME='eb200_set_grid')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), INTENT(IN) :: n_local(3), n_global(3), n_global_min(3)
+      REAL(C_DOUBLE), INTENT(IN) :: d(3), grid_min_local(3), min_local(3), max_local(3)
+      REAL(C_DOUBLE), INTENT(IN) :: min_global(3), max_global(3)
+      INTEGER(C_INT32_T), VALUE :: cpml_thickness
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_time(ctx, dt, time, step) BIND(C, NAME='eb200_set_time')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      REAL(C_DOUBLE), VALUE :: dt, time
+      INTEGER(C_INT32_T), VALUE :: step
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_field_bcs(ctx, bc_field) BIND(C, NAME='eb200_set_field_bcs')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), INTENT(IN) :: bc_field(6)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_solver(ctx, field_order, maxwell_solver, coeffs) &
+        BIND(C, NAME='eb200_set_solver')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: field_order, maxwell_solver
+      REAL(C_DOUBLE), INTENT(IN) :: coeffs(15)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_species(ctx, ispecies, charge, mass, weight, immobile, &
+        zero_current, species_type, bc_particle) BIND(C, NAME='eb200_set_species')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: ispecies, immobile, zero_current, species_type
+      REAL(C_DOUBLE), VALUE :: charge, mass, weight
+      INTEGER(C_INT32_T), INTENT(IN) :: bc_particle(6)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_upload_particles(ctx, ispecies, n, packed, nvar) &
+        BIND(C, NAME='eb200_upload_particles')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: ispecies, nvar
+      INTEGER(C_INT64_T), VALUE :: n
+      REAL(C_DOUBLE), INTENT(IN) :: packed(*)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_append_particles(ctx, ispecies, n, packed, nvar) &
+        BIND(C, NAME='eb200_append_particles')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: ispecies, nvar
+      INTEGER(C_INT64_T), VALUE :: n
+      REAL(C_DOUBLE), INTENT(IN) :: packed(*)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_particle_count(ctx, ispecies, n) BIND(C, NAME='eb200_particle_count')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: ispecies
+      INTEGER(C_INT64_T), INTENT(OUT) :: n
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_download_particles(ctx, ispecies, first, capacity, packed, nvar, n_out) &
+        BIND(C, NAME='eb200_download_particles')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: ispecies, nvar
+      INTEGER(C_INT64_T), VALUE :: first, capacity
+      REAL(C_DOUBLE), INTENT(OUT) :: packed(*)
+      INTEGER(C_INT64_T), INTENT(OUT) :: n_out
+    END FUNCTION
+    ! fields: pass C_LOC(array) or C_NULL_PTR to skip a component
+    INTEGER(C_INT32_T) FUNCTION eb200_upload_fields(ctx, ex, ey, ez, bx, by, bz, jx, jy, jz) &
+        BIND(C, NAME='eb200_upload_fields')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx, ex, ey, ez, bx, by, bz, jx, jy, jz
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_download_fields(ctx, ex, ey, ez, bx, by, bz, jx, jy, jz) &
+        BIND(C, NAME='eb200_download_fields')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx, ex, ey, ez, bx, by, bz, jx, jy, jz
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_laser(ctx, boundary, id, amp, pol_angle, t_start, t_end, &
+        profile, phase) BIND(C, NAME='eb200_set_laser')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx, profile, phase
+      INTEGER(C_INT32_T), VALUE :: boundary, id
+      REAL(C_DOUBLE), VALUE :: amp, pol_angle, t_start, t_end
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_laser_step(ctx, boundary, id, t_env, integral_phase) &
+        BIND(C, NAME='eb200_set_laser_step')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: boundary, id
+      REAL(C_DOUBLE), VALUE :: t_env, integral_phase
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_update_eb_fields_half(ctx) BIND(C, NAME='eb200_update_eb_fields_half')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_push_particles(ctx) BIND(C, NAME='eb200_push_particles')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_current_finish(ctx) BIND(C, NAME='eb200_current_finish')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_update_eb_fields_final(ctx) BIND(C, NAME='eb200_update_eb_fields_final')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_particle_bcs(ctx) BIND(C, NAME='eb200_particle_bcs')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_efield_bcs(ctx) BIND(C, NAME='eb200_efield_bcs')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_bfield_final_bcs(ctx) BIND(C, NAME='eb200_bfield_final_bcs')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_energy(ctx, field_energy, particle_energy) BIND(C, NAME='eb200_energy')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      REAL(C_DOUBLE), INTENT(OUT) :: field_energy, particle_energy(*)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_charge_residual(ctx, max_res, max_rho) BIND(C, NAME='eb200_charge_residual')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      REAL(C_DOUBLE), INTENT(OUT) :: max_res, max_rho
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_option(ctx, key, val) BIND(C, NAME='eb200_set_option')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      CHARACTER(KIND=C_CHAR), INTENT(IN) :: key(*), val(*)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_sync(ctx) BIND(C, NAME='eb200_sync')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_mark(ctx, phase, begin) BIND(C, NAME='eb200_mark')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      CHARACTER(KIND=C_CHAR), INTENT(IN) :: phase(*)
+      INTEGER(C_INT32_T), VALUE :: begin
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_timer(ctx, phase, reset, ms, launches) BIND(C, NAME='eb200_timer')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      CHARACTER(KIND=C_CHAR), INTENT(IN) :: phase(*)
+      INTEGER(C_INT32_T), VALUE :: reset
+      REAL(C_DOUBLE), INTENT(OUT) :: ms
+      INTEGER(C_INT64_T), INTENT(OUT) :: launches
+    END FUNCTION
+    TYPE(C_PTR) FUNCTION eb200_last_error(ctx) BIND(C, NAME='eb200_last_error')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+    END FUNCTION
+    TYPE(C_PTR) FUNCTION eb200_version() BIND(C, NAME='eb200_version')
+      IMPORT
+    END FUNCTION
+  END INTERFACE
+
+END MODULE epoch_b200_iface

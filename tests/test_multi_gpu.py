@@ -1,0 +1,25 @@
+"""-m gpu, needs >= 2 GPUs (skipped otherwise): the domain-decomposed run over NCCL
+(field halos, current ghost sums, particle migration) equals the single-GPU run."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+@pytest.mark.parametrize("axis,shape", [(2, "triangle"), (0, "triangle"), (1, "tophat"), (2, "bspline3")])
+def test_two_ranks_equal_one(axis, shape):
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(29611 + axis), os.path.join(ROOT, "tests", "mgpu_worker.py"), str(axis), "4", shape]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

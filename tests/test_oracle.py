@@ -162,3 +162,53 @@ def test_gather_of_constant_field(oracle_abi, shape, nw, norm):
     Q = sim.ctx.download_particles(0)
     expect = -Q0 * E0 * sim.dt
     assert np.allclose(Q[:, 3], expect, rtol=1e-13, atol=0)
+
+
+def test_factored_esirkepov():
+    """The tiled CUDA kernel uses J = -fj * cumsum(h_A) * (g_P (g_Q + h_Q/2) + h_P (h_Q/3 + g_Q/2))
+    instead of the reference's nested running sums (particles.F90:522-563); both are
+    evaluated here in numpy for random fractions and cell shifts (triangle, 3D)."""
+    def W(f):
+        c = f * f
+        return np.array([0.25 + c + f, 1.5 - 2 * c, 0.25 + c - f])
+    rng = np.random.default_rng(1)
+    third = 1.0 / 3.0
+    for _ in range(20):
+        f1, f3, dc = rng.uniform(-.5, .5, 3), rng.uniform(-.5, .5, 3), rng.integers(-1, 2, 3)
+        g, h = np.zeros((3, 5)), np.zeros((3, 5))        # slots -2..2
+        for d in range(3):
+            g[d, 1:4] = W(f1[d])
+            h[d, 1 + dc[d]:4 + dc[d]] = W(f3[d])
+            h[d] -= g[d]
+        lo = [1 + int((dc[d] - 1) / 2) for d in range(3)]    # truncating division, as Fortran
+        hi = [3 + int((dc[d] + 1) / 2) for d in range(3)]
+        J = np.zeros((3, 5, 5, 5))
+        jzh = np.zeros((5, 5))
+        for iz in range(lo[2], hi[2] + 1):
+            zf1, zf2 = g[2, iz] + .5 * h[2, iz], third * h[2, iz] + .5 * g[2, iz]
+            jyh = np.zeros(5)
+            for iy in range(lo[1], hi[1] + 1):
+                yf1, yf2 = g[1, iy] + .5 * h[1, iy], third * h[1, iy] + .5 * g[1, iy]
+                hygz, hyhz = h[1, iy] * g[2, iz], h[1, iy] * h[2, iz]
+                yzfac = g[1, iy] * zf1 + h[1, iy] * zf2
+                jxh = 0.0
+                for ix in range(lo[0], hi[0] + 1):
+                    xf1, xf2 = g[0, ix] + .5 * h[0, ix], third * h[0, ix] + .5 * g[0, ix]
+                    jxh -= h[0, ix] * yzfac
+                    jyh[ix] -= xf1 * hygz + xf2 * hyhz
+                    jzh[ix, iy] -= g[0, ix] * h[2, iz] * yf1 + h[0, ix] * h[2, iz] * yf2
+                    J[0, ix, iy, iz] += jxh
+                    J[1, ix, iy, iz] += jyh[ix]
+                    J[2, ix, iy, iz] += jzh[ix, iy]
+        C = np.cumsum(h, axis=1)
+        M = np.zeros_like(J)
+        for A in range(3):
+            P, Q = (A + 1) % 3, (A + 2) % 3
+            qf1, qf2 = g[Q] + .5 * h[Q], third * h[Q] + .5 * g[Q]
+            for a in range(5):
+                for u in range(5):
+                    for v in range(5):
+                        idx = [0, 0, 0]
+                        idx[A], idx[P], idx[Q] = a, u, v
+                        M[A][tuple(idx)] = -C[A, a] * (g[P, u] * qf1[v] + h[P, u] * qf2[v])
+        assert np.abs(M - J).max() < 1e-14 * np.abs(J).max() + 1e-15
