@@ -270,7 +270,7 @@ def run_ours(args):
     for _ in range(args.warmup):
         sim.step_once()
     sim.ctx.sync()
-    for ph in ("push", "push_kernel", "sort", "fields", "halo", "bcs", "step"):
+    for ph in ("push", "push_kernel", "push_A", "push_B", "sort", "fields", "halo", "bcs", "step"):
         sim.ctx.timer(ph, reset=True)
     l0 = sim.ctx.timer("launches")[1]
     clocks = ClockSampler(local)
@@ -289,7 +289,7 @@ def run_ours(args):
     dev_ms = sim.ctx.timer("step")[0]
     launches = sim.ctx.timer("launches")[1] - l0
     ms = max_over_ranks(dev_ms)
-    phases = {ph: sim.ctx.timer(ph) for ph in ("push", "push_kernel", "sort", "fields", "halo", "bcs")}
+    phases = {ph: sim.ctx.timer(ph) for ph in ("push", "push_kernel", "push_A", "push_B", "sort", "fields", "halo", "bcs")}
     n_live = sim.ctx.particle_count(0)
     value = n_part * world * args.steps / (ms * 1e-3)
 

@@ -35,6 +35,9 @@ static void free_species(SpeciesD& sp) {
   for (int k = 0; k < 7; ++k) if (sp.a[k]) { cudaFree(sp.a[k]); sp.a[k] = nullptr; }
   if (sp.key) cudaFree(sp.key);
   if (sp.dest) cudaFree(sp.dest);
+  if (sp.d_tile_start) cudaFree(sp.d_tile_start);
+  if (sp.h_tile_start) cudaFreeHost(sp.h_tile_start);
+  sp.d_tile_start = sp.h_tile_start = nullptr; sp.tile_cap = 0;
   if (sp.cell_start) cudaFree(sp.cell_start);
   sp.cell_start = nullptr; sp.cell_cap = 0;
   sp.key = sp.dest = nullptr; sp.n = sp.cap = 0;
@@ -118,7 +121,7 @@ int32_t eb200_destroy(eb200_ctx* c) {
   comm_destroy(c);
   for (SpeciesD& sp : c->species) free_species(sp);
   for (int b = 0; b < 6; ++b) for (Laser& L : c->lasers[b]) { if (L.profile) cudaFree(L.profile); if (L.phase) cudaFree(L.phase); }
-  void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->cub_tmp, c->halo_send, c->halo_recv,
+  void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->rec_scratch, c->cub_tmp, c->halo_send, c->halo_recv,
                   c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (c->h_counters) cudaFreeHost(c->h_counters);
@@ -368,7 +371,8 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
   if (k == "capture_charge_reference") { NEED_GRID(c); NEED_DT(c); double a, b; return charge_residual(c, &a, &b, true); }
   if (k == "push_kernel") {
     if (v == "auto") c->push_kernel = 0; else if (v == "baseline") c->push_kernel = 1; else if (v == "tiled") c->push_kernel = 2;
-    else return fail(c, EB200_E_ARG, "push_kernel: auto|baseline|tiled");
+    else if (v == "split") c->push_kernel = 3;
+    else return fail(c, EB200_E_ARG, "push_kernel: auto|baseline|tiled|split");
     return 0;
   }
   if (k == "deterministic_deposit") { c->deterministic = atoi(value) != 0; return 0; }
@@ -382,6 +386,7 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
     if (isp < 0 || (size_t)isp >= c->species.size() || !c->species[isp].defined || n < 0) return fail(c, EB200_E_ARG, "reserve: bad species or count");
     return species_reserve(c, c->species[isp], n, true);
   }
+  if (k == "deposit_scratch") { c->rec_scratch_max = atoll(value) < 1024 ? 1024 : atoll(value); return 0; }
   if (k == "mig_capacity") { c->mig_min_particles = atoll(value); return 0; }
   return fail(c, EB200_E_ARG, "unknown option " + k);
 }

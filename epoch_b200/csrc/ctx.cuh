@@ -68,6 +68,9 @@ struct SpeciesD {
   uint32_t* dest = nullptr; // destination index per slot
   uint32_t* cell_start = nullptr;   // per species: first particle of every key bucket (ncell_ext + 2)
   long long cell_cap = 0;
+  uint32_t* d_tile_start = nullptr; // first particle of every tile (+1 entry), device and pinned host copy
+  uint32_t* h_tile_start = nullptr;
+  long long tile_cap = 0;
   bool sorted = false;      // keys/cell_start valid for the current positions
 };
 
@@ -125,8 +128,11 @@ struct eb200_ctx {
   double* h_red = nullptr;
   double* res_ref = nullptr;                  // captured charge residual
   double* rho = nullptr;
+  double* rec_scratch = nullptr;              // deposit records of the split push/deposit kernels
+  long long rec_scratch_cap = 0;              // ... capacity in particles
+  long long rec_scratch_max = 1LL << 27;      // option deposit_scratch (particles per slab, 64 B each)
   // options
-  int push_kernel = 0;          // 0 auto, 1 baseline, 2 tiled
+  int push_kernel = 0;          // 0 auto, 1 baseline, 2 tiled (fused), 3 split (push + deposit kernels)
   int deterministic = 0;
   int sort_every = 1;
   bool timers_on = false;

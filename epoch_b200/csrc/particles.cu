@@ -11,6 +11,7 @@ namespace eb {
 
 int32_t launch_push_baseline(eb200_ctx* c, const SpeciesD& sp, const PushP& p);   // push_baseline.cu
 int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled);  // push_tiled.cu
+int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled);  // push_tiled.cu
 
 // ---------------------------------------------------------------------------------
 // storage
@@ -184,6 +185,10 @@ __global__ void k_permute(const double* __restrict__ src, double* __restrict__ d
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dst[dest[i]] = src[i];
 }
+__global__ void k_tile_start(const uint32_t* __restrict__ cell_start, uint32_t* ts, long long ntile1, int cpt) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < ntile1) ts[t] = cell_start[t * cpt];
+}
 __global__ void k_fill_u32(uint32_t* a, long long n, uint32_t v) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) a[i] = v;
@@ -278,6 +283,21 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
     k_permute<<<gp, B, 0, c->stream>>>(sp.a[k], c->attr_scratch, sp.dest, n_slots);
     std::swap(sp.a[k], c->attr_scratch);
     c->launches++;
+  }
+  // first particle of every tile, for the host's slab partition of the split push/deposit kernels
+  {
+    const long long nt1 = c->g.ncell_ext / c->g.cpt + 1;
+    if (sp.tile_cap < nt1) {
+      if (sp.d_tile_start) cudaFree(sp.d_tile_start);
+      if (sp.h_tile_start) cudaFreeHost(sp.h_tile_start);
+      sp.d_tile_start = sp.h_tile_start = nullptr; sp.tile_cap = 0;
+      EB_CUDA(c, cudaMalloc(&sp.d_tile_start, (size_t)nt1 * sizeof(uint32_t)));
+      EB_CUDA(c, cudaMallocHost(&sp.h_tile_start, (size_t)nt1 * sizeof(uint32_t)));
+      sp.tile_cap = nt1;
+    }
+    k_tile_start<<<(unsigned)((nt1 + 255) / 256), 256, 0, c->stream>>>(sp.cell_start, sp.d_tile_start, nt1, c->g.cpt);
+    c->launches++;
+    EB_CUDA(c, cudaMemcpyAsync(sp.h_tile_start, sp.d_tile_start, (size_t)nt1 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
   }
   // live count = start of the invalid bucket
   EB_CUDA(c, cudaMemcpyAsync(c->h_counters, sp.cell_start + (nbucket - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
@@ -465,7 +485,8 @@ int32_t push_particles(eb200_ctx* c) {
     PushP p = make_push_params(c, sp, sp.n);
     bool handled = false;
     ScopedPhase pk(c, "push_kernel");     // the kernel alone (roofline figure of bench.py)
-    if (c->push_kernel != 1) EB_TRY(launch_push_tiled(c, sp, p, &handled));
+    if (c->push_kernel == 0 || c->push_kernel == 3) EB_TRY(launch_push_split(c, sp, p, &handled));
+    if (!handled && c->push_kernel != 1) EB_TRY(launch_push_tiled(c, sp, p, &handled));
     if (!handled) EB_TRY(launch_push_baseline(c, sp, p));
   }
   // current_bcs(species) is a no-op without mixed per-species BCs (boundary.F90:1130-1136)

@@ -36,6 +36,9 @@ namespace {
 #ifndef EB_MINB
 #define EB_MINB 2
 #endif
+#ifndef EB_MINB_A
+#define EB_MINB_A 2
+#endif
 constexpr int NT = 192;          // threads per CTA = 64 cells x 3 components in phase 2
 constexpr int G = 32;            // cells per chunk: 32 cells x 2 halves x 3 components = NT phase-2 threads
 constexpr int RCAP = 512;        // particles per sub-range (record capacity)
@@ -54,11 +57,27 @@ struct TL {
   // deposit region: cells c0+SFM-1 .. c0+T-1+SFM+NW  (T + NW + 1 wide)
   static constexpr int JX = TX + NW + 1, JY = ND >= 2 ? TY + NW + 1 : 1, JZ = ND >= 3 ? TZ + NW + 1 : 1;
   static constexpr int JN = JX * JY * JZ;
-  static constexpr int NACC = ND == 3 ? NW * NW * NW : NW * NW;
+  // register accumulators per component.  3D: the last box slot along the running-sum axis is
+  // left out -- the sum has returned to zero there (rounding residue) unless the particle moved
+  // up a cell, and then the slot is deposited by a work item (mover_item3, m == A, dcell = +1)
+  static constexpr int NACC = ND == 3 ? (NW - 1) * NW * NW : NW * NW;
   static constexpr size_t SMEM = sizeof(double) * (6 * FN + 3 * JN + NREC * RPAD) + sizeof(int) * (RPAD + MCAP + G + 1 + 3);
 };
 
 __device__ __forceinline__ int swz(int r) { return r + (r >> 4); }
+
+// deposit record: doubles f1[ND], f3[ND], weight[, v_z] and an int = packed cell shift
+// (2 bits per axis, value dcell + 1) | tile-local cell << 8.  Two storages:
+struct RecS {            // shared memory, structure of arrays (fused kernel)
+  const double* sR; const int* sD; int rs;
+  __device__ __forceinline__ double get(int k) const { return sR[k * RPAD + rs]; }
+  __device__ __forceinline__ int pack() const { return sD[rs]; }
+};
+struct RecG {            // global scratch, 8 doubles per particle (split kernels)
+  const double* r;
+  __device__ __forceinline__ double get(int k) const { return __ldg(r + k); }
+  __device__ __forceinline__ int pack() const { return (int)__double_as_longlong(__ldg(r + 7)); }
+};
 
 // weights at t+3dt/2 expressed on the t+dt/2 stencil: box part hb[i] (slot SFM+i),
 // and the single slots one beyond the box on either side
@@ -119,10 +138,10 @@ __device__ __forceinline__ void box3(double* acc, const double (*g)[NW], const d
                                      double fj) {
   constexpr int P = (A + 1) % 3, Q = (A + 2) % 3;
   const double third = 1.0 / 3.0;
-  double ca[NW], qf1[NW], qf2[NW];
+  double ca[NW - 1], qf1[NW], qf2[NW];
   double c = hlo[A];
 #pragma unroll
-  for (int i = 0; i < NW; ++i) { c += hb[A][i]; ca[i] = fj * c; }
+  for (int i = 0; i < NW - 1; ++i) { c += hb[A][i]; ca[i] = fj * c; }
 #pragma unroll
   for (int v = 0; v < NW; ++v) {
     qf1[v] = g[Q][v] + 0.5 * hb[Q][v];
@@ -134,7 +153,7 @@ __device__ __forceinline__ void box3(double* acc, const double (*g)[NW], const d
     for (int u = 0; u < NW; ++u) {
       const double w = g[P][u] * qf1[v] + hb[P][u] * qf2[v];
 #pragma unroll
-      for (int i = 0; i < NW; ++i) acc[(v * NW + u) * NW + i] += ca[i] * w;
+      for (int i = 0; i < NW - 1; ++i) acc[(v * NW + u) * (NW - 1) + i] += ca[i] * w;
     }
 }
 
@@ -157,7 +176,7 @@ __device__ __forceinline__ void flush3(double* sj, const double* acc, const int*
 #pragma unroll
         for (int dz = 0; dz < NW; ++dz) {
           const int o[3] = {dx, dy, dz};
-          b[dx + dy * JX + dz * JX * JY] += acc[(o[Q] * NW + o[P]) * NW + o[A]];
+          if (o[A] < NW - 1) b[dx + dy * JX + dz * JX * JY] += acc[(o[Q] * NW + o[P]) * (NW - 1) + o[A]];
         }
       }
       __syncwarp();
@@ -180,31 +199,29 @@ __device__ __forceinline__ double pick(const double* a, int t) {
 
 namespace {
 
-// One overflow work item of a 3D particle that changed cell: current component A,
-// overflowing axis m.  The window cells outside the home box are split, per
-// component, by the first overflowing axis in the order (A, P, Q):
-//   m == A: cells one below the box along A (dcell = -1; above the box the running
-//           sum has returned to zero), any (u, v) of the P x Q window;
+// One work item of a 3D particle that changed cell: current component A, moving
+// axis m.  The window cells not covered by the register boxes are split, per
+// component, by the first such axis in the order (A, P, Q):
+//   m == A: dcell = -1: cells one below the box along A, any (u, v) of the P x Q window;
+//           dcell = +1: the last box slot along A (left out of the register boxes), (u, v)
+//           inside the box; one above the box the running sum has returned to zero;
 //   m == P: u beyond the box, a inside it, any v of the Q window;
 //   m == Q: v beyond the box, a and u inside it.
 // Thread per item; the values go to the shared J tile with atomics.
-template <int SHAPE>
-__device__ __forceinline__ void mover_item3(const PushP& p, const double* __restrict__ sR, const int* __restrict__ sD,
-                                            double* __restrict__ sJ, int code) {
+template <int SHAPE, class R>
+__device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double* __restrict__ sJ, int A, int m) {
   using T = TL<3, SHAPE>;
   constexpr int NW = T::NW, NS = NW + 2;
-  const int r = code & 0xffff, A = (code >> 16) & 3, m = (code >> 18) & 3;
   const int P = A == 2 ? 0 : A + 1, Q = P == 2 ? 0 : P + 1;
-  const int rs = swz(r);
-  const int pk = sD[rs];
+  const int pk = rec.pack();
   const int lc = pk >> 8;
   const int l0 = lc % T::TX, l1 = (lc / T::TX) % T::TY, l2 = lc / (T::TX * T::TY);
   const int dcA = ((pk >> (2 * A)) & 3) - 1, dcP = ((pk >> (2 * P)) & 3) - 1, dcQ = ((pk >> (2 * Q)) & 3) - 1;
   double gA[NW], hA[NW], gP[NW], hP[NW], gQ[NW], hQ[NW], loA, hiA, loP, hiP, loQ, hiQ;
-  axis_weights<SHAPE>(sR[A * RPAD + rs], sR[(3 + A) * RPAD + rs], dcA, gA, hA, loA, hiA);
-  axis_weights<SHAPE>(sR[P * RPAD + rs], sR[(3 + P) * RPAD + rs], dcP, gP, hP, loP, hiP);
-  axis_weights<SHAPE>(sR[Q * RPAD + rs], sR[(3 + Q) * RPAD + rs], dcQ, gQ, hQ, loQ, hiQ);
-  const double fj = -(p.fc[A] * sR[6 * RPAD + rs] * p.q);
+  axis_weights<SHAPE>(rec.get(A), rec.get(3 + A), dcA, gA, hA, loA, hiA);
+  axis_weights<SHAPE>(rec.get(P), rec.get(3 + P), dcP, gP, hP, loP, hiP);
+  axis_weights<SHAPE>(rec.get(Q), rec.get(3 + Q), dcQ, gQ, hQ, loQ, hiQ);
+  const double fj = -(p.fc[A] * rec.get(6) * p.q);
   const double third = 1.0 / 3.0;
   const int stA = A == 0 ? 1 : (A == 1 ? T::JX : T::JX * T::JY);
   const int stP = P == 0 ? 1 : (P == 1 ? T::JX : T::JX * T::JY);
@@ -216,7 +233,12 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const double* __rest
 #pragma unroll
   for (int v = 0; v < NW; ++v) { q1[v + 1] = gQ[v] + 0.5 * hQ[v]; q2[v + 1] = third * hQ[v] + 0.5 * gQ[v]; }
   if (m == A) {
-    const double cov = fj * loA;
+    // dcell = -1: the slot below the box (t_A = 0), running sum = h_lo, any (u, v) of the window;
+    // dcell = +1: the last box slot (t_A = NW), which the register boxes leave out, running sum
+    //             = -h_hi, (u, v) inside the box (u or v beyond it belongs to the m == P / Q items)
+    const double cov = dcA < 0 ? fj * loA : -(fj * hiA);
+    const int ta = dcA < 0 ? 0 : NW;
+    const int lo = dcA < 0 ? 0 : 1, hi = dcA < 0 ? NS : NS - 1;
     double g5[NS], h5[NS];
     g5[0] = 0.0; g5[NS - 1] = 0.0; h5[0] = loP; h5[NS - 1] = hiP;
 #pragma unroll
@@ -226,7 +248,7 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const double* __rest
 #pragma unroll
       for (int u = 0; u < NS; ++u) {
         const double val = cov * (g5[u] * q1[v] + h5[u] * q2[v]);
-        if (val != 0.0) atomicAdd(base + u * stP + v * stQ, val);
+        if (val != 0.0 && u >= lo && u < hi && v >= lo && v < hi) atomicAdd(base + ta * stA + u * stP + v * stQ, val);
       }
   } else {
     double ca[NW];
@@ -266,10 +288,9 @@ struct PArr { double* x[3]; double* m[3]; const double* w; };
 // phase 1 for one particle: particles.F90:219-452 (gather stage, Boris, drift, store,
 // extra half drift); leaves the deposit inputs in the record arrays
 template <int ND, int SHAPE>
-__device__ __forceinline__ void push_one(const PushP& p, const PArr& a, long long ip, const int* c0,
-                                         const double* __restrict__ sF, double* __restrict__ sR, int* __restrict__ sD,
-                                         int* __restrict__ sM, int* __restrict__ sCnt, double* __restrict__ sJ, int r,
-                                         unsigned long long* counters) {
+__device__ __forceinline__ bool push_one(const PushP& p, const PArr& a, long long ip, const int* c0,
+                                         const double* __restrict__ sF, unsigned long long* counters,
+                                         double* rec /* NREC doubles */, int& rec_pack) {
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW;
   double pos[3] = {0, 0, 0}, px[3] = {0, 0, 0}, ux, uy, uz;
@@ -323,10 +344,9 @@ __device__ __forceinline__ void push_one(const PushP& p, const PArr& a, long lon
     a.x[d][ip] = px[d] + p.gml[d];
   }
   a.m[0][ip] = p.part_mc * ux; a.m[1][ip] = p.part_mc * uy; a.m[2][ip] = p.part_mc * uz;
-  if (p.zero_current) return;
+  if (p.zero_current) return false;
 
   int pack = 0;
-  const int rs = swz(r);
 #pragma unroll
   for (int d = 0; d < ND; ++d) {
     px[d] = px[d] + delta[d];
@@ -335,39 +355,14 @@ __device__ __forceinline__ void push_one(const PushP& p, const PArr& a, long lon
     int dc = cell3 - cell1[d];
     dc = dc < -1 ? -1 : (dc > 1 ? 1 : dc);          // |dcell| <= 1 by the CFL condition (particles.F90:506-507)
     pack |= (dc + 1) << (2 * d);
-    sR[d * RPAD + rs] = f1[d];
-    sR[(ND + d) * RPAD + rs] = f3;
+    rec[d] = f1[d];
+    rec[ND + d] = f3;
   }
-  sR[2 * ND * RPAD + rs] = part_weight;
-  if (ND == 2) sR[(2 * ND + 1) * RPAD + rs] = part_vz;
+  rec[2 * ND] = part_weight;
+  if (ND == 2) rec[2 * ND + 1] = part_vz;
   const int lc = (l1[2] * T::TY + l1[1]) * T::TX + l1[0];
-  sD[rs] = pack | (lc << 8);
-  const int stay = ND == 3 ? 0x15 : 0x5;             // all dcell == 0
-  if (pack != stay) {
-    if (ND == 2) {
-      const int slot = atomicAdd(sCnt, 1);
-      if (slot < MCAP) sM[slot] = r;
-    } else {
-      // one work item per (component A, overflowing axis m); none for m == A with dcell = +1
-      int n = 0;
-#pragma unroll
-      for (int m = 0; m < 3; ++m) { const int dc = ((pack >> (2 * m)) & 3) - 1; n += dc == 0 ? 0 : (dc > 0 ? 2 : 3); }
-      int slot = atomicAdd(sCnt, n);
-#pragma unroll
-      for (int m = 0; m < 3; ++m) {
-        const int dc = ((pack >> (2 * m)) & 3) - 1;
-        if (dc == 0) continue;
-#pragma unroll
-        for (int A = 0; A < 3; ++A) {
-          if (A == m && dc > 0) continue;
-          const int code = r | (A << 16) | (m << 18);
-          if (slot < MCAP) sM[slot] = code;
-          else mover_item3<SHAPE>(p, sR, sD, sJ, code);    // list full: deposit right away
-          ++slot;
-        }
-      }
-    }
-  }
+  rec_pack = pack | (lc << 8);
+  return true;
 }
 
 }  // namespace
@@ -376,16 +371,14 @@ namespace {
 
 // phase 2b: the warp adds the contributions of one cell-changing particle that fall
 // outside its home box (at most one layer per axis), lane per (component, cell)
-template <int ND, int SHAPE>
-__device__ __forceinline__ void mover_overflow(const PushP& p, const double* __restrict__ sR, const int* __restrict__ sD,
-                                               double* __restrict__ sJ, int r, int lane) {
+template <int ND, int SHAPE, class R>
+__device__ __forceinline__ void mover_overflow(const PushP& p, const R& rec, double* __restrict__ sJ, int lane) {
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW, NS = NW + 2;
-  const int rs = swz(r);
-  const int pk = sD[rs];
+  const int pk = rec.pack();
   const int lc = pk >> 8;
   const int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
-  const double w = sR[2 * ND * RPAD + rs];
+  const double w = rec.get(2 * ND);
   // full-window arrays per axis: index t = 0 (slot below the box), 1..NW (box), NW+1 (slot above)
   double g5[ND][NS], h5[ND][NS], c5[ND][NS];
   int dc[ND], wd[ND], tlo[ND], tov[ND], ov[ND];
@@ -393,7 +386,7 @@ __device__ __forceinline__ void mover_overflow(const PushP& p, const double* __r
   for (int d = 0; d < ND; ++d) {
     dc[d] = ((pk >> (2 * d)) & 3) - 1;
     double g[NW], hb[NW], hlo, hhi;
-    axis_weights<SHAPE>(sR[d * RPAD + rs], sR[(ND + d) * RPAD + rs], dc[d], g, hb, hlo, hhi);
+    axis_weights<SHAPE>(rec.get(d), rec.get(ND + d), dc[d], g, hb, hlo, hhi);
     g5[d][0] = 0.0; g5[d][NS - 1] = 0.0; h5[d][0] = hlo; h5[d][NS - 1] = hhi;
 #pragma unroll
     for (int i = 0; i < NW; ++i) { g5[d][i + 1] = g[i]; h5[d][i + 1] = hb[i]; }
@@ -444,11 +437,77 @@ __device__ __forceinline__ void mover_overflow(const PushP& p, const double* __r
       const double yf1 = gv[1] + 0.5 * hv[1], yf2 = third * hv[1] + 0.5 * gv[1];
       if (comp == 0) val = -(p.fc[0] * w * p.q) * cv[0] * yf1;
       else if (comp == 1) val = -(p.fc[1] * w * p.q) * cv[1] * xf1;
-      else val = (p.fc[2] * w * p.q * sR[(2 * ND + 1) * RPAD + rs]) * (gv[0] * yf1 + hv[0] * yf2);
+      else val = (p.fc[2] * w * p.q * rec.get(2 * ND + 1)) * (gv[0] * yf1 + hv[0] * yf2);
     }
     const int idx = ((ND >= 3 ? (l[2] + t[2]) : 0) * T::JY + (ND >= 2 ? (l[1] + t[1]) : 0)) * T::JX + l[0] + t[0];
     atomicAdd(sJ + comp * T::JN + idx, val);
   }
+}
+
+}  // namespace
+
+namespace {
+
+// Box contributions of one particle.  ALL = false: component `comp` into acc[NACC]
+// (fused kernel, thread per (cell, component)); ALL = true: the three components into
+// acc[3 * NACC] (split deposit kernel, thread per cell; the weights are computed once).
+template <int ND, int SHAPE, bool ALL, class R>
+__device__ __forceinline__ void deposit_box(const PushP& p, const R& rec, int comp, double* acc) {
+  using T = TL<ND, SHAPE>;
+  constexpr int NW = T::NW, NA = T::NACC;
+  const int pk = rec.pack();
+  double gw[ND][NW], hb[ND][NW], hlo[ND], hhi;
+#pragma unroll
+  for (int d = 0; d < ND; ++d)
+    axis_weights<SHAPE>(rec.get(d), rec.get(ND + d), ((pk >> (2 * d)) & 3) - 1, gw[d], hb[d], hlo[d], hhi);
+  const double wq = rec.get(2 * ND) * p.q;
+  if (ND == 3) {
+    if (ALL || comp == 0) box3<0, NW>(acc, gw, hb, hlo, -(p.fc[0] * wq));
+    if (ALL || comp == 1) box3<1, NW>(acc + (ALL ? NA : 0), gw, hb, hlo, -(p.fc[1] * wq));
+    if (ALL || comp == 2) box3<2, NW>(acc + (ALL ? 2 * NA : 0), gw, hb, hlo, -(p.fc[2] * wq));
+  } else {
+    const double third = 1.0 / 3.0;
+    if (ALL || comp == 0) {          // Jx = -fjx * cumsum_x(hx) * (gy + hy/2)
+      double c = hlo[0];
+#pragma unroll
+      for (int i = 0; i < NW; ++i) {
+        c += hb[0][i];
+        const double ca = -(p.fc[0] * wq) * c;
+#pragma unroll
+        for (int j = 0; j < NW; ++j) acc[j * NW + i] += ca * (gw[1][j] + 0.5 * hb[1][j]);
+      }
+    }
+    if (ALL || comp == 1) {          // Jy = -fjy * cumsum_y(hy) * (gx + hx/2)
+      double* ay = acc + (ALL ? NA : 0);
+      double c = hlo[1];
+#pragma unroll
+      for (int j = 0; j < NW; ++j) {
+        c += hb[1][j];
+        const double ca = -(p.fc[1] * wq) * c;
+#pragma unroll
+        for (int i = 0; i < NW; ++i) ay[j * NW + i] += ca * (gw[0][i] + 0.5 * hb[0][i]);
+      }
+    }
+    if (ALL || comp == 2) {          // Jz = fjz * (gx*(gy + hy/2) + hx*(hy/3 + gy/2))
+      double* az = acc + (ALL ? 2 * NA : 0);
+      const double fjz = p.fc[2] * wq * rec.get(2 * ND + 1);
+#pragma unroll
+      for (int j = 0; j < NW; ++j) {
+        const double yf1 = gw[1][j] + 0.5 * hb[1][j], yf2 = third * hb[1][j] + 0.5 * gw[1][j];
+#pragma unroll
+        for (int i = 0; i < NW; ++i) az[j * NW + i] += fjz * (gw[0][i] * yf1 + hb[0][i] * yf2);
+      }
+    }
+  }
+}
+
+// work items of a 3D particle that changed cell: one per (component A, moving axis m);
+// code = record | A << 16 | m << 18
+__device__ __forceinline__ int mover_item_count(int pack) {
+  int n = 0;
+#pragma unroll
+  for (int m = 0; m < 3; ++m) n += ((pack >> (2 * m)) & 3) != 1 ? 3 : 0;
+  return n;
 }
 
 }  // namespace
@@ -520,61 +579,49 @@ __global__ void __launch_bounds__(NT, EB_MINB) k_push_tiled(GridP g, FieldP F, P
       if (tid == 0) sCnt[0] = 0;
       __syncthreads();
       // ---- phase 1: thread per particle ----
-      for (uint32_t q = sb + tid; q < se; q += NT)
-        push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, sR, sD, sM, sCnt, sJ, (int)(q - sb), counters);
+      for (uint32_t q = sb + tid; q < se; q += NT) {
+        double rec[NREC];
+        int pack;
+        if (!push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, counters, rec, pack)) continue;
+        const int r = (int)(q - sb), rs = swz(r);
+#pragma unroll
+        for (int k = 0; k < 2 * ND + (ND == 2 ? 2 : 1); ++k) sR[k * RPAD + rs] = rec[k];
+        sD[rs] = pack;
+        if ((pack & 0xff) == (ND == 3 ? 0x15 : 0x5)) continue;     // all dcell == 0
+        if (ND == 2) {
+          const int slot = atomicAdd(sCnt, 1);
+          if (slot < MCAP) sM[slot] = r;
+        } else {
+          int slot = atomicAdd(sCnt, mover_item_count(pack));
+#pragma unroll
+          for (int m = 0; m < 3; ++m) {
+            const int dc = ((pack >> (2 * m)) & 3) - 1;
+            if (dc == 0) continue;
+#pragma unroll
+            for (int A = 0; A < 3; ++A) {
+              if (slot < MCAP) sM[slot] = r | (A << 16) | (m << 18);
+              else mover_item3<SHAPE>(p, RecS{sR, sD, rs}, sJ, A, m);    // list full: deposit right away
+              ++slot;
+            }
+          }
+        }
+      }
       __syncthreads();
       if (!p.zero_current) {
         // ---- phase 2: thread per (cell, component) over the cell's records ----
         const uint32_t qb = my_b > sb ? my_b : sb, qe = my_e < se ? my_e : se;
         for (uint32_t q = qb + half; q < qe; q += 2) {
-          const int rs = swz((int)(q - sb));
-          const int pk = sD[rs];
-          double gw[ND][NW], hb[ND][NW], hlo[ND], hhi;
-#pragma unroll
-          for (int d = 0; d < ND; ++d)
-            axis_weights<SHAPE>(sR[d * RPAD + rs], sR[(ND + d) * RPAD + rs], ((pk >> (2 * d)) & 3) - 1, gw[d], hb[d], hlo[d], hhi);
-          const double wq = sR[2 * ND * RPAD + rs] * p.q;
-          if (ND == 3) {
-            if (comp == 0) box3<0, NW>(acc, gw, hb, hlo, -(p.fc[0] * wq));
-            else if (comp == 1) box3<1, NW>(acc, gw, hb, hlo, -(p.fc[1] * wq));
-            else box3<2, NW>(acc, gw, hb, hlo, -(p.fc[2] * wq));
-          } else {
-            const double third = 1.0 / 3.0;
-            if (comp == 0) {          // Jx = -fjx * cumsum_x(hx) * (gy + hy/2)
-              double c = hlo[0];
-#pragma unroll
-              for (int i = 0; i < NW; ++i) {
-                c += hb[0][i];
-                const double ca = -(p.fc[0] * wq) * c;
-#pragma unroll
-                for (int j = 0; j < NW; ++j) acc[j * NW + i] += ca * (gw[1][j] + 0.5 * hb[1][j]);
-              }
-            } else if (comp == 1) {   // Jy = -fjy * cumsum_y(hy) * (gx + hx/2)
-              double c = hlo[1];
-#pragma unroll
-              for (int j = 0; j < NW; ++j) {
-                c += hb[1][j];
-                const double ca = -(p.fc[1] * wq) * c;
-#pragma unroll
-                for (int i = 0; i < NW; ++i) acc[j * NW + i] += ca * (gw[0][i] + 0.5 * hb[0][i]);
-              }
-            } else {                  // Jz = fjz * (gx*(gy + hy/2) + hx*(hy/3 + gy/2))
-              const double fjz = p.fc[2] * wq * sR[(2 * ND + 1) * RPAD + rs];
-#pragma unroll
-              for (int j = 0; j < NW; ++j) {
-                const double yf1 = gw[1][j] + 0.5 * hb[1][j], yf2 = third * hb[1][j] + 0.5 * gw[1][j];
-#pragma unroll
-                for (int i = 0; i < NW; ++i) acc[j * NW + i] += fjz * (gw[0][i] * yf1 + hb[0][i] * yf2);
-              }
-            }
-          }
+          deposit_box<ND, SHAPE, false>(p, RecS{sR, sD, swz((int)(q - sb))}, comp, acc);
         }
         // ---- phase 2b: particles that changed cell, warp per particle ----
         const int nm = sCnt[0] < MCAP ? sCnt[0] : MCAP;
         if (ND == 3) {
-          for (int m = tid; m < nm; m += NT) mover_item3<SHAPE>(p, sR, sD, sJ, sM[m]);
+          for (int m = tid; m < nm; m += NT) {
+            const int code = sM[m];
+            mover_item3<SHAPE>(p, RecS{sR, sD, swz(code & 0xffff)}, sJ, (code >> 16) & 3, (code >> 18) & 3);
+          }
         } else {
-          for (int m = warp; m < nm; m += NT / 32) mover_overflow<ND, SHAPE>(p, sR, sD, sJ, sM[m], lane);
+          for (int m = warp; m < nm; m += NT / 32) mover_overflow<ND, SHAPE>(p, RecS{sR, sD, swz(sM[m])}, sJ, lane);
         }
       }
       __syncthreads();
@@ -621,6 +668,176 @@ __global__ void __launch_bounds__(NT, EB_MINB) k_push_tiled(GridP g, FieldP F, P
 
 }  // namespace
 
+
+// =====================================================================================
+// Split variant: push and deposit as two kernels over the same tiles, the deposit
+// records passing through a global scratch (64 B per particle, L2/HBM).  The push
+// kernel then carries no accumulators (more resident warps to hide the gather and
+// Boris latencies) and the deposit kernel can give one thread ALL THREE components of a
+// cell (81 register accumulators in 3D), so the shape weights of a particle are
+// evaluated once instead of once per component.  Tiles are processed in slabs whose
+// particles fit the scratch.
+// =====================================================================================
+namespace {
+
+constexpr int NTA = 256;         // push kernel threads
+constexpr int MCAPB = 4096;      // overflow work items per tile in the deposit kernel
+
+template <int ND, int SHAPE>
+__global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F, PushP p, PArr a,
+                                                              const uint32_t* __restrict__ cell_start, long long tile0,
+                                                              double* __restrict__ scratch, unsigned long long* counters) {
+  using T = TL<ND, SHAPE>;
+  constexpr int SFM = T::SFM;
+  extern __shared__ double smem[];
+  double* sF = smem;
+  const int tid = threadIdx.x;
+  const long long tile = tile0 + blockIdx.x;
+  const long long kbase = tile * T::CPT;
+  const uint32_t pb = cell_start[kbase], pe = cell_start[kbase + T::CPT];
+  if (pb == pe) return;
+  const uint32_t base = cell_start[tile0 * T::CPT];      // first particle of the slab
+  int tc[3];
+  tc[0] = (int)(tile % g.ntile[0]);
+  tc[1] = (int)((tile / g.ntile[0]) % g.ntile[1]);
+  tc[2] = (int)(tile / ((long long)g.ntile[0] * g.ntile[1]));
+  int c0[3], org[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    c0[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) : 1;
+    org[d] = d < ND ? c0[d] + SFM - 1 : 1;
+  }
+  for (int i = tid; i < 6 * T::FN; i += NTA) {
+    const int comp = i / T::FN, r = i - comp * T::FN;
+    const int fx = r % T::FX, fy = (r / T::FX) % T::FY, fz = r / (T::FX * T::FY);
+    const int X = org[0] + fx, Y = org[1] + fy, Z = org[2] + fz;
+    const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
+                    Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
+    sF[i] = in ? __ldg(F.f[comp] + g.idx(X, Y, Z)) : 0.0;
+  }
+  __syncthreads();
+  for (uint32_t q = pb + tid; q < pe; q += NTA) {
+    double rec[8];
+    int pack;
+    rec[6] = 0.0;
+    if (!push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, counters, rec, pack)) continue;
+    rec[7] = __longlong_as_double((long long)pack);
+    double2* out = reinterpret_cast<double2*>(scratch + (size_t)(q - base) * 8);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) out[k] = make_double2(rec[2 * k], rec[2 * k + 1]);
+  }
+}
+
+template <int ND, int SHAPE>
+__global__ void __launch_bounds__(TL<ND, SHAPE>::CPT, 1) k_deposit_split(GridP g, FieldP F, PushP p,
+                                                                        const uint32_t* __restrict__ cell_start,
+                                                                        long long tile0, const double* __restrict__ scratch) {
+  using T = TL<ND, SHAPE>;
+  constexpr int NW = T::NW, SFM = T::SFM, NA = T::NACC, NTB = T::CPT;
+  extern __shared__ double smem[];
+  double* sJ = smem;                          // [3][JN]
+  int* sM = (int*)(sJ + 3 * T::JN);           // [2 * MCAPB] overflow work items (record, A | m << 2)
+  int* sCnt = sM + 2 * MCAPB;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long tile = tile0 + blockIdx.x;
+  const long long kbase = tile * T::CPT;
+  const uint32_t pb = cell_start[kbase], pe = cell_start[kbase + T::CPT];
+  if (pb == pe) return;
+  const uint32_t base = cell_start[tile0 * T::CPT];
+  int tc[3];
+  tc[0] = (int)(tile % g.ntile[0]);
+  tc[1] = (int)((tile / g.ntile[0]) % g.ntile[1]);
+  tc[2] = (int)(tile / ((long long)g.ntile[0] * g.ntile[1]));
+  int org[3];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) org[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) + SFM - 1 : 1;
+  for (int i = tid; i < 3 * T::JN; i += NTB) sJ[i] = 0.0;
+  if (tid == 0) sCnt[0] = 0;
+  __syncthreads();
+
+  // ---- thread per cell: all components of the cell's box in registers ----
+  const uint32_t my_b = cell_start[kbase + tid], my_e = cell_start[kbase + tid + 1];
+  const int l[3] = {tid % T::TX, (tid / T::TX) % T::TY, tid / (T::TX * T::TY)};
+  double acc[3 * NA];
+#pragma unroll
+  for (int i = 0; i < 3 * NA; ++i) acc[i] = 0.0;
+  for (uint32_t q = my_b; q < my_e; ++q) {
+    const RecG rec{scratch + (size_t)(q - base) * 8};
+    deposit_box<ND, SHAPE, true>(p, rec, 0, acc);
+    const int pack = rec.pack();
+    if ((pack & 0xff) == (ND == 3 ? 0x15 : 0x5)) continue;
+    const int r = (int)(q - pb);
+    if (ND == 2) {
+      const int slot = atomicAdd(sCnt, 1);
+      if (slot < MCAPB) sM[2 * slot] = r;
+      else if (lane >= 0) {   // list full: this thread deposits the particle's overflow alone
+        for (int ln = 0; ln < 32; ++ln) mover_overflow<ND, SHAPE>(p, rec, sJ, ln);
+      }
+    } else {
+      int slot = atomicAdd(sCnt, mover_item_count(pack));
+#pragma unroll
+      for (int m = 0; m < 3; ++m) {
+        const int dc = ((pack >> (2 * m)) & 3) - 1;
+        if (dc == 0) continue;
+#pragma unroll
+        for (int A = 0; A < 3; ++A) {
+          if (slot < MCAPB) { sM[2 * slot] = r; sM[2 * slot + 1] = A | (m << 2); }
+          else mover_item3<SHAPE>(p, rec, sJ, A, m);
+          ++slot;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  // ---- register boxes -> shared J tile: every thread applies the same stencil offset to its own
+  //      cell, so the addresses of a step are distinct; steps are separated by barriers ----
+#pragma unroll
+  for (int dz = 0; dz < (ND == 3 ? NW : 1); ++dz)
+#pragma unroll
+    for (int dy = 0; dy < NW; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < NW; ++dx) {
+        const int off = (l[0] + 1 + dx) + (l[1] + 1 + dy) * T::JX + (ND == 3 ? (l[2] + 1 + dz) * T::JX * T::JY : 0);
+        if (ND == 3) {
+          // component A: acc[(o[Q] * NW + o[P]) * NW + o[A]], P = A + 1, Q = A + 2
+          if (dx < NW - 1) sJ[off] += acc[(dz * NW + dy) * (NW - 1) + dx];                       // A = x: (i, u, v) = (dx, dy, dz)
+          if (dy < NW - 1) sJ[T::JN + off] += acc[NA + (dx * NW + dz) * (NW - 1) + dy];           // A = y: (dy, dz, dx)
+          if (dz < NW - 1) sJ[2 * T::JN + off] += acc[2 * NA + (dy * NW + dx) * (NW - 1) + dz];   // A = z: (dz, dx, dy)
+        } else {
+          sJ[off] += acc[dy * NW + dx];
+          sJ[T::JN + off] += acc[NA + dy * NW + dx];
+          sJ[2 * T::JN + off] += acc[2 * NA + dy * NW + dx];
+        }
+        __syncthreads();
+      }
+  // ---- particles that changed cell ----
+  const int nm = sCnt[0] < MCAPB ? sCnt[0] : MCAPB;
+  if (ND == 3) {
+    for (int m = tid; m < nm; m += NTB) {
+      const RecG rec{scratch + (size_t)(pb - base + (uint32_t)sM[2 * m]) * 8};
+      mover_item3<SHAPE>(p, rec, sJ, sM[2 * m + 1] & 3, (sM[2 * m + 1] >> 2) & 3);
+    }
+  } else {
+    for (int m = warp; m < nm; m += NTB / 32) {
+      const RecG rec{scratch + (size_t)(pb - base + (uint32_t)sM[2 * m]) * 8};
+      mover_overflow<ND, SHAPE>(p, rec, sJ, lane);
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < 3 * T::JN; i += NTB) {
+    const double v = sJ[i];
+    if (v == 0.0) continue;
+    const int cj = i / T::JN, r = i - cj * T::JN;
+    const int jx = r % T::JX, jy = (r / T::JX) % T::JY, jz = r / (T::JX * T::JY);
+    const int X = org[0] + jx, Y = org[1] + jy, Z = org[2] + jz;
+    const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
+                    Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
+    if (in) atomicAdd(F.f[JX + cj] + g.idx(X, Y, Z), v);
+  }
+}
+
+}  // namespace
+
 int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled) {
   *handled = false;
   if (c->ndims < 2 || c->shape == SHAPE_BSPLINE3 || !sp.sorted) return 0;
@@ -638,6 +855,56 @@ int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool
   L(2, 0) L(2, 1) L(3, 0) L(3, 1)
 #undef L
   c->launches++;
+  EB_CUDA(c, cudaGetLastError());
+  *handled = true;
+  return 0;
+}
+
+
+int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled) {
+  *handled = false;
+  if (c->ndims < 2 || c->shape == SHAPE_BSPLINE3 || !sp.sorted || !sp.h_tile_start) return 0;
+  PArr a;
+  for (int d = 0; d < 3; ++d) { a.x[d] = sp.a[d]; a.m[d] = sp.a[3 + d]; }
+  a.w = sp.a[6];
+  const long long ntiles = (long long)c->g.ntile[0] * c->g.ntile[1] * c->g.ntile[2];
+  const uint32_t* ts = sp.h_tile_start;      // ntiles + 1 entries, valid since the sort's synchronise
+  // scratch: 64 B per particle of a slab of tiles
+  long long want = sp.n < c->rec_scratch_max ? sp.n : c->rec_scratch_max;
+  long long biggest = 0;
+  for (long long t = 0; t < ntiles; ++t) biggest = biggest > (long long)(ts[t + 1] - ts[t]) ? biggest : (long long)(ts[t + 1] - ts[t]);
+  if (want < biggest) want = biggest;       // a slab is at least one tile
+  if (want < 1) return 0;
+  if (c->rec_scratch_cap < want) {
+    if (c->rec_scratch) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(c->rec_scratch); }
+    c->rec_scratch = nullptr; c->rec_scratch_cap = 0;
+    EB_CUDA(c, cudaMalloc(&c->rec_scratch, (size_t)want * 8 * sizeof(double)));
+    c->rec_scratch_cap = want;
+  }
+  const long long cap = c->rec_scratch_cap;
+  for (long long t0 = 0; t0 < ntiles;) {
+    if (ts[t0 + 1] == ts[t0]) { ++t0; continue; }               // skip leading empty tiles
+    long long t1 = t0 + 1;
+    while (t1 < ntiles && (long long)(ts[t1 + 1] - ts[t0]) <= cap) ++t1;
+    const unsigned nb = (unsigned)(t1 - t0);
+#define L(ND, SH)                                                                                          \
+    if (c->ndims == ND && c->shape == SH) {                                                                \
+      auto ka = k_push_split<ND, SH>;                                                                      \
+      auto kb = k_deposit_split<ND, SH>;                                                                   \
+      const size_t sa = sizeof(double) * 6 * TL<ND, SH>::FN;                                               \
+      const size_t sb = sizeof(double) * 3 * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4);               \
+      EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
+      EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
+      { ScopedPhase pa(c, "push_A");                                                                       \
+        ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, sp.cell_start, t0, c->rec_scratch, c->d_counters); } \
+      if (!p.zero_current) { ScopedPhase pb(c, "push_B");                                                  \
+        kb<<<nb, TL<ND, SH>::CPT, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch); }    \
+    }
+    L(2, 0) L(2, 1) L(3, 0) L(3, 1)
+#undef L
+    c->launches += p.zero_current ? 1 : 2;
+    t0 = t1;
+  }
   EB_CUDA(c, cudaGetLastError());
   *handled = true;
   return 0;

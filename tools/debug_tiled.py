@@ -10,7 +10,7 @@ abi = _abi.product()
 for nd, shape, n, uth in [(3, "triangle", [16, 12, 8], 0.05), (3, "triangle", [16, 12, 8], 0.5), (2, "triangle", [24, 20], 0.5),
                           (3, "tophat", [16, 12, 8], 0.5), (2, "tophat", [24, 20], 0.5)]:
     sims = []
-    for kern in ("baseline", "tiled"):
+    for kern in ("baseline", os.environ.get("KERN", "split")):
         s = make_plasma(abi, nd, shape, n, seed=7, ppc=8, u_th=uth)
         s.ctx.set_option("push_kernel", kern)
         s.ctx.set_time(s.dt, 0.5 * s.dt, 0)
