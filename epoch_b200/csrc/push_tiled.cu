@@ -73,6 +73,11 @@ struct RecS {            // shared memory, structure of arrays (fused kernel)
   __device__ __forceinline__ double get(int k) const { return sR[k * RPAD + rs]; }
   __device__ __forceinline__ int pack() const { return sD[rs]; }
 };
+struct RecR {            // 8 doubles already in registers (static indices only)
+  const double* r;
+  __device__ __forceinline__ double get(int k) const { return r[k]; }
+  __device__ __forceinline__ int pack() const { return (int)__double_as_longlong(r[7]); }
+};
 struct RecG {            // global scratch, 8 doubles per particle (split kernels)
   const double* r;
   __device__ __forceinline__ double get(int k) const { return __ldg(r + k); }
@@ -209,7 +214,8 @@ namespace {
 //   m == Q: v beyond the box, a and u inside it.
 // Thread per item; the values go to the shared J tile with atomics.
 template <int SHAPE, class R>
-__device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double* __restrict__ sJ, int A, int m) {
+__device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double* __restrict__ sJ, int A, int m,
+                                            int jn = TL<3, SHAPE>::JN, int sub_off = 0) {
   using T = TL<3, SHAPE>;
   constexpr int NW = T::NW, NS = NW + 2;
   const int P = A == 2 ? 0 : A + 1, Q = P == 2 ? 0 : P + 1;
@@ -226,7 +232,7 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double
   const int stA = A == 0 ? 1 : (A == 1 ? T::JX : T::JX * T::JY);
   const int stP = P == 0 ? 1 : (P == 1 ? T::JX : T::JX * T::JY);
   const int stQ = Q == 0 ? 1 : (Q == 1 ? T::JX : T::JX * T::JY);
-  double* base = sJ + A * T::JN + l0 + l1 * T::JX + l2 * T::JX * T::JY;   // window index t = 0 <-> region index l
+  double* base = sJ + A * jn + l0 + l1 * T::JX + (l2 - sub_off) * T::JX * T::JY;   // window index t = 0 <-> region index l
   // full-window arrays along Q (t = 0 .. NW+1)
   double q1[NS], q2[NS];
   q1[0] = 0.5 * loQ; q2[0] = third * loQ; q1[NS - 1] = 0.5 * hiQ; q2[NS - 1] = third * hiQ;
@@ -247,8 +253,10 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double
     for (int v = 0; v < NS; ++v)
 #pragma unroll
       for (int u = 0; u < NS; ++u) {
-        const double val = cov * (g5[u] * q1[v] + h5[u] * q2[v]);
-        if (val != 0.0 && u >= lo && u < hi && v >= lo && v < hi) atomicAdd(base + ta * stA + u * stP + v * stQ, val);
+        // window membership first: the slots beyond the box exist only where P / Q moved too
+        const bool in = u >= lo && u < hi && v >= lo && v < hi && (u != 0 || dcP < 0) && (u != NS - 1 || dcP > 0) &&
+                        (v != 0 || dcQ < 0) && (v != NS - 1 || dcQ > 0);
+        if (in) atomicAdd(base + ta * stA + u * stP + v * stQ, cov * (g5[u] * q1[v] + h5[u] * q2[v]));
       }
   } else {
     double ca[NW];
@@ -261,7 +269,7 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double
 #pragma unroll
       for (int v = 0; v < NS; ++v) {
         const double w = hov * q2[v];
-        if (w != 0.0) {
+        if ((v != 0 || dcQ < 0) && (v != NS - 1 || dcQ > 0)) {
 #pragma unroll
           for (int i = 0; i < NW; ++i) atomicAdd(base + (1 + i) * stA + tu * stP + v * stQ, ca[i] * w);
         }
@@ -372,12 +380,14 @@ namespace {
 // phase 2b: the warp adds the contributions of one cell-changing particle that fall
 // outside its home box (at most one layer per axis), lane per (component, cell)
 template <int ND, int SHAPE, class R>
-__device__ __forceinline__ void mover_overflow(const PushP& p, const R& rec, double* __restrict__ sJ, int lane) {
+__device__ __forceinline__ void mover_overflow(const PushP& p, const R& rec, double* __restrict__ sJ, int lane,
+                                               int jn = TL<ND, SHAPE>::JN, int sub_off = 0) {
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW, NS = NW + 2;
   const int pk = rec.pack();
   const int lc = pk >> 8;
-  const int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
+  int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
+  l[ND - 1] -= sub_off;
   const double w = rec.get(2 * ND);
   // full-window arrays per axis: index t = 0 (slot below the box), 1..NW (box), NW+1 (slot above)
   double g5[ND][NS], h5[ND][NS], c5[ND][NS];
@@ -440,7 +450,7 @@ __device__ __forceinline__ void mover_overflow(const PushP& p, const R& rec, dou
       else val = (p.fc[2] * w * p.q * rec.get(2 * ND + 1)) * (gv[0] * yf1 + hv[0] * yf2);
     }
     const int idx = ((ND >= 3 ? (l[2] + t[2]) : 0) * T::JY + (ND >= 2 ? (l[1] + t[1]) : 0)) * T::JX + l[0] + t[0];
-    atomicAdd(sJ + comp * T::JN + idx, val);
+    atomicAdd(sJ + comp * jn + idx, val);
   }
 }
 
@@ -728,21 +738,34 @@ __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F
   }
 }
 
+constexpr int SUB = 2;           // a deposit CTA owns 1/SUB of a tile, split along the slowest tile axis
+
+__device__ __forceinline__ void load_rec(double* r, const double* src) {
+  const double2* s2 = reinterpret_cast<const double2*>(src);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { const double2 v = __ldg(s2 + k); r[2 * k] = v.x; r[2 * k + 1] = v.y; }
+}
+
 template <int ND, int SHAPE>
-__global__ void __launch_bounds__(TL<ND, SHAPE>::CPT, 1) k_deposit_split(GridP g, FieldP F, PushP p,
-                                                                        const uint32_t* __restrict__ cell_start,
-                                                                        long long tile0, const double* __restrict__ scratch) {
+__global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, SUB) k_deposit_split(GridP g, FieldP F, PushP p,
+                                                                                const uint32_t* __restrict__ cell_start,
+                                                                                long long tile0, const double* __restrict__ scratch) {
   using T = TL<ND, SHAPE>;
-  constexpr int NW = T::NW, SFM = T::SFM, NA = T::NACC, NTB = T::CPT;
+  constexpr int NW = T::NW, SFM = T::SFM, NA = T::NACC, NTB = T::CPT / SUB;
+  constexpr int SA = ND - 1;                                   // split axis
+  constexpr int TS = tile_dim(ND, SA) / SUB;                   // cells of the sub-tile along it
+  constexpr int JXs = T::JX, JYs = ND == 3 ? T::JY : TS + NW + 1, JZs = ND == 3 ? TS + NW + 1 : 1;
+  constexpr int JNs = JXs * JYs * JZs;
   extern __shared__ double smem[];
-  double* sJ = smem;                          // [3][JN]
-  int* sM = (int*)(sJ + 3 * T::JN);           // [2 * MCAPB] overflow work items (record, A | m << 2)
+  double* sJ = smem;                          // [3][JNs]
+  int* sM = (int*)(sJ + 3 * JNs);             // [2 * MCAPB] work items (record, A | m << 2)
   int* sCnt = sM + 2 * MCAPB;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const long long tile = tile0 + blockIdx.x;
+  const long long tile = tile0 + blockIdx.x / SUB;
+  const int sub = blockIdx.x % SUB;
   const long long kbase = tile * T::CPT;
-  const uint32_t pb = cell_start[kbase], pe = cell_start[kbase + T::CPT];
-  if (pb == pe) return;
+  const uint32_t pb = cell_start[kbase], sb0 = cell_start[kbase + sub * NTB], sb1 = cell_start[kbase + (sub + 1) * NTB];
+  if (sb0 == sb1) return;
   const uint32_t base = cell_start[tile0 * T::CPT];
   int tc[3];
   tc[0] = (int)(tile % g.ntile[0]);
@@ -750,43 +773,51 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT, 1) k_deposit_split(GridP g
   tc[2] = (int)(tile / ((long long)g.ntile[0] * g.ntile[1]));
   int org[3];
 #pragma unroll
-  for (int d = 0; d < 3; ++d) org[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) + SFM - 1 : 1;
-  for (int i = tid; i < 3 * T::JN; i += NTB) sJ[i] = 0.0;
+  for (int d = 0; d < 3; ++d) org[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) + SFM - 1 + (d == SA ? sub * TS : 0) : 1;
+  for (int i = tid; i < 3 * JNs; i += NTB) sJ[i] = 0.0;
   if (tid == 0) sCnt[0] = 0;
   __syncthreads();
 
-  // ---- thread per cell: all components of the cell's box in registers ----
-  const uint32_t my_b = cell_start[kbase + tid], my_e = cell_start[kbase + tid + 1];
-  const int l[3] = {tid % T::TX, (tid / T::TX) % T::TY, tid / (T::TX * T::TY)};
+  // ---- thread per cell: all components of the cell's box in registers; the next record is
+  //      fetched while the current one is deposited ----
+  const int lc = sub * NTB + tid;
+  const uint32_t my_b = cell_start[kbase + lc], my_e = cell_start[kbase + lc + 1];
+  int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
+  l[SA] -= sub * TS;
   double acc[3 * NA];
 #pragma unroll
   for (int i = 0; i < 3 * NA; ++i) acc[i] = 0.0;
+  double cur[8], nx1[8];
+  if (my_b < my_e) load_rec(cur, scratch + (size_t)(my_b - base) * 8);
+  if (my_b + 1 < my_e) load_rec(nx1, scratch + (size_t)(my_b + 1 - base) * 8);
   for (uint32_t q = my_b; q < my_e; ++q) {
-    const RecG rec{scratch + (size_t)(q - base) * 8};
-    deposit_box<ND, SHAPE, true>(p, rec, 0, acc);
-    const int pack = rec.pack();
-    if ((pack & 0xff) == (ND == 3 ? 0x15 : 0x5)) continue;
-    const int r = (int)(q - pb);
-    if (ND == 2) {
-      const int slot = atomicAdd(sCnt, 1);
-      if (slot < MCAPB) sM[2 * slot] = r;
-      else if (lane >= 0) {   // list full: this thread deposits the particle's overflow alone
-        for (int ln = 0; ln < 32; ++ln) mover_overflow<ND, SHAPE>(p, rec, sJ, ln);
-      }
-    } else {
-      int slot = atomicAdd(sCnt, mover_item_count(pack));
+    double nxt[8];
+    if (q + 2 < my_e) load_rec(nxt, scratch + (size_t)(q + 2 - base) * 8);
+    deposit_box<ND, SHAPE, true>(p, RecR{cur}, 0, acc);
+    const int pack = (int)__double_as_longlong(cur[7]);
+    if ((pack & 0xff) != (ND == 3 ? 0x15 : 0x5)) {
+      const RecG rec{scratch + (size_t)(q - base) * 8};
+      const int r = (int)(q - pb);
+      if (ND == 2) {
+        const int slot = atomicAdd(sCnt, 1);
+        if (slot < MCAPB) sM[2 * slot] = r;
+        else for (int ln = 0; ln < 32; ++ln) mover_overflow<ND, SHAPE>(p, rec, sJ, ln, JNs, sub * TS);   // list full
+      } else {
+        int slot = atomicAdd(sCnt, mover_item_count(pack));
 #pragma unroll
-      for (int m = 0; m < 3; ++m) {
-        const int dc = ((pack >> (2 * m)) & 3) - 1;
-        if (dc == 0) continue;
+        for (int m = 0; m < 3; ++m) {
+          if (((pack >> (2 * m)) & 3) == 1) continue;
 #pragma unroll
-        for (int A = 0; A < 3; ++A) {
-          if (slot < MCAPB) { sM[2 * slot] = r; sM[2 * slot + 1] = A | (m << 2); }
-          else mover_item3<SHAPE>(p, rec, sJ, A, m);
-          ++slot;
+          for (int A = 0; A < 3; ++A) {
+            if (slot < MCAPB) { sM[2 * slot] = r; sM[2 * slot + 1] = A | (m << 2); }
+            else mover_item3<SHAPE>(p, rec, sJ, A, m, JNs, sub * TS);
+            ++slot;
+          }
         }
       }
     }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { cur[k] = nx1[k]; nx1[k] = nxt[k]; }
   }
   __syncthreads();
   // ---- register boxes -> shared J tile: every thread applies the same stencil offset to its own
@@ -797,16 +828,16 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT, 1) k_deposit_split(GridP g
     for (int dy = 0; dy < NW; ++dy)
 #pragma unroll
       for (int dx = 0; dx < NW; ++dx) {
-        const int off = (l[0] + 1 + dx) + (l[1] + 1 + dy) * T::JX + (ND == 3 ? (l[2] + 1 + dz) * T::JX * T::JY : 0);
+        const int off = (l[0] + 1 + dx) + (l[1] + 1 + dy) * JXs + (ND == 3 ? (l[2] + 1 + dz) * JXs * JYs : 0);
         if (ND == 3) {
-          // component A: acc[(o[Q] * NW + o[P]) * NW + o[A]], P = A + 1, Q = A + 2
-          if (dx < NW - 1) sJ[off] += acc[(dz * NW + dy) * (NW - 1) + dx];                       // A = x: (i, u, v) = (dx, dy, dz)
-          if (dy < NW - 1) sJ[T::JN + off] += acc[NA + (dx * NW + dz) * (NW - 1) + dy];           // A = y: (dy, dz, dx)
-          if (dz < NW - 1) sJ[2 * T::JN + off] += acc[2 * NA + (dy * NW + dx) * (NW - 1) + dz];   // A = z: (dz, dx, dy)
+          // component A: acc[(o[Q] * NW + o[P]) * (NW - 1) + o[A]], P = A + 1, Q = A + 2, o[A] < NW - 1
+          if (dx < NW - 1) sJ[off] += acc[(dz * NW + dy) * (NW - 1) + dx];
+          if (dy < NW - 1) sJ[JNs + off] += acc[NA + (dx * NW + dz) * (NW - 1) + dy];
+          if (dz < NW - 1) sJ[2 * JNs + off] += acc[2 * NA + (dy * NW + dx) * (NW - 1) + dz];
         } else {
           sJ[off] += acc[dy * NW + dx];
-          sJ[T::JN + off] += acc[NA + dy * NW + dx];
-          sJ[2 * T::JN + off] += acc[2 * NA + dy * NW + dx];
+          sJ[JNs + off] += acc[NA + dy * NW + dx];
+          sJ[2 * JNs + off] += acc[2 * NA + dy * NW + dx];
         }
         __syncthreads();
       }
@@ -815,24 +846,29 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT, 1) k_deposit_split(GridP g
   if (ND == 3) {
     for (int m = tid; m < nm; m += NTB) {
       const RecG rec{scratch + (size_t)(pb - base + (uint32_t)sM[2 * m]) * 8};
-      mover_item3<SHAPE>(p, rec, sJ, sM[2 * m + 1] & 3, (sM[2 * m + 1] >> 2) & 3);
+      mover_item3<SHAPE>(p, rec, sJ, sM[2 * m + 1] & 3, (sM[2 * m + 1] >> 2) & 3, JNs, sub * TS);
     }
   } else {
     for (int m = warp; m < nm; m += NTB / 32) {
       const RecG rec{scratch + (size_t)(pb - base + (uint32_t)sM[2 * m]) * 8};
-      mover_overflow<ND, SHAPE>(p, rec, sJ, lane);
+      mover_overflow<ND, SHAPE>(p, rec, sJ, lane, JNs, sub * TS);
     }
   }
   __syncthreads();
-  for (int i = tid; i < 3 * T::JN; i += NTB) {
-    const double v = sJ[i];
-    if (v == 0.0) continue;
-    const int cj = i / T::JN, r = i - cj * T::JN;
-    const int jx = r % T::JX, jy = (r / T::JX) % T::JY, jz = r / (T::JX * T::JY);
-    const int X = org[0] + jx, Y = org[1] + jy, Z = org[2] + jz;
-    const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
-                    Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
-    if (in) atomicAdd(F.f[JX + cj] + g.idx(X, Y, Z), v);
+  // tile J -> HBM (RED.ADD.F64: tile halos overlap): thread per (component, y, z) row, walking x
+  for (int row = tid; row < 3 * JYs * JZs; row += NTB) {
+    const int cj = row / (JYs * JZs), r = row - cj * (JYs * JZs);
+    const int jy = r % JYs, jz = r / JYs;
+    const int Y = org[1] + jy, Z = org[2] + jz;
+    if (Y < 1 - g.ngd[1] || Y > g.n[1] + g.ngd[1] || Z < 1 - g.ngd[2] || Z > g.n[2] + g.ngd[2]) continue;
+    const double* src = sJ + cj * JNs + (jz * JYs + jy) * JXs;
+    double* dst = F.f[JX + cj] + g.idx(org[0], Y, Z);
+    const int x_lo = 1 - g.ngd[0] - org[0], x_hi = g.n[0] + g.ngd[0] - org[0];
+#pragma unroll
+    for (int jx = 0; jx < JXs; ++jx) {
+      const double v = src[jx];
+      if (v != 0.0 && jx >= x_lo && jx <= x_hi) atomicAdd(dst + jx, v);
+    }
   }
 }
 
@@ -892,13 +928,13 @@ int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool
       auto ka = k_push_split<ND, SH>;                                                                      \
       auto kb = k_deposit_split<ND, SH>;                                                                   \
       const size_t sa = sizeof(double) * 6 * TL<ND, SH>::FN;                                               \
-      const size_t sb = sizeof(double) * 3 * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4);               \
+      const size_t sb = sizeof(double) * 3 * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4);  /* >= sub-tile need */ \
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
       { ScopedPhase pa(c, "push_A");                                                                       \
         ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, sp.cell_start, t0, c->rec_scratch, c->d_counters); } \
       if (!p.zero_current) { ScopedPhase pb(c, "push_B");                                                  \
-        kb<<<nb, TL<ND, SH>::CPT, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch); }    \
+        kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch); }    \
     }
     L(2, 0) L(2, 1) L(3, 0) L(3, 1)
 #undef L
