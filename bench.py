@@ -263,6 +263,9 @@ def run_ours(args):
     t_gen = time.perf_counter() - t_setup
     sim.ctx.set_option("reserve", f"0:{n_part + n_part // 64 if world > 1 else n_part}")
     sim.ctx.set_option("timers", 1)
+    for kv in args.opt:                       # tuning experiments: --opt push_kernel=tiled
+        k, v = kv.split("=", 1)
+        sim.ctx.set_option(k, v)
     sim.ctx.upload_particles(0, host)
     sim.ctx.sync()
     t_up = time.perf_counter() - t_setup - t_gen
@@ -386,6 +389,7 @@ def main():
     ap.add_argument("--seed", type=int, default=12345)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="library option key=value (tuning experiments)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":

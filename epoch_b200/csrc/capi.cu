@@ -375,6 +375,7 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
     else return fail(c, EB200_E_ARG, "push_kernel: auto|baseline|tiled|split");
     return 0;
   }
+  if (k == "fuse_keys") { c->fuse_keys = atoi(value) != 0; return 0; }
   if (k == "deterministic_deposit") { c->deterministic = atoi(value) != 0; return 0; }
   if (k == "sort_every") { c->sort_every = atoi(value) < 1 ? 1 : atoi(value); return 0; }
   if (k == "timers") { c->timers_on = atoi(value) != 0; return 0; }

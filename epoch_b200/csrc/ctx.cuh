@@ -134,6 +134,7 @@ struct eb200_ctx {
   // options
   int push_kernel = 0;          // 0 auto, 1 baseline, 2 tiled (fused), 3 split (push + deposit kernels)
   int deterministic = 0;
+  int fuse_keys = 1;            // option fuse_keys: push kernel emits the next sort keys (single rank)
   int sort_every = 1;
   bool timers_on = false;
   std::map<std::string, eb::PhaseTimer> timers;
@@ -188,7 +189,7 @@ int32_t particle_bcs(eb200_ctx* c);
 int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need, bool exact = false);
 int32_t add_particles(eb200_ctx* c, int isp, long long n, const double* packed, int nvar, bool replace);
 int32_t get_particles(eb200_ctx* c, int isp, long long first, long long cap, double* packed, int nvar, long long* n_out);
-int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots);
+int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_ready = false);
 // reduce.cu
 int32_t energy(eb200_ctx* c, double* fe, double* per_species);
 int32_t charge_residual(eb200_ctx* c, double* max_res, double* max_rho, bool capture);

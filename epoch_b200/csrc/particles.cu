@@ -11,7 +11,9 @@ namespace eb {
 
 int32_t launch_push_baseline(eb200_ctx* c, const SpeciesD& sp, const PushP& p);   // push_baseline.cu
 int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled);  // push_tiled.cu
-int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled);  // push_tiled.cu
+int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled, const void* keysink);  // push_tiled.cu
+size_t keysink_size();
+void keysink_fill(void* dst, const BcP3& bc, uint32_t* key, uint32_t* count, uint32_t nbucket);
 
 // ---------------------------------------------------------------------------------
 // storage
@@ -130,26 +132,40 @@ int32_t get_particles(eb200_ctx* c, int isp, long long first, long long cap, dou
 // ---------------------------------------------------------------------------------
 // key = extended-grid linear index of (cell_x1, cell_y1, cell_z1) evaluated exactly
 // as the push does (half drift with the stored momentum, particles.F90:242-291).
+// particle boundary condition of one axis (particle_bcs, boundary.F90:1316-1972)
+
+// Fused pass over the particles of a species: (i) particle_bcs of the axes that are not
+// decomposed (no migration there: periodic wrap, reflection, open-boundary removal),
+// (ii) sort key of the cell the next push gathers from, (iii) warp-aggregated histogram of
+// the keys.  Removed particles get KEY_INVALID and are counted in the last bucket.
 template <int ND, int SHAPE>
-__global__ void k_keys(GridP g, PushP p, const double* __restrict__ X, const double* __restrict__ Y,
-                       const double* __restrict__ Z, const double* __restrict__ PX,
-                       const double* __restrict__ PY, const double* __restrict__ PZ, uint32_t* key) {
+__global__ void k_keys(GridP g, PushP p, BcP3 bc, double* __restrict__ X, double* __restrict__ Y,
+                       double* __restrict__ Z, double* __restrict__ PX, double* __restrict__ PY,
+                       double* __restrict__ PZ, uint32_t* key, uint32_t* count, uint32_t nbucket) {
   const long long ip = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (ip >= p.n) return;
-  if (key[ip] == KEY_INVALID) return;
-  const double* POS[3] = {X, Y, Z};
-  double pos[3] = {0, 0, 0}, px[3] = {0, 0, 0}, ux, uy, uz;
+  const bool act = ip < p.n;
+  uint32_t k = nbucket - 1;
+  if (act && key[ip] != KEY_INVALID) {
+    double* POS[3] = {X, Y, Z};
+    double* MOM[3] = {PX, PY, PZ};
+    double pos[3] = {0, 0, 0}, mom[3];
+    mom[0] = PX[ip]; mom[1] = PY[ip]; mom[2] = PZ[ip];
 #pragma unroll
-  for (int d = 0; d < ND; ++d) pos[d] = POS[d][ip];
-  half_drift<ND>(p, pos, PX[ip], PY[ip], PZ[ip], px, ux, uy, uz);
-  int cell[3] = {1, 1, 1};
+    for (int d = 0; d < ND; ++d) pos[d] = POS[d][ip];
+    const int ch = bc_and_key<ND, SHAPE>(g, p, bc, pos, mom, k);
+    if (ch < 0) { k = nbucket - 1; key[ip] = KEY_INVALID; }
+    else {
+      key[ip] = k;
 #pragma unroll
-  for (int d = 0; d < ND; ++d) {
-    double frac;
-    cell[d] = cell_round(cell_coord<SHAPE>(px[d], p.idx[d]), frac);   // 1-based
+      for (int d = 0; d < ND; ++d)
+        if (ch & (1 << d)) { POS[d][ip] = pos[d]; MOM[d][ip] = mom[d]; }
+    }
   }
-  const uint32_t k = cell_key<ND>(g, cell);
-  key[ip] = k;
+  // histogram: sorted input => few distinct keys per warp
+  const unsigned am = __ballot_sync(0xffffffffu, act);
+  if (!act) return;
+  const unsigned peers = __match_any_sync(am, k);
+  if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(count + k, (uint32_t)__popc(peers));
 }
 
 // warp-aggregated histogram / rank: sorted input => few distinct keys per warp
@@ -194,6 +210,20 @@ __global__ void k_fill_u32(uint32_t* a, long long n, uint32_t v) {
   if (i < n) a[i] = v;
 }
 
+static BcP make_bc(const eb200_ctx* c, const SpeciesD& sp, int ax) {
+  const GridP& g = c->g;
+  BcP b;
+  b.axis = ax; b.min_bnd = c->min_bnd[ax]; b.max_bnd = c->max_bnd[ax];
+  b.bc_min = sp.bc[2 * ax]; b.bc_max = sp.bc[2 * ax + 1];
+  b.multi = c->nprocdir[ax] > 1;
+  b.min_local = g.min_local[ax]; b.max_local = g.max_local[ax];
+  b.gmin = g.gmin[ax]; b.gmax = g.gmax[ax];
+  const double boundary_shift = g.d[ax] * (double)((1 + c->png + 0) / 2);   // boundary.F90:1336-1338
+  b.min_outer = b.gmin - boundary_shift; b.max_outer = b.gmax + boundary_shift;
+  b.shift = (b.gmax - b.gmin);                                             // x_shift, cpml_thickness = 0
+  return b;
+}
+
 static PushP make_push_params(eb200_ctx* c, const SpeciesD& sp, long long n) {
   PushP p;
   const int nd = c->ndims;
@@ -236,7 +266,7 @@ static int32_t ensure_cells(eb200_ctx* c, SpeciesD& sp) {
 // sort slots [0, n_slots) of a species; dead slots (key == KEY_INVALID) go last
 // and are dropped.  `need_count`: read the live count back (it can only change
 // when particles were removed or appended).
-int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
+int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_ready) {
   ScopedPhase ph(c, "sort");
   if (n_slots == 0) { sp.n = 0; sp.sorted = true; return 0; }
   if (n_slots >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "more than 2^32 particles per species per GPU");
@@ -245,13 +275,19 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
   const int B = 256;
   const unsigned gp = (unsigned)((n_slots + B - 1) / B);
   PushP p = make_push_params(c, sp, n_slots);
+  BcP3 bc;
+  for (int d = 0; d < 3; ++d) {
+    bc.on[d] = d < c->ndims && c->nprocdir[d] == 1;      // decomposed axes were handled by species_bcs (migration)
+    bc.b[d] = make_bc(c, sp, d < c->ndims ? d : 0);
+  }
+  if (!keys_ready) {      // else the push kernel has already written keys and histogram
+  EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
 #define LK(ND, SH)                                                                               \
   if (c->ndims == ND && c->shape == SH)                                                          \
-    k_keys<ND, SH><<<gp, B, 0, c->stream>>>(c->g, p, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.key);
+    k_keys<ND, SH><<<gp, B, 0, c->stream>>>(c->g, p, bc, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.key, c->cell_count, nbucket);
   LK(1, 0) LK(1, 1) LK(1, 2) LK(2, 0) LK(2, 1) LK(2, 2) LK(3, 0) LK(3, 1) LK(3, 2)
 #undef LK
-  EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
-  k_hist<<<gp, B, 0, c->stream>>>(sp.key, n_slots, c->cell_count, nbucket);
+  }
   size_t tmp = 0;
   cub::DeviceScan::ExclusiveSum(nullptr, tmp, c->cell_count, sp.cell_start, (int)(nbucket + 1), c->stream);
   if (tmp > c->cub_tmp_bytes) {
@@ -263,7 +299,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
   cub::DeviceScan::ExclusiveSum(c->cub_tmp, tmp, c->cell_count, sp.cell_start, (int)(nbucket + 1), c->stream);
   EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
   k_dest<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket);
-  c->launches += 5;
+  c->launches += keys_ready ? 3 : 4;
   // scatter each attribute through one spare array; the spare rotates
   if (c->attr_scratch_cap < sp.cap) {
     if (c->attr_scratch) cudaFree(c->attr_scratch);
@@ -303,9 +339,11 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
   EB_CUDA(c, cudaMemcpyAsync(c->h_counters, sp.cell_start + (nbucket - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
   EB_CUDA(c, cudaStreamSynchronize(c->stream));
   sp.n = (long long)(*(uint32_t*)c->h_counters);
-  // keys of the live range are now implied by cell_start; reset them to "valid"
-  k_fill_u32<<<(unsigned)((n_slots + B - 1) / B), B, 0, c->stream>>>(sp.key, n_slots, 0u);
-  c->launches++;
+  // keys are not permuted: if any slot was dropped, stale KEY_INVALID marks must not survive
+  if (sp.n != n_slots) {
+    k_fill_u32<<<(unsigned)((n_slots + B - 1) / B), B, 0, c->stream>>>(sp.key, n_slots, 0u);
+    c->launches++;
+  }
   sp.sorted = true;
   EB_CUDA(c, cudaGetLastError());
   return 0;
@@ -314,10 +352,6 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
 // ---------------------------------------------------------------------------------
 // particle boundary conditions (one axis at a time: x, then y, then z)
 // ---------------------------------------------------------------------------------
-struct BcP {
-  int axis, min_bnd, max_bnd, bc_min, bc_max, multi;   // multi: nprocdir[axis] > 1
-  double min_local, max_local, gmin, gmax, min_outer, max_outer, shift;
-};
 // flags: dest[i] = 0 stay, 1 send to low neighbour, 2 send to high neighbour
 __global__ void k_particle_bc(BcP b, long long n, double* __restrict__ pos, double* __restrict__ mom,
                               uint32_t* key, uint32_t* flag, unsigned long long* counters) {
@@ -378,18 +412,10 @@ static int32_t read_counters(eb200_ctx* c, int n) {
 // applies particle_bcs to slots [0, n_slots) of one species; returns the new slot
 // count (arrivals are appended) and whether the live count may have changed
 static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool& changed) {
-  const GridP& g = c->g;
   const int nvar = c->ndims + 4;
   for (int ax = 0; ax < c->ndims; ++ax) {
-    BcP b;
-    b.axis = ax; b.min_bnd = c->min_bnd[ax]; b.max_bnd = c->max_bnd[ax];
-    b.bc_min = sp.bc[2 * ax]; b.bc_max = sp.bc[2 * ax + 1];
-    b.multi = c->nprocdir[ax] > 1;
-    b.min_local = g.min_local[ax]; b.max_local = g.max_local[ax];
-    b.gmin = g.gmin[ax]; b.gmax = g.gmax[ax];
-    const double boundary_shift = g.d[ax] * (double)((1 + c->png + 0) / 2);   // boundary.F90:1336-1338
-    b.min_outer = b.gmin - boundary_shift; b.max_outer = b.gmax + boundary_shift;
-    b.shift = (b.gmax - b.gmin);                                             // x_shift, cpml_thickness = 0
+    const BcP b = make_bc(c, sp, ax);
+    if (!b.multi) continue;        // axes that are not decomposed are handled inside the sort's key pass
     const bool open_here = (b.min_bnd && b.bc_min == EB200_BC_OPEN) || (b.max_bnd && b.bc_max == EB200_BC_OPEN);
     if (n_slots > 0 || b.multi) {
       if (b.multi || open_here) EB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
@@ -477,20 +503,53 @@ int32_t push_particles(eb200_ctx* c) {
     ScopedPhase ph(c, "push");
     EB_CUDA(c, cudaMemsetAsync(c->f.f[JX], 0, (size_t)3 * c->g.total * sizeof(double), c->stream));
   }
-  for (SpeciesD& sp : c->species) {
+  std::vector<char> done(c->species.size(), 0);
+  for (size_t is = 0; is < c->species.size(); ++is) {
+    SpeciesD& sp = c->species[is];
     if (!sp.defined || sp.immobile || sp.species_type == 1) continue;
     if (!sp.sorted) EB_TRY(sort_species(c, sp, sp.n));
     if (sp.n == 0) continue;
-    ScopedPhase ph(c, "push");
     PushP p = make_push_params(c, sp, sp.n);
-    bool handled = false;
-    ScopedPhase pk(c, "push_kernel");     // the kernel alone (roofline figure of bench.py)
-    if (c->push_kernel == 0 || c->push_kernel == 3) EB_TRY(launch_push_split(c, sp, p, &handled));
-    if (!handled && c->push_kernel != 1) EB_TRY(launch_push_tiled(c, sp, p, &handled));
-    if (!handled) EB_TRY(launch_push_baseline(c, sp, p));
+    bool handled = false, fused_keys = false;
+    {
+      ScopedPhase ph(c, "push");
+      ScopedPhase pk(c, "push_kernel");     // the kernel(s) alone (roofline figure of bench.py)
+      if (c->push_kernel == 0 || c->push_kernel == 3) {
+        // single rank: no migration, so the push kernel can apply the particle BCs itself and emit
+        // the next sort keys + histogram (saves the sort's pass over the particle arrays)
+        std::vector<char> ksbuf(keysink_size());
+        const void* ks = nullptr;
+        if (c->nproc == 1 && c->fuse_keys) {
+          EB_TRY(ensure_cells(c, sp));
+          const uint32_t nbucket = (uint32_t)(c->g.ncell_ext + 1);
+          EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
+          BcP3 bc;
+          for (int d = 0; d < 3; ++d) { bc.on[d] = d < c->ndims; bc.b[d] = make_bc(c, sp, d < c->ndims ? d : 0); }
+          keysink_fill(ksbuf.data(), bc, sp.key, c->cell_count, nbucket);
+          ks = ksbuf.data();
+        }
+        EB_TRY(launch_push_split(c, sp, p, &handled, ks));
+        fused_keys = handled && ks != nullptr;
+      }
+      if (!handled && c->push_kernel != 1) EB_TRY(launch_push_tiled(c, sp, p, &handled));
+      if (!handled) EB_TRY(launch_push_baseline(c, sp, p));
+    }
+    if (fused_keys) { EB_TRY(sort_species(c, sp, sp.n, true)); done[is] = 1; }
   }
   // current_bcs(species) is a no-op without mixed per-species BCs (boundary.F90:1130-1136)
-  return particle_bcs(c);
+  // particle_bcs for the species the push did not already finish
+  for (size_t is = 0; is < c->species.size(); ++is) {
+    SpeciesD& sp = c->species[is];
+    if (!sp.defined || done[is]) continue;
+    long long n_slots = sp.n;
+    bool changed = false;
+    {
+      ScopedPhase ph(c, "bcs");
+      EB_TRY(species_bcs(c, sp, n_slots, changed));
+    }
+    EB_TRY(sort_species(c, sp, n_slots));
+  }
+  return 0;
 }
 
 }  // namespace eb

@@ -102,6 +102,51 @@ __device__ __forceinline__ uint32_t cell_key(const GridP& g, const int* cell) {
   return tile * (uint32_t)g.cpt + loc;
 }
 
+// particle boundary condition of one axis (particle_bcs, boundary.F90:1316-1972)
+struct BcP {
+  int axis, min_bnd, max_bnd, bc_min, bc_max, multi;   // multi: nprocdir[axis] > 1
+  double min_local, max_local, gmin, gmax, min_outer, max_outer, shift;
+};
+struct BcP3 { BcP b[3]; int on[3]; };
+
+// particle_bcs of the axes that are not decomposed (periodic wrap, reflection, open-boundary
+// removal; boundary.F90:1390-1461: the min side tests <, the max side >=), then the sort key of
+// the cell the next push gathers from.  pos/mom are updated in place; returns -1 when the
+// particle left through an open boundary, else a bit mask of the axes that were changed.
+template <int ND, int SHAPE>
+__device__ __forceinline__ int bc_and_key(const GridP& g, const PushP& p, const BcP3& bc, double* pos, double* mom,
+                                          uint32_t& key) {
+  int changed = 0;
+  bool out = false;
+#pragma unroll
+  for (int d = 0; d < ND; ++d) {
+    if (!bc.on[d]) continue;
+    const BcP& b = bc.b[d];
+    const double part_pos = pos[d];
+    if (part_pos < b.min_local) {
+      if (b.bc_min == EB200_BC_REFLECT) { pos[d] = 2.0 * b.gmin - part_pos; mom[d] = -mom[d]; changed |= 1 << d; }
+      else if (b.bc_min == EB200_BC_PERIODIC) { pos[d] = part_pos + b.shift; changed |= 1 << d; }
+      if (part_pos < b.min_outer && b.bc_min != EB200_BC_PERIODIC) out = true;
+    }
+    if (part_pos >= b.max_local) {
+      if (b.bc_max == EB200_BC_REFLECT) { pos[d] = 2.0 * b.gmax - part_pos; mom[d] = -mom[d]; changed |= 1 << d; }
+      else if (b.bc_max == EB200_BC_PERIODIC) { pos[d] = part_pos - b.shift; changed |= 1 << d; }
+      if (part_pos >= b.max_outer && b.bc_max != EB200_BC_PERIODIC) out = true;
+    }
+  }
+  if (out) return -1;
+  double px[3] = {0, 0, 0}, ux, uy, uz;
+  half_drift<ND>(p, pos, mom[0], mom[1], mom[2], px, ux, uy, uz);
+  int cell[3] = {1, 1, 1};
+#pragma unroll
+  for (int d = 0; d < ND; ++d) {
+    double frac;
+    cell[d] = cell_round(cell_coord<SHAPE>(px[d], p.idx[d]), frac);   // 1-based
+  }
+  key = cell_key<ND>(g, cell);
+  return changed;
+}
+
 // Boris rotation (particles.F90:347-394); u is updated in place
 __device__ __forceinline__ void boris(double& ux, double& uy, double& uz, double ex, double ey, double ez,
                                       double bx, double by, double bz, double cmratio, double ccmratio) {

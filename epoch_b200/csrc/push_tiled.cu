@@ -292,13 +292,17 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double
 namespace {
 
 struct PArr { double* x[3]; double* m[3]; const double* w; };
+// when on: the push also applies the particle BCs of the (undecomposed) axes to the values it
+// stores and produces the next sort key + key histogram, saving the sort's own pass
+struct KeySink { int on; BcP3 bc; uint32_t* key; uint32_t* count; uint32_t nbucket; };
 
 // phase 1 for one particle: particles.F90:219-452 (gather stage, Boris, drift, store,
 // extra half drift); leaves the deposit inputs in the record arrays
 template <int ND, int SHAPE>
 __device__ __forceinline__ bool push_one(const PushP& p, const PArr& a, long long ip, const int* c0,
                                          const double* __restrict__ sF, unsigned long long* counters,
-                                         double* rec /* NREC doubles */, int& rec_pack) {
+                                         double* rec /* NREC doubles */, int& rec_pack, const GridP* g = nullptr,
+                                         const KeySink* ks = nullptr) {
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW;
   double pos[3] = {0, 0, 0}, px[3] = {0, 0, 0}, ux, uy, uz;
@@ -346,12 +350,23 @@ __device__ __forceinline__ bool push_one(const PushP& p, const PArr& a, long lon
     delta[0] = ux * root; delta[1] = uy * root;
     part_vz = uz * C0 * igamma;
   }
+  double posn[3] = {0, 0, 0}, momn[3] = {p.part_mc * ux, p.part_mc * uy, p.part_mc * uz};
 #pragma unroll
   for (int d = 0; d < ND; ++d) {
     px[d] = px[d] + delta[d];
-    a.x[d][ip] = px[d] + p.gml[d];
+    posn[d] = px[d] + p.gml[d];
   }
-  a.m[0][ip] = p.part_mc * ux; a.m[1][ip] = p.part_mc * uy; a.m[2][ip] = p.part_mc * uz;
+  if (ks != nullptr && ks->on) {
+    uint32_t k = ks->nbucket - 1;
+    const int ch = bc_and_key<ND, SHAPE>(*g, p, ks->bc, posn, momn, k);
+    if (ch < 0) k = ks->nbucket - 1;
+    ks->key[ip] = ch < 0 ? KEY_INVALID : k;
+    const unsigned peers = __match_any_sync(__activemask(), k);
+    if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(ks->count + k, (uint32_t)__popc(peers));
+  }
+#pragma unroll
+  for (int d = 0; d < ND; ++d) a.x[d][ip] = posn[d];
+  a.m[0][ip] = momn[0]; a.m[1][ip] = momn[1]; a.m[2][ip] = momn[2];
   if (p.zero_current) return false;
 
   int pack = 0;
@@ -696,7 +711,8 @@ constexpr int MCAPB = 4096;      // overflow work items per tile in the deposit 
 template <int ND, int SHAPE>
 __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F, PushP p, PArr a,
                                                               const uint32_t* __restrict__ cell_start, long long tile0,
-                                                              double* __restrict__ scratch, unsigned long long* counters) {
+                                                              double* __restrict__ scratch, unsigned long long* counters,
+                                                              KeySink ks) {
   using T = TL<ND, SHAPE>;
   constexpr int SFM = T::SFM;
   extern __shared__ double smem[];
@@ -730,7 +746,7 @@ __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F
     double rec[8];
     int pack;
     rec[6] = 0.0;
-    if (!push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, counters, rec, pack)) continue;
+    if (!push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, counters, rec, pack, &g, &ks)) continue;
     rec[7] = __longlong_as_double((long long)pack);
     double2* out = reinterpret_cast<double2*>(scratch + (size_t)(q - base) * 8);
 #pragma unroll
@@ -874,6 +890,13 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, SUB) k_deposit_split
 
 }  // namespace
 
+size_t keysink_size() { return sizeof(KeySink); }
+void keysink_fill(void* dst, const BcP3& bc, uint32_t* key, uint32_t* count, uint32_t nbucket) {
+  KeySink ks;
+  ks.on = 1; ks.bc = bc; ks.key = key; ks.count = count; ks.nbucket = nbucket;
+  *(KeySink*)dst = ks;
+}
+
 int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled) {
   *handled = false;
   if (c->ndims < 2 || c->shape == SHAPE_BSPLINE3 || !sp.sorted) return 0;
@@ -897,8 +920,10 @@ int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool
 }
 
 
-int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled) {
+int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled, const void* keysink) {
   *handled = false;
+  KeySink ks;
+  if (keysink) ks = *(const KeySink*)keysink; else ks.on = 0;
   if (c->ndims < 2 || c->shape == SHAPE_BSPLINE3 || !sp.sorted || !sp.h_tile_start) return 0;
   PArr a;
   for (int d = 0; d < 3; ++d) { a.x[d] = sp.a[d]; a.m[d] = sp.a[3 + d]; }
@@ -932,7 +957,7 @@ int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
       { ScopedPhase pa(c, "push_A");                                                                       \
-        ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, sp.cell_start, t0, c->rec_scratch, c->d_counters); } \
+        ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks); } \
       if (!p.zero_current) { ScopedPhase pb(c, "push_B");                                                  \
         kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch); }    \
     }
