@@ -296,10 +296,20 @@ struct PArr { double* x[3]; double* m[3]; const double* w; };
 // stores and produces the next sort key + key histogram, saving the sort's own pass
 struct KeySink { int on; BcP3 bc; uint32_t* key; uint32_t* count; uint32_t nbucket; };
 
+template <int ND>
+__device__ __forceinline__ void load_particle(const PArr& a, long long ip, double* in) {
+#pragma unroll
+  for (int d = 0; d < ND; ++d) in[d] = a.x[d][ip];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) in[3 + d] = a.m[d][ip];
+  in[6] = a.w[ip];
+}
+
 // phase 1 for one particle: particles.F90:219-452 (gather stage, Boris, drift, store,
 // extra half drift); leaves the deposit inputs in the record arrays
 template <int ND, int SHAPE>
-__device__ __forceinline__ bool push_one(const PushP& p, const PArr& a, long long ip, const int* c0,
+__device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos[3], mom[3], weight */, const PArr& a,
+                                         long long ip, const int* c0,
                                          const double* __restrict__ sF, unsigned long long* counters,
                                          double* rec /* NREC doubles */, int& rec_pack, const GridP* g = nullptr,
                                          const KeySink* ks = nullptr) {
@@ -307,9 +317,9 @@ __device__ __forceinline__ bool push_one(const PushP& p, const PArr& a, long lon
   constexpr int NW = T::NW;
   double pos[3] = {0, 0, 0}, px[3] = {0, 0, 0}, ux, uy, uz;
 #pragma unroll
-  for (int d = 0; d < ND; ++d) pos[d] = a.x[d][ip];
-  const double part_weight = a.w[ip];
-  half_drift<ND>(p, pos, a.m[0][ip], a.m[1][ip], a.m[2][ip], px, ux, uy, uz);
+  for (int d = 0; d < ND; ++d) pos[d] = in[d];
+  const double part_weight = in[6];
+  half_drift<ND>(p, pos, in[3], in[4], in[5], px, ux, uy, uz);
   int cell1[3] = {1, 1, 1}, l1[3] = {0, 0, 0}, l2[3] = {0, 0, 0};
   double f1[3] = {0, 0, 0};
   double wg[3][NW], wh[3][NW];
@@ -607,7 +617,9 @@ __global__ void __launch_bounds__(NT, EB_MINB) k_push_tiled(GridP g, FieldP F, P
       for (uint32_t q = sb + tid; q < se; q += NT) {
         double rec[NREC];
         int pack;
-        if (!push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, counters, rec, pack)) continue;
+        double in[7];
+        load_particle<ND>(a, (long long)q, in);
+        if (!push_one<ND, SHAPE>(p, in, a, (long long)q, c0, sF, counters, rec, pack)) continue;
         const int r = (int)(q - sb), rs = swz(r);
 #pragma unroll
         for (int k = 0; k < 2 * ND + (ND == 2 ? 2 : 1); ++k) sR[k * RPAD + rs] = rec[k];
@@ -733,24 +745,62 @@ __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F
     c0[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) : 1;
     org[d] = d < ND ? c0[d] + SFM - 1 : 1;
   }
-  for (int i = tid; i < 6 * T::FN; i += NTA) {
-    const int comp = i / T::FN, r = i - comp * T::FN;
-    const int fx = r % T::FX, fy = (r / T::FX) % T::FY, fz = r / (T::FX * T::FY);
-    const int X = org[0] + fx, Y = org[1] + fy, Z = org[2] + fz;
-    const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
-                    Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
-    sF[i] = in ? __ldg(F.f[comp] + g.idx(X, Y, Z)) : 0.0;
+  for (int i0 = 0; i0 < 6 * T::FN; i0 += 4 * NTA) {
+    double v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * NTA + tid;
+      v[u] = 0.0;
+      if (i < 6 * T::FN) {
+        const int comp = i / T::FN, r = i - comp * T::FN;
+        const int fx = r % T::FX, fy = (r / T::FX) % T::FY, fz = r / (T::FX * T::FY);
+        const int X = org[0] + fx, Y = org[1] + fy, Z = org[2] + fz;
+        const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
+                        Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
+        if (in) v[u] = __ldg(F.f[comp] + g.idx(X, Y, Z));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * NTA + tid;
+      if (i < 6 * T::FN) sF[i] = v[u];
+    }
   }
   __syncthreads();
-  for (uint32_t q = pb + tid; q < pe; q += NTA) {
-    double rec[8];
-    int pack;
-    rec[6] = 0.0;
-    if (!push_one<ND, SHAPE>(p, a, (long long)q, c0, sF, counters, rec, pack, &g, &ks)) continue;
-    rec[7] = __longlong_as_double((long long)pack);
-    double2* out = reinterpret_cast<double2*>(scratch + (size_t)(q - base) * 8);
+  // warp-uniform loop over the tile's particles; the next particle is in flight while the current
+  // one is pushed.  The 64 B records of a warp are transposed through shared memory (16 B units,
+  // XOR-swizzled) so that the warp writes its 2 KB block of the scratch with full-line stores.
+  const int lane = tid & 31, warp = tid >> 5;
+  double2* stage = reinterpret_cast<double2*>(smem + 6 * T::FN) + warp * 128;
+  double nxt[7];
+  uint32_t q0 = pb + warp * 32;
+  if (q0 + lane < pe) load_particle<ND>(a, (long long)(q0 + lane), nxt);
+  for (; q0 < pe; q0 += NTA) {
+    const uint32_t q = q0 + lane;
+    const bool act = q < pe;
+    double in[7];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) out[k] = make_double2(rec[2 * k], rec[2 * k + 1]);
+    for (int k = 0; k < 7; ++k) in[k] = nxt[k];
+    if (q + NTA < pe) load_particle<ND>(a, (long long)(q + NTA), nxt);
+    if (act) {
+      double rec[8];
+      int pack;
+      rec[6] = 0.0;
+      push_one<ND, SHAPE>(p, in, a, (long long)q, c0, sF, counters, rec, pack, &g, &ks);
+      rec[7] = __longlong_as_double((long long)pack);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) stage[lane * 4 + (k ^ ((lane >> 1) & 3))] = make_double2(rec[2 * k], rec[2 * k + 1]);
+    }
+    if (p.zero_current) continue;
+    __syncwarp();
+    double2* out = reinterpret_cast<double2*>(scratch + (size_t)(q0 - base) * 8);
+    const uint32_t nrec = pe - q0 < 32u ? pe - q0 : 32u;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int u = j * 32 + lane, r = u >> 2;
+      if ((uint32_t)r < nrec) out[u] = stage[r * 4 + ((u & 3) ^ ((r >> 1) & 3))];
+    }
+    __syncwarp();
   }
 }
 
@@ -952,7 +1002,7 @@ int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool
     if (c->ndims == ND && c->shape == SH) {                                                                \
       auto ka = k_push_split<ND, SH>;                                                                      \
       auto kb = k_deposit_split<ND, SH>;                                                                   \
-      const size_t sa = sizeof(double) * 6 * TL<ND, SH>::FN;                                               \
+      const size_t sa = sizeof(double) * (6 * TL<ND, SH>::FN + (NTA / 32) * 256);                                               \
       const size_t sb = sizeof(double) * 3 * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4);  /* >= sub-tile need */ \
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
