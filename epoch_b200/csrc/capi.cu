@@ -370,9 +370,9 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
   const std::string k(key), v(value);
   if (k == "capture_charge_reference") { NEED_GRID(c); NEED_DT(c); double a, b; return charge_residual(c, &a, &b, true); }
   if (k == "push_kernel") {
-    if (v == "auto") c->push_kernel = 0; else if (v == "baseline") c->push_kernel = 1; else if (v == "tiled") c->push_kernel = 2;
-    else if (v == "split") c->push_kernel = 3;
-    else return fail(c, EB200_E_ARG, "push_kernel: auto|baseline|tiled|split");
+    if (v == "auto") c->push_kernel = 0; else if (v == "baseline") c->push_kernel = 1;
+    else if (v == "tiled" || v == "split") c->push_kernel = 3;
+    else return fail(c, EB200_E_ARG, "push_kernel: auto|baseline|tiled");
     return 0;
   }
   if (k == "fuse_keys") { c->fuse_keys = atoi(value) != 0; return 0; }

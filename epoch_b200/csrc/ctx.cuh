@@ -132,7 +132,7 @@ struct eb200_ctx {
   long long rec_scratch_cap = 0;              // ... capacity in particles
   long long rec_scratch_max = 1LL << 27;      // option deposit_scratch (particles per slab, 64 B each)
   // options
-  int push_kernel = 0;          // 0 auto, 1 baseline, 2 tiled (fused), 3 split (push + deposit kernels)
+  int push_kernel = 0;          // 0 auto, 1 baseline (global atomics), 3 tiled (push + deposit kernels)
   int deterministic = 0;
   int fuse_keys = 1;            // option fuse_keys: push kernel emits the next sort keys (single rank)
   int sort_every = 1;

@@ -10,7 +10,6 @@
 namespace eb {
 
 int32_t launch_push_baseline(eb200_ctx* c, const SpeciesD& sp, const PushP& p);   // push_baseline.cu
-int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled);  // push_tiled.cu
 int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled, const void* keysink);  // push_tiled.cu
 size_t keysink_size();
 void keysink_fill(void* dst, const BcP3& bc, uint32_t* key, uint32_t* count, uint32_t nbucket);
@@ -531,7 +530,6 @@ int32_t push_particles(eb200_ctx* c) {
         EB_TRY(launch_push_split(c, sp, p, &handled, ks));
         fused_keys = handled && ks != nullptr;
       }
-      if (!handled && c->push_kernel != 1) EB_TRY(launch_push_tiled(c, sp, p, &handled));
       if (!handled) EB_TRY(launch_push_baseline(c, sp, p));
     }
     if (fused_keys) { EB_TRY(sort_species(c, sp, sp.n, true)); done[is] = 1; }

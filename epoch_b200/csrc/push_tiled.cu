@@ -2,27 +2,24 @@
 // and triangle shapes).  Replaces the per-particle loop of push_particles
 // (epoch3d/src/particles.F90:214-608, epoch2d :199-540).
 //
-// One CTA owns one tile of cells (3D 8x8x4, 2D 16x16; ctx.cuh tile_dim) whose
-// particles are contiguous because the sort key is tile-major.  Per tile:
-//   * E,B of the tile + gather halo are staged in shared memory once; J of the
-//     tile + deposit halo is accumulated in shared memory and flushed to HBM once
+// The particles are sorted by a tile-major cell key (3D tiles 8x8x4 cells, 2D 16x16;
+// ctx.cuh tile_dim), so a tile's particles are contiguous.  Two kernels run over the
+// tiles of a slab, passing a 64 B deposit record per particle through a global scratch:
+//   k_push_split, CTA per tile, thread per particle: E,B of the tile + gather halo are
+//     staged in shared memory once; half drift, gather (same-cell lanes -> broadcast
+//     shared loads), Boris, drift, store, particle BCs + next sort key (single rank);
+//     the record (fractions at t+dt/2 and t+3dt/2, cell shift, weight[, v_z]) goes to
+//     the scratch through a warp transpose (full-line stores).
+//   k_deposit_split, CTA per half tile, thread per CELL: walks the records of its own
+//     cell (cp.async ring) and accumulates all three current components on the cell's
+//     NW^ND stencil box in REGISTERS -- no atomics, no shuffles: the reduction over the
+//     particles of a cell is a serial sum in one thread.  A particle that changed cell
+//     (|dcell| = 1 on some axis) reaches one layer beyond the box; those few values
+//     are added afterwards by work items (thread per (particle, moving axis)) with
+//     shared-memory atomics.  The register boxes are added to the shared J tile with
+//     plain read-modify-writes, one stencil offset per barrier step (all threads apply
+//     the same offset to distinct cells), and the tile is flushed to HBM once
 //     (RED.ADD.F64 -- neighbouring tiles overlap in their halos).
-//   * The tile is walked in chunks of G = 64 consecutive cells.  Each chunk's
-//     particles are processed in sub-ranges of <= RCAP particles, in two phases:
-//       phase 1, thread per particle (coalesced, same-cell lanes -> broadcast
-//         shared loads): half drift, gather, Boris, drift, store; then the deposit
-//         inputs are left in shared memory as a compact record (fractions at
-//         t+dt/2 and t+3dt/2, cell shift, weight[, v_z]);
-//       phase 2, thread per (cell, current component): walks the records of its own
-//         cell and accumulates the component's contributions on the cell's
-//         NW^ND stencil box in REGISTERS -- no atomics, no shuffles: the reduction
-//         over the particles of a cell is a serial sum in one thread.
-//     A particle that changed cell (|dcell| = 1 on some axis) reaches one layer
-//     beyond the box; those few values are added by phase 2b, one warp per such
-//     particle, lane per (component, cell), with shared-memory atomics.
-//   * After the chunk the register boxes are added to the shared J tile with plain
-//     read-modify-writes: lanes of a warp are distinct cells of one component, and
-//     the two warps of a component take turns.
 // The Esirkepov sums are evaluated in factored form,
 //   Jx(i,j,k) = -fjx * cumsum_i(hx) * (gy(j) zf1(k) + hy(j) zf2(k)),   (cyclic)
 // which is the reference's running sum (particles.F90:522-563) with the common
@@ -33,19 +30,9 @@ namespace eb {
 
 namespace {
 
-#ifndef EB_MINB
-#define EB_MINB 2
-#endif
 #ifndef EB_MINB_A
 #define EB_MINB_A 2
 #endif
-constexpr int NT = 192;          // threads per CTA = 64 cells x 3 components in phase 2
-constexpr int G = 32;            // cells per chunk: 32 cells x 2 halves x 3 components = NT phase-2 threads
-constexpr int RCAP = 512;        // particles per sub-range (record capacity)
-constexpr int RPAD = RCAP + RCAP / 16 + 1;   // swizzled record index r + (r >> 4)
-constexpr int NREC = 7;          // doubles per record
-constexpr int MCAP = 1024;       // overflow work items per sub-range (more are deposited inline)
-
 template <int ND, int SHAPE>
 struct TL {
   static constexpr int NW = Sh<SHAPE>::NW, SFM = Sh<SHAPE>::SFMIN;
@@ -61,18 +48,10 @@ struct TL {
   // left out -- the sum has returned to zero there (rounding residue) unless the particle moved
   // up a cell, and then the slot is deposited by a work item (mover_item3, m == A, dcell = +1)
   static constexpr int NACC = ND == 3 ? (NW - 1) * NW * NW : NW * NW;
-  static constexpr size_t SMEM = sizeof(double) * (6 * FN + 3 * JN + NREC * RPAD) + sizeof(int) * (RPAD + MCAP + G + 1 + 3);
 };
-
-__device__ __forceinline__ int swz(int r) { return r + (r >> 4); }
 
 // deposit record: doubles f1[ND], f3[ND], weight[, v_z] and an int = packed cell shift
-// (2 bits per axis, value dcell + 1) | tile-local cell << 8.  Two storages:
-struct RecS {            // shared memory, structure of arrays (fused kernel)
-  const double* sR; const int* sD; int rs;
-  __device__ __forceinline__ double get(int k) const { return sR[k * RPAD + rs]; }
-  __device__ __forceinline__ int pack() const { return sD[rs]; }
-};
+// (2 bits per axis, value dcell + 1) | tile-local cell << 8.  Two views:
 struct RecR {            // 8 doubles already in registers (static indices only)
   const double* r;
   __device__ __forceinline__ double get(int k) const { return r[k]; }
@@ -162,36 +141,6 @@ __device__ __forceinline__ void box3(double* acc, const double (*g)[NW], const d
     }
 }
 
-// add the register box of component A to the shared J tile with plain read-modify-
-// writes (even lanes; the odd lane of each pair has been folded in by shuffle).  The
-// writing lanes of a warp are 16 distinct cells of ONE z-plane of the tile, so
-// for a fixed (dx, dy) the NW updates along z never collide between lanes; updates
-// with different (dx, dy) can (lane A's cell+1 is lane B's cell), so those steps are
-// ordered with __syncwarp() -- which also keeps the compiler from hoisting the
-// loads of a later step above the stores of an earlier one.
-template <int A, int NW, int JX, int JY>
-__device__ __forceinline__ void flush3(double* sj, const double* acc, const int* l, bool writer, int bar_id) {
-  constexpr int P = (A + 1) % 3, Q = (A + 2) % 3;
-  double* b = sj + (l[0] + 1) + (l[1] + 1) * JX + (l[2] + 1) * JX * JY;
-#pragma unroll
-  for (int dy = 0; dy < NW; ++dy) {
-#pragma unroll
-    for (int dx = 0; dx < NW; ++dx) {
-      if (writer) {
-#pragma unroll
-        for (int dz = 0; dz < NW; ++dz) {
-          const int o[3] = {dx, dy, dz};
-          if (o[A] < NW - 1) b[dx + dy * JX + dz * JX * JY] += acc[(o[Q] * NW + o[P]) * (NW - 1) + o[A]];
-        }
-      }
-      __syncwarp();
-    }
-    // the two warps of a component hold disjoint cell rows: at the same dy they touch disjoint
-    // J rows, so they only have to stay in step
-    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(64) : "memory");
-  }
-}
-
 template <int N>
 __device__ __forceinline__ double pick(const double* a, int t) {
   double r = a[0];
@@ -204,85 +153,100 @@ __device__ __forceinline__ double pick(const double* a, int t) {
 
 namespace {
 
-// One work item of a 3D particle that changed cell: current component A, moving
-// axis m.  The window cells not covered by the register boxes are split, per
-// component, by the first such axis in the order (A, P, Q):
+// One work item of a 3D particle that changed cell along axis m: everything the particle
+// deposits outside the register boxes because of that axis.  The window cells not covered
+// by the boxes are split, per current component A (P = A+1, Q = A+2 cyclic), by the first
+// such axis in the order (A, P, Q):
 //   m == A: dcell = -1: cells one below the box along A, any (u, v) of the P x Q window;
 //           dcell = +1: the last box slot along A (left out of the register boxes), (u, v)
 //           inside the box; one above the box the running sum has returned to zero;
 //   m == P: u beyond the box, a inside it, any v of the Q window;
 //   m == Q: v beyond the box, a and u inside it.
-// Thread per item; the values go to the shared J tile with atomics.
+// With the axes rotated to (a0, a1, a2) = (m, m+1, m+2) the item is role "A" for component
+// a0, role "P" for component a2 and role "Q" for component a1, so the weights of the three
+// axes are evaluated once.  The values go to the shared J tile with atomics.
 template <int SHAPE, class R>
-__device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double* __restrict__ sJ, int A, int m,
+__device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double* __restrict__ sJ, int m,
                                             int jn = TL<3, SHAPE>::JN, int sub_off = 0) {
   using T = TL<3, SHAPE>;
   constexpr int NW = T::NW, NS = NW + 2;
-  const int P = A == 2 ? 0 : A + 1, Q = P == 2 ? 0 : P + 1;
+  const int a0 = m, a1 = m == 2 ? 0 : m + 1, a2 = a1 == 2 ? 0 : a1 + 1;
   const int pk = rec.pack();
   const int lc = pk >> 8;
   const int l0 = lc % T::TX, l1 = (lc / T::TX) % T::TY, l2 = lc / (T::TX * T::TY);
-  const int dcA = ((pk >> (2 * A)) & 3) - 1, dcP = ((pk >> (2 * P)) & 3) - 1, dcQ = ((pk >> (2 * Q)) & 3) - 1;
-  double gA[NW], hA[NW], gP[NW], hP[NW], gQ[NW], hQ[NW], loA, hiA, loP, hiP, loQ, hiQ;
-  axis_weights<SHAPE>(rec.get(A), rec.get(3 + A), dcA, gA, hA, loA, hiA);
-  axis_weights<SHAPE>(rec.get(P), rec.get(3 + P), dcP, gP, hP, loP, hiP);
-  axis_weights<SHAPE>(rec.get(Q), rec.get(3 + Q), dcQ, gQ, hQ, loQ, hiQ);
-  const double fj = -(p.fc[A] * rec.get(6) * p.q);
+  const int dc0 = ((pk >> (2 * a0)) & 3) - 1, dc1 = ((pk >> (2 * a1)) & 3) - 1, dc2 = ((pk >> (2 * a2)) & 3) - 1;
+  double g0[NW], h0[NW], g1[NW], h1[NW], g2[NW], h2[NW], lo0, hi0, lo1, hi1, lo2, hi2;
+  axis_weights<SHAPE>(rec.get(a0), rec.get(3 + a0), dc0, g0, h0, lo0, hi0);
+  axis_weights<SHAPE>(rec.get(a1), rec.get(3 + a1), dc1, g1, h1, lo1, hi1);
+  axis_weights<SHAPE>(rec.get(a2), rec.get(3 + a2), dc2, g2, h2, lo2, hi2);
+  const double wq = rec.get(6) * p.q;
   const double third = 1.0 / 3.0;
-  const int stA = A == 0 ? 1 : (A == 1 ? T::JX : T::JX * T::JY);
-  const int stP = P == 0 ? 1 : (P == 1 ? T::JX : T::JX * T::JY);
-  const int stQ = Q == 0 ? 1 : (Q == 1 ? T::JX : T::JX * T::JY);
-  double* base = sJ + A * jn + l0 + l1 * T::JX + (l2 - sub_off) * T::JX * T::JY;   // window index t = 0 <-> region index l
-  // full-window arrays along Q (t = 0 .. NW+1)
-  double q1[NS], q2[NS];
-  q1[0] = 0.5 * loQ; q2[0] = third * loQ; q1[NS - 1] = 0.5 * hiQ; q2[NS - 1] = third * hiQ;
+  const int s0 = a0 == 0 ? 1 : (a0 == 1 ? T::JX : T::JX * T::JY);
+  const int s1 = a1 == 0 ? 1 : (a1 == 1 ? T::JX : T::JX * T::JY);
+  const int s2 = a2 == 0 ? 1 : (a2 == 1 ? T::JX : T::JX * T::JY);
+  double* cell = sJ + l0 + l1 * T::JX + (l2 - sub_off) * T::JX * T::JY;   // window index t = 0 <-> region index l
+  const double ov0 = dc0 < 0 ? lo0 : hi0;          // the weight of axis m in its slot beyond the box
+  const int t0 = dc0 < 0 ? 0 : NW + 1;             // ... and that slot's window index
+  {
+    // component a0, role A: dcell = -1: slot t = 0, running sum = h_lo, any (u, v) of the window;
+    // dcell = +1: the last box slot t = NW, running sum = -h_hi, (u, v) inside the box
+    const double fj = -(p.fc[a0] * wq);
+    const double cov = dc0 < 0 ? fj * lo0 : -(fj * hi0);
+    const int ta = dc0 < 0 ? 0 : NW;
+    const int lo = dc0 < 0 ? 0 : 1, hi = dc0 < 0 ? NS : NS - 1;
+    double g5[NS], h5[NS], q1[NS], q2[NS];
+    g5[0] = 0.0; g5[NS - 1] = 0.0; h5[0] = lo1; h5[NS - 1] = hi1;
+    q1[0] = 0.5 * lo2; q2[0] = third * lo2; q1[NS - 1] = 0.5 * hi2; q2[NS - 1] = third * hi2;
 #pragma unroll
-  for (int v = 0; v < NW; ++v) { q1[v + 1] = gQ[v] + 0.5 * hQ[v]; q2[v + 1] = third * hQ[v] + 0.5 * gQ[v]; }
-  if (m == A) {
-    // dcell = -1: the slot below the box (t_A = 0), running sum = h_lo, any (u, v) of the window;
-    // dcell = +1: the last box slot (t_A = NW), which the register boxes leave out, running sum
-    //             = -h_hi, (u, v) inside the box (u or v beyond it belongs to the m == P / Q items)
-    const double cov = dcA < 0 ? fj * loA : -(fj * hiA);
-    const int ta = dcA < 0 ? 0 : NW;
-    const int lo = dcA < 0 ? 0 : 1, hi = dcA < 0 ? NS : NS - 1;
-    double g5[NS], h5[NS];
-    g5[0] = 0.0; g5[NS - 1] = 0.0; h5[0] = loP; h5[NS - 1] = hiP;
+    for (int u = 0; u < NW; ++u) { g5[u + 1] = g1[u]; h5[u + 1] = h1[u]; }
 #pragma unroll
-    for (int u = 0; u < NW; ++u) { g5[u + 1] = gP[u]; h5[u + 1] = hP[u]; }
+    for (int v = 0; v < NW; ++v) { q1[v + 1] = g2[v] + 0.5 * h2[v]; q2[v + 1] = third * h2[v] + 0.5 * g2[v]; }
+    double* base = cell + a0 * jn + ta * s0;
 #pragma unroll
     for (int v = 0; v < NS; ++v)
 #pragma unroll
       for (int u = 0; u < NS; ++u) {
         // window membership first: the slots beyond the box exist only where P / Q moved too
-        const bool in = u >= lo && u < hi && v >= lo && v < hi && (u != 0 || dcP < 0) && (u != NS - 1 || dcP > 0) &&
-                        (v != 0 || dcQ < 0) && (v != NS - 1 || dcQ > 0);
-        if (in) atomicAdd(base + ta * stA + u * stP + v * stQ, cov * (g5[u] * q1[v] + h5[u] * q2[v]));
+        const bool in = u >= lo && u < hi && v >= lo && v < hi && (u != 0 || dc1 < 0) && (u != NS - 1 || dc1 > 0) &&
+                        (v != 0 || dc2 < 0) && (v != NS - 1 || dc2 > 0);
+        if (in) atomicAdd(base + u * s1 + v * s2, cov * (g5[u] * q1[v] + h5[u] * q2[v]));
       }
-  } else {
+  }
+  {
+    // component a2 (P = a0 = m, Q = a1), role P: u in the slot beyond the box (g = 0 there), a inside
+    // the box, any v of the Q window
+    const double fj = -(p.fc[a2] * wq);
     double ca[NW];
-    double c = loA;
+    double c = lo2;
 #pragma unroll
-    for (int i = 0; i < NW; ++i) { c += hA[i]; ca[i] = fj * c; }
-    if (m == P) {
-      const int tu = dcP < 0 ? 0 : NW + 1;
-      const double hov = dcP < 0 ? loP : hiP;
+    for (int i = 0; i < NW; ++i) { c += h2[i]; ca[i] = fj * c * ov0; }
+    double* base = cell + a2 * jn + t0 * s0 + s2;
 #pragma unroll
-      for (int v = 0; v < NS; ++v) {
-        const double w = hov * q2[v];
-        if ((v != 0 || dcQ < 0) && (v != NS - 1 || dcQ > 0)) {
+    double q2[NS];
+    q2[0] = third * lo1; q2[NS - 1] = third * hi1;
 #pragma unroll
-          for (int i = 0; i < NW; ++i) atomicAdd(base + (1 + i) * stA + tu * stP + v * stQ, ca[i] * w);
-        }
+    for (int v = 0; v < NW; ++v) q2[v + 1] = third * h1[v] + 0.5 * g1[v];
+#pragma unroll
+    for (int v = 0; v < NS; ++v) {
+      if ((v != 0 || dc1 < 0) && (v != NS - 1 || dc1 > 0)) {
+#pragma unroll
+        for (int i = 0; i < NW; ++i) atomicAdd(base + i * s2 + v * s1, ca[i] * q2[v]);
       }
-    } else {
-      const int tv = dcQ < 0 ? 0 : NW + 1;
-      const double hq = dcQ < 0 ? loQ : hiQ;
+    }
+  }
+  {
+    // component a1 (P = a2, Q = a0 = m), role Q: v in the slot beyond the box, a and u inside it
+    const double fj = -(p.fc[a1] * wq);
+    double ca[NW];
+    double c = lo1;
 #pragma unroll
-      for (int u = 0; u < NW; ++u) {
-        const double w = gP[u] * (0.5 * hq) + hP[u] * (third * hq);
+    for (int i = 0; i < NW; ++i) { c += h1[i]; ca[i] = fj * c; }
+    double* base = cell + a1 * jn + t0 * s0 + s1 + s2;
 #pragma unroll
-        for (int i = 0; i < NW; ++i) atomicAdd(base + (1 + i) * stA + (1 + u) * stP + tv * stQ, ca[i] * w);
-      }
+    for (int u = 0; u < NW; ++u) {
+      const double w = g2[u] * (0.5 * ov0) + h2[u] * (third * ov0);
+#pragma unroll
+      for (int i = 0; i < NW; ++i) atomicAdd(base + i * s1 + u * s2, ca[i] * w);
     }
   }
 }
@@ -536,175 +500,15 @@ __device__ __forceinline__ void deposit_box(const PushP& p, const R& rec, int co
   }
 }
 
-// work items of a 3D particle that changed cell: one per (component A, moving axis m);
-// code = record | A << 16 | m << 18
+// work items of a 3D particle that changed cell: one per moving axis
 __device__ __forceinline__ int mover_item_count(int pack) {
   int n = 0;
 #pragma unroll
-  for (int m = 0; m < 3; ++m) n += ((pack >> (2 * m)) & 3) != 1 ? 3 : 0;
+  for (int m = 0; m < 3; ++m) n += ((pack >> (2 * m)) & 3) != 1 ? 1 : 0;
   return n;
 }
 
 }  // namespace
-
-namespace {
-
-template <int ND, int SHAPE>
-__global__ void __launch_bounds__(NT, EB_MINB) k_push_tiled(GridP g, FieldP F, PushP p, PArr a,
-                                                      const uint32_t* __restrict__ cell_start,
-                                                      unsigned long long* counters) {
-  using T = TL<ND, SHAPE>;
-  constexpr int NW = T::NW, SFM = T::SFM;
-  extern __shared__ double smem[];
-  double* sF = smem;                       // [6][FN]   E,B of the tile + gather halo
-  double* sJ = sF + 6 * T::FN;             // [3][JN]   J of the tile + deposit halo
-  double* sR = sJ + 3 * T::JN;             // [NREC][RPAD] deposit records of the current sub-range
-  int* sD = (int*)(sR + NREC * RPAD);      // [RPAD]    cell shift pack | tile-local cell << 8
-  int* sM = sD + RPAD;                     // [MCAP]    overflow work items of particles that changed cell
-  uint32_t* sStart = (uint32_t*)(sM + MCAP);   // [G+1] particle offsets of the chunk's cells
-  int* sCnt = (int*)(sStart + G + 1);
-
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const long long tile = blockIdx.x;
-  const long long kbase = tile * T::CPT;
-  const uint32_t pb = cell_start[kbase], pe = cell_start[kbase + T::CPT];
-  if (pb == pe) return;
-  int tc[3];
-  tc[0] = (int)(tile % g.ntile[0]);
-  tc[1] = (int)((tile / g.ntile[0]) % g.ntile[1]);
-  tc[2] = (int)(tile / ((long long)g.ntile[0] * g.ntile[1]));
-  int c0[3], org[3];
-#pragma unroll
-  for (int d = 0; d < 3; ++d) {
-    c0[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) : 1;   // Fortran coordinate of the tile's first cell
-    org[d] = d < ND ? c0[d] + SFM - 1 : 1;                     // ... of the first staged cell
-  }
-  // stage E,B (zero outside the allocated array)
-  for (int i = tid; i < 6 * T::FN; i += NT) {
-    const int comp = i / T::FN, r = i - comp * T::FN;
-    const int fx = r % T::FX, fy = (r / T::FX) % T::FY, fz = r / (T::FX * T::FY);
-    const int X = org[0] + fx, Y = org[1] + fy, Z = org[2] + fz;
-    const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
-                    Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
-    sF[i] = in ? __ldg(F.f[comp] + g.idx(X, Y, Z)) : 0.0;
-  }
-  for (int i = tid; i < 3 * T::JN; i += NT) sJ[i] = 0.0;
-
-  // phase 2 identity: component, cell of the chunk and which half of the cell's particles;
-  // the two lanes of a pair share a cell, the two warps of a component share a chunk
-  const int comp = warp >> 1;
-  const int ci = ((warp & 1) << 4) + (lane >> 1);
-  const int half = lane & 1;
-  double acc[T::NACC];
-
-  for (int ch = 0; ch < T::CPT / G; ++ch) {
-    __syncthreads();
-    if (tid <= G) sStart[tid] = cell_start[kbase + ch * G + tid];
-    __syncthreads();
-    const uint32_t cb = sStart[0], ce = sStart[G];
-    if (cb == ce) continue;
-#pragma unroll
-    for (int i = 0; i < T::NACC; ++i) acc[i] = 0.0;
-    const uint32_t my_b = sStart[ci], my_e = sStart[ci + 1];
-    const int lc = ch * G + ci;
-    const int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
-
-    for (uint32_t sb = cb; sb < ce; sb += RCAP) {
-      const uint32_t se = ce - sb > (uint32_t)RCAP ? sb + RCAP : ce;
-      if (tid == 0) sCnt[0] = 0;
-      __syncthreads();
-      // ---- phase 1: thread per particle ----
-      for (uint32_t q = sb + tid; q < se; q += NT) {
-        double rec[NREC];
-        int pack;
-        double in[7];
-        load_particle<ND>(a, (long long)q, in);
-        if (!push_one<ND, SHAPE>(p, in, a, (long long)q, c0, sF, counters, rec, pack)) continue;
-        const int r = (int)(q - sb), rs = swz(r);
-#pragma unroll
-        for (int k = 0; k < 2 * ND + (ND == 2 ? 2 : 1); ++k) sR[k * RPAD + rs] = rec[k];
-        sD[rs] = pack;
-        if ((pack & 0xff) == (ND == 3 ? 0x15 : 0x5)) continue;     // all dcell == 0
-        if (ND == 2) {
-          const int slot = atomicAdd(sCnt, 1);
-          if (slot < MCAP) sM[slot] = r;
-        } else {
-          int slot = atomicAdd(sCnt, mover_item_count(pack));
-#pragma unroll
-          for (int m = 0; m < 3; ++m) {
-            const int dc = ((pack >> (2 * m)) & 3) - 1;
-            if (dc == 0) continue;
-#pragma unroll
-            for (int A = 0; A < 3; ++A) {
-              if (slot < MCAP) sM[slot] = r | (A << 16) | (m << 18);
-              else mover_item3<SHAPE>(p, RecS{sR, sD, rs}, sJ, A, m);    // list full: deposit right away
-              ++slot;
-            }
-          }
-        }
-      }
-      __syncthreads();
-      if (!p.zero_current) {
-        // ---- phase 2: thread per (cell, component) over the cell's records ----
-        const uint32_t qb = my_b > sb ? my_b : sb, qe = my_e < se ? my_e : se;
-        for (uint32_t q = qb + half; q < qe; q += 2) {
-          deposit_box<ND, SHAPE, false>(p, RecS{sR, sD, swz((int)(q - sb))}, comp, acc);
-        }
-        // ---- phase 2b: particles that changed cell, warp per particle ----
-        const int nm = sCnt[0] < MCAP ? sCnt[0] : MCAP;
-        if (ND == 3) {
-          for (int m = tid; m < nm; m += NT) {
-            const int code = sM[m];
-            mover_item3<SHAPE>(p, RecS{sR, sD, swz(code & 0xffff)}, sJ, (code >> 16) & 3, (code >> 18) & 3);
-          }
-        } else {
-          for (int m = warp; m < nm; m += NT / 32) mover_overflow<ND, SHAPE>(p, RecS{sR, sD, swz(sM[m])}, sJ, lane);
-        }
-      }
-      __syncthreads();
-    }
-    if (!p.zero_current) {
-      // ---- phase 3: fold the odd lane of each pair into the even one, then register boxes ->
-      //      shared J tile, the two warps of a component in step ----
-#pragma unroll
-      for (int i = 0; i < T::NACC; ++i) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], 1);
-      double* sj = sJ + comp * T::JN;
-      if (ND == 3) {
-        if (comp == 0) flush3<0, NW, T::JX, T::JY>(sj, acc, l, half == 0, 1 + comp);
-        else if (comp == 1) flush3<1, NW, T::JX, T::JY>(sj, acc, l, half == 0, 1 + comp);
-        else flush3<2, NW, T::JX, T::JY>(sj, acc, l, half == 0, 1 + comp);
-      } else {
-        double* b = sj + (l[1] + 1) * T::JX + l[0] + 1;
-#pragma unroll
-        for (int j = 0; j < NW; ++j) {
-#pragma unroll
-          for (int i = 0; i < NW; ++i) {
-            if (half == 0) b[j * T::JX + i] += acc[j * NW + i];
-            __syncwarp();
-          }
-          asm volatile("bar.sync %0, %1;" ::"r"(1 + comp), "r"(64) : "memory");
-        }
-      }
-    }
-  }
-  __syncthreads();
-  // tile J -> HBM (neighbouring tiles overlap in the halo: RED.ADD.F64)
-  if (!p.zero_current) {
-    for (int i = tid; i < 3 * T::JN; i += NT) {
-      const double v = sJ[i];
-      if (v == 0.0) continue;
-      const int cj = i / T::JN, r = i - cj * T::JN;
-      const int jx = r % T::JX, jy = (r / T::JX) % T::JY, jz = r / (T::JX * T::JY);
-      const int X = org[0] + jx, Y = org[1] + jy, Z = org[2] + jz;
-      const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
-                      Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
-      if (in) atomicAdd(F.f[JX + cj] + g.idx(X, Y, Z), v);
-    }
-  }
-}
-
-}  // namespace
-
 
 // =====================================================================================
 // Split variant: push and deposit as two kernels over the same tiles, the deposit
@@ -718,7 +522,14 @@ __global__ void __launch_bounds__(NT, EB_MINB) k_push_tiled(GridP g, FieldP F, P
 namespace {
 
 constexpr int NTA = 256;         // push kernel threads
-constexpr int MCAPB = 4096;      // overflow work items per tile in the deposit kernel
+constexpr int MCAPB = 2048;      // overflow work items per sub-tile in the deposit kernel (more are deposited inline)
+#ifndef EB_MINB_B
+#define EB_MINB_B 2
+#endif
+#ifndef EB_RING
+#define EB_RING 3
+#endif
+constexpr int RING = EB_RING;    // record slots per thread of the deposit kernel's cp.async ring
 
 template <int ND, int SHAPE>
 __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F, PushP p, PArr a,
@@ -813,7 +624,7 @@ __device__ __forceinline__ void load_rec(double* r, const double* src) {
 }
 
 template <int ND, int SHAPE>
-__global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, SUB) k_deposit_split(GridP g, FieldP F, PushP p,
+__global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit_split(GridP g, FieldP F, PushP p,
                                                                                 const uint32_t* __restrict__ cell_start,
                                                                                 long long tile0, const double* __restrict__ scratch) {
   using T = TL<ND, SHAPE>;
@@ -824,8 +635,9 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, SUB) k_deposit_split
   constexpr int JNs = JXs * JYs * JZs;
   extern __shared__ double smem[];
   double* sJ = smem;                          // [3][JNs]
-  int* sM = (int*)(sJ + 3 * JNs);             // [2 * MCAPB] work items (record, A | m << 2)
+  int* sM = (int*)(sJ + 3 * JNs);             // [2 * MCAPB] work items (record, moving axis)
   int* sCnt = sM + 2 * MCAPB;
+  double2* ring = reinterpret_cast<double2*>(((uintptr_t)(sCnt + 4) + 15) & ~(uintptr_t)15);   // [RING][4][NTB] 16 B units
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const long long tile = tile0 + blockIdx.x / SUB;
   const int sub = blockIdx.x % SUB;
@@ -853,12 +665,33 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, SUB) k_deposit_split
   double acc[3 * NA];
 #pragma unroll
   for (int i = 0; i < 3 * NA; ++i) acc[i] = 0.0;
-  double cur[8], nx1[8];
-  if (my_b < my_e) load_rec(cur, scratch + (size_t)(my_b - base) * 8);
-  if (my_b + 1 < my_e) load_rec(nx1, scratch + (size_t)(my_b + 1 - base) * 8);
+  // the thread's records stream through a private shared-memory ring filled by cp.async
+  // (RING - 1 records in flight, none of them held in registers)
+  double cur[8];
+  const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(ring) + (uint32_t)tid * 16u;
+  auto issue = [&](uint32_t q, int slot) {
+    const double* src = scratch + (size_t)(q - base) * 8;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring0 + (uint32_t)((slot * 4 + k) * NTB) * 16u), "l"(src + 2 * k) : "memory");
+  };
+#pragma unroll
+  for (int s = 0; s < RING - 1; ++s) {
+    if (my_b + s < my_e) issue(my_b + s, s);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  int slot = 0;
   for (uint32_t q = my_b; q < my_e; ++q) {
-    double nxt[8];
-    if (q + 2 < my_e) load_rec(nxt, scratch + (size_t)(q + 2 - base) * 8);
+    asm volatile("cp.async.wait_group %0;" ::"n"(RING - 2) : "memory");
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const double2 v = ring[(slot * 4 + k) * NTB + tid];
+      cur[2 * k] = v.x; cur[2 * k + 1] = v.y;
+    }
+    // refill the slot that the previous iteration consumed
+    if (q + (RING - 1) < my_e) issue(q + (RING - 1), slot == 0 ? RING - 1 : slot - 1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    slot = slot == RING - 1 ? 0 : slot + 1;
     deposit_box<ND, SHAPE, true>(p, RecR{cur}, 0, acc);
     const int pack = (int)__double_as_longlong(cur[7]);
     if ((pack & 0xff) != (ND == 3 ? 0x15 : 0x5)) {
@@ -873,17 +706,12 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, SUB) k_deposit_split
 #pragma unroll
         for (int m = 0; m < 3; ++m) {
           if (((pack >> (2 * m)) & 3) == 1) continue;
-#pragma unroll
-          for (int A = 0; A < 3; ++A) {
-            if (slot < MCAPB) { sM[2 * slot] = r; sM[2 * slot + 1] = A | (m << 2); }
-            else mover_item3<SHAPE>(p, rec, sJ, A, m, JNs, sub * TS);
-            ++slot;
-          }
+          if (slot < MCAPB) { sM[2 * slot] = r; sM[2 * slot + 1] = m; }
+          else mover_item3<SHAPE>(p, rec, sJ, m, JNs, sub * TS);
+          ++slot;
         }
       }
     }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) { cur[k] = nx1[k]; nx1[k] = nxt[k]; }
   }
   __syncthreads();
   // ---- register boxes -> shared J tile: every thread applies the same stencil offset to its own
@@ -912,7 +740,7 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, SUB) k_deposit_split
   if (ND == 3) {
     for (int m = tid; m < nm; m += NTB) {
       const RecG rec{scratch + (size_t)(pb - base + (uint32_t)sM[2 * m]) * 8};
-      mover_item3<SHAPE>(p, rec, sJ, sM[2 * m + 1] & 3, (sM[2 * m + 1] >> 2) & 3, JNs, sub * TS);
+      mover_item3<SHAPE>(p, rec, sJ, sM[2 * m + 1], JNs, sub * TS);
     }
   } else {
     for (int m = warp; m < nm; m += NTB / 32) {
@@ -947,29 +775,6 @@ void keysink_fill(void* dst, const BcP3& bc, uint32_t* key, uint32_t* count, uin
   *(KeySink*)dst = ks;
 }
 
-int32_t launch_push_tiled(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled) {
-  *handled = false;
-  if (c->ndims < 2 || c->shape == SHAPE_BSPLINE3 || !sp.sorted) return 0;
-  PArr a;
-  for (int d = 0; d < 3; ++d) { a.x[d] = sp.a[d]; a.m[d] = sp.a[3 + d]; }
-  a.w = sp.a[6];
-  const long long ntiles = (long long)c->g.ntile[0] * c->g.ntile[1] * c->g.ntile[2];
-#define L(ND, SH)                                                                                       \
-  if (c->ndims == ND && c->shape == SH) {                                                               \
-    auto k = k_push_tiled<ND, SH>;                                                                      \
-    const size_t smem = TL<ND, SH>::SMEM;                                                               \
-    EB_CUDA(c, cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
-    k<<<(unsigned)ntiles, NT, smem, c->stream>>>(c->g, c->f, p, a, sp.cell_start, c->d_counters);       \
-  }
-  L(2, 0) L(2, 1) L(3, 0) L(3, 1)
-#undef L
-  c->launches++;
-  EB_CUDA(c, cudaGetLastError());
-  *handled = true;
-  return 0;
-}
-
-
 int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled, const void* keysink) {
   *handled = false;
   KeySink ks;
@@ -1003,7 +808,8 @@ int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool
       auto ka = k_push_split<ND, SH>;                                                                      \
       auto kb = k_deposit_split<ND, SH>;                                                                   \
       const size_t sa = sizeof(double) * (6 * TL<ND, SH>::FN + (NTA / 32) * 256);                                               \
-      const size_t sb = sizeof(double) * 3 * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4);  /* >= sub-tile need */ \
+      const size_t sb = sizeof(double) * 3 * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4)   /* >= sub-tile need */ \
+                        + (size_t)RING * 64 * (TL<ND, SH>::CPT / SUB) + 16;                                      \
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
       { ScopedPhase pa(c, "push_A");                                                                       \
