@@ -124,6 +124,7 @@ int32_t eb200_destroy(eb200_ctx* c) {
   void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->rec_scratch, c->cub_tmp, c->halo_send, c->halo_recv,
                   c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho};
   for (void* p : ptrs) if (p) cudaFree(p);
+  free_pinned(c);
   if (c->h_counters) cudaFreeHost(c->h_counters);
   if (c->h_red) cudaFreeHost(c->h_red);
   for (auto& kv : c->timers) for (auto& ev : kv.second.ev) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
@@ -290,8 +291,12 @@ int32_t eb200_upload_fields(eb200_ctx* c, const double* ex, const double* ey, co
   CHECK_CTX(c); NEED_GRID(c);
   const double* src[NFIELD] = {ex, ey, ez, bx, by, bz, jx, jy, jz};
   for (int f = 0; f < NFIELD; ++f)
-    if (src[f]) EB_CUDA(c, cudaMemcpyAsync(c->f.f[f], src[f], (size_t)c->g.total * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  EB_CUDA(c, cudaStreamSynchronize(c->stream));   // host buffers are not retained past the call
+    if (src[f]) {
+      char* dev = (char*)c->f.f[f];
+      EB_TRY(staged_h2d(c, src[f], (size_t)c->g.total * sizeof(double), sizeof(double),
+                        [dev](size_t o, size_t) { return (void*)(dev + o); }, nullptr));
+    }
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
   return 0;
 }
 int32_t eb200_download_fields(eb200_ctx* c, double* ex, double* ey, double* ez, double* bx, double* by, double* bz,
@@ -299,7 +304,11 @@ int32_t eb200_download_fields(eb200_ctx* c, double* ex, double* ey, double* ez, 
   CHECK_CTX(c); NEED_GRID(c);
   double* dst[NFIELD] = {ex, ey, ez, bx, by, bz, jx, jy, jz};
   for (int f = 0; f < NFIELD; ++f)
-    if (dst[f]) EB_CUDA(c, cudaMemcpyAsync(dst[f], c->f.f[f], (size_t)c->g.total * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (dst[f]) {
+      const char* dev = (const char*)c->f.f[f];
+      EB_TRY(staged_d2h(c, dst[f], (size_t)c->g.total * sizeof(double), sizeof(double),
+                        [dev](size_t o, size_t) { return (const void*)(dev + o); }));
+    }
   EB_CUDA(c, cudaStreamSynchronize(c->stream));
   return 0;
 }
@@ -388,6 +397,7 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
     return species_reserve(c, c->species[isp], n, true);
   }
   if (k == "deposit_scratch") { c->rec_scratch_max = atoll(value) < 1024 ? 1024 : atoll(value); return 0; }
+  if (k == "host_threads") { c->host_threads = atoi(value); return 0; }
   if (k == "mig_capacity") { c->mig_min_particles = atoll(value); return 0; }
   return fail(c, EB200_E_ARG, "unknown option " + k);
 }

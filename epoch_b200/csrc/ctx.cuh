@@ -6,6 +6,7 @@
 #include <string>
 #include <vector>
 #include <map>
+#include <functional>
 #include "../../include/epoch_b200.h"
 
 namespace eb {
@@ -122,6 +123,14 @@ struct eb200_ctx {
   double* mig_send[2] = {nullptr, nullptr}; double* mig_recv[2] = {nullptr, nullptr};
   long long mig_cap = 0;
   long long mig_min_particles = 1 << 16;   // option mig_capacity
+  // pinned staging ring of the host <-> device transfers (hostio.cu)
+  static constexpr int NPIN = 3;
+  void* pin[NPIN] = {nullptr, nullptr, nullptr};
+  cudaEvent_t pin_ev[NPIN];
+  bool pin_busy[NPIN] = {false, false, false};
+  int pin_next = 0;
+  size_t pin_bytes = (size_t)64 << 20;
+  int host_threads = 0;         // option host_threads (0: min(12, hardware threads - 2))
   unsigned long long* d_counters = nullptr;   // small device scalar block (64 x u64)
   unsigned long long* h_counters = nullptr;   // pinned mirror
   double* d_red = nullptr;                    // reductions (64 doubles)
@@ -146,6 +155,12 @@ struct eb200_ctx {
 namespace eb {
 
 int32_t fail(eb200_ctx* c, int32_t code, const std::string& msg);
+// hostio.cu
+int32_t staged_h2d(eb200_ctx* c, const void* host, size_t bytes, size_t granule,
+                   const std::function<void*(size_t, size_t)>& dst, const std::function<int32_t(size_t, size_t)>& after);
+int32_t staged_d2h(eb200_ctx* c, void* host, size_t bytes, size_t granule,
+                   const std::function<const void*(size_t, size_t)>& src);
+void free_pinned(eb200_ctx* c);
 #define EB_CUDA(c, call)                                                                 \
   do {                                                                                   \
     cudaError_t e__ = (call);                                                            \

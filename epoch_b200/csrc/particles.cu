@@ -91,18 +91,22 @@ int32_t add_particles(eb200_ctx* c, int isp, long long n, const double* packed, 
   if (replace) sp.n = 0;
   if (n == 0) { sp.sorted = false; return 0; }
   EB_TRY(species_reserve(c, sp, sp.n + n));
-  const long long chunk = std::min<long long>(n, 4LL << 20);   // <= 4M particles per staging copy
-  EB_TRY(ensure_stage(c, std::max<long long>(chunk * nvar, 1 << 16)));
-  for (long long done = 0; done < n; done += chunk) {
-    const long long m = std::min(chunk, n - done);
-    EB_CUDA(c, cudaMemcpyAsync(c->mig_recv[0], packed + done * nvar, (size_t)m * nvar * sizeof(double),
-                               cudaMemcpyHostToDevice, c->stream));
-    k_unpack_aos<<<(unsigned)((m + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[0], c->ndims, m, sp.n + done,
-        sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
-    c->launches++;
-    // the staging buffer is reused by the next chunk
-    EB_CUDA(c, cudaStreamSynchronize(c->stream));
-  }
+  const size_t rec = (size_t)nvar * sizeof(double);
+  EB_TRY(ensure_stage(c, std::max<long long>((long long)(c->pin_bytes / sizeof(double)), 1 << 16)));
+  // chunks of whole particles go pinned ring -> device staging -> SoA arrays (stream-ordered)
+  double* stage = c->mig_recv[0];
+  const long long n0 = sp.n;
+  EB_TRY(staged_h2d(c, packed, (size_t)n * rec, rec,
+      [stage](size_t, size_t) { return (void*)stage; },
+      [c, &sp, stage, rec, n0](size_t o, size_t mbytes) -> int32_t {
+        const long long m = (long long)(mbytes / rec), first = (long long)(o / rec);
+        k_unpack_aos<<<(unsigned)((m + 255) / 256), 256, 0, c->stream>>>(stage, c->ndims, m, n0 + first,
+            sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
+        c->launches++;
+        EB_CUDA(c, cudaGetLastError());
+        return 0;
+      }));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
   sp.n += n;
   sp.sorted = false;
   return 0;
@@ -111,17 +115,18 @@ int32_t add_particles(eb200_ctx* c, int isp, long long n, const double* packed, 
 int32_t get_particles(eb200_ctx* c, int isp, long long first, long long cap, double* packed, int nvar, long long* n_out) {
   SpeciesD& sp = c->species[isp];
   const long long n = std::max<long long>(0, std::min(sp.n - first, cap));
-  const long long chunk = std::min<long long>(std::max<long long>(n, 1), 4LL << 20);
-  EB_TRY(ensure_stage(c, std::max<long long>(chunk * nvar, 1 << 16)));
-  for (long long done = 0; done < n; done += chunk) {
-    const long long m = std::min(chunk, n - done);
-    k_pack_aos<<<(unsigned)((m + 255) / 256), 256, 0, c->stream>>>(c->mig_send[0], c->ndims, m, first + done,
-        sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6]);
-    c->launches++;
-    EB_CUDA(c, cudaMemcpyAsync(packed + done * nvar, c->mig_send[0], (size_t)m * nvar * sizeof(double),
-                               cudaMemcpyDeviceToHost, c->stream));
-    EB_CUDA(c, cudaStreamSynchronize(c->stream));
-  }
+  const size_t rec = (size_t)nvar * sizeof(double);
+  EB_TRY(ensure_stage(c, std::max<long long>((long long)(c->pin_bytes / sizeof(double)), 1 << 16)));
+  double* stage = c->mig_send[0];
+  EB_TRY(staged_d2h(c, packed, (size_t)n * rec, rec,
+      [c, &sp, stage, rec, first](size_t o, size_t mbytes) -> const void* {
+        const long long m = (long long)(mbytes / rec), f0 = first + (long long)(o / rec);
+        k_pack_aos<<<(unsigned)((m + 255) / 256), 256, 0, c->stream>>>(stage, c->ndims, m, f0,
+            sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6]);
+        c->launches++;
+        return cudaGetLastError() == cudaSuccess ? (const void*)stage : nullptr;
+      }));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
   if (n_out) *n_out = n;
   return 0;
 }
