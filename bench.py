@@ -59,10 +59,12 @@ def make_sim(abi, cells_global, rank=0, nproc=1, nccl_id=None, device=0):
                       abi=abi, device=device, rank=rank, nproc=nproc, nprocdir=(1, 1, nproc), nccl_id=nccl_id)
 
 
-def fill_particles(out, sim, seed, nthreads):
-    """Reference loader rule for a uniform plasma on this rank's cells, written
-    into `out` ((n_cells*PPC, 7) float64, partlist wire order x,y,z,px,py,pz,w)."""
+def fill_particles(out, sim, seed, nthreads, k_begin=0, k_end=None):
+    """Reference loader rule for a uniform plasma on this rank's cells (z planes
+    k_begin..k_end), written into `out` ((planes*nx*ny*PPC, 7) float64, partlist wire
+    order x,y,z,px,py,pz,w)."""
     nx, ny, nz = sim.n_local
+    k_end = nz if k_end is None else k_end
     dx = sim.d[0]
     weight = DENSITY * dx ** 3 / PPC
     sigma = math.sqrt(M0 * KB * T_KELVIN)
@@ -73,7 +75,7 @@ def fill_particles(out, sim, seed, nthreads):
     def work(k0, k1):
         for k in range(k0, k1):
             rng = np.random.default_rng([seed, sim.rank, k])
-            P = out[k * per_plane:(k + 1) * per_plane]
+            P = out[(k - k_begin) * per_plane:(k - k_begin + 1) * per_plane]
             u = rng.random((per_plane, 3))
             u -= 0.5
             cells = np.arange(nx * ny).repeat(PPC)
@@ -82,8 +84,8 @@ def fill_particles(out, sim, seed, nthreads):
             P[:, 2] = (sim.grid_min_local[2] + k * sim.d[2]) + u[:, 2] * dx
             P[:, 3:6] = rng.standard_normal((per_plane, 3)) * sigma
             P[:, 6] = weight
-    nthreads = max(1, min(nthreads, nz))
-    bounds = np.linspace(0, nz, nthreads + 1).astype(int)
+    nthreads = max(1, min(nthreads, k_end - k_begin))
+    bounds = np.linspace(k_begin, k_end, nthreads + 1).astype(int)
     ts = [threading.Thread(target=work, args=(bounds[i], bounds[i + 1])) for i in range(nthreads)]
     [t.start() for t in ts]
     [t.join() for t in ts]
@@ -233,13 +235,19 @@ def run_ours(args):
     nccl_id = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def fresh_nccl_id():
+        """one ncclUniqueId per communicator (rank 0 makes it, torch.distributed carries it)"""
+        if world == 1:
+            return None
         buf = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             raw = (128 * __import__("ctypes").c_char)()
             assert abi.nccl_unique_id(raw) == 0
             buf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
         dist.broadcast(buf, 0)
-        nccl_id = bytes(buf.cpu().numpy().tobytes())
+        return bytes(buf.cpu().numpy().tobytes())
+    nccl_id = fresh_nccl_id()
 
     def barrier():
         if world > 1:
@@ -257,16 +265,39 @@ def run_ours(args):
     n_part = c ** 3 * PPC
     t_setup = time.perf_counter()
     sim = make_sim(abi, cells_global, rank, world, nccl_id, device=local)
-    # host copy of this rank's particle load (also the e2e leg's host buffer)
-    host = np.empty((n_part, 7))
-    fill_particles(host, sim, args.seed, host_cores() // max(1, world))
-    t_gen = time.perf_counter() - t_setup
     sim.ctx.set_option("reserve", f"0:{n_part + n_part // 64 if world > 1 else n_part}")
     sim.ctx.set_option("timers", 1)
     for kv in args.opt:                       # tuning experiments: --opt push_kernel=tiled
         k, v = kv.split("=", 1)
         sim.ctx.set_option(k, v)
-    sim.ctx.upload_particles(0, host)
+    # host copy of this rank's particle load (also the e2e leg's host buffer) -- if the host
+    # has the memory for one per rank; else the load is generated and uploaded in slabs and
+    # the e2e leg (which needs the whole state in host buffers) is skipped
+    import psutil
+    local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
+    host_budget = 0.85 * psutil.virtual_memory().available / max(1, local_world)
+    if args.host_gb is not None:
+        host_budget = args.host_gb * 1e9
+    full_host = n_part * 56 * 1.04 < host_budget
+    gen_threads = max(1, host_cores() // max(1, local_world))
+    if full_host:
+        host_all = np.empty((n_part + (n_part // 64 if world > 1 else 0), 7))   # room for migrated-in particles
+        host = host_all[:n_part]
+        fill_particles(host, sim, args.seed, gen_threads)
+        t_gen = time.perf_counter() - t_setup
+        sim.ctx.upload_particles(0, host)
+    else:
+        per_plane = c * c * PPC
+        planes = max(1, min(c, int(host_budget / (per_plane * 56 * (1 + 1 / 64)))))
+        host_all = np.empty((planes * per_plane + planes * per_plane // 64, 7))
+        host = host_all[:planes * per_plane]
+        t_gen = 0.0
+        for k0 in range(0, c, planes):
+            k1 = min(c, k0 + planes)
+            tg = time.perf_counter()
+            fill_particles(host, sim, args.seed, gen_threads, k0, k1)
+            t_gen += time.perf_counter() - tg
+            sim.ctx.upload_particles(0, host[:(k1 - k0) * per_plane], append=k0 > 0)
     sim.ctx.sync()
     t_up = time.perf_counter() - t_setup - t_gen
 
@@ -327,16 +358,30 @@ def run_ours(args):
         field_line = {"cell_updates_per_s": 4 * cells * args.steps / (fields_ms * 1e-3),
                       "achieved_gbs": fb / (fields_ms * 1e-3) / 1e9,
                       "frac_of_hbm": fb / (fields_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+    sim_d, sim_gml = tuple(sim.d), tuple(sim.grid_min_local)
     sim.ctx.close()
     del sim
 
     # e2e: same metric through the C ABI from host buffers (upload, K steps, download)
     e2e = None
+    e2e_note = None
     if not args.no_e2e:
+        cells_e2e, n_e2e = cells_global, n_part
+        if not full_host:
+            # the host cannot hold this rank's whole state: the e2e leg runs the same deck on the
+            # z extent whose particles fit the host buffer (said in e2e.what)
+            import types
+            cells_e2e, n_e2e = (c, c, planes * world), planes * per_plane
+            geo = types.SimpleNamespace(n_local=(c, c, planes), d=sim_d, rank=rank,
+                                        grid_min_local=(sim_gml[0], sim_gml[1], sim_gml[2] - rank * (c - planes) * sim_d[2]))
+            fill_particles(host, geo, args.seed, gen_threads)
+            e2e_note = (f"host memory holds {planes} of the {c} z planes per rank: this leg runs "
+                        f"{c}x{c}x{planes} cells per GPU (the device-timed value is on the full {c}^3)")
+        nccl_id2 = fresh_nccl_id()
         barrier(); torch.cuda.synchronize()
         t0 = time.perf_counter()
-        sim2 = make_sim(abi, cells_global, rank, world, nccl_id, device=local)
-        sim2.ctx.set_option("reserve", f"0:{n_part + n_part // 64 if world > 1 else n_part}")
+        sim2 = make_sim(abi, cells_e2e, rank, world, nccl_id2, device=local)
+        sim2.ctx.set_option("reserve", f"0:{n_e2e + n_e2e // 64 if world > 1 else n_e2e}")
         for kv in args.opt:
             k, v = kv.split("=", 1)
             sim2.ctx.set_option(k, v)
@@ -354,14 +399,14 @@ def run_ours(args):
                 t2a = time.perf_counter()
         sim2.ctx.sync()
         t3 = time.perf_counter()
-        got = sim2.ctx.download_particles(0, out=host)
+        got = sim2.ctx.download_particles(0, out=host_all)
         fld = sim2.ctx.download_fields()
         sim2.ctx.sync()
         t4 = time.perf_counter()
         t_e2e = max_over_ranks(t4 - t0)
         h2d = host.nbytes + 6 * fzero.nbytes
         d2h = got.nbytes + 9 * fzero.nbytes
-        e2e = {"value": n_part * world * args.steps / t_e2e, "unit": "particle-steps/s",
+        e2e = {"value": n_e2e * world * args.steps / t_e2e, "unit": "particle-steps/s",
                "h2d_bytes_per_step": h2d * world / args.steps, "d2h_bytes_per_step": d2h * world / args.steps,
                "seconds": t_e2e, "steps_per_residency": args.steps,
                "seconds_split": {"create_alloc_upload_fields": t1 - t0, "upload_particles": t2 - t1,
@@ -370,7 +415,7 @@ def run_ours(args):
                "what": "eb200_create + upload_fields + upload_particles (pageable host numpy buffers, staged "
                        "through the library's pinned ring) + K full steps + download_particles + download_fields "
                        "+ sync, wall clock; the state lives on the device between steps, so the copies are "
-                       "amortised over K steps"}
+                       "amortised over K steps" + ("; " + e2e_note if e2e_note else "")}
         del fld
         sim2.ctx.close()
     if rank != 0:
@@ -405,6 +450,7 @@ def main():
     ap.add_argument("--seed", type=int, default=12345)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--host-gb", type=float, default=None, help="host memory per rank for the particle copy (default: from free memory)")
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (tuning experiments)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
