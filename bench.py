@@ -337,7 +337,7 @@ def run_ours(args):
         n_launch = args.steps      # one species => one push launch per step
         alg_bytes = 104.0 * n_live + 72.0 * c ** 3
         ach = alg_bytes / (pk_ms / n_launch * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "push+deposit (k_push_*)", "achieved": ach, "peak": peaks["hbm_gbs"],
+        roof = {"bound": "hbm", "kernel": "k_push_split + k_deposit_split (one push+deposit pass over all slabs = one 'launch')", "achieved": ach, "peak": peaks["hbm_gbs"],
                 "unit": "GB/s", "frac": ach / peaks["hbm_gbs"], "traffic": None, "peak_source": how,
                 "ms_per_launch": pk_ms / n_launch, "algorithmic_bytes_per_launch": alg_bytes,
                 "particle_steps_per_s_kernel_only": n_live / (pk_ms / n_launch * 1e-3),
@@ -346,8 +346,9 @@ def run_ours(args):
         if os.path.exists(tr):
             try:
                 roof["traffic"] = json.load(open(tr)).get("push_bytes_per_particle", None)
-                if roof["traffic"] is not None:
+                if roof["traffic"] is not None:       # ncu DRAM bytes per particle (profiles/) x particles of a pass
                     roof["traffic"] = roof["traffic"] * n_live
+                    roof["traffic_source"] = "profiles/traffic.json (ncu --set full dram bytes per particle, 128^3 capture)"
             except Exception:
                 pass
     fields_ms, fields_l = phases["fields"]
