@@ -212,7 +212,10 @@ int32_t eb200_set_field_bcs(eb200_ctx* c, const int32_t bc_field[6]) {
 int32_t eb200_set_solver(eb200_ctx* c, int32_t field_order, int32_t maxwell_solver, const double coeffs[15]) {
   CHECK_CTX(c);
   if (field_order != 2 && field_order != 4 && field_order != 6) return fail(c, EB200_E_ARG, "field_order must be 2, 4 or 6");
-  if (maxwell_solver != 0) return fail(c, EB200_E_UNSUPPORTED, "extended-stencil Maxwell solvers are not built yet (SURVEY 8f-4)");
+  // constants.F90:125-132: custom -1, yee 0, lehe_x/y/z 2/3/4, cowan 5, pukhov 6 (1 = "lehe" is an
+  // alias the deck reader resolves); the coefficients come from set_maxwell_solver on the host
+  if (maxwell_solver < -1 || maxwell_solver > 6 || maxwell_solver == 1) return fail(c, EB200_E_ARG, "unknown maxwell_solver");
+  if (maxwell_solver != 0 && !coeffs) return fail(c, EB200_E_ARG, "an extended-stencil solver needs its 15 coefficients");
   if (field_order / 2 > c->ng) return fail(c, EB200_E_ARG, "field_order needs more ghost cells");
   c->field_order = field_order; c->maxwell_solver = maxwell_solver;
   if (coeffs) std::memcpy(c->coeffs, coeffs, 15 * sizeof(double));

@@ -60,10 +60,15 @@ class SpeciesSpec:
         self.temperature = temperature
 
 
+# constants.F90:125-132
+MAXWELL_SOLVERS = {"custom": -1, "yee": 0, "lehe": 1, "lehe_x": 2, "lehe_y": 3, "lehe_z": 4, "cowan": 5, "pukhov": 6}
+
+
 class Simulation:
     def __init__(self, ndims, n_global, mins, maxs, shape="triangle", bc_field=None, species=(),
                  lasers=(), dt_multiplier=0.95, field_order=2, t_end=None, abi=None, device=0,
-                 rank=0, nproc=1, nprocdir=(1, 1, 1), nccl_id=None, dt=None):
+                 rank=0, nproc=1, nprocdir=(1, 1, 1), nccl_id=None, dt=None, maxwell_solver="yee",
+                 stencil=None):
         self.ndims = nd = ndims
         self.shape = SHAPES[shape] if isinstance(shape, str) else shape
         self.n_global = tuple(n_global[:nd])
@@ -98,11 +103,16 @@ class Simulation:
         self.ctx.set_grid(self.n_local, self.d, self.grid_min_local, self.min_local, self.max_local,
                           self.mins, self.maxs, n_global=self.n_global, n_global_min=self.cell_min)
         self.ctx.set_field_bcs(self.bc_field)
-        self.ctx.set_solver(field_order, 0)
-        for i, sp in enumerate(self.species):
-            self.ctx.set_species(i, sp.charge, sp.mass, 1.0, sp.immobile, sp.zero_current, 0, sp.bcs)
+        self.maxwell_solver = MAXWELL_SOLVERS[maxwell_solver] if isinstance(maxwell_solver, str) else maxwell_solver
+        if self.maxwell_solver == 1:          # "lehe" is the deck's alias of lehe_x (deck_control_block.F90:121-122)
+            self.maxwell_solver = 2
+        self.stencil = dict(stencil or {})    # custom solver: betaxy ... deltaz (+ dt) from the deck's stencil block
         self.dt_multiplier = dt_multiplier
         self.dt = dt if dt is not None else self.set_dt()
+        self.coeffs = self.set_maxwell_solver()
+        self.ctx.set_solver(field_order, self.maxwell_solver, self.coeffs)
+        for i, sp in enumerate(self.species):
+            self.ctx.set_species(i, sp.charge, sp.mass, 1.0, sp.immobile, sp.zero_current, 0, sp.bcs)
         self.time = 0.0
         self.step = 0
         self._setup_lasers()
@@ -120,10 +130,28 @@ class Simulation:
             solver = d[0] * d[1] * d[2] / math.sqrt((d[0] * d[1]) ** 2 + (d[1] * d[2]) ** 2
                                                    + (d[2] * d[0]) ** 2) / C
         dt = cfl * solver
+        ms = self.maxwell_solver
+        if ms in (2, 3, 4):
+            # R. Lehe: dt = MIN(d_a, transverse CFL) / c  (setup.F90:713-721; 2D/1D analogues)
+            a = ms - 2
+            if a >= nd:
+                raise ValueError("lehe solver axis outside the simulation's dimensions")
+            others = [d[k] for k in range(nd) if k != a]
+            if len(others) == 2:
+                trans = others[0] * others[1] / math.sqrt(others[0] ** 2 + others[1] ** 2)
+            elif len(others) == 1:
+                trans = others[0]
+            else:
+                trans = d[a]
+            dt = min(d[a], trans) / C
+        elif ms in (5, 6):
+            dt = min(d) / C                    # Cowan, Pukhov (setup.F90:723-727)
         bcs = [self._norm_field_bc(b) for b in self.bc_field]
         any_open = any(b in (BC["simple_laser"], BC["simple_outflow"]) for b in bcs)
         if any_open:
             dt = min(dt, solver)
+        if ms == -1:                           # custom stencil: the deck gives dt (setup.F90:734-746)
+            dt = self.stencil["dt"]
         # set_plasma_frequency_dt (setup.F90:640-696; 1D :514-563)
         min_dt = 1000000.0
         k_max = 2.0 * PI / d[0]
@@ -140,6 +168,62 @@ class Simulation:
             if dt_laser > C_TINY:
                 dt = min(dt, dt_laser)
         return self.dt_multiplier * dt
+
+    # -- set_maxwell_solver ------------------------------------------------------
+    def set_maxwell_solver(self):
+        """Coefficients of the extended B-update stencils (fields.f90:53-179; 2D :51-100; 1D
+        :50-72) in the ABI's order: alpha x,y,z | beta xy,xz,yx,yz,zx,zy | gamma x,y,z |
+        delta x,y,z.  Terms of directions the simulation does not have stay zero."""
+        nd, ms = self.ndims, self.maxwell_solver
+        d = list(self.d) + [1.0] * (3 - nd)
+        al = [1.0, 1.0, 1.0]
+        be = {k: 0.0 for k in ("xy", "xz", "yx", "yz", "zx", "zy")}
+        ga = [0.0, 0.0, 0.0]
+        de = [0.0, 0.0, 0.0]
+        ax = "xyz"
+        has = lambda k: ax.index(k[0]) < nd and ax.index(k[1]) < nd
+        if ms == 0:
+            return [0.0] * 15
+        if ms == -1:
+            for k in be:
+                be[k] = float(self.stencil.get("beta" + k, 0.0)) if has(k) else 0.0
+            for i in range(nd):
+                de[i] = float(self.stencil.get("delta" + ax[i], 0.0))
+                if nd == 3:
+                    ga[i] = float(self.stencil.get("gamma" + ax[i], 0.0))
+        elif ms in (2, 3, 4):
+            a = ms - 2
+            dx_cdt = d[a] / (C * self.dt)
+            for o in range(nd):
+                if o == a:
+                    continue
+                be[ax[a] + ax[o]] = 0.125 * (d[a] / d[o]) ** 2
+                be[ax[o] + ax[a]] = 0.125
+            de[a] = 0.25 * (1.0 - dx_cdt ** 2 * math.sin(0.5 * PI / dx_cdt) ** 2)
+        elif ms in (5, 6):
+            if nd == 1 or (ms == 5 and nd != 3):
+                raise ValueError("this maxwell_solver does not exist in this dimensionality")
+            delta = min(d[:nd])
+            cc = [(delta / d[i]) ** 2 for i in range(3)]
+            if ms == 5:      # Cowan
+                cx1 = 1.0 / (cc[0] * cc[1] + cc[1] * cc[2] + cc[0] * cc[2])
+                cx2 = 1.0 - cc[0] * cc[1] * cc[2] * cx1
+                be["yx"] = 0.125 * cc[0] * cx2
+                be["xy"] = 0.125 * cc[1] * cx2
+                be["xz"] = 0.125 * cc[2] * cx2
+                ga[0] = cc[1] * cc[2] * (0.0625 - 0.125 * cc[1] * cc[2] * cx1)
+                ga[1] = cc[0] * cc[2] * (0.0625 - 0.125 * cc[0] * cc[2] * cx1)
+                ga[2] = cc[0] * cc[1] * (0.0625 - 0.125 * cc[0] * cc[1] * cx1)
+            else:            # Pukhov
+                be["yx"] = 0.125 * cc[0]
+                be["xy"] = 0.125 * cc[1]
+                be["xz"] = 0.125 * cc[2] if nd == 3 else 0.0
+            if nd == 3:
+                be["zx"], be["zy"], be["yz"] = be["yx"], be["xy"], be["xz"]
+        al[0] = 1.0 - 2.0 * be["xy"] - 2.0 * be["xz"] - 4.0 * ga[0] - 3.0 * de[0]
+        al[1] = 1.0 - 2.0 * be["yx"] - 2.0 * be["yz"] - 4.0 * ga[1] - 3.0 * de[1]
+        al[2] = 1.0 - 2.0 * be["zx"] - 2.0 * be["zy"] - 4.0 * ga[2] - 3.0 * de[2]
+        return al + [be["xy"], be["xz"], be["yx"], be["yz"], be["zx"], be["zy"]] + ga + de
 
     @staticmethod
     def _norm_field_bc(b):

@@ -103,9 +103,12 @@ int32_t EB200_NAME(set_time)(EB200_CTX*, double dt, double time, int32_t step);
 /* bc_field(1:6) after setup_boundaries normalisation is applied internally
  * (boundary.F90:30-75). */
 int32_t EB200_NAME(set_field_bcs)(EB200_CTX*, const int32_t bc_field[6]);
-/* set_field_order / set_maxwell_solver (fields.f90:34-179).  coeffs = alphax,
- * alphay,alphaz, betaxy,betaxz,betayx,betayz,betazx,betazy, gammax,gammay,gammaz,
- * deltax,deltay,deltaz; ignored for maxwell_solver == 0 (Yee). */
+/* set_field_order / set_maxwell_solver (fields.f90:34-179).  maxwell_solver uses
+ * the reference's codes (constants.F90:125-132: custom -1, yee 0, lehe_x/y/z 2/3/4,
+ * cowan 5, pukhov 6).  coeffs = alphax,alphay,alphaz, betaxy,betaxz,betayx,betayz,
+ * betazx,betazy, gammax,gammay,gammaz, deltax,deltay,deltaz as set_maxwell_solver
+ * leaves them on the host (terms of absent dimensions zero); ignored for Yee.  The
+ * extended stencils act in the second-order update_b_field only (fields.f90:655-732). */
 int32_t EB200_NAME(set_solver)(EB200_CTX*, int32_t field_order, int32_t maxwell_solver,
                                const double coeffs[15]);
 

@@ -104,7 +104,8 @@ int32_t orc_set_field_bcs(orc_ctx* c, const int32_t bc_field[6]) {
 int32_t orc_set_solver(orc_ctx* c, int32_t field_order, int32_t maxwell_solver, const double coeffs[15]) {
   if (!c) return EB200_E_ARG;
   if (field_order != 2 && field_order != 4 && field_order != 6) return fail(c, EB200_E_ARG, "field_order");
-  if (maxwell_solver != 0) return fail(c, EB200_E_UNSUPPORTED, "only the Yee solver is supported");
+  if (maxwell_solver < -1 || maxwell_solver > 6 || maxwell_solver == 1) return fail(c, EB200_E_ARG, "unknown maxwell_solver");
+  if (maxwell_solver != 0 && !coeffs) return fail(c, EB200_E_ARG, "an extended-stencil solver needs its 15 coefficients");
   c->s.field_order = field_order; c->s.maxwell_solver = maxwell_solver;
   if (coeffs) std::copy(coeffs, coeffs + 15, c->s.coeffs);
   return 0;

@@ -97,8 +97,48 @@ void update_e_field(State& s) {
       }
 }
 
+// difference along axis a of the extended stencils (fields.f90:655-732; 2D :426-470; 1D :296-306),
+// terms and summation order as written there; so1 / so2 = strides of the other axes in index
+// order, h1 / h2 = whether they exist
+static inline double ext_diff(const double* f, int64_t i, int64_t sa, int64_t so1, int64_t so2, bool h1, bool h2,
+                              double alpha, double beta1, double beta2, double gamma, double delta) {
+  double r = alpha * (f[i + sa] - f[i]);
+  if (h1) r = r + beta1 * (f[i + sa + so1] - f[i + so1] + f[i + sa - so1] - f[i - so1]);
+  if (h2) r = r + beta2 * (f[i + sa + so2] - f[i + so2] + f[i + sa - so2] - f[i - so2]);
+  if (h1 && h2)
+    r = r + gamma * (f[i + sa + so1 - so2] - f[i + so1 - so2] + f[i + sa - so1 - so2] - f[i - so1 - so2]
+                   + f[i + sa + so1 + so2] - f[i + so1 + so2] + f[i + sa - so1 + so2] - f[i - so1 + so2]);
+  r = r + delta * (f[i + 2 * sa] - f[i - sa]);
+  return r;
+}
+
+// update_b_field, second order, maxwell_solver /= yee (fields.f90:655-732)
+static void update_b_field_ext(State& s) {
+  const int nd = s.ndims;
+  const double* ex = s.f[EX].data(); const double* ey = s.f[EY].data(); const double* ez = s.f[EZ].data();
+  double* bx = s.f[BX].data(); double* by = s.f[BY].data(); double* bz = s.f[BZ].data();
+  const int64_t sx = s.st[0], sy = s.st[1], sz = s.st[2];
+  const bool hy = nd >= 2, hz = nd >= 3;
+  const double* q = s.coeffs;   // alpha x,y,z | beta xy,xz,yx,yz,zx,zy | gamma x,y,z | delta x,y,z
+  const double cx1 = s.hdtd[0], cy1 = s.hdtd[1], cz1 = s.hdtd[2];
+  for (int iz = s.lo0(2); iz <= s.hi(2); ++iz)
+    for (int iy = s.lo0(1); iy <= s.hi(1); ++iy)
+      for (int ix = 0; ix <= s.n[0]; ++ix) {
+        const int64_t i = s.idx(ix, iy, iz);
+        double vx = bx[i], vy = by[i], vz = bz[i];
+        if (hy) vx = vx - cy1 * ext_diff(ez, i, sy, sx, sz, true, hz, q[1], q[5], q[6], q[10], q[13]);
+        if (hz) vx = vx + cz1 * ext_diff(ey, i, sz, sx, sy, true, true, q[2], q[7], q[8], q[11], q[14]);
+        if (hz) vy = vy - cz1 * ext_diff(ex, i, sz, sx, sy, true, true, q[2], q[7], q[8], q[11], q[14]);
+        vy = vy + cx1 * ext_diff(ez, i, sx, sy, sz, hy, hz, q[0], q[3], q[4], q[9], q[12]);
+        vz = vz - cx1 * ext_diff(ey, i, sx, sy, sz, hy, hz, q[0], q[3], q[4], q[9], q[12]);
+        if (hy) vz = vz + cy1 * ext_diff(ex, i, sy, sx, sz, true, hz, q[1], q[5], q[6], q[10], q[13]);
+        bx[i] = vx; by[i] = vy; bz[i] = vz;
+      }
+}
+
 // fields.f90:428-815 (Yee branches :637-654, orders 4/6 :734-812)
 void update_b_field(State& s) {
+  if (s.maxwell_solver != 0 && s.field_order == 2) { update_b_field_ext(s); return; }
   const int nd = s.ndims;
   const double* ex = s.f[EX].data(); const double* ey = s.f[EY].data(); const double* ez = s.f[EZ].data();
   double* bx = s.f[BX].data(); double* by = s.f[BY].data(); double* bz = s.f[BZ].data();
