@@ -261,3 +261,13 @@ def test_maxwell_solver_group_velocity_3d(product_abi, solver, printed):
     # the recorded values sit up to 0.65 % above the scheme's exact dispersion value (CPML run)
     assert abs(vg / printed - 1) < 0.01, (vg, printed)
     assert abs(vg / exact_group_velocity(sim) - 1) < 3e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["1d_optimized", "2d_optimized", "2d_optimized_symm", "2d_optimized_xaxis",
+                                  "3d_optimized", "3d_optimized_xaxis", "3d_optimized_xaxis_soft"])
+def test_custom_stencil_goldens_on_gpu(product_abi, name):
+    """epoch{1,2,3}d/tests/test_custom_stencils.py on the CUDA library (these decks use the open
+    boundaries of this path): the reference's assertion and its recorded velocities."""
+    from test_maxwell_solvers import custom_deck, check_custom
+    check_custom(custom_deck(product_abi, name), name)
