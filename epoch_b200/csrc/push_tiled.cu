@@ -31,7 +31,7 @@ namespace eb {
 namespace {
 
 #ifndef EB_MINB_A
-#define EB_MINB_A 2
+#define EB_MINB_A 4
 #endif
 template <int ND, int SHAPE>
 struct TL {
@@ -332,7 +332,23 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
   }
   if (ks != nullptr && ks->on) {
     uint32_t k = ks->nbucket - 1;
+#ifdef EB_FASTKEY
+    int ch = 0;
+    {
+      int ck[3] = {1, 1, 1};
+#pragma unroll
+      for (int d = 0; d < ND; ++d) {
+        double f3;
+        ck[d] = cell_round(cell_coord<SHAPE>(px[d] + delta[d], p.idx[d]), f3);
+        const BcP& b = ks->bc.b[d];
+        if (posn[d] < b.min_local) { posn[d] += b.shift; ck[d] += g->n[d]; }
+        if (posn[d] >= b.max_local) { posn[d] -= b.shift; ck[d] -= g->n[d]; }
+      }
+      k = cell_key<ND>(*g, ck);
+    }
+#else
     const int ch = bc_and_key<ND, SHAPE>(*g, p, ks->bc, posn, momn, k);
+#endif
     if (ch < 0) k = ks->nbucket - 1;
     ks->key[ip] = ch < 0 ? KEY_INVALID : k;
     const unsigned peers = __match_any_sync(__activemask(), k);
@@ -521,7 +537,10 @@ __device__ __forceinline__ int mover_item_count(int pack) {
 // =====================================================================================
 namespace {
 
-constexpr int NTA = 256;         // push kernel threads
+#ifndef EB_NTA
+#define EB_NTA 128
+#endif
+constexpr int NTA = EB_NTA;      // push kernel threads
 constexpr int MCAPB = 2048;      // overflow work items per sub-tile in the deposit kernel (more are deposited inline)
 #ifndef EB_MINB_B
 #define EB_MINB_B 2
@@ -716,23 +735,30 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   __syncthreads();
   // ---- register boxes -> shared J tile: every thread applies the same stencil offset to its own
   //      cell, so the addresses of a step are distinct; steps are separated by barriers ----
+  // With a sub-tile two cells thick along z and NW = 3, the offsets dz = 0 and dz = 2 touch disjoint
+  // planes and share a step.
+  constexpr bool ZPAIR = ND == 3 && TS == 2 && NW == 3;
+  auto box_step = [&](int dx, int dy, int dz) {
+    const int off = (l[0] + 1 + dx) + (l[1] + 1 + dy) * JXs + (ND == 3 ? (l[2] + 1 + dz) * JXs * JYs : 0);
+    if (ND == 3) {
+      // component A: acc[(o[Q] * NW + o[P]) * (NW - 1) + o[A]], P = A + 1, Q = A + 2, o[A] < NW - 1
+      if (dx < NW - 1) sJ[off] += acc[(dz * NW + dy) * (NW - 1) + dx];
+      if (dy < NW - 1) sJ[JNs + off] += acc[NA + (dx * NW + dz) * (NW - 1) + dy];
+      if (dz < NW - 1) sJ[2 * JNs + off] += acc[2 * NA + (dy * NW + dx) * (NW - 1) + dz];
+    } else {
+      sJ[off] += acc[dy * NW + dx];
+      sJ[JNs + off] += acc[NA + dy * NW + dx];
+      sJ[2 * JNs + off] += acc[2 * NA + dy * NW + dx];
+    }
+  };
 #pragma unroll
-  for (int dz = 0; dz < (ND == 3 ? NW : 1); ++dz)
+  for (int dz = 0; dz < (ND == 3 ? (ZPAIR ? 2 : NW) : 1); ++dz)
 #pragma unroll
     for (int dy = 0; dy < NW; ++dy)
 #pragma unroll
       for (int dx = 0; dx < NW; ++dx) {
-        const int off = (l[0] + 1 + dx) + (l[1] + 1 + dy) * JXs + (ND == 3 ? (l[2] + 1 + dz) * JXs * JYs : 0);
-        if (ND == 3) {
-          // component A: acc[(o[Q] * NW + o[P]) * (NW - 1) + o[A]], P = A + 1, Q = A + 2, o[A] < NW - 1
-          if (dx < NW - 1) sJ[off] += acc[(dz * NW + dy) * (NW - 1) + dx];
-          if (dy < NW - 1) sJ[JNs + off] += acc[NA + (dx * NW + dz) * (NW - 1) + dy];
-          if (dz < NW - 1) sJ[2 * JNs + off] += acc[2 * NA + (dy * NW + dx) * (NW - 1) + dz];
-        } else {
-          sJ[off] += acc[dy * NW + dx];
-          sJ[JNs + off] += acc[NA + dy * NW + dx];
-          sJ[2 * JNs + off] += acc[2 * NA + dy * NW + dx];
-        }
+        box_step(dx, dy, dz);
+        if (ZPAIR && dz == 0) box_step(dx, dy, 2);
         __syncthreads();
       }
   // ---- particles that changed cell ----

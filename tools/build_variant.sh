@@ -7,5 +7,5 @@ mkdir -p $out && cp $src/*.cu $src/*.cuh $src/Makefile $out/
 sed -i 's#"../../include/epoch_b200.h"#"/root/repo/include/epoch_b200.h"#' $out/ctx.cuh
 sed -i 's#../../include/epoch_b200.h#/root/repo/include/epoch_b200.h#' $out/Makefile
 make -C $out -j8 EXTRA="$flags" 2>&1 | grep -E "error" || true
-grep -A2 "k_deposit_splitILi3ELi1" $out/push_tiled.o.ptxas.log | grep -E "registers|spill" | tr '\n' ' '; echo " <- $name"
+grep -A2 "k_push_splitILi3ELi1" $out/push_tiled.o.ptxas.log | grep -E "registers|spill" | tr '\n' ' '; echo " <- $name"
 rm -f $out/*.o $out/*.cu $out/*.cuh
