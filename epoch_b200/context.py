@@ -101,6 +101,17 @@ class PicContext:
         self._ck(self.abi.set_solver(self._ctx, field_order, maxwell_solver,
                                      _f64(coeffs if coeffs is not None else [0.0] * 15)))
 
+    def set_current_options(self, smooth=False, smooth_its=1, smooth_comp_its=0, strides=None,
+                            initial_j=None):
+        """current_finish options (current_smooth.F90:29-151): binomial filter passes and
+        the subtraction of the host's initial_jx,jy,jz (use_current_correction)."""
+        st = np.ascontiguousarray(list(strides) if strides else [], dtype=np.int32)
+        j0 = None if initial_j is None else _f64(initial_j)
+        self._ck(self.abi.set_current_options(
+            self._ctx, int(bool(smooth)), int(smooth_its), int(smooth_comp_its), len(st),
+            st.ctypes.data_as(C.POINTER(C.c_int32)) if len(st) else None,
+            int(initial_j is not None), j0))
+
     def set_species(self, isp, charge, mass, weight=1.0, immobile=False, zero_current=False,
                     species_type=0, bcs=None):
         nd = self.ndims

@@ -12,6 +12,7 @@
 // consecutive threads walk consecutive x => coalesced; x-normal slabs are ng-wide
 // strided pieces and small.
 #include "ctx.cuh"
+#include <algorithm>
 
 namespace eb {
 
@@ -90,10 +91,14 @@ static int32_t ensure_halo(eb200_ctx* c, size_t doubles) {
 }
 
 // do_field_mpi_with_lengths: x then y then z, full extents in the other axes
+static int32_t field_bc_arrays(eb200_ctx* c, Arr3 A, int ncomp);
 int32_t field_bc(eb200_ctx* c, int first_comp, int ncomp) {
-  ScopedPhase ph(c, "halo");
   Arr3 A;
   for (int k = 0; k < 3; ++k) A.a[k] = c->f.f[first_comp + (k < ncomp ? k : 0)];
+  return field_bc_arrays(c, A, ncomp);
+}
+static int32_t field_bc_arrays(eb200_ctx* c, Arr3 A, int ncomp) {
+  ScopedPhase ph(c, "halo");
   for (int ax = 0; ax < c->ndims; ++ax) {
     const LineP p = line_params(c, ax);
     const bool per = c->bc_field[2 * ax] == EB200_BC_PERIODIC;
@@ -370,7 +375,81 @@ int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir) {
   return 0;
 }
 
-// current_finish (current_smooth.F90:29-45); smoothing / current correction are off
+// ---- smooth_current (current_smooth.F90:49-151, the strided compensated binomial filter) ----
+// one pass: interior of dst = alpha * src + beta * (the 2 * ND neighbours of src at +-stride),
+// neighbours summed in the reference's order (x-, x+, y-, y+, z-, z+)
+template <int ND>
+__global__ void __launch_bounds__(256) k_smooth_pass(GridP g, Arr3 src, Arr3 dst, double alpha, double beta, int stride,
+                                                     long long count) {
+  const long long cs = stride;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < count; t += (long long)gridDim.x * blockDim.x) {
+    const int ix = 1 + (int)(t % g.n[0]);
+    const long long r = t / g.n[0];
+    const int iy = ND >= 2 ? 1 + (int)(r % g.n[1]) : 1;
+    const int iz = ND >= 3 ? 1 + (int)(r / g.n[1]) : 1;
+    const long long i = g.idx(ix, iy, iz);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double* w = src.a[k];
+      double nb = w[i - cs * g.st[0]] + w[i + cs * g.st[0]];
+      if (ND >= 2) { nb = nb + w[i - cs * g.st[1]]; nb = nb + w[i + cs * g.st[1]]; }
+      if (ND >= 3) { nb = nb + w[i - cs * g.st[2]]; nb = nb + w[i + cs * g.st[2]]; }
+      dst.a[k][i] = __dadd_rn(__dmul_rn(alpha, w[i]), __dmul_rn(nb, beta));
+    }
+  }
+}
+template <int ND>
+__global__ void __launch_bounds__(256) k_copy_interior(GridP g, Arr3 src, Arr3 dst, long long count) {
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < count; t += (long long)gridDim.x * blockDim.x) {
+    const int ix = 1 + (int)(t % g.n[0]);
+    const long long r = t / g.n[0];
+    const int iy = ND >= 2 ? 1 + (int)(r % g.n[1]) : 1;
+    const int iz = ND >= 3 ? 1 + (int)(r / g.n[1]) : 1;
+    const long long i = g.idx(ix, iy, iz);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) dst.a[k][i] = src.a[k][i];
+  }
+}
+__global__ void k_sub_scalar(double* a, long long n, double v) {
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x)
+    a[t] = a[t] - v;
+}
+
+static int32_t smooth_current(eb200_ctx* c) {
+  const long long total = c->g.total;
+  if (!c->smooth_wk) EB_CUDA(c, cudaMalloc(&c->smooth_wk, (size_t)3 * total * sizeof(double)));
+  Arr3 J, W;
+  for (int k = 0; k < 3; ++k) { J.a[k] = c->f.f[JX + k]; W.a[k] = c->smooth_wk + (size_t)k * total; }
+  // wk = array, ghosts included (ng_l = MAX(sng, jng) = jng since strides <= ng)
+  EB_CUDA(c, cudaMemcpyAsync(c->smooth_wk, c->f.f[JX], (size_t)3 * total * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  long long count = c->g.n[0];
+  if (c->ndims >= 2) count *= c->g.n[1];
+  if (c->ndims >= 3) count *= c->g.n[2];
+  const int block = 256;
+  const int grid = (int)std::min<long long>((count + block - 1) / block, 148LL * 32);
+  double alpha = 0.5;
+  const double beta = (1.0 - alpha) / (2.0 * c->ndims);     // computed once, as in the reference
+  for (int it = 1; it <= c->smooth_its + c->smooth_comp_its; ++it) {
+    for (int stride : c->smooth_strides) {
+      EB_TRY(field_bc_arrays(c, W, 3));
+#define L(ND)                                                                                              \
+      if (c->ndims == ND) {                                                                                \
+        k_smooth_pass<ND><<<grid, block, 0, c->stream>>>(c->g, W, J, alpha, beta, stride, count);           \
+        k_copy_interior<ND><<<grid, block, 0, c->stream>>>(c->g, J, W, count);                             \
+      }
+      L(1) L(2) L(3)
+#undef L
+      c->launches += 2;
+    }
+    // the compensation weight takes effect only for passes after its + 1 (reference behaviour)
+    if (it > c->smooth_its) alpha = (double)c->smooth_its * 0.5 + 1.0;
+  }
+  // array(interior) = wk(interior): already equal after the last pass
+  EB_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+// current_finish (current_smooth.F90:29-45)
 int32_t current_finish(eb200_ctx* c) {
   {
     ScopedPhase ph(c, "halo");
@@ -378,7 +457,17 @@ int32_t current_finish(eb200_ctx* c) {
     EB_TRY(summation_bcs(c, c->f.f[JY], 1));
     EB_TRY(summation_bcs(c, c->f.f[JZ], 2));
   }
-  return field_bc(c, JX, 3);
+  EB_TRY(field_bc(c, JX, 3));
+  if (c->smooth) EB_TRY(smooth_current(c));
+  if (c->use_current_correction) {
+    ScopedPhase ph(c, "fields");
+    for (int k = 0; k < 3; ++k) {
+      k_sub_scalar<<<148 * 8, 256, 0, c->stream>>>(c->f.f[JX + k], c->g.total, c->initial_j[k]);
+      c->launches++;
+    }
+    EB_CUDA(c, cudaGetLastError());
+  }
+  return 0;
 }
 
 }  // namespace eb

@@ -122,7 +122,7 @@ int32_t eb200_destroy(eb200_ctx* c) {
   for (SpeciesD& sp : c->species) free_species(sp);
   for (int b = 0; b < 6; ++b) for (Laser& L : c->lasers[b]) { if (L.profile) cudaFree(L.profile); if (L.phase) cudaFree(L.phase); }
   void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->rec_scratch, c->cub_tmp, c->halo_send, c->halo_recv,
-                  c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho};
+                  c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho, c->smooth_wk};
   for (void* p : ptrs) if (p) cudaFree(p);
   free_pinned(c);
   if (c->h_counters) cudaFreeHost(c->h_counters);
@@ -219,6 +219,21 @@ int32_t eb200_set_solver(eb200_ctx* c, int32_t field_order, int32_t maxwell_solv
   if (field_order / 2 > c->ng) return fail(c, EB200_E_ARG, "field_order needs more ghost cells");
   c->field_order = field_order; c->maxwell_solver = maxwell_solver;
   if (coeffs) std::memcpy(c->coeffs, coeffs, 15 * sizeof(double));
+  return 0;
+}
+
+int32_t eb200_set_current_options(eb200_ctx* c, int32_t smooth, int32_t its, int32_t comp_its, int32_t nstrides,
+                                  const int32_t* strides, int32_t use_corr, const double initial_j[3]) {
+  CHECK_CTX(c);
+  if (its < 0 || comp_its < 0 || nstrides < 0 || (nstrides > 0 && !strides)) return fail(c, EB200_E_ARG, "bad smoothing parameters");
+  for (int k = 0; k < nstrides; ++k)
+    if (strides[k] < 1 || strides[k] > c->ng) return fail(c, EB200_E_ARG, "smooth_strides must lie in 1..ng");
+  if (use_corr && !initial_j) return fail(c, EB200_E_ARG, "current correction needs initial_j");
+  c->smooth = smooth != 0; c->smooth_its = its; c->smooth_comp_its = comp_its;
+  c->smooth_strides.assign(strides, strides + nstrides);
+  if (c->smooth_strides.empty()) c->smooth_strides.push_back(1);
+  c->use_current_correction = use_corr != 0;
+  for (int k = 0; k < 3; ++k) c->initial_j[k] = use_corr ? initial_j[k] : 0.0;
   return 0;
 }
 

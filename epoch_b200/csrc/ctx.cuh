@@ -108,6 +108,12 @@ struct eb200_ctx {
   bool add_laser[6] = {false, false, false, false, false, false};
   int field_order = 2, maxwell_solver = 0;
   double coeffs[15] = {0};
+  // current_finish options (current_smooth.F90)
+  int smooth = 0, smooth_its = 1, smooth_comp_its = 0;
+  std::vector<int> smooth_strides;
+  int use_current_correction = 0;
+  double initial_j[3] = {0, 0, 0};
+  double* smooth_wk = nullptr;      // 3 work arrays (allocated on first use)
   double* fbase = nullptr;     // 9 * total doubles
   eb::FieldP f;
   std::vector<eb::SpeciesD> species;

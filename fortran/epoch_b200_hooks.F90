@@ -67,6 +67,15 @@ CONTAINS
     CALL gpu_check(eb200_set_solver(gpu, field_order, maxwell_solver, &
         [alphax, alphay, alphaz, betaxy, betaxz, betayx, betayz, betazx, betazy, &
          gammax, gammay, gammaz, deltax, deltay, deltaz]))
+    ! current_finish options; initial_jx,jy,jz are valid after calc_initial_current (epoch3d.F90:140)
+    IF (ALLOCATED(smooth_strides)) THEN
+      CALL gpu_check(eb200_set_current_options(gpu, MERGE(1, 0, smooth_currents), smooth_its, smooth_comp_its, &
+          SIZE(smooth_strides), INT(smooth_strides, C_INT32_T), MERGE(1, 0, use_current_correction), &
+          [initial_jx, initial_jy, initial_jz]))
+    ELSE
+      CALL gpu_check(eb200_set_current_options(gpu, MERGE(1, 0, smooth_currents), smooth_its, smooth_comp_its, &
+          0, [1_C_INT32_T], MERGE(1, 0, use_current_correction), [initial_jx, initial_jy, initial_jz]))
+    END IF
     DO ispecies = 1, n_species
       bcp = INT(species_list(ispecies)%bc_particle, C_INT32_T)
       CALL gpu_check(eb200_set_species(gpu, ispecies - 1, species_list(ispecies)%charge, &

@@ -53,6 +53,14 @@ MODULE epoch_b200_iface
       INTEGER(C_INT32_T), VALUE :: field_order, maxwell_solver
       REAL(C_DOUBLE), INTENT(IN) :: coeffs(15)
     END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_current_options(ctx, smooth, smooth_its, smooth_comp_its, &
+        nstrides, strides, use_current_correction, initial_j) BIND(C, NAME='eb200_set_current_options')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: smooth, smooth_its, smooth_comp_its, nstrides, use_current_correction
+      INTEGER(C_INT32_T), INTENT(IN) :: strides(*)
+      REAL(C_DOUBLE), INTENT(IN) :: initial_j(3)
+    END FUNCTION
     INTEGER(C_INT32_T) FUNCTION eb200_set_species(ctx, ispecies, charge, mass, weight, immobile, &
         zero_current, species_type, bc_particle) BIND(C, NAME='eb200_set_species')
       IMPORT

@@ -112,6 +112,15 @@ int32_t EB200_NAME(set_field_bcs)(EB200_CTX*, const int32_t bc_field[6]);
 int32_t EB200_NAME(set_solver)(EB200_CTX*, int32_t field_order, int32_t maxwell_solver,
                                const double coeffs[15]);
 
+/* current_finish options (housekeeping/current_smooth.F90:29-151): the strided compensated
+ * binomial filter of smooth_current (smooth_its passes, smooth_comp_its = 0|1 extra pass, the
+ * deck's smooth_strides; strides <= ng) and use_current_correction, which subtracts the three
+ * scalars initial_jx,jy,jz that calc_initial_current (io/calc_df.F90:1292-1389) leaves on the
+ * host.  nstrides = 0 means the default stride list {1}; smooth = 0 switches the filter off. */
+int32_t EB200_NAME(set_current_options)(EB200_CTX*, int32_t smooth, int32_t smooth_its, int32_t smooth_comp_its,
+                                        int32_t nstrides, const int32_t* strides, int32_t use_current_correction,
+                                        const double initial_j[3]);
+
 /* ---- species / particles ---------------------------------------------------
  * TYPE particle_species scalars used by the push (shared_data.F90:184-263). */
 int32_t EB200_NAME(set_species)(EB200_CTX*, int32_t ispecies, double charge, double mass,

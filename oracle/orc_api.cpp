@@ -101,6 +101,20 @@ int32_t orc_set_field_bcs(orc_ctx* c, const int32_t bc_field[6]) {
   return 0;
 }
 
+int32_t orc_set_current_options(orc_ctx* c, int32_t smooth, int32_t its, int32_t comp_its, int32_t nstrides,
+                                const int32_t* strides, int32_t use_corr, const double initial_j[3]) {
+  if (!c) return EB200_E_ARG;
+  if (its < 0 || comp_its < 0 || nstrides < 0 || (nstrides > 0 && !strides)) return fail(c, EB200_E_ARG, "bad smoothing parameters");
+  for (int k = 0; k < nstrides; ++k)
+    if (strides[k] < 1 || strides[k] > c->s.ng) return fail(c, EB200_E_ARG, "smooth_strides must lie in 1..ng");
+  if (use_corr && !initial_j) return fail(c, EB200_E_ARG, "current correction needs initial_j");
+  c->s.smooth = smooth != 0; c->s.smooth_its = its; c->s.smooth_comp_its = comp_its;
+  c->s.smooth_strides.assign(strides, strides + nstrides);
+  c->s.use_current_correction = use_corr != 0;
+  for (int k = 0; k < 3; ++k) c->s.initial_j[k] = use_corr ? initial_j[k] : 0.0;
+  return 0;
+}
+
 int32_t orc_set_solver(orc_ctx* c, int32_t field_order, int32_t maxwell_solver, const double coeffs[15]) {
   if (!c) return EB200_E_ARG;
   if (field_order != 2 && field_order != 4 && field_order != 6) return fail(c, EB200_E_ARG, "field_order");

@@ -451,12 +451,50 @@ static void processor_summation_bcs(State& s, int comp, int flip_dir /*0..2*/) {
   }
 }
 
-// housekeeping/current_smooth.F90:29-45 (smoothing and current correction off)
+// smooth_array, housekeeping/current_smooth.F90:61-151 (default build: strided compensated
+// binomial filter).  wk holds the array with ghosts; every pass refreshes wk's ghosts with
+// field_bc, writes alpha * wk + beta * (neighbours at +-stride) into the array's interior and
+// copies that back into wk.  beta is computed once; alpha changes only after a pass with
+// it > its -- both exactly as the reference does.
+static void smooth_array(State& s, int comp) {
+  std::vector<double>& arr = s.f[comp];
+  std::vector<double> wk = arr;            // ng_l = MAX(sng, jng) = jng for strides <= ng
+  std::vector<int> strides = s.smooth_strides;
+  if (strides.empty()) strides.push_back(1);
+  double alpha = 0.5;
+  const double beta = (1.0 - alpha) / (2.0 * s.ndims);
+  for (int it = 1; it <= s.smooth_its + s.smooth_comp_its; ++it) {
+    for (int cs : strides) {
+      std::swap(arr, wk);                  // field_bc works on s.f[comp]
+      field_bc(s, comp);
+      std::swap(arr, wk);
+      for (int iz = (s.ndims >= 3 ? 1 : 1); iz <= (s.ndims >= 3 ? s.n[2] : 1); ++iz)
+        for (int iy = 1; iy <= (s.ndims >= 2 ? s.n[1] : 1); ++iy)
+          for (int ix = 1; ix <= s.n[0]; ++ix) {
+            const int64_t i = s.idx(ix, iy, iz);
+            double nb = wk[i - cs * s.st[0]] + wk[i + cs * s.st[0]];
+            if (s.ndims >= 2) { nb = nb + wk[i - cs * s.st[1]]; nb = nb + wk[i + cs * s.st[1]]; }
+            if (s.ndims >= 3) { nb = nb + wk[i - cs * s.st[2]]; nb = nb + wk[i + cs * s.st[2]]; }
+            arr[i] = alpha * wk[i] + nb * beta;
+          }
+      for (int iz = 1; iz <= (s.ndims >= 3 ? s.n[2] : 1); ++iz)
+        for (int iy = 1; iy <= (s.ndims >= 2 ? s.n[1] : 1); ++iy)
+          for (int ix = 1; ix <= s.n[0]; ++ix) { const int64_t i = s.idx(ix, iy, iz); wk[i] = arr[i]; }
+    }
+    if (it > s.smooth_its) alpha = (double)s.smooth_its * 0.5 + 1.0;
+  }
+}
+
+// housekeeping/current_smooth.F90:29-45
 void current_finish(State& s) {
   processor_summation_bcs(s, JX, 0);
   processor_summation_bcs(s, JY, 1);
   processor_summation_bcs(s, JZ, 2);
   field_bc(s, JX); field_bc(s, JY); field_bc(s, JZ);
+  if (s.smooth) { smooth_array(s, JX); smooth_array(s, JY); smooth_array(s, JZ); }
+  if (s.use_current_correction)
+    for (int k = 0; k < 3; ++k)
+      for (double& v : s.f[JX + k]) v = v - s.initial_j[k];
 }
 
 }  // namespace orc

@@ -79,6 +79,11 @@ struct State {
   bool add_laser[6] = {false, false, false, false, false, false};
   int field_order = 2, maxwell_solver = 0;
   double coeffs[15] = {0};
+  // current_finish options (housekeeping/current_smooth.F90)
+  bool smooth = false, use_current_correction = false;
+  int smooth_its = 1, smooth_comp_its = 0;
+  std::vector<int> smooth_strides;
+  double initial_j[3] = {0, 0, 0};
   // half-step scalars (fields.f90:821-830)
   double hdt = 0, hdtd[3] = {0, 0, 0}, cn[3] = {0, 0, 0}, fac = 0;
   std::vector<double> f[NFIELD];

@@ -271,3 +271,20 @@ def test_custom_stencil_goldens_on_gpu(product_abi, name):
     boundaries of this path): the reference's assertion and its recorded velocities."""
     from test_maxwell_solvers import custom_deck, check_custom
     check_custom(custom_deck(product_abi, name), name)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("fbc", ["periodic", "open"])
+def test_current_smoothing_and_correction(product_abi, oracle_abi, ndims, fbc):
+    """current_finish with smooth_current (2 passes + compensation pass, strides 1, 2, 3) and
+    use_current_correction, after a real push: CUDA == oracle, ghosts included."""
+    bc_field = [fbc, fbc] + ["periodic"] * (2 * ndims - 2)
+    pbc = ["reflect" if fbc == "open" else "periodic"] * 2 + ["periodic"] * (2 * ndims - 2)
+    sims = [make_plasma(a, ndims, "triangle", [16, 12, 10], seed=8, ppc=3, bc_field=bc_field, bcs=pbc)
+            for a in (product_abi, oracle_abi)]
+    for s in sims:
+        s.ctx.set_current_options(smooth=True, smooth_its=2, smooth_comp_its=1, strides=[1, 2, 3],
+                                  initial_j=[1.0e9, -2.0e9, 0.5e9])
+        s.step_once()
+    compare_fields(sims[0], sims[1], ALL9, tol=1e-11)

@@ -212,3 +212,68 @@ def test_factored_esirkepov():
                         idx[A], idx[P], idx[Q] = a, u, v
                         M[A][tuple(idx)] = -C[A, a] * (g[P, u] * qf1[v] + h[P, u] * qf2[v])
         assert np.abs(M - J).max() < 1e-14 * np.abs(J).max() + 1e-15
+
+
+# ---- current_finish options (housekeeping/current_smooth.F90) ----------------------------------
+def _random_j(sim, seed=21):
+    rng = np.random.default_rng(seed)
+    shp = sim.ctx._np_shape()
+    j = {k: rng.normal(0, 1.0, shp) for k in ("jx", "jy", "jz")}
+    sim.ctx.upload_fields(**j)
+    sim.ctx.set_time(sim.dt, 0.0, 0)
+    return j
+
+
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+def test_binomial_filter_known_answers(oracle_abi, ndims):
+    """One pass, stride 1, periodic: J' = J/2 + (sum of the 2*ND neighbours)/(4*ND) -- checked
+    against numpy rolls; a constant is a fixed point; the total is conserved."""
+    n = [12, 10, 8][:ndims]
+    sim = Simulation(ndims, n, [0.0] * ndims, [1e-6 * k for k in n], abi=oracle_abi)
+    j = _random_j(sim)
+    sim.ctx.set_current_options(smooth=True)
+    sim.ctx.current_finish()
+    got = sim.ctx.interior(sim.ctx.download_fields(["jx"])["jx"])
+    # what current_finish does before the filter on one periodic rank: ghost sums, then halos
+    sim2 = Simulation(ndims, n, [0.0] * ndims, [1e-6 * k for k in n], abi=oracle_abi)
+    sim2.ctx.upload_fields(**j)
+    sim2.ctx.set_time(sim2.dt, 0.0, 0)
+    sim2.ctx.current_finish()
+    base = sim2.ctx.interior(sim2.ctx.download_fields(["jx"])["jx"])
+    nb = sum(np.roll(base, s, axis=a) for a in range(ndims) for s in (1, -1))
+    want = 0.5 * base + nb * (0.5 / (2 * ndims))
+    assert np.max(np.abs(got - want)) < 1e-14 * np.max(np.abs(base))
+    assert abs(got.sum() - base.sum()) < 1e-12 * np.abs(base).sum()
+
+
+def test_filter_passes_strides_and_correction(oracle_abi):
+    """its = 2 + compensation pass with strides (1, 2) equals five single passes applied by hand
+    (alpha stays 0.5 through pass its + 1, as in the reference); the current correction subtracts
+    the three scalars everywhere, ghosts included."""
+    n = [12, 10]
+    def fresh():
+        s = Simulation(2, n, [0.0, 0.0], [12e-6, 10e-6], abi=oracle_abi)
+        s.ctx.upload_fields(**j)
+        s.ctx.set_time(s.dt, 0.0, 0)
+        return s
+    s0 = Simulation(2, n, [0.0, 0.0], [12e-6, 10e-6], abi=oracle_abi)
+    j = _random_j(s0)
+    s0.ctx.current_finish()
+    base = s0.ctx.interior(s0.ctx.download_fields(["jy"])["jy"])
+    want = base
+    for it in range(3):
+        for cs in (1, 2):
+            nb = sum(np.roll(want, s * cs, axis=a) for a in range(2) for s in (1, -1))
+            want = 0.5 * want + nb * 0.125
+    s1 = fresh()
+    s1.ctx.set_current_options(smooth=True, smooth_its=2, smooth_comp_its=1, strides=[1, 2])
+    s1.ctx.current_finish()
+    got = s1.ctx.interior(s1.ctx.download_fields(["jy"])["jy"])
+    assert np.max(np.abs(got - want)) < 1e-13 * np.max(np.abs(base))
+    s2 = fresh()
+    s2.ctx.set_current_options(initial_j=[0.25, -1.5, 3.0])
+    s2.ctx.current_finish()
+    a = s2.ctx.download_fields(["jx", "jy", "jz"])
+    b = s0.ctx.download_fields(["jx", "jy", "jz"])
+    for k, v in zip(("jx", "jy", "jz"), (0.25, -1.5, 3.0)):
+        assert np.array_equal(a[k], b[k] - v)
