@@ -25,6 +25,8 @@ SIGNATURES = {
     "set_time": (i32, [c_ctx_p, f64, f64, i32]),
     "set_field_bcs": (i32, [c_ctx_p, pi32]),
     "set_solver": (i32, [c_ctx_p, i32, i32, pf64]),
+    "set_window_fields": (i32, [c_ctx_p, pf64, pf64, pf64, pf64, pf64, pf64]),
+    "shift_window": (i32, [c_ctx_p, f64, f64, f64, f64, f64]),
     "set_current_options": (i32, [c_ctx_p, i32, i32, i32, i32, pi32, i32, pf64]),
     "set_species": (i32, [c_ctx_p, i32, f64, f64, f64, i32, i32, i32, pi32]),
     "upload_particles": (i32, [c_ctx_p, i32, i64, C.c_void_p, i32]),

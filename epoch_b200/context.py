@@ -101,6 +101,18 @@ class PicContext:
         self._ck(self.abi.set_solver(self._ctx, field_order, maxwell_solver,
                                      _f64(coeffs if coeffs is not None else [0.0] * 15)))
 
+    def set_window_fields(self, planes=None):
+        """ex_x_max .. bz_x_max of setup_field_boundaries (setup.F90:425-470); None = zeros."""
+        planes = planes or {}
+        keep = [None if planes.get(k) is None else np.ascontiguousarray(planes[k], dtype=np.float64)
+                for k in ("ex", "ey", "ez", "bx", "by", "bz")]
+        ptrs = [None if a is None else a.ctypes.data_as(C.POINTER(C.c_double)) for a in keep]
+        self._ck(self.abi.set_window_fields(self._ctx, *ptrs))
+
+    def shift_window(self, x_grid_min_local, x_min_local, x_max_local, x_min, x_max):
+        """one cell of shift_window (window.F90:62-94) minus insert_particles"""
+        self._ck(self.abi.shift_window(self._ctx, x_grid_min_local, x_min_local, x_max_local, x_min, x_max))
+
     def set_current_options(self, smooth=False, smooth_its=1, smooth_comp_its=0, strides=None,
                             initial_j=None):
         """current_finish options (current_smooth.F90:29-151): binomial filter passes and

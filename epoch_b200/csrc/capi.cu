@@ -122,7 +122,7 @@ int32_t eb200_destroy(eb200_ctx* c) {
   for (SpeciesD& sp : c->species) free_species(sp);
   for (int b = 0; b < 6; ++b) for (Laser& L : c->lasers[b]) { if (L.profile) cudaFree(L.profile); if (L.phase) cudaFree(L.phase); }
   void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->rec_scratch, c->cub_tmp, c->halo_send, c->halo_recv,
-                  c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho, c->smooth_wk};
+                  c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho, c->smooth_wk, c->win_planes};
   for (void* p : ptrs) if (p) cudaFree(p);
   free_pinned(c);
   if (c->h_counters) cudaFreeHost(c->h_counters);
@@ -235,6 +235,19 @@ int32_t eb200_set_current_options(eb200_ctx* c, int32_t smooth, int32_t its, int
   c->use_current_correction = use_corr != 0;
   for (int k = 0; k < 3; ++k) c->initial_j[k] = use_corr ? initial_j[k] : 0.0;
   return 0;
+}
+
+int32_t eb200_set_window_fields(eb200_ctx* c, const double* ex, const double* ey, const double* ez, const double* bx,
+                                const double* by, const double* bz) {
+  CHECK_CTX(c); NEED_GRID(c);
+  const double* pl[6] = {ex, ey, ez, bx, by, bz};
+  return set_window_planes(c, pl);
+}
+int32_t eb200_shift_window(eb200_ctx* c, double x_grid_min_local, double x_min_local, double x_max_local, double x_min,
+                           double x_max) {
+  CHECK_CTX(c); NEED_GRID(c);
+  if (c->g.n[0] < 3) return fail(c, EB200_E_ARG, "moving window needs nx >= 3");
+  return shift_window(c, x_grid_min_local, x_min_local, x_max_local, x_min, x_max);
 }
 
 int32_t eb200_set_species(eb200_ctx* c, int32_t isp, double charge, double mass, double weight, int32_t immobile,

@@ -114,6 +114,7 @@ struct eb200_ctx {
   int use_current_correction = 0;
   double initial_j[3] = {0, 0, 0};
   double* smooth_wk = nullptr;      // 3 work arrays (allocated on first use)
+  double* win_planes = nullptr;     // moving window: e*_x_max, b*_x_max planes (6 x y-z extent with ghosts)
   double* fbase = nullptr;     // 9 * total doubles
   eb::FieldP f;
   std::vector<eb::SpeciesD> species;
@@ -167,6 +168,10 @@ int32_t staged_h2d(eb200_ctx* c, const void* host, size_t bytes, size_t granule,
 int32_t staged_d2h(eb200_ctx* c, void* host, size_t bytes, size_t granule,
                    const std::function<const void*(size_t, size_t)>& src);
 void free_pinned(eb200_ctx* c);
+// window.cu
+int32_t set_window_planes(eb200_ctx* c, const double* const planes[6]);
+int32_t shift_window(eb200_ctx* c, double grid_min_local, double min_local, double max_local, double gmin, double gmax);
+int32_t field_bc(eb200_ctx* c, int first_comp, int ncomp);
 #define EB_CUDA(c, call)                                                                 \
   do {                                                                                   \
     cudaError_t e__ = (call);                                                            \

@@ -292,6 +292,63 @@ class Simulation:
         ctx.set_time(dt_store, self.time, self.step)
         self._started = True
 
+    # -- moving window (housekeeping/window.F90) ---------------------------------
+    def enable_window(self, v_x, start_time=0.0, stop_time=1e300, insert=None, planes=None):
+        """move_window = T.  `insert(sim, x0)` stands for insert_particles (:198-358): it returns,
+        per species, the particles of the incoming cell column [x0, x0 + dx) of this rank (or None);
+        in EPOCH this is the deck's density / temperature expressions and the host RNG."""
+        self.window = dict(v_x=v_x, start=start_time, stop=stop_time, insert=insert, started=False, frac=0.0)
+        self.window_offset = 0.0
+        self.ctx.set_window_fields(planes)
+        # global grid bookkeeping of shift_window: x_grid_min (centre of global cell 1), xb_min, x_min, x_max
+        self._x_grid_min = self.grid_min[0]
+        self._xb_min = self.mins[0]
+        self._x_min, self._x_max = self.mins[0], self.maxs[0]
+
+    def _shift_window(self, cells):
+        dx = self.d[0]
+        for _ in range(cells):
+            if self.window["insert"] is not None and self.coords[0] == self.nprocdir[0] - 1:
+                x_grid_max = self._x_grid_min + (self.n_global[0] - 1) * dx
+                x0 = x_grid_max + 0.5 * dx
+                new = self.window["insert"](self, x0)
+                for isp, P in enumerate(new or []):
+                    if P is not None and len(P):
+                        self.ctx.upload_particles(isp, P, append=True)
+            # shift the box (window.F90:74-86) and setup_grid_x (utilities.f90:343-373)
+            self._x_grid_min = self._x_grid_min + dx
+            self._xb_min = self._xb_min + dx
+            self._x_min = self._xb_min
+            self._x_max = (self._xb_min + self.n_global[0] * dx)
+            self.grid_min[0] = self._x_grid_min
+            self.grid_min_local[0] = self._x_grid_min + (self.cell_min[0] - 1) * dx
+            grid_max_local = self._x_grid_min + (self.cell_max[0] - 1) * dx
+            self.min_local[0] = self.grid_min_local[0] + (0 - 0.5) * dx
+            self.max_local[0] = grid_max_local - (0 - 0.5) * dx
+            self.mins = (self._x_min,) + tuple(self.mins[1:])
+            self.maxs = (self._x_max,) + tuple(self.maxs[1:])
+            self.ctx.shift_window(self.grid_min_local[0], self.min_local[0], self.max_local[0], self._x_min, self._x_max)
+
+    def moving_window(self):
+        """moving_window (window.F90:388-436), called where epoch3d.F90:248 does"""
+        w = getattr(self, "window", None)
+        if w is None:
+            return
+        if not w["started"]:
+            if w["start"] <= self.time < w["stop"]:
+                w["frac"] = 0.0
+                w["started"] = True
+        if w["started"]:
+            if self.time >= w["stop"] or w["v_x"] <= 0.0:
+                return
+            w["frac"] = w["frac"] + self.dt * w["v_x"] / self.d[0]
+            cells = int(math.floor(w["frac"]))
+            if cells > 0:
+                self.window_offset = self.window_offset + float(cells) * self.d[0]
+                self._shift_window(cells)
+                self.ctx.particle_bcs()
+                w["frac"] = w["frac"] - float(cells)
+
     def finished(self):
         return self.t_end is not None and self.time >= self.t_end
 
@@ -317,3 +374,4 @@ class Simulation:
         ctx.set_time(self.dt, self.time, self.step)
         self._laser_step()
         ctx.update_eb_fields_final()
+        self.moving_window()             # epoch3d.F90:248

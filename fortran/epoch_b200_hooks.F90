@@ -177,6 +177,16 @@ CONTAINS
     CALL gpu_check(eb200_current_finish(gpu))
   END SUBROUTINE current_finish
 
+  ! Device half of shift_window (window.F90:62-94) for one cell.  In window.F90 the loop body becomes
+  !   CALL insert_particles_to_gpu      ! the reference's insert_particles building a partlist that is
+  !                                     ! packed (pack_particle) and passed to eb200_append_particles
+  !   <shift x_grid_min, xb_min, x_min, x_max; CALL setup_grid_x>        (unchanged host code)
+  !   CALL gpu_shift_window
+  ! and remove_particles / shift_fields are no longer called on the host.
+  SUBROUTINE gpu_shift_window
+    CALL gpu_check(eb200_shift_window(gpu, x_grid_min_local, x_min_local, x_max_local, x_min, x_max))
+  END SUBROUTINE gpu_shift_window
+
   SUBROUTINE update_eb_fields_final         ! fields.f90:851
     CALL gpu_check(eb200_set_time(gpu, dt, time, step))
     CALL gpu_laser_step

@@ -141,6 +141,18 @@ MODULE epoch_b200_iface
       IMPORT
       TYPE(C_PTR), VALUE :: ctx
     END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_shift_window(ctx, x_grid_min_local, x_min_local, x_max_local, x_min, x_max) &
+        BIND(C, NAME='eb200_shift_window')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      REAL(C_DOUBLE), VALUE :: x_grid_min_local, x_min_local, x_max_local, x_min, x_max
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_window_fields(ctx, ex_x_max, ey_x_max, ez_x_max, bx_x_max, by_x_max, &
+        bz_x_max) BIND(C, NAME='eb200_set_window_fields')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      REAL(C_DOUBLE), INTENT(IN) :: ex_x_max(*), ey_x_max(*), ez_x_max(*), bx_x_max(*), by_x_max(*), bz_x_max(*)
+    END FUNCTION
     INTEGER(C_INT32_T) FUNCTION eb200_particle_bcs(ctx) BIND(C, NAME='eb200_particle_bcs')
       IMPORT
       TYPE(C_PTR), VALUE :: ctx

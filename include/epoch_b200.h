@@ -121,6 +121,22 @@ int32_t EB200_NAME(set_current_options)(EB200_CTX*, int32_t smooth, int32_t smoo
                                         int32_t nstrides, const int32_t* strides, int32_t use_current_correction,
                                         const double initial_j[3]);
 
+/* Moving window (housekeeping/window.F90).  shift_window moves the window by ONE cell, i.e. one
+ * iteration of the loop in shift_window (window.F90:62-94): it takes this rank's new
+ * x_grid_min_local, x_min_local, x_max_local (setup_grid_x, utilities.f90:343-373) and the new
+ * global x_min, x_max, drops the particles with pos_x < x_min on an x_min boundary rank
+ * (remove_particles, :362-384) and shifts all nine grid arrays one cell towards -x, refreshes
+ * their halos and fixes the incoming cells on an x_max boundary rank (shift_fields, :98-194).
+ * The new plasma of insert_particles (:198-358; deck expressions + host RNG) is appended by the
+ * host with append_particles BEFORE the call; particle_bcs follows it (moving_window, :425).
+ * set_window_fields uploads the planes ex_x_max .. bz_x_max of setup_field_boundaries
+ * (setup.F90:425-470), each (1-ng:ny+ng [, 1-ng:nz+ng]), NULL = zero. */
+int32_t EB200_NAME(set_window_fields)(EB200_CTX*, const double* ex_x_max, const double* ey_x_max,
+                                      const double* ez_x_max, const double* bx_x_max,
+                                      const double* by_x_max, const double* bz_x_max);
+int32_t EB200_NAME(shift_window)(EB200_CTX*, double x_grid_min_local, double x_min_local, double x_max_local,
+                                 double x_min, double x_max);
+
 /* ---- species / particles ---------------------------------------------------
  * TYPE particle_species scalars used by the push (shared_data.F90:184-263). */
 int32_t EB200_NAME(set_species)(EB200_CTX*, int32_t ispecies, double charge, double mass,

@@ -101,6 +101,25 @@ int32_t orc_set_field_bcs(orc_ctx* c, const int32_t bc_field[6]) {
   return 0;
 }
 
+int32_t orc_set_window_fields(orc_ctx* c, const double* ex, const double* ey, const double* ez, const double* bx,
+                              const double* by, const double* bz) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  const double* pl[6] = {ex, ey, ez, bx, by, bz};
+  const size_t cnt = (size_t)(c->s.total / (c->s.n[0] + 2 * c->s.ngd[0]));
+  for (int k = 0; k < 6; ++k) {
+    c->s.win_planes[k].assign(cnt, 0.0);
+    if (pl[k]) std::copy(pl[k], pl[k] + cnt, c->s.win_planes[k].begin());
+  }
+  return 0;
+}
+int32_t orc_shift_window(orc_ctx* c, double x_grid_min_local, double x_min_local, double x_max_local, double x_min,
+                         double x_max) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  if (c->s.n[0] < 3) return fail(c, EB200_E_ARG, "moving window needs nx >= 3");
+  orc::shift_window(c->s, x_grid_min_local, x_min_local, x_max_local, x_min, x_max);
+  return 0;
+}
+
 int32_t orc_set_current_options(orc_ctx* c, int32_t smooth, int32_t its, int32_t comp_its, int32_t nstrides,
                                 const int32_t* strides, int32_t use_corr, const double initial_j[3]) {
   if (!c) return EB200_E_ARG;

@@ -497,4 +497,57 @@ void current_finish(State& s) {
       for (double& v : s.f[JX + k]) v = v - s.initial_j[k];
 }
 
+// One iteration of shift_window's loop without insert_particles (housekeeping/window.F90:62-194,
+// :362-384): grid scalars of setup_grid_x, remove_particles, shift_fields.
+void shift_window(State& s, double grid_min_local, double min_local, double max_local, double gmin, double gmax) {
+  s.grid_min_local[0] = grid_min_local; s.min_local[0] = min_local; s.max_local[0] = max_local;
+  s.gmin[0] = gmin; s.gmax[0] = gmax;
+  if (s.min_bnd[0]) {
+    for (Species& sp : s.species) {
+      if (!sp.defined) continue;
+      size_t w = 0;
+      for (size_t i = 0; i < sp.count(); ++i) {
+        if (sp.pos[0][i] < gmin) continue;               // current%part_pos(1) < x_min: destroyed
+        if (w != i) {
+          for (int d = 0; d < 3; ++d) { if (d < s.ndims) sp.pos[d][w] = sp.pos[d][i]; sp.p[d][w] = sp.p[d][i]; }
+          sp.w[w] = sp.w[i];
+        }
+        ++w;
+      }
+      for (int d = 0; d < 3; ++d) { if (d < s.ndims) sp.pos[d].resize(w); sp.p[d].resize(w); }
+      sp.w.resize(w);
+    }
+  }
+  const int len = s.n[0] + 2 * s.ngd[0];
+  const int64_t nlines = s.total / len;
+  for (int f = 0; f < NFIELD; ++f) {
+    double* a = s.f[f].data();
+    for (int64_t l = 0; l < nlines; ++l)
+      for (int i = 0; i < len - 1; ++i) a[l * len + i] = a[l * len + i + 1];
+    field_bc(s, f);
+  }
+  if (s.max_bnd[0]) {
+    double *ex = s.f[EX].data(), *ey = s.f[EY].data(), *ez = s.f[EZ].data();
+    double *bx = s.f[BX].data(), *by = s.f[BY].data(), *bz = s.f[BZ].data();
+    const int nx = s.n[0];
+    for (int64_t l = 0; l < nlines; ++l) {
+      const int64_t o = l * len + s.ngd[0] - 1;          // o + i = element with x index i
+      auto pl = [&](int k) { return s.win_planes[k].empty() ? 0.0 : s.win_planes[k][l]; };
+      ex[o + nx] = pl(0);
+      ex[o + nx + 1] = pl(0);
+      ey[o + nx + 1] = pl(1);
+      ez[o + nx + 1] = pl(2);
+      ex[o + nx - 1] = 0.5 * (ex[o + nx - 2] + ex[o + nx]);
+      ey[o + nx] = 0.5 * (ey[o + nx - 1] + ey[o + nx + 1]);
+      ez[o + nx] = 0.5 * (ez[o + nx - 1] + ez[o + nx + 1]);
+      bx[o + nx + 1] = pl(3);
+      by[o + nx] = pl(4);
+      bz[o + nx] = pl(5);
+      bx[o + nx] = 0.5 * (bx[o + nx - 1] + bx[o + nx + 1]);
+      by[o + nx - 1] = 0.5 * (by[o + nx - 2] + by[o + nx]);
+      bz[o + nx - 1] = 0.5 * (bz[o + nx - 2] + bz[o + nx]);
+    }
+  }
+}
+
 }  // namespace orc

@@ -84,6 +84,7 @@ struct State {
   int smooth_its = 1, smooth_comp_its = 0;
   std::vector<int> smooth_strides;
   double initial_j[3] = {0, 0, 0};
+  std::vector<double> win_planes[6];   // moving window: e*_x_max, b*_x_max (setup.F90:425-470)
   // half-step scalars (fields.f90:821-830)
   double hdt = 0, hdtd[3] = {0, 0, 0}, cn[3] = {0, 0, 0}, fac = 0;
   std::vector<double> f[NFIELD];
@@ -113,6 +114,7 @@ void bfield_final_bcs(State& s);
 void update_eb_fields_half(State& s);
 void update_eb_fields_final(State& s);
 void current_finish(State& s);
+void shift_window(State& s, double grid_min_local, double min_local, double max_local, double gmin, double gmax);
 // orc_particles.cpp
 void push_particles(State& s);
 void particle_bcs(State& s);

@@ -18,6 +18,7 @@ from epoch_b200.driver import Simulation, SpeciesSpec, Q0, M0, C  # noqa: E402
 AXIS = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 STEPS = int(sys.argv[2]) if len(sys.argv) > 2 else 4
 SHAPE = sys.argv[3] if len(sys.argv) > 3 else "triangle"
+WINDOW = len(sys.argv) > 4 and sys.argv[4] == "window"      # moving window at 0.9 c (x decomposition, open x boundaries)
 N = [16, 12, 20]
 CELL = 1e-6
 
@@ -42,8 +43,14 @@ def build(abi, rank, nproc, nccl_id, device):
     nprocdir[AXIS] = nproc
     sp = [SpeciesSpec("e", -Q0, M0, density=1e25, temperature=(1e6,) * 3),
           SpeciesSpec("p", Q0, 1836.2 * M0, density=1e25, temperature=(1e6,) * 3)]
+    kw = {}
+    if WINDOW:
+        obc = ["open", "open"] + ["periodic"] * 4
+        kw = dict(bc_field=obc)
+        for s in sp:
+            s.bcs = obc
     sim = Simulation(3, N, [0.0] * 3, [n * CELL for n in N], shape=SHAPE, species=sp, abi=abi, device=device,
-                     rank=rank, nproc=nproc, nprocdir=tuple(nprocdir), nccl_id=nccl_id)
+                     rank=rank, nproc=nproc, nprocdir=tuple(nprocdir), nccl_id=nccl_id, **kw)
     rng = np.random.default_rng(11)
     npart = 6 * N[0] * N[1] * N[2]
     for isp, s in enumerate(sp):
@@ -57,6 +64,26 @@ def build(abi, rank, nproc, nccl_id, device):
             own &= (P[:, d] >= sim.min_local[d]) & (P[:, d] < sim.max_local[d])
         sim.ctx.upload_particles(isp, P[own])
     sim.ctx.upload_fields(**fields_on(sim))
+    if WINDOW:
+        shifts = [0]
+
+        def insert(s_, x0):
+            # the incoming column over the full y-z extent (only the last x rank inserts): the same
+            # particles whatever the decomposition along x
+            shifts[0] += 1
+            r = np.random.default_rng([5, shifts[0]])
+            n = 3 * N[1] * N[2]
+            out = []
+            for isp, spc in enumerate(sp):
+                P = np.empty((n, 7))
+                P[:, 0] = x0 + r.random(n) * CELL
+                P[:, 1] = r.uniform(0.0, N[1] * CELL, n)
+                P[:, 2] = r.uniform(0.0, N[2] * CELL, n)
+                P[:, 3:6] = r.normal(0.0, 0.3, (n, 3)) * spc.mass * C
+                P[:, 6] = 1e25 * CELL ** 3 / 6 * (3.0 + shifts[0] + np.arange(n) / n + 0.5 * isp)
+                out.append(P)
+            return out
+        sim.enable_window(v_x=0.9 * C, insert=insert)
     return sim
 
 
@@ -96,7 +123,7 @@ def main():
             # periodic wrap: compare positions modulo the box length
             for d in range(3):
                 L = N[d] * CELL
-                dx = np.abs(A[:, d] - B[:, d]); dx = np.minimum(dx, L - dx)
+                dx = np.abs(A[:, d] - B[:, d]); dx = np.minimum(dx, np.abs(L - dx))
                 if dx.max() / L > 1e-11: print("pos", isp, d, dx.max() / L); ok = False
             e = np.abs(A[:, 3:6] - B[:, 3:6]).max() / np.abs(B[:, 3:6]).max()
             if e > 1e-11: print("mom", isp, e); ok = False

@@ -288,3 +288,19 @@ def test_current_smoothing_and_correction(product_abi, oracle_abi, ndims, fbc):
                                   initial_j=[1.0e9, -2.0e9, 0.5e9])
         s.step_once()
     compare_fields(sims[0], sims[1], ALL9, tol=1e-11)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndims,shape", [(1, "triangle"), (2, "triangle"), (2, "tophat"), (3, "triangle"), (3, "bspline3")])
+def test_moving_window(product_abi, oracle_abi, ndims, shape):
+    """housekeeping/window.F90 through the ABI: a window at 0.9 c with particle insertion on the
+    right, removal on the left, field shift + incoming-cell fix, 12 steps (4-7 shifts): CUDA ==
+    oracle for fields and every particle."""
+    from test_window import window_deck
+    sims = [window_deck(a, ndims, shape) for a in (product_abi, oracle_abi)]
+    for s in sims:
+        for _ in range(12):
+            s.step_once()
+    assert sims[0].window_offset == sims[1].window_offset > 3 * sims[0].d[0]
+    compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
+    compare_particles(sims[0], sims[1], tol=1e-10)

@@ -23,3 +23,14 @@ def test_two_ranks_equal_one(axis, shape):
            "--master-port", str(29611 + axis), os.path.join(ROOT, "tests", "mgpu_worker.py"), str(axis), "4", shape]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_two_ranks_moving_window():
+    """moving window with the domain cut along x: insertion on the last rank, removal on the first,
+    shifted fields exchanged through the halos -- equals the single-GPU run"""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29621", os.path.join(ROOT, "tests", "mgpu_worker.py"), "0", "8", "triangle", "window"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
