@@ -25,6 +25,7 @@ SIGNATURES = {
     "set_time": (i32, [c_ctx_p, f64, f64, i32]),
     "set_field_bcs": (i32, [c_ctx_p, pi32]),
     "set_solver": (i32, [c_ctx_p, i32, i32, pf64]),
+    "set_cpml": (i32, [c_ctx_p, i32, pf64, pf64, pf64, pf64, pf64, pf64, i32, i32, i32, i32, i32, i32]),
     "set_window_fields": (i32, [c_ctx_p, pf64, pf64, pf64, pf64, pf64, pf64]),
     "shift_window": (i32, [c_ctx_p, f64, f64, f64, f64, f64]),
     "set_current_options": (i32, [c_ctx_p, i32, i32, i32, i32, pi32, i32, pf64]),

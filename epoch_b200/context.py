@@ -101,6 +101,15 @@ class PicContext:
         self._ck(self.abi.set_solver(self._ctx, field_order, maxwell_solver,
                                      _f64(coeffs if coeffs is not None else [0.0] * 15)))
 
+    def set_cpml(self, axis, kappa_e, kappa_b, sigma_e, sigma_b, a_e, a_b, min_start, min_end, max_start, max_end,
+                 laser_idx_min=-1, laser_idx_max=-1):
+        """what set_cpml_helpers leaves on the host for one axis (boundary.F90:1989-2479)"""
+        arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in (kappa_e, kappa_b, sigma_e, sigma_b, a_e, a_b)]
+        assert all(len(a) == self.n[axis] + 2 * self.ng for a in arrs)
+        self._ck(self.abi.set_cpml(self._ctx, axis, *[a.ctypes.data_as(C.POINTER(C.c_double)) for a in arrs],
+                                   int(min_start), int(min_end), int(max_start), int(max_end),
+                                   int(laser_idx_min), int(laser_idx_max)))
+
     def set_window_fields(self, planes=None):
         """ex_x_max .. bz_x_max of setup_field_boundaries (setup.F90:425-470); None = zeros."""
         planes = planes or {}

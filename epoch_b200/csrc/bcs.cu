@@ -97,6 +97,11 @@ int32_t field_bc(eb200_ctx* c, int first_comp, int ncomp) {
   for (int k = 0; k < 3; ++k) A.a[k] = c->f.f[first_comp + (k < ncomp ? k : 0)];
   return field_bc_arrays(c, A, ncomp);
 }
+int32_t field_bc_array(eb200_ctx* c, double* a) {
+  Arr3 A;
+  for (int k = 0; k < 3; ++k) A.a[k] = a;
+  return field_bc_arrays(c, A, 1);
+}
 static int32_t field_bc_arrays(eb200_ctx* c, Arr3 A, int ncomp) {
   ScopedPhase ph(c, "halo");
   for (int ax = 0; ax < c->ndims; ++ax) {
@@ -186,7 +191,7 @@ static int32_t physical_bcs(eb200_ctx* c, bool efield) {
           m.mode[k] = efield ? (normal ? 1 : 2) : (normal ? 2 : 1);
         }
         if (pass == 1 && (bc == EB200_BC_CLAMP || bc == EB200_BC_SIMPLE_LASER || bc == EB200_BC_SIMPLE_OUTFLOW)) m.mode[k] = 1;
-        if (pass == 1 && bc == EB200_BC_ZERO_GRADIENT) m.mode[k] = 2;
+        if (pass == 1 && (bc == EB200_BC_ZERO_GRADIENT || bc == EB200_BC_CPML_LASER || bc == EB200_BC_CPML_OUTFLOW)) m.mode[k] = 2;
         any = any || m.mode[k] != 0;
       }
       if (!any) continue;
@@ -270,6 +275,7 @@ static int32_t outflow_bcs(eb200_ctx* c, int b) {
   OutflowP p;
   p.a = b / 2; p.t1 = (p.a + 1) % 3; p.t2 = (p.a + 2) % 3; p.is_max = b & 1; p.nd = c->ndims;
   p.lp = p.is_max ? g.n[p.a] : 1;
+  if (c->bc_field[b] == EB200_BC_CPML_LASER) p.lp = c->cpml_laser_idx[b];     // laser.f90:529-531
   const double dtc2 = c->dt * (C0 * C0);
   const double la = dtc2 / g.d[p.a];
   p.l1 = p.t1 < c->ndims ? dtc2 / g.d[p.t1] : 0.0;

@@ -122,7 +122,8 @@ int32_t eb200_destroy(eb200_ctx* c) {
   for (SpeciesD& sp : c->species) free_species(sp);
   for (int b = 0; b < 6; ++b) for (Laser& L : c->lasers[b]) { if (L.profile) cudaFree(L.profile); if (L.phase) cudaFree(L.phase); }
   void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->rec_scratch, c->cub_tmp, c->halo_send, c->halo_recv,
-                  c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho, c->smooth_wk, c->win_planes};
+                  c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho, c->smooth_wk, c->win_planes, c->cpml_psi,
+                  c->cpml_prof[0], c->cpml_prof[1], c->cpml_prof[2]};
   for (void* p : ptrs) if (p) cudaFree(p);
   free_pinned(c);
   if (c->h_counters) cudaFreeHost(c->h_counters);
@@ -140,7 +141,8 @@ int32_t eb200_set_grid(eb200_ctx* c, const int32_t n_local[3], const int32_t n_g
   CHECK_CTX(c);
   if (!n_local || !d || !grid_min_local || !min_local || !max_local || !min_global || !max_global)
     return fail(c, EB200_E_ARG, "null argument");
-  if (cpml_thickness != 0) return fail(c, EB200_E_UNSUPPORTED, "CPML boundaries are outside the hot path (SURVEY 8f-2)");
+  if (cpml_thickness < 0) return fail(c, EB200_E_ARG, "cpml_thickness < 0");
+  c->cpml_thickness = cpml_thickness;
   GridP& g = c->g;
   g.ndims = c->ndims; g.shape = c->shape; g.ng = c->ng;
   long long stride = 1, ncell = 1;
@@ -193,19 +195,46 @@ int32_t eb200_set_field_bcs(eb200_ctx* c, const int32_t bc_field[6]) {
     int bc = i < 2 * c->ndims ? bc_field[i] : EB200_BC_PERIODIC;
     c->add_laser[i] = false;
     if (bc == EB200_BC_OTHER) bc = EB200_BC_CLAMP;
-    if (bc == EB200_BC_CPML_LASER || bc == EB200_BC_CPML_OUTFLOW)
-      return fail(c, EB200_E_UNSUPPORTED, "CPML boundaries are outside the hot path (SURVEY 8f-2)");
-    if (bc == EB200_BC_SIMPLE_LASER) c->add_laser[i] = true;
+    if (bc == EB200_BC_SIMPLE_LASER) c->add_laser[i] = true;       // cpml_laser: set by set_cpml (one rank only)
     if (bc == EB200_BC_REFLECT) bc = EB200_BC_CLAMP;
     if (bc == EB200_BC_OPEN) bc = EB200_BC_SIMPLE_OUTFLOW;
     if (bc != EB200_BC_PERIODIC && bc != EB200_BC_CLAMP && bc != EB200_BC_SIMPLE_LASER && bc != EB200_BC_SIMPLE_OUTFLOW &&
-        bc != EB200_BC_ZERO_GRADIENT && bc != EB200_BC_CONDUCT)
+        bc != EB200_BC_ZERO_GRADIENT && bc != EB200_BC_CONDUCT && bc != EB200_BC_CPML_LASER && bc != EB200_BC_CPML_OUTFLOW)
       return fail(c, EB200_E_ARG, "unrecognised field boundary code");
     c->bc_field[i] = bc;
   }
   for (int d = 0; d < c->ndims; ++d)
     if ((c->bc_field[2 * d] == EB200_BC_PERIODIC) != (c->bc_field[2 * d + 1] == EB200_BC_PERIODIC))
       return fail(c, EB200_E_ARG, "periodic field boundaries must come in min/max pairs");
+  c->cpml_on = false;
+  for (int i = 0; i < 2 * c->ndims; ++i)
+    if (c->bc_field[i] == EB200_BC_CPML_LASER || c->bc_field[i] == EB200_BC_CPML_OUTFLOW) c->cpml_on = true;
+  return 0;
+}
+
+int32_t eb200_set_cpml(eb200_ctx* c, int32_t axis, const double* kappa_e, const double* kappa_b, const double* sigma_e,
+                       const double* sigma_b, const double* a_e, const double* a_b, int32_t min_start, int32_t min_end,
+                       int32_t max_start, int32_t max_end, int32_t laser_idx_min, int32_t laser_idx_max) {
+  CHECK_CTX(c); NEED_GRID(c);
+  if (axis < 0 || axis >= c->ndims) return fail(c, EB200_E_ARG, "axis");
+  if (!kappa_e || !kappa_b || !sigma_e || !sigma_b || !a_e || !a_b) return fail(c, EB200_E_ARG, "null profile");
+  const size_t len = (size_t)(c->g.n[axis] + 2 * c->ng);
+  if (!c->cpml_prof[axis]) EB_CUDA(c, cudaMalloc(&c->cpml_prof[axis], 6 * len * sizeof(double)));
+  const double* src[6] = {kappa_e, kappa_b, sigma_e, sigma_b, a_e, a_b};
+  for (int k = 0; k < 6; ++k)
+    EB_CUDA(c, cudaMemcpyAsync(c->cpml_prof[axis] + k * len, src[k], len * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  c->cpml_start[2 * axis] = min_start; c->cpml_end[2 * axis] = min_end;
+  c->cpml_start[2 * axis + 1] = max_start; c->cpml_end[2 * axis + 1] = max_end;
+  // a negative index = the laser plane of that side is not on this rank (add_laser stays false)
+  for (int side = 0; side < 2; ++side) {
+    const int b = 2 * axis + side, idx = side ? laser_idx_max : laser_idx_min;
+    if (c->bc_field[b] == EB200_BC_CPML_LASER) { c->add_laser[b] = idx >= 0; c->cpml_laser_idx[b] = idx >= 0 ? idx : 1; }
+  }
+  if (!c->cpml_psi) {
+    EB_CUDA(c, cudaMalloc(&c->cpml_psi, (size_t)12 * c->g.total * sizeof(double)));
+    EB_CUDA(c, cudaMemsetAsync(c->cpml_psi, 0, (size_t)12 * c->g.total * sizeof(double), c->stream));
+  }
   return 0;
 }
 

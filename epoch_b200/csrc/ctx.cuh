@@ -114,6 +114,16 @@ struct eb200_ctx {
   int use_current_correction = 0;
   double initial_j[3] = {0, 0, 0};
   double* smooth_wk = nullptr;      // 3 work arrays (allocated on first use)
+  // CPML (boundary.F90 set_cpml_helpers / cpml_advance_*_currents): per axis the six 1-D profiles
+  // kappa_e, kappa_b, sigma_e, sigma_b, a_e, a_b over (1-ng : n+ng) (device, contiguous), the slab
+  // index ranges of both sides, the laser plane of a cpml_laser side, and the psi arrays
+  // [axis][0: E(next axis), 1: E(next-next axis), 2: B(next axis), 3: B(next-next axis)]
+  int cpml_thickness = 0;
+  bool cpml_on = false;
+  double* cpml_prof[3] = {nullptr, nullptr, nullptr};
+  int cpml_start[6] = {0, 0, 0, 0, 0, 0}, cpml_end[6] = {-1, -1, -1, -1, -1, -1};
+  int cpml_laser_idx[6] = {1, 1, 1, 1, 1, 1};
+  double* cpml_psi = nullptr;       // 12 arrays of g.total doubles (allocated when a CPML side exists)
   double* win_planes = nullptr;     // moving window: e*_x_max, b*_x_max planes (6 x y-z extent with ghosts)
   double* fbase = nullptr;     // 9 * total doubles
   eb::FieldP f;
@@ -171,7 +181,6 @@ void free_pinned(eb200_ctx* c);
 // window.cu
 int32_t set_window_planes(eb200_ctx* c, const double* const planes[6]);
 int32_t shift_window(eb200_ctx* c, double grid_min_local, double min_local, double max_local, double gmin, double gmax);
-int32_t field_bc(eb200_ctx* c, int first_comp, int ncomp);
 #define EB_CUDA(c, call)                                                                 \
   do {                                                                                   \
     cudaError_t e__ = (call);                                                            \
@@ -194,8 +203,10 @@ struct ScopedPhase {
 // fdtd.cu
 int32_t update_e_field(eb200_ctx* c);
 int32_t update_b_field(eb200_ctx* c);
+int32_t cpml_advance_currents(eb200_ctx* c, bool efield, double tstep);
 // bcs.cu
 int32_t field_bc(eb200_ctx* c, int first_comp, int ncomp);       // halo exchange of ncomp consecutive components
+int32_t field_bc_array(eb200_ctx* c, double* a);                  // the same for one array of the field shape
 int32_t efield_bcs(eb200_ctx* c);
 int32_t bfield_bcs(eb200_ctx* c, bool mpi_only);
 int32_t bfield_final_bcs(eb200_ctx* c);

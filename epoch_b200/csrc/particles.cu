@@ -222,9 +222,12 @@ static BcP make_bc(const eb200_ctx* c, const SpeciesD& sp, int ax) {
   b.multi = c->nprocdir[ax] > 1;
   b.min_local = g.min_local[ax]; b.max_local = g.max_local[ax];
   b.gmin = g.gmin[ax]; b.gmax = g.gmax[ax];
-  const double boundary_shift = g.d[ax] * (double)((1 + c->png + 0) / 2);   // boundary.F90:1336-1338
+  const double boundary_shift = g.d[ax] * (double)((1 + c->png + c->cpml_thickness) / 2);   // boundary.F90:1336-1338
   b.min_outer = b.gmin - boundary_shift; b.max_outer = b.gmax + boundary_shift;
-  b.shift = (b.gmax - b.gmin);                                             // x_shift, cpml_thickness = 0
+  b.shift = (b.gmax - b.gmin) + 2.0 * g.d[ax] * (double)c->cpml_thickness;                  // x_shift
+  const int fmin = c->bc_field[2 * ax], fmax = c->bc_field[2 * ax + 1];
+  b.cpml_min = fmin == EB200_BC_CPML_LASER || fmin == EB200_BC_CPML_OUTFLOW;
+  b.cpml_max = fmax == EB200_BC_CPML_LASER || fmax == EB200_BC_CPML_OUTFLOW;
   return b;
 }
 
@@ -365,7 +368,10 @@ __global__ void k_particle_bc(BcP b, long long n, double* __restrict__ pos, doub
   const double part_pos = pos[i];
   int xbd = 0;
   bool out = false;
-  if (part_pos < b.min_local) {
+  if (b.cpml_min) {
+    if (b.min_bnd) { if (part_pos < b.min_outer) out = true; }
+    else if (part_pos < b.min_local) xbd = -1;
+  } else if (part_pos < b.min_local) {
     xbd = -1;
     if (b.min_bnd) {
       xbd = 0;
@@ -374,7 +380,10 @@ __global__ void k_particle_bc(BcP b, long long n, double* __restrict__ pos, doub
       if (part_pos < b.min_outer && b.bc_min != EB200_BC_PERIODIC) out = true;
     }
   }
-  if (part_pos >= b.max_local) {
+  if (b.cpml_max) {
+    if (b.max_bnd) { if (part_pos >= b.max_outer) out = true; }
+    else if (part_pos >= b.max_local) xbd = 1;
+  } else if (part_pos >= b.max_local) {
     xbd = 1;
     if (b.max_bnd) {
       xbd = 0;

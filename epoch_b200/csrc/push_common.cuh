@@ -105,6 +105,7 @@ __device__ __forceinline__ uint32_t cell_key(const GridP& g, const int* cell) {
 // particle boundary condition of one axis (particle_bcs, boundary.F90:1316-1972)
 struct BcP {
   int axis, min_bnd, max_bnd, bc_min, bc_max, multi;   // multi: nprocdir[axis] > 1
+  int cpml_min, cpml_max;   // the FIELD boundary of that side is a CPML: particles are only removed beyond *_outer
   double min_local, max_local, gmin, gmax, min_outer, max_outer, shift;
 };
 struct BcP3 { BcP b[3]; int on[3]; };
@@ -123,12 +124,16 @@ __device__ __forceinline__ int bc_and_key(const GridP& g, const PushP& p, const 
     if (!bc.on[d]) continue;
     const BcP& b = bc.b[d];
     const double part_pos = pos[d];
-    if (part_pos < b.min_local) {
+    if (b.cpml_min) {                       // boundary.F90:1390-1402: left the system through the CPML
+      if (part_pos < b.min_outer) out = true;
+    } else if (part_pos < b.min_local) {
       if (b.bc_min == EB200_BC_REFLECT) { pos[d] = 2.0 * b.gmin - part_pos; mom[d] = -mom[d]; changed |= 1 << d; }
       else if (b.bc_min == EB200_BC_PERIODIC) { pos[d] = part_pos + b.shift; changed |= 1 << d; }
       if (part_pos < b.min_outer && b.bc_min != EB200_BC_PERIODIC) out = true;
     }
-    if (part_pos >= b.max_local) {
+    if (b.cpml_max) {
+      if (part_pos >= b.max_outer) out = true;
+    } else if (part_pos >= b.max_local) {
       if (b.bc_max == EB200_BC_REFLECT) { pos[d] = 2.0 * b.gmax - part_pos; mom[d] = -mom[d]; changed |= 1 << d; }
       else if (b.bc_max == EB200_BC_PERIODIC) { pos[d] = part_pos - b.shift; changed |= 1 << d; }
       if (part_pos >= b.max_outer && b.bc_max != EB200_BC_PERIODIC) out = true;

@@ -56,6 +56,14 @@ __global__ void k_window_incoming(WinP w) {
 #undef AT
 }
 
+// cpml_psi(nx+1) = cpml_psi(nx) on the x_max boundary rank (window.F90:151-169), for npsi arrays
+__global__ void k_window_psi(double* psi, long long total, int npsi, int nx, long long sx, long long sy, long long nlines) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nlines * npsi) return;
+  double* a = psi + (t / nlines) * total + (t % nlines) * sy - sx;
+  a[nx + 1] = a[nx];
+}
+
 __global__ void k_window_remove(const double* __restrict__ x, uint32_t* key, long long n, double x_min) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n && x[i] < x_min) key[i] = KEY_INVALID;
@@ -96,6 +104,14 @@ int32_t shift_window(eb200_ctx* c, double grid_min_local, double min_local, doub
     c->launches++;
     EB_TRY(field_bc(c, f, 1));
   }
+  // the psi arrays of the CPML layers move with the fields (window.F90:114-129)
+  const int npsi = c->cpml_psi ? 4 * c->ndims : 0;
+  for (int k = 0; k < npsi; ++k) {
+    double* a = c->cpml_psi + (size_t)k * g.total;
+    k_shift_x<<<grid, 256, 0, c->stream>>>(a, len, nlines);
+    c->launches++;
+    EB_TRY(field_bc_array(c, a));
+  }
   if (c->max_bnd[0]) {
     if (!c->win_planes) EB_TRY(set_window_planes(c, nullptr));
     WinP w;
@@ -103,6 +119,10 @@ int32_t shift_window(eb200_ctx* c, double grid_min_local, double min_local, doub
     w.nx = g.n[0]; w.sy = len; w.sx = 1 - g.ngd[0]; w.nlines = nlines;   // o + i = b + (i + ng - 1)
     k_window_incoming<<<(unsigned)((nlines + 127) / 128), 128, 0, c->stream>>>(w);
     c->launches++;
+    if (npsi) {
+      k_window_psi<<<(unsigned)((nlines * npsi + 127) / 128), 128, 0, c->stream>>>(c->cpml_psi, g.total, npsi, g.n[0], w.sx, w.sy, nlines);
+      c->launches++;
+    }
   }
   EB_CUDA(c, cudaGetLastError());
   return 0;

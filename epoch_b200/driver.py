@@ -68,7 +68,7 @@ class Simulation:
     def __init__(self, ndims, n_global, mins, maxs, shape="triangle", bc_field=None, species=(),
                  lasers=(), dt_multiplier=0.95, field_order=2, t_end=None, abi=None, device=0,
                  rank=0, nproc=1, nprocdir=(1, 1, 1), nccl_id=None, dt=None, maxwell_solver="yee",
-                 stencil=None):
+                 stencil=None, cpml_thickness=6, cpml_kappa_max=20.0, cpml_a_max=0.15, cpml_sigma_max=0.7):
         self.ndims = nd = ndims
         self.shape = SHAPES[shape] if isinstance(shape, str) else shape
         self.n_global = tuple(n_global[:nd])
@@ -81,10 +81,17 @@ class Simulation:
         self.rank, self.nproc = rank, nproc
         self.nprocdir = tuple(nprocdir)
         self.coords = decomp.rank_to_coords(rank, self.nprocdir)
+        # CPML: any cpml_* field boundary widens the grid by cpml_thickness cells on BOTH sides of
+        # EVERY axis (setup.F90:400-414), else the thickness is zero (:254-258)
+        bcn = [self._norm_field_bc(b) for b in self.bc_field]
+        self.cpml_boundaries = any(b in (BC["cpml_laser"], BC["cpml_outflow"]) for b in bcn)
+        self.cpml_thickness = t = int(cpml_thickness) if self.cpml_boundaries else 0
+        self.cpml_kappa_max, self.cpml_a_max, self.cpml_sigma_max = cpml_kappa_max, cpml_a_max, cpml_sigma_max
+        self.n_global = tuple(n + 2 * t for n in self.n_global)
         # setup_grid: setup.F90:174-231
         self.length = [self.maxs[d] - self.mins[d] for d in range(nd)]
-        self.d = [self.length[d] / float(self.n_global[d]) for d in range(nd)]
-        self.grid_min = [self.mins[d] + self.d[d] / 2.0 for d in range(nd)]
+        self.d = [self.length[d] / float(self.n_global[d] - 2 * t) for d in range(nd)]
+        self.grid_min = [(self.mins[d] - self.d[d] * t) + self.d[d] / 2.0 for d in range(nd)]
         # split_domain: near-even split (mpi_routines.F90:44-270)
         self.cell_min, self.cell_max = [], []
         for d in range(nd):
@@ -95,14 +102,22 @@ class Simulation:
         # setup_grid_x: utilities.f90:343-373 (x_global(ix) = x_grid_min + (ix-1)*dx)
         self.grid_min_local = [self.grid_min[d] + (self.cell_min[d] - 1) * self.d[d] for d in range(nd)]
         grid_max_local = [self.grid_min[d] + (self.cell_max[d] - 1) * self.d[d] for d in range(nd)]
-        self.min_local = [self.grid_min_local[d] + (0 - 0.5) * self.d[d] for d in range(nd)]
-        self.max_local = [grid_max_local[d] - (0 - 0.5) * self.d[d] for d in range(nd)]
+        self.fng = field_order // 2      # set_field_order, fields.f90:34-49
+        cp = [self.set_cpml_helpers(d) for d in range(nd)] if self.cpml_boundaries else None
+        off = [(c["min_offset"], c["max_offset"]) for c in cp] if cp else [(0, 0)] * nd
+        self.min_local = [self.grid_min_local[d] + (off[d][0] - 0.5) * self.d[d] for d in range(nd)]
+        self.max_local = [grid_max_local[d] - (off[d][1] - 0.5) * self.d[d] for d in range(nd)]
+        self._cpml_off = off
 
         self.ctx = PicContext(nd, self.shape, abi=abi, device=device, rank=rank, nproc=nproc,
                               nprocdir=self.nprocdir, coords=self.coords, nccl_id=nccl_id)
         self.ctx.set_grid(self.n_local, self.d, self.grid_min_local, self.min_local, self.max_local,
-                          self.mins, self.maxs, n_global=self.n_global, n_global_min=self.cell_min)
+                          self.mins, self.maxs, n_global=self.n_global, n_global_min=self.cell_min,
+                          cpml_thickness=self.cpml_thickness)
         self.ctx.set_field_bcs(self.bc_field)
+        if cp:
+            for d in range(nd):
+                self.ctx.set_cpml(d, **{k: v for k, v in cp[d].items() if k not in ("min_offset", "max_offset")})
         self.maxwell_solver = MAXWELL_SOLVERS[maxwell_solver] if isinstance(maxwell_solver, str) else maxwell_solver
         if self.maxwell_solver == 1:          # "lehe" is the deck's alias of lehe_x (deck_control_block.F90:121-122)
             self.maxwell_solver = 2
@@ -168,6 +183,62 @@ class Simulation:
             if dt_laser > C_TINY:
                 dt = min(dt, dt_laser)
         return self.dt_multiplier * dt
+
+    # -- set_cpml_helpers ----------------------------------------------------------
+    def set_cpml_helpers(self, axis):
+        """One axis of set_cpml_helpers (boundary.F90:1989-2479; 1D :815-966): profiles over
+        (1-ng : n+ng), local slab ranges, offsets of x_min_local / x_max_local, laser planes."""
+        from .context import PNG
+        ng = PNG[self.shape] + 2
+        n, d = self.n_local[axis], self.d[axis]
+        gmin, gmax, nglob = self.cell_min[axis], self.cell_max[axis], self.n_global[axis]
+        t, fng = self.cpml_thickness, self.fng
+        cpml_m, cpml_ma = 3, 1
+        kap_e, kap_b = np.ones(n + 2 * ng), np.ones(n + 2 * ng)
+        sig_e, sig_b, a_e, a_b = (np.zeros(n + 2 * ng) for _ in range(4))
+        at = lambda i: i + ng - 1                     # array position of local index i
+        sigma_maxval = self.cpml_sigma_max * C * 0.8 * (cpml_m + 1.0) / d
+        out = dict(min_start=n + 1, min_end=0, max_start=n + 1, max_end=0, min_offset=0, max_offset=0,
+                   laser_idx_min=-1, laser_idx_max=-1)
+        bc_min = self._norm_field_bc(self.bc_field[2 * axis])
+        bc_max = self._norm_field_bc(self.bc_field[2 * axis + 1])
+        cp = (BC["cpml_laser"], BC["cpml_outflow"])
+
+        def profile(x_pos):
+            return (1.0 + (self.cpml_kappa_max - 1.0) * x_pos ** cpml_m, sigma_maxval * x_pos ** cpml_m,
+                    self.cpml_a_max * (1.0 - x_pos) ** cpml_ma)
+        if bc_min in cp:
+            if gmin <= t:
+                out["min_start"] = 1
+                if gmax >= t:
+                    out["min_end"] = t - gmin + 1
+                    out["min_offset"] = t - gmin + 1
+                else:
+                    out["min_end"] = n
+                    out["min_offset"] = t
+                for i in range(out["min_start"], out["min_end"] + 1):
+                    ig = i + gmin - 1
+                    kap_e[at(i)], sig_e[at(i)], a_e[at(i)] = profile(1.0 - float(ig - 1) / float(t))
+                    kap_b[at(i)], sig_b[at(i)], a_b[at(i)] = profile(1.0 - (float(ig) - 0.5) / float(t))
+            if gmin <= t + fng + 1 <= gmax:
+                out["laser_idx_min"] = t + fng + 1 - gmin
+        if bc_max in cp:
+            if gmax >= nglob - t + 1:
+                out["max_end"] = n
+                if gmin <= nglob - t + 1:
+                    out["max_start"] = nglob - t + 1 - gmin + 1
+                    out["max_offset"] = t - nglob + gmax
+                else:
+                    out["max_start"] = 1
+                    out["max_offset"] = t
+                for i in range(out["max_start"], out["max_end"] + 1):
+                    ig = nglob - (i + gmin - 1) + 1
+                    kap_e[at(i)], sig_e[at(i)], a_e[at(i)] = profile(1.0 - float(ig - 1) / float(t))
+                    kap_b[at(i - 1)], sig_b[at(i - 1)], a_b[at(i - 1)] = profile(1.0 - (float(ig) - 0.5) / float(t))
+            if gmin <= nglob - t - fng + 2 <= gmax:
+                out["laser_idx_max"] = nglob - t - fng + 2 - gmin
+        out.update(kappa_e=kap_e, kappa_b=kap_b, sigma_e=sig_e, sigma_b=sig_b, a_e=a_e, a_b=a_b)
+        return out
 
     # -- set_maxwell_solver ------------------------------------------------------
     def set_maxwell_solver(self):
@@ -302,7 +373,7 @@ class Simulation:
         self.ctx.set_window_fields(planes)
         # global grid bookkeeping of shift_window: x_grid_min (centre of global cell 1), xb_min, x_min, x_max
         self._x_grid_min = self.grid_min[0]
-        self._xb_min = self.mins[0]
+        self._xb_min = self.mins[0] - self.d[0] * self.cpml_thickness      # xb_global(1): outer edge of the layer
         self._x_min, self._x_max = self.mins[0], self.maxs[0]
 
     def _shift_window(self, cells):
@@ -318,13 +389,13 @@ class Simulation:
             # shift the box (window.F90:74-86) and setup_grid_x (utilities.f90:343-373)
             self._x_grid_min = self._x_grid_min + dx
             self._xb_min = self._xb_min + dx
-            self._x_min = self._xb_min
-            self._x_max = (self._xb_min + self.n_global[0] * dx)
+            self._x_min = self._xb_min + dx * self.cpml_thickness
+            self._x_max = (self._xb_min + self.n_global[0] * dx) - dx * self.cpml_thickness
             self.grid_min[0] = self._x_grid_min
             self.grid_min_local[0] = self._x_grid_min + (self.cell_min[0] - 1) * dx
             grid_max_local = self._x_grid_min + (self.cell_max[0] - 1) * dx
-            self.min_local[0] = self.grid_min_local[0] + (0 - 0.5) * dx
-            self.max_local[0] = grid_max_local - (0 - 0.5) * dx
+            self.min_local[0] = self.grid_min_local[0] + (self._cpml_off[0][0] - 0.5) * dx
+            self.max_local[0] = grid_max_local - (self._cpml_off[0][1] - 0.5) * dx
             self.mins = (self._x_min,) + tuple(self.mins[1:])
             self.maxs = (self._x_max,) + tuple(self.maxs[1:])
             self.ctx.shift_window(self.grid_min_local[0], self.min_local[0], self.max_local[0], self._x_min, self._x_max)

@@ -64,6 +64,7 @@ CONTAINS
     CALL gpu_check(eb200_create(gpu, c_ndims, gpu_shape, MOD(rank, ndev), rank, nproc, nprocdir, crd, C_LOC(id)))
     CALL gpu_set_grid
     CALL gpu_check(eb200_set_field_bcs(gpu, INT(bc_field, C_INT32_T)))
+    IF (cpml_boundaries) CALL gpu_set_cpml
     CALL gpu_check(eb200_set_solver(gpu, field_order, maxwell_solver, &
         [alphax, alphay, alphaz, betaxy, betaxz, betayx, betayz, betazx, betazy, &
          gammax, gammay, gammaz, deltax, deltay, deltaz]))
@@ -94,6 +95,27 @@ CONTAINS
         [x_min_local, y_min_local, z_min_local], [x_max_local, y_max_local, z_max_local], &
         [x_min, y_min, z_min], [x_max, y_max, z_max], cpml_thickness))
   END SUBROUTINE gpu_set_grid
+
+  SUBROUTINE gpu_set_cpml
+    ! after set_cpml_helpers (boundary.F90:1989): profiles, slab ranges and laser planes of every axis;
+    ! call again whenever set_cpml_helpers ran again (balance_workload)
+    INTEGER :: lmin, lmax
+    lmin = -1; lmax = -1
+    IF (add_laser(c_bd_x_min)) lmin = cpml_x_min_laser_idx
+    IF (add_laser(c_bd_x_max)) lmax = cpml_x_max_laser_idx
+    CALL gpu_check(eb200_set_cpml(gpu, 0, cpml_kappa_ex, cpml_kappa_bx, cpml_sigma_ex, cpml_sigma_bx, &
+        cpml_a_ex, cpml_a_bx, cpml_x_min_start, cpml_x_min_end, cpml_x_max_start, cpml_x_max_end, lmin, lmax))
+    lmin = -1; lmax = -1
+    IF (add_laser(c_bd_y_min)) lmin = cpml_y_min_laser_idx
+    IF (add_laser(c_bd_y_max)) lmax = cpml_y_max_laser_idx
+    CALL gpu_check(eb200_set_cpml(gpu, 1, cpml_kappa_ey, cpml_kappa_by, cpml_sigma_ey, cpml_sigma_by, &
+        cpml_a_ey, cpml_a_by, cpml_y_min_start, cpml_y_min_end, cpml_y_max_start, cpml_y_max_end, lmin, lmax))
+    lmin = -1; lmax = -1
+    IF (add_laser(c_bd_z_min)) lmin = cpml_z_min_laser_idx
+    IF (add_laser(c_bd_z_max)) lmax = cpml_z_max_laser_idx
+    CALL gpu_check(eb200_set_cpml(gpu, 2, cpml_kappa_ez, cpml_kappa_bz, cpml_sigma_ez, cpml_sigma_bz, &
+        cpml_a_ez, cpml_a_bz, cpml_z_min_start, cpml_z_min_end, cpml_z_max_start, cpml_z_max_end, lmin, lmax))
+  END SUBROUTINE gpu_set_cpml
 
   SUBROUTINE gpu_sync_to_device
     ! host lists/arrays -> device (start of run, after restart_data, balance, window, injectors)

@@ -61,6 +61,13 @@ MODULE epoch_b200_iface
       INTEGER(C_INT32_T), INTENT(IN) :: strides(*)
       REAL(C_DOUBLE), INTENT(IN) :: initial_j(3)
     END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_set_cpml(ctx, axis, kappa_e, kappa_b, sigma_e, sigma_b, a_e, a_b, &
+        min_start, min_end, max_start, max_end, laser_idx_min, laser_idx_max) BIND(C, NAME='eb200_set_cpml')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: axis, min_start, min_end, max_start, max_end, laser_idx_min, laser_idx_max
+      REAL(C_DOUBLE), INTENT(IN) :: kappa_e(*), kappa_b(*), sigma_e(*), sigma_b(*), a_e(*), a_b(*)
+    END FUNCTION
     INTEGER(C_INT32_T) FUNCTION eb200_set_species(ctx, ispecies, charge, mass, weight, immobile, &
         zero_current, species_type, bc_particle) BIND(C, NAME='eb200_set_species')
       IMPORT

@@ -112,6 +112,23 @@ int32_t EB200_NAME(set_field_bcs)(EB200_CTX*, const int32_t bc_field[6]);
 int32_t EB200_NAME(set_solver)(EB200_CTX*, int32_t field_order, int32_t maxwell_solver,
                                const double coeffs[15]);
 
+/* CPML absorbing boundaries (bc_field = cpml_laser / cpml_outflow).  set_grid's cpml_thickness
+ * is the deck's value (the host has already widened the grid, setup.F90:180-189,400-414).
+ * set_cpml hands over, per axis, what set_cpml_helpers (boundary.F90:1989-2479; 1D :815-966)
+ * leaves on the host: the six profiles cpml_kappa_e*, cpml_kappa_b*, cpml_sigma_e*,
+ * cpml_sigma_b*, cpml_a_e*, cpml_a_b* over (1-ng : n+ng) (kappa = 1, others 0 outside the
+ * layer), the local slab ranges cpml_*_min_start/end and cpml_*_max_start/end, and the local
+ * laser-plane indices cpml_*_min/max_laser_idx (pass -1 when that plane is on another rank).
+ * It must be called for EVERY axis of the simulation once a CPML boundary is set.  The library
+ * then uses the kappa-scaled branches of update_e_field / update_b_field (fields.f90:192-310,
+ * :437-630) followed by cpml_advance_e_currents / cpml_advance_b_currents (boundary.F90:
+ * 2483-2815), zero-gradient ghosts on CPML sides, the laser plane at laser_idx, and removes
+ * particles beyond x_min_outer / x_max_outer on a CPML side (boundary.F90:1386-1402). */
+int32_t EB200_NAME(set_cpml)(EB200_CTX*, int32_t axis, const double* kappa_e, const double* kappa_b,
+                             const double* sigma_e, const double* sigma_b, const double* a_e,
+                             const double* a_b, int32_t min_start, int32_t min_end, int32_t max_start,
+                             int32_t max_end, int32_t laser_idx_min, int32_t laser_idx_max);
+
 /* current_finish options (housekeeping/current_smooth.F90:29-151): the strided compensated
  * binomial filter of smooth_current (smooth_its passes, smooth_comp_its = 0|1 extra pass, the
  * deck's smooth_strides; strides <= ng) and use_current_correction, which subtracts the three

@@ -53,7 +53,7 @@ int32_t orc_set_grid(orc_ctx* c, const int32_t n_local[3], const int32_t n_globa
                      const double max_global[3], int32_t cpml_thickness) {
   if (!c) return EB200_E_ARG;
   State& s = c->s;
-  if (cpml_thickness != 0) return fail(c, EB200_E_UNSUPPORTED, "CPML not supported");
+  if (cpml_thickness < 0) return fail(c, EB200_E_ARG, "cpml_thickness < 0");
   int64_t stride = 1;
   for (int k = 0; k < 3; ++k) {
     const bool ex = k < s.ndims;
@@ -92,12 +92,34 @@ int32_t orc_set_field_bcs(orc_ctx* c, const int32_t bc_field[6]) {
     int bc = i < 2 * s.ndims ? bc_field[i] : BC_PERIODIC;
     s.add_laser[i] = false;
     if (bc == BC_OTHER) bc = BC_CLAMP;
-    if (bc == BC_CPML_LASER || bc == BC_CPML_OUTFLOW) return fail(c, EB200_E_UNSUPPORTED, "CPML not supported");
-    if (bc == BC_SIMPLE_LASER) s.add_laser[i] = true;
+    if (bc == BC_SIMPLE_LASER) s.add_laser[i] = true;       // cpml_laser: set by set_cpml
     if (bc == BC_REFLECT) bc = BC_CLAMP;
     if (bc == BC_OPEN) bc = BC_SIMPLE_OUTFLOW;
     s.bc_field[i] = bc;
   }
+  s.cpml_on = false;
+  for (int i = 0; i < 2 * s.ndims; ++i)
+    if (s.bc_field[i] == BC_CPML_LASER || s.bc_field[i] == BC_CPML_OUTFLOW) s.cpml_on = true;
+  return 0;
+}
+
+int32_t orc_set_cpml(orc_ctx* c, int32_t axis, const double* kappa_e, const double* kappa_b, const double* sigma_e,
+                     const double* sigma_b, const double* a_e, const double* a_b, int32_t min_start, int32_t min_end,
+                     int32_t max_start, int32_t max_end, int32_t laser_idx_min, int32_t laser_idx_max) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  State& s = c->s;
+  if (axis < 0 || axis >= s.ndims) return fail(c, EB200_E_ARG, "axis");
+  if (!kappa_e || !kappa_b || !sigma_e || !sigma_b || !a_e || !a_b) return fail(c, EB200_E_ARG, "null profile");
+  const size_t len = (size_t)(s.n[axis] + 2 * s.ng);
+  const double* src[6] = {kappa_e, kappa_b, sigma_e, sigma_b, a_e, a_b};
+  for (int k = 0; k < 6; ++k) s.cpml_prof[axis][k].assign(src[k], src[k] + len);
+  s.cpml_start[2 * axis] = min_start; s.cpml_end[2 * axis] = min_end;
+  s.cpml_start[2 * axis + 1] = max_start; s.cpml_end[2 * axis + 1] = max_end;
+  for (int side = 0; side < 2; ++side) {
+    const int b = 2 * axis + side, idx = side ? laser_idx_max : laser_idx_min;
+    if (s.bc_field[b] == BC_CPML_LASER) { s.add_laser[b] = idx >= 0; s.cpml_laser_idx[b] = idx >= 0 ? idx : 1; }
+  }
+  for (int k = 0; k < 4; ++k) if (s.cpml_psi[axis][k].empty()) s.cpml_psi[axis][k].assign((size_t)s.total, 0.0);
   return 0;
 }
 

@@ -52,13 +52,21 @@ void update_e_field(State& s) {
   if (s.field_order == 4) { c1 = 9.0 / 8.0; c2 = -1.0 / 24.0; }
   else if (s.field_order == 6) { c1 = 75.0 / 64.0; c2 = -25.0 / 384.0; c3 = 3.0 / 640.0; }
   const int ord = s.field_order;
-  const double cx1 = ord == 2 ? s.cn[0] : c1 * s.cn[0], cx2 = c2 * s.cn[0], cx3 = c3 * s.cn[0];
-  const double cy1 = ord == 2 ? s.cn[1] : c1 * s.cn[1], cy2 = c2 * s.cn[1], cy3 = c3 * s.cn[1];
-  const double cz1 = ord == 2 ? s.cn[2] : c1 * s.cn[2], cz2 = c2 * s.cn[2], cz3 = c3 * s.cn[2];
+  double cx1 = ord == 2 ? s.cn[0] : c1 * s.cn[0], cx2 = c2 * s.cn[0], cx3 = c3 * s.cn[0];
+  double cy1 = ord == 2 ? s.cn[1] : c1 * s.cn[1], cy2 = c2 * s.cn[1], cy3 = c3 * s.cn[1];
+  double cz1 = ord == 2 ? s.cn[2] : c1 * s.cn[2], cz2 = c2 * s.cn[2], cz3 = c3 * s.cn[2];
+  // CPML branches (fields.f90:192-310): every coefficient is divided by cpml_kappa_e*(index)
+  auto kap = [&](int d, int idx) { return s.cpml_prof[d][0][idx + s.ng - 1]; };
   for (int iz = s.lo0(2); iz <= s.hi(2); ++iz)
     for (int iy = s.lo0(1); iy <= s.hi(1); ++iy)
       for (int ix = 0; ix <= s.n[0]; ++ix) {
         const int64_t i = s.idx(ix, iy, iz);
+        if (s.cpml_on) {
+          const double qx = s.cn[0] / kap(0, ix);
+          cx1 = ord == 2 ? qx : c1 * qx; cx2 = c2 * qx; cx3 = c3 * qx;
+          if (nd >= 2) { const double qy = s.cn[1] / kap(1, iy); cy1 = ord == 2 ? qy : c1 * qy; cy2 = c2 * qy; cy3 = c3 * qy; }
+          if (nd >= 3) { const double qz = s.cn[2] / kap(2, iz); cz1 = ord == 2 ? qz : c1 * qz; cz2 = c2 * qz; cz3 = c3 * qz; }
+        }
         // the reference evaluates left to right: e + A - B - fac*j
         double vx = ex[i], vy = ey[i], vz = ez[i];
         // ex: + cy*(d_y bz) - cz*(d_z by)
@@ -95,6 +103,7 @@ void update_e_field(State& s) {
         vz = vz - fac * jz[i];
         ex[i] = vx; ey[i] = vy; ez[i] = vz;
       }
+  if (s.cpml_on) cpml_advance_currents(s, true, s.hdt);
 }
 
 // difference along axis a of the extended stencils (fields.f90:655-732; 2D :426-470; 1D :296-306),
@@ -120,11 +129,16 @@ static void update_b_field_ext(State& s) {
   const int64_t sx = s.st[0], sy = s.st[1], sz = s.st[2];
   const bool hy = nd >= 2, hz = nd >= 3;
   const double* q = s.coeffs;   // alpha x,y,z | beta xy,xz,yx,yz,zx,zy | gamma x,y,z | delta x,y,z
-  const double cx1 = s.hdtd[0], cy1 = s.hdtd[1], cz1 = s.hdtd[2];
+  double cx1 = s.hdtd[0], cy1 = s.hdtd[1], cz1 = s.hdtd[2];
   for (int iz = s.lo0(2); iz <= s.hi(2); ++iz)
     for (int iy = s.lo0(1); iy <= s.hi(1); ++iy)
       for (int ix = 0; ix <= s.n[0]; ++ix) {
         const int64_t i = s.idx(ix, iy, iz);
+        if (s.cpml_on) {            // cx1 = hdtx / cpml_kappa_bx(ix) (2D fields.f90:338-341)
+          cx1 = s.hdtd[0] / s.cpml_prof[0][1][ix + s.ng - 1];
+          if (hy) cy1 = s.hdtd[1] / s.cpml_prof[1][1][iy + s.ng - 1];
+          if (hz) cz1 = s.hdtd[2] / s.cpml_prof[2][1][iz + s.ng - 1];
+        }
         double vx = bx[i], vy = by[i], vz = bz[i];
         if (hy) vx = vx - cy1 * ext_diff(ez, i, sy, sx, sz, true, hz, q[1], q[5], q[6], q[10], q[13]);
         if (hz) vx = vx + cz1 * ext_diff(ey, i, sz, sx, sy, true, true, q[2], q[7], q[8], q[11], q[14]);
@@ -134,6 +148,7 @@ static void update_b_field_ext(State& s) {
         if (hy) vz = vz + cy1 * ext_diff(ex, i, sy, sx, sz, true, hz, q[1], q[5], q[6], q[10], q[13]);
         bx[i] = vx; by[i] = vy; bz[i] = vz;
       }
+  if (s.cpml_on) cpml_advance_currents(s, false, s.hdt);
 }
 
 // fields.f90:428-815 (Yee branches :637-654, orders 4/6 :734-812)
@@ -147,13 +162,20 @@ void update_b_field(State& s) {
   if (s.field_order == 4) { c1 = 9.0 / 8.0; c2 = -1.0 / 24.0; }
   else if (s.field_order == 6) { c1 = 75.0 / 64.0; c2 = -25.0 / 384.0; c3 = 3.0 / 640.0; }
   const int ord = s.field_order;
-  const double cx1 = ord == 2 ? s.hdtd[0] : c1 * s.hdtd[0], cx2 = c2 * s.hdtd[0], cx3 = c3 * s.hdtd[0];
-  const double cy1 = ord == 2 ? s.hdtd[1] : c1 * s.hdtd[1], cy2 = c2 * s.hdtd[1], cy3 = c3 * s.hdtd[1];
-  const double cz1 = ord == 2 ? s.hdtd[2] : c1 * s.hdtd[2], cz2 = c2 * s.hdtd[2], cz3 = c3 * s.hdtd[2];
+  double cx1 = ord == 2 ? s.hdtd[0] : c1 * s.hdtd[0], cx2 = c2 * s.hdtd[0], cx3 = c3 * s.hdtd[0];
+  double cy1 = ord == 2 ? s.hdtd[1] : c1 * s.hdtd[1], cy2 = c2 * s.hdtd[1], cy3 = c3 * s.hdtd[1];
+  double cz1 = ord == 2 ? s.hdtd[2] : c1 * s.hdtd[2], cz2 = c2 * s.hdtd[2], cz3 = c3 * s.hdtd[2];
+  auto kap = [&](int d, int idx) { return s.cpml_prof[d][1][idx + s.ng - 1]; };
   for (int iz = s.lo0(2); iz <= s.hi(2); ++iz)
     for (int iy = s.lo0(1); iy <= s.hi(1); ++iy)
       for (int ix = 0; ix <= s.n[0]; ++ix) {
         const int64_t i = s.idx(ix, iy, iz);
+        if (s.cpml_on) {            // fields.f90:437-630
+          const double qx = s.hdtd[0] / kap(0, ix);
+          cx1 = ord == 2 ? qx : c1 * qx; cx2 = c2 * qx; cx3 = c3 * qx;
+          if (nd >= 2) { const double qy = s.hdtd[1] / kap(1, iy); cy1 = ord == 2 ? qy : c1 * qy; cy2 = c2 * qy; cy3 = c3 * qy; }
+          if (nd >= 3) { const double qz = s.hdtd[2] / kap(2, iz); cz1 = ord == 2 ? qz : c1 * qz; cz2 = c2 * qz; cz3 = c3 * qz; }
+        }
         double vx = bx[i], vy = by[i], vz = bz[i];
         // bx: - cy*(d_y ez) + cz*(d_z ey)
         if (nd >= 2) {
@@ -186,14 +208,67 @@ void update_b_field(State& s) {
         }
         bx[i] = vx; by[i] = vy; bz[i] = vz;
       }
+  if (s.cpml_on) cpml_advance_currents(s, false, s.hdt);
+}
+
+// cpml_advance_e_currents / cpml_advance_b_currents (boundary.F90:2483-2815; 1D :998-1106).  The
+// six blocks per routine are cyclic permutations: axis a, b = a + 1, c = a + 2,
+//   E: psi_e{b}{a} <- d_a B_c, E_b -= fac psi;  psi_e{c}{a} <- d_a B_b, E_c += fac psi
+//   B: psi_b{b}{a} <- d_a E_c, B_b += t psi;    psi_b{c}{a} <- d_a E_b, B_c -= t psi
+// over the slab [start, end] (B on a max side: start-1 .. end-1) and 1..n of the other axes.
+void cpml_advance_currents(State& s, bool efield, double tstep) {
+  const double fac = tstep * (C * C);
+  for (int a = 0; a < s.ndims; ++a)
+    for (int side = 0; side < 2; ++side) {
+      const int bnd = 2 * a + side;
+      if (s.bc_field[bnd] != BC_CPML_LASER && s.bc_field[bnd] != BC_CPML_OUTFLOW) continue;
+      int start = s.cpml_start[bnd], end = s.cpml_end[bnd];
+      if (!efield && side == 1) { start -= 1; end -= 1; }
+      const int b = (a + 1) % 3, c = (a + 2) % 3;
+      const std::vector<double>& kp = s.cpml_prof[a][efield ? 0 : 1];
+      const std::vector<double>& sg = s.cpml_prof[a][efield ? 2 : 3];
+      const std::vector<double>& ac = s.cpml_prof[a][efield ? 4 : 5];
+      double* psi0 = s.cpml_psi[a][efield ? 0 : 2].data();
+      double* psi1 = s.cpml_psi[a][efield ? 1 : 3].data();
+      double* F0 = s.f[(efield ? EX : BX) + b].data();
+      double* F1 = s.f[(efield ? EX : BX) + c].data();
+      const double* S0 = s.f[(efield ? BX : EX) + c].data();
+      const double* S1 = s.f[(efield ? BX : EX) + b].data();
+      const int64_t sa = s.st[a];
+      int lo[3] = {1, 1, 1}, hi[3] = {1, 1, 1};
+      for (int d = 0; d < s.ndims; ++d) hi[d] = s.n[d];
+      lo[a] = start; hi[a] = end;
+      for (int iz = lo[2]; iz <= hi[2]; ++iz)
+        for (int iy = lo[1]; iy <= hi[1]; ++iy)
+          for (int ix = lo[0]; ix <= hi[0]; ++ix) {
+            const int cc[3] = {ix, iy, iz};
+            const int ipos = cc[a];
+            const int64_t i = s.idx(ix, iy, iz);
+            const double kappa = kp[ipos + s.ng - 1], sigma = sg[ipos + s.ng - 1], acoeff = ac[ipos + s.ng - 1];
+            const double bcoeff = std::exp(-(sigma / kappa + acoeff) * tstep);
+            const double ccoeff_d = (bcoeff - 1.0) * sigma / kappa / (sigma + kappa * acoeff) / s.d[a];
+            if (efield) {
+              psi0[i] = bcoeff * psi0[i] + ccoeff_d * (S0[i] - S0[i - sa]);
+              F0[i] = F0[i] - fac * psi0[i];
+              psi1[i] = bcoeff * psi1[i] + ccoeff_d * (S1[i] - S1[i - sa]);
+              F1[i] = F1[i] + fac * psi1[i];
+            } else {
+              psi0[i] = bcoeff * psi0[i] + ccoeff_d * (S0[i + sa] - S0[i]);
+              F0[i] = F0[i] + tstep * psi0[i];
+              psi1[i] = bcoeff * psi1[i] + ccoeff_d * (S1[i + sa] - S1[i]);
+              F1[i] = F1[i] - tstep * psi1[i];
+            }
+          }
+    }
 }
 
 // boundary.F90:145-152,321-468 do_field_mpi_with_lengths, single-rank form: the
 // x_min neighbour of a periodic rank is itself, so A(nx+1:nx+ng) <- A(1:ng) and
 // A(1-ng:0) <- A(nx+1-ng:nx); x then y then z over FULL extents of the other dims;
 // on a non-periodic physical boundary the ghost cells are left untouched.
-void field_bc(State& s, int comp) {
-  double* a = s.f[comp].data();
+static void field_bc_array(State& s, double* a);
+void field_bc(State& s, int comp) { field_bc_array(s, s.f[comp].data()); }
+static void field_bc_array(State& s, double* a) {
   const int ng = s.ng;
   for (int ax = 0; ax < s.ndims; ++ax) {
     const int nn = s.n[ax];
@@ -305,7 +380,8 @@ void bfield_bcs(State& s, bool mpi_only) {
 static void outflow_bcs(State& s, int boundary) {
   const int a = boundary / 2, t1 = (a + 1) % 3, t2 = (a + 2) % 3;
   const bool is_max = boundary & 1;
-  const int lp = is_max ? s.n[a] : 1;
+  int lp = is_max ? s.n[a] : 1;
+  if (s.bc_field[boundary] == BC_CPML_LASER) lp = s.cpml_laser_idx[boundary];   // laser.f90:529-531
   const double dtc2 = s.dt * (C * C);
   const double la = dtc2 / s.d[a];
   const double l1 = t1 < s.ndims ? dtc2 / s.d[t1] : 0.0;
@@ -526,6 +602,18 @@ void shift_window(State& s, double grid_min_local, double min_local, double max_
       for (int i = 0; i < len - 1; ++i) a[l * len + i] = a[l * len + i + 1];
     field_bc(s, f);
   }
+  // the CPML psi arrays move with the fields (window.F90:114-129) ...
+  for (int ax = 0; ax < s.ndims; ++ax)
+    for (int k = 0; k < 4; ++k) {
+      if (s.cpml_psi[ax][k].empty()) continue;
+      double* a = s.cpml_psi[ax][k].data();
+      for (int64_t l = 0; l < nlines; ++l)
+        for (int i = 0; i < len - 1; ++i) a[l * len + i] = a[l * len + i + 1];
+      field_bc_array(s, a);
+      // ... and psi(nx+1) = psi(nx) on the x_max boundary (window.F90:151-169)
+      if (s.max_bnd[0])
+        for (int64_t l = 0; l < nlines; ++l) a[l * len + s.ngd[0] + s.n[0]] = a[l * len + s.ngd[0] - 1 + s.n[0]];
+    }
   if (s.max_bnd[0]) {
     double *ex = s.f[EX].data(), *ey = s.f[EY].data(), *ez = s.f[EZ].data();
     double *bx = s.f[BX].data(), *by = s.f[BY].data(), *bz = s.f[BZ].data();

@@ -327,7 +327,12 @@ void particle_bcs(State& s) {
         const double min_outer = s.gmin[d] - boundary_shift, max_outer = s.gmax[d] + boundary_shift;
         const double shift = (s.gmax[d] - s.gmin[d]) + 2.0 * s.d[d] * (double)s.cpml_thickness;
         const double part_pos = sp.pos[d][ip];
-        if (part_pos < s.min_local[d]) {
+        const int fmin = s.bc_field[2 * d], fmax = s.bc_field[2 * d + 1];
+        const bool cpml_min = fmin == BC_CPML_LASER || fmin == BC_CPML_OUTFLOW;
+        const bool cpml_max = fmax == BC_CPML_LASER || fmax == BC_CPML_OUTFLOW;
+        if (cpml_min) {        // boundary.F90:1386-1402: through a CPML the particle only ever leaves
+          if (s.min_bnd[d] && part_pos < min_outer) out_of_bounds = true;
+        } else if (part_pos < s.min_local[d]) {
           if (s.min_bnd[d]) {
             const int bc = sp.bc[2 * d];
             if (bc == BC_REFLECT) {
@@ -339,7 +344,9 @@ void particle_bcs(State& s) {
             if (part_pos < min_outer && bc != BC_PERIODIC) out_of_bounds = true;
           }
         }
-        if (part_pos >= s.max_local[d]) {
+        if (cpml_max) {
+          if (s.max_bnd[d] && part_pos >= max_outer) out_of_bounds = true;
+        } else if (part_pos >= s.max_local[d]) {
           if (s.max_bnd[d]) {
             const int bc = sp.bc[2 * d + 1];
             if (bc == BC_REFLECT) {

@@ -84,6 +84,14 @@ struct State {
   int smooth_its = 1, smooth_comp_its = 0;
   std::vector<int> smooth_strides;
   double initial_j[3] = {0, 0, 0};
+  // CPML (set_cpml_helpers): per axis kappa_e, kappa_b, sigma_e, sigma_b, a_e, a_b over (1-ng : n+ng),
+  // slab ranges per boundary, laser plane index per boundary, psi[axis][0..3] = E(next), E(next-next),
+  // B(next), B(next-next)
+  bool cpml_on = false;
+  std::vector<double> cpml_prof[3][6];
+  int cpml_start[6] = {0, 0, 0, 0, 0, 0}, cpml_end[6] = {-1, -1, -1, -1, -1, -1};
+  int cpml_laser_idx[6] = {1, 1, 1, 1, 1, 1};
+  std::vector<double> cpml_psi[3][4];
   std::vector<double> win_planes[6];   // moving window: e*_x_max, b*_x_max (setup.F90:425-470)
   // half-step scalars (fields.f90:821-830)
   double hdt = 0, hdtd[3] = {0, 0, 0}, cn[3] = {0, 0, 0}, fac = 0;
@@ -114,6 +122,7 @@ void bfield_final_bcs(State& s);
 void update_eb_fields_half(State& s);
 void update_eb_fields_final(State& s);
 void current_finish(State& s);
+void cpml_advance_currents(State& s, bool efield, double tstep);
 void shift_window(State& s, double grid_min_local, double min_local, double max_local, double gmin, double gmax);
 // orc_particles.cpp
 void push_particles(State& s);

@@ -19,6 +19,7 @@ AXIS = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 STEPS = int(sys.argv[2]) if len(sys.argv) > 2 else 4
 SHAPE = sys.argv[3] if len(sys.argv) > 3 else "triangle"
 WINDOW = len(sys.argv) > 4 and sys.argv[4] == "window"      # moving window at 0.9 c (x decomposition, open x boundaries)
+CPML = len(sys.argv) > 4 and sys.argv[4] == "cpml"          # CPML layers on the decomposed axis and on x
 N = [16, 12, 20]
 CELL = 1e-6
 
@@ -49,6 +50,14 @@ def build(abi, rank, nproc, nccl_id, device):
         kw = dict(bc_field=obc)
         for s in sp:
             s.bcs = obc
+    if CPML:
+        fbc, pbc = ["periodic"] * 6, ["periodic"] * 6
+        for d in {0, AXIS}:
+            fbc[2 * d:2 * d + 2] = ["cpml_outflow"] * 2
+            pbc[2 * d:2 * d + 2] = ["open"] * 2
+        kw = dict(bc_field=fbc)
+        for s in sp:
+            s.bcs = pbc
     sim = Simulation(3, N, [0.0] * 3, [n * CELL for n in N], shape=SHAPE, species=sp, abi=abi, device=device,
                      rank=rank, nproc=nproc, nprocdir=tuple(nprocdir), nccl_id=nccl_id, **kw)
     rng = np.random.default_rng(11)

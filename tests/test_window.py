@@ -30,9 +30,9 @@ def window_insert(ppc=2, seed=77):
     return insert
 
 
-def window_deck(abi, ndims, shape="triangle", planes=True, **kw):
+def window_deck(abi, ndims, shape="triangle", planes=True, fbc="open", **kw):
     n = [20, 12, 8]
-    bc_field = ["open", "open"] + ["periodic"] * (2 * ndims - 2)
+    bc_field = [fbc, fbc] + ["periodic"] * (2 * ndims - 2)
     bcs = ["open", "open"] + ["periodic"] * (2 * ndims - 2)
     sim = make_plasma(abi, ndims, shape, n, seed=12, ppc=2, u_th=0.2, bc_field=bc_field, bcs=bcs, **kw)
     pl = None
