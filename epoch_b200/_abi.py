@@ -47,6 +47,7 @@ SIGNATURES = {
     "bfield_final_bcs": (i32, [c_ctx_p]),
     "energy": (i32, [c_ctx_p, pf64, pf64]),
     "charge_residual": (i32, [c_ctx_p, pf64, pf64]),
+    "calc_derived": (i32, [c_ctx_p, i32, i32, i32, pf64]),
     "set_option": (i32, [c_ctx_p, C.c_char_p, C.c_char_p]),
     "sync": (i32, [c_ctx_p]),
     "timer": (i32, [c_ctx_p, C.c_char_p, i32, pf64, pi64]),

@@ -248,6 +248,19 @@ class PicContext:
         self._ck(self.abi.charge_residual(self._ctx, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    DERIVED = {"mass_density": 0, "ekbar": 1, "ekflux": 2, "poynt_flux": 3, "charge_density": 4,
+               "number_density": 5, "ppc": 6, "average_weight": 7, "temperature": 8,
+               "species_current": 9, "average_momentum": 10}
+
+    def calc_derived(self, kind, ispecies=-1, direction=0):
+        """calc_<kind>(data_array, current_species, direction) of io/calc_df.F90; returns the
+        array with ghosts (ispecies -1 = summed over species, direction 1..3 / -1..-3 / 0)"""
+        out = np.empty(self._np_shape(), dtype=np.float64)
+        k = self.DERIVED[kind] if isinstance(kind, str) else int(kind)
+        self._ck(self.abi.calc_derived(self._ctx, k, int(ispecies), int(direction),
+                                       out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
     def set_option(self, key, value):
         self._ck(self.abi.set_option(self._ctx, key.encode(), str(value).encode()))
 

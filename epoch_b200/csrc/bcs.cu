@@ -203,6 +203,23 @@ static int32_t physical_bcs(eb200_ctx* c, bool efield) {
   return 0;
 }
 
+// field_zero_gradient(array, c_stagger_centre, b) on every boundary (the tail of the calc_df routines)
+int32_t zero_gradient_centre(eb200_ctx* c, double* a) {
+  Arr3 A; A.a[0] = A.a[1] = A.a[2] = a;
+  MirrorP m;
+  for (int k = 0; k < 3; ++k) { m.mode[k] = k == 0 ? 2 : 0; m.stg[k] = 0; }
+  for (int b = 0; b < 2 * c->ndims; ++b) {
+    const int ax = b / 2, is_max = b & 1;
+    if (c->bc_field[b] == EB200_BC_PERIODIC) continue;
+    if (is_max ? !c->max_bnd[ax] : !c->min_bnd[ax]) continue;
+    const LineP p = line_params(c, ax);
+    k_mirror<<<line_grid(p, 1), 128, 0, c->stream>>>(p, A, m, is_max);
+    c->launches++;
+  }
+  EB_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
 int32_t efield_bcs(eb200_ctx* c) {
   EB_TRY(field_bc(c, EX, 3));
   ScopedPhase ph(c, "bcs");

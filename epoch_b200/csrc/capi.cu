@@ -122,7 +122,7 @@ int32_t eb200_destroy(eb200_ctx* c) {
   for (SpeciesD& sp : c->species) free_species(sp);
   for (int b = 0; b < 6; ++b) for (Laser& L : c->lasers[b]) { if (L.profile) cudaFree(L.profile); if (L.phase) cudaFree(L.phase); }
   void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->rec_scratch, c->cub_tmp, c->halo_send, c->halo_recv,
-                  c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho, c->smooth_wk, c->win_planes, c->cpml_psi,
+                  c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho, c->smooth_wk, c->win_planes, c->cpml_psi, c->diag_wk,
                   c->cpml_prof[0], c->cpml_prof[1], c->cpml_prof[2]};
   for (void* p : ptrs) if (p) cudaFree(p);
   free_pinned(c);
@@ -169,8 +169,11 @@ int32_t eb200_set_grid(eb200_ctx* c, const int32_t n_local[3], const int32_t n_g
   if (ncell >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "local grid too large for 32-bit cell keys");
   g.total = stride; g.ncell_ext = ncell;
   if (c->fbase) { cudaStreamSynchronize(c->stream); cudaFree(c->fbase); c->fbase = nullptr; }
-  if (c->rho) { cudaFree(c->rho); c->rho = nullptr; }
-  if (c->res_ref) { cudaFree(c->res_ref); c->res_ref = nullptr; }
+  // every work array of the field shape belongs to the old grid (set_grid again = rebalance / restart)
+  double** shaped[] = {&c->rho, &c->res_ref, &c->smooth_wk, &c->win_planes, &c->cpml_psi, &c->diag_wk,
+                       &c->cpml_prof[0], &c->cpml_prof[1], &c->cpml_prof[2]};
+  for (double** p : shaped)
+    if (*p) { cudaFree(*p); *p = nullptr; }
   EB_CUDA(c, cudaMalloc(&c->fbase, (size_t)NFIELD * g.total * sizeof(double)));
   EB_CUDA(c, cudaMemsetAsync(c->fbase, 0, (size_t)NFIELD * g.total * sizeof(double), c->stream));
   for (int f = 0; f < NFIELD; ++f) c->f.f[f] = c->fbase + (size_t)f * g.total;
@@ -371,6 +374,20 @@ int32_t eb200_download_fields(eb200_ctx* c, double* ex, double* ey, double* ez, 
     }
   EB_CUDA(c, cudaStreamSynchronize(c->stream));
   return 0;
+}
+
+int32_t eb200_calc_derived(eb200_ctx* c, int32_t kind, int32_t ispecies, int32_t direction, double* out) {
+  CHECK_CTX(c); NEED_GRID(c);
+  if (!out) return fail(c, EB200_E_ARG, "calc_derived: null output array");
+  if (kind < 0 || kind > EB200_DF_AVERAGE_MOMENTUM) return fail(c, EB200_E_ARG, "calc_derived: unknown kind");
+  if (ispecies >= (int32_t)c->species.size() || (ispecies >= 0 && !c->species[ispecies].defined))
+    return fail(c, EB200_E_ARG, "calc_derived: species not defined");
+  const int ad = direction < 0 ? -direction : direction;
+  const bool need_dir = kind == EB200_DF_EKFLUX || kind == EB200_DF_POYNT_FLUX || kind == EB200_DF_SPECIES_CURRENT ||
+                        kind == EB200_DF_AVERAGE_MOMENTUM;
+  if (ad > 3 || (need_dir && ad == 0) || (direction < 0 && kind != EB200_DF_EKFLUX))
+    return fail(c, EB200_E_ARG, "calc_derived: direction must be 1..3 (negative only for ekflux; 0 only where optional)");
+  return calc_derived(c, kind, ispecies, direction, out);
 }
 
 int32_t eb200_set_laser(eb200_ctx* c, int32_t boundary, int32_t id, double amp, double pol_angle, double t_start,

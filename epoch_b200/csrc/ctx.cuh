@@ -123,6 +123,7 @@ struct eb200_ctx {
   double* cpml_prof[3] = {nullptr, nullptr, nullptr};
   int cpml_start[6] = {0, 0, 0, 0, 0, 0}, cpml_end[6] = {-1, -1, -1, -1, -1, -1};
   int cpml_laser_idx[6] = {1, 1, 1, 1, 1, 1};
+  double* diag_wk = nullptr;        // 5 arrays of g.total doubles (calc_derived)
   double* cpml_psi = nullptr;       // 12 arrays of g.total doubles (allocated when a CPML side exists)
   double* win_planes = nullptr;     // moving window: e*_x_max, b*_x_max planes (6 x y-z extent with ghosts)
   double* fbase = nullptr;     // 9 * total doubles
@@ -207,6 +208,9 @@ int32_t cpml_advance_currents(eb200_ctx* c, bool efield, double tstep);
 // bcs.cu
 int32_t field_bc(eb200_ctx* c, int first_comp, int ncomp);       // halo exchange of ncomp consecutive components
 int32_t field_bc_array(eb200_ctx* c, double* a);                  // the same for one array of the field shape
+int32_t zero_gradient_centre(eb200_ctx* c, double* a);
+// diag.cu
+int32_t calc_derived(eb200_ctx* c, int kind, int ispecies, int direction, double* out_host);
 int32_t efield_bcs(eb200_ctx* c);
 int32_t bfield_bcs(eb200_ctx* c, bool mpi_only);
 int32_t bfield_final_bcs(eb200_ctx* c);

@@ -215,6 +215,30 @@ int32_t EB200_NAME(energy)(EB200_CTX*, double* field_energy,
  * with the normalised weights of calc_charge_density (calc_df.F90:439-519). */
 int32_t EB200_NAME(charge_residual)(EB200_CTX*, double* max_abs_residual,
                                     double* max_abs_rho_over_eps0);
+/* Derived grid variables of io/calc_df.F90, computed where the particles live so that
+ * output_routines pulls one reduced grid instead of the particle lists.
+ * kind: EB200_DF_* below; ispecies: 0-based species, or -1 for the sum over species
+ * (current_species <= 0; zero_current species are then skipped as the reference does);
+ * direction: 1, 2, 3 = c_dir_x, c_dir_y, c_dir_z, negative for the backward ekflux, 0 = absent
+ * (temperature: all three degrees of freedom).  `out` is a host array of the field shape
+ * (1-ng : n+ng per axis); cells the reference leaves undefined (poynt_flux ghosts) are zero.
+ *   MASS_DENSITY calc_mass_density :35      EKBAR calc_ekbar :119         EKFLUX calc_ekflux :232
+ *   POYNT_FLUX calc_poynt_flux :382         CHARGE_DENSITY calc_charge_density :439
+ *   NUMBER_DENSITY calc_number_density :523 PPC calc_ppc :598             AVERAGE_WEIGHT :652
+ *   TEMPERATURE calc_temperature :723       SPECIES_CURRENT calc_per_species_current :994
+ *   AVERAGE_MOMENTUM calc_average_momentum :1104 */
+#define EB200_DF_MASS_DENSITY 0
+#define EB200_DF_EKBAR 1
+#define EB200_DF_EKFLUX 2
+#define EB200_DF_POYNT_FLUX 3
+#define EB200_DF_CHARGE_DENSITY 4
+#define EB200_DF_NUMBER_DENSITY 5
+#define EB200_DF_PPC 6
+#define EB200_DF_AVERAGE_WEIGHT 7
+#define EB200_DF_TEMPERATURE 8
+#define EB200_DF_SPECIES_CURRENT 9
+#define EB200_DF_AVERAGE_MOMENTUM 10
+int32_t EB200_NAME(calc_derived)(EB200_CTX*, int32_t kind, int32_t ispecies, int32_t direction, double* out);
 /* options: "deterministic_deposit"="0|1", "push_kernel"="auto|baseline|tiled",
  * "sort_every"="<n>" */
 int32_t EB200_NAME(set_option)(EB200_CTX*, const char* key, const char* value);

@@ -309,6 +309,15 @@ int32_t orc_charge_residual(orc_ctx* c, double* max_res, double* max_rho) {
   charge_residual(c->s, max_res, max_rho, false);
   return 0;
 }
+int32_t orc_calc_derived(orc_ctx* c, int32_t kind, int32_t ispecies, int32_t direction, double* out) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  if (!out || kind < 0 || kind > 10 || ispecies >= (int32_t)c->s.species.size()) return EB200_E_ARG;
+  const int ad = direction < 0 ? -direction : direction;
+  const bool need_dir = kind == 2 || kind == 3 || kind == 9 || kind == 10;
+  if (ad > 3 || (need_dir && ad == 0) || (direction < 0 && kind != 2)) return EB200_E_ARG;
+  calc_derived(c->s, kind, ispecies, direction, out);
+  return 0;
+}
 int32_t orc_set_option(orc_ctx* c, const char* key, const char*) {
   if (c && key && std::string(key) == "capture_charge_reference") {
     double a, b;

@@ -266,9 +266,8 @@ void cpml_advance_currents(State& s, bool efield, double tstep) {
 // x_min neighbour of a periodic rank is itself, so A(nx+1:nx+ng) <- A(1:ng) and
 // A(1-ng:0) <- A(nx+1-ng:nx); x then y then z over FULL extents of the other dims;
 // on a non-periodic physical boundary the ghost cells are left untouched.
-static void field_bc_array(State& s, double* a);
 void field_bc(State& s, int comp) { field_bc_array(s, s.f[comp].data()); }
-static void field_bc_array(State& s, double* a) {
+void field_bc_array(State& s, double* a) {
   const int ng = s.ng;
   for (int ax = 0; ax < s.ndims; ++ax) {
     const int nn = s.n[ax];
@@ -286,15 +285,17 @@ static void field_bc_array(State& s, double* a) {
 
 // boundary.F90:623-698
 static void field_zero_gradient(State& s, int comp, int boundary /*0..5*/) {
+  if (boundary / 2 >= s.ndims) return;
+  field_zero_gradient_array(s, s.f[comp].data(), stagger(boundary / 2, comp), boundary);
+}
+void field_zero_gradient_array(State& s, double* a, bool stg, int boundary) {
   if (s.bc_field[boundary] == BC_PERIODIC) return;
   const int ax = boundary / 2;
   if (ax >= s.ndims) return;
   const bool is_max = boundary & 1;
   if (is_max ? !s.max_bnd[ax] : !s.min_bnd[ax]) return;
-  double* a = s.f[comp].data();
   const int ng = s.ng, nn = s.n[ax];
   const int64_t sa = s.st[ax];
-  const bool stg = stagger(ax, comp);
   for_each_line(s, ax, [&](int64_t base) {
     auto A = [&](int c) -> double& { return a[base + (int64_t)(c + ng - 1) * sa]; };
     if (!is_max) {
@@ -484,7 +485,9 @@ static int bc_allspecies(const State& s, int b) {
 
 // boundary.F90:787-919 particle_reflection_bcs + :923-1084 particle_periodic_bcs
 static void processor_summation_bcs(State& s, int comp, int flip_dir /*0..2*/) {
-  double* a = s.f[comp].data();
+  processor_summation_array(s, s.f[comp].data(), flip_dir);
+}
+void processor_summation_array(State& s, double* a, int flip_dir) {
   const int ng = s.ng;
   // reflection first
   for (int ax = 0; ax < s.ndims; ++ax) {

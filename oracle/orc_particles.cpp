@@ -410,7 +410,7 @@ void energy(const State& s, double* field_energy, double* per_species) {
 }
 
 // normalised weights of include/*/gxfac.inc
-static inline void weights_fac(int shape, double f, double* out) {
+void weights_fac(int shape, double f, double* out) {
   if (shape == 0) { out[0] = 0.5 + f; out[1] = 0.5 - f; }
   else if (shape == 1) {
     const double c2 = f * f;

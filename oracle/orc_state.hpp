@@ -25,6 +25,7 @@ constexpr double Q0 = 1.602176565e-19;
 constexpr double M0 = 9.10938291e-31;
 constexpr double C = 2.99792458e8;
 constexpr double KB = 1.3806488e-23;
+constexpr double C_TINY = 2.2250738585072014e-308;   // TINY(1.0_num), constants.F90:29
 constexpr double MU0 = 4.e-7 * PI;
 constexpr double EPS0 = 8.854187817620389850536563031710750e-12;
 
@@ -116,6 +117,11 @@ void update_e_field(State& s);
 void update_b_field(State& s);
 void set_half_step_scalars(State& s);
 void field_bc(State& s, int comp);                 // halo (single rank: periodic wrap)
+void field_bc_array(State& s, double* a);          // the same for any array of the field shape
+void field_zero_gradient_array(State& s, double* a, bool staggered, int boundary);   // boundary.F90:623-698
+void processor_summation_array(State& s, double* a, int flip_dir);                   // boundary.F90:1123-1144
+void weights_fac(int shape, double f, double* out);                                  // include/*/gxfac.inc
+void calc_derived(State& s, int kind, int ispecies, int direction, double* out);     // io/calc_df.F90
 void efield_bcs(State& s);
 void bfield_bcs(State& s, bool mpi_only);
 void bfield_final_bcs(State& s);

@@ -114,6 +114,10 @@ def main():
     ng = sim.ctx.ng
     parts = [sim.ctx.download_particles(i) for i in range(2)]
     f = sim.ctx.download_fields()
+    # derived grid variables (calc_df.F90) take part in the comparison like fields
+    DERIVED = [("charge_density", -1, 0), ("temperature", 0, 0), ("ekbar", 1, 0), ("species_current", -1, 1)]
+    for kind, isp, direction in DERIVED:
+        f["%s:%d:%d" % (kind, isp, direction)] = sim.ctx.calc_derived(kind, isp, direction)
     inter = {k: v[ng:-ng, ng:-ng, ng:-ng].copy() for k, v in f.items()}
     gathered = [None] * world
     dist.all_gather_object(gathered, (sim.cell_min, sim.cell_max, parts, inter))
@@ -123,6 +127,8 @@ def main():
         for _ in range(STEPS):
             ref.step_once()
         rf = ref.ctx.download_fields()
+        for kind, isp, direction in DERIVED:
+            rf["%s:%d:%d" % (kind, isp, direction)] = ref.ctx.calc_derived(kind, isp, direction)
         for isp in range(2):
             A = np.concatenate([g[2][isp] for g in gathered])
             B = ref.ctx.download_particles(isp)

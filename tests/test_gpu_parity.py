@@ -353,3 +353,29 @@ def test_group_velocity_cpml_gpu(product_abi, ndims, solver, rtol, printed, ptol
     record (Yee, Cowan, Pukhov to 10 digits; the Lehe recordings predate its present coefficients)."""
     from test_maxwell_solvers import cpml_deck, check_cpml
     check_cpml(cpml_deck(product_abi, ndims, solver), ndims, solver, rtol, printed, ptol)
+
+
+# ---- derived grid variables (io/calc_df.F90) -------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndims,shape,pbc,fbc", [(1, "triangle", "periodic", "periodic"), (1, "tophat", "reflect", "open"),
+                                                 (2, "triangle", "periodic", "periodic"), (2, "bspline3", "reflect", "conduct"),
+                                                 (3, "triangle", "reflect", "open"), (3, "tophat", "periodic", "periodic"),
+                                                 (3, "bspline3", "periodic", "periodic")])
+def test_derived_grid_variables(product_abi, oracle_abi, ndims, shape, pbc, fbc):
+    """every calc_df.F90 routine (mass/charge/number density, ekbar, ekflux, Poynting flux, ppc,
+    average weight, temperature, per-species current, average momentum) after two PIC steps:
+    CUDA == oracle on the whole array, ghosts included"""
+    from test_derived import CASES
+    bc_field = [fbc, fbc] + ["periodic"] * (2 * ndims - 2)
+    bcs = [pbc, pbc] + ["periodic"] * (2 * ndims - 2)
+    sims = [make_plasma(a, ndims, shape, [14, 10, 8], seed=17, ppc=3, u_th=0.8, bc_field=bc_field, bcs=bcs)
+            for a in (product_abi, oracle_abi)]
+    for s in sims:
+        for _ in range(2):
+            s.step_once()
+    for kind, isp, direction in CASES:
+        a, b = (s.ctx.calc_derived(kind, isp, direction) for s in sims)
+        scale = np.max(np.abs(b))
+        assert scale > 0, (kind, isp, direction)
+        tol = 1e-9 if kind == "temperature" else 1e-11      # the variance subtracts the mean momentum
+        assert np.max(np.abs(a - b)) <= tol * scale, (kind, isp, direction, np.max(np.abs(a - b)) / scale)
