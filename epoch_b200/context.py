@@ -248,6 +248,21 @@ class PicContext:
         self._ck(self.abi.charge_residual(self._ctx, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    # -- load balancing (housekeeping/balance.F90) ---------------------------------
+    def get_load(self, grid_min_global, n_global):
+        """this rank's load_x, load_y, load_z of part_load_func (before the ALLREDUCE)"""
+        out = [np.zeros(int(n_global[a]) + 2 * self.ng, dtype=np.int64) for a in range(self.ndims)]
+        ptr = [o.ctypes.data_as(C.POINTER(C.c_int64)) for o in out] + [None] * (3 - self.ndims)
+        self._ck(self.abi.get_load(self._ctx, _f64(_pad3(grid_min_global, 0.0)), *ptr))
+        return out
+
+    def redistribute(self, old_min, old_max, new_min, new_max, grid_min_global, grid_min_local, min_local, max_local):
+        """old_min .. new_max: per axis lists of the 1-based cell ranges of every processor coordinate"""
+        flat = [_i32([int(v) for ax in t for v in ax]) for t in (old_min, old_max, new_min, new_max)]
+        self._ck(self.abi.redistribute(self._ctx, *flat, _f64(_pad3(grid_min_global, 0.0)),
+                                       _f64(_pad3(grid_min_local, 0.0)), _f64(_pad3(min_local, 0.0)),
+                                       _f64(_pad3(max_local, 0.0))))
+
     DERIVED = {"mass_density": 0, "ekbar": 1, "ekflux": 2, "poynt_flux": 3, "charge_density": 4,
                "number_density": 5, "ppc": 6, "average_weight": 7, "temperature": 8,
                "species_current": 9, "average_momentum": 10}

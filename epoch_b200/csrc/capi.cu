@@ -376,6 +376,24 @@ int32_t eb200_download_fields(eb200_ctx* c, double* ex, double* ey, double* ez, 
   return 0;
 }
 
+int32_t eb200_get_load(eb200_ctx* c, const double grid_min_global[3], int64_t* load_x, int64_t* load_y, int64_t* load_z) {
+  CHECK_CTX(c); NEED_GRID(c);
+  if (!grid_min_global) return fail(c, EB200_E_ARG, "get_load: null grid_min_global");
+  long long* const load[3] = {(long long*)load_x, (long long*)load_y, (long long*)load_z};
+  return get_load(c, grid_min_global, load);
+}
+
+int32_t eb200_redistribute(eb200_ctx* c, const int32_t* old_cell_min, const int32_t* old_cell_max,
+                           const int32_t* new_cell_min, const int32_t* new_cell_max, const double grid_min_global[3],
+                           const double grid_min_local[3], const double min_local[3], const double max_local[3]) {
+  CHECK_CTX(c); NEED_GRID(c);
+  if (!old_cell_min || !old_cell_max || !new_cell_min || !new_cell_max || !grid_min_global || !grid_min_local ||
+      !min_local || !max_local)
+    return fail(c, EB200_E_ARG, "redistribute: null argument");
+  return redistribute(c, old_cell_min, old_cell_max, new_cell_min, new_cell_max, grid_min_global, grid_min_local,
+                      min_local, max_local);
+}
+
 int32_t eb200_calc_derived(eb200_ctx* c, int32_t kind, int32_t ispecies, int32_t direction, double* out) {
   CHECK_CTX(c); NEED_GRID(c);
   if (!out) return fail(c, EB200_E_ARG, "calc_derived: null output array");

@@ -106,4 +106,28 @@ int32_t comm_sendrecv_v(eb200_ctx* c, const double* send, int dst, size_t nsend,
   return 0;
 }
 
+// every rank sends cnt_s[r] doubles at send + off_s[r] to rank r and receives cnt_r[r] doubles at
+// recv + off_r[r] from it, in one NCCL group (balance.F90's MPI_ALLTOALLW of redistribute_field_*);
+// the part a rank keeps is a device-to-device copy
+int32_t comm_alltoallv(eb200_ctx* c, const double* send, const size_t* off_s, const size_t* cnt_s, double* recv,
+                       const size_t* off_r, const size_t* cnt_r) {
+  const int me = c->rank;
+  if (cnt_s[me] != cnt_r[me]) return fail(c, EB200_E_STATE, "alltoallv: self counts differ");
+  if (cnt_s[me])
+    EB_CUDA(c, cudaMemcpyAsync(recv + off_r[me], send + off_s[me], cnt_s[me] * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+  if (c->nproc <= 1) return 0;
+  if (!c->nccl) return fail(c, EB200_E_STATE, "NCCL communicator not initialised");
+  Nccl* l = c->nccl;
+  ncclResult_t r = l->GroupStart();
+  for (int p = 0; p < c->nproc && r == 0; ++p) {
+    if (p == me) continue;
+    if (cnt_s[p]) r = l->Send(send + off_s[p], cnt_s[p], ncclFloat64, p, l->comm, c->stream);
+    if (r == 0 && cnt_r[p]) r = l->Recv(recv + off_r[p], cnt_r[p], ncclFloat64, p, l->comm, c->stream);
+  }
+  ncclResult_t r2 = l->GroupEnd();
+  if (r != 0 || r2 != 0)
+    return fail(c, EB200_E_NCCL, std::string("nccl alltoallv: ") + (l->GetErrorString ? l->GetErrorString(r ? r : r2) : "error"));
+  return 0;
+}
+
 }  // namespace eb

@@ -224,6 +224,17 @@ void comm_destroy(eb200_ctx* c);
 // recv_hi comes from nbr_hi (first call), etc.  Null neighbours are skipped.
 int32_t comm_sendrecv(eb200_ctx* c, const double* send, int dst, double* recv, int src, size_t count);
 int32_t comm_sendrecv_v(eb200_ctx* c, const double* send, int dst, size_t nsend, double* recv, int src, size_t nrecv);
+int32_t comm_alltoallv(eb200_ctx* c, const double* send, const size_t* off_s, const size_t* cnt_s, double* recv,
+                       const size_t* off_r, const size_t* cnt_r);
+// balance.cu / particles.cu: the new owner of a position (get_particle_processor, balance.F90:2673-2746):
+// lb[a][i] = lower edge x_grid_mins(i) - dx/2 of processor coordinate i along axis a (lb[a][0] unused)
+constexpr int MAXP_AXIS = 32;
+struct OwnerP { int np[3]; double lb[3][MAXP_AXIS]; };
+int32_t redistribute_particles(eb200_ctx* c, const OwnerP& own, std::vector<long long>& n_slots);
+int32_t get_load(eb200_ctx* c, const double grid_min_global[3], long long* const load[3]);
+int32_t redistribute(eb200_ctx* c, const int32_t* old_cell_min, const int32_t* old_cell_max, const int32_t* new_cell_min,
+                     const int32_t* new_cell_max, const double grid_min_global[3], const double grid_min_local[3],
+                     const double min_local[3], const double max_local[3]);
 // particles.cu
 int32_t push_particles(eb200_ctx* c);
 int32_t particle_bcs(eb200_ctx* c);

@@ -493,6 +493,95 @@ static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool&
   return 0;
 }
 
+// ---------------------------------------------------------------------------------
+// distribute_particles (balance.F90:2751-2809): after the domain was re-sliced every particle
+// goes to the rank that owns its position.  A ring of nproc - 1 shifts; per shift the leavers
+// for one destination are packed and exchanged in bounded chunks (the staging buffers stay small
+// however much of the plasma changes hands).
+// ---------------------------------------------------------------------------------
+__global__ void k_flag_owner(OwnerP own, int nd, int npx, int npy, long long n, const double* __restrict__ x,
+                             const double* __restrict__ y, const double* __restrict__ z, const uint32_t* __restrict__ key,
+                             uint32_t* flag, unsigned long long* counters, int dst, unsigned long long cap) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  flag[i] = 0;
+  if (key[i] == KEY_INVALID) return;
+  const double pos[3] = {x[i], nd >= 2 ? y[i] : 0.0, nd >= 3 ? z[i] : 0.0};
+  int co[3] = {0, 0, 0};
+  for (int a = 0; a < nd; ++a)
+    for (int p = own.np[a] - 1; p >= 1; --p)
+      if (pos[a] >= own.lb[a][p]) { co[a] = p; break; }
+  const int owner = (co[2] * npy + co[1]) * npx + co[0];
+  if (owner != dst) return;
+  if (atomicAdd(counters + 0, 1ULL) < cap) flag[i] = 1;
+  else atomicAdd(counters + 1, 1ULL);
+}
+
+int32_t redistribute_particles(eb200_ctx* c, const OwnerP& own, std::vector<long long>& slots) {
+  const int nvar = c->ndims + 4, P = c->nproc;
+  slots.assign(c->species.size(), 0);
+  for (size_t is = 0; is < c->species.size(); ++is) {
+    SpeciesD& sp = c->species[is];
+    if (!sp.defined) continue;
+    long long n_slots = sp.n;
+    if (n_slots > 0) {                     // every live slot is a candidate
+      EB_TRY(species_reserve(c, sp, n_slots));
+      k_fill_u32<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(sp.key, n_slots, 0u);
+      c->launches++;
+    }
+    const long long chunk = std::max<long long>(c->mig_min_particles, 1LL << 22);
+    EB_TRY(ensure_stage(c, chunk * nvar));
+    for (int s = 1; s < P; ++s) {
+      const int dst = (c->rank + s) % P, src = (c->rank - s + P) % P;
+      for (;;) {
+        EB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
+        if (n_slots > 0) {
+          k_flag_owner<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(own, c->ndims, c->nprocdir[0], c->nprocdir[1],
+              n_slots, sp.a[0], sp.a[1], sp.a[2], sp.key, sp.dest, c->d_counters, dst, (unsigned long long)chunk);
+          c->launches++;
+        }
+        EB_TRY(read_counters(c, 2));
+        const long long total = (long long)c->h_counters[0], left = (long long)c->h_counters[1], nsend = total - left;
+        if (nsend > 0) {
+          k_pack_leavers<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(n_slots, c->ndims, sp.a[0], sp.a[1], sp.a[2],
+              sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key, sp.dest, c->d_counters, c->mig_send[0], c->mig_send[1]);
+          c->launches++;
+        }
+        double* cnt = c->d_red;            // [0] sent now, [1] still to come -> [2], [3] from src
+        const double hc[2] = {(double)nsend, (double)left};
+        EB_CUDA(c, cudaMemcpyAsync(cnt, hc, 2 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        EB_TRY(comm_sendrecv(c, cnt, dst, cnt + 2, src, 2));
+        EB_CUDA(c, cudaMemcpyAsync(c->h_red, cnt, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        EB_CUDA(c, cudaStreamSynchronize(c->stream));
+        const long long nrecv = (long long)c->h_red[2], src_left = (long long)c->h_red[3];
+        EB_TRY(comm_sendrecv_v(c, c->mig_send[0], nsend > 0 ? dst : -1, (size_t)nsend * nvar,
+                               c->mig_recv[0], nrecv > 0 ? src : -1, (size_t)nrecv * nvar));
+        if (nrecv > 0) {
+          const long long keep_n = sp.n;
+          sp.n = n_slots;
+          EB_TRY(species_reserve(c, sp, n_slots + nrecv));
+          sp.n = keep_n;
+          k_unpack_aos<<<(unsigned)((nrecv + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[0], c->ndims, nrecv, n_slots,
+              sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
+          n_slots += nrecv; c->launches++;
+        }
+        if (left == 0 && src_left == 0) break;
+      }
+    }
+    sp.sorted = false;
+    slots[is] = n_slots;
+  }
+  EB_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+// sort_species for the caller of redistribute_particles (after the new grid is set)
+int32_t resort_after_redistribute(eb200_ctx* c, const std::vector<long long>& slots) {
+  for (size_t is = 0; is < c->species.size(); ++is)
+    if (c->species[is].defined) EB_TRY(sort_species(c, c->species[is], slots[is]));
+  return 0;
+}
+
 int32_t particle_bcs(eb200_ctx* c) {
   for (SpeciesD& sp : c->species) {
     if (!sp.defined) continue;

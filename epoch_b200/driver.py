@@ -99,6 +99,11 @@ class Simulation:
             self.cell_min.append(lo)
             self.cell_max.append(hi)
         self.n_local = [self.cell_max[d] - self.cell_min[d] + 1 for d in range(nd)]
+        # cell_x_min / cell_x_max ... of every processor coordinate (mpi_routines.F90:444-476)
+        self.cell_mins = [[decomp.cell_range(self.n_global[d], self.nprocdir[d], p)[0] for p in range(self.nprocdir[d])]
+                          for d in range(nd)]
+        self.cell_maxs = [[decomp.cell_range(self.n_global[d], self.nprocdir[d], p)[1] for p in range(self.nprocdir[d])]
+                          for d in range(nd)]
         # setup_grid_x: utilities.f90:343-373 (x_global(ix) = x_grid_min + (ix-1)*dx)
         self.grid_min_local = [self.grid_min[d] + (self.cell_min[d] - 1) * self.d[d] for d in range(nd)]
         grid_max_local = [self.grid_min[d] + (self.cell_max[d] - 1) * self.d[d] for d in range(nd)]
@@ -362,6 +367,51 @@ class Simulation:
         ctx.bfield_final_bcs()
         ctx.set_time(dt_store, self.time, self.step)
         self._started = True
+
+    # -- load balancing (housekeeping/balance.F90) --------------------------------
+    def balance_workload(self, allreduce=None, new_tables=None):
+        """The re-slicing part of balance_workload (balance.F90:175-319) with over_ride: global
+        load histograms from the device (get_load), calculate_breaks per decomposed axis, then
+        redistribute_domain on the device.  allreduce(np.int64 array) -> sum over ranks.
+        new_tables = (mins, maxs) overrides the computed breaks (tests)."""
+        from . import balance
+        nd = self.ndims
+        if new_tables is None:
+            local = self.ctx.get_load(self.grid_min, self.n_global)
+            loads = balance.global_load(local, self.n_global, self.ctx.ng, allreduce)
+            new_mins, new_maxs = [], []
+            for a in range(nd):
+                mn, mx = balance.calculate_breaks(loads[a], self.nprocdir[a], self.ctx.ng, balance.ncell_min(PNG[self.shape]))
+                new_mins.append(mn)
+                new_maxs.append(mx)
+        else:
+            new_mins, new_maxs = [list(map(int, t)) for t in new_tables[0]], [list(map(int, t)) for t in new_tables[1]]
+        if new_mins == self.cell_mins and new_maxs == self.cell_maxs:
+            return False
+        old_mins, old_maxs = self.cell_mins, self.cell_maxs
+        self.cell_mins, self.cell_maxs = new_mins, new_maxs
+        self.cell_min = [new_mins[d][self.coords[d]] for d in range(nd)]
+        self.cell_max = [new_maxs[d][self.coords[d]] for d in range(nd)]
+        self.n_local = [self.cell_max[d] - self.cell_min[d] + 1 for d in range(nd)]
+        self.grid_min_local = [self.grid_min[d] + (self.cell_min[d] - 1) * self.d[d] for d in range(nd)]
+        grid_max_local = [self.grid_min[d] + (self.cell_max[d] - 1) * self.d[d] for d in range(nd)]
+        cp = [self.set_cpml_helpers(d) for d in range(nd)] if self.cpml_boundaries else None
+        off = [(c["min_offset"], c["max_offset"]) for c in cp] if cp else [(0, 0)] * nd
+        self._cpml_off = off
+        self.min_local = [self.grid_min_local[d] + (off[d][0] - 0.5) * self.d[d] for d in range(nd)]
+        self.max_local = [grid_max_local[d] - (off[d][1] - 0.5) * self.d[d] for d in range(nd)]
+        self.ctx.redistribute(old_mins, old_maxs, new_mins, new_maxs, self.grid_min, self.grid_min_local,
+                              self.min_local, self.max_local)
+        self.ctx.n = tuple(self.n_local)
+        self.ctx.field_shape = tuple(x + 2 * self.ctx.ng for x in self.ctx.n)
+        # what the host redistributes itself and hands over again
+        if cp:
+            for d in range(nd):
+                self.ctx.set_cpml(d, **{k: v for k, v in cp[d].items() if k not in ("min_offset", "max_offset")})
+        self._setup_lasers()
+        if getattr(self, "window", None) is not None:
+            self.ctx.set_window_fields(None)
+        return True
 
     # -- moving window (housekeeping/window.F90) ---------------------------------
     def enable_window(self, v_x, start_time=0.0, stop_time=1e300, insert=None, planes=None):

@@ -77,6 +77,7 @@ CONTAINS
       CALL gpu_check(eb200_set_current_options(gpu, MERGE(1, 0, smooth_currents), smooth_its, smooth_comp_its, &
           0, [1_C_INT32_T], MERGE(1, 0, use_current_correction), [initial_jx, initial_jy, initial_jz]))
     END IF
+    CALL gpu_resend_lasers
     DO ispecies = 1, n_species
       bcp = INT(species_list(ispecies)%bc_particle, C_INT32_T)
       CALL gpu_check(eb200_set_species(gpu, ispecies - 1, species_list(ispecies)%charge, &
@@ -166,6 +167,21 @@ CONTAINS
     host_stale = .FALSE.
   END SUBROUTINE gpu_sync_to_host
 
+  SUBROUTINE gpu_resend_lasers
+    ! TYPE(laser_block) amplitudes and the profile / phase planes on this rank's boundary
+    ! (laser.f90:232-330); again after the planes were re-sliced by balance_workload
+    TYPE(laser_block), POINTER :: current
+    INTEGER :: ib
+    DO ib = 1, 2 * c_ndims
+      current => laser_boundary_head(ib)
+      DO WHILE (ASSOCIATED(current))
+        CALL gpu_check(eb200_set_laser(gpu, ib, current%id, current%amp, current%pol_angle, current%t_start, &
+            current%t_end, C_LOC(current%profile), C_LOC(current%phase)))
+        current => current%next
+      END DO
+    END DO
+  END SUBROUTINE gpu_resend_lasers
+
   SUBROUTINE gpu_laser_step
     ! the host keeps evaluating the deck's time profiles (laser.f90:207-226,334-346)
     TYPE(laser_block), POINTER :: current
@@ -208,6 +224,48 @@ CONTAINS
   SUBROUTINE gpu_shift_window
     CALL gpu_check(eb200_shift_window(gpu, x_grid_min_local, x_min_local, x_max_local, x_min, x_max))
   END SUBROUTINE gpu_shift_window
+
+  ! ---- load balancing (housekeeping/balance.F90) ----
+  ! part_load_func (:2468): the device counts this rank's particles per global cell; get_load's
+  ! MPI_ALLREDUCE and push_per_field weighting (:2446-2460) stay as they are.
+  SUBROUTINE part_load_func(load_x, load_y, load_z)
+    INTEGER(i8), DIMENSION(1-ng:), INTENT(OUT) :: load_x, load_y, load_z
+    CALL gpu_check(eb200_get_load(gpu, [x_grid_min, y_grid_min, z_grid_min], load_x, load_y, load_z))
+  END SUBROUTINE part_load_func
+
+  ! redistribute_domain (:411-472): called by balance_workload after calculate_breaks filled
+  ! new_cell_*_min/max and after the new local grid scalars were set (setup_grid_x etc. with the
+  ! new nx_global_min); fields, psi arrays and particles move on the device, rank to rank.
+  SUBROUTINE gpu_redistribute_domain(x_grid_min_local_new, y_grid_min_local_new, z_grid_min_local_new, &
+      mins_new, maxs_new)
+    REAL(num), INTENT(IN) :: x_grid_min_local_new, y_grid_min_local_new, z_grid_min_local_new
+    REAL(num), INTENT(IN) :: mins_new(3), maxs_new(3)
+    CALL gpu_check(eb200_redistribute(gpu, &
+        INT([cell_x_min, cell_y_min, cell_z_min], C_INT32_T), INT([cell_x_max, cell_y_max, cell_z_max], C_INT32_T), &
+        INT([new_cell_x_min, new_cell_y_min, new_cell_z_min], C_INT32_T), &
+        INT([new_cell_x_max, new_cell_y_max, new_cell_z_max], C_INT32_T), &
+        [x_grid_min, y_grid_min, z_grid_min], &
+        [x_grid_min_local_new, y_grid_min_local_new, z_grid_min_local_new], mins_new, maxs_new))
+    ! the host keeps redistributing its own small arrays (laser profiles, window planes, CPML
+    ! profiles via set_cpml_helpers) and hands them over again
+    IF (cpml_boundaries) CALL gpu_set_cpml
+    CALL gpu_resend_lasers
+    host_stale = .TRUE.
+  END SUBROUTINE gpu_redistribute_domain
+
+  ! ---- derived grid variables for output_routines (io/calc_df.F90) ----
+  ! e.g. calc_number_density(array, ispecies) becomes
+  !   CALL gpu_calc_derived(EB200_DF_NUMBER_DENSITY, array, ispecies)
+  SUBROUTINE gpu_calc_derived(kind, data_array, current_species, direction)
+    INTEGER, INTENT(IN) :: kind, current_species
+    REAL(num), DIMENSION(1-ng:,1-ng:,1-ng:), INTENT(OUT) :: data_array
+    INTEGER, INTENT(IN), OPTIONAL :: direction
+    INTEGER :: dir
+    dir = 0
+    IF (PRESENT(direction)) dir = direction
+    ! current_species <= 0 means the sum over species (-1 in the C ABI); species are 0-based there
+    CALL gpu_check(eb200_calc_derived(gpu, kind, MAX(current_species, 0) - 1, dir, data_array))
+  END SUBROUTINE gpu_calc_derived
 
   SUBROUTINE update_eb_fields_final         ! fields.f90:851
     CALL gpu_check(eb200_set_time(gpu, dt, time, step))

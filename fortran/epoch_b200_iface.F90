@@ -68,6 +68,27 @@ MODULE epoch_b200_iface
       INTEGER(C_INT32_T), VALUE :: axis, min_start, min_end, max_start, max_end, laser_idx_min, laser_idx_max
       REAL(C_DOUBLE), INTENT(IN) :: kappa_e(*), kappa_b(*), sigma_e(*), sigma_b(*), a_e(*), a_b(*)
     END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_get_load(ctx, grid_min_global, load_x, load_y, load_z) &
+        BIND(C, NAME='eb200_get_load')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      REAL(C_DOUBLE), INTENT(IN) :: grid_min_global(3)
+      INTEGER(C_INT64_T), INTENT(OUT) :: load_x(*), load_y(*), load_z(*)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_redistribute(ctx, old_cell_min, old_cell_max, new_cell_min, new_cell_max, &
+        grid_min_global, grid_min_local, min_local, max_local) BIND(C, NAME='eb200_redistribute')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), INTENT(IN) :: old_cell_min(*), old_cell_max(*), new_cell_min(*), new_cell_max(*)
+      REAL(C_DOUBLE), INTENT(IN) :: grid_min_global(3), grid_min_local(3), min_local(3), max_local(3)
+    END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_calc_derived(ctx, kind, ispecies, direction, data_array) &
+        BIND(C, NAME='eb200_calc_derived')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: kind, ispecies, direction
+      REAL(C_DOUBLE), INTENT(OUT) :: data_array(*)
+    END FUNCTION
     INTEGER(C_INT32_T) FUNCTION eb200_set_species(ctx, ispecies, charge, mass, weight, immobile, &
         zero_current, species_type, bc_particle) BIND(C, NAME='eb200_set_species')
       IMPORT

@@ -215,6 +215,29 @@ int32_t EB200_NAME(energy)(EB200_CTX*, double* field_energy,
  * with the normalised weights of calc_charge_density (calc_df.F90:439-519). */
 int32_t EB200_NAME(charge_residual)(EB200_CTX*, double* max_abs_residual,
                                     double* max_abs_rho_over_eps0);
+/* Load balancing (housekeeping/balance.F90).  The decision -- balance_workload :107-319 and
+ * calculate_breaks :2526-2669, a few hundred integers -- stays on the host; the device supplies
+ * its input and carries the result out.
+ * get_load: this rank's part of part_load_func (:2468-2495), i.e. the arrays load_x, load_y,
+ * load_z (1-ng : n_global+ng, any of them may be NULL) BEFORE the MPI_ALLREDUCE and the
+ * push_per_field weighting of get_load (:2411-2464); grid_min_global = x_grid_min, y_grid_min,
+ * z_grid_min (centre of global cell 1).
+ * redistribute: redistribute_domain (:411-472) for the state the library holds: the nine field
+ * arrays and the CPML psi arrays move as redistribute_field_3d does (:1652-1966: intersections of
+ * old and new sub-domains, edge ghost cells travel with the edge cells, then
+ * do_field_mpi_with_lengths), the particles as distribute_particles does (:2751-2809,
+ * get_particle_processor :2673-2746).  The four tables are cell_{x,y,z}_min/max and
+ * new_cell_{x,y,z}_min/max concatenated [x | y | z] with nprocdir[a] entries per existing axis;
+ * the three scalar triples are the rank's NEW *_grid_min_local, *_min_local, *_max_local.
+ * Afterwards the grid is the new one (as after set_grid); the host re-sends what it redistributes
+ * itself: laser profiles (set_laser), window planes (set_window_fields), CPML profiles (set_cpml). */
+int32_t EB200_NAME(get_load)(EB200_CTX*, const double grid_min_global[3], int64_t* load_x, int64_t* load_y,
+                             int64_t* load_z);
+int32_t EB200_NAME(redistribute)(EB200_CTX*, const int32_t* old_cell_min, const int32_t* old_cell_max,
+                                 const int32_t* new_cell_min, const int32_t* new_cell_max,
+                                 const double grid_min_global[3], const double grid_min_local[3],
+                                 const double min_local[3], const double max_local[3]);
+
 /* Derived grid variables of io/calc_df.F90, computed where the particles live so that
  * output_routines pulls one reduced grid instead of the particle lists.
  * kind: EB200_DF_* below; ispecies: 0-based species, or -1 for the sum over species

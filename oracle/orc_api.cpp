@@ -309,6 +309,37 @@ int32_t orc_charge_residual(orc_ctx* c, double* max_res, double* max_rho) {
   charge_residual(c->s, max_res, max_rho, false);
   return 0;
 }
+// part_load_func (balance.F90:2468-2495) for this (single) rank
+int32_t orc_get_load(orc_ctx* c, const double grid_min_global[3], int64_t* load_x, int64_t* load_y, int64_t* load_z) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  if (!grid_min_global) return EB200_E_ARG;
+  State& s = c->s;
+  int64_t* load[3] = {load_x, load_y, load_z};
+  for (int a = 0; a < s.ndims; ++a)
+    if (load[a]) std::fill(load[a], load[a] + s.nglob[a] + 2 * s.ng, (int64_t)0);
+  for (const Species& sp : s.species) {
+    if (!sp.defined) continue;
+    for (size_t ip = 0; ip < sp.count(); ++ip)
+      for (int a = 0; a < s.ndims; ++a) {
+        if (!load[a]) continue;
+        const double r = (sp.pos[a][ip] - grid_min_global[a]) / s.d[a];
+        const int cell = s.shape == 0 ? (int)std::floor(r) + 1 : (int)std::floor(r + 1.5);
+        const int pos = std::min(std::max(cell + s.ng - 1, 0), s.nglob[a] + 2 * s.ng - 1);
+        load[a][pos] += 1;
+      }
+  }
+  return 0;
+}
+// the oracle is a single rank: a redistribution can only map the whole grid onto itself
+int32_t orc_redistribute(orc_ctx* c, const int32_t* old_cell_min, const int32_t* old_cell_max, const int32_t* new_cell_min,
+                         const int32_t* new_cell_max, const double*, const double*, const double*, const double*) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  if (!old_cell_min || !old_cell_max || !new_cell_min || !new_cell_max) return EB200_E_ARG;
+  for (int a = 0; a < c->s.ndims; ++a)
+    if (new_cell_min[a] != 1 || new_cell_max[a] != c->s.nglob[a] || old_cell_min[a] != 1 || old_cell_max[a] != c->s.nglob[a])
+      return EB200_E_ARG;
+  return 0;
+}
 int32_t orc_calc_derived(orc_ctx* c, int32_t kind, int32_t ispecies, int32_t direction, double* out) {
   if (!c || !c->s.grid_set) return EB200_E_STATE;
   if (!out || kind < 0 || kind > 10 || ispecies >= (int32_t)c->s.species.size()) return EB200_E_ARG;

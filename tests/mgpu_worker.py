@@ -20,6 +20,7 @@ STEPS = int(sys.argv[2]) if len(sys.argv) > 2 else 4
 SHAPE = sys.argv[3] if len(sys.argv) > 3 else "triangle"
 WINDOW = len(sys.argv) > 4 and sys.argv[4] == "window"      # moving window at 0.9 c (x decomposition, open x boundaries)
 CPML = len(sys.argv) > 4 and sys.argv[4] == "cpml"          # CPML layers on the decomposed axis and on x
+BALANCE = len(sys.argv) > 4 and sys.argv[4] == "balance"    # lopsided plasma, re-sliced after 2 steps
 N = [16, 12, 20]
 CELL = 1e-6
 
@@ -69,6 +70,8 @@ def build(abi, rank, nproc, nccl_id, device):
         P[:, 3:6] = rng.normal(0.0, 0.6, (npart, 3)) * s.mass * C
         P[:, 6] = 1e25 * CELL ** 3 / 6 * (1.0 + np.arange(npart) / npart)      # unique weights
         own = np.ones(npart, bool)
+        if BALANCE:       # most of the plasma sits in the low 40 % of the decomposed axis
+            own &= (P[:, AXIS] < 0.4 * N[AXIS] * CELL) | (rng.random(npart) < 0.15)
         for d in range(3):
             own &= (P[:, d] >= sim.min_local[d]) & (P[:, d] < sim.max_local[d])
         sim.ctx.upload_particles(isp, P[own])
@@ -109,7 +112,23 @@ def main():
         buf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
     dist.broadcast(buf, 0)
     sim = build(abi, rank, world, bytes(buf.cpu().numpy().tobytes()), local)
-    for _ in range(STEPS):
+    def allreduce(a):
+        t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        dist.all_reduce(t)
+        return t.cpu().numpy()
+    for it in range(STEPS):
+        if BALANCE and it == 2:
+            before = [sim.ctx.particle_count(i) for i in range(2)]
+            changed = sim.balance_workload(allreduce)
+            after = [sim.ctx.particle_count(i) for i in range(2)]
+            tot = allreduce(np.array([sum(before), sum(after), max(sum(after), 0)], dtype=np.int64))
+            mx = torch.tensor([sum(before), sum(after)], device="cuda")
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            if rank == 0:
+                print("balance: changed", changed, "tables", sim.cell_mins[AXIS], sim.cell_maxs[AXIS],
+                      "particles total", int(tot[0]), "->", int(tot[1]), "max per rank", mx.tolist())
+            assert changed and tot[0] == tot[1], "re-slicing must move the break and keep every particle"
+            assert mx[1].item() < mx[0].item(), "the fullest rank must hold fewer particles afterwards"
         sim.step_once()
     ng = sim.ctx.ng
     parts = [sim.ctx.download_particles(i) for i in range(2)]

@@ -379,3 +379,35 @@ def test_derived_grid_variables(product_abi, oracle_abi, ndims, shape, pbc, fbc)
         assert scale > 0, (kind, isp, direction)
         tol = 1e-9 if kind == "temperature" else 1e-11      # the variance subtracts the mean momentum
         assert np.max(np.abs(a - b)) <= tol * scale, (kind, isp, direction, np.max(np.abs(a - b)) / scale)
+
+
+# ---- load-balancing hooks (housekeeping/balance.F90) ---------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndims,shape", [(1, "triangle"), (2, "tophat"), (3, "triangle"), (3, "bspline3")])
+def test_get_load(product_abi, oracle_abi, ndims, shape):
+    """part_load_func histograms after three steps: CUDA == oracle exactly (integers)"""
+    sims = [make_plasma(a, ndims, shape, [14, 10, 8], seed=23, ppc=4, u_th=0.8) for a in (product_abi, oracle_abi)]
+    for s in sims:
+        for _ in range(3):
+            s.step_once()
+    la, lb = (s.ctx.get_load(s.grid_min, s.n_global) for s in sims)
+    for a in range(ndims):
+        assert np.array_equal(la[a], lb[a]) and la[a].sum() == sum(len(p) for p in sims[0].loads)
+
+
+@pytest.mark.gpu
+def test_redistribute_single_rank_identity(product_abi, oracle_abi):
+    """re-slicing onto the same (whole) domain goes through the full device path (pack, copy,
+    unpack, halo refresh, re-sort) and must change nothing"""
+    sims = [make_plasma(a, 3, "triangle", [12, 10, 8], seed=29, ppc=3, bc_field=["open"] * 2 + ["periodic"] * 4,
+                        bcs=["reflect"] * 2 + ["periodic"] * 4) for a in (product_abi, oracle_abi)]
+    for s in sims:
+        s.step_once()
+    g = sims[0]
+    g.ctx.redistribute(g.cell_mins, g.cell_maxs, g.cell_mins, g.cell_maxs, g.grid_min, g.grid_min_local,
+                       g.min_local, g.max_local)
+    g._setup_lasers()
+    for s in sims:
+        s.step_once()
+    compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
+    compare_particles(sims[0], sims[1], tol=1e-10)

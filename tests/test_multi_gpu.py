@@ -46,3 +46,16 @@ def test_two_ranks_cpml(axis):
            "--master-port", str(29631 + axis), os.path.join(ROOT, "tests", "mgpu_worker.py"), str(axis), "6", "triangle", "cpml"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("axis", [0, 2])
+def test_two_ranks_rebalance(axis):
+    """a lopsided plasma is re-sliced mid-run (get_load -> calculate_breaks -> redistribute of
+    fields and particles over NCCL): the break moves, no particle is lost, the fullest rank gets
+    lighter and the run still equals the single-GPU run"""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(29641 + axis), os.path.join(ROOT, "tests", "mgpu_worker.py"), str(axis), "6", "triangle", "balance"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
