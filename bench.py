@@ -265,11 +265,15 @@ def run_ours(args):
     n_part = c ** 3 * PPC
     t_setup = time.perf_counter()
     sim = make_sim(abi, cells_global, rank, world, nccl_id, device=local)
-    sim.ctx.set_option("reserve", f"0:{n_part + n_part // 64 if world > 1 else n_part}")
-    sim.ctx.set_option("timers", 1)
+    # deferred permute: head room between the two states of the particle arrays (7 % of the species:
+    # one layer of tiles of displacement + one slab of tiles per launch) and room for migration arrivals
+    sim.ctx.set_option("defer_window", max(n_part // 14, min(n_part // 2, 1 << 24)))
+    sim.ctx.set_option("defer_gap", n_part // 256 if world > 1 else 0)
     for kv in args.opt:                       # tuning experiments: --opt push_kernel=tiled
         k, v = kv.split("=", 1)
         sim.ctx.set_option(k, v)
+    sim.ctx.set_option("reserve", f"0:{n_part + n_part // 64 if world > 1 else n_part}")
+    sim.ctx.set_option("timers", 1)
     # host copy of this rank's particle load (also the e2e leg's host buffer) -- if the host
     # has the memory for one per rank; else the load is generated and uploaded in slabs and
     # the e2e leg (which needs the whole state in host buffers) is skipped
@@ -324,6 +328,7 @@ def run_ours(args):
     launches = sim.ctx.timer("launches")[1] - l0
     ms = max_over_ranks(dev_ms)
     phases = {ph: sim.ctx.timer(ph) for ph in ("push", "push_kernel", "push_A", "push_B", "sort", "fields", "halo", "bcs")}
+    sorts = {"deferred_to_next_push": sim.ctx.timer("deferred_sorts")[1], "permuted_in_sort": sim.ctx.timer("permuted_sorts")[1]}
     n_live = sim.ctx.particle_count(0)
     value = n_part * world * args.steps / (ms * 1e-3)
 
@@ -382,10 +387,12 @@ def run_ours(args):
         barrier(); torch.cuda.synchronize()
         t0 = time.perf_counter()
         sim2 = make_sim(abi, cells_e2e, rank, world, nccl_id2, device=local)
-        sim2.ctx.set_option("reserve", f"0:{n_e2e + n_e2e // 64 if world > 1 else n_e2e}")
+        sim2.ctx.set_option("defer_window", max(n_e2e // 14, min(n_e2e // 2, 1 << 24)))
+        sim2.ctx.set_option("defer_gap", n_e2e // 256 if world > 1 else 0)
         for kv in args.opt:
             k, v = kv.split("=", 1)
             sim2.ctx.set_option(k, v)
+        sim2.ctx.set_option("reserve", f"0:{n_e2e + n_e2e // 64 if world > 1 else n_e2e}")
         shp = sim2.ctx._np_shape()
         fzero = np.zeros(shp)
         sim2.ctx.upload_fields(ex=fzero, ey=fzero, ez=fzero, bx=fzero, by=fzero, bz=fzero)
@@ -428,6 +435,7 @@ def run_ours(args):
         "config": workload_config(args, world), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
         "roofline": roof, "fields": field_line,
         "phases_ms_per_step": {k: v[0] / args.steps for k, v in phases.items()},
+        "sorts_whole_run": sorts,
         "wall_ms_per_step": wall * 1e3 / args.steps,
         "setup_seconds": {"generate_host": t_gen, "upload": t_up},
     }

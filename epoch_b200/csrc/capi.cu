@@ -32,8 +32,11 @@ ScopedPhase::~ScopedPhase() {
 }
 
 static void free_species(SpeciesD& sp) {
-  for (int k = 0; k < 7; ++k) if (sp.a[k]) { cudaFree(sp.a[k]); sp.a[k] = nullptr; }
-  if (sp.key) cudaFree(sp.key);
+  for (int k = 0; k < 7; ++k) { if (sp.base[k]) cudaFree(sp.base[k]); sp.base[k] = sp.a[k] = nullptr; }
+  if (sp.key_base) cudaFree(sp.key_base);
+  sp.key_base = nullptr; sp.off = 0; sp.deferred = false;
+  if (sp.far) cudaFree(sp.far);
+  sp.far = nullptr; sp.far_cap = 0;
   if (sp.dest) cudaFree(sp.dest);
   if (sp.d_tile_start) cudaFree(sp.d_tile_start);
   if (sp.h_tile_start) cudaFreeHost(sp.h_tile_start);
@@ -279,6 +282,7 @@ int32_t eb200_shift_window(eb200_ctx* c, double x_grid_min_local, double x_min_l
                            double x_max) {
   CHECK_CTX(c); NEED_GRID(c);
   if (c->g.n[0] < 3) return fail(c, EB200_E_ARG, "moving window needs nx >= 3");
+  EB_TRY(settle_particles(c));
   return shift_window(c, x_grid_min_local, x_min_local, x_max_local, x_min, x_max);
 }
 
@@ -324,12 +328,14 @@ int32_t eb200_upload_particles(eb200_ctx* c, int32_t isp, int64_t n, const doubl
   CHECK_CTX(c); NEED_GRID(c);
   EB_TRY(check_species(c, isp, nvar));
   if (n < 0 || (n > 0 && !packed)) return fail(c, EB200_E_ARG, "bad particle buffer");
+  c->species[isp].deferred = false;      // the old particles are dropped
   return add_particles(c, isp, n, packed, nvar, true);
 }
 int32_t eb200_append_particles(eb200_ctx* c, int32_t isp, int64_t n, const double* packed, int32_t nvar) {
   CHECK_CTX(c); NEED_GRID(c);
   EB_TRY(check_species(c, isp, nvar));
   if (n < 0 || (n > 0 && !packed)) return fail(c, EB200_E_ARG, "bad particle buffer");
+  EB_TRY(settle_species(c, c->species[isp]));
   return add_particles(c, isp, n, packed, nvar, false);
 }
 int32_t eb200_particle_count(eb200_ctx* c, int32_t isp, int64_t* n) {
@@ -344,6 +350,7 @@ int32_t eb200_download_particles(eb200_ctx* c, int32_t isp, int64_t first, int64
   EB_TRY(check_species(c, isp, nvar));
   if (first < 0 || capacity < 0 || (capacity > 0 && !packed)) return fail(c, EB200_E_ARG, "bad particle buffer");
   long long got = 0;
+  EB_TRY(settle_species(c, c->species[isp]));
   EB_TRY(get_particles(c, isp, first, capacity, packed, nvar, &got));
   if (n_out) *n_out = got;
   return 0;
@@ -380,6 +387,7 @@ int32_t eb200_get_load(eb200_ctx* c, const double grid_min_global[3], int64_t* l
   CHECK_CTX(c); NEED_GRID(c);
   if (!grid_min_global) return fail(c, EB200_E_ARG, "get_load: null grid_min_global");
   long long* const load[3] = {(long long*)load_x, (long long*)load_y, (long long*)load_z};
+  EB_TRY(settle_particles(c));
   return get_load(c, grid_min_global, load);
 }
 
@@ -390,6 +398,7 @@ int32_t eb200_redistribute(eb200_ctx* c, const int32_t* old_cell_min, const int3
   if (!old_cell_min || !old_cell_max || !new_cell_min || !new_cell_max || !grid_min_global || !grid_min_local ||
       !min_local || !max_local)
     return fail(c, EB200_E_ARG, "redistribute: null argument");
+  EB_TRY(settle_particles(c));
   return redistribute(c, old_cell_min, old_cell_max, new_cell_min, new_cell_max, grid_min_global, grid_min_local,
                       min_local, max_local);
 }
@@ -405,6 +414,7 @@ int32_t eb200_calc_derived(eb200_ctx* c, int32_t kind, int32_t ispecies, int32_t
                         kind == EB200_DF_AVERAGE_MOMENTUM;
   if (ad > 3 || (need_dir && ad == 0) || (direction < 0 && kind != EB200_DF_EKFLUX))
     return fail(c, EB200_E_ARG, "calc_derived: direction must be 1..3 (negative only for ekflux; 0 only where optional)");
+  EB_TRY(settle_particles(c));
   return calc_derived(c, kind, ispecies, direction, out);
 }
 
@@ -458,13 +468,14 @@ int32_t eb200_update_eb_fields_final(eb200_ctx* c) {
 }
 int32_t eb200_push_particles(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); NEED_DT(c); return push_particles(c); }
 int32_t eb200_current_finish(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); return current_finish(c); }
-int32_t eb200_particle_bcs(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); NEED_DT(c); return particle_bcs(c); }
+int32_t eb200_particle_bcs(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); NEED_DT(c); EB_TRY(settle_particles(c)); return particle_bcs(c); }
 int32_t eb200_efield_bcs(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); return efield_bcs(c); }
 int32_t eb200_bfield_final_bcs(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); NEED_DT(c); return bfield_final_bcs(c); }
 
-int32_t eb200_energy(eb200_ctx* c, double* fe, double* per_species) { CHECK_CTX(c); NEED_GRID(c); return energy(c, fe, per_species); }
+int32_t eb200_energy(eb200_ctx* c, double* fe, double* per_species) { CHECK_CTX(c); NEED_GRID(c); EB_TRY(settle_particles(c)); return energy(c, fe, per_species); }
 int32_t eb200_charge_residual(eb200_ctx* c, double* max_res, double* max_rho) {
   CHECK_CTX(c); NEED_GRID(c); NEED_DT(c);
+  EB_TRY(settle_particles(c));
   return charge_residual(c, max_res, max_rho, false);
 }
 
@@ -472,7 +483,7 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
   CHECK_CTX(c);
   if (!key || !value) return fail(c, EB200_E_ARG, "null");
   const std::string k(key), v(value);
-  if (k == "capture_charge_reference") { NEED_GRID(c); NEED_DT(c); double a, b; return charge_residual(c, &a, &b, true); }
+  if (k == "capture_charge_reference") { NEED_GRID(c); NEED_DT(c); double a, b; EB_TRY(settle_particles(c)); return charge_residual(c, &a, &b, true); }
   if (k == "push_kernel") {
     if (v == "auto") c->push_kernel = 0; else if (v == "baseline") c->push_kernel = 1;
     else if (v == "tiled" || v == "split") c->push_kernel = 3;
@@ -480,6 +491,10 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
     return 0;
   }
   if (k == "fuse_keys") { c->fuse_keys = atoi(value) != 0; return 0; }
+  // deferred permute: head room (slots) between the two states of the particle arrays; takes effect when
+  // the arrays are next (re)allocated.  "auto" = need / 8, "0" = off (permute inside the sort)
+  if (k == "defer_window") { c->defer_window = v == "auto" ? -1 : atoll(value); return 0; }
+  if (k == "defer_gap") { c->defer_gap = v == "auto" ? -1 : atoll(value); return 0; }
   if (k == "deterministic_deposit") { c->deterministic = atoi(value) != 0; return 0; }
   if (k == "sort_every") { c->sort_every = atoi(value) < 1 ? 1 : atoi(value); return 0; }
   if (k == "timers") { c->timers_on = atoi(value) != 0; return 0; }
@@ -512,6 +527,12 @@ int32_t eb200_timer(eb200_ctx* c, const char* phase, int32_t reset, double* ms, 
     if (ms) *ms = 0;
     if (launches) *launches = c->launches;
     if (reset) c->launches = 0;
+    return 0;
+  }
+  if (k == "deferred_sorts" || k == "permuted_sorts") {   // sorts whose permute was left to the next push / done in the sort
+    if (ms) *ms = 0;
+    if (launches) *launches = k == "deferred_sorts" ? c->n_deferred : c->n_permuted;
+    if (reset) { c->n_deferred = 0; c->n_permuted = 0; }
     return 0;
   }
   if (k == "cell_mismatch") {   // particles whose sort key and push disagreed on the cell (must stay 0)

@@ -64,9 +64,21 @@ struct SpeciesD {
   int bc[6] = {1, 1, 1, 1, 1, 1};
   long long n = 0;          // live particles (valid after the last compaction)
   long long cap = 0;        // allocated slots per attribute
-  double* a[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // x,y,z,px,py,pz,w
-  uint32_t* key = nullptr;  // sort key per slot
-  uint32_t* dest = nullptr; // destination index per slot
+  double* a[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // x,y,z,px,py,pz,w: VIEW = base + off
+  uint32_t* key = nullptr;  // sort key per slot (view = key_base + off)
+  uint32_t* dest = nullptr; // destination index per slot; while `deferred`: src[i] = old slot of sorted index i
+  // Deferred permute (particles.cu): the allocations are `cap` = need + win + 2 gap slots long and the
+  // live slots start at `off` (low state: gap, high state: gap + win).  After a sort with `deferred`
+  // set the arrays still hold the PRE-sort order; the next push gathers through src and writes the
+  // sorted order into the other state, so the sort's permute passes never run.
+  double* base[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  uint32_t* key_base = nullptr;
+  long long off = 0, win = 0, gap = 0;
+  bool deferred = false;
+  double* far = nullptr;    // side buffer [7][far_cap] of the deferred permute: particles displaced beyond the window
+  long long far_cap = 0;
+  long long n_old = 0;      // slots of the pre-sort order spanned by src (deferred only)
+  long long disp_fwd = 0, disp_bwd = 0;   // max(dest - j), max(j - dest) over the live slots j
   uint32_t* cell_start = nullptr;   // per species: first particle of every key bucket (ncell_ext + 2)
   long long cell_cap = 0;
   uint32_t* d_tile_start = nullptr; // first particle of every tile (+1 entry), device and pinned host copy
@@ -162,6 +174,9 @@ struct eb200_ctx {
   int push_kernel = 0;          // 0 auto, 1 baseline (global atomics), 3 tiled (push + deposit kernels)
   int deterministic = 0;
   int fuse_keys = 1;            // option fuse_keys: push kernel emits the next sort keys (single rank)
+  long long defer_window = -1;  // option defer_window: head room in slots of the deferred permute (-1 auto, 0 off)
+  long long defer_gap = -1;     // option defer_gap: room for migration arrivals before / after the live slots (-1 auto)
+  long long n_deferred = 0, n_permuted = 0;   // sorts that deferred / physically permuted (timer "deferred_sorts")
   int sort_every = 1;
   bool timers_on = false;
   std::map<std::string, eb::PhaseTimer> timers;
@@ -241,7 +256,10 @@ int32_t particle_bcs(eb200_ctx* c);
 int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need, bool exact = false);
 int32_t add_particles(eb200_ctx* c, int isp, long long n, const double* packed, int nvar, bool replace);
 int32_t get_particles(eb200_ctx* c, int isp, long long first, long long cap, double* packed, int nvar, long long* n_out);
-int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_ready = false);
+int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_ready = false, bool may_defer = false);
+void set_view(SpeciesD& sp, long long off);             // a[k] = base[k] + off, key = key_base + off
+int32_t settle_species(eb200_ctx* c, SpeciesD& sp);    // finish a deferred permute (no-op otherwise)
+int32_t settle_particles(eb200_ctx* c);                // ... for every species
 // reduce.cu
 int32_t energy(eb200_ctx* c, double* fe, double* per_species);
 int32_t charge_residual(eb200_ctx* c, double* max_res, double* max_rho, bool capture);

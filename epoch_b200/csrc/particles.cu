@@ -10,36 +10,54 @@
 namespace eb {
 
 int32_t launch_push_baseline(eb200_ctx* c, const SpeciesD& sp, const PushP& p);   // push_baseline.cu
-int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled, const void* keysink);  // push_tiled.cu
+int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* handled, const void* keysink);  // push_tiled.cu
 size_t keysink_size();
 void keysink_fill(void* dst, const BcP3& bc, uint32_t* key, uint32_t* count, uint32_t nbucket);
 
 // ---------------------------------------------------------------------------------
 // storage
 // ---------------------------------------------------------------------------------
+void set_view(SpeciesD& sp, long long off) {
+  sp.off = off;
+  for (int k = 0; k < 7; ++k) sp.a[k] = sp.base[k] ? sp.base[k] + off : nullptr;
+  sp.key = sp.key_base ? sp.key_base + off : nullptr;
+}
+
 template <class T>
-static int32_t regrow(eb200_ctx* c, T*& ptr, long long old_n, long long new_cap) {
+static int32_t regrow(eb200_ctx* c, T*& base, const T* view, long long old_n, long long new_cap, long long new_off) {
   T* np = nullptr;
   EB_CUDA(c, cudaMalloc(&np, (size_t)new_cap * sizeof(T)));
-  if (ptr && old_n > 0) EB_CUDA(c, cudaMemcpyAsync(np, ptr, (size_t)old_n * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
-  if (ptr) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(ptr); }
-  ptr = np;
+  if (view && old_n > 0) EB_CUDA(c, cudaMemcpyAsync(np + new_off, view, (size_t)old_n * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
+  if (base) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(base); }
+  base = np;
   return 0;
 }
 
+// room for `need` live slots (+ the head room of the deferred permute: win slots between the low and
+// the high state, gap slots for migration arrivals at either end).  The live slots [0, sp.n) of
+// the current view are kept and end up in the low state.
 int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need, bool exact) {
-  if (need <= sp.cap) return 0;
-  long long ncap = exact ? std::max<long long>(need, 1024) : std::max<long long>(need + need / 32 + 1024, 4096);
-  const int nattr = c->ndims + 4;
+  if (sp.base[6] && need + sp.win + 2 * sp.gap <= sp.cap) return 0;
+  EB_TRY(settle_species(c, sp));
+  const bool tiled = c->ndims >= 2 && c->shape != SHAPE_BSPLINE3 && c->push_kernel != 1;
+  long long win = !tiled ? 0 : (c->defer_window >= 0 ? c->defer_window : std::max<long long>(need / 8, 1 << 16));
+  long long gap = win == 0 ? 0 : (c->defer_gap >= 0 ? c->defer_gap : (c->nproc > 1 ? std::max<long long>(need / 64, 1 << 14) : 0));
+  const long long body = exact ? std::max<long long>(need, 1024) : std::max<long long>(need + need / 32 + 1024, 4096);
+  const long long ncap = body + win + 2 * gap;
   // attributes live in a[0..ndims-1] (pos), a[3..5] (p), a[6] (w)
   for (int k = 0; k < 7; ++k) {
     if (k < 3 && k >= c->ndims) continue;
-    EB_TRY(regrow(c, sp.a[k], sp.n, ncap));
+    EB_TRY(regrow(c, sp.base[k], (const double*)sp.a[k], sp.n, ncap, gap));
   }
-  (void)nattr;
-  EB_TRY(regrow(c, sp.key, sp.n, ncap));
-  EB_TRY(regrow(c, sp.dest, 0, ncap));
-  sp.cap = ncap;
+  EB_TRY(regrow(c, sp.key_base, (const uint32_t*)sp.key, sp.n, ncap, gap));
+  {
+    uint32_t* nd = nullptr;
+    EB_CUDA(c, cudaMalloc(&nd, (size_t)ncap * sizeof(uint32_t)));
+    if (sp.dest) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(sp.dest); }
+    sp.dest = nd;
+  }
+  sp.cap = ncap; sp.win = win; sp.gap = gap;
+  set_view(sp, gap);
   return 0;
 }
 
@@ -205,6 +223,62 @@ __global__ void k_permute(const double* __restrict__ src, double* __restrict__ d
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dst[dest[i]] = src[i];
 }
+// k_dest of the deferred permute: stores the INVERSE map (src[sorted index] = slot) and the extreme
+// displacements of the live slots, disp[0] = max(dest - slot), disp[1] = max(slot - dest).  A slot whose
+// displacement exceeds `limit` (a particle wrapped around a periodic boundary of the slowest tile axis) is
+// copied to the species' side buffer instead -- src = n + index there -- and left out of the extremes;
+// disp[2] counts them (beyond far_cap they stay in place and the host falls back to a permute).
+struct Attr7 { const double* a[7]; };
+__global__ void k_src(const uint32_t* __restrict__ key, long long n, const uint32_t* __restrict__ start,
+                      uint32_t* cursor, uint32_t* src, uint32_t nbucket, unsigned long long* disp,
+                      Attr7 at, double* __restrict__ far, long long far_cap, long long limit) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool act = i < n;
+  const unsigned am = __ballot_sync(0xffffffffu, act);
+  if (!act) return;
+  uint32_t k = key[i];
+  const bool live = k != KEY_INVALID;
+  if (!live) k = nbucket - 1;
+  const unsigned peers = __match_any_sync(am, k);
+  const int lane = threadIdx.x & 31;
+  const int leader = __ffs(peers) - 1;
+  uint32_t base = 0;
+  if (lane == leader) base = atomicAdd(cursor + k, (uint32_t)__popc(peers));
+  base = __shfl_sync(peers, base, leader);
+  const uint32_t d = start[k] + base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+  long long df = 0, db = 0;
+  if (live) {
+    uint32_t s = (uint32_t)i;
+    df = (long long)d - i; db = -df;
+    if (df > limit || db > limit) {
+      const unsigned long long slot = atomicAdd(disp + 2, 1ULL);
+      if ((long long)slot < far_cap) {
+#pragma unroll
+        for (int a = 0; a < 7; ++a)
+          if (at.a[a]) far[(size_t)a * far_cap + slot] = at.a[a][i];
+        s = (uint32_t)(n + (long long)slot);
+      }
+      df = db = 0;
+    }
+    src[d] = s;
+  }
+  const unsigned f32 = (unsigned)(df < 0 ? 0 : df), b32 = (unsigned)(db < 0 ? 0 : db);   // <= limit < 2^31
+  const unsigned mf = __reduce_max_sync(am, f32), mb = __reduce_max_sync(am, b32);
+  // one address for the whole grid: look before the atomic (the running maxima settle within the first blocks)
+  if (lane == __ffs(am) - 1) {
+    volatile unsigned long long* vd = disp;
+    if ((unsigned long long)mf > vd[0]) atomicMax(disp, (unsigned long long)mf);
+    if ((unsigned long long)mb > vd[1]) atomicMax(disp + 1, (unsigned long long)mb);
+  }
+}
+// dst[i] = from[src[i]] for i in [i0, i1); src >= n_main points into the side buffer
+__global__ void k_gather_copy(const double* __restrict__ from, const double* __restrict__ far, long long n_main,
+                              double* __restrict__ dst, const uint32_t* __restrict__ src, long long i0, long long i1) {
+  const long long i = i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= i1) return;
+  const long long s = (long long)src[i];
+  dst[i] = s >= n_main ? far[s - n_main] : from[s];
+}
 __global__ void k_tile_start(const uint32_t* __restrict__ cell_start, uint32_t* ts, long long ntile1, int cpt) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t < ntile1) ts[t] = cell_start[t * cpt];
@@ -270,10 +344,70 @@ static int32_t ensure_cells(eb200_ctx* c, SpeciesD& sp) {
   return 0;
 }
 
+static int32_t ensure_spare(eb200_ctx* c, long long cap) {
+  if (c->attr_scratch_cap == cap) return 0;   // spare and attribute must be interchangeable: same capacity
+  if (c->attr_scratch) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(c->attr_scratch); }
+  c->attr_scratch = nullptr; c->attr_scratch_cap = 0;
+  EB_CUDA(c, cudaMalloc(&c->attr_scratch, (size_t)cap * sizeof(double)));
+  c->attr_scratch_cap = cap;
+  return 0;
+}
+
+// the deferred permute moves the live slots from the current state to the other one
+struct DeferPlan { bool fwd; long long off_new, room; };
+static DeferPlan defer_plan(const SpeciesD& sp) {
+  DeferPlan d;
+  d.fwd = sp.off >= sp.gap + sp.win;            // high -> low: sorted index i lands BELOW its old slots
+  d.off_new = d.fwd ? sp.gap : sp.gap + sp.win;
+  const long long W = d.fwd ? sp.off - d.off_new : d.off_new - sp.off;
+  // A kernel that writes the sorted indices [a, b) overwrites the old slots [a - W, b - W) (fwd; [a + W, b + W)
+  // otherwise).  With chunks taken in increasing (decreasing) order those slots have all been read by earlier
+  // kernels iff b - a <= W - max displacement.
+  d.room = W - (d.fwd ? sp.disp_fwd : sp.disp_bwd);
+  return d;
+}
+
+// finish a deferred permute without a push: gather-copy every attribute into the other state
+int32_t settle_species(eb200_ctx* c, SpeciesD& sp) {
+  if (!sp.deferred) return 0;
+  ScopedPhase ph(c, "sort");
+  const DeferPlan d = defer_plan(sp);
+  const long long chunk = d.room;
+  for (int k = 0; k < 7; ++k) {
+    if (k < 3 && k >= c->ndims) continue;
+    double* dst = sp.base[k] + d.off_new;
+    const long long nch = (sp.n + chunk - 1) / chunk;
+    for (long long ic = 0; ic < nch; ++ic) {
+      const long long q = d.fwd ? ic : nch - 1 - ic;
+      const long long i0 = q * chunk, i1 = std::min(sp.n, i0 + chunk);
+      k_gather_copy<<<(unsigned)((i1 - i0 + 255) / 256), 256, 0, c->stream>>>(sp.a[k], sp.far + (size_t)k * sp.far_cap, sp.n_old,
+                                                                               dst, sp.dest, i0, i1);
+      c->launches++;
+    }
+  }
+  set_view(sp, d.off_new);
+  if (sp.n > 0) {
+    k_fill_u32<<<(unsigned)((sp.n + 255) / 256), 256, 0, c->stream>>>(sp.key, sp.n, 0u);
+    c->launches++;
+  }
+  sp.deferred = false;
+  EB_CUDA(c, cudaGetLastError());
+  return 0;
+}
+int32_t settle_particles(eb200_ctx* c) {
+  for (SpeciesD& sp : c->species) if (sp.defined) EB_TRY(settle_species(c, sp));
+  return 0;
+}
+
 // sort slots [0, n_slots) of a species; dead slots (key == KEY_INVALID) go last
-// and are dropped.  `need_count`: read the live count back (it can only change
-// when particles were removed or appended).
-int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_ready) {
+// and are dropped.  keys_ready: the push kernel has already written keys and histogram.
+// may_defer: leave the arrays in their present order and let the next push gather through
+// sp.dest (= src) when the displacements fit the window (deferred permute).
+int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_ready, bool may_defer) {
+  if (sp.deferred) {
+    if (keys_ready) return fail(c, EB200_E_STATE, "sort_species: keys handed over for a deferred species");
+    EB_TRY(settle_species(c, sp));
+  }
   ScopedPhase ph(c, "sort");
   if (n_slots == 0) { sp.n = 0; sp.sorted = true; return 0; }
   if (n_slots >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "more than 2^32 particles per species per GPU");
@@ -305,31 +439,39 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
   }
   cub::DeviceScan::ExclusiveSum(c->cub_tmp, tmp, c->cell_count, sp.cell_start, (int)(nbucket + 1), c->stream);
   EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
-  k_dest<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket);
-  c->launches += keys_ready ? 3 : 4;
-  // scatter each attribute through one spare array; the spare rotates
-  if (c->attr_scratch_cap < sp.cap) {
-    if (c->attr_scratch) cudaFree(c->attr_scratch);
-    c->attr_scratch = nullptr; c->attr_scratch_cap = 0;
-    EB_CUDA(c, cudaMalloc(&c->attr_scratch, (size_t)sp.cap * sizeof(double)));
-    c->attr_scratch_cap = sp.cap;
-  }
-  for (int k = 0; k < 7; ++k) {
-    if (k < 3 && k >= c->ndims) continue;
-    if (c->attr_scratch_cap != sp.cap) {
-      // spare and attribute must be interchangeable: same capacity
-      if (c->attr_scratch) cudaFree(c->attr_scratch);
-      c->attr_scratch = nullptr; c->attr_scratch_cap = 0;
-      EB_CUDA(c, cudaMalloc(&c->attr_scratch, (size_t)sp.cap * sizeof(double)));
-      c->attr_scratch_cap = sp.cap;
+  const bool inverse = may_defer && sp.win > 0;
+  if (inverse) {
+    if (!sp.far) {
+      sp.far_cap = std::max<long long>(sp.cap / 256, 1 << 14);
+      EB_CUDA(c, cudaMalloc(&sp.far, (size_t)7 * sp.far_cap * sizeof(double)));
     }
-    k_permute<<<gp, B, 0, c->stream>>>(sp.a[k], c->attr_scratch, sp.dest, n_slots);
-    std::swap(sp.a[k], c->attr_scratch);
-    c->launches++;
+    if (n_slots + sp.far_cap >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "more than 2^32 particles per species per GPU");
+    Attr7 at;
+    for (int k = 0; k < 7; ++k) at.a[k] = (k < 3 && k >= c->ndims) ? nullptr : sp.a[k];
+    // the window is shared between the displacements (<= limit) and the particles of one launch
+    const long long W = sp.off >= sp.gap + sp.win ? sp.off - sp.gap : sp.gap + sp.win - sp.off;
+    const long long limit = std::min<long long>(W / 2, 0x7fffffffLL);
+    EB_CUDA(c, cudaMemsetAsync(c->d_counters + 12, 0, 3 * sizeof(unsigned long long), c->stream));
+    k_src<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket, c->d_counters + 12,
+                                   at, sp.far, sp.far_cap, limit);
+    EB_CUDA(c, cudaMemcpyAsync(c->h_counters + 12, c->d_counters + 12, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+  } else {
+    k_dest<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket);
+  }
+  c->launches += keys_ready ? 3 : 4;
+  if (!inverse) {
+    // scatter each attribute through one spare array; the spare rotates.  The result is the low state.
+    EB_TRY(ensure_spare(c, sp.cap));
+    for (int k = 0; k < 7; ++k) {
+      if (k < 3 && k >= c->ndims) continue;
+      k_permute<<<gp, B, 0, c->stream>>>(sp.a[k], c->attr_scratch + sp.gap, sp.dest, n_slots);
+      std::swap(sp.base[k], c->attr_scratch);
+      c->launches++;
+    }
   }
   // first particle of every tile, for the host's slab partition of the split push/deposit kernels
+  const long long nt1 = c->g.ncell_ext / c->g.cpt + 1;
   {
-    const long long nt1 = c->g.ncell_ext / c->g.cpt + 1;
     if (sp.tile_cap < nt1) {
       if (sp.d_tile_start) cudaFree(sp.d_tile_start);
       if (sp.h_tile_start) cudaFreeHost(sp.h_tile_start);
@@ -346,10 +488,49 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
   EB_CUDA(c, cudaMemcpyAsync(c->h_counters, sp.cell_start + (nbucket - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
   EB_CUDA(c, cudaStreamSynchronize(c->stream));
   sp.n = (long long)(*(uint32_t*)c->h_counters);
-  // keys are not permuted: if any slot was dropped, stale KEY_INVALID marks must not survive
-  if (sp.n != n_slots) {
-    k_fill_u32<<<(unsigned)((n_slots + B - 1) / B), B, 0, c->stream>>>(sp.key, n_slots, 0u);
-    c->launches++;
+  bool view_changed = false;
+  if (inverse) {
+    sp.disp_fwd = (long long)c->h_counters[12]; sp.disp_bwd = (long long)c->h_counters[13];
+    const DeferPlan d = defer_plan(sp);
+    long long biggest = 1;
+    for (long long t = 0; t + 1 < nt1; ++t) biggest = std::max<long long>(biggest, (long long)(sp.h_tile_start[t + 1] - sp.h_tile_start[t]));
+    const long long n_far = (long long)c->h_counters[14];
+    if (d.room >= biggest && n_far <= sp.far_cap && d.off_new + sp.n + sp.gap <= sp.cap) {
+      sp.deferred = true; sp.n_old = n_slots;
+      c->n_deferred++;
+    } else if (sp.n > 0) {
+      // displacements beyond the window (first sort of an unordered load, a re-sliced domain, ...):
+      // permute now, gathering through the spare into the low state
+      EB_TRY(ensure_spare(c, sp.cap));
+      const unsigned gl = (unsigned)((sp.n + B - 1) / B);
+      for (int k = 0; k < 7; ++k) {
+        if (k < 3 && k >= c->ndims) continue;
+        k_gather_copy<<<gl, B, 0, c->stream>>>(sp.a[k], sp.far + (size_t)k * sp.far_cap, n_slots, c->attr_scratch + sp.gap,
+                                               sp.dest, 0, sp.n);
+        std::swap(sp.base[k], c->attr_scratch);
+        c->launches++;
+      }
+      view_changed = true;
+      c->n_permuted++;
+    }
+  } else {
+    view_changed = true;
+    c->n_permuted++;
+  }
+  if (view_changed) {
+    const bool moved = sp.off != sp.gap;
+    set_view(sp, sp.gap);
+    // keys are not permuted: stale KEY_INVALID marks must not survive in the slots now live
+    if ((sp.n != n_slots || moved) && sp.n > 0) {
+      k_fill_u32<<<(unsigned)((sp.n + B - 1) / B), B, 0, c->stream>>>(sp.key, sp.n, 0u);
+      c->launches++;
+    }
+    // a spare of tens of GB is given back once the deferred permute carries the steady state
+    if (sp.win > 0 && c->attr_scratch && (size_t)c->attr_scratch_cap * sizeof(double) > ((size_t)1 << 30)) {
+      EB_CUDA(c, cudaStreamSynchronize(c->stream));
+      cudaFree(c->attr_scratch);
+      c->attr_scratch = nullptr; c->attr_scratch_cap = 0;
+    }
   }
   sp.sorted = true;
   EB_CUDA(c, cudaGetLastError());
@@ -477,16 +658,23 @@ static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool&
       sp.n = n_slots;                       // regrow copies [0, sp.n)
       EB_TRY(species_reserve(c, sp, n_slots + arrivals));
       sp.n = keep_n;
+      // Low state: the next deferred permute runs towards higher slots, where only particles stored ABOVE
+      // their sorted index are a hazard -- so the arrivals go in FRONT of the live slots (the view moves
+      // down; nothing index-based is alive at this point).  High state / no window: appended.
+      const bool prepend = sp.win > 0 && sp.off < sp.gap + sp.win && arrivals <= sp.off;
+      long long at = n_slots;
+      if (prepend) { set_view(sp, sp.off - arrivals); at = 0; }
       if (from_hi > 0) {
-        k_unpack_aos<<<(unsigned)((from_hi + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[0], c->ndims, from_hi, n_slots,
+        k_unpack_aos<<<(unsigned)((from_hi + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[0], c->ndims, from_hi, at,
             sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
-        n_slots += from_hi; c->launches++;
+        at += from_hi; c->launches++;
       }
       if (from_lo > 0) {
-        k_unpack_aos<<<(unsigned)((from_lo + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[1], c->ndims, from_lo, n_slots,
+        k_unpack_aos<<<(unsigned)((from_lo + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[1], c->ndims, from_lo, at,
             sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
-        n_slots += from_lo; c->launches++;
+        c->launches++;
       }
+      n_slots += arrivals;
     }
   }
   EB_CUDA(c, cudaGetLastError());
@@ -605,12 +793,13 @@ int32_t push_particles(eb200_ctx* c) {
     ScopedPhase ph(c, "push");
     EB_CUDA(c, cudaMemsetAsync(c->f.f[JX], 0, (size_t)3 * c->g.total * sizeof(double), c->stream));
   }
-  std::vector<char> done(c->species.size(), 0);
+  std::vector<char> done(c->species.size(), 0), tiled(c->species.size(), 0);
   for (size_t is = 0; is < c->species.size(); ++is) {
     SpeciesD& sp = c->species[is];
-    if (!sp.defined || sp.immobile || sp.species_type == 1) continue;
+    if (!sp.defined) continue;
+    if (sp.immobile || sp.species_type == 1) { EB_TRY(settle_species(c, sp)); continue; }
     if (!sp.sorted) EB_TRY(sort_species(c, sp, sp.n));
-    if (sp.n == 0) continue;
+    if (sp.n == 0) { sp.deferred = false; continue; }
     PushP p = make_push_params(c, sp, sp.n);
     bool handled = false, fused_keys = false;
     {
@@ -630,12 +819,16 @@ int32_t push_particles(eb200_ctx* c) {
           keysink_fill(ksbuf.data(), bc, sp.key, c->cell_count, nbucket);
           ks = ksbuf.data();
         }
-        EB_TRY(launch_push_split(c, sp, p, &handled, ks));
+        EB_TRY(launch_push_split(c, sp, p, &handled, ks));     // consumes a deferred permute
         fused_keys = handled && ks != nullptr;
+        tiled[is] = handled;
       }
-      if (!handled) EB_TRY(launch_push_baseline(c, sp, p));
+      if (!handled) {
+        EB_TRY(settle_species(c, sp));
+        EB_TRY(launch_push_baseline(c, sp, p));
+      }
     }
-    if (fused_keys) { EB_TRY(sort_species(c, sp, sp.n, true)); done[is] = 1; }
+    if (fused_keys) { EB_TRY(sort_species(c, sp, sp.n, true, true)); done[is] = 1; }
   }
   // current_bcs(species) is a no-op without mixed per-species BCs (boundary.F90:1130-1136)
   // particle_bcs for the species the push did not already finish
@@ -648,7 +841,7 @@ int32_t push_particles(eb200_ctx* c) {
       ScopedPhase ph(c, "bcs");
       EB_TRY(species_bcs(c, sp, n_slots, changed));
     }
-    EB_TRY(sort_species(c, sp, n_slots));
+    EB_TRY(sort_species(c, sp, n_slots, false, tiled[is] != 0));
   }
   return 0;
 }

@@ -255,11 +255,22 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double
 
 namespace {
 
-struct PArr { double* x[3]; double* m[3]; const double* w; };
+struct PArr { double* x[3]; double* m[3]; double* w; };
 // when on: the push also applies the particle BCs of the (undecomposed) axes to the values it
 // stores and produces the next sort key + key histogram, saving the sort's own pass
 struct KeySink { int on; BcP3 bc; uint32_t* key; uint32_t* count; uint32_t nbucket; };
 
+// deferred permute: slot s of the pre-sort order, or entry s - n_main of the side buffer
+template <int ND>
+__device__ __forceinline__ void load_particle_g(const PArr& a, const PArr& side, uint32_t s, uint32_t n_main, double* in) {
+  const bool far = s >= n_main;
+  const long long ip = far ? (long long)(s - n_main) : (long long)s;
+#pragma unroll
+  for (int d = 0; d < ND; ++d) in[d] = (far ? side.x[d] : a.x[d])[ip];
+#pragma unroll
+  for (int d = 0; d < 3; ++d) in[3 + d] = (far ? side.m[d] : a.m[d])[ip];
+  in[6] = (far ? side.w : a.w)[ip];
+}
 template <int ND>
 __device__ __forceinline__ void load_particle(const PArr& a, long long ip, double* in) {
 #pragma unroll
@@ -271,8 +282,8 @@ __device__ __forceinline__ void load_particle(const PArr& a, long long ip, doubl
 
 // phase 1 for one particle: particles.F90:219-452 (gather stage, Boris, drift, store,
 // extra half drift); leaves the deposit inputs in the record arrays
-template <int ND, int SHAPE>
-__device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos[3], mom[3], weight */, const PArr& a,
+template <int ND, int SHAPE, bool GATHER>
+__device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos[3], mom[3], weight */, const PArr& a /* output */,
                                          long long ip, const int* c0,
                                          const double* __restrict__ sF, unsigned long long* counters,
                                          double* rec /* NREC doubles */, int& rec_pack, const GridP* g = nullptr,
@@ -353,7 +364,10 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
     ks->key[ip] = ch < 0 ? KEY_INVALID : k;
     const unsigned peers = __match_any_sync(__activemask(), k);
     if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(ks->count + k, (uint32_t)__popc(peers));
+  } else if (GATHER) {
+    ks->key[ip] = 0u;        // fresh slots: no stale KEY_INVALID mark may survive
   }
+  if (GATHER) a.w[ip] = part_weight;
 #pragma unroll
   for (int d = 0; d < ND; ++d) a.x[d][ip] = posn[d];
   a.m[0][ip] = momn[0]; a.m[1][ip] = momn[1]; a.m[2][ip] = momn[2];
@@ -550,8 +564,11 @@ constexpr int MCAPB = 2048;      // overflow work items per sub-tile in the depo
 #endif
 constexpr int RING = EB_RING;    // record slots per thread of the deposit kernel's cp.async ring
 
-template <int ND, int SHAPE>
-__global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F, PushP p, PArr a,
+// GATHER (deferred permute, particles.cu): the particle of sorted index q is read from slot src[q] of the
+// arrays `a` (the pre-sort order) and stored to slot q of `o` (the other state of the same allocations)
+template <int ND, int SHAPE, bool GATHER>
+__global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F, PushP p, PArr a, PArr o, PArr side,
+                                                              const uint32_t* __restrict__ src, uint32_t n_main,
                                                               const uint32_t* __restrict__ cell_start, long long tile0,
                                                               double* __restrict__ scratch, unsigned long long* counters,
                                                               KeySink ks) {
@@ -604,19 +621,27 @@ __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F
   double2* stage = reinterpret_cast<double2*>(smem + 6 * T::FN) + warp * 128;
   double nxt[7];
   uint32_t q0 = pb + warp * 32;
-  if (q0 + lane < pe) load_particle<ND>(a, (long long)(q0 + lane), nxt);
+  uint32_t s2 = 0;           // GATHER: slot of the particle after next
+  if (GATHER) {
+    if (q0 + lane < pe) load_particle_g<ND>(a, side, __ldg(src + q0 + lane), n_main, nxt);
+    if (q0 + lane + NTA < pe) s2 = __ldg(src + q0 + lane + NTA);
+  } else if (q0 + lane < pe) load_particle<ND>(a, (long long)(q0 + lane), nxt);
   for (; q0 < pe; q0 += NTA) {
     const uint32_t q = q0 + lane;
     const bool act = q < pe;
     double in[7];
 #pragma unroll
     for (int k = 0; k < 7; ++k) in[k] = nxt[k];
-    if (q + NTA < pe) load_particle<ND>(a, (long long)(q + NTA), nxt);
+    if (q + NTA < pe) {
+      if (GATHER) load_particle_g<ND>(a, side, s2, n_main, nxt);
+      else load_particle<ND>(a, (long long)(q + NTA), nxt);
+    }
+    if (GATHER && q + 2 * NTA < pe) s2 = __ldg(src + q + 2 * NTA);
     if (act) {
       double rec[8];
       int pack;
       rec[6] = 0.0;
-      push_one<ND, SHAPE>(p, in, a, (long long)q, c0, sF, counters, rec, pack, &g, &ks);
+      push_one<ND, SHAPE, GATHER>(p, in, o, (long long)q, c0, sF, counters, rec, pack, &g, &ks);
       rec[7] = __longlong_as_double((long long)pack);
 #pragma unroll
       for (int k = 0; k < 4; ++k) stage[lane * 4 + (k ^ ((lane >> 1) & 3))] = make_double2(rec[2 * k], rec[2 * k + 1]);
@@ -796,19 +821,35 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
 
 size_t keysink_size() { return sizeof(KeySink); }
 void keysink_fill(void* dst, const BcP3& bc, uint32_t* key, uint32_t* count, uint32_t nbucket) {
-  KeySink ks;
+  KeySink ks{};
   ks.on = 1; ks.bc = bc; ks.key = key; ks.count = count; ks.nbucket = nbucket;
   *(KeySink*)dst = ks;
 }
 
-int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool* handled, const void* keysink) {
+int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* handled, const void* keysink) {
   *handled = false;
   KeySink ks;
-  if (keysink) ks = *(const KeySink*)keysink; else ks.on = 0;
+  if (keysink) ks = *(const KeySink*)keysink; else { ks.on = 0; ks.count = nullptr; ks.nbucket = 0; }
   if (c->ndims < 2 || c->shape == SHAPE_BSPLINE3 || !sp.sorted || !sp.h_tile_start) return 0;
-  PArr a;
-  for (int d = 0; d < 3; ++d) { a.x[d] = sp.a[d]; a.m[d] = sp.a[3 + d]; }
-  a.w = sp.a[6];
+  // deferred permute: read the pre-sort order through src, write the sorted order into the other state
+  const bool gather = sp.deferred;
+  bool fwd = true;
+  long long off_new = sp.off, room = 1LL << 62;
+  if (gather) {
+    fwd = sp.off >= sp.gap + sp.win;
+    off_new = fwd ? sp.gap : sp.gap + sp.win;
+    const long long W = fwd ? sp.off - off_new : off_new - sp.off;
+    room = W - (fwd ? sp.disp_fwd : sp.disp_bwd);       // particles per launch (see defer_plan, particles.cu)
+  }
+  PArr a, o, side;
+  for (int d = 0; d < 3; ++d) {
+    a.x[d] = sp.a[d]; a.m[d] = sp.a[3 + d];
+    o.x[d] = sp.base[d] ? sp.base[d] + off_new : nullptr; o.m[d] = sp.base[3 + d] + off_new;
+    side.x[d] = sp.far ? sp.far + (size_t)d * sp.far_cap : nullptr; side.m[d] = sp.far ? sp.far + (size_t)(3 + d) * sp.far_cap : nullptr;
+  }
+  a.w = sp.a[6]; o.w = sp.base[6] + off_new; side.w = sp.far ? sp.far + (size_t)6 * sp.far_cap : nullptr;
+  const uint32_t n_main = gather ? (uint32_t)sp.n_old : 0u;
+  ks.key = sp.key_base + off_new;
   const long long ntiles = (long long)c->g.ntile[0] * c->g.ntile[1] * c->g.ntile[2];
   const uint32_t* ts = sp.h_tile_start;      // ntiles + 1 entries, valid since the sort's synchronise
   // scratch: 64 B per particle of a slab of tiles
@@ -817,21 +858,29 @@ int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool
   for (long long t = 0; t < ntiles; ++t) biggest = biggest > (long long)(ts[t + 1] - ts[t]) ? biggest : (long long)(ts[t + 1] - ts[t]);
   if (want < biggest) want = biggest;       // a slab is at least one tile
   if (want < 1) return 0;
+  if (gather && room < biggest) return fail(c, EB200_E_STATE, "deferred permute: window smaller than a tile");
   if (c->rec_scratch_cap < want) {
     if (c->rec_scratch) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(c->rec_scratch); }
     c->rec_scratch = nullptr; c->rec_scratch_cap = 0;
     EB_CUDA(c, cudaMalloc(&c->rec_scratch, (size_t)want * 8 * sizeof(double)));
     c->rec_scratch_cap = want;
   }
-  const long long cap = c->rec_scratch_cap;
+  const long long cap = c->rec_scratch_cap < room ? c->rec_scratch_cap : room;
+  // slabs of consecutive tiles, run upwards (or downwards: deferred permute towards higher slots)
+  std::vector<std::pair<long long, long long>> slabs;
   for (long long t0 = 0; t0 < ntiles;) {
     if (ts[t0 + 1] == ts[t0]) { ++t0; continue; }               // skip leading empty tiles
     long long t1 = t0 + 1;
     while (t1 < ntiles && (long long)(ts[t1 + 1] - ts[t0]) <= cap) ++t1;
+    slabs.emplace_back(t0, t1);
+    t0 = t1;
+  }
+  for (size_t is = 0; is < slabs.size(); ++is) {
+    const long long t0 = slabs[fwd ? is : slabs.size() - 1 - is].first, t1 = slabs[fwd ? is : slabs.size() - 1 - is].second;
     const unsigned nb = (unsigned)(t1 - t0);
 #define L(ND, SH)                                                                                          \
     if (c->ndims == ND && c->shape == SH) {                                                                \
-      auto ka = k_push_split<ND, SH>;                                                                      \
+      auto ka = gather ? k_push_split<ND, SH, true> : k_push_split<ND, SH, false>;                         \
       auto kb = k_deposit_split<ND, SH>;                                                                   \
       const size_t sa = sizeof(double) * (6 * TL<ND, SH>::FN + (NTA / 32) * 256);                                               \
       const size_t sb = sizeof(double) * 3 * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4)   /* >= sub-tile need */ \
@@ -839,16 +888,16 @@ int32_t launch_push_split(eb200_ctx* c, const SpeciesD& sp, const PushP& p, bool
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
       { ScopedPhase pa(c, "push_A");                                                                       \
-        ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks); } \
+        ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks); } \
       if (!p.zero_current) { ScopedPhase pb(c, "push_B");                                                  \
         kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch); }    \
     }
     L(2, 0) L(2, 1) L(3, 0) L(3, 1)
 #undef L
     c->launches += p.zero_current ? 1 : 2;
-    t0 = t1;
   }
   EB_CUDA(c, cudaGetLastError());
+  if (gather) { set_view(sp, off_new); sp.deferred = false; }
   *handled = true;
   return 0;
 }

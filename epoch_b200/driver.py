@@ -68,7 +68,8 @@ class Simulation:
     def __init__(self, ndims, n_global, mins, maxs, shape="triangle", bc_field=None, species=(),
                  lasers=(), dt_multiplier=0.95, field_order=2, t_end=None, abi=None, device=0,
                  rank=0, nproc=1, nprocdir=(1, 1, 1), nccl_id=None, dt=None, maxwell_solver="yee",
-                 stencil=None, cpml_thickness=6, cpml_kappa_max=20.0, cpml_a_max=0.15, cpml_sigma_max=0.7):
+                 stencil=None, cpml_thickness=6, cpml_kappa_max=20.0, cpml_a_max=0.15, cpml_sigma_max=0.7,
+                 options=None):
         self.ndims = nd = ndims
         self.shape = SHAPES[shape] if isinstance(shape, str) else shape
         self.n_global = tuple(n_global[:nd])
@@ -116,6 +117,8 @@ class Simulation:
 
         self.ctx = PicContext(nd, self.shape, abi=abi, device=device, rank=rank, nproc=nproc,
                               nprocdir=self.nprocdir, coords=self.coords, nccl_id=nccl_id)
+        for k, v in (options or {}).items():      # library tuning options (eb200_set_option), before any allocation
+            self.ctx.set_option(k, v)
         self.ctx.set_grid(self.n_local, self.d, self.grid_min_local, self.min_local, self.max_local,
                           self.mins, self.maxs, n_global=self.n_global, n_global_min=self.cell_min,
                           cpml_thickness=self.cpml_thickness)

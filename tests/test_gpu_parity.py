@@ -411,3 +411,34 @@ def test_redistribute_single_rank_identity(product_abi, oracle_abi):
         s.step_once()
     compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
     compare_particles(sims[0], sims[1], tol=1e-10)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndims,shape,pbc,n,window,expect", [
+    (3, "triangle", "periodic", [16, 8, 48], 8000, True), (3, "tophat", "periodic", [16, 8, 48], 9000, True),
+    (2, "triangle", "periodic", [32, 64], 6000, True), (2, "tophat", "reflect", [32, 64], 7000, True),
+    (3, "triangle", "open", [16, 8, 48], 8000, True), (3, "triangle", "periodic", [16, 8, 48], 600, False),
+    (3, "triangle", "periodic", [16, 8, 48], "auto", True), (3, "triangle", "periodic", [16, 8, 48], 0, False)])
+def test_deferred_permute(product_abi, oracle_abi, ndims, shape, pbc, n, window, expect):
+    """The sort leaves its permute to the next push (gather through src, write into the other state of the
+    arrays).  A window far smaller than the species forces many launches per step in both directions and,
+    where the displacements do not fit (window 600 < one tile), the fall-back permute; downloads,
+    energy sums and diagnostics in mid-run settle a deferred permute.  Everything must equal the oracle
+    (as does window = 0, the plain sort)."""
+    bcs = [pbc] * (2 * ndims)
+    fbc = ["periodic" if pbc == "periodic" else "clamp"] * (2 * ndims)
+    opts = {"defer_window": window, "deposit_scratch": 2048}
+    sims = [make_plasma(a, ndims, shape, n, seed=5, ppc=6, u_th=0.4, e_amp=1e9, b_amp=3.0, bcs=bcs, bc_field=fbc,
+                        options=opts) for a in (product_abi, oracle_abi)]
+    for it in range(9):
+        for s in sims:
+            s.step_once()
+        if it == 3:
+            e = [s.ctx.energy() for s in sims]
+            assert np.allclose(e[0][1], e[1][1], rtol=1e-11, atol=0)
+        if it in (4, 8):
+            compare_particles(sims[0], sims[1], tol=1e-10)
+            compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
+    deferred, permuted = sims[0].ctx.timer("deferred_sorts")[1], sims[0].ctx.timer("permuted_sorts")[1]
+    assert sims[0].ctx.timer("cell_mismatch")[1] == 0
+    assert (deferred > 0) == expect, (deferred, permuted)
