@@ -266,9 +266,8 @@ def run_ours(args):
     t_setup = time.perf_counter()
     sim = make_sim(abi, cells_global, rank, world, nccl_id, device=local)
     # deferred permute: head room between the two states of the particle arrays (7 % of the species:
-    # one layer of tiles of displacement + one slab of tiles per launch) and room for migration arrivals
+    # a quarter for the displacements -- one layer of tiles -- and three quarters for the particles of a launch)
     sim.ctx.set_option("defer_window", max(n_part // 14, min(n_part // 2, 1 << 24)))
-    sim.ctx.set_option("defer_gap", n_part // 256 if world > 1 else 0)
     for kv in args.opt:                       # tuning experiments: --opt push_kernel=tiled
         k, v = kv.split("=", 1)
         sim.ctx.set_option(k, v)
@@ -388,7 +387,6 @@ def run_ours(args):
         t0 = time.perf_counter()
         sim2 = make_sim(abi, cells_e2e, rank, world, nccl_id2, device=local)
         sim2.ctx.set_option("defer_window", max(n_e2e // 14, min(n_e2e // 2, 1 << 24)))
-        sim2.ctx.set_option("defer_gap", n_e2e // 256 if world > 1 else 0)
         for kv in args.opt:
             k, v = kv.split("=", 1)
             sim2.ctx.set_option(k, v)

@@ -494,7 +494,6 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
   // deferred permute: head room (slots) between the two states of the particle arrays; takes effect when
   // the arrays are next (re)allocated.  "auto" = need / 8, "0" = off (permute inside the sort)
   if (k == "defer_window") { c->defer_window = v == "auto" ? -1 : atoll(value); return 0; }
-  if (k == "defer_gap") { c->defer_gap = v == "auto" ? -1 : atoll(value); return 0; }
   if (k == "deterministic_deposit") { c->deterministic = atoi(value) != 0; return 0; }
   if (k == "sort_every") { c->sort_every = atoi(value) < 1 ? 1 : atoi(value); return 0; }
   if (k == "timers") { c->timers_on = atoi(value) != 0; return 0; }

@@ -78,7 +78,7 @@ struct SpeciesD {
   double* far = nullptr;    // side buffer [7][far_cap] of the deferred permute: particles displaced beyond the window
   long long far_cap = 0;
   long long n_old = 0;      // slots of the pre-sort order spanned by src (deferred only)
-  long long disp_fwd = 0, disp_bwd = 0;   // max(dest - j), max(j - dest) over the live slots j
+  long long disp_fwd = 0, disp_bwd = 0;   // bounds of dest - j and j - dest over the slots j that src points at
   uint32_t* cell_start = nullptr;   // per species: first particle of every key bucket (ncell_ext + 2)
   long long cell_cap = 0;
   uint32_t* d_tile_start = nullptr; // first particle of every tile (+1 entry), device and pinned host copy
@@ -175,7 +175,6 @@ struct eb200_ctx {
   int deterministic = 0;
   int fuse_keys = 1;            // option fuse_keys: push kernel emits the next sort keys (single rank)
   long long defer_window = -1;  // option defer_window: head room in slots of the deferred permute (-1 auto, 0 off)
-  long long defer_gap = -1;     // option defer_gap: room for migration arrivals before / after the live slots (-1 auto)
   long long n_deferred = 0, n_permuted = 0;   // sorts that deferred / physically permuted (timer "deferred_sorts")
   int sort_every = 1;
   bool timers_on = false;

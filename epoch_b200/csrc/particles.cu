@@ -41,7 +41,7 @@ int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need, bool exact) 
   EB_TRY(settle_species(c, sp));
   const bool tiled = c->ndims >= 2 && c->shape != SHAPE_BSPLINE3 && c->push_kernel != 1;
   long long win = !tiled ? 0 : (c->defer_window >= 0 ? c->defer_window : std::max<long long>(need / 8, 1 << 16));
-  long long gap = win == 0 ? 0 : (c->defer_gap >= 0 ? c->defer_gap : (c->nproc > 1 ? std::max<long long>(need / 64, 1 << 14) : 0));
+  const long long gap = 0;      // (slots kept free below the low state: none needed, arrivals are appended)
   const long long body = exact ? std::max<long long>(need, 1024) : std::max<long long>(need + need / 32 + 1024, 4096);
   const long long ncap = body + win + 2 * gap;
   // attributes live in a[0..ndims-1] (pos), a[3..5] (p), a[6] (w)
@@ -223,14 +223,13 @@ __global__ void k_permute(const double* __restrict__ src, double* __restrict__ d
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) dst[dest[i]] = src[i];
 }
-// k_dest of the deferred permute: stores the INVERSE map (src[sorted index] = slot) and the extreme
-// displacements of the live slots, disp[0] = max(dest - slot), disp[1] = max(slot - dest).  A slot whose
-// displacement exceeds `limit` (a particle wrapped around a periodic boundary of the slowest tile axis) is
-// copied to the species' side buffer instead -- src = n + index there -- and left out of the extremes;
-// disp[2] counts them (beyond far_cap they stay in place and the host falls back to a permute).
+// k_dest of the deferred permute: stores the INVERSE map (src[sorted index] = slot).  A slot displaced by
+// more than `limit` (a particle wrapped around a periodic boundary of the slowest tile axis, a migration
+// arrival, ...) is copied to the species' side buffer instead -- src = n + index there; far_count counts
+// them (beyond far_cap they stay in place and the host falls back to a permute).
 struct Attr7 { const double* a[7]; };
 __global__ void k_src(const uint32_t* __restrict__ key, long long n, const uint32_t* __restrict__ start,
-                      uint32_t* cursor, uint32_t* src, uint32_t nbucket, unsigned long long* disp,
+                      uint32_t* cursor, uint32_t* src, uint32_t nbucket, unsigned long long* far_count,
                       Attr7 at, double* __restrict__ far, long long far_cap, long long limit) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const bool act = i < n;
@@ -246,29 +245,19 @@ __global__ void k_src(const uint32_t* __restrict__ key, long long n, const uint3
   if (lane == leader) base = atomicAdd(cursor + k, (uint32_t)__popc(peers));
   base = __shfl_sync(peers, base, leader);
   const uint32_t d = start[k] + base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
-  long long df = 0, db = 0;
   if (live) {
     uint32_t s = (uint32_t)i;
-    df = (long long)d - i; db = -df;
-    if (df > limit || db > limit) {
-      const unsigned long long slot = atomicAdd(disp + 2, 1ULL);
+    const long long df = (long long)d - i;
+    if (df > limit || -df > limit) {
+      const unsigned long long slot = atomicAdd(far_count, 1ULL);
       if ((long long)slot < far_cap) {
 #pragma unroll
         for (int a = 0; a < 7; ++a)
           if (at.a[a]) far[(size_t)a * far_cap + slot] = at.a[a][i];
         s = (uint32_t)(n + (long long)slot);
       }
-      df = db = 0;
     }
     src[d] = s;
-  }
-  const unsigned f32 = (unsigned)(df < 0 ? 0 : df), b32 = (unsigned)(db < 0 ? 0 : db);   // <= limit < 2^31
-  const unsigned mf = __reduce_max_sync(am, f32), mb = __reduce_max_sync(am, b32);
-  // one address for the whole grid: look before the atomic (the running maxima settle within the first blocks)
-  if (lane == __ffs(am) - 1) {
-    volatile unsigned long long* vd = disp;
-    if ((unsigned long long)mf > vd[0]) atomicMax(disp, (unsigned long long)mf);
-    if ((unsigned long long)mb > vd[1]) atomicMax(disp + 1, (unsigned long long)mb);
   }
 }
 // dst[i] = from[src[i]] for i in [i0, i1); src >= n_main points into the side buffer
@@ -448,13 +437,14 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
     if (n_slots + sp.far_cap >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "more than 2^32 particles per species per GPU");
     Attr7 at;
     for (int k = 0; k < 7; ++k) at.a[k] = (k < 3 && k >= c->ndims) ? nullptr : sp.a[k];
-    // the window is shared between the displacements (<= limit) and the particles of one launch
     const long long W = sp.off >= sp.gap + sp.win ? sp.off - sp.gap : sp.gap + sp.win - sp.off;
-    const long long limit = std::min<long long>(W / 2, 0x7fffffffLL);
-    EB_CUDA(c, cudaMemsetAsync(c->d_counters + 12, 0, 3 * sizeof(unsigned long long), c->stream));
+    // the window is shared between the displacements (<= limit) and the particles of one launch
+    const long long limit = W / 4;
+    sp.disp_fwd = sp.disp_bwd = limit;
+    EB_CUDA(c, cudaMemsetAsync(c->d_counters + 12, 0, sizeof(unsigned long long), c->stream));
     k_src<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket, c->d_counters + 12,
                                    at, sp.far, sp.far_cap, limit);
-    EB_CUDA(c, cudaMemcpyAsync(c->h_counters + 12, c->d_counters + 12, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    EB_CUDA(c, cudaMemcpyAsync(c->h_counters + 12, c->d_counters + 12, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
   } else {
     k_dest<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket);
   }
@@ -490,11 +480,10 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
   sp.n = (long long)(*(uint32_t*)c->h_counters);
   bool view_changed = false;
   if (inverse) {
-    sp.disp_fwd = (long long)c->h_counters[12]; sp.disp_bwd = (long long)c->h_counters[13];
     const DeferPlan d = defer_plan(sp);
     long long biggest = 1;
     for (long long t = 0; t + 1 < nt1; ++t) biggest = std::max<long long>(biggest, (long long)(sp.h_tile_start[t + 1] - sp.h_tile_start[t]));
-    const long long n_far = (long long)c->h_counters[14];
+    const long long n_far = (long long)c->h_counters[12];
     if (d.room >= biggest && n_far <= sp.far_cap && d.off_new + sp.n + sp.gap <= sp.cap) {
       sp.deferred = true; sp.n_old = n_slots;
       c->n_deferred++;
@@ -658,12 +647,8 @@ static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool&
       sp.n = n_slots;                       // regrow copies [0, sp.n)
       EB_TRY(species_reserve(c, sp, n_slots + arrivals));
       sp.n = keep_n;
-      // Low state: the next deferred permute runs towards higher slots, where only particles stored ABOVE
-      // their sorted index are a hazard -- so the arrivals go in FRONT of the live slots (the view moves
-      // down; nothing index-based is alive at this point).  High state / no window: appended.
-      const bool prepend = sp.win > 0 && sp.off < sp.gap + sp.win && arrivals <= sp.off;
+      // appended; the deferred permute takes slots this far from their sorted place through its side buffer
       long long at = n_slots;
-      if (prepend) { set_view(sp, sp.off - arrivals); at = 0; }
       if (from_hi > 0) {
         k_unpack_aos<<<(unsigned)((from_hi + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[0], c->ndims, from_hi, at,
             sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
