@@ -163,8 +163,8 @@ int32_t get_particles(eb200_ctx* c, int isp, long long first, long long cap, dou
 template <int ND, int SHAPE>
 __global__ void k_keys(GridP g, PushP p, BcP3 bc, double* __restrict__ X, double* __restrict__ Y,
                        double* __restrict__ Z, double* __restrict__ PX, double* __restrict__ PY,
-                       double* __restrict__ PZ, uint32_t* key, uint32_t* count, uint32_t nbucket) {
-  const long long ip = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+                       double* __restrict__ PZ, uint32_t* key, uint32_t* count, uint32_t nbucket, long long i0 = 0) {
+  const long long ip = i0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const bool act = ip < p.n;
   uint32_t k = nbucket - 1;
   if (act && key[ip] != KEY_INVALID) {
@@ -572,7 +572,8 @@ __global__ void k_particle_bc(BcP b, long long n, double* __restrict__ pos, doub
 __global__ void k_pack_leavers(long long n, int nd, const double* x, const double* y, const double* z,
                                const double* px, const double* py, const double* pz, const double* w,
                                uint32_t* key, const uint32_t* flag, unsigned long long* cursors,
-                               double* send_lo, double* send_hi) {
+                               double* send_lo, double* send_hi, uint32_t* count = nullptr, uint32_t invalid_bucket = 0,
+                               long long n_counted = 0) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t f = flag[i];
@@ -583,6 +584,8 @@ __global__ void k_pack_leavers(long long n, int nd, const double* x, const doubl
   if (nd >= 2) q[1] = y[i];
   if (nd >= 3) q[2] = z[i];
   q[nd] = px[i]; q[nd + 1] = py[i]; q[nd + 2] = pz[i]; q[nd + 3] = w[i];
+  // the push kernel has already counted this slot under its key (fused keys): move the count to the dead bucket
+  if (count && i < n_counted) { atomicSub(count + key[i], 1u); atomicAdd(count + invalid_bucket, 1u); }
   key[i] = KEY_INVALID;
 }
 
@@ -594,7 +597,8 @@ static int32_t read_counters(eb200_ctx* c, int n) {
 
 // applies particle_bcs to slots [0, n_slots) of one species; returns the new slot
 // count (arrivals are appended) and whether the live count may have changed
-static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool& changed) {
+// n_counted > 0: the push kernel wrote keys + histogram for the slots [0, n_counted) (fused keys)
+static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool& changed, long long n_counted = 0) {
   const int nvar = c->ndims + 4;
   for (int ax = 0; ax < c->ndims; ++ax) {
     const BcP b = make_bc(c, sp, ax);
@@ -616,7 +620,8 @@ static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool&
     EB_TRY(ensure_stage(c, std::max<long long>(std::max<long long>(4 * std::max(nlo, nhi), c->mig_min_particles) * nvar, 1 << 16)));
     if (nlo + nhi > 0) {
       k_pack_leavers<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(n_slots, c->ndims, sp.a[0], sp.a[1], sp.a[2],
-          sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key, sp.dest, c->d_counters, c->mig_send[0], c->mig_send[1]);
+          sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key, sp.dest, c->d_counters, c->mig_send[0], c->mig_send[1],
+          n_counted > 0 ? c->cell_count : nullptr, (uint32_t)c->g.ncell_ext, n_counted);
       c->launches++;
     }
     // exchange counts (as doubles, exact below 2^53), then payloads; low side first.
@@ -795,12 +800,18 @@ int32_t push_particles(eb200_ctx* c) {
         // the next sort keys + histogram (saves the sort's pass over the particle arrays)
         std::vector<char> ksbuf(keysink_size());
         const void* ks = nullptr;
-        if (c->nproc == 1 && c->fuse_keys) {
+        // Several ranks: the same, when the decomposed axes are periodic for the particles (nothing but
+        // migration happens there): leavers give their count back when they are packed, arrivals are keyed
+        // and counted by a pass over the arrivals alone.
+        bool fusable = c->fuse_keys != 0;
+        for (int d = 0; d < c->ndims; ++d)
+          if (c->nprocdir[d] > 1 && (sp.bc[2 * d] != EB200_BC_PERIODIC || sp.bc[2 * d + 1] != EB200_BC_PERIODIC)) fusable = false;
+        if (fusable) {
           EB_TRY(ensure_cells(c, sp));
           const uint32_t nbucket = (uint32_t)(c->g.ncell_ext + 1);
           EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
           BcP3 bc;
-          for (int d = 0; d < 3; ++d) { bc.on[d] = d < c->ndims; bc.b[d] = make_bc(c, sp, d < c->ndims ? d : 0); }
+          for (int d = 0; d < 3; ++d) { bc.on[d] = d < c->ndims && c->nprocdir[d] == 1; bc.b[d] = make_bc(c, sp, d < c->ndims ? d : 0); }
           keysink_fill(ksbuf.data(), bc, sp.key, c->cell_count, nbucket);
           ks = ksbuf.data();
         }
@@ -813,7 +824,31 @@ int32_t push_particles(eb200_ctx* c) {
         EB_TRY(launch_push_baseline(c, sp, p));
       }
     }
-    if (fused_keys) { EB_TRY(sort_species(c, sp, sp.n, true, true)); done[is] = 1; }
+    if (fused_keys && c->nproc == 1) { EB_TRY(sort_species(c, sp, sp.n, true, true)); done[is] = 1; }
+    else if (fused_keys) {
+      const long long n_counted = sp.n;
+      long long n_slots = sp.n;
+      bool changed = false;
+      {
+        ScopedPhase ph(c, "bcs");
+        EB_TRY(species_bcs(c, sp, n_slots, changed, n_counted));
+        if (n_slots > n_counted) {       // arrivals: BCs of the other axes, key, histogram
+          BcP3 bc;
+          for (int d = 0; d < 3; ++d) { bc.on[d] = d < c->ndims && c->nprocdir[d] == 1; bc.b[d] = make_bc(c, sp, d < c->ndims ? d : 0); }
+          PushP pk2 = make_push_params(c, sp, n_slots);
+          const uint32_t nbucket = (uint32_t)(c->g.ncell_ext + 1);
+          const unsigned ga = (unsigned)((n_slots - n_counted + 255) / 256);
+#define LK(ND, SH)                                                                               \
+          if (c->ndims == ND && c->shape == SH)                                                  \
+            k_keys<ND, SH><<<ga, 256, 0, c->stream>>>(c->g, pk2, bc, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.key, c->cell_count, nbucket, n_counted);
+          LK(2, 0) LK(2, 1) LK(3, 0) LK(3, 1)
+#undef LK
+          c->launches++;
+        }
+      }
+      EB_TRY(sort_species(c, sp, n_slots, true, true));
+      done[is] = 1;
+    }
   }
   // current_bcs(species) is a no-op without mixed per-species BCs (boundary.F90:1130-1136)
   // particle_bcs for the species the push did not already finish

@@ -81,7 +81,11 @@ __device__ __forceinline__ void half_drift(const PushP& p, const double* pos, do
                                            double* px, double& ux, double& uy, double& uz) {
   ux = __dmul_rn(mx, p.ipart_mc); uy = __dmul_rn(my, p.ipart_mc); uz = __dmul_rn(mz, p.ipart_mc);
   const double g2 = __fma_rn(uz, uz, __fma_rn(uy, uy, __fma_rn(ux, ux, 1.0)));
+#ifdef EB_EXACT_DIV
   const double root = __ddiv_rn(p.dtco2, __dsqrt_rn(g2));
+#else
+  const double root = __dmul_rn(p.dtco2, rsqrt(g2));     // (c dt / 2) / gamma, ~1 ulp; the same function keys and pushes
+#endif
   const double u0[3] = {ux, uy, uz};
 #pragma unroll
   for (int d = 0; d < ND; ++d) px[d] = __fma_rn(u0[d], root, __dadd_rn(pos[d], -p.gml[d]));
@@ -156,8 +160,12 @@ __device__ __forceinline__ int bc_and_key(const GridP& g, const PushP& p, const 
 __device__ __forceinline__ void boris(double& ux, double& uy, double& uz, double ex, double ey, double ez,
                                       double bx, double by, double bz, double cmratio, double ccmratio) {
   const double uxm = ux + cmratio * ex, uym = uy + cmratio * ey, uzm = uz + cmratio * ez;
+#ifdef EB_EXACT_DIV
   const double gamma_rel = sqrt(uxm * uxm + uym * uym + uzm * uzm + 1.0);
   const double root = ccmratio / gamma_rel;
+#else
+  const double root = ccmratio * rsqrt(uxm * uxm + uym * uym + uzm * uzm + 1.0);
+#endif
   const double taux = bx * root, tauy = by * root, tauz = bz * root;
   const double taux2 = taux * taux, tauy2 = tauy * tauy, tauz2 = tauz * tauz;
   const double tau = 1.0 / (1.0 + taux2 + tauy2 + tauz2);

@@ -324,13 +324,18 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
 
   boris(ux, uy, uz, ex_part, ey_part, ez_part, bx_part, by_part, bz_part, p.cmratio, p.ccmratio);
 
-  const double gamma_rel = sqrt(ux * ux + uy * uy + uz * uz + 1.0);
   double delta[3] = {0, 0, 0}, part_vz = 0.0;
+#ifdef EB_EXACT_DIV
+  const double gamma_rel = sqrt(ux * ux + uy * uy + uz * uz + 1.0);
+  const double igamma3 = 1.0 / gamma_rel;
+#else
+  const double igamma3 = rsqrt(ux * ux + uy * uy + uz * uz + 1.0);
+#endif
   if (ND == 3) {
-    const double root = p.dtco2 / gamma_rel;
+    const double root = p.dtco2 * igamma3;
     delta[0] = ux * root; delta[1] = uy * root; delta[2] = uz * root;
   } else {
-    const double igamma = 1.0 / gamma_rel;
+    const double igamma = igamma3;
     const double root = p.dtco2 * igamma;
     delta[0] = ux * root; delta[1] = uy * root;
     part_vz = uz * C0 * igamma;
