@@ -268,6 +268,49 @@ __global__ void k_gather_copy(const double* __restrict__ from, const double* __r
   const long long s = (long long)src[i];
   dst[i] = s >= n_main ? far[s - n_main] : from[s];
 }
+// Deterministic mode: the atomic cursors of k_src leave the order INSIDE a cell to the warp scheduler.
+// Thread per cell: re-order the cell's src entries by the particles' content (x, then y, z, px, py, pz,
+// w, then slot) so that the sorted order -- and with it every serial sum of the deposit -- is a function
+// of the particle set alone.
+struct Canon {
+  Attr7 at; const double* far; long long far_cap, n_main;
+  __device__ __forceinline__ double get(int a, uint32_t s) const {
+    return (long long)s >= n_main ? far[(size_t)a * far_cap + ((long long)s - n_main)] : at.a[a][s];
+  }
+  __device__ bool less(uint32_t sa, uint32_t sb, double xa, double xb) const {
+    if (xa != xb) return xa < xb;
+#pragma unroll 1
+    for (int a = 1; a < 7; ++a) {
+      if (!at.a[a]) continue;
+      const double va = get(a, sa), vb = get(a, sb);
+      if (va != vb) return va < vb;
+    }
+    return sa < sb;
+  }
+};
+__global__ void k_canon(Canon cn, const uint32_t* __restrict__ start, long long nbucket_live, uint32_t* src) {
+  const long long cell = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell >= nbucket_live) return;
+  const uint32_t b = start[cell], e = start[cell + 1];
+  // insertion sort; the keys of the entries already placed sit in a small window of local memory
+  constexpr int WN = 48;
+  double kx[WN];
+  for (uint32_t i = b; i < e; ++i) {
+    const uint32_t si = src[i];
+    const double xi = cn.get(0, si);
+    uint32_t j = i;
+    while (j > b) {
+      const uint32_t sj = src[j - 1];
+      const double xj = (j - 1 - b) < (uint32_t)WN ? kx[j - 1 - b] : cn.get(0, sj);
+      if (!cn.less(si, sj, xi, xj)) break;
+      src[j] = sj;
+      if ((j - b) < (uint32_t)WN) kx[j - b] = xj;
+      --j;
+    }
+    src[j] = si;
+    if ((j - b) < (uint32_t)WN) kx[j - b] = xi;
+  }
+}
 __global__ void k_tile_start(const uint32_t* __restrict__ cell_start, uint32_t* ts, long long ntile1, int cpt) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (t < ntile1) ts[t] = cell_start[t * cpt];
@@ -428,7 +471,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
   }
   cub::DeviceScan::ExclusiveSum(c->cub_tmp, tmp, c->cell_count, sp.cell_start, (int)(nbucket + 1), c->stream);
   EB_CUDA(c, cudaMemsetAsync(c->cell_count, 0, (size_t)(nbucket + 1) * sizeof(uint32_t), c->stream));
-  const bool inverse = may_defer && sp.win > 0;
+  const bool inverse = (may_defer && sp.win > 0) || c->deterministic;
   if (inverse) {
     if (!sp.far) {
       sp.far_cap = std::max<long long>(sp.cap / 256, 1 << 14);
@@ -439,12 +482,19 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
     for (int k = 0; k < 7; ++k) at.a[k] = (k < 3 && k >= c->ndims) ? nullptr : sp.a[k];
     const long long W = sp.off >= sp.gap + sp.win ? sp.off - sp.gap : sp.gap + sp.win - sp.off;
     // the window is shared between the displacements (<= limit) and the particles of one launch
-    const long long limit = W / 4;
-    sp.disp_fwd = sp.disp_bwd = limit;
+    const bool deferrable = may_defer && sp.win > 0;      // else: deterministic mode, permute below
+    const long long limit = deferrable ? W / 4 : (1LL << 62);
+    sp.disp_fwd = sp.disp_bwd = deferrable ? limit : W;
     EB_CUDA(c, cudaMemsetAsync(c->d_counters + 12, 0, sizeof(unsigned long long), c->stream));
     k_src<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket, c->d_counters + 12,
                                    at, sp.far, sp.far_cap, limit);
     EB_CUDA(c, cudaMemcpyAsync(c->h_counters + 12, c->d_counters + 12, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    if (c->deterministic) {
+      Canon cn; cn.at = at; cn.far = sp.far; cn.far_cap = sp.far_cap; cn.n_main = n_slots;
+      const long long ncell = (long long)nbucket - 1;      // the dead bucket keeps its order: it is dropped
+      k_canon<<<(unsigned)((ncell + 127) / 128), 128, 0, c->stream>>>(cn, sp.cell_start, ncell, sp.dest);
+      c->launches++;
+    }
   } else {
     k_dest<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket);
   }
@@ -484,7 +534,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
     long long biggest = 1;
     for (long long t = 0; t + 1 < nt1; ++t) biggest = std::max<long long>(biggest, (long long)(sp.h_tile_start[t + 1] - sp.h_tile_start[t]));
     const long long n_far = (long long)c->h_counters[12];
-    if (d.room >= biggest && n_far <= sp.far_cap && d.off_new + sp.n + sp.gap <= sp.cap) {
+    if (may_defer && sp.win > 0 && d.room >= biggest && n_far <= sp.far_cap && d.off_new + sp.n + sp.gap <= sp.cap) {
       sp.deferred = true; sp.n_old = n_slots;
       c->n_deferred++;
     } else if (sp.n > 0) {
