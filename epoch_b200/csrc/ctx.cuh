@@ -169,6 +169,8 @@ struct eb200_ctx {
   double* rho = nullptr;
   double* rec_scratch = nullptr;              // deposit records of the split push/deposit kernels
   long long rec_scratch_cap = 0;              // ... capacity in particles
+  double* det_tiles = nullptr;                // deterministic deposit: one J tile per deposit CTA of a launch
+  size_t det_tiles_cap = 0;                   // ... capacity in doubles
   long long rec_scratch_max = 1LL << 27;      // option deposit_scratch (particles per slab, 64 B each)
   // options
   int push_kernel = 0;          // 0 auto, 1 baseline (global atomics), 3 tiled (push + deposit kernels)

@@ -870,6 +870,8 @@ int32_t push_particles(eb200_ctx* c) {
         tiled[is] = handled;
       }
       if (!handled) {
+        if (c->deterministic)
+          return fail(c, EB200_E_UNSUPPORTED, "deterministic_deposit needs the tiled kernels (2D/3D, tophat or triangle shape)");
         EB_TRY(settle_species(c, sp));
         EB_TRY(launch_push_baseline(c, sp, p));
       }

@@ -153,6 +153,16 @@ __device__ __forceinline__ double pick(const double* a, int t) {
 
 namespace {
 
+// Overflow contributions go to the shared J tile with atomics.  FX (deterministic mode): as 64-bit
+// fixed-point integers into a second tile `fx.delta` doubles further on -- integer sums do not depend
+// on the order of the adds; the tile is folded into J once all items are done.
+struct FxP { long long delta; double inv_unit; };
+template <bool FX>
+__device__ __forceinline__ void ovf_add(double* addr, double v, const FxP& fx) {
+  if (FX) atomicAdd(reinterpret_cast<unsigned long long*>(addr + fx.delta), (unsigned long long)__double2ll_rn(v * fx.inv_unit));
+  else atomicAdd(addr, v);
+}
+
 // One work item of a 3D particle that changed cell along axis m: everything the particle
 // deposits outside the register boxes because of that axis.  The window cells not covered
 // by the boxes are split, per current component A (P = A+1, Q = A+2 cyclic), by the first
@@ -165,9 +175,9 @@ namespace {
 // With the axes rotated to (a0, a1, a2) = (m, m+1, m+2) the item is role "A" for component
 // a0, role "P" for component a2 and role "Q" for component a1, so the weights of the three
 // axes are evaluated once.  The values go to the shared J tile with atomics.
-template <int SHAPE, class R>
+template <int SHAPE, class R, bool FX = false>
 __device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double* __restrict__ sJ, int m,
-                                            int jn = TL<3, SHAPE>::JN, int sub_off = 0) {
+                                            int jn = TL<3, SHAPE>::JN, int sub_off = 0, const FxP fx = FxP{0, 0.0}) {
   using T = TL<3, SHAPE>;
   constexpr int NW = T::NW, NS = NW + 2;
   const int a0 = m, a1 = m == 2 ? 0 : m + 1, a2 = a1 == 2 ? 0 : a1 + 1;
@@ -209,7 +219,7 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double
         // window membership first: the slots beyond the box exist only where P / Q moved too
         const bool in = u >= lo && u < hi && v >= lo && v < hi && (u != 0 || dc1 < 0) && (u != NS - 1 || dc1 > 0) &&
                         (v != 0 || dc2 < 0) && (v != NS - 1 || dc2 > 0);
-        if (in) atomicAdd(base + u * s1 + v * s2, cov * (g5[u] * q1[v] + h5[u] * q2[v]));
+        if (in) ovf_add<FX>(base + u * s1 + v * s2, cov * (g5[u] * q1[v] + h5[u] * q2[v]), fx);
       }
   }
   {
@@ -230,7 +240,7 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double
     for (int v = 0; v < NS; ++v) {
       if ((v != 0 || dc1 < 0) && (v != NS - 1 || dc1 > 0)) {
 #pragma unroll
-        for (int i = 0; i < NW; ++i) atomicAdd(base + i * s2 + v * s1, ca[i] * q2[v]);
+        for (int i = 0; i < NW; ++i) ovf_add<FX>(base + i * s2 + v * s1, ca[i] * q2[v], fx);
       }
     }
   }
@@ -246,7 +256,7 @@ __device__ __forceinline__ void mover_item3(const PushP& p, const R& rec, double
     for (int u = 0; u < NW; ++u) {
       const double w = g2[u] * (0.5 * ov0) + h2[u] * (third * ov0);
 #pragma unroll
-      for (int i = 0; i < NW; ++i) atomicAdd(base + i * s1 + u * s2, ca[i] * w);
+      for (int i = 0; i < NW; ++i) ovf_add<FX>(base + i * s1 + u * s2, ca[i] * w, fx);
     }
   }
 }
@@ -403,9 +413,9 @@ namespace {
 
 // phase 2b: the warp adds the contributions of one cell-changing particle that fall
 // outside its home box (at most one layer per axis), lane per (component, cell)
-template <int ND, int SHAPE, class R>
+template <int ND, int SHAPE, class R, bool FX = false>
 __device__ __forceinline__ void mover_overflow(const PushP& p, const R& rec, double* __restrict__ sJ, int lane,
-                                               int jn = TL<ND, SHAPE>::JN, int sub_off = 0) {
+                                               int jn = TL<ND, SHAPE>::JN, int sub_off = 0, const FxP fx = FxP{0, 0.0}) {
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW, NS = NW + 2;
   const int pk = rec.pack();
@@ -474,7 +484,7 @@ __device__ __forceinline__ void mover_overflow(const PushP& p, const R& rec, dou
       else val = (p.fc[2] * w * p.q * rec.get(2 * ND + 1)) * (gv[0] * yf1 + hv[0] * yf2);
     }
     const int idx = ((ND >= 3 ? (l[2] + t[2]) : 0) * T::JY + (ND >= 2 ? (l[1] + t[1]) : 0)) * T::JX + l[0] + t[0];
-    atomicAdd(sJ + comp * jn + idx, val);
+    ovf_add<FX>(sJ + comp * jn + idx, val, fx);
   }
 }
 
@@ -672,10 +682,15 @@ __device__ __forceinline__ void load_rec(double* r, const double* src) {
   for (int k = 0; k < 4; ++k) { const double2 v = __ldg(s2 + k); r[2 * k] = v.x; r[2 * k + 1] = v.y; }
 }
 
-template <int ND, int SHAPE>
+// DET (option deterministic_deposit): the overflow items accumulate in fixed point and the tile is stored to
+// `tile_out` (one J tile per CTA) instead of being added to HBM with RED; k_reduce_tiles then sums the
+// tiles that overlap a cell in a fixed order.  With the canonical particle order of the sort (k_canon) the
+// currents are bitwise reproducible from run to run.
+template <int ND, int SHAPE, bool DET>
 __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit_split(GridP g, FieldP F, PushP p,
                                                                                 const uint32_t* __restrict__ cell_start,
-                                                                                long long tile0, const double* __restrict__ scratch) {
+                                                                                long long tile0, const double* __restrict__ scratch,
+                                                                                double* __restrict__ tile_out) {
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW, SFM = T::SFM, NA = T::NACC, NTB = T::CPT / SUB;
   constexpr int SA = ND - 1;                                   // split axis
@@ -683,8 +698,8 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   constexpr int JXs = T::JX, JYs = ND == 3 ? T::JY : TS + NW + 1, JZs = ND == 3 ? TS + NW + 1 : 1;
   constexpr int JNs = JXs * JYs * JZs;
   extern __shared__ double smem[];
-  double* sJ = smem;                          // [3][JNs]
-  int* sM = (int*)(sJ + 3 * JNs);             // [2 * MCAPB] work items (record, moving axis)
+  double* sJ = smem;                          // [3][JNs] (DET: + [3][JNs] fixed-point overflow sums)
+  int* sM = (int*)(sJ + (DET ? 6 : 3) * JNs); // [2 * MCAPB] work items (record, moving axis)
   int* sCnt = sM + 2 * MCAPB;
   double2* ring = reinterpret_cast<double2*>(((uintptr_t)(sCnt + 4) + 15) & ~(uintptr_t)15);   // [RING][4][NTB] 16 B units
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -701,9 +716,26 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   int org[3];
 #pragma unroll
   for (int d = 0; d < 3; ++d) org[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) + SFM - 1 + (d == SA ? sub * TS : 0) : 1;
-  for (int i = tid; i < 3 * JNs; i += NTB) sJ[i] = 0.0;
-  if (tid == 0) sCnt[0] = 0;
+  for (int i = tid; i < (DET ? 6 : 3) * JNs; i += NTB) sJ[i] = 0.0;      // (+0.0 is the integer 0)
+  if (tid == 0) { sCnt[0] = 0; sCnt[1] = 0; sCnt[2] = 0; sCnt[3] = 0; }
   __syncthreads();
+  FxP fx{0, 0.0};
+  if (DET) {
+    // fixed-point unit of the overflow sums: 2^-44 of the largest |fc w q| of the sub-tile (a power of two;
+    // the maximum does not depend on the order it is taken in)
+    double wmax = 0.0;
+    for (uint32_t q = sb0 + tid; q < sb1; q += NTB) wmax = fmax(wmax, fabs(__ldg(scratch + (size_t)(q - base) * 8 + 2 * ND)));
+    atomicMax(reinterpret_cast<unsigned long long*>(sCnt + 2), (unsigned long long)__double_as_longlong(wmax));
+    __syncthreads();
+    const double wm = __longlong_as_double((long long)*reinterpret_cast<unsigned long long*>(sCnt + 2));
+    double fcm = fmax(fabs(p.fc[0]), fabs(p.fc[1]));
+    fcm = fmax(fcm, fabs(p.fc[2]) * (ND == 2 ? C0 : 1.0));
+    const double S = fmax(wm * fabs(p.q) * fcm, 1e-300);
+    int ex;
+    frexp(S, &ex);                                  // S < 2^ex
+    fx.delta = 3 * JNs;
+    fx.inv_unit = ldexp(1.0, 44 - ex);
+  }
 
   // ---- thread per cell: all components of the cell's box in registers; the next record is
   //      fetched while the current one is deposited ----
@@ -749,14 +781,14 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
       if (ND == 2) {
         const int slot = atomicAdd(sCnt, 1);
         if (slot < MCAPB) sM[2 * slot] = r;
-        else for (int ln = 0; ln < 32; ++ln) mover_overflow<ND, SHAPE>(p, rec, sJ, ln, JNs, sub * TS);   // list full
+        else for (int ln = 0; ln < 32; ++ln) mover_overflow<ND, SHAPE, RecG, DET>(p, rec, sJ, ln, JNs, sub * TS, fx);   // list full
       } else {
         int slot = atomicAdd(sCnt, mover_item_count(pack));
 #pragma unroll
         for (int m = 0; m < 3; ++m) {
           if (((pack >> (2 * m)) & 3) == 1) continue;
           if (slot < MCAPB) { sM[2 * slot] = r; sM[2 * slot + 1] = m; }
-          else mover_item3<SHAPE>(p, rec, sJ, m, JNs, sub * TS);
+          else mover_item3<SHAPE, RecG, DET>(p, rec, sJ, m, JNs, sub * TS, fx);
           ++slot;
         }
       }
@@ -796,15 +828,23 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   if (ND == 3) {
     for (int m = tid; m < nm; m += NTB) {
       const RecG rec{scratch + (size_t)(pb - base + (uint32_t)sM[2 * m]) * 8};
-      mover_item3<SHAPE>(p, rec, sJ, sM[2 * m + 1], JNs, sub * TS);
+      mover_item3<SHAPE, RecG, DET>(p, rec, sJ, sM[2 * m + 1], JNs, sub * TS, fx);
     }
   } else {
     for (int m = warp; m < nm; m += NTB / 32) {
       const RecG rec{scratch + (size_t)(pb - base + (uint32_t)sM[2 * m]) * 8};
-      mover_overflow<ND, SHAPE>(p, rec, sJ, lane, JNs, sub * TS);
+      mover_overflow<ND, SHAPE, RecG, DET>(p, rec, sJ, lane, JNs, sub * TS, fx);
     }
   }
   __syncthreads();
+  if (DET) {
+    // fold the fixed-point overflow sums into the tile and store it: k_reduce_tiles adds the tiles up
+    const double unit = 1.0 / fx.inv_unit;
+    double* out = tile_out + (size_t)blockIdx.x * (3 * JNs);
+    for (int i = tid; i < 3 * JNs; i += NTB)
+      out[i] = sJ[i] + (double)__double_as_longlong(sJ[3 * JNs + i]) * unit;
+    return;
+  }
   // tile J -> HBM (RED.ADD.F64: tile halos overlap): thread per (component, y, z) row, walking x
   for (int row = tid; row < 3 * JYs * JZs; row += NTB) {
     const int cj = row / (JYs * JZs), r = row - cj * (JYs * JZs);
@@ -822,6 +862,66 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   }
 }
 
+}  // namespace
+
+namespace {
+// Deterministic mode: J(cell) += the entries of all sub-tile J tiles of this launch that cover the cell, taken
+// in ascending (z, y, x) sub-tile order.  Thread per cell of the planes [lo, hi] along the slowest axis.
+template <int ND, int SHAPE>
+__global__ void k_reduce_tiles(GridP g, FieldP F, const uint32_t* __restrict__ cell_start, long long t0, long long t1,
+                               const double* __restrict__ tiles, int lo, int hi) {
+  using T = TL<ND, SHAPE>;
+  constexpr int NW = T::NW, SFM = T::SFM, NTB = T::CPT / SUB, SA = ND - 1;
+  constexpr int TS = tile_dim(ND, SA) / SUB;
+  constexpr int JXs = T::JX, JYs = ND == 3 ? T::JY : TS + NW + 1, JZs = ND == 3 ? TS + NW + 1 : 1;
+  constexpr int JNs = JXs * JYs * JZs;
+  const int ex = g.n[0] + 2 * g.ngd[0], ey = ND >= 2 ? g.n[1] + 2 * g.ngd[1] : 1;
+  const long long planes = (long long)(hi - lo + 1);
+  const long long per_plane = ND == 3 ? (long long)ex * ey : ex;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= planes * per_plane) return;
+  int X[3] = {1, 1, 1};
+  X[0] = 1 - g.ngd[0] + (int)(i % ex);
+  if (ND == 3) { X[1] = 1 - g.ngd[1] + (int)((i / ex) % ey); X[2] = lo + (int)(i / per_plane); }
+  else X[1] = lo + (int)(i / per_plane);
+  // candidate (sub-)tile ranges per axis: origin(u) = b0 + u * stride <= X <= origin(u) + extent - 1
+  int u_lo[3] = {0, 0, 0}, u_hi[3] = {0, 0, 0};
+#pragma unroll
+  for (int d = 0; d < ND; ++d) {
+    const int b0 = (1 - KM) + SFM - 1;
+    const int stride = d == SA ? TS : tile_dim(ND, d);
+    const int extent = stride + NW + 1;
+    const int nu = g.ntile[d] * (d == SA ? SUB : 1);
+    const int rel = X[d] - b0;
+    int hi_u = rel >= 0 ? rel / stride : -1;
+    int lo_u = rel - extent + 1 > 0 ? (rel - extent + 1 + stride - 1) / stride : 0;
+    if (hi_u > nu - 1) hi_u = nu - 1;
+    u_lo[d] = lo_u; u_hi[d] = hi_u;
+  }
+  double sum[3] = {0.0, 0.0, 0.0};
+  for (int uz = u_lo[2]; uz <= u_hi[2]; ++uz)
+    for (int uy = u_lo[1]; uy <= u_hi[1]; ++uy)
+      for (int ux = u_lo[0]; ux <= u_hi[0]; ++ux) {
+        const int u[3] = {ux, uy, uz};
+        const int sub = u[SA] % SUB;
+        int tcd[3] = {ux, uy, uz};
+        tcd[SA] = u[SA] / SUB;
+        const long long tile = ((long long)(ND == 3 ? tcd[2] : 0) * g.ntile[1] + (ND >= 2 ? tcd[1] : 0)) * g.ntile[0] + tcd[0];
+        if (tile < t0 || tile >= t1) continue;
+        const long long kbase = tile * T::CPT;
+        if (cell_start[kbase + sub * NTB] == cell_start[kbase + (sub + 1) * NTB]) continue;   // the CTA returned early
+        int j[3] = {0, 0, 0};
+#pragma unroll
+        for (int d = 0; d < ND; ++d) j[d] = X[d] - ((1 - KM) + SFM - 1 + u[d] * (d == SA ? TS : tile_dim(ND, d)));
+        const double* tl = tiles + (size_t)((tile - t0) * SUB + sub) * (3 * JNs) + (j[2] * JYs + j[1]) * JXs + j[0];
+#pragma unroll
+        for (int cj = 0; cj < 3; ++cj) sum[cj] += tl[cj * JNs];
+      }
+  const size_t gi = g.idx(X[0], X[1], X[2]);
+#pragma unroll
+  for (int cj = 0; cj < 3; ++cj)
+    if (sum[cj] != 0.0) F.f[JX + cj][gi] += sum[cj];
+}
 }  // namespace
 
 size_t keysink_size() { return sizeof(KeySink); }
@@ -871,12 +971,24 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
     c->rec_scratch_cap = want;
   }
   const long long cap = c->rec_scratch_cap < room ? c->rec_scratch_cap : room;
+  // deterministic mode: one J tile per deposit CTA (1 GB of them at most per launch)
+  const bool det = c->deterministic && !p.zero_current;
+  const size_t tile_doubles = 3 * (size_t)(c->ndims == 3 ? (c->shape == 0 ? TL<3, 0>::JN : TL<3, 1>::JN)
+                                                         : (c->shape == 0 ? TL<2, 0>::JN : TL<2, 1>::JN));   // >= the sub-tile's
+  const long long max_tiles = det ? std::max<long long>(1, (long long)(((size_t)1 << 30) / (tile_doubles * 8 * SUB))) : (1LL << 62);
+  if (det && c->det_tiles_cap < (size_t)std::min<long long>(max_tiles, ntiles) * SUB * tile_doubles) {
+    if (c->det_tiles) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(c->det_tiles); }
+    c->det_tiles = nullptr; c->det_tiles_cap = 0;
+    const size_t want_t = (size_t)std::min<long long>(max_tiles, ntiles) * SUB * tile_doubles;
+    EB_CUDA(c, cudaMalloc(&c->det_tiles, want_t * sizeof(double)));
+    c->det_tiles_cap = want_t;
+  }
   // slabs of consecutive tiles, run upwards (or downwards: deferred permute towards higher slots)
   std::vector<std::pair<long long, long long>> slabs;
   for (long long t0 = 0; t0 < ntiles;) {
     if (ts[t0 + 1] == ts[t0]) { ++t0; continue; }               // skip leading empty tiles
     long long t1 = t0 + 1;
-    while (t1 < ntiles && (long long)(ts[t1 + 1] - ts[t0]) <= cap) ++t1;
+    while (t1 < ntiles && (long long)(ts[t1 + 1] - ts[t0]) <= cap && t1 - t0 < max_tiles) ++t1;
     slabs.emplace_back(t0, t1);
     t0 = t1;
   }
@@ -886,16 +998,31 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
 #define L(ND, SH)                                                                                          \
     if (c->ndims == ND && c->shape == SH) {                                                                \
       auto ka = gather ? k_push_split<ND, SH, true> : k_push_split<ND, SH, false>;                         \
-      auto kb = k_deposit_split<ND, SH>;                                                                   \
+      auto kb = det ? k_deposit_split<ND, SH, true> : k_deposit_split<ND, SH, false>;                      \
       const size_t sa = sizeof(double) * (6 * TL<ND, SH>::FN + (NTA / 32) * 256);                                               \
-      const size_t sb = sizeof(double) * 3 * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4)   /* >= sub-tile need */ \
+      const size_t sb = sizeof(double) * (det ? 6 : 3) * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4)   /* >= sub-tile need */ \
                         + (size_t)RING * 64 * (TL<ND, SH>::CPT / SUB) + 16;                                      \
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
       { ScopedPhase pa(c, "push_A");                                                                       \
         ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks); } \
       if (!p.zero_current) { ScopedPhase pb(c, "push_B");                                                  \
-        kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch); }    \
+        kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch, c->det_tiles); \
+        if (det) {                                                                                         \
+          /* planes of the slowest axis that the tiles [t0, t1) can reach */                              \
+          const long long per_layer = ND == 3 ? (long long)c->g.ntile[0] * c->g.ntile[1] : c->g.ntile[0];  \
+          const int TDS = tile_dim(ND, ND - 1);                                                            \
+          int lo = (1 - KM) + (int)(t0 / per_layer) * TDS + TL<ND, SH>::SFM - 1;                           \
+          int hi = (1 - KM) + (int)((t1 - 1) / per_layer) * TDS + TL<ND, SH>::SFM - 1 + TDS + TL<ND, SH>::NW; \
+          lo = std::max(lo, 1 - c->g.ngd[ND - 1]); hi = std::min(hi, c->g.n[ND - 1] + c->g.ngd[ND - 1]);   \
+          if (hi >= lo) {                                                                                  \
+            const long long cells = (long long)(hi - lo + 1) * (c->g.n[0] + 2 * c->g.ngd[0]) *             \
+                                    (ND == 3 ? (c->g.n[1] + 2 * c->g.ngd[1]) : 1);                         \
+            k_reduce_tiles<ND, SH><<<(unsigned)((cells + 255) / 256), 256, 0, c->stream>>>(c->g, c->f, sp.cell_start, t0, t1, \
+                                                                                           c->det_tiles, lo, hi);           \
+            c->launches++;                                                                                 \
+          }                                                                                                \
+        } }                                                                                                \
     }
     L(2, 0) L(2, 1) L(3, 0) L(3, 1)
 #undef L

@@ -442,3 +442,36 @@ def test_deferred_permute(product_abi, oracle_abi, ndims, shape, pbc, n, window,
     deferred, permuted = sims[0].ctx.timer("deferred_sorts")[1], sims[0].ctx.timer("permuted_sorts")[1]
     assert sims[0].ctx.timer("cell_mismatch")[1] == 0
     assert (deferred > 0) == expect, (deferred, permuted)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndims,shape,pbc,window", [(3, "triangle", "periodic", "auto"), (3, "tophat", "reflect", 0),
+                                                    (2, "triangle", "periodic", "auto"), (2, "tophat", "open", 4000)])
+def test_deterministic_deposit(product_abi, oracle_abi, ndims, shape, pbc, window):
+    """option deterministic_deposit: two runs of the same deck give bitwise identical currents, fields and
+    particle arrays (canonical order inside a cell, fixed-point overflow sums, ordered sum of the tile
+    halos), and they still equal the oracle within the usual tolerance."""
+    n = [24, 16, 12] if ndims == 3 else [40, 48]
+    bcs = [pbc] * (2 * ndims)
+    fbc = ["periodic" if pbc == "periodic" else "clamp"] * (2 * ndims)
+    opts = {"deterministic_deposit": 1, "defer_window": window, "deposit_scratch": 4096}
+
+    def run(abi):
+        s = make_plasma(abi, ndims, shape, n, seed=9, ppc=7, u_th=0.5, e_amp=1e9, b_amp=3.0, bcs=bcs, bc_field=fbc,
+                        options=opts)
+        for _ in range(6):
+            s.step_once()
+        return s
+    a, b, o = run(product_abi), run(product_abi), run(oracle_abi)
+    fa, fb = a.ctx.download_fields(ALL9), b.ctx.download_fields(ALL9)
+    for k in ALL9:
+        assert np.array_equal(fa[k], fb[k]), k
+    for isp in range(len(a.species)):
+        assert np.array_equal(a.ctx.download_particles(isp), b.ctx.download_particles(isp))
+    compare_fields(a, o, ALL9, tol=1e-10)
+    compare_particles(a, o, tol=1e-10)
+    # not on the general kernel
+    if ndims == 3:
+        s = make_plasma(product_abi, 3, "bspline3", [8, 8, 8], seed=1, ppc=2, options={"deterministic_deposit": 1})
+        with pytest.raises(Exception):
+            s.step_once()
