@@ -491,6 +491,7 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
     return 0;
   }
   if (k == "fuse_keys") { c->fuse_keys = atoi(value) != 0; return 0; }
+  if (k == "tma") { c->use_tma = atoi(value) != 0; c->tmap_valid = false; return 0; }
   // deferred permute: head room (slots) between the two states of the particle arrays; takes effect when
   // the arrays are next (re)allocated.  "auto" = need / 8, "0" = off (permute inside the sort)
   if (k == "defer_window") { c->defer_window = v == "auto" ? -1 : atoll(value); return 0; }

@@ -169,6 +169,11 @@ struct eb200_ctx {
   double* rho = nullptr;
   double* rec_scratch = nullptr;              // deposit records of the split push/deposit kernels
   long long rec_scratch_cap = 0;              // ... capacity in particles
+  // TMA descriptor of the E,B arrays for the push kernel's tile load (push_tiled.cu)
+  alignas(64) unsigned char tmap[128] = {0};
+  long long tmap_sig[6] = {0, 0, 0, 0, 0, 0};
+  bool tmap_valid = false, tmap_ok = false;
+  int use_tma = 1;              // option tma: 0 = stage the field tile with plain loads
   double* det_tiles = nullptr;                // deterministic deposit: one J tile per deposit CTA of a launch
   size_t det_tiles_cap = 0;                   // ... capacity in doubles
   long long rec_scratch_max = 1LL << 27;      // option deposit_scratch (particles per slab, 64 B each)

@@ -25,6 +25,8 @@
 // which is the reference's running sum (particles.F90:522-563) with the common
 // factor taken out; the result differs from the reference order by rounding only.
 #include "push_common.cuh"
+#include <cuda.h>          // CUtensorMap and its enums (the encoder is fetched with cudaGetDriverEntryPoint)
+#include <algorithm>
 
 namespace eb {
 
@@ -39,8 +41,20 @@ struct TL {
   static constexpr int TX = tile_dim(ND, 0), TY = tile_dim(ND, 1), TZ = tile_dim(ND, 2);
   static constexpr int CPT = TX * TY * TZ;
   // gather region: cells c0+SFM-1 .. c0+T-1+SFM+NW-1  (T + NW wide)
-  static constexpr int FX = TX + NW, FY = ND >= 2 ? TY + NW : 1, FZ = ND >= 3 ? TZ + NW : 1;
+  // (x extent rounded up to an even number of doubles: a TMA box row is a multiple of 16 bytes)
+#ifndef EB_FXPAD
+#define EB_FXPAD 1
+#endif
+  static constexpr int FX = EB_FXPAD ? ((TX + NW + 1) & ~1) : TX + NW, FY = ND >= 2 ? TY + NW : 1, FZ = ND >= 3 ? TZ + NW : 1;
   static constexpr int FN = FX * FY * FZ;
+  // shared layout of the staged E,B: [z][component][y][x].  With FX = 12 (3D triangle) the strides of a step in
+  // x, y, z are 1, 12, 6 * 132 = 8 (mod 16 doubles), so the 2 x 2 x 2 corner offsets of neighbouring
+  // particles (g- and h-type cells) and neighbouring cells in x fall into distinct banks.
+#ifndef EB_ZCOMP
+#define EB_ZCOMP 1
+#endif
+  static constexpr int FCS = EB_ZCOMP ? FX * FY : FN;         // component stride  (EB_ZCOMP = 0: [component][z][y][x])
+  static constexpr int FZS = EB_ZCOMP ? 6 * FX * FY : FX * FY;   // z stride
   // deposit region: cells c0+SFM-1 .. c0+T-1+SFM+NW  (T + NW + 1 wide)
   static constexpr int JX = TX + NW + 1, JY = ND >= 2 ? TY + NW + 1 : 1, JZ = ND >= 3 ? TZ + NW + 1 : 1;
   static constexpr int JN = JX * JY * JZ;
@@ -94,7 +108,7 @@ __device__ __forceinline__ double gather_tile(const double* __restrict__ f, cons
                                               const double* wz, int bx, int by, int bz) {
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW;
-  const double* b = f + ((ND >= 3 ? bz : 0) * T::FY + (ND >= 2 ? by : 0)) * T::FX + bx;
+  const double* b = f + (ND >= 3 ? bz : 0) * T::FZS + (ND >= 2 ? by : 0) * T::FX + bx;
   double accz = 0.0;
 #pragma unroll
   for (int k = 0; k < (ND >= 3 ? NW : 1); ++k) {
@@ -104,7 +118,7 @@ __device__ __forceinline__ double gather_tile(const double* __restrict__ f, cons
       double accx = 0.0;
 #pragma unroll
       for (int i = 0; i < NW; ++i) {
-        const double t = wx[i] * b[(k * T::FY + j) * T::FX + i];
+        const double t = wx[i] * b[k * T::FZS + j * T::FX + i];
         accx = i == 0 ? t : accx + t;
       }
       if (ND >= 2) { const double t = wy[j] * accx; accy = j == 0 ? t : accy + t; }
@@ -325,12 +339,12 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
   if (bad) atomicAdd(counters + 8, 1ULL);   // key and push disagree on the cell: must never happen
   // region index of weight slot i: g-type l1 + 1 + i, h-type l2 + 1 + i
   const int gx = l1[0] + 1, gy = l1[1] + 1, gz = l1[2] + 1, hx = l2[0] + 1, hy = l2[1] + 1, hz = l2[2] + 1;
-  const double ex_part = gather_tile<ND, SHAPE>(sF + 0 * T::FN, wh[0], wg[1], wg[2], hx, gy, gz);
-  const double ey_part = gather_tile<ND, SHAPE>(sF + 1 * T::FN, wg[0], wh[1], wg[2], gx, hy, gz);
-  const double ez_part = gather_tile<ND, SHAPE>(sF + 2 * T::FN, wg[0], wg[1], wh[2], gx, gy, hz);
-  const double bx_part = gather_tile<ND, SHAPE>(sF + 3 * T::FN, wg[0], wh[1], wh[2], gx, hy, hz);
-  const double by_part = gather_tile<ND, SHAPE>(sF + 4 * T::FN, wh[0], wg[1], wh[2], hx, gy, hz);
-  const double bz_part = gather_tile<ND, SHAPE>(sF + 5 * T::FN, wh[0], wh[1], wg[2], hx, hy, gz);
+  const double ex_part = gather_tile<ND, SHAPE>(sF + 0 * T::FCS, wh[0], wg[1], wg[2], hx, gy, gz);
+  const double ey_part = gather_tile<ND, SHAPE>(sF + 1 * T::FCS, wg[0], wh[1], wg[2], gx, hy, gz);
+  const double ez_part = gather_tile<ND, SHAPE>(sF + 2 * T::FCS, wg[0], wg[1], wh[2], gx, gy, hz);
+  const double bx_part = gather_tile<ND, SHAPE>(sF + 3 * T::FCS, wg[0], wh[1], wh[2], gx, hy, hz);
+  const double by_part = gather_tile<ND, SHAPE>(sF + 4 * T::FCS, wh[0], wg[1], wh[2], hx, gy, hz);
+  const double bz_part = gather_tile<ND, SHAPE>(sF + 5 * T::FCS, wh[0], wh[1], wg[2], hx, hy, gz);
 
   boris(ux, uy, uz, ex_part, ey_part, ez_part, bx_part, by_part, bz_part, p.cmratio, p.ccmratio);
 
@@ -566,6 +580,12 @@ __device__ __forceinline__ int mover_item_count(int pack) {
 // =====================================================================================
 namespace {
 
+#ifndef EB_STAGE_HALF
+#define EB_STAGE_HALF 1
+#endif
+#ifndef EB_SMEM_PAD
+#define EB_SMEM_PAD 0
+#endif
 #ifndef EB_NTA
 #define EB_NTA 128
 #endif
@@ -586,11 +606,13 @@ __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F
                                                               const uint32_t* __restrict__ src, uint32_t n_main,
                                                               const uint32_t* __restrict__ cell_start, long long tile0,
                                                               double* __restrict__ scratch, unsigned long long* counters,
-                                                              KeySink ks) {
+                                                              KeySink ks, const __grid_constant__ CUtensorMap tmap, int use_tma) {
   using T = TL<ND, SHAPE>;
   constexpr int SFM = T::SFM;
-  extern __shared__ double smem[];
+  extern __shared__ __align__(128) double smem_a[];
+  double* smem = smem_a;
   double* sF = smem;
+  __shared__ __align__(8) unsigned long long mbar;
   const int tid = threadIdx.x;
   const long long tile = tile0 + blockIdx.x;
   const long long kbase = tile * T::CPT;
@@ -607,33 +629,55 @@ __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F
     c0[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) : 1;
     org[d] = d < ND ? c0[d] + SFM - 1 : 1;
   }
-  for (int i0 = 0; i0 < 6 * T::FN; i0 += 4 * NTA) {
-    double v[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int i = i0 + u * NTA + tid;
-      v[u] = 0.0;
-      if (i < 6 * T::FN) {
-        const int comp = i / T::FN, r = i - comp * T::FN;
-        const int fx = r % T::FX, fy = (r / T::FX) % T::FY, fz = r / (T::FX * T::FY);
-        const int X = org[0] + fx, Y = org[1] + fy, Z = org[2] + fz;
-        const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
-                        Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
-        if (in) v[u] = __ldg(F.f[comp] + g.idx(X, Y, Z));
+  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&mbar);
+  if (use_tma) {
+    // E,B of the tile + gather halo: ONE bulk tensor copy (TMA) of the box [FZ][6 components][FY][FX] out of the
+    // nine-array field allocation; cells outside the allocation arrive as zeros
+    if (tid == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(1) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0) {
+      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(sF);
+      const int x0 = org[0] + g.ngd[0] - 1, x1 = ND >= 2 ? org[1] + g.ngd[1] - 1 : 0, x2 = ND >= 3 ? org[2] + g.ngd[2] - 1 : 0;
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)(6 * T::FN * sizeof(double))) : "memory");
+      if (ND == 3)
+        asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];"
+                     ::"r"(dst), "l"((unsigned long long)&tmap), "r"(x0), "r"(x1), "r"(EB_ZCOMP ? 0 : x2), "r"(EB_ZCOMP ? x2 : 0), "r"(bar) : "memory");
+      else
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                     ::"r"(dst), "l"((unsigned long long)&tmap), "r"(x0), "r"(x1), "r"(0), "r"(bar) : "memory");
+    }
+  } else {
+    for (int i0 = 0; i0 < 6 * T::FN; i0 += 4 * NTA) {
+      double v[4];
+  #pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * NTA + tid;
+        v[u] = 0.0;
+        if (i < 6 * T::FN) {
+          const int fx = i % T::FX, fy = (i / T::FX) % T::FY;
+          const int comp = EB_ZCOMP ? (i / T::FCS) % 6 : i / T::FN, fz = EB_ZCOMP ? i / T::FZS : (i / T::FCS) % T::FZ;
+          const int X = org[0] + fx, Y = org[1] + fy, Z = org[2] + fz;
+          const bool in = X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0] && Y >= 1 - g.ngd[1] && Y <= g.n[1] + g.ngd[1] &&
+                          Z >= 1 - g.ngd[2] && Z <= g.n[2] + g.ngd[2];
+          if (in) v[u] = __ldg(F.f[comp] + g.idx(X, Y, Z));
+        }
+      }
+  #pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int i = i0 + u * NTA + tid;
+        if (i < 6 * T::FN) sF[i] = v[u];
       }
     }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int i = i0 + u * NTA + tid;
-      if (i < 6 * T::FN) sF[i] = v[u];
-    }
+    __syncthreads();
   }
-  __syncthreads();
   // warp-uniform loop over the tile's particles; the next particle is in flight while the current
   // one is pushed.  The 64 B records of a warp are transposed through shared memory (16 B units,
   // XOR-swizzled) so that the warp writes its 2 KB block of the scratch with full-line stores.
   const int lane = tid & 31, warp = tid >> 5;
-  double2* stage = reinterpret_cast<double2*>(smem + 6 * T::FN) + warp * 128;
+  double2* stage = reinterpret_cast<double2*>(smem + 6 * T::FN) + warp * (EB_STAGE_HALF ? 64 : 128);
   double nxt[7];
   uint32_t q0 = pb + warp * 32;
   uint32_t s2 = 0;           // GATHER: slot of the particle after next
@@ -641,6 +685,17 @@ __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F
     if (q0 + lane < pe) load_particle_g<ND>(a, side, __ldg(src + q0 + lane), n_main, nxt);
     if (q0 + lane + NTA < pe) s2 = __ldg(src + q0 + lane + NTA);
   } else if (q0 + lane < pe) load_particle<ND>(a, (long long)(q0 + lane), nxt);
+  if (use_tma) {      // the first particles are already in flight: now wait for the tile
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}" ::"r"(bar), "r"(0) : "memory");
+  }
   for (; q0 < pe; q0 += NTA) {
     const uint32_t q = q0 + lane;
     const bool act = q < pe;
@@ -652,25 +707,46 @@ __global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F
       else load_particle<ND>(a, (long long)(q + NTA), nxt);
     }
     if (GATHER && q + 2 * NTA < pe) s2 = __ldg(src + q + 2 * NTA);
+    double rec[8];
     if (act) {
-      double rec[8];
       int pack;
       rec[6] = 0.0;
       push_one<ND, SHAPE, GATHER>(p, in, o, (long long)q, c0, sF, counters, rec, pack, &g, &ks);
       rec[7] = __longlong_as_double((long long)pack);
+    }
+    if (p.zero_current) continue;
+    double2* out = reinterpret_cast<double2*>(scratch + (size_t)(q0 - base) * 8);
+    const uint32_t nrec = pe - q0 < 32u ? pe - q0 : 32u;
+#if EB_STAGE_HALF
+    // 16 records (1 KB) per round: the staging area stays at 1 KB per warp, which keeps four CTAs within the
+    // 196 KB shared-memory carve-out (60 KB of L1 left for the stack and the particle loads)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      if (act && (lane >> 4) == h) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) stage[(lane & 15) * 4 + (k ^ ((lane >> 1) & 3))] = make_double2(rec[2 * k], rec[2 * k + 1]);
+      }
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int u = j * 32 + lane, r = u >> 2;
+        if ((uint32_t)(h * 16 + r) < nrec) out[h * 64 + u] = stage[r * 4 + ((u & 3) ^ ((r >> 1) & 3))];
+      }
+      __syncwarp();
+    }
+#else
+    if (act) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) stage[lane * 4 + (k ^ ((lane >> 1) & 3))] = make_double2(rec[2 * k], rec[2 * k + 1]);
     }
-    if (p.zero_current) continue;
     __syncwarp();
-    double2* out = reinterpret_cast<double2*>(scratch + (size_t)(q0 - base) * 8);
-    const uint32_t nrec = pe - q0 < 32u ? pe - q0 : 32u;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int u = j * 32 + lane, r = u >> 2;
       if ((uint32_t)r < nrec) out[u] = stage[r * 4 + ((u & 3) ^ ((r >> 1) & 3))];
     }
     __syncwarp();
+#endif
   }
 }
 
@@ -931,6 +1007,52 @@ void keysink_fill(void* dst, const BcP3& bc, uint32_t* key, uint32_t* count, uin
   *(KeySink*)dst = ks;
 }
 
+// One tensor map over E,B as a fp64 tensor with the dimensions (x, y, component, z) -- the six arrays are
+// consecutive in the field allocation -- box = the tile's gather region in the kernel's shared layout.  Needs an even x extent (16-byte strides); else, or when the
+// driver lacks the encoder, the kernel stages the tile with plain loads.
+static void ensure_tmap(eb200_ctx* c) {
+  const long long sig[6] = {(long long)(uintptr_t)c->fbase, c->g.n[0], c->g.n[1], c->g.n[2], c->shape, c->ndims};
+  if (c->tmap_valid && std::equal(sig, sig + 6, c->tmap_sig)) return;
+  std::copy(sig, sig + 6, c->tmap_sig);
+  c->tmap_valid = true; c->tmap_ok = false;
+  if (!c->use_tma || c->ndims < 2 || c->shape == SHAPE_BSPLINE3) return;
+  const int nd = c->ndims;
+  const cuuint64_t ex = (cuuint64_t)(c->g.n[0] + 2 * c->g.ngd[0]), ey = (cuuint64_t)(c->g.n[1] + 2 * c->g.ngd[1]),
+                   ez = (cuuint64_t)(nd == 3 ? c->g.n[2] + 2 * c->g.ngd[2] : 1);
+  if ((c->shape == 0 ? TL<3, 0>::FX : TL<3, 1>::FX) % 2 != 0 || (c->shape == 0 ? TL<2, 0>::FX : TL<2, 1>::FX) % 2 != 0) return;
+  if (ex % 2 != 0 || ((uintptr_t)c->fbase & 15) != 0 || (c->g.total * sizeof(double)) % 16 != 0) return;
+  typedef CUresult (*Encode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                             const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                             CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qr;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn ||
+      qr != cudaDriverEntryPointSuccess) { cudaGetLastError(); return; }
+  cuuint32_t box3[4], box2[3];
+  if (c->shape == 0) { box3[0] = TL<3, 0>::FX; box3[1] = TL<3, 0>::FY; box3[2] = TL<3, 0>::FZ; box2[0] = TL<2, 0>::FX; box2[1] = TL<2, 0>::FY; }
+  else { box3[0] = TL<3, 1>::FX; box3[1] = TL<3, 1>::FY; box3[2] = TL<3, 1>::FZ; box2[0] = TL<2, 1>::FX; box2[1] = TL<2, 1>::FY; }
+  box2[2] = 6;
+  if (EB_ZCOMP) { box3[3] = box3[2]; box3[2] = 6; }     // 3D tensor order: x, y, component, z
+  else box3[3] = 6;
+  const cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r;
+  if (nd == 3) {
+    const cuuint64_t dims[4] = {ex, ey, EB_ZCOMP ? 6 : ez, EB_ZCOMP ? ez : 6};
+    const cuuint64_t strides[3] = {ex * 8, EB_ZCOMP ? (cuuint64_t)c->g.total * 8 : ex * ey * 8,
+                                   EB_ZCOMP ? ex * ey * 8 : (cuuint64_t)c->g.total * 8};
+    r = ((Encode)fn)((CUtensorMap*)c->tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, c->fbase, dims, strides, box3, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else {
+    const cuuint64_t dims[3] = {ex, ey, 6};
+    const cuuint64_t strides[2] = {ex * 8, (cuuint64_t)c->g.total * 8};
+    r = ((Encode)fn)((CUtensorMap*)c->tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, c->fbase, dims, strides, box2, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  c->tmap_ok = r == CUDA_SUCCESS;
+}
+
 int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* handled, const void* keysink) {
   *handled = false;
   KeySink ks;
@@ -955,6 +1077,9 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
   a.w = sp.a[6]; o.w = sp.base[6] + off_new; side.w = sp.far ? sp.far + (size_t)6 * sp.far_cap : nullptr;
   const uint32_t n_main = gather ? (uint32_t)sp.n_old : 0u;
   ks.key = sp.key_base + off_new;
+  ensure_tmap(c);
+  const CUtensorMap tmap = *(const CUtensorMap*)c->tmap;
+  const int use_tma = c->tmap_ok ? 1 : 0;
   const long long ntiles = (long long)c->g.ntile[0] * c->g.ntile[1] * c->g.ntile[2];
   const uint32_t* ts = sp.h_tile_start;      // ntiles + 1 entries, valid since the sort's synchronise
   // scratch: 64 B per particle of a slab of tiles
@@ -999,13 +1124,13 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
     if (c->ndims == ND && c->shape == SH) {                                                                \
       auto ka = gather ? k_push_split<ND, SH, true> : k_push_split<ND, SH, false>;                         \
       auto kb = det ? k_deposit_split<ND, SH, true> : k_deposit_split<ND, SH, false>;                      \
-      const size_t sa = sizeof(double) * (6 * TL<ND, SH>::FN + (NTA / 32) * 256);                                               \
+      const size_t sa = sizeof(double) * (6 * TL<ND, SH>::FN + (NTA / 32) * (EB_STAGE_HALF ? 128 : 256)) + EB_SMEM_PAD;                                               \
       const size_t sb = sizeof(double) * (det ? 6 : 3) * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4)   /* >= sub-tile need */ \
                         + (size_t)RING * 64 * (TL<ND, SH>::CPT / SUB) + 16;                                      \
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
       { ScopedPhase pa(c, "push_A");                                                                       \
-        ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks); } \
+        ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks, tmap, use_tma); } \
       if (!p.zero_current) { ScopedPhase pb(c, "push_B");                                                  \
         kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch, c->det_tiles); \
         if (det) {                                                                                         \
