@@ -284,7 +284,7 @@ def run_ours(args):
     full_host = n_part * 56 * 1.04 < host_budget
     gen_threads = max(1, host_cores() // max(1, local_world))
     if full_host:
-        host_all = np.empty((n_part + (n_part // 64 if world > 1 else 0), 7))   # room for migrated-in particles
+        host_all = sim.ctx.host_empty((n_part + (n_part // 64 if world > 1 else 0), 7))   # room for migrated-in particles
         host = host_all[:n_part]
         fill_particles(host, sim, args.seed, gen_threads)
         t_gen = time.perf_counter() - t_setup
@@ -292,7 +292,7 @@ def run_ours(args):
     else:
         per_plane = c * c * PPC
         planes = max(1, min(c, int(host_budget / (per_plane * 56 * (1 + 1 / 64)))))
-        host_all = np.empty((planes * per_plane + planes * per_plane // 64, 7))
+        host_all = sim.ctx.host_empty((planes * per_plane + planes * per_plane // 64, 7))
         host = host_all[:planes * per_plane]
         t_gen = 0.0
         for k0 in range(0, c, planes):
@@ -363,9 +363,22 @@ def run_ours(args):
         field_line = {"cell_updates_per_s": 4 * cells * args.steps / (fields_ms * 1e-3),
                       "achieved_gbs": fb / (fields_ms * 1e-3) / 1e9,
                       "frac_of_hbm": fb / (fields_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
-    sim_d, sim_gml = tuple(sim.d), tuple(sim.grid_min_local)
+    sim_d, sim_gml, sim_ng = tuple(sim.d), tuple(sim.grid_min_local), sim.ctx.ng
+    pinned_host = bool(getattr(sim.ctx, "pinned_host", False))
     sim.ctx.close()
     del sim
+
+    def sim_host_empty(shape):
+        """page-locked float64 array (no context needed), ordinary memory if that fails"""
+        import ctypes
+        n = int(np.prod(shape))
+        p = ctypes.c_void_p()
+        if not pinned_host or abi.host_alloc(ctypes.byref(p), n * 8) != 0 or not p.value:
+            return np.empty(shape)
+        buf = (ctypes.c_double * n).from_address(p.value)
+        import weakref
+        weakref.finalize(buf, abi.host_free, p.value)
+        return np.frombuffer(buf, dtype=np.float64).reshape(shape)
 
     # e2e: same metric through the C ABI from host buffers (upload, K steps, download)
     e2e = None
@@ -383,6 +396,14 @@ def run_ours(args):
             e2e_note = (f"host memory holds {planes} of the {c} z planes per rank: this leg runs "
                         f"{c}x{c}x{planes} cells per GPU (the device-timed value is on the full {c}^3)")
         nccl_id2 = fresh_nccl_id()
+        # host-side field buffers of the e2e leg (page-locked like the particle buffer): six zero input
+        # arrays, nine output arrays
+        shp_e2e = tuple(reversed([n + 2 * sim_ng for n in (cells_e2e[0], cells_e2e[1], cells_e2e[2] // world)]))
+        fzero = sim_host_empty(shp_e2e)
+        fzero[...] = 0.0
+        fout = {k: sim_host_empty(shp_e2e) for k in ("ex", "ey", "ez", "bx", "by", "bz", "jx", "jy", "jz")}
+        for a in fout.values():
+            a[...] = 0.0          # touch the pages before the clock starts
         barrier(); torch.cuda.synchronize()
         t0 = time.perf_counter()
         sim2 = make_sim(abi, cells_e2e, rank, world, nccl_id2, device=local)
@@ -392,7 +413,6 @@ def run_ours(args):
             sim2.ctx.set_option(k, v)
         sim2.ctx.set_option("reserve", f"0:{n_e2e + n_e2e // 64 if world > 1 else n_e2e}")
         shp = sim2.ctx._np_shape()
-        fzero = np.zeros(shp)
         sim2.ctx.upload_fields(ex=fzero, ey=fzero, ez=fzero, bx=fzero, by=fzero, bz=fzero)
         t1 = time.perf_counter()
         sim2.ctx.upload_particles(0, host)
@@ -406,7 +426,7 @@ def run_ours(args):
         sim2.ctx.sync()
         t3 = time.perf_counter()
         got = sim2.ctx.download_particles(0, out=host_all)
-        fld = sim2.ctx.download_fields()
+        fld = sim2.ctx.download_fields(out=fout)
         sim2.ctx.sync()
         t4 = time.perf_counter()
         t_e2e = max_over_ranks(t4 - t0)
@@ -418,8 +438,9 @@ def run_ours(args):
                "seconds_split": {"create_alloc_upload_fields": t1 - t0, "upload_particles": t2 - t1,
                                  "first_step": t2a - t2, "other_steps": t3 - t2a, "download": t4 - t3},
                "h2d_gbs": host.nbytes / (t2 - t1) / 1e9, "d2h_gbs": (got.nbytes + 9 * fzero.nbytes) / (t4 - t3) / 1e9,
-               "what": "eb200_create + upload_fields + upload_particles (pageable host numpy buffers, staged "
-                       "through the library's pinned ring) + K full steps + download_particles + download_fields "
+               "host_buffers": "page-locked (eb200_host_alloc)" if pinned_host else "pageable (staged through the library's pinned ring)",
+               "what": "eb200_create + upload_fields + upload_particles from host buffers + K full steps + "
+                       "download_particles + download_fields into host buffers "
                        "+ sync, wall clock; the state lives on the device between steps, so the copies are "
                        "amortised over K steps" + ("; " + e2e_note if e2e_note else "")}
         del fld

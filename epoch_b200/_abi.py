@@ -21,6 +21,8 @@ SIGNATURES = {
     "create": (i32, [C.POINTER(c_ctx_p), i32, i32, i32, i32, i32, pi32, pi32, C.c_void_p]),
     "nccl_unique_id": (i32, [C.c_void_p]),
     "destroy": (i32, [c_ctx_p]),
+    "host_alloc": (i32, [C.POINTER(C.c_void_p), C.c_int64]),
+    "host_free": (i32, [C.c_void_p]),
     "set_grid": (i32, [c_ctx_p, pi32, pi32, pi32, pf64, pf64, pf64, pf64, pf64, pf64, i32]),
     "set_time": (i32, [c_ctx_p, f64, f64, i32]),
     "set_field_bcs": (i32, [c_ctx_p, pi32]),

@@ -143,6 +143,21 @@ class PicContext:
         self.nspecies = max(self.nspecies, isp + 1)
 
     # -- particles (partlist wire format: pos(ndims), p(3), weight) ---------
+    def host_empty(self, shape):
+        """float64 array in page-locked host memory (eb200_host_alloc): uploads and downloads of such
+        buffers skip the library's staging ring.  Falls back to ordinary memory when the allocation fails."""
+        n = int(np.prod(shape))
+        p = C.c_void_p()
+        if n == 0 or self.abi.host_alloc(C.byref(p), n * 8) != 0 or not p.value:
+            return np.empty(shape, dtype=np.float64)
+        buf = (C.c_double * n).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=np.float64).reshape(shape)
+        import weakref
+        weakref.finalize(buf, self.abi.host_free, p.value)
+        arr.flags.writeable = True
+        self.pinned_host = True
+        return arr
+
     def upload_particles(self, isp, packed, append=False):
         packed = np.ascontiguousarray(packed, dtype=np.float64).reshape(-1, self.nvar)
         fn = self.abi.append_particles if append else self.abi.upload_particles
@@ -181,12 +196,14 @@ class PicContext:
                 ptrs.append(a.ctypes.data_as(C.c_void_p))
         self._ck(self.abi.upload_fields(self._ctx, *ptrs))
 
-    def download_fields(self, names=FIELD_NAMES):
-        out = {}
+    def download_fields(self, names=FIELD_NAMES, out=None):
+        """`out`: dict of preallocated arrays of the field shape to fill (e.g. from host_empty)"""
+        out = dict(out) if out else {}
         ptrs = []
         for name in FIELD_NAMES:
             if name in names:
-                out[name] = np.empty(self._np_shape(), dtype=np.float64)
+                if name not in out:
+                    out[name] = np.empty(self._np_shape(), dtype=np.float64)
                 ptrs.append(out[name].ctypes.data_as(C.c_void_p))
             else:
                 ptrs.append(None)

@@ -117,6 +117,19 @@ int32_t eb200_nccl_unique_id(void* out128) {
   return nccl_unique_id(out128);
 }
 
+int32_t eb200_host_alloc(void** out, int64_t bytes) {
+  if (!out || bytes < 0) return EB200_E_ARG;
+  *out = nullptr;
+  if (bytes == 0) return 0;
+  const cudaError_t e = cudaHostAlloc(out, (size_t)bytes, cudaHostAllocPortable);
+  if (e != cudaSuccess) { cudaGetLastError(); *out = nullptr; return e == cudaErrorMemoryAllocation ? EB200_E_NOMEM : EB200_E_CUDA; }
+  return 0;
+}
+int32_t eb200_host_free(void* p) {
+  if (p && cudaFreeHost(p) != cudaSuccess) { cudaGetLastError(); return EB200_E_CUDA; }
+  return 0;
+}
+
 int32_t eb200_destroy(eb200_ctx* c) {
   if (!c) return 0;
   cudaSetDevice(c->device);
@@ -508,6 +521,11 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
   }
   if (k == "deposit_scratch") { c->rec_scratch_max = atoll(value) < 1024 ? 1024 : atoll(value); return 0; }
   if (k == "host_threads") { c->host_threads = atoi(value); return 0; }
+  if (k == "pin_bytes") {      // chunk size of the host transfers (before the first transfer)
+    if (c->pin[0]) return fail(c, EB200_E_STATE, "pin_bytes: the staging ring is already allocated");
+    c->pin_bytes = (size_t)std::max<long long>(atoll(value), 1024);
+    return 0;
+  }
   if (k == "mig_capacity") { c->mig_min_particles = atoll(value); return 0; }
   return fail(c, EB200_E_ARG, "unknown option " + k);
 }

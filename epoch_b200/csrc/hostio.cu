@@ -57,6 +57,13 @@ static int32_t pin_acquire(eb200_ctx* c, int& b) {
   return 0;
 }
 
+// page-locked (eb200_host_alloc / cudaHostAlloc / cudaHostRegister) buffers need no staging
+static bool is_pinned(const void* host) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, host) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+
 // host -> device.  The transfer is cut into chunks of whole granules (<= one pinned buffer);
 // dst(o, m) names the device address chunk [o, o + m) is copied to and after(o, m) may enqueue
 // a kernel that consumes it (both stream-ordered, so one device staging area can be reused).
@@ -66,6 +73,14 @@ int32_t staged_h2d(eb200_ctx* c, const void* host, size_t bytes, size_t granule,
   EB_TRY(ensure_pinned(c));
   const size_t chunk = std::max<size_t>(1, c->pin_bytes / granule) * granule;
   if (chunk > c->pin_bytes) return fail(c, EB200_E_ARG, "transfer granule larger than the pinned staging buffer");
+  if (is_pinned(host)) {          // the copy engine reads the caller's buffer directly
+    for (size_t done = 0; done < bytes; done += chunk) {
+      const size_t m = std::min(chunk, bytes - done);
+      EB_CUDA(c, cudaMemcpyAsync(dst(done, m), (const char*)host + done, m, cudaMemcpyHostToDevice, c->stream));
+      if (after) EB_TRY(after(done, m));
+    }
+    return 0;
+  }
   for (size_t done = 0; done < bytes; done += chunk) {
     const size_t m = std::min(chunk, bytes - done);
     int b;
@@ -88,6 +103,15 @@ int32_t staged_d2h(eb200_ctx* c, void* host, size_t bytes, size_t granule,
   const size_t chunk = std::max<size_t>(1, c->pin_bytes / granule) * granule;
   if (chunk > c->pin_bytes) return fail(c, EB200_E_ARG, "transfer granule larger than the pinned staging buffer");
   const size_t nchunk = (bytes + chunk - 1) / chunk;
+  if (is_pinned(host)) {          // ... and writes it directly
+    for (size_t i = 0; i < nchunk; ++i) {
+      const size_t o = i * chunk, m = std::min(chunk, bytes - o);
+      const void* d = src(o, m);
+      if (!d) return EB200_E_CUDA;
+      EB_CUDA(c, cudaMemcpyAsync((char*)host + o, d, m, cudaMemcpyDeviceToHost, c->stream));
+    }
+    return 0;
+  }
   constexpr int NP = eb200_ctx::NPIN;
   int slot[NP];
   size_t issued = 0;

@@ -17,6 +17,15 @@ MODULE epoch_b200_iface
       INTEGER(C_INT32_T), INTENT(IN) :: nprocdir(3), coords(3)
       TYPE(C_PTR), VALUE :: nccl_id
     END FUNCTION
+    INTEGER(C_INT32_T) FUNCTION eb200_host_alloc(out, bytes) BIND(C, NAME='eb200_host_alloc')
+      IMPORT :: C_INT32_T, C_INT64_T, C_PTR
+      TYPE(C_PTR), INTENT(OUT) :: out
+      INTEGER(C_INT64_T), VALUE :: bytes
+    END FUNCTION eb200_host_alloc
+    INTEGER(C_INT32_T) FUNCTION eb200_host_free(p) BIND(C, NAME='eb200_host_free')
+      IMPORT :: C_INT32_T, C_PTR
+      TYPE(C_PTR), VALUE :: p
+    END FUNCTION eb200_host_free
     INTEGER(C_INT32_T) FUNCTION eb200_nccl_unique_id(out128) BIND(C, NAME='eb200_nccl_unique_id')
       IMPORT
       CHARACTER(KIND=C_CHAR), INTENT(OUT) :: out128(128)

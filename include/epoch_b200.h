@@ -84,6 +84,12 @@ int32_t EB200_NAME(create)(EB200_CTX** out, int32_t ndims, int32_t shape,
                            const void* nccl_unique_id);
 int32_t EB200_NAME(nccl_unique_id)(void* out128);
 int32_t EB200_NAME(destroy)(EB200_CTX*);
+/* Page-locked host memory for the caller's particle / field buffers (in Fortran: C_F_POINTER on the result
+ * instead of ALLOCATE, cf. the packed buffers of partlist.F90:808-862).  Uploads and downloads recognise such
+ * buffers and let the copy engine read / write them directly at the PCIe rate; any other (pageable) buffer is
+ * staged through the library's own pinned ring.  No context needed. */
+int32_t EB200_NAME(host_alloc)(void** out, int64_t bytes);
+int32_t EB200_NAME(host_free)(void* p);
 
 /* ---- grid / time -----------------------------------------------------------
  * Mirrors the scalars of shared_data.F90:453,508-523 set by setup_grid

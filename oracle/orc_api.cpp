@@ -4,6 +4,7 @@
 // multi-rank tests exchange halos themselves through orc_field_ptr).
 #define EB200_NAME(x) orc_##x
 #define EB200_CTX orc_ctx
+#include <cstdlib>
 #include "../include/epoch_b200.h"
 #include "orc_state.hpp"
 #include <algorithm>
@@ -44,6 +45,12 @@ int32_t orc_create(orc_ctx** out, int32_t ndims, int32_t shape, int32_t, int32_t
   *out = c;
   return 0;
 }
+int32_t orc_host_alloc(void** out, int64_t bytes) {
+  if (!out || bytes < 0) return EB200_E_ARG;
+  *out = bytes ? std::malloc((size_t)bytes) : nullptr;
+  return (bytes && !*out) ? EB200_E_NOMEM : 0;
+}
+int32_t orc_host_free(void* p) { std::free(p); return 0; }
 int32_t orc_nccl_unique_id(void* out128) { if (out128) std::memset(out128, 0, 128); return 0; }
 int32_t orc_destroy(orc_ctx* c) { delete c; return 0; }
 

@@ -201,6 +201,20 @@ def test_upload_download_roundtrip(product_abi):
     s.ctx.upload_particles(0, P[10:], append=True)
     A, B = match_particles(s.ctx.download_particles(0), P)
     assert np.array_equal(A, B)
+    # page-locked host buffers (eb200_host_alloc) take the direct path past the staging ring; several chunks
+    s = make_plasma(product_abi, 3, "triangle", [6, 5, 4], seed=1, ppc=7, options={"pin_bytes": 4096})
+    big = np.random.default_rng(3).normal(size=(5000, 7))
+    hp = s.ctx.host_empty(big.shape)
+    assert getattr(s.ctx, "pinned_host", False)
+    hp[...] = big
+    s.ctx.upload_particles(1, hp)
+    out = s.ctx.host_empty(big.shape)
+    got = s.ctx.download_particles(1, out=out)
+    A, B = match_particles(got, big)
+    assert np.array_equal(A, B)
+    fo = s.ctx.download_fields(FIELDS6, out={k: s.ctx.host_empty(s.ctx._np_shape()) for k in FIELDS6})
+    for k in FIELDS6:
+        assert np.array_equal(fo[k], s.init_fields[k])
 
 
 def test_error_behaviour(product_abi):
