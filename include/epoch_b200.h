@@ -268,8 +268,15 @@ int32_t EB200_NAME(redistribute)(EB200_CTX*, const int32_t* old_cell_min, const 
 #define EB200_DF_SPECIES_CURRENT 9
 #define EB200_DF_AVERAGE_MOMENTUM 10
 int32_t EB200_NAME(calc_derived)(EB200_CTX*, int32_t kind, int32_t ispecies, int32_t direction, double* out);
-/* options: "deterministic_deposit"="0|1", "push_kernel"="auto|baseline|tiled",
- * "sort_every"="<n>" */
+/* options (key, value as strings):
+ *   "deterministic_deposit" "0|1"   run-to-run bitwise reproducible currents (tiled kernels: 2D/3D, tophat/triangle)
+ *   "push_kernel"   "auto|baseline|tiled"
+ *   "defer_window"  "auto|<slots>"  head room of the deferred permute (0: permute inside the sort); takes effect
+ *                                   when the particle arrays are next allocated ("reserve", upload)
+ *   "reserve"       "<species>:<particles>"  allocate a species' storage once
+ *   "deposit_scratch" "<particles>" particles per push/deposit launch (64 B of scratch each)
+ *   "fuse_keys" "0|1", "tma" "0|1", "timers" "0|1", "host_threads" "<n>", "pin_bytes" "<bytes>",
+ *   "mig_capacity" "<particles>", "capture_charge_reference" "1" */
 int32_t EB200_NAME(set_option)(EB200_CTX*, const char* key, const char* value);
 int32_t EB200_NAME(sync)(EB200_CTX*);
 /* milliseconds of device time spent in the named phase since the last call with
