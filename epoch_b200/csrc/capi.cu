@@ -201,7 +201,8 @@ int32_t eb200_set_grid(eb200_ctx* c, const int32_t n_local[3], const int32_t n_g
 int32_t eb200_set_time(eb200_ctx* c, double dt, double time, int32_t step) {
   CHECK_CTX(c);
   if (!(dt > 0)) return fail(c, EB200_E_ARG, "dt must be > 0");
-  if (dt != c->dt) for (SpeciesD& sp : c->species) sp.sorted = false;   // sort keys depend on dt
+  // (the sort keys depend on dt: push_particles re-sorts a species whose keys were made for another dt; the
+  //  dt/2 excursion of the initial bfield_final_bcs, epoch3d.F90:153-159, costs nothing)
   c->dt = dt; c->time = time; c->step = step;
   return 0;
 }

@@ -84,7 +84,8 @@ struct SpeciesD {
   uint32_t* d_tile_start = nullptr; // first particle of every tile (+1 entry), device and pinned host copy
   uint32_t* h_tile_start = nullptr;
   long long tile_cap = 0;
-  bool sorted = false;      // keys/cell_start valid for the current positions
+  bool sorted = false;      // keys/cell_start valid for the current positions ...
+  double sort_dt = 0.0;     // ... and for this time step (the key is the cell after the half drift)
 };
 
 struct Laser {

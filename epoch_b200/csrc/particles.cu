@@ -39,7 +39,7 @@ static int32_t regrow(eb200_ctx* c, T*& base, const T* view, long long old_n, lo
 int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need, bool exact) {
   if (sp.base[6] && need + sp.win + 2 * sp.gap <= sp.cap) return 0;
   EB_TRY(settle_species(c, sp));
-  const bool tiled = c->ndims >= 2 && c->shape != SHAPE_BSPLINE3 && c->push_kernel != 1;
+  const bool tiled = c->ndims >= 2 && c->push_kernel != 1;
   long long win = !tiled ? 0 : (c->defer_window >= 0 ? c->defer_window : std::max<long long>(need / 8, 1 << 16));
   const long long gap = 0;      // (slots kept free below the low state: none needed, arrivals are appended)
   const long long body = exact ? std::max<long long>(need, 1024) : std::max<long long>(need + need / 32 + 1024, 4096);
@@ -441,7 +441,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
     EB_TRY(settle_species(c, sp));
   }
   ScopedPhase ph(c, "sort");
-  if (n_slots == 0) { sp.n = 0; sp.sorted = true; return 0; }
+  if (n_slots == 0) { sp.n = 0; sp.sorted = true; sp.sort_dt = c->dt; return 0; }
   if (n_slots >= 0xFFFFFFF0LL) return fail(c, EB200_E_UNSUPPORTED, "more than 2^32 particles per species per GPU");
   EB_TRY(ensure_cells(c, sp));
   const uint32_t nbucket = (uint32_t)(c->g.ncell_ext + 1);   // last = invalid
@@ -572,6 +572,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
     }
   }
   sp.sorted = true;
+  sp.sort_dt = c->dt;
   EB_CUDA(c, cudaGetLastError());
   return 0;
 }
@@ -838,7 +839,7 @@ int32_t push_particles(eb200_ctx* c) {
     SpeciesD& sp = c->species[is];
     if (!sp.defined) continue;
     if (sp.immobile || sp.species_type == 1) { EB_TRY(settle_species(c, sp)); continue; }
-    if (!sp.sorted) EB_TRY(sort_species(c, sp, sp.n));
+    if (!sp.sorted || sp.sort_dt != c->dt) EB_TRY(sort_species(c, sp, sp.n));
     if (sp.n == 0) { sp.deferred = false; continue; }
     PushP p = make_push_params(c, sp, sp.n);
     bool handled = false, fused_keys = false;
@@ -871,7 +872,7 @@ int32_t push_particles(eb200_ctx* c) {
       }
       if (!handled) {
         if (c->deterministic)
-          return fail(c, EB200_E_UNSUPPORTED, "deterministic_deposit needs the tiled kernels (2D/3D, tophat or triangle shape)");
+          return fail(c, EB200_E_UNSUPPORTED, "deterministic_deposit needs the tiled kernels (2D/3D)");
         EB_TRY(settle_species(c, sp));
         EB_TRY(launch_push_baseline(c, sp, p));
       }
@@ -893,7 +894,7 @@ int32_t push_particles(eb200_ctx* c) {
 #define LK(ND, SH)                                                                               \
           if (c->ndims == ND && c->shape == SH)                                                  \
             k_keys<ND, SH><<<ga, 256, 0, c->stream>>>(c->g, pk2, bc, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.key, c->cell_count, nbucket, n_counted);
-          LK(2, 0) LK(2, 1) LK(3, 0) LK(3, 1)
+          LK(2, 0) LK(2, 1) LK(2, 2) LK(3, 0) LK(3, 1) LK(3, 2)
 #undef LK
           c->launches++;
         }

@@ -602,7 +602,7 @@ constexpr int RING = EB_RING;    // record slots per thread of the deposit kerne
 // GATHER (deferred permute, particles.cu): the particle of sorted index q is read from slot src[q] of the
 // arrays `a` (the pre-sort order) and stored to slot q of `o` (the other state of the same allocations)
 template <int ND, int SHAPE, bool GATHER>
-__global__ void __launch_bounds__(NTA, EB_MINB_A) k_push_split(GridP g, FieldP F, PushP p, PArr a, PArr o, PArr side,
+__global__ void __launch_bounds__(NTA, SHAPE == SHAPE_BSPLINE3 ? 2 : EB_MINB_A) k_push_split(GridP g, FieldP F, PushP p, PArr a, PArr o, PArr side,
                                                               const uint32_t* __restrict__ src, uint32_t n_main,
                                                               const uint32_t* __restrict__ cell_start, long long tile0,
                                                               double* __restrict__ scratch, unsigned long long* counters,
@@ -814,17 +814,13 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   }
 
   // ---- thread per cell: all components of the cell's box in registers; the next record is
-  //      fetched while the current one is deposited ----
+  //      fetched while the current one is deposited.  ONEC (3D bspline3: 3 x 100 accumulators):
+  //      one pass over the cell's records per component instead ----
+  constexpr bool ONEC = 3 * NA > 128;
   const int lc = sub * NTB + tid;
   const uint32_t my_b = cell_start[kbase + lc], my_e = cell_start[kbase + lc + 1];
   int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
   l[SA] -= sub * TS;
-  double acc[3 * NA];
-#pragma unroll
-  for (int i = 0; i < 3 * NA; ++i) acc[i] = 0.0;
-  // the thread's records stream through a private shared-memory ring filled by cp.async
-  // (RING - 1 records in flight, none of them held in registers)
-  double cur[8];
   const uint32_t ring0 = (uint32_t)__cvta_generic_to_shared(ring) + (uint32_t)tid * 16u;
   auto issue = [&](uint32_t q, int slot) {
     const double* src = scratch + (size_t)(q - base) * 8;
@@ -832,6 +828,14 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
     for (int k = 0; k < 4; ++k)
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ring0 + (uint32_t)((slot * 4 + k) * NTB) * 16u), "l"(src + 2 * k) : "memory");
   };
+#pragma unroll
+  for (int pass = 0; pass < (ONEC ? 3 : 1); ++pass) {
+  double acc[ONEC ? NA : 3 * NA];
+#pragma unroll
+  for (int i = 0; i < (ONEC ? NA : 3 * NA); ++i) acc[i] = 0.0;
+  // the thread's records stream through a private shared-memory ring filled by cp.async
+  // (RING - 1 records in flight, none of them held in registers)
+  double cur[8];
 #pragma unroll
   for (int s = 0; s < RING - 1; ++s) {
     if (my_b + s < my_e) issue(my_b + s, s);
@@ -849,9 +853,9 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
     if (q + (RING - 1) < my_e) issue(q + (RING - 1), slot == 0 ? RING - 1 : slot - 1);
     asm volatile("cp.async.commit_group;" ::: "memory");
     slot = slot == RING - 1 ? 0 : slot + 1;
-    deposit_box<ND, SHAPE, true>(p, RecR{cur}, 0, acc);
+    deposit_box<ND, SHAPE, !ONEC>(p, RecR{cur}, pass, acc);
     const int pack = (int)__double_as_longlong(cur[7]);
-    if ((pack & 0xff) != (ND == 3 ? 0x15 : 0x5)) {
+    if (pass == 0 && (pack & 0xff) != (ND == 3 ? 0x15 : 0x5)) {
       const RecG rec{scratch + (size_t)(q - base) * 8};
       const int r = (int)(q - pb);
       if (ND == 2) {
@@ -870,6 +874,7 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
       }
     }
   }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
   // ---- register boxes -> shared J tile: every thread applies the same stencil offset to its own
   //      cell, so the addresses of a step are distinct; steps are separated by barriers ----
@@ -880,9 +885,9 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
     const int off = (l[0] + 1 + dx) + (l[1] + 1 + dy) * JXs + (ND == 3 ? (l[2] + 1 + dz) * JXs * JYs : 0);
     if (ND == 3) {
       // component A: acc[(o[Q] * NW + o[P]) * (NW - 1) + o[A]], P = A + 1, Q = A + 2, o[A] < NW - 1
-      if (dx < NW - 1) sJ[off] += acc[(dz * NW + dy) * (NW - 1) + dx];
-      if (dy < NW - 1) sJ[JNs + off] += acc[NA + (dx * NW + dz) * (NW - 1) + dy];
-      if (dz < NW - 1) sJ[2 * JNs + off] += acc[2 * NA + (dy * NW + dx) * (NW - 1) + dz];
+      if ((!ONEC || pass == 0) && dx < NW - 1) sJ[off] += acc[(dz * NW + dy) * (NW - 1) + dx];
+      if ((!ONEC || pass == 1) && dy < NW - 1) sJ[JNs + off] += acc[(ONEC ? 0 : NA) + (dx * NW + dz) * (NW - 1) + dy];
+      if ((!ONEC || pass == 2) && dz < NW - 1) sJ[2 * JNs + off] += acc[(ONEC ? 0 : 2 * NA) + (dy * NW + dx) * (NW - 1) + dz];
     } else {
       sJ[off] += acc[dy * NW + dx];
       sJ[JNs + off] += acc[NA + dy * NW + dx];
@@ -899,6 +904,7 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
         if (ZPAIR && dz == 0) box_step(dx, dy, 2);
         __syncthreads();
       }
+  }   // pass
   // ---- particles that changed cell ----
   const int nm = sCnt[0] < MCAPB ? sCnt[0] : MCAPB;
   if (ND == 3) {
@@ -1015,11 +1021,12 @@ static void ensure_tmap(eb200_ctx* c) {
   if (c->tmap_valid && std::equal(sig, sig + 6, c->tmap_sig)) return;
   std::copy(sig, sig + 6, c->tmap_sig);
   c->tmap_valid = true; c->tmap_ok = false;
-  if (!c->use_tma || c->ndims < 2 || c->shape == SHAPE_BSPLINE3) return;
+  if (!c->use_tma || c->ndims < 2) return;
   const int nd = c->ndims;
   const cuuint64_t ex = (cuuint64_t)(c->g.n[0] + 2 * c->g.ngd[0]), ey = (cuuint64_t)(c->g.n[1] + 2 * c->g.ngd[1]),
                    ez = (cuuint64_t)(nd == 3 ? c->g.n[2] + 2 * c->g.ngd[2] : 1);
-  if ((c->shape == 0 ? TL<3, 0>::FX : TL<3, 1>::FX) % 2 != 0 || (c->shape == 0 ? TL<2, 0>::FX : TL<2, 1>::FX) % 2 != 0) return;
+  const int fx3[3] = {TL<3, 0>::FX, TL<3, 1>::FX, TL<3, 2>::FX}, fx2[3] = {TL<2, 0>::FX, TL<2, 1>::FX, TL<2, 2>::FX};
+  if (fx3[c->shape] % 2 != 0 || fx2[c->shape] % 2 != 0) return;
   if (ex % 2 != 0 || ((uintptr_t)c->fbase & 15) != 0 || (c->g.total * sizeof(double)) % 16 != 0) return;
   typedef CUresult (*Encode)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -1029,8 +1036,9 @@ static void ensure_tmap(eb200_ctx* c) {
   if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn ||
       qr != cudaDriverEntryPointSuccess) { cudaGetLastError(); return; }
   cuuint32_t box3[4], box2[3];
-  if (c->shape == 0) { box3[0] = TL<3, 0>::FX; box3[1] = TL<3, 0>::FY; box3[2] = TL<3, 0>::FZ; box2[0] = TL<2, 0>::FX; box2[1] = TL<2, 0>::FY; }
-  else { box3[0] = TL<3, 1>::FX; box3[1] = TL<3, 1>::FY; box3[2] = TL<3, 1>::FZ; box2[0] = TL<2, 1>::FX; box2[1] = TL<2, 1>::FY; }
+  const int fy3[3] = {TL<3, 0>::FY, TL<3, 1>::FY, TL<3, 2>::FY}, fz3[3] = {TL<3, 0>::FZ, TL<3, 1>::FZ, TL<3, 2>::FZ};
+  const int fy2[3] = {TL<2, 0>::FY, TL<2, 1>::FY, TL<2, 2>::FY};
+  box3[0] = fx3[c->shape]; box3[1] = fy3[c->shape]; box3[2] = fz3[c->shape]; box2[0] = fx2[c->shape]; box2[1] = fy2[c->shape];
   box2[2] = 6;
   if (EB_ZCOMP) { box3[3] = box3[2]; box3[2] = 6; }     // 3D tensor order: x, y, component, z
   else box3[3] = 6;
@@ -1057,7 +1065,7 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
   *handled = false;
   KeySink ks;
   if (keysink) ks = *(const KeySink*)keysink; else { ks.on = 0; ks.count = nullptr; ks.nbucket = 0; }
-  if (c->ndims < 2 || c->shape == SHAPE_BSPLINE3 || !sp.sorted || !sp.h_tile_start) return 0;
+  if (c->ndims < 2 || !sp.sorted || !sp.h_tile_start) return 0;
   // deferred permute: read the pre-sort order through src, write the sorted order into the other state
   const bool gather = sp.deferred;
   bool fwd = true;
@@ -1098,8 +1106,8 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
   const long long cap = c->rec_scratch_cap < room ? c->rec_scratch_cap : room;
   // deterministic mode: one J tile per deposit CTA (1 GB of them at most per launch)
   const bool det = c->deterministic && !p.zero_current;
-  const size_t tile_doubles = 3 * (size_t)(c->ndims == 3 ? (c->shape == 0 ? TL<3, 0>::JN : TL<3, 1>::JN)
-                                                         : (c->shape == 0 ? TL<2, 0>::JN : TL<2, 1>::JN));   // >= the sub-tile's
+  const int jn3[3] = {TL<3, 0>::JN, TL<3, 1>::JN, TL<3, 2>::JN}, jn2[3] = {TL<2, 0>::JN, TL<2, 1>::JN, TL<2, 2>::JN};
+  const size_t tile_doubles = 3 * (size_t)(c->ndims == 3 ? jn3[c->shape] : jn2[c->shape]);   // >= the sub-tile's
   const long long max_tiles = det ? std::max<long long>(1, (long long)(((size_t)1 << 30) / (tile_doubles * 8 * SUB))) : (1LL << 62);
   if (det && c->det_tiles_cap < (size_t)std::min<long long>(max_tiles, ntiles) * SUB * tile_doubles) {
     if (c->det_tiles) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(c->det_tiles); }
@@ -1149,7 +1157,7 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
           }                                                                                                \
         } }                                                                                                \
     }
-    L(2, 0) L(2, 1) L(3, 0) L(3, 1)
+    L(2, 0) L(2, 1) L(2, 2) L(3, 0) L(3, 1) L(3, 2)
 #undef L
     c->launches += p.zero_current ? 1 : 2;
   }

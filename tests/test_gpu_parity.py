@@ -432,7 +432,8 @@ def test_redistribute_single_rank_identity(product_abi, oracle_abi):
     (3, "triangle", "periodic", [16, 8, 48], 8000, True), (3, "tophat", "periodic", [16, 8, 48], 9000, True),
     (2, "triangle", "periodic", [32, 64], 6000, True), (2, "tophat", "reflect", [32, 64], 7000, True),
     (3, "triangle", "open", [16, 8, 48], 8000, True), (3, "triangle", "periodic", [16, 8, 48], 600, False),
-    (3, "triangle", "periodic", [16, 8, 48], "auto", True), (3, "triangle", "periodic", [16, 8, 48], 0, False)])
+    (3, "triangle", "periodic", [16, 8, 48], "auto", True), (3, "triangle", "periodic", [16, 8, 48], 0, False),
+    (3, "bspline3", "periodic", [16, 8, 48], 9000, True), (2, "bspline3", "open", [32, 64], 7000, True)])
 def test_deferred_permute(product_abi, oracle_abi, ndims, shape, pbc, n, window, expect):
     """The sort leaves its permute to the next push (gather through src, write into the other state of the
     arrays).  A window far smaller than the species forces many launches per step in both directions and,
@@ -460,7 +461,8 @@ def test_deferred_permute(product_abi, oracle_abi, ndims, shape, pbc, n, window,
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("ndims,shape,pbc,window", [(3, "triangle", "periodic", "auto"), (3, "tophat", "reflect", 0),
-                                                    (2, "triangle", "periodic", "auto"), (2, "tophat", "open", 4000)])
+                                                    (2, "triangle", "periodic", "auto"), (2, "tophat", "open", 4000),
+                                                    (3, "bspline3", "periodic", "auto"), (2, "bspline3", "reflect", "auto")])
 def test_deterministic_deposit(product_abi, oracle_abi, ndims, shape, pbc, window):
     """option deterministic_deposit: two runs of the same deck give bitwise identical currents, fields and
     particle arrays (canonical order inside a cell, fixed-point overflow sums, ordered sum of the tile
@@ -484,8 +486,8 @@ def test_deterministic_deposit(product_abi, oracle_abi, ndims, shape, pbc, windo
         assert np.array_equal(a.ctx.download_particles(isp), b.ctx.download_particles(isp))
     compare_fields(a, o, ALL9, tol=1e-10)
     compare_particles(a, o, tol=1e-10)
-    # not on the general kernel
+    # not on the general kernel (1D)
     if ndims == 3:
-        s = make_plasma(product_abi, 3, "bspline3", [8, 8, 8], seed=1, ppc=2, options={"deterministic_deposit": 1})
+        s = make_plasma(product_abi, 1, "triangle", [32], seed=1, ppc=2, options={"deterministic_deposit": 1})
         with pytest.raises(Exception):
             s.step_once()
