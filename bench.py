@@ -51,11 +51,14 @@ def deck_geometry(cells):
     return dx, [c * dx for c in cells]
 
 
+SHAPE = "triangle"      # --shape (tuning / comparison runs; the bench line is quoted on triangle)
+
+
 def make_sim(abi, cells_global, rank=0, nproc=1, nccl_id=None, device=0):
     from epoch_b200.driver import Simulation, SpeciesSpec
     dx, length = deck_geometry(cells_global)
     sp = SpeciesSpec("electron", -Q0, M0, density=DENSITY, temperature=(T_KELVIN,) * 3)
-    return Simulation(3, list(cells_global), [0.0, 0.0, 0.0], length, shape="triangle", species=[sp],
+    return Simulation(3, list(cells_global), [0.0, 0.0, 0.0], length, shape=SHAPE, species=[sp],
                       abi=abi, device=device, rank=rank, nproc=nproc, nprocdir=(1, 1, nproc), nccl_id=nccl_id)
 
 
@@ -201,7 +204,7 @@ def run_reference(args):
 def workload_config(args, n_gpus):
     c = args.cells
     return {"workload": f"epoch3d uniform thermal plasma {c}x{c}x{c * n_gpus} cells x {PPC} ppc electrons, periodic, "
-                        f"triangle shape, fp64 (BASELINE.json configs[2]; {c}^3 per GPU, slabs along z)",
+                        f"{SHAPE} shape, fp64 (BASELINE.json configs[2]; {c}^3 per GPU, slabs along z)",
             "cells_per_gpu": [c, c, c], "ppc": PPC, "particles_per_gpu": c ** 3 * PPC,
             "density_m3": DENSITY, "temperature_keV": 1.0, "dx_over_debye": 0.5, "dt_over_cfl": 0.95,
             "l2_policy": "inputs larger than L2 (particle arrays %.1f GB per GPU)" % (c ** 3 * PPC * 56 / 1e9),
@@ -476,11 +479,14 @@ def main():
     ap.add_argument("--cells", type=int, default=512, help="cells per dimension per GPU")
     ap.add_argument("--cpu-cells", type=int, default=64, help="cells per dimension per CPU process (cpu arm)")
     ap.add_argument("--seed", type=int, default=12345)
+    ap.add_argument("--shape", default="triangle", choices=["tophat", "triangle", "bspline3"])
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--host-gb", type=float, default=None, help="host memory per rank for the particle copy (default: from free memory)")
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (tuning experiments)")
     args = ap.parse_args()
+    global SHAPE
+    SHAPE = args.shape
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
         run_reference(args)
