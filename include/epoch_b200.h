@@ -269,7 +269,7 @@ int32_t EB200_NAME(redistribute)(EB200_CTX*, const int32_t* old_cell_min, const 
 #define EB200_DF_AVERAGE_MOMENTUM 10
 int32_t EB200_NAME(calc_derived)(EB200_CTX*, int32_t kind, int32_t ispecies, int32_t direction, double* out);
 /* options (key, value as strings):
- *   "deterministic_deposit" "0|1"   run-to-run bitwise reproducible currents (tiled kernels: 2D/3D, tophat/triangle)
+ *   "deterministic_deposit" "0|1"   run-to-run bitwise reproducible currents (tiled kernels: 2D/3D)
  *   "push_kernel"   "auto|baseline|tiled"
  *   "defer_window"  "auto|<slots>"  head room of the deferred permute (0: permute inside the sort); takes effect
  *                                   when the particle arrays are next allocated ("reserve", upload)
