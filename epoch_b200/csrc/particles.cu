@@ -820,7 +820,7 @@ int32_t particle_bcs(eb200_ctx* c) {
       ScopedPhase ph(c, "bcs");
       EB_TRY(species_bcs(c, sp, n_slots, changed));
     }
-    EB_TRY(sort_species(c, sp, n_slots));
+    EB_TRY(sort_species(c, sp, n_slots, false, c->ndims >= 2 && (c->push_kernel == 0 || c->push_kernel == 3)));
   }
   return 0;
 }
@@ -839,7 +839,10 @@ int32_t push_particles(eb200_ctx* c) {
     SpeciesD& sp = c->species[is];
     if (!sp.defined) continue;
     if (sp.immobile || sp.species_type == 1) { EB_TRY(settle_species(c, sp)); continue; }
-    if (!sp.sorted || sp.sort_dt != c->dt) EB_TRY(sort_species(c, sp, sp.n));
+    // (a re-sort after a window shift or a dt change moves particles by about a tile: the permute can be
+    //  left to the push like any other; an unordered load overflows the side buffer and is permuted at once)
+    if (!sp.sorted || sp.sort_dt != c->dt)
+      EB_TRY(sort_species(c, sp, sp.n, false, c->ndims >= 2 && (c->push_kernel == 0 || c->push_kernel == 3)));
     if (sp.n == 0) { sp.deferred = false; continue; }
     PushP p = make_push_params(c, sp, sp.n);
     bool handled = false, fused_keys = false;
