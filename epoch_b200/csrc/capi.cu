@@ -193,7 +193,7 @@ int32_t eb200_set_grid(eb200_ctx* c, const int32_t n_local[3], const int32_t n_g
   EB_CUDA(c, cudaMalloc(&c->fbase, (size_t)NFIELD * g.total * sizeof(double)));
   EB_CUDA(c, cudaMemsetAsync(c->fbase, 0, (size_t)NFIELD * g.total * sizeof(double), c->stream));
   for (int f = 0; f < NFIELD; ++f) c->f.f[f] = c->fbase + (size_t)f * g.total;
-  for (SpeciesD& sp : c->species) sp.sorted = false;
+  for (SpeciesD& sp : c->species) { sp.sorted = false; sp.was_ordered = false; }
   c->grid_set = true;
   return 0;
 }

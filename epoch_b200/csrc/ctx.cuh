@@ -85,6 +85,7 @@ struct SpeciesD {
   uint32_t* h_tile_start = nullptr;
   long long tile_cap = 0;
   bool sorted = false;      // keys/cell_start valid for the current positions ...
+  bool was_ordered = false; // the slots are in (an older) cell order: a re-sort moves particles by about a tile
   double sort_dt = 0.0;     // ... and for this time step (the key is the cell after the half drift)
 };
 

@@ -106,7 +106,7 @@ static int32_t ensure_stage(eb200_ctx* c, long long doubles) {
 
 int32_t add_particles(eb200_ctx* c, int isp, long long n, const double* packed, int nvar, bool replace) {
   SpeciesD& sp = c->species[isp];
-  if (replace) sp.n = 0;
+  if (replace) { sp.n = 0; sp.was_ordered = false; }
   if (n == 0) { sp.sorted = false; return 0; }
   EB_TRY(species_reserve(c, sp, sp.n + n));
   const size_t rec = (size_t)nvar * sizeof(double);
@@ -249,7 +249,9 @@ __global__ void k_src(const uint32_t* __restrict__ key, long long n, const uint3
     uint32_t s = (uint32_t)i;
     const long long df = (long long)d - i;
     if (df > limit || -df > limit) {
-      const unsigned long long slot = atomicAdd(far_count, 1ULL);
+      // (an unordered load displaces everything: once the buffer is full nobody queues at the counter any more;
+      //  a count >= far_cap tells the host to permute at once)
+      const unsigned long long slot = *far_count < (unsigned long long)far_cap ? atomicAdd(far_count, 1ULL) : (unsigned long long)far_cap;
       if ((long long)slot < far_cap) {
 #pragma unroll
         for (int a = 0; a < 7; ++a)
@@ -534,7 +536,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
     long long biggest = 1;
     for (long long t = 0; t + 1 < nt1; ++t) biggest = std::max<long long>(biggest, (long long)(sp.h_tile_start[t + 1] - sp.h_tile_start[t]));
     const long long n_far = (long long)c->h_counters[12];
-    if (may_defer && sp.win > 0 && d.room >= biggest && n_far <= sp.far_cap && d.off_new + sp.n + sp.gap <= sp.cap) {
+    if (may_defer && sp.win > 0 && d.room >= biggest && n_far < sp.far_cap && d.off_new + sp.n + sp.gap <= sp.cap) {
       sp.deferred = true; sp.n_old = n_slots;
       c->n_deferred++;
     } else if (sp.n > 0) {
@@ -572,6 +574,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
     }
   }
   sp.sorted = true;
+  sp.was_ordered = true;
   sp.sort_dt = c->dt;
   EB_CUDA(c, cudaGetLastError());
   return 0;
@@ -820,7 +823,7 @@ int32_t particle_bcs(eb200_ctx* c) {
       ScopedPhase ph(c, "bcs");
       EB_TRY(species_bcs(c, sp, n_slots, changed));
     }
-    EB_TRY(sort_species(c, sp, n_slots, false, c->ndims >= 2 && (c->push_kernel == 0 || c->push_kernel == 3)));
+    EB_TRY(sort_species(c, sp, n_slots, false, sp.was_ordered && c->ndims >= 2 && (c->push_kernel == 0 || c->push_kernel == 3)));
   }
   return 0;
 }
@@ -842,7 +845,7 @@ int32_t push_particles(eb200_ctx* c) {
     // (a re-sort after a window shift or a dt change moves particles by about a tile: the permute can be
     //  left to the push like any other; an unordered load overflows the side buffer and is permuted at once)
     if (!sp.sorted || sp.sort_dt != c->dt)
-      EB_TRY(sort_species(c, sp, sp.n, false, c->ndims >= 2 && (c->push_kernel == 0 || c->push_kernel == 3)));
+      EB_TRY(sort_species(c, sp, sp.n, false, sp.was_ordered && c->ndims >= 2 && (c->push_kernel == 0 || c->push_kernel == 3)));
     if (sp.n == 0) { sp.deferred = false; continue; }
     PushP p = make_push_params(c, sp, sp.n);
     bool handled = false, fused_keys = false;

@@ -58,6 +58,8 @@ struct TL {
   // deposit region: cells c0+SFM-1 .. c0+T-1+SFM+NW  (T + NW + 1 wide)
   static constexpr int JX = TX + NW + 1, JY = ND >= 2 ? TY + NW + 1 : 1, JZ = ND >= 3 ? TZ + NW + 1 : 1;
   static constexpr int JN = JX * JY * JZ;
+  // ... of a deposit CTA's sub-tile (half a tile along the slowest axis)
+  static constexpr int JNS = ND == 3 ? JX * JY * (TZ / 2 + NW + 1) : JX * (TY / 2 + NW + 1);
   // register accumulators per component.  3D: the last box slot along the running-sum axis is
   // left out -- the sum has returned to zero there (rounding residue) unless the particle moved
   // up a cell, and then the slot is deposited by a work item (mover_item3, m == A, dcell = +1)
@@ -590,7 +592,13 @@ namespace {
 #define EB_NTA 128
 #endif
 constexpr int NTA = EB_NTA;      // push kernel threads
-constexpr int MCAPB = 2048;      // overflow work items per sub-tile in the deposit kernel (more are deposited inline)
+#ifndef EB_MCAPB
+#define EB_MCAPB 2048
+#endif
+#ifndef EB_ONEC
+#define EB_ONEC 0                // 1: one pass per current component for every shape (fewer registers, more CTAs per SM)
+#endif
+constexpr int MCAPB = EB_MCAPB;  // overflow work items per sub-tile in the deposit kernel (more are deposited inline)
 #ifndef EB_MINB_B
 #define EB_MINB_B 2
 #endif
@@ -816,7 +824,7 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   // ---- thread per cell: all components of the cell's box in registers; the next record is
   //      fetched while the current one is deposited.  ONEC (3D bspline3: 3 x 100 accumulators):
   //      one pass over the cell's records per component instead ----
-  constexpr bool ONEC = 3 * NA > 128;
+  constexpr bool ONEC = 3 * NA > 128 || (EB_ONEC && ND == 3);
   const int lc = sub * NTB + tid;
   const uint32_t my_b = cell_start[kbase + lc], my_e = cell_start[kbase + lc + 1];
   int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
@@ -1133,7 +1141,7 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
       auto ka = gather ? k_push_split<ND, SH, true> : k_push_split<ND, SH, false>;                         \
       auto kb = det ? k_deposit_split<ND, SH, true> : k_deposit_split<ND, SH, false>;                      \
       const size_t sa = sizeof(double) * (6 * TL<ND, SH>::FN + (NTA / 32) * (EB_STAGE_HALF ? 128 : 256)) + EB_SMEM_PAD;                                               \
-      const size_t sb = sizeof(double) * (det ? 6 : 3) * TL<ND, SH>::JN + sizeof(int) * (2 * MCAPB + 4)   /* >= sub-tile need */ \
+      const size_t sb = sizeof(double) * (det ? 6 : 3) * TL<ND, SH>::JNS + sizeof(int) * (2 * MCAPB + 4)                     \
                         + (size_t)RING * 64 * (TL<ND, SH>::CPT / SUB) + 16;                                      \
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
