@@ -281,7 +281,8 @@ def run_ours(args):
     # the e2e leg (which needs the whole state in host buffers) is skipped
     import psutil
     local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
-    host_budget = 0.85 * psutil.virtual_memory().available / max(1, local_world)
+    # (the host buffers are page-locked: keep a good part of the host's memory unpinned)
+    host_budget = 0.70 * psutil.virtual_memory().available / max(1, local_world)
     if args.host_gb is not None:
         host_budget = args.host_gb * 1e9
     full_host = n_part * 56 * 1.04 < host_budget

@@ -137,7 +137,7 @@ int32_t eb200_destroy(eb200_ctx* c) {
   comm_destroy(c);
   for (SpeciesD& sp : c->species) free_species(sp);
   for (int b = 0; b < 6; ++b) for (Laser& L : c->lasers[b]) { if (L.profile) cudaFree(L.profile); if (L.phase) cudaFree(L.phase); }
-  void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->rec_scratch, c->det_tiles, c->cub_tmp, c->halo_send, c->halo_recv,
+  void* ptrs[] = {c->fbase, c->attr_scratch, c->cell_count, c->rec_scratch, c->det_tiles, c->mig_list[0], c->mig_list[1], c->cub_tmp, c->halo_send, c->halo_recv,
                   c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho, c->smooth_wk, c->win_planes, c->cpml_psi, c->diag_wk,
                   c->cpml_prof[0], c->cpml_prof[1], c->cpml_prof[2]};
   for (void* p : ptrs) if (p) cudaFree(p);

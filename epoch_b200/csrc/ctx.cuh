@@ -155,6 +155,8 @@ struct eb200_ctx {
   double* mig_send[2] = {nullptr, nullptr}; double* mig_recv[2] = {nullptr, nullptr};
   long long mig_cap = 0;
   long long mig_min_particles = 1 << 16;   // option mig_capacity
+  uint32_t* mig_list[2] = {nullptr, nullptr};   // slots leaving through the low / high side (listed by the push kernel)
+  long long mig_list_cap = 0, mig_list_want = 0;
   // pinned staging ring of the host <-> device transfers (hostio.cu)
   static constexpr int NPIN = 3;
   void* pin[NPIN] = {nullptr, nullptr, nullptr};

@@ -13,6 +13,8 @@ int32_t launch_push_baseline(eb200_ctx* c, const SpeciesD& sp, const PushP& p); 
 int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* handled, const void* keysink);  // push_tiled.cu
 size_t keysink_size();
 void keysink_fill(void* dst, const BcP3& bc, uint32_t* key, uint32_t* count, uint32_t nbucket);
+void keysink_set_migration(void* dst, int axis, double mn, double mx, uint32_t* list_lo, uint32_t* list_hi,
+                           unsigned long long* cnt, uint32_t cap);
 
 // ---------------------------------------------------------------------------------
 // storage
@@ -643,6 +645,27 @@ __global__ void k_pack_leavers(long long n, int nd, const double* x, const doubl
   key[i] = KEY_INVALID;
 }
 
+// the same from the slot lists the push kernel made (fused migration): blockIdx.y = side; a leaver through a
+// global periodic boundary is shifted to the other end (boundary.F90:1390-1461) as it is packed
+__global__ void k_pack_list(const uint32_t* __restrict__ list_lo, const uint32_t* __restrict__ list_hi, long long nlo,
+                            long long nhi, int nd, int ax, double shift_lo, double shift_hi, const double* x,
+                            const double* y, const double* z, const double* px, const double* py, const double* pz,
+                            const double* w, uint32_t* key, double* send_lo, double* send_hi, uint32_t* count,
+                            uint32_t invalid_bucket) {
+  const int side = blockIdx.y;
+  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= (side == 0 ? nlo : nhi)) return;
+  const uint32_t i = (side == 0 ? list_lo : list_hi)[j];
+  double* q = (side == 0 ? send_lo : send_hi) + j * (nd + 4);
+  q[0] = x[i];
+  if (nd >= 2) q[1] = y[i];
+  if (nd >= 3) q[2] = z[i];
+  q[ax] += side == 0 ? shift_lo : shift_hi;
+  q[nd] = px[i]; q[nd + 1] = py[i]; q[nd + 2] = pz[i]; q[nd + 3] = w[i];
+  atomicSub(count + key[i], 1u); atomicAdd(count + invalid_bucket, 1u);
+  key[i] = KEY_INVALID;
+}
+
 static int32_t read_counters(eb200_ctx* c, int n) {
   EB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
   EB_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -652,13 +675,21 @@ static int32_t read_counters(eb200_ctx* c, int n) {
 // applies particle_bcs to slots [0, n_slots) of one species; returns the new slot
 // count (arrivals are appended) and whether the live count may have changed
 // n_counted > 0: the push kernel wrote keys + histogram for the slots [0, n_counted) (fused keys)
-static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool& changed, long long n_counted = 0) {
+// list_axis >= 0: the push kernel has listed the leavers of that axis (c->mig_list, counts in d_counters[0..1])
+static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool& changed, long long n_counted = 0,
+                           int list_axis = -1) {
   const int nvar = c->ndims + 4;
   for (int ax = 0; ax < c->ndims; ++ax) {
     const BcP b = make_bc(c, sp, ax);
     if (!b.multi) continue;        // axes that are not decomposed are handled inside the sort's key pass
     const bool open_here = (b.min_bnd && b.bc_min == EB200_BC_OPEN) || (b.max_bnd && b.bc_max == EB200_BC_OPEN);
-    if (n_slots > 0 || b.multi) {
+    bool lists = ax == list_axis;
+    if (lists) {
+      EB_TRY(read_counters(c, 2));
+      const long long most = (long long)std::max(c->h_counters[0], c->h_counters[1]);
+      if (most > c->mig_list_cap) { c->mig_list_want = 4 * most; lists = false; }   // too many: find them the usual way
+    }
+    if (!lists && (n_slots > 0 || b.multi)) {
       if (b.multi || open_here) EB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
       if (n_slots > 0) {
         k_particle_bc<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(b, n_slots, sp.a[ax], sp.a[3 + ax],
@@ -669,10 +700,16 @@ static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool&
     if (open_here) changed = true;
     if (!b.multi) continue;
     changed = true;
-    EB_TRY(read_counters(c, 3));
+    if (!lists) EB_TRY(read_counters(c, 3));
     const long long nlo = (long long)c->h_counters[0], nhi = (long long)c->h_counters[1];
     EB_TRY(ensure_stage(c, std::max<long long>(std::max<long long>(4 * std::max(nlo, nhi), c->mig_min_particles) * nvar, 1 << 16)));
-    if (nlo + nhi > 0) {
+    if (lists && nlo + nhi > 0) {
+      const dim3 gl((unsigned)((std::max(nlo, nhi) + 255) / 256), 2);
+      k_pack_list<<<gl, 256, 0, c->stream>>>(c->mig_list[0], c->mig_list[1], nlo, nhi, c->ndims, ax,
+          b.min_bnd ? b.shift : 0.0, b.max_bnd ? -b.shift : 0.0, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6],
+          sp.key, c->mig_send[0], c->mig_send[1], c->cell_count, (uint32_t)c->g.ncell_ext);
+      c->launches++;
+    } else if (nlo + nhi > 0) {
       k_pack_leavers<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(n_slots, c->ndims, sp.a[0], sp.a[1], sp.a[2],
           sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key, sp.dest, c->d_counters, c->mig_send[0], c->mig_send[1],
           n_counted > 0 ? c->cell_count : nullptr, (uint32_t)c->g.ncell_ext, n_counted);
@@ -849,6 +886,7 @@ int32_t push_particles(eb200_ctx* c) {
     if (sp.n == 0) { sp.deferred = false; continue; }
     PushP p = make_push_params(c, sp, sp.n);
     bool handled = false, fused_keys = false;
+    int mig_axis = -1;
     {
       ScopedPhase ph(c, "push");
       ScopedPhase pk(c, "push_kernel");     // the kernel(s) alone (roofline figure of bench.py)
@@ -871,6 +909,25 @@ int32_t push_particles(eb200_ctx* c) {
           for (int d = 0; d < 3; ++d) { bc.on[d] = d < c->ndims && c->nprocdir[d] == 1; bc.b[d] = make_bc(c, sp, d < c->ndims ? d : 0); }
           keysink_fill(ksbuf.data(), bc, sp.key, c->cell_count, nbucket);
           ks = ksbuf.data();
+          // one decomposed axis: the push lists its leavers as well (fused migration search)
+          int ndec = 0, dax = -1;
+          for (int d = 0; d < c->ndims; ++d) if (c->nprocdir[d] > 1) { ++ndec; dax = d; }
+          mig_axis = -1;
+          if (ndec == 1 && c->fuse_keys) {
+            const long long want = std::max<long long>(std::max<long long>(c->mig_list_want, c->mig_min_particles), 1 << 16);
+            if (c->mig_list_cap < want) {
+              for (int s2 = 0; s2 < 2; ++s2) {
+                if (c->mig_list[s2]) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(c->mig_list[s2]); c->mig_list[s2] = nullptr; }
+                EB_CUDA(c, cudaMalloc(&c->mig_list[s2], (size_t)want * sizeof(uint32_t)));
+              }
+              c->mig_list_cap = want;
+            }
+            EB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
+            const BcP bm = make_bc(c, sp, dax);
+            keysink_set_migration(ksbuf.data(), dax, bm.min_local, bm.max_local, c->mig_list[0], c->mig_list[1], c->d_counters,
+                                  (uint32_t)std::min<long long>(c->mig_list_cap, 0xFFFFFFF0LL));
+            mig_axis = dax;
+          }
         }
         EB_TRY(launch_push_split(c, sp, p, &handled, ks));     // consumes a deferred permute
         fused_keys = handled && ks != nullptr;
@@ -890,7 +947,7 @@ int32_t push_particles(eb200_ctx* c) {
       bool changed = false;
       {
         ScopedPhase ph(c, "bcs");
-        EB_TRY(species_bcs(c, sp, n_slots, changed, n_counted));
+        EB_TRY(species_bcs(c, sp, n_slots, changed, n_counted, mig_axis));
         if (n_slots > n_counted) {       // arrivals: BCs of the other axes, key, histogram
           BcP3 bc;
           for (int d = 0; d < 3; ++d) { bc.on[d] = d < c->ndims && c->nprocdir[d] == 1; bc.b[d] = make_bc(c, sp, d < c->ndims ? d : 0); }

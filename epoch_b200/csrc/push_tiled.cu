@@ -284,7 +284,12 @@ namespace {
 struct PArr { double* x[3]; double* m[3]; double* w; };
 // when on: the push also applies the particle BCs of the (undecomposed) axes to the values it
 // stores and produces the next sort key + key histogram, saving the sort's own pass
-struct KeySink { int on; BcP3 bc; uint32_t* key; uint32_t* count; uint32_t nbucket; };
+// mig_axis >= 0 (one decomposed, periodic axis): the push also lists the slots that leave the sub-domain along
+// that axis (low side / high side), so that particle_bcs needs no pass over the particles to find them
+struct KeySink {
+  int on; BcP3 bc; uint32_t* key; uint32_t* count; uint32_t nbucket;
+  int mig_axis; double mig_min, mig_max; uint32_t* mig_list[2]; unsigned long long* mig_cnt; uint32_t mig_cap;
+};
 
 // deferred permute: slot s of the pre-sort order, or entry s - n_main of the side buffer
 template <int ND>
@@ -392,6 +397,14 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
     const int ch = bc_and_key<ND, SHAPE>(*g, p, ks->bc, posn, momn, k);
 #endif
     if (ch < 0) k = ks->nbucket - 1;
+    if (ks->mig_axis >= 0 && ch >= 0) {
+      const double xm = ks->mig_axis == 0 ? posn[0] : (ks->mig_axis == 1 ? posn[1] : posn[2]);
+      const int side = xm < ks->mig_min ? 0 : (xm >= ks->mig_max ? 1 : -1);
+      if (side >= 0) {
+        const unsigned long long slot = atomicAdd(ks->mig_cnt + side, 1ULL);
+        if (slot < (unsigned long long)ks->mig_cap) ks->mig_list[side][slot] = (uint32_t)ip;
+      }
+    }
     ks->key[ip] = ch < 0 ? KEY_INVALID : k;
     const unsigned peers = __match_any_sync(__activemask(), k);
     if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(ks->count + k, (uint32_t)__popc(peers));
@@ -1018,7 +1031,14 @@ size_t keysink_size() { return sizeof(KeySink); }
 void keysink_fill(void* dst, const BcP3& bc, uint32_t* key, uint32_t* count, uint32_t nbucket) {
   KeySink ks{};
   ks.on = 1; ks.bc = bc; ks.key = key; ks.count = count; ks.nbucket = nbucket;
+  ks.mig_axis = -1;
   *(KeySink*)dst = ks;
+}
+void keysink_set_migration(void* dst, int axis, double mn, double mx, uint32_t* list_lo, uint32_t* list_hi,
+                           unsigned long long* cnt, uint32_t cap) {
+  KeySink& ks = *(KeySink*)dst;
+  ks.mig_axis = axis; ks.mig_min = mn; ks.mig_max = mx; ks.mig_list[0] = list_lo; ks.mig_list[1] = list_hi;
+  ks.mig_cnt = cnt; ks.mig_cap = cap;
 }
 
 // One tensor map over E,B as a fp64 tensor with the dimensions (x, y, component, z) -- the six arrays are
@@ -1072,7 +1092,7 @@ static void ensure_tmap(eb200_ctx* c) {
 int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* handled, const void* keysink) {
   *handled = false;
   KeySink ks;
-  if (keysink) ks = *(const KeySink*)keysink; else { ks.on = 0; ks.count = nullptr; ks.nbucket = 0; }
+  if (keysink) ks = *(const KeySink*)keysink; else { ks.on = 0; ks.count = nullptr; ks.nbucket = 0; ks.mig_axis = -1; }
   if (c->ndims < 2 || !sp.sorted || !sp.h_tile_start) return 0;
   // deferred permute: read the pre-sort order through src, write the sorted order into the other state
   const bool gather = sp.deferred;
