@@ -595,6 +595,10 @@ __device__ __forceinline__ int mover_item_count(int pack) {
 // =====================================================================================
 namespace {
 
+#ifndef EB_PUSH_CHUNK
+#define EB_PUSH_CHUNK 16384
+#endif
+constexpr int PUSH_CHUNK = EB_PUSH_CHUNK;   // particles per push CTA (a multiple of the CTA size)
 #ifndef EB_STAGE_HALF
 #define EB_STAGE_HALF 1
 #endif
@@ -637,8 +641,12 @@ __global__ void __launch_bounds__(NTA, SHAPE == SHAPE_BSPLINE3 ? 2 : EB_MINB_A) 
   const int tid = threadIdx.x;
   const long long tile = tile0 + blockIdx.x;
   const long long kbase = tile * T::CPT;
-  const uint32_t pb = cell_start[kbase], pe = cell_start[kbase + T::CPT];
-  if (pb == pe) return;
+  // a tile's particles are shared out in chunks of PUSH_CHUNK among the CTAs (blockIdx.x, 0 .. gridDim.y - 1): one CTA
+  // per tile for a uniform plasma, many for the dense tiles of a foil (each stages the tile's fields itself)
+  const uint32_t tb = cell_start[kbase], te = cell_start[kbase + T::CPT];
+  if ((unsigned long long)tb + (unsigned long long)blockIdx.y * PUSH_CHUNK >= (unsigned long long)te) return;
+  const uint32_t pb = tb + blockIdx.y * (uint32_t)PUSH_CHUNK;
+  const uint32_t pe = te - pb > (uint32_t)PUSH_CHUNK ? pb + (uint32_t)PUSH_CHUNK : te;
   const uint32_t base = cell_start[tile0 * T::CPT];      // first particle of the slab
   int tc[3];
   tc[0] = (int)(tile % g.ntile[0]);
@@ -1156,6 +1164,9 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
   for (size_t is = 0; is < slabs.size(); ++is) {
     const long long t0 = slabs[fwd ? is : slabs.size() - 1 - is].first, t1 = slabs[fwd ? is : slabs.size() - 1 - is].second;
     const unsigned nb = (unsigned)(t1 - t0);
+    long long big = 1;
+    for (long long t = t0; t < t1; ++t) big = std::max<long long>(big, (long long)(ts[t + 1] - ts[t]));
+    const dim3 ga(nb, (unsigned)((big + PUSH_CHUNK - 1) / PUSH_CHUNK));
 #define L(ND, SH)                                                                                          \
     if (c->ndims == ND && c->shape == SH) {                                                                \
       auto ka = gather ? k_push_split<ND, SH, true> : k_push_split<ND, SH, false>;                         \
@@ -1166,7 +1177,7 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
       { ScopedPhase pa(c, "push_A");                                                                       \
-        ka<<<nb, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks, tmap, use_tma); } \
+        ka<<<ga, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks, tmap, use_tma); } \
       if (!p.zero_current) { ScopedPhase pb(c, "push_B");                                                  \
         kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch, c->det_tiles); \
         if (det) {                                                                                         \

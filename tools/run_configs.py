@@ -140,6 +140,46 @@ def run_cfg4(abi, scale, steps=10, warm=3):
             "phases_ms_per_step": {k: sim.ctx.timer(k)[0] / (steps + warm) for k in ("push_A", "push_B", "sort", "fields", "bcs")}}
 
 
+def run_cfg5(abi, scale, steps=8, warm=3):
+    """configs[4]: 2D laser-solid foil, highly non-uniform particles per cell (a thin dense slab, vacuum elsewhere)"""
+    nx, ny = max(256, int(4096 * scale)), max(128, int(2048 * scale))
+    lam = 1.0e-6
+    dx = lam / 32.0
+    dens, ppc = 5.0e28, 256                      # ~45 n_c, 256 e- + 256 p+ per cell inside the foil
+    thick = max(8, int(32 * scale))
+    species = [SpeciesSpec("electron", -Q0, M0, bcs=["open", "open", "periodic", "periodic"], density=dens, temperature=(1e5,) * 3),
+               SpeciesSpec("proton", Q0, 1836.2 * M0, bcs=["open", "open", "periodic", "periodic"], density=dens, temperature=(1e5,) * 3)]
+    las = LaserSpec(1, intensity_w_cm2=1.0e20, lambda_=lam, t_profile=lambda t: min(1.0, t / 10e-15))
+    sim = Simulation(2, [nx, ny], [0.0, 0.0], [nx * dx, ny * dx], shape="triangle", species=species, lasers=[las],
+                     bc_field=["simple_laser", "simple_outflow", "periodic", "periodic"], abi=abi, options={"timers": 1})
+    x0 = sim.min_local[0] + (nx // 2) * dx
+    w = dens * dx * dx / ppc
+    m = thick * ny * ppc
+    rng = np.random.default_rng(11)
+    t0 = time.perf_counter()
+    for isp, sp in enumerate(species):
+        P = sim.ctx.host_empty((m, 6))
+        P[:, 0] = x0 + rng.random(m) * (thick * dx)
+        P[:, 1] = rng.random(m) * (sim.max_local[1] - sim.min_local[1]) + sim.min_local[1]
+        P[:, 2:5] = rng.standard_normal((m, 3)) * math.sqrt(sp.mass * KB * 1e5)
+        P[:, 5] = w
+        sim.ctx.upload_particles(isp, P)
+    t_load = time.perf_counter() - t0
+    n0 = [sim.ctx.particle_count(i) for i in range(2)]
+    dev_s, wall = timed_steps(sim, warm, steps)
+    n1 = [sim.ctx.particle_count(i) for i in range(2)]
+    fe, ke = sim.ctx.energy()
+    npart = sum(n0)
+    return {"config": "cfg5 epoch2d laser-foil %dx%d cells, foil %d cells thick with 256 e- + 256 p+ per cell (vacuum elsewhere), "
+                      "triangle, laser 1e20 W/cm^2, one B200" % (nx, ny, thick),
+            "particles": npart, "steps": steps, "ms_per_step": 1e3 * dev_s / steps,
+            "particle_steps_per_s": npart * steps / dev_s, "load_seconds": t_load,
+            "checks": {"cell_mismatch": sim.ctx.timer("cell_mismatch")[1], "particles_before": n0, "particles_after": n1,
+                       "none_lost": n0 == n1, "field_energy_J_per_m": fe, "kinetic_finite": bool(np.all(np.isfinite(ke)))},
+            "sorts": {"deferred": sim.ctx.timer("deferred_sorts")[1], "permuted": sim.ctx.timer("permuted_sorts")[1]},
+            "phases_ms_per_step": {k: sim.ctx.timer(k)[0] / (steps + warm) for k in ("push_A", "push_B", "sort", "fields", "bcs")}}
+
+
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "both"
     scale = float(sys.argv[2]) if len(sys.argv) > 2 else 1.0
@@ -148,3 +188,5 @@ if __name__ == "__main__":
         print(json.dumps(run_cfg2(abi, scale)), flush=True)
     if which in ("cfg4", "both"):
         print(json.dumps(run_cfg4(abi, scale)), flush=True)
+    if which == "cfg5":
+        print(json.dumps(run_cfg5(abi, scale)), flush=True)
