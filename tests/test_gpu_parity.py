@@ -491,3 +491,19 @@ def test_deterministic_deposit(product_abi, oracle_abi, ndims, shape, pbc, windo
         s = make_plasma(product_abi, 1, "triangle", [32], seed=1, ppc=2, options={"deterministic_deposit": 1})
         with pytest.raises(Exception):
             s.step_once()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndims,shape,n,ppc", [(2, "triangle", [32, 32], 70), (3, "triangle", [8, 8, 8], 70),
+                                               (2, "bspline3", [16, 32], 80)])
+def test_dense_tiles(product_abi, oracle_abi, ndims, shape, n, ppc):
+    """tiles with more than PUSH_CHUNK (16384) particles are pushed by several CTAs; dense cells overflow the
+    deposit's work-item list (inline path): same answers as the oracle"""
+    sims = [make_plasma(a, ndims, shape, n, seed=13, ppc=ppc, u_th=0.5, e_amp=1e9, b_amp=3.0, two_species=False)
+            for a in (product_abi, oracle_abi)]
+    for _ in range(3):
+        for s in sims:
+            s.step_once()
+    compare_particles(sims[0], sims[1], tol=1e-10)
+    compare_fields(sims[0], sims[1], ALL9, tol=1e-10)
+    assert sims[0].ctx.timer("cell_mismatch")[1] == 0
