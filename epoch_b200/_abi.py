@@ -50,6 +50,7 @@ SIGNATURES = {
     "energy": (i32, [c_ctx_p, pf64, pf64]),
     "charge_residual": (i32, [c_ctx_p, pf64, pf64]),
     "calc_derived": (i32, [c_ctx_p, i32, i32, i32, pf64]),
+    "dist_fn": (i32, [c_ctx_p, i32, i32, pi32, pf64, pi32, pf64, pf64, pi32, pf64]),
     "get_load": (i32, [c_ctx_p, pf64, pi64, pi64, pi64]),
     "redistribute": (i32, [c_ctx_p, pi32, pi32, pi32, pi32, pf64, pf64, pf64, pf64]),
     "set_option": (i32, [c_ctx_p, C.c_char_p, C.c_char_p]),

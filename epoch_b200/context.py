@@ -177,6 +177,30 @@ class PicContext:
                                              self.nvar, C.byref(got)))
         return out[:got.value]
 
+    def dist_fn(self, isp, direction, ranges, resolution, dgrid, restrictions=None, use_restrictions=None):
+        """particle loop of general_dist_fn (io/dist_fn.F90:532-628): this rank's weighted histogram.
+        direction: 1-based c_dir_* codes; ranges [(lo, hi)] per dimension.  Returns an array shaped
+        resolution[::-1] (C order of the Fortran array(res1, res2, res3))."""
+        cur = len(direction)
+        res3 = [int(r) for r in resolution] + [1] * (3 - cur)
+        rng = np.zeros(6)
+        for i, (lo, hi) in enumerate(ranges):
+            rng[2 * i], rng[2 * i + 1] = lo, hi
+        dg = np.ones(3)
+        dg[:cur] = dgrid
+        out = np.zeros(res3[::-1])
+        rp = up = None
+        if restrictions is not None:
+            rarr = np.ascontiguousarray(restrictions, dtype=np.float64).reshape(-1)
+            uarr = np.ascontiguousarray(use_restrictions, dtype=np.int32)
+            assert len(uarr) == self.ndims + 9 and len(rarr) == 2 * len(uarr)
+            rp, up = rarr.ctypes.data_as(C.POINTER(C.c_double)), uarr.ctypes.data_as(C.POINTER(C.c_int32))
+        self._ck(self.abi.dist_fn(self._ctx, isp, cur, _i32(list(direction) + [1] * (3 - cur)),
+                                  rng.ctypes.data_as(C.POINTER(C.c_double)), _i32(res3),
+                                  dg.ctypes.data_as(C.POINTER(C.c_double)), rp, up,
+                                  out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out[(0,) * (3 - cur)] if cur < 3 else out
+
     # -- fields (Fortran-shaped with ghosts; returned as numpy arrays indexed
     #    [k, j, i] i.e. C order of the column-major reference array) ---------
     def _np_shape(self):

@@ -432,6 +432,23 @@ int32_t eb200_calc_derived(eb200_ctx* c, int32_t kind, int32_t ispecies, int32_t
   return calc_derived(c, kind, ispecies, direction, out);
 }
 
+int32_t eb200_dist_fn(eb200_ctx* c, int32_t ispecies, int32_t curdims, const int32_t direction[3], const double ranges[6],
+                      const int32_t resolution[3], const double dgrid[3], const double* restrictions,
+                      const int32_t* use_restrictions, double* out) {
+  CHECK_CTX(c); NEED_GRID(c);
+  if (ispecies < 0 || (size_t)ispecies >= c->species.size() || !c->species[ispecies].defined)
+    return fail(c, EB200_E_ARG, "dist_fn: species not defined");
+  if (curdims < 1 || curdims > 3 || !direction || !ranges || !resolution || !dgrid || !out)
+    return fail(c, EB200_E_ARG, "dist_fn: bad argument");
+  for (int i = 0; i < curdims; ++i) {
+    if (direction[i] < 1 || direction[i] > c->ndims + 9) return fail(c, EB200_E_ARG, "dist_fn: unknown direction (dist_fn.F90:378-385)");
+    if (resolution[i] < 1 || !(dgrid[i] > 0.0)) return fail(c, EB200_E_ARG, "dist_fn: resolution and dgrid must be positive");
+  }
+  if ((restrictions == nullptr) != (use_restrictions == nullptr)) return fail(c, EB200_E_ARG, "dist_fn: restrictions and use_restrictions go together");
+  EB_TRY(settle_species(c, c->species[ispecies]));
+  return dist_fn(c, ispecies, curdims, direction, ranges, resolution, dgrid, restrictions, use_restrictions, out);
+}
+
 int32_t eb200_set_laser(eb200_ctx* c, int32_t boundary, int32_t id, double amp, double pol_angle, double t_start,
                         double t_end, const double* profile, const double* phase) {
   CHECK_CTX(c); NEED_GRID(c);

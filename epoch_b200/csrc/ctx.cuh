@@ -236,6 +236,9 @@ int32_t field_bc_array(eb200_ctx* c, double* a);                  // the same fo
 int32_t zero_gradient_centre(eb200_ctx* c, double* a);
 // diag.cu
 int32_t calc_derived(eb200_ctx* c, int kind, int ispecies, int direction, double* out_host);
+int32_t dist_fn(eb200_ctx* c, int ispecies, int curdims, const int32_t* direction, const double* ranges,
+                const int32_t* resolution, const double* dgrid, const double* restrictions,
+                const int32_t* use_restrictions, double* out_host);
 int32_t efield_bcs(eb200_ctx* c);
 int32_t bfield_bcs(eb200_ctx* c, bool mpi_only);
 int32_t bfield_final_bcs(eb200_ctx* c);

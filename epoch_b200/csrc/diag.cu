@@ -293,4 +293,109 @@ int32_t calc_derived(eb200_ctx* c, int kind, int ispecies, int direction, double
   return 0;
 }
 
+// ---------------------------------------------------------------------------------
+// general_dist_fn (io/dist_fn.F90:118-762): the particle loop (:532-628).  Thread per particle,
+// one fp64 RED per particle into the histogram.
+// ---------------------------------------------------------------------------------
+struct DistP {
+  long long n;
+  const double* a[7];
+  int nd, curdims, photon;
+  int dir[3];                 // 1-based c_dir_* codes
+  double lo[3], dgrid[3];
+  int res[3];
+  double ang_max[3];          // xy_max, yz_max, zx_max (:505-510)
+  int use_ang[3];
+  int use_r[12];
+  double r_lo[12], r_hi[12];
+  double part_mc, part_mc2;
+  double* out;
+};
+
+__global__ void k_dist_fn(DistP p) {
+  const long long ip = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (ip >= p.n) return;
+  const double PI_ = 3.141592653589793238462643383279503, pi2 = 2.0 * PI_;
+  const int nd = p.nd;
+  double data[13];            // particle_data(1 : c_df_maxdirs), index = code
+#pragma unroll
+  for (int k = 0; k < 13; ++k) data[k] = 0.0;
+  for (int d = 0; d < nd; ++d) data[1 + d] = p.a[d][ip];
+  const double px = p.a[3][ip], py = p.a[4][ip], pz = p.a[5][ip];
+  const double ux = px / p.part_mc, uy = py / p.part_mc, uz = pz / p.part_mc;
+  const double part_u2 = ux * ux + uy * uy + uz * uz;
+  const double gamma_rel = sqrt(part_u2 + 1.0);
+  const double gamma_rel_m1 = part_u2 / (gamma_rel + 1.0);
+  if (p.photon) {             // (:554-566 without PHOTONS / BREMSSTRAHLUNG)
+    data[nd + EB200_DIR_GAMMA_M1] = 1.0;
+  } else {
+    data[nd + EB200_DIR_PX] = px; data[nd + EB200_DIR_PY] = py; data[nd + EB200_DIR_PZ] = pz;
+    data[nd + EB200_DIR_EN] = gamma_rel_m1 * p.part_mc2;
+    data[nd + EB200_DIR_GAMMA_M1] = gamma_rel_m1;
+    data[nd + EB200_DIR_MOD_P] = sqrt(px * px + py * py + pz * pz);
+  }
+  const double pa[3] = {px, py, pz};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {          // xy: (px, py), yz: (py, pz), zx: (pz, px)   (:576-604)
+    if (!p.use_ang[k]) continue;
+    const double a0 = pa[k], a1 = pa[(k + 1) % 3];
+    const double pp = sqrt(a0 * a0 + a1 * a1);
+    if (pp < C_TINY) return;
+    double theta = asin(a1 / pp);
+    if (a0 < 0.0) theta = copysign(1.0, a1) * PI_ - theta;
+    if ((theta + pi2) < p.ang_max[k]) theta = theta + pi2;
+    data[nd + EB200_DIR_XY_ANGLE + k] = theta;
+  }
+  for (int idir = 1; idir <= nd + 9; ++idir)
+    if (p.use_r[idir - 1] && (data[idir] < p.r_lo[idir - 1] || data[idir] > p.r_hi[idir - 1])) return;
+  long long idx = 0, mul = 1;
+  for (int idim = 0; idim < p.curdims; ++idim) {
+    const double cur = data[p.dir[idim]];
+    const double cf = floor((cur - p.lo[idim]) / p.dgrid[idim]) + 1.0;
+    if (!(cf >= 1.0) || cf > (double)p.res[idim]) return;
+    idx += mul * ((long long)cf - 1);
+    mul *= p.res[idim];
+  }
+  atomicAdd(p.out + idx, p.a[6][ip]);
+}
+
+int32_t dist_fn(eb200_ctx* c, int ispecies, int curdims, const int32_t* direction, const double* ranges,
+                const int32_t* resolution, const double* dgrid, const double* restrictions,
+                const int32_t* use_restrictions, double* out_host) {
+  SpeciesD& sp = c->species[ispecies];
+  const int nd = c->ndims;
+  DistP p;
+  p.n = sp.n; p.nd = nd; p.curdims = curdims; p.photon = sp.species_type == 1;
+  for (int k = 0; k < 7; ++k) p.a[k] = sp.a[k];
+  long long tot = 1;
+  for (int k = 0; k < 3; ++k) { p.use_ang[k] = 0; p.ang_max[k] = 0.0; p.dir[k] = 1; p.lo[k] = 0; p.dgrid[k] = 1; p.res[k] = 1; }
+  for (int i = 0; i < curdims; ++i) {
+    p.dir[i] = direction[i]; p.lo[i] = ranges[2 * i]; p.dgrid[i] = dgrid[i]; p.res[i] = resolution[i];
+    tot *= resolution[i];
+    for (int k = 0; k < 3; ++k)
+      if (direction[i] == nd + EB200_DIR_XY_ANGLE + k) { p.use_ang[k] = 1; p.ang_max[k] = ranges[2 * i + 1]; }
+  }
+  for (int k = 0; k < 12; ++k) {
+    p.use_r[k] = (use_restrictions && k < nd + 9) ? (use_restrictions[k] != 0) : 0;
+    p.r_lo[k] = (restrictions && k < nd + 9) ? restrictions[2 * k] : 0.0;
+    p.r_hi[k] = (restrictions && k < nd + 9) ? restrictions[2 * k + 1] : 0.0;
+  }
+  p.part_mc = sp.mass * C0; p.part_mc2 = p.part_mc * C0;
+  double* dev = nullptr;
+  EB_CUDA(c, cudaMalloc(&dev, (size_t)tot * sizeof(double)));
+  EB_CUDA(c, cudaMemsetAsync(dev, 0, (size_t)tot * sizeof(double), c->stream));
+  p.out = dev;
+  if (sp.n > 0) {
+    k_dist_fn<<<(unsigned)((sp.n + 255) / 256), 256, 0, c->stream>>>(p);
+    c->launches++;
+  }
+  int32_t rc = cudaGetLastError() == cudaSuccess ? 0 : EB200_E_CUDA;
+  const char* d8 = (const char*)dev;
+  if (rc == 0) rc = staged_d2h(c, out_host, (size_t)tot * sizeof(double), sizeof(double),
+                               [d8](size_t o, size_t) { return (const void*)(d8 + o); });
+  cudaStreamSynchronize(c->stream);
+  cudaFree(dev);
+  return rc;
+}
+
 }  // namespace eb

@@ -371,6 +371,60 @@ class Simulation:
         ctx.set_time(dt_store, self.time, self.step)
         self._started = True
 
+    # -- distribution functions (io/dist_fn.F90) -----------------------------------
+    DIRS = ("px", "py", "pz", "en", "gamma_m1", "xy_angle", "yz_angle", "zx_angle", "mod_p")
+
+    def dir_code(self, name):
+        """c_dir_* of constants.F90:202-213 for this dimensionality"""
+        if name in ("x", "y", "z"):
+            return "xyz".index(name) + 1
+        return self.ndims + 1 + self.DIRS.index(name)
+
+    def general_dist_fn(self, isp, direction, ranges_in, resolution_in, restrictions=None):
+        """general_dist_fn (io/dist_fn.F90:118-762) up to the local array: the host part before the particle
+        loop -- spatial ranges snapped to cells and clipped to this rank (:204-335), the -1..1 fall-back of an
+        empty range and dgrid (:490-518) -- then the loop on the device.  direction: names ("x", "px", "en", ...);
+        restrictions: {name: (lo, hi)}.  Returns (array, [grid per dimension]); the MPI_REDUCE over ranks that share
+        the spatial range stays with the caller."""
+        nd = self.ndims
+        c_tiny = 2.2250738585072014e-308
+        ranges, resolution, dgrid, codes = [], [], [], []
+        outside = False
+        for name, (r1, r2), res in zip(direction, ranges_in, resolution_in):
+            code = self.dir_code(name)
+            codes.append(code)
+            if code <= nd:
+                d = code - 1
+                dx = self.d[d]
+                gmin_l = self.grid_min_local[d]
+                gmax_l = self.grid_min_local[d] + (self.n_local[d] - 1) * dx
+                if abs(r1 - r2) <= c_tiny:
+                    r1, r2 = gmin_l - 0.5 * dx, gmax_l + 0.5 * dx
+                else:
+                    r1, r2 = max(r1, self.mins[d]), min(r2, self.maxs[d])
+                    r1 = self.min_local[d] + math.floor((r1 - self.min_local[d]) / dx) * dx
+                    r2 = self.min_local[d] + math.ceil((r2 - self.min_local[d]) / dx) * dx
+                    r1, r2 = max(r1, gmin_l - 0.5 * dx), min(r2, gmax_l + 0.5 * dx)
+                res = int(round((r2 - r1) / dx))        # NINT
+                if res <= 0:
+                    outside, res = True, 0
+                dg = dx
+            else:
+                if abs(r1 - r2) <= c_tiny:
+                    r1, r2 = -1.0, 1.0
+                dg = (r2 - r1) / float(res)
+            ranges.append((r1, r2)); resolution.append(res); dgrid.append(dg)
+        grids = [np.asarray([r[0] + 0.5 * g + i * g for i in range(n)]) for r, g, n in zip(ranges, dgrid, resolution)]
+        if outside:
+            return np.zeros((1,) * len(direction)), grids
+        rs = us = None
+        if restrictions:
+            rs, us = np.zeros((nd + 9, 2)), np.zeros(nd + 9, dtype=np.int32)
+            for name, (lo, hi) in restrictions.items():
+                k = self.dir_code(name) - 1
+                rs[k], us[k] = (lo, hi), 1
+        return self.ctx.dist_fn(isp, codes, ranges, resolution, dgrid, rs, us), grids
+
     # -- load balancing (housekeeping/balance.F90) --------------------------------
     def balance_workload(self, allreduce=None, new_tables=None):
         """The re-slicing part of balance_workload (balance.F90:175-319) with over_ride: global

@@ -26,6 +26,16 @@ MODULE epoch_b200_iface
       IMPORT :: C_INT32_T, C_PTR
       TYPE(C_PTR), VALUE :: p
     END FUNCTION eb200_host_free
+    INTEGER(C_INT32_T) FUNCTION eb200_dist_fn(ctx, ispecies, curdims, direction, ranges, resolution, dgrid, &
+        restrictions, use_restrictions, array) BIND(C, NAME='eb200_dist_fn')
+      IMPORT :: C_INT32_T, C_DOUBLE, C_PTR
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: ispecies, curdims
+      INTEGER(C_INT32_T), INTENT(IN) :: direction(3), resolution(3)
+      REAL(C_DOUBLE), INTENT(IN) :: ranges(2,3), dgrid(3)
+      TYPE(C_PTR), VALUE :: restrictions, use_restrictions   ! (2,c_df_maxdirs) reals / c_df_maxdirs int32, or C_NULL_PTR
+      REAL(C_DOUBLE), INTENT(OUT) :: array(*)
+    END FUNCTION eb200_dist_fn
     INTEGER(C_INT32_T) FUNCTION eb200_nccl_unique_id(out128) BIND(C, NAME='eb200_nccl_unique_id')
       IMPORT
       CHARACTER(KIND=C_CHAR), INTENT(OUT) :: out128(128)

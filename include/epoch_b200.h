@@ -268,6 +268,26 @@ int32_t EB200_NAME(redistribute)(EB200_CTX*, const int32_t* old_cell_min, const 
 #define EB200_DF_SPECIES_CURRENT 9
 #define EB200_DF_AVERAGE_MOMENTUM 10
 int32_t EB200_NAME(calc_derived)(EB200_CTX*, int32_t kind, int32_t ispecies, int32_t direction, double* out);
+/* The particle loop of general_dist_fn (io/dist_fn.F90:532-628): weighted histogram of one species over
+ * curdims (1..3) of the directions c_dir_* of constants.F90:202-213 -- 1..ndims = x,y,z; then, numbered from
+ * ndims+1: px, py, pz, en, gamma_m1, xy_angle, yz_angle, zx_angle, mod_p (EB200_DIR_* below are those offsets).
+ * The host keeps what precedes the loop in the reference (:204-335,490-518: snapping spatial ranges to cells,
+ * the -1..1 fall-back of an empty range, dgrid) and hands over ranges[2*idim + {0,1}], resolution, dgrid;
+ * restrictions[2*(dir-1) + {0,1}] / use_restrictions[dir-1] for dir = 1..ndims+9, or NULL for none.  out has
+ * resolution[0]*resolution[1]*resolution[2] doubles (unused dimensions: 1), first dimension fastest, and
+ * receives this rank's sums (the reference's MPI_REDUCE over the sub-communicator stays on the host). */
+#define EB200_DIR_PX 1
+#define EB200_DIR_PY 2
+#define EB200_DIR_PZ 3
+#define EB200_DIR_EN 4
+#define EB200_DIR_GAMMA_M1 5
+#define EB200_DIR_XY_ANGLE 6
+#define EB200_DIR_YZ_ANGLE 7
+#define EB200_DIR_ZX_ANGLE 8
+#define EB200_DIR_MOD_P 9
+int32_t EB200_NAME(dist_fn)(EB200_CTX*, int32_t ispecies, int32_t curdims, const int32_t direction[3],
+                            const double ranges[6], const int32_t resolution[3], const double dgrid[3],
+                            const double* restrictions, const int32_t* use_restrictions, double* out);
 /* options (key, value as strings):
  *   "deterministic_deposit" "0|1"   run-to-run bitwise reproducible currents (tiled kernels: 2D/3D)
  *   "push_kernel"   "auto|baseline|tiled"

@@ -356,6 +356,18 @@ int32_t orc_calc_derived(orc_ctx* c, int32_t kind, int32_t ispecies, int32_t dir
   calc_derived(c->s, kind, ispecies, direction, out);
   return 0;
 }
+int32_t orc_dist_fn(orc_ctx* c, int32_t ispecies, int32_t curdims, const int32_t direction[3], const double ranges[6],
+                    const int32_t resolution[3], const double dgrid[3], const double* restrictions,
+                    const int32_t* use_restrictions, double* out) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  if (ispecies < 0 || ispecies >= (int32_t)c->s.species.size() || curdims < 1 || curdims > 3 || !direction || !ranges ||
+      !resolution || !dgrid || !out || ((restrictions == nullptr) != (use_restrictions == nullptr)))
+    return EB200_E_ARG;
+  for (int i = 0; i < curdims; ++i)
+    if (direction[i] < 1 || direction[i] > c->s.ndims + 9 || resolution[i] < 1 || !(dgrid[i] > 0.0)) return EB200_E_ARG;
+  dist_fn(c->s, ispecies, curdims, direction, ranges, resolution, dgrid, restrictions, use_restrictions, out);
+  return 0;
+}
 int32_t orc_set_option(orc_ctx* c, const char* key, const char*) {
   if (c && key && std::string(key) == "capture_charge_reference") {
     double a, b;

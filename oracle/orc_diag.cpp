@@ -5,6 +5,9 @@
 // calc_average_weight :652, calc_temperature :723, calc_per_species_current :994,
 // calc_average_momentum :1104 -- with the weights of include/particle_to_grid.inc.
 #include "orc_state.hpp"
+#include <vector>
+#include <algorithm>
+#include <cmath>
 
 namespace orc {
 
@@ -217,6 +220,77 @@ void calc_derived(State& s, int kind, int ispecies, int direction, double* out) 
     for (int64_t i = 0; i < s.total; ++i) out[i] = out[i] * scale;
   }
   zero_gradient_all(s, out);
+}
+
+// general_dist_fn, the particle loop (io/dist_fn.F90:532-628), statement by statement; `out` is
+// array(resolution(1), resolution(2), resolution(3)) in Fortran order.  xy_max etc.: :505-510.
+void dist_fn(const State& s, int ispecies, int curdims, const int32_t* direction, const double* ranges,
+             const int32_t* resolution, const double* dgrid, const double* restrictions,
+             const int32_t* use_restrictions, double* out) {
+  const Species& sp = s.species[ispecies];
+  const int nd = s.ndims, maxdirs = nd + 9;
+  const int c_dir_px = nd + 1, c_dir_py = nd + 2, c_dir_pz = nd + 3, c_dir_en = nd + 4, c_dir_gamma_m1 = nd + 5,
+            c_dir_xy_angle = nd + 6, c_dir_yz_angle = nd + 7, c_dir_zx_angle = nd + 8, c_dir_mod_p = nd + 9;
+  long long tot = 1;
+  bool use_xy = false, use_yz = false, use_zx = false;
+  double xy_max = 0, yz_max = 0, zx_max = 0;
+  for (int i = 0; i < curdims; ++i) {
+    tot *= resolution[i];
+    if (direction[i] == c_dir_xy_angle) { use_xy = true; xy_max = ranges[2 * i + 1]; }
+    if (direction[i] == c_dir_yz_angle) { use_yz = true; yz_max = ranges[2 * i + 1]; }
+    if (direction[i] == c_dir_zx_angle) { use_zx = true; zx_max = ranges[2 * i + 1]; }
+  }
+  for (long long i = 0; i < tot; ++i) out[i] = 0.0;
+  const double part_mc = sp.mass * C, part_mc2 = part_mc * C, pi2 = 2.0 * PI;
+  std::vector<double> particle_data(maxdirs + 1, 0.0);
+  for (size_t ip = 0; ip < sp.count(); ++ip) {
+    const double part_weight = sp.w[ip];
+    const double px = sp.p[0][ip], py = sp.p[1][ip], pz = sp.p[2][ip];
+    const double a = px / part_mc, b = py / part_mc, cc = pz / part_mc;
+    const double part_u2 = a * a + b * b + cc * cc;
+    const double gamma_rel = std::sqrt(part_u2 + 1.0);
+    const double gamma_rel_m1 = part_u2 / (gamma_rel + 1.0);
+    std::fill(particle_data.begin(), particle_data.end(), 0.0);
+    for (int d = 0; d < nd; ++d) particle_data[1 + d] = sp.pos[d][ip];
+    if (sp.species_type == 1) {
+      particle_data[c_dir_gamma_m1] = 1.0;
+    } else {
+      particle_data[c_dir_px] = px; particle_data[c_dir_py] = py; particle_data[c_dir_pz] = pz;
+      particle_data[c_dir_en] = gamma_rel_m1 * part_mc2;
+      particle_data[c_dir_gamma_m1] = gamma_rel_m1;
+      particle_data[c_dir_mod_p] = std::sqrt(px * px + py * py + pz * pz);
+    }
+    bool skip = false;
+    auto angle = [&](double q0, double q1, double amax, int code) {
+      const double p = std::sqrt(q0 * q0 + q1 * q1);
+      if (p < C_TINY) { skip = true; return; }
+      double theta = std::asin(q1 / p);
+      if (q0 < 0.0) theta = std::copysign(1.0, q1) * PI - theta;
+      if ((theta + pi2) < amax) theta = theta + pi2;
+      particle_data[code] = theta;
+    };
+    if (use_xy) angle(px, py, xy_max, c_dir_xy_angle);
+    if (!skip && use_yz) angle(py, pz, yz_max, c_dir_yz_angle);
+    if (!skip && use_zx) angle(pz, px, zx_max, c_dir_zx_angle);
+    if (skip) continue;
+    if (restrictions) {
+      for (int idir = 1; idir <= maxdirs && !skip; ++idir)
+        if (use_restrictions[idir - 1] &&
+            (particle_data[idir] < restrictions[2 * (idir - 1)] || particle_data[idir] > restrictions[2 * (idir - 1) + 1]))
+          skip = true;
+      if (skip) continue;
+    }
+    long long idx = 0, mul = 1;
+    for (int idim = 0; idim < curdims && !skip; ++idim) {
+      const double current_data = particle_data[direction[idim]];
+      const double cf = std::floor((current_data - ranges[2 * idim]) / dgrid[idim]) + 1.0;
+      if (!(cf >= 1.0) || cf > (double)resolution[idim]) { skip = true; break; }
+      idx += mul * ((long long)cf - 1);
+      mul *= resolution[idim];
+    }
+    if (skip) continue;
+    out[idx] += part_weight;
+  }
 }
 
 }  // namespace orc

@@ -122,6 +122,9 @@ void field_zero_gradient_array(State& s, double* a, bool staggered, int boundary
 void processor_summation_array(State& s, double* a, int flip_dir);                   // boundary.F90:1123-1144
 void weights_fac(int shape, double f, double* out);                                  // include/*/gxfac.inc
 void calc_derived(State& s, int kind, int ispecies, int direction, double* out);     // io/calc_df.F90
+void dist_fn(const State& s, int ispecies, int curdims, const int32_t* direction, const double* ranges,
+             const int32_t* resolution, const double* dgrid, const double* restrictions,
+             const int32_t* use_restrictions, double* out);                            // io/dist_fn.F90
 void efield_bcs(State& s);
 void bfield_bcs(State& s, bool mpi_only);
 void bfield_final_bcs(State& s);
