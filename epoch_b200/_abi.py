@@ -50,6 +50,8 @@ SIGNATURES = {
     "energy": (i32, [c_ctx_p, pf64, pf64]),
     "charge_residual": (i32, [c_ctx_p, pf64, pf64]),
     "calc_derived": (i32, [c_ctx_p, i32, i32, i32, pf64]),
+    "set_probe": (i32, [c_ctx_p, i32, i32, pf64, pf64, f64, f64]),
+    "download_probe": (i32, [c_ctx_p, i32, i32, C.c_int64, pf64, i32, pi64, i32]),
     "dist_fn": (i32, [c_ctx_p, i32, i32, pi32, pf64, pi32, pf64, pf64, pi32, pf64]),
     "get_load": (i32, [c_ctx_p, pf64, pi64, pi64, pi64]),
     "redistribute": (i32, [c_ctx_p, pi32, pi32, pi32, pi32, pf64, pf64, pf64, pf64]),

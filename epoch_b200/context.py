@@ -177,6 +177,19 @@ class PicContext:
                                              self.nvar, C.byref(got)))
         return out[:got.value]
 
+    def set_probe(self, isp, iprobe, point, normal, ek_min=0.0, ek_max=1e300):
+        """particle probe (shared_data.F90:392-404) iprobe = 0..7 of species isp"""
+        self._ck(self.abi.set_probe(self._ctx, isp, iprobe, _f64(_pad3(point, 0.0)), _f64(_pad3(normal, 0.0)), ek_min, ek_max))
+
+    def download_probe(self, isp, iprobe, clear=True):
+        """the probe's sampled particles since the last clear (rows pos, p(3), weight) and the number sampled"""
+        n = C.c_int64()
+        self._ck(self.abi.download_probe(self._ctx, isp, iprobe, 0, None, self.nvar, C.byref(n), 0))
+        out = np.empty((n.value, self.nvar))
+        self._ck(self.abi.download_probe(self._ctx, isp, iprobe, n.value, out.ctypes.data_as(C.POINTER(C.c_double)),
+                                         self.nvar, C.byref(n), int(bool(clear))))
+        return out, n.value
+
     def dist_fn(self, isp, direction, ranges, resolution, dgrid, restrictions=None, use_restrictions=None):
         """particle loop of general_dist_fn (io/dist_fn.F90:532-628): this rank's weighted histogram.
         direction: 1-based c_dir_* codes; ranges [(lo, hi)] per dimension.  Returns an array shaped

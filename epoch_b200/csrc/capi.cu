@@ -35,6 +35,9 @@ static void free_species(SpeciesD& sp) {
   for (int k = 0; k < 7; ++k) { if (sp.base[k]) cudaFree(sp.base[k]); sp.base[k] = sp.a[k] = nullptr; }
   if (sp.key_base) cudaFree(sp.key_base);
   sp.key_base = nullptr; sp.off = 0; sp.deferred = false;
+  if (sp.probes.buf) cudaFree(sp.probes.buf);
+  if (sp.probes.count) cudaFree(sp.probes.count);
+  sp.probes = ProbeSet();
   if (sp.far) cudaFree(sp.far);
   sp.far = nullptr; sp.far_cap = 0;
   if (sp.dest) cudaFree(sp.dest);
@@ -432,6 +435,44 @@ int32_t eb200_calc_derived(eb200_ctx* c, int32_t kind, int32_t ispecies, int32_t
   return calc_derived(c, kind, ispecies, direction, out);
 }
 
+int32_t eb200_set_probe(eb200_ctx* c, int32_t isp, int32_t iprobe, const double* point, const double* normal, double ek_min,
+                        double ek_max) {
+  CHECK_CTX(c);
+  if (isp < 0 || (size_t)isp >= c->species.size() || !c->species[isp].defined) return fail(c, EB200_E_ARG, "set_probe: species not defined");
+  if (iprobe < 0 || iprobe >= MAX_PROBES || !point || !normal) return fail(c, EB200_E_ARG, "set_probe: iprobe 0..7, point and normal required");
+  ProbeSet& ps = c->species[isp].probes;
+  if (!ps.buf) {
+    ps.cap = c->probe_capacity;
+    EB_CUDA(c, cudaMalloc(&ps.buf, (size_t)MAX_PROBES * ps.cap * (c->ndims + 4) * sizeof(double)));
+    EB_CUDA(c, cudaMalloc(&ps.count, MAX_PROBES * sizeof(unsigned long long)));
+    EB_CUDA(c, cudaMemsetAsync(ps.count, 0, MAX_PROBES * sizeof(unsigned long long), c->stream));
+  }
+  ps.on[iprobe] = 1; ps.ek_min[iprobe] = ek_min; ps.ek_max[iprobe] = ek_max;
+  for (int d = 0; d < 3; ++d) { ps.point[iprobe][d] = d < c->ndims ? point[d] : 0.0; ps.normal[iprobe][d] = d < c->ndims ? normal[d] : 0.0; }
+  if (iprobe + 1 > ps.n) ps.n = iprobe + 1;
+  EB_CUDA(c, cudaMemsetAsync(ps.count + iprobe, 0, sizeof(unsigned long long), c->stream));
+  return 0;
+}
+int32_t eb200_download_probe(eb200_ctx* c, int32_t isp, int32_t iprobe, int64_t capacity, double* packed, int32_t nvar,
+                             int64_t* n_out, int32_t clear) {
+  CHECK_CTX(c);
+  EB_TRY(check_species(c, isp, nvar));
+  ProbeSet& ps = c->species[isp].probes;
+  if (iprobe < 0 || iprobe >= MAX_PROBES || !ps.on[iprobe] || capacity < 0) return fail(c, EB200_E_ARG, "download_probe: probe not defined");
+  unsigned long long n = 0;
+  EB_CUDA(c, cudaMemcpyAsync(&n, ps.count + iprobe, sizeof(n), cudaMemcpyDeviceToHost, c->stream));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  const long long kept = std::min<long long>((long long)n, ps.cap), m = std::min<long long>(kept, capacity);
+  if (packed && m > 0) {
+    const char* src = (const char*)(ps.buf + (size_t)iprobe * ps.cap * nvar);
+    EB_TRY(staged_d2h(c, packed, (size_t)m * nvar * sizeof(double), (size_t)nvar * sizeof(double),
+                      [src](size_t o, size_t) { return (const void*)(src + o); }));
+    EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  if (n_out) *n_out = (int64_t)n;
+  if (clear) EB_CUDA(c, cudaMemsetAsync(ps.count + iprobe, 0, sizeof(unsigned long long), c->stream));
+  return 0;
+}
 int32_t eb200_dist_fn(eb200_ctx* c, int32_t ispecies, int32_t curdims, const int32_t direction[3], const double ranges[6],
                       const int32_t resolution[3], const double dgrid[3], const double* restrictions,
                       const int32_t* use_restrictions, double* out) {
@@ -538,6 +579,7 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
     return species_reserve(c, c->species[isp], n, true);
   }
   if (k == "deposit_scratch") { c->rec_scratch_max = atoll(value) < 1024 ? 1024 : atoll(value); return 0; }
+  if (k == "probe_capacity") { c->probe_capacity = std::max<long long>(atoll(value), 16); return 0; }
   if (k == "host_threads") { c->host_threads = atoi(value); return 0; }
   if (k == "pin_bytes") {      // chunk size of the host transfers (before the first transfer)
     if (c->pin[0]) return fail(c, EB200_E_STATE, "pin_bytes: the staging ring is already allocated");

@@ -57,8 +57,20 @@ constexpr uint32_t KEY_INVALID = 0xFFFFFFFFu;
 struct FieldP { double* f[NFIELD]; };
 
 // per-species device storage: structure of arrays, fp64
+// particle probes of a species (shared_data.F90:392-404), passed to the general push kernel by value
+constexpr int MAX_PROBES = 8;
+struct ProbeSet {
+  int n = 0;                  // highest defined probe + 1
+  int on[MAX_PROBES] = {0, 0, 0, 0, 0, 0, 0, 0};
+  double point[MAX_PROBES][3], normal[MAX_PROBES][3], ek_min[MAX_PROBES], ek_max[MAX_PROBES];
+  double* buf = nullptr;                  // [MAX_PROBES][cap][nvar] sampled particles (wire format)
+  unsigned long long* count = nullptr;    // [MAX_PROBES]
+  long long cap = 0;
+};
+
 struct SpeciesD {
   bool defined = false;
+  ProbeSet probes;
   double charge = 0, mass = 0, weight = 0;
   int immobile = 0, zero_current = 0, species_type = 0;
   int bc[6] = {1, 1, 1, 1, 1, 1};
@@ -177,6 +189,7 @@ struct eb200_ctx {
   alignas(64) unsigned char tmap[128] = {0};
   long long tmap_sig[6] = {0, 0, 0, 0, 0, 0};
   bool tmap_valid = false, tmap_ok = false;
+  long long probe_capacity = 1 << 18;   // option probe_capacity: sampled particles kept per probe
   int use_tma = 1;              // option tma: 0 = stage the field tile with plain loads
   double* det_tiles = nullptr;                // deterministic deposit: one J tile per deposit CTA of a launch
   size_t det_tiles_cap = 0;                   // ... capacity in doubles

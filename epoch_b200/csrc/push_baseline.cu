@@ -39,7 +39,7 @@ template <int ND, int SHAPE>
 __global__ void __launch_bounds__(128) k_push_baseline(GridP g, FieldP F, PushP p,
     double* __restrict__ X, double* __restrict__ Y, double* __restrict__ Z,
     double* __restrict__ PX, double* __restrict__ PY, double* __restrict__ PZ,
-    const double* __restrict__ W) {
+    const double* __restrict__ W, const ProbeSet pr) {
   constexpr int NW = Sh<SHAPE>::NW, SFM = Sh<SHAPE>::SFMIN, NS = NW + 2;
   const long long ip = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (ip >= p.n) return;
@@ -95,6 +95,29 @@ __global__ void __launch_bounds__(128) k_push_baseline(GridP g, FieldP F, PushP 
     POS[d][ip] = px[d] + p.gml[d];
   }
   PX[ip] = p.part_mc * ux; PY[ip] = p.part_mc * uy; PZ[ip] = p.part_mc * uz;
+  if (pr.n > 0) {
+    // particle probes (particles.F90:567-606): energy window, then the plane crossed along its normal
+    const double gamma_rel_m1 = part_u2 / (gamma_rel + 1.0);
+    const double probe_energy = gamma_rel_m1 * (C0 * p.part_mc);
+    for (int k = 0; k < pr.n; ++k) {
+      if (!pr.on[k] || !(probe_energy > pr.ek_min[k]) || !(probe_energy < pr.ek_max[k])) continue;
+      double d_init = 0.0, d_final = 0.0;
+#pragma unroll
+      for (int d = 0; d < ND; ++d) {
+        d_init += pr.normal[k][d] * (pr.point[k][d] - pos0[d]);
+        d_final += pr.normal[k][d] * (pr.point[k][d] - (px[d] + p.gml[d]));
+      }
+      if (d_final < 0.0 && d_init >= 0.0) {
+        const unsigned long long slot = atomicAdd(pr.count + k, 1ULL);
+        if ((long long)slot < pr.cap) {
+          double* q = pr.buf + ((size_t)k * pr.cap + slot) * (ND + 4);
+#pragma unroll
+          for (int d = 0; d < ND; ++d) q[d] = px[d] + p.gml[d];
+          q[ND] = p.part_mc * ux; q[ND + 1] = p.part_mc * uy; q[ND + 2] = p.part_mc * uz; q[ND + 3] = part_weight;
+        }
+      }
+    }
+  }
   if (p.zero_current) return;
 
   // ---- deposit (particles.F90:443-563) ----
@@ -228,7 +251,7 @@ int32_t launch_push_baseline(eb200_ctx* c, const SpeciesD& sp, const PushP& p) {
 #define L(ND, SH)                                                                              \
   if (c->ndims == ND && c->shape == SH)                                                        \
     k_push_baseline<ND, SH><<<grid, block, 0, c->stream>>>(c->g, c->f, p, sp.a[0], sp.a[1],    \
-        sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6]);
+        sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.probes);
   L(1, 0) L(1, 1) L(1, 2) L(2, 0) L(2, 1) L(2, 2) L(3, 0) L(3, 1) L(3, 2)
 #undef L
   c->launches++;

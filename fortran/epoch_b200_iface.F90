@@ -26,6 +26,22 @@ MODULE epoch_b200_iface
       IMPORT :: C_INT32_T, C_PTR
       TYPE(C_PTR), VALUE :: p
     END FUNCTION eb200_host_free
+    INTEGER(C_INT32_T) FUNCTION eb200_set_probe(ctx, ispecies, iprobe, point, normal, ek_min, ek_max) &
+        BIND(C, NAME='eb200_set_probe')
+      IMPORT :: C_INT32_T, C_DOUBLE, C_PTR
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: ispecies, iprobe
+      REAL(C_DOUBLE), INTENT(IN) :: point(*), normal(*)
+      REAL(C_DOUBLE), VALUE :: ek_min, ek_max
+    END FUNCTION eb200_set_probe
+    INTEGER(C_INT32_T) FUNCTION eb200_download_probe(ctx, ispecies, iprobe, capacity, packed, nvar, n_out, clear) &
+        BIND(C, NAME='eb200_download_probe')
+      IMPORT :: C_INT32_T, C_INT64_T, C_PTR
+      TYPE(C_PTR), VALUE :: ctx, packed
+      INTEGER(C_INT32_T), VALUE :: ispecies, iprobe, nvar, clear
+      INTEGER(C_INT64_T), VALUE :: capacity
+      INTEGER(C_INT64_T), INTENT(OUT) :: n_out
+    END FUNCTION eb200_download_probe
     INTEGER(C_INT32_T) FUNCTION eb200_dist_fn(ctx, ispecies, curdims, direction, ranges, resolution, dgrid, &
         restrictions, use_restrictions, array) BIND(C, NAME='eb200_dist_fn')
       IMPORT :: C_INT32_T, C_DOUBLE, C_PTR

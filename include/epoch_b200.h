@@ -288,6 +288,18 @@ int32_t EB200_NAME(calc_derived)(EB200_CTX*, int32_t kind, int32_t ispecies, int
 int32_t EB200_NAME(dist_fn)(EB200_CTX*, int32_t ispecies, int32_t curdims, const int32_t direction[3],
                             const double ranges[6], const int32_t resolution[3], const double dgrid[3],
                             const double* restrictions, const int32_t* use_restrictions, double* out);
+/* Particle probes (particles.F90:567-606, TYPE particle_probe shared_data.F90:392-404): a plane (point, normal)
+ * and an energy window per (species, probe).  During push_particles every particle of the species whose kinetic
+ * energy (gamma - 1) m c^2 lies in (ek_min, ek_max) and that crosses the plane in the direction of the normal
+ * (d_init >= 0 > d_final, :587-592) is copied -- position and momentum at the end of the step, weight -- to the
+ * probe's list (the reference's sampled_particles), which the host reads and clears when it writes a dump.
+ * iprobe = 0..7; point/normal have ndims components.  A species with probes is pushed by the general kernel. */
+int32_t EB200_NAME(set_probe)(EB200_CTX*, int32_t ispecies, int32_t iprobe, const double* point, const double* normal,
+                              double ek_min, double ek_max);
+/* n_out: particles sampled since the last clear (those beyond option "probe_capacity", default 262144, are counted
+ * but not kept); copies min(n, capacity) of them (partlist wire format) when packed != NULL; clear != 0 empties the list */
+int32_t EB200_NAME(download_probe)(EB200_CTX*, int32_t ispecies, int32_t iprobe, int64_t capacity, double* packed,
+                                   int32_t nvar, int64_t* n_out, int32_t clear);
 /* options (key, value as strings):
  *   "deterministic_deposit" "0|1"   run-to-run bitwise reproducible currents (tiled kernels: 2D/3D)
  *   "push_kernel"   "auto|baseline|tiled"

@@ -356,6 +356,25 @@ int32_t orc_calc_derived(orc_ctx* c, int32_t kind, int32_t ispecies, int32_t dir
   calc_derived(c->s, kind, ispecies, direction, out);
   return 0;
 }
+int32_t orc_set_probe(orc_ctx* c, int32_t isp, int32_t iprobe, const double* point, const double* normal, double ek_min,
+                      double ek_max) {
+  if (!c || isp < 0 || isp >= (int32_t)c->s.species.size() || iprobe < 0 || iprobe > 7 || !point || !normal) return EB200_E_ARG;
+  orc::Species::Probe& pr = c->s.species[isp].probes[iprobe];
+  pr.on = true; pr.ek_min = ek_min; pr.ek_max = ek_max; pr.sampled.clear();
+  for (int d = 0; d < c->s.ndims; ++d) { pr.point[d] = point[d]; pr.normal[d] = normal[d]; }
+  return 0;
+}
+int32_t orc_download_probe(orc_ctx* c, int32_t isp, int32_t iprobe, int64_t capacity, double* packed, int32_t nvar,
+                           int64_t* n_out, int32_t clear) {
+  if (!c || isp < 0 || isp >= (int32_t)c->s.species.size() || iprobe < 0 || iprobe > 7 || nvar != c->s.ndims + 4) return EB200_E_ARG;
+  orc::Species::Probe& pr = c->s.species[isp].probes[iprobe];
+  if (!pr.on) return EB200_E_ARG;
+  const int64_t n = (int64_t)(pr.sampled.size() / nvar);
+  if (packed) std::copy(pr.sampled.begin(), pr.sampled.begin() + (size_t)std::min(n, capacity) * nvar, packed);
+  if (n_out) *n_out = n;
+  if (clear) pr.sampled.clear();
+  return 0;
+}
 int32_t orc_dist_fn(orc_ctx* c, int32_t ispecies, int32_t curdims, const int32_t direction[3], const double ranges[6],
                     const int32_t resolution[3], const double dgrid[3], const double* restrictions,
                     const int32_t* use_restrictions, double* out) {

@@ -121,6 +121,8 @@ void push_particles(State& s) {
       const double part_weight = sp.w[ip];
       const double fcx = fc0 * part_weight, fcy = fc1 * part_weight, fcz = fc2 * part_weight;
       double px[3] = {0, 0, 0};
+      double init_pos[3] = {0, 0, 0};                       // init_part_x, .. (particles.F90:226-228)
+      for (int d = 0; d < nd; ++d) init_pos[d] = sp.pos[d][ip];
       for (int d = 0; d < nd; ++d) px[d] = sp.pos[d][ip] - s.grid_min_local[d];
       double ux = sp.p[0][ip] * ipart_mc, uy = sp.p[1][ip] * ipart_mc, uz = sp.p[2][ip] * ipart_mc;
       double gamma_rel = std::sqrt(ux * ux + uy * uy + uz * uz + 1.0);
@@ -199,6 +201,27 @@ void push_particles(State& s) {
       for (int d = 0; d < nd; ++d) px[d] = px[d] + delta[d];
       for (int d = 0; d < nd; ++d) sp.pos[d][ip] = px[d] + s.grid_min_local[d];
       sp.p[0][ip] = part_mc * ux; sp.p[1][ip] = part_mc * uy; sp.p[2][ip] = part_mc * uz;
+      {
+        // particle probes (particles.F90:567-606; in the reference after the deposit, which does not touch
+        // the quantities used here)
+        const double gamma_rel_m1 = part_u2 / (gamma_rel + 1.0);
+        const double probe_energy = gamma_rel_m1 * (C * part_mc);
+        for (Species::Probe& pr : sp.probes) {
+          if (!pr.on) continue;
+          if (probe_energy > pr.ek_min && probe_energy < pr.ek_max) {
+            double d_init = 0.0, d_final = 0.0;
+            for (int d = 0; d < nd; ++d) {
+              d_init += pr.normal[d] * (pr.point[d] - init_pos[d]);
+              d_final += pr.normal[d] * (pr.point[d] - sp.pos[d][ip]);
+            }
+            if (d_final < 0.0 && d_init >= 0.0) {
+              for (int d = 0; d < nd; ++d) pr.sampled.push_back(sp.pos[d][ip]);
+              for (int k = 0; k < 3; ++k) pr.sampled.push_back(sp.p[k][ip]);
+              pr.sampled.push_back(part_weight);
+            }
+          }
+        }
+      }
 
       if (sp.zero_current) continue;
 

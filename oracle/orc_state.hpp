@@ -50,6 +50,9 @@ struct Species {
   int bc[6] = {BC_PERIODIC, BC_PERIODIC, BC_PERIODIC, BC_PERIODIC, BC_PERIODIC, BC_PERIODIC};
   // SoA: pos[d], p[3], w
   std::vector<double> pos[3], p[3], w;
+  // particle probes (shared_data.F90:392-404) and their sampled particles (packed pos, p(3), weight)
+  struct Probe { bool on = false; double point[3] = {0, 0, 0}, normal[3] = {0, 0, 0}, ek_min = 0, ek_max = 0; std::vector<double> sampled; };
+  Probe probes[8];
   size_t count() const { return w.size(); }
 };
 
