@@ -355,14 +355,36 @@ __global__ void k_periodic_sum(LineP p, double* a) {
   for (int i = 1; i <= ng; ++i) a[AT(b, nn - ng + i)] = a[AT(b, nn - ng + i)] + a[AT(b, i - ng)];
 }
 
-static int bc_allspecies(const eb200_ctx* c, int b) {
-  int bc = -1;
-  for (const SpeciesD& sp : c->species) if (sp.defined) { bc = sp.bc[b]; break; }
-  return bc < 0 ? EB200_BC_PERIODIC : bc;   // mixed BCs are rejected in set_species
+// particle_clear_bcs (boundary.F90:1088-1119): the ghost zones of one axis
+__global__ void k_clear_ghost_lines(LineP p, double* a) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= p.nlines) return;
+  const long long b = line_base(p, t);
+  for (int i = 1; i <= p.ng; ++i) { a[AT(b, 1 - i)] = 0.0; a[AT(b, p.nn + i)] = 0.0; }
 }
 
-// processor_summation_bcs (boundary.F90:1123-1144) on one array
-int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir) {
+static int bc_allspecies_of(const eb200_ctx* c, int b) {
+  int bc = -1;
+  for (const SpeciesD& sp : c->species) if (sp.defined) { bc = sp.bc[b]; break; }
+  return bc < 0 ? EB200_BC_PERIODIC : bc;
+}
+// ANY(bc_allspecies == c_bc_mixed) (deck_species_block.F90:231-245)
+bool bc_mixed(const eb200_ctx* c) {
+  for (int b = 0; b < 2 * c->ndims; ++b) {
+    int bc = -1;
+    for (const SpeciesD& sp : c->species) {
+      if (!sp.defined) continue;
+      if (bc < 0) bc = sp.bc[b];
+      else if (bc != sp.bc[b]) return true;
+    }
+  }
+  return false;
+}
+
+// processor_summation_bcs (boundary.F90:1123-1144) on one array.  bc6: the species form
+// (current_bcs(species) with mixed per-species boundaries): that species' codes, ghosts cleared afterwards.
+int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir, const int* bc6) {
+  auto bc_allspecies = [bc6](const eb200_ctx* cc, int b) { return bc6 ? bc6[b] : bc_allspecies_of(cc, b); };
   Arr3 A; A.a[0] = A.a[1] = A.a[2] = arr;
   for (int ax = 0; ax < c->ndims; ++ax) {
     const bool rmin = c->min_bnd[ax] && bc_allspecies(c, 2 * ax) == EB200_BC_REFLECT;
@@ -392,6 +414,13 @@ int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir) {
       EB_TRY(comm_sendrecv(c, c->halo_send, lo, c->halo_recv, hi, cnt));
       if (hi >= 0) k_unpack<<<line_grid(p, 1), 128, 0, c->stream>>>(p, A, p.nn - p.ng, c->halo_recv, 1);
       c->launches += 4;
+    }
+  }
+  if (bc6) {
+    for (int ax = 0; ax < c->ndims; ++ax) {
+      const LineP p = line_params(c, ax);
+      k_clear_ghost_lines<<<line_grid(p, 1), 128, 0, c->stream>>>(p, arr);
+      c->launches++;
     }
   }
   EB_CUDA(c, cudaGetLastError());
@@ -476,9 +505,11 @@ static int32_t smooth_current(eb200_ctx* c) {
 int32_t current_finish(eb200_ctx* c) {
   {
     ScopedPhase ph(c, "halo");
-    EB_TRY(summation_bcs(c, c->f.f[JX], 0));
-    EB_TRY(summation_bcs(c, c->f.f[JY], 1));
-    EB_TRY(summation_bcs(c, c->f.f[JZ], 2));
+    if (!bc_mixed(c)) {       // (mixed: done species by species inside push_particles, boundary.F90:1130-1136)
+      EB_TRY(summation_bcs(c, c->f.f[JX], 0));
+      EB_TRY(summation_bcs(c, c->f.f[JY], 1));
+      EB_TRY(summation_bcs(c, c->f.f[JZ], 2));
+    }
   }
   EB_TRY(field_bc(c, JX, 3));
   if (c->smooth) EB_TRY(smooth_current(c));

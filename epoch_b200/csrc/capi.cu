@@ -324,11 +324,7 @@ int32_t eb200_set_species(eb200_ctx* c, int32_t isp, double charge, double mass,
   for (int d = 0; d < c->ndims; ++d)
     if ((bcs[2 * d] == EB200_BC_PERIODIC) != (bcs[2 * d + 1] == EB200_BC_PERIODIC))
       return fail(c, EB200_E_ARG, "periodic particle boundaries must come in min/max pairs");
-  for (size_t o = 0; o < c->species.size(); ++o)
-    if (c->species[o].defined && (int)o != isp)
-      for (int i = 0; i < 6; ++i)
-        if (c->species[o].bc[i] != bcs[i])
-          return fail(c, EB200_E_UNSUPPORTED, "per-species (mixed) particle boundaries are not supported (boundary.F90:1130-1136)");
+  // (species may differ in their boundaries: bc_allspecies = c_bc_mixed, current_bcs(species) per species)
   sp.defined = true; sp.charge = charge; sp.mass = mass; sp.weight = weight;
   sp.immobile = immobile; sp.zero_current = zero_current; sp.species_type = species_type;
   for (int i = 0; i < 6; ++i) sp.bc[i] = bcs[i];
@@ -431,6 +427,7 @@ int32_t eb200_calc_derived(eb200_ctx* c, int32_t kind, int32_t ispecies, int32_t
                         kind == EB200_DF_AVERAGE_MOMENTUM;
   if (ad > 3 || (need_dir && ad == 0) || (direction < 0 && kind != EB200_DF_EKFLUX))
     return fail(c, EB200_E_ARG, "calc_derived: direction must be 1..3 (negative only for ekflux; 0 only where optional)");
+  if (bc_mixed(c)) return fail(c, EB200_E_UNSUPPORTED, "calc_derived with mixed per-species particle boundaries");
   EB_TRY(settle_particles(c));
   return calc_derived(c, kind, ispecies, direction, out);
 }
@@ -547,6 +544,7 @@ int32_t eb200_bfield_final_bcs(eb200_ctx* c) { CHECK_CTX(c); NEED_GRID(c); NEED_
 int32_t eb200_energy(eb200_ctx* c, double* fe, double* per_species) { CHECK_CTX(c); NEED_GRID(c); EB_TRY(settle_particles(c)); return energy(c, fe, per_species); }
 int32_t eb200_charge_residual(eb200_ctx* c, double* max_res, double* max_rho) {
   CHECK_CTX(c); NEED_GRID(c); NEED_DT(c);
+  if (bc_mixed(c)) return fail(c, EB200_E_UNSUPPORTED, "charge_residual with mixed per-species particle boundaries");
   EB_TRY(settle_particles(c));
   return charge_residual(c, max_res, max_rho, false);
 }

@@ -256,7 +256,8 @@ int32_t efield_bcs(eb200_ctx* c);
 int32_t bfield_bcs(eb200_ctx* c, bool mpi_only);
 int32_t bfield_final_bcs(eb200_ctx* c);
 int32_t current_finish(eb200_ctx* c);
-int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir);  // processor_summation_bcs on one array
+int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir, const int* bc6 = nullptr);  // processor_summation_bcs on one array
+bool bc_mixed(const eb200_ctx* c);                               // species with different particle boundaries
 // comm.cu
 int32_t nccl_unique_id(void* out128);
 int32_t comm_init(eb200_ctx* c, const void* id);

@@ -875,6 +875,7 @@ int32_t push_particles(eb200_ctx* c) {
     EB_CUDA(c, cudaMemsetAsync(c->f.f[JX], 0, (size_t)3 * c->g.total * sizeof(double), c->stream));
   }
   std::vector<char> done(c->species.size(), 0), tiled(c->species.size(), 0);
+  const bool mixed = bc_mixed(c);
   for (size_t is = 0; is < c->species.size(); ++is) {
     SpeciesD& sp = c->species[is];
     if (!sp.defined) continue;
@@ -939,6 +940,10 @@ int32_t push_particles(eb200_ctx* c) {
         EB_TRY(settle_species(c, sp));
         EB_TRY(launch_push_baseline(c, sp, p));
       }
+    }
+    if (mixed) {      // current_bcs(species) (particles.F90:609): fold this species' current with ITS boundaries
+      ScopedPhase ph(c, "halo");
+      for (int k = 0; k < 3; ++k) EB_TRY(summation_bcs(c, c->f.f[JX + k], k, sp.bc));
     }
     if (fused_keys && c->nproc == 1) { EB_TRY(sort_species(c, sp, sp.n, true, true)); done[is] = 1; }
     else if (fused_keys) {

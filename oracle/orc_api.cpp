@@ -191,10 +191,6 @@ int32_t orc_set_species(orc_ctx* c, int32_t isp, double charge, double mass, dou
     if (bc != BC_PERIODIC && bc != BC_REFLECT && bc != BC_OPEN) return fail(c, EB200_E_ARG, "bad particle BC");
     sp.bc[i] = bc;
   }
-  for (const Species& o : s.species)
-    if (o.defined)
-      for (int i = 0; i < 6; ++i)
-        if (o.bc[i] != sp.bc[i]) return fail(c, EB200_E_UNSUPPORTED, "mixed per-species particle BCs not supported");
   return 0;
 }
 
@@ -312,6 +308,7 @@ int32_t orc_energy(orc_ctx* c, double* fe, double* per_species) {
   return 0;
 }
 int32_t orc_charge_residual(orc_ctx* c, double* max_res, double* max_rho) {
+  if (c && bc_mixed(c->s)) return fail(c, EB200_E_UNSUPPORTED, "charge_residual with mixed per-species particle BCs");
   if (!c || !c->s.grid_set) return EB200_E_STATE;
   charge_residual(c->s, max_res, max_rho, false);
   return 0;
@@ -349,6 +346,7 @@ int32_t orc_redistribute(orc_ctx* c, const int32_t* old_cell_min, const int32_t*
 }
 int32_t orc_calc_derived(orc_ctx* c, int32_t kind, int32_t ispecies, int32_t direction, double* out) {
   if (!c || !c->s.grid_set) return EB200_E_STATE;
+  if (bc_mixed(c->s)) return fail(c, EB200_E_UNSUPPORTED, "calc_derived with mixed per-species particle BCs");
   if (!out || kind < 0 || kind > 10 || ispecies >= (int32_t)c->s.species.size()) return EB200_E_ARG;
   const int ad = direction < 0 ? -direction : direction;
   const bool need_dir = kind == 2 || kind == 3 || kind == 9 || kind == 10;

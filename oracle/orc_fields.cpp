@@ -473,7 +473,7 @@ void update_eb_fields_final(State& s) {
 }
 
 // bc_allspecies (deck_species_block.F90:231-245): common particle BC or mixed
-static int bc_allspecies(const State& s, int b) {
+int bc_allspecies_of(const State& s, int b) {
   int bc = -1;
   for (const Species& sp : s.species) {
     if (!sp.defined) continue;
@@ -487,8 +487,13 @@ static int bc_allspecies(const State& s, int b) {
 static void processor_summation_bcs(State& s, int comp, int flip_dir /*0..2*/) {
   processor_summation_array(s, s.f[comp].data(), flip_dir);
 }
-void processor_summation_array(State& s, double* a, int flip_dir) {
+bool bc_mixed(const State& s) {
+  for (int b = 0; b < 2 * s.ndims; ++b) if (bc_allspecies_of(s, b) == BC_MIXED) return true;
+  return false;
+}
+void processor_summation_array(State& s, double* a, int flip_dir, const int* bc6) {
   const int ng = s.ng;
+  auto bc_allspecies = [&](const State& st, int b) { return bc6 ? bc6[b] : ::orc::bc_allspecies_of(st, b); };
   // reflection first
   for (int ax = 0; ax < s.ndims; ++ax) {
     const int nn = s.n[ax];
@@ -528,6 +533,15 @@ void processor_summation_array(State& s, double* a, int flip_dir) {
       }
     });
   }
+  if (bc6) {      // particle_clear_bcs: every ghost zone
+    for (int ax = 0; ax < s.ndims; ++ax) {
+      const int nn = s.n[ax];
+      const int64_t sa = s.st[ax];
+      for_each_line(s, ax, [&](int64_t base) {
+        for (int i = 1; i <= ng; ++i) { a[base + (int64_t)(ng - i) * sa] = 0.0; a[base + (int64_t)(nn + i + ng - 1) * sa] = 0.0; }
+      });
+    }
+  }
 }
 
 // smooth_array, housekeeping/current_smooth.F90:61-151 (default build: strided compensated
@@ -566,9 +580,11 @@ static void smooth_array(State& s, int comp) {
 
 // housekeeping/current_smooth.F90:29-45
 void current_finish(State& s) {
-  processor_summation_bcs(s, JX, 0);
-  processor_summation_bcs(s, JY, 1);
-  processor_summation_bcs(s, JZ, 2);
+  if (!bc_mixed(s)) {       // (mixed: done species by species inside push_particles, boundary.F90:1130-1136)
+    processor_summation_bcs(s, JX, 0);
+    processor_summation_bcs(s, JY, 1);
+    processor_summation_bcs(s, JZ, 2);
+  }
   field_bc(s, JX); field_bc(s, JY); field_bc(s, JZ);
   if (s.smooth) { smooth_array(s, JX); smooth_array(s, JY); smooth_array(s, JZ); }
   if (s.use_current_correction)

@@ -327,8 +327,12 @@ void push_particles(State& s) {
         }
       }
     }
-    // current_bcs(species) is a no-op unless per-species BCs are mixed
-    // (boundary.F90:1130-1136); mixed BCs are rejected at set_species time.
+    // current_bcs(species) (particles.F90:609, boundary.F90:1976-1985): a no-op unless per-species BCs are mixed
+    if (bc_mixed(s)) {
+      processor_summation_array(s, s.f[JX].data(), 0, sp.bc);
+      processor_summation_array(s, s.f[JY].data(), 1, sp.bc);
+      processor_summation_array(s, s.f[JZ].data(), 2, sp.bc);
+    }
   }
   particle_bcs(s);
 }

@@ -122,7 +122,10 @@ void set_half_step_scalars(State& s);
 void field_bc(State& s, int comp);                 // halo (single rank: periodic wrap)
 void field_bc_array(State& s, double* a);          // the same for any array of the field shape
 void field_zero_gradient_array(State& s, double* a, bool staggered, int boundary);   // boundary.F90:623-698
-void processor_summation_array(State& s, double* a, int flip_dir);                   // boundary.F90:1123-1144
+// bc6 != null: the species form (current_bcs(species) with mixed per-species BCs): that species' boundary codes,
+// ghosts cleared afterwards (particle_clear_bcs, boundary.F90:1088-1119)
+void processor_summation_array(State& s, double* a, int flip_dir, const int* bc6 = nullptr);   // boundary.F90:1123-1144
+bool bc_mixed(const State& s);                                                      // ANY(bc_allspecies == c_bc_mixed)
 void weights_fac(int shape, double f, double* out);                                  // include/*/gxfac.inc
 void calc_derived(State& s, int kind, int ispecies, int direction, double* out);     // io/calc_df.F90
 void dist_fn(const State& s, int ispecies, int curdims, const int32_t* direction, const double* ranges,
