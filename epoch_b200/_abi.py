@@ -29,6 +29,8 @@ SIGNATURES = {
     "set_solver": (i32, [c_ctx_p, i32, i32, pf64]),
     "set_cpml": (i32, [c_ctx_p, i32, pf64, pf64, pf64, pf64, pf64, pf64, i32, i32, i32, i32, i32, i32]),
     "set_window_fields": (i32, [c_ctx_p, pf64, pf64, pf64, pf64, pf64, pf64]),
+    "setup_field_boundaries": (i32, [c_ctx_p]),
+    "set_boundary_fields": (i32, [c_ctx_p, i32, pf64, pf64, pf64, pf64, pf64, pf64]),
     "shift_window": (i32, [c_ctx_p, f64, f64, f64, f64, f64]),
     "set_current_options": (i32, [c_ctx_p, i32, i32, i32, i32, pi32, i32, pf64]),
     "set_species": (i32, [c_ctx_p, i32, f64, f64, f64, i32, i32, i32, pi32]),

@@ -118,6 +118,18 @@ class PicContext:
         ptrs = [None if a is None else a.ctypes.data_as(C.POINTER(C.c_double)) for a in keep]
         self._ck(self.abi.set_window_fields(self._ctx, *ptrs))
 
+    def setup_field_boundaries(self):
+        """setup_field_boundaries (setup.F90:426-510) from the fields now on the device"""
+        self._ck(self.abi.setup_field_boundaries(self._ctx))
+
+    def set_boundary_fields(self, boundary, planes=None):
+        """the six planes ex..bz of one boundary (1..6), None = zeros"""
+        planes = planes or {}
+        keep = [None if planes.get(k) is None else np.ascontiguousarray(planes[k], dtype=np.float64)
+                for k in ("ex", "ey", "ez", "bx", "by", "bz")]
+        ptrs = [None if a is None else a.ctypes.data_as(C.POINTER(C.c_double)) for a in keep]
+        self._ck(self.abi.set_boundary_fields(self._ctx, int(boundary), *ptrs))
+
     def shift_window(self, x_grid_min_local, x_min_local, x_max_local, x_min, x_max):
         """one cell of shift_window (window.F90:62-94) minus insert_particles"""
         self._ck(self.abi.shift_window(self._ctx, x_grid_min_local, x_min_local, x_max_local, x_min, x_max))

@@ -201,6 +201,8 @@ int32_t redistribute(eb200_ctx* c, const int32_t* old_cell_min, const int32_t* o
   cudaStreamSynchronize(c->stream);
   cudaFree(sbuf); cudaFree(rbuf); cudaFree(old_f);
   if (old_psi) cudaFree(old_psi);
+  // the boundary planes of setup_field_boundaries belong to the old slicing: the host hands them over again
+  for (int b = 0; b < 6; ++b) if (c->bnd_planes[b]) { cudaFree(c->bnd_planes[b]); c->bnd_planes[b] = nullptr; }
   if (err) return err;
   EB_CUDA(c, cudaGetLastError());
   // do_field_mpi_with_lengths on every remapped array (remap_field :1371-1374)

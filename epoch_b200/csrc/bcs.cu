@@ -242,6 +242,9 @@ struct OutflowP {
   double amp[MAX_LASERS], ph0[MAX_LASERS], cpol[MAX_LASERS], spol[MAX_LASERS];
   const double* profile[MAX_LASERS];
   const double* phase[MAX_LASERS];
+  const double* planes;      // six boundary planes ex..bz of setup_field_boundaries (or null = zero)
+  long long plane_cnt;
+  int ext_lo;                // extent of the plane's fast axis incl. ghosts
 };
 __global__ void k_outflow(GridP g, FieldP F, OutflowP p) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -264,23 +267,36 @@ __global__ void k_outflow(GridP g, FieldP F, OutflowP p) {
     source1 = source1 + base * p.cpol[l];
     source2 = source2 + base * p.spol[l];
   }
+  // boundary planes (laser.f90:536,559-572): the normal B is set to its plane, the tangential pairs add
+  // 2 (E_plane +- c B_plane)
+  double PBa = 0.0, PE1 = 0.0, PE2 = 0.0, PB1 = 0.0, PB2 = 0.0;
+  if (p.planes) {
+    const long long l = (long long)(cc[p.lo_axis] + g.ngd[p.lo_axis] - 1) + (long long)p.ext_lo * (cc[p.hi_axis] + g.ngd[p.hi_axis] - 1);
+    PBa = p.planes[(BX + p.a) * p.plane_cnt + l];
+    PE1 = p.planes[(EX + p.t1) * p.plane_cnt + l]; PE2 = p.planes[(EX + p.t2) * p.plane_cnt + l];
+    PB1 = p.planes[(BX + p.t1) * p.plane_cnt + l]; PB2 = p.planes[(BX + p.t2) * p.plane_cnt + l];
+  }
   if (!p.is_max) {
-    Ba[i - sa] = 0.0;
-    double v2 = 4.0 * source1 - 2.0 * E1[i];
+    Ba[i - sa] = PBa;
+    double v2 = 4.0 * source1 + 2.0 * (PE1 + C0 * PB2);
+    v2 = v2 - 2.0 * E1[i];
     if (p.t2 < p.nd) v2 = v2 - p.l2 * (Ba[i] - Ba[i - g.st[p.t2]]);
     v2 = v2 + p.dt_eps * J1[i] + p.diff * B2[i];
     B2[i - sa] = p.sum * v2;
-    double v1 = -4.0 * source2 + 2.0 * E2[i];
+    double v1 = -4.0 * source2 - 2.0 * (PE2 - C0 * PB1);
+    v1 = v1 + 2.0 * E2[i];
     if (p.t1 < p.nd) v1 = v1 - p.l1 * (Ba[i] - Ba[i - g.st[p.t1]]);
     v1 = v1 - p.dt_eps * J2[i] + p.diff * B1[i];
     B1[i - sa] = p.sum * v1;
   } else {
-    Ba[i + sa] = 0.0;
-    double v2 = -4.0 * source1 + 2.0 * E1[i];
+    Ba[i + sa] = PBa;
+    double v2 = -4.0 * source1 - 2.0 * (PE1 - C0 * PB2);
+    v2 = v2 + 2.0 * E1[i];
     if (p.t2 < p.nd) v2 = v2 + p.l2 * (Ba[i] - Ba[i - g.st[p.t2]]);
     v2 = v2 - p.dt_eps * J1[i] + p.diff * B2[i - sa];
     B2[i] = p.sum * v2;
-    double v1 = 4.0 * source2 - 2.0 * E2[i];
+    double v1 = 4.0 * source2 + 2.0 * (PE2 + C0 * PB1);
+    v1 = v1 - 2.0 * E2[i];
     if (p.t1 < p.nd) v1 = v1 + p.l1 * (Ba[i] - Ba[i - g.st[p.t1]]);
     v1 = v1 + p.dt_eps * J2[i] + p.diff * B1[i - sa];
     B1[i] = p.sum * v1;
@@ -311,10 +327,58 @@ static int32_t outflow_bcs(eb200_ctx* c, int b) {
       p.profile[p.nl] = L.profile; p.phase[p.nl] = L.phase;
       p.nl++;
     }
+  p.planes = c->bnd_planes[b];
+  p.ext_lo = g.n[p.lo_axis] + 2 * g.ngd[p.lo_axis];
+  p.plane_cnt = g.total / (g.n[p.a] + 2 * g.ngd[p.a]);
   const long long cnt = (long long)p.nlo * p.nhi;
   k_outflow<<<(unsigned)((cnt + 127) / 128), 128, 0, c->stream>>>(c->g, c->f, p);
   c->launches++;
   EB_CUDA(c, cudaGetLastError());
+  return 0;
+}
+
+// setup_field_boundaries (housekeeping/setup.F90:426-510): thread per point of the plane normal to axis a
+// (other axes incl. ghosts, lower axis fastest); n0 = the boundary plane (1 / n, or one beyond the laser plane)
+__global__ void k_setup_bnd(GridP g, FieldP F, int a, int n0, double* planes, long long cnt) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= cnt) return;
+  const int lo = a == 0 ? 1 : 0, hi = a == 2 ? 1 : 2;
+  const int ext_lo = g.n[lo] + 2 * g.ngd[lo];
+  int cc[3];
+  cc[a] = n0; cc[lo] = 1 - g.ngd[lo] + (int)(t % ext_lo); cc[hi] = 1 - g.ngd[hi] + (int)(t / ext_lo);
+  const long long i = g.idx(cc[0], cc[1], cc[2]);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const double* E = F.f[EX + k]; const double* B = F.f[BX + k];
+    planes[(EX + k) * cnt + t] = k == a ? 0.5 * (E[i] + E[i - g.st[a]]) : E[i];
+    planes[(BX + k) * cnt + t] = k == a ? B[i] : 0.5 * (B[i] + B[i - g.st[a]]);
+  }
+}
+int32_t setup_field_boundaries(eb200_ctx* c) {
+  const GridP& g = c->g;
+  for (int b = 0; b < 2 * c->ndims; ++b) {
+    const int a = b / 2;
+    const bool is_max = b & 1;
+    int n0 = is_max ? g.n[a] : 1;
+    if (c->bc_field[b] == EB200_BC_CPML_LASER) n0 = is_max ? c->cpml_laser_idx[b] + 1 : c->cpml_laser_idx[b] - 1;
+    const long long cnt = g.total / (g.n[a] + 2 * g.ngd[a]);
+    if (!c->bnd_planes[b]) EB_CUDA(c, cudaMalloc(&c->bnd_planes[b], 6 * cnt * sizeof(double)));
+    k_setup_bnd<<<(unsigned)((cnt + 127) / 128), 128, 0, c->stream>>>(c->g, c->f, a, n0, c->bnd_planes[b], cnt);
+    c->launches++;
+  }
+  EB_CUDA(c, cudaGetLastError());
+  return 0;
+}
+int32_t set_boundary_fields(eb200_ctx* c, int b, const double* const planes[6]) {
+  const GridP& g = c->g;
+  const int a = b / 2;
+  const size_t cnt = (size_t)(g.total / (g.n[a] + 2 * g.ngd[a]));
+  if (!c->bnd_planes[b]) EB_CUDA(c, cudaMalloc(&c->bnd_planes[b], 6 * cnt * sizeof(double)));
+  EB_CUDA(c, cudaMemsetAsync(c->bnd_planes[b], 0, 6 * cnt * sizeof(double), c->stream));
+  for (int k = 0; k < 6; ++k)
+    if (planes[k])
+      EB_CUDA(c, cudaMemcpyAsync(c->bnd_planes[b] + k * cnt, planes[k], cnt * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
   return 0;
 }
 

@@ -144,6 +144,7 @@ int32_t eb200_destroy(eb200_ctx* c) {
                   c->mig_send[0], c->mig_send[1], c->mig_recv[0], c->mig_recv[1], c->d_counters, c->d_red, c->res_ref, c->rho, c->smooth_wk, c->win_planes, c->cpml_psi, c->diag_wk,
                   c->cpml_prof[0], c->cpml_prof[1], c->cpml_prof[2]};
   for (void* p : ptrs) if (p) cudaFree(p);
+  for (int b = 0; b < 6; ++b) if (c->bnd_planes[b]) cudaFree(c->bnd_planes[b]);
   free_pinned(c);
   if (c->h_counters) cudaFreeHost(c->h_counters);
   if (c->h_red) cudaFreeHost(c->h_red);
@@ -190,7 +191,8 @@ int32_t eb200_set_grid(eb200_ctx* c, const int32_t n_local[3], const int32_t n_g
   if (c->fbase) { cudaStreamSynchronize(c->stream); cudaFree(c->fbase); c->fbase = nullptr; }
   // every work array of the field shape belongs to the old grid (set_grid again = rebalance / restart)
   double** shaped[] = {&c->rho, &c->res_ref, &c->smooth_wk, &c->win_planes, &c->cpml_psi, &c->diag_wk,
-                       &c->cpml_prof[0], &c->cpml_prof[1], &c->cpml_prof[2]};
+                       &c->cpml_prof[0], &c->cpml_prof[1], &c->cpml_prof[2], &c->bnd_planes[0], &c->bnd_planes[1],
+                       &c->bnd_planes[2], &c->bnd_planes[3], &c->bnd_planes[4], &c->bnd_planes[5]};
   for (double** p : shaped)
     if (*p) { cudaFree(*p); *p = nullptr; }
   EB_CUDA(c, cudaMalloc(&c->fbase, (size_t)NFIELD * g.total * sizeof(double)));
@@ -294,6 +296,17 @@ int32_t eb200_set_window_fields(eb200_ctx* c, const double* ex, const double* ey
   CHECK_CTX(c); NEED_GRID(c);
   const double* pl[6] = {ex, ey, ez, bx, by, bz};
   return set_window_planes(c, pl);
+}
+int32_t eb200_setup_field_boundaries(eb200_ctx* c) {
+  CHECK_CTX(c); NEED_GRID(c);
+  return setup_field_boundaries(c);
+}
+int32_t eb200_set_boundary_fields(eb200_ctx* c, int32_t boundary, const double* ex, const double* ey, const double* ez,
+                                  const double* bx, const double* by, const double* bz) {
+  CHECK_CTX(c); NEED_GRID(c);
+  if (boundary < 1 || boundary > 2 * c->ndims) return fail(c, EB200_E_ARG, "boundary out of range");
+  const double* pl[6] = {ex, ey, ez, bx, by, bz};
+  return set_boundary_fields(c, boundary - 1, pl);
 }
 int32_t eb200_shift_window(eb200_ctx* c, double x_grid_min_local, double x_min_local, double x_max_local, double x_min,
                            double x_max) {

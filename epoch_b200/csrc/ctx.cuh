@@ -152,6 +152,7 @@ struct eb200_ctx {
   double* diag_wk = nullptr;        // 5 arrays of g.total doubles (calc_derived)
   double* cpml_psi = nullptr;       // 12 arrays of g.total doubles (allocated when a CPML side exists)
   double* win_planes = nullptr;     // moving window: e*_x_max, b*_x_max planes (6 x y-z extent with ghosts)
+  double* bnd_planes[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // setup_field_boundaries: per boundary 6 planes (ex..bz)
   double* fbase = nullptr;     // 9 * total doubles
   eb::FieldP f;
   std::vector<eb::SpeciesD> species;
@@ -255,6 +256,8 @@ int32_t dist_fn(eb200_ctx* c, int ispecies, int curdims, const int32_t* directio
 int32_t efield_bcs(eb200_ctx* c);
 int32_t bfield_bcs(eb200_ctx* c, bool mpi_only);
 int32_t bfield_final_bcs(eb200_ctx* c);
+int32_t setup_field_boundaries(eb200_ctx* c);
+int32_t set_boundary_fields(eb200_ctx* c, int b, const double* const planes[6]);
 int32_t current_finish(eb200_ctx* c);
 int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir, const int* bc6 = nullptr);  // processor_summation_bcs on one array
 bool bc_mixed(const eb200_ctx* c);                               // species with different particle boundaries

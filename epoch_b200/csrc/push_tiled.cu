@@ -157,6 +157,58 @@ __device__ __forceinline__ void box3(double* acc, const double (*g)[NW], const d
     }
 }
 
+// The same interpolation with the x row fetched as aligned 16-byte pairs (LDS.128): the row starts at the even
+// column e = bx & ~1 and the NW weights are shifted by the parity of bx inside a vector of 2 * NP weights
+// (zero in the unused slot), so a row costs NP loads instead of NW.  Same value as gather_tile: the extra term is
+// an exact zero at either end of the sum.
+#ifndef EB_PAIR
+#define EB_PAIR 1
+#endif
+template <int SHAPE>
+struct PairW {
+  static constexpr int NW = Sh<SHAPE>::NW, NP = (NW + 2) / 2;
+  double w[2 * NP];
+  int e;
+  __device__ __forceinline__ void set(const double* wx, int bx) {
+    const bool odd = bx & 1;
+    e = bx & ~1;
+#pragma unroll
+    for (int i = 0; i < 2 * NP; ++i) {
+      const double lo = i < NW ? wx[i < NW ? i : 0] : 0.0;            // even start: slot i holds weight i
+      const double hi = i >= 1 && i - 1 < NW ? wx[i >= 1 && i - 1 < NW ? i - 1 : 0] : 0.0;   // odd start: weight i - 1
+      w[i] = odd ? hi : lo;
+    }
+  }
+};
+template <int ND, int SHAPE>
+__device__ __forceinline__ double gather_tile_pair(const double* __restrict__ f, const PairW<SHAPE>& wx, const double* wy,
+                                                   const double* wz, int by, int bz) {
+  using T = TL<ND, SHAPE>;
+  constexpr int NW = T::NW, NP = PairW<SHAPE>::NP;
+  const double2* b = reinterpret_cast<const double2*>(f + (ND >= 3 ? bz : 0) * T::FZS + (ND >= 2 ? by : 0) * T::FX + wx.e);
+  double accz = 0.0;
+#pragma unroll
+  for (int k = 0; k < (ND >= 3 ? NW : 1); ++k) {
+    double accy = 0.0;
+#pragma unroll
+    for (int j = 0; j < (ND >= 2 ? NW : 1); ++j) {
+      double accx = 0.0;
+#pragma unroll
+      for (int i = 0; i < NP; ++i) {
+        const double2 v = b[(k * T::FZS + j * T::FX) / 2 + i];
+        const double t = wx.w[2 * i] * v.x;
+        accx = i == 0 ? t : accx + t;
+        accx = accx + wx.w[2 * i + 1] * v.y;
+      }
+      if (ND >= 2) { const double t = wy[j] * accx; accy = j == 0 ? t : accy + t; }
+      else accy = accx;
+    }
+    if (ND >= 3) { const double t = wz[k] * accy; accz = k == 0 ? t : accz + t; }
+    else accz = accy;
+  }
+  return accz;
+}
+
 template <int N>
 __device__ __forceinline__ double pick(const double* a, int t) {
   double r = a[0];
@@ -346,12 +398,25 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
   if (bad) atomicAdd(counters + 8, 1ULL);   // key and push disagree on the cell: must never happen
   // region index of weight slot i: g-type l1 + 1 + i, h-type l2 + 1 + i
   const int gx = l1[0] + 1, gy = l1[1] + 1, gz = l1[2] + 1, hx = l2[0] + 1, hy = l2[1] + 1, hz = l2[2] + 1;
-  const double ex_part = gather_tile<ND, SHAPE>(sF + 0 * T::FCS, wh[0], wg[1], wg[2], hx, gy, gz);
-  const double ey_part = gather_tile<ND, SHAPE>(sF + 1 * T::FCS, wg[0], wh[1], wg[2], gx, hy, gz);
-  const double ez_part = gather_tile<ND, SHAPE>(sF + 2 * T::FCS, wg[0], wg[1], wh[2], gx, gy, hz);
-  const double bx_part = gather_tile<ND, SHAPE>(sF + 3 * T::FCS, wg[0], wh[1], wh[2], gx, hy, hz);
-  const double by_part = gather_tile<ND, SHAPE>(sF + 4 * T::FCS, wh[0], wg[1], wh[2], hx, gy, hz);
-  const double bz_part = gather_tile<ND, SHAPE>(sF + 5 * T::FCS, wh[0], wh[1], wg[2], hx, hy, gz);
+  double ex_part, ey_part, ez_part, bx_part, by_part, bz_part;
+  if (EB_PAIR && SHAPE != SHAPE_TOPHAT && (T::FX % 2 == 0) && (T::FZS % 2 == 0)) {
+    PairW<SHAPE> pg, ph;
+    pg.set(wg[0], gx);
+    ph.set(wh[0], hx);
+    ex_part = gather_tile_pair<ND, SHAPE>(sF + 0 * T::FCS, ph, wg[1], wg[2], gy, gz);
+    ey_part = gather_tile_pair<ND, SHAPE>(sF + 1 * T::FCS, pg, wh[1], wg[2], hy, gz);
+    ez_part = gather_tile_pair<ND, SHAPE>(sF + 2 * T::FCS, pg, wg[1], wh[2], gy, hz);
+    bx_part = gather_tile_pair<ND, SHAPE>(sF + 3 * T::FCS, pg, wh[1], wh[2], hy, hz);
+    by_part = gather_tile_pair<ND, SHAPE>(sF + 4 * T::FCS, ph, wg[1], wh[2], gy, hz);
+    bz_part = gather_tile_pair<ND, SHAPE>(sF + 5 * T::FCS, ph, wh[1], wg[2], hy, gz);
+  } else {
+    ex_part = gather_tile<ND, SHAPE>(sF + 0 * T::FCS, wh[0], wg[1], wg[2], hx, gy, gz);
+    ey_part = gather_tile<ND, SHAPE>(sF + 1 * T::FCS, wg[0], wh[1], wg[2], gx, hy, gz);
+    ez_part = gather_tile<ND, SHAPE>(sF + 2 * T::FCS, wg[0], wg[1], wh[2], gx, gy, hz);
+    bx_part = gather_tile<ND, SHAPE>(sF + 3 * T::FCS, wg[0], wh[1], wh[2], gx, hy, hz);
+    by_part = gather_tile<ND, SHAPE>(sF + 4 * T::FCS, wh[0], wg[1], wh[2], hx, gy, hz);
+    bz_part = gather_tile<ND, SHAPE>(sF + 5 * T::FCS, wh[0], wh[1], wg[2], hx, hy, gz);
+  }
 
   boris(ux, uy, uz, ex_part, ey_part, ez_part, bx_part, by_part, bz_part, p.cmratio, p.ccmratio);
 
@@ -781,6 +846,29 @@ __global__ void __launch_bounds__(NTA, SHAPE == SHAPE_BSPLINE3 ? 2 : EB_MINB_A) 
 
 constexpr int SUB = 2;           // a deposit CTA owns 1/SUB of a tile, split along the slowest tile axis
 
+// Lane balance of the deposit kernel (EB_BALANCE): a thread owns one cell and a warp runs as long as its fullest
+// cell, so the cells are dealt to the warps by particle count.  Any permutation of cells over threads keeps the
+// register-box flush valid (the cells of a step stay distinct), but the flush is conflict-free only if a warp
+// holds exactly two cells of each of the 16 shared-memory bank classes (8-byte words): the cells of a class are
+// ranked by count and warp w takes ranks 2w and 2w + 1 of every class.  Available when the sub-tile's cells fall
+// evenly into the classes (3D triangle, 2D triangle / bspline3).
+#ifndef EB_BALANCE
+#define EB_BALANCE 1
+#endif
+template <int ND, int SHAPE>
+constexpr bool uniform_bank_classes() {
+  using T = TL<ND, SHAPE>;
+  constexpr int NTB = T::CPT / SUB;
+  int cnt[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  for (int c = 0; c < NTB; ++c) {
+    const int l0 = c % T::TX, l1 = (c / T::TX) % T::TY, l2 = c / (T::TX * T::TY);
+    cnt[(l0 + l1 * T::JX + (ND == 3 ? l2 * T::JX * T::JY : 0)) & 15]++;
+  }
+  for (int b = 0; b < 16; ++b)
+    if (cnt[b] != NTB / 16) return false;
+  return NTB % 64 == 0;
+}
+
 __device__ __forceinline__ void load_rec(double* r, const double* src) {
   const double2* s2 = reinterpret_cast<const double2*>(src);
 #pragma unroll
@@ -846,7 +934,32 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   //      fetched while the current one is deposited.  ONEC (3D bspline3: 3 x 100 accumulators):
   //      one pass over the cell's records per component instead ----
   constexpr bool ONEC = 3 * NA > 128 || (EB_ONEC && ND == 3);
-  const int lc = sub * NTB + tid;
+  int lc = sub * NTB + tid;
+  if (EB_BALANCE && uniform_bank_classes<ND, SHAPE>()) {
+    constexpr int PER = NTB / 16;                 // cells per bank class
+    int* cls_n = sM;                              // (the work-item list is not in use yet)
+    int* cls_list = sM + 16;                      // [16][PER] count << 8 | cell
+    int* cell_of = sM + 16 + NTB;                 // [16][PER] cell of (class, rank)
+    if (tid < 16) cls_n[tid] = 0;
+    __syncthreads();
+    const int n0 = (int)min(cell_start[kbase + lc + 1] - cell_start[kbase + lc], 0x7fffffu);
+    const int m0 = tid % T::TX, m1 = (tid / T::TX) % T::TY, m2 = tid / (T::TX * T::TY);
+    const int cls = (m0 + m1 * JXs + (ND == 3 ? m2 * JXs * JYs : 0)) & 15;
+    cls_list[cls * PER + atomicAdd(cls_n + cls, 1)] = n0 << 8 | tid;
+    __syncthreads();
+    int r = 0;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) {
+      const int e = cls_list[cls * PER + i];
+      r += ((e >> 8) > n0 || ((e >> 8) == n0 && (e & 255) < tid)) ? 1 : 0;
+    }
+    cell_of[cls * PER + r] = tid;
+    __syncthreads();
+    // fullest cells to warp (0 + rot): neighbouring CTAs rotate so that an SM sub-partition sees a mix
+    const int w = (warp + (int)(blockIdx.x & 3)) % (NTB / 32);
+    lc = sub * NTB + cell_of[(lane & 15) * PER + (PER / (NTB / 32)) * w + (lane >> 4)];
+    __syncthreads();
+  }
   const uint32_t my_b = cell_start[kbase + lc], my_e = cell_start[kbase + lc + 1];
   int l[3] = {lc % T::TX, (lc / T::TX) % T::TY, lc / (T::TX * T::TY)};
   l[SA] -= sub * TS;

@@ -361,6 +361,9 @@ class Simulation:
         """epoch3d.F90:141-158: particle_bcs; efield_bcs; half-dt bfield_final_bcs."""
         ctx = self.ctx
         ctx.set_time(self.dt, self.time, self.step)
+        if not getattr(self, "_bnd_fields_done", False):
+            ctx.setup_field_boundaries()      # after_deck_last (setup.F90:241): planes of the initial fields
+            self._bnd_fields_done = True
         ctx.particle_bcs()
         ctx.efield_bcs()
         dt_store = self.dt

@@ -157,6 +157,18 @@ int32_t EB200_NAME(set_current_options)(EB200_CTX*, int32_t smooth, int32_t smoo
 int32_t EB200_NAME(set_window_fields)(EB200_CTX*, const double* ex_x_max, const double* ey_x_max,
                                       const double* ez_x_max, const double* bx_x_max,
                                       const double* by_x_max, const double* bz_x_max);
+/* setup_field_boundaries (housekeeping/setup.F90:426-510, called from after_deck_last :241): capture, from
+ * the fields NOW on the device, the 36 planes ex_x_min .. bz_z_max -- the field at the boundary plane
+ * (tangential E, normal B) or the mean of the boundary plane and the one below it (normal E, tangential B);
+ * the plane beyond the laser plane on a cpml_laser side.  outflow_bcs_* add them back at open / laser
+ * boundaries (laser.f90:536,559-572 and the five cyclic copies): an external static field, or the fields of a
+ * restart, pass through such a boundary unchanged.  Without the call the planes are zero.
+ * set_boundary_fields uploads the six planes of ONE boundary (1..6 = x_min, x_max, y_min, ...; each over the
+ * other axes incl. ghosts, lower axis fastest; NULL = zero) -- for a host that keeps its own copies, and after
+ * redistribute, which drops them. */
+int32_t EB200_NAME(setup_field_boundaries)(EB200_CTX*);
+int32_t EB200_NAME(set_boundary_fields)(EB200_CTX*, int32_t boundary, const double* ex, const double* ey,
+                                        const double* ez, const double* bx, const double* by, const double* bz);
 int32_t EB200_NAME(shift_window)(EB200_CTX*, double x_grid_min_local, double x_min_local, double x_max_local,
                                  double x_min, double x_max);
 

@@ -141,6 +141,24 @@ int32_t orc_set_window_fields(orc_ctx* c, const double* ex, const double* ey, co
   }
   return 0;
 }
+int32_t orc_setup_field_boundaries(orc_ctx* c) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  orc::setup_field_boundaries(c->s);
+  return 0;
+}
+int32_t orc_set_boundary_fields(orc_ctx* c, int32_t boundary, const double* ex, const double* ey, const double* ez,
+                                const double* bx, const double* by, const double* bz) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  if (boundary < 1 || boundary > 2 * c->s.ndims) return fail(c, EB200_E_ARG, "boundary out of range");
+  const int b = boundary - 1, a = b / 2;
+  const double* pl[6] = {ex, ey, ez, bx, by, bz};
+  const size_t cnt = (size_t)(c->s.total / (c->s.n[a] + 2 * c->s.ngd[a]));
+  for (int k = 0; k < 6; ++k) {
+    c->s.bnd_planes[b][k].assign(cnt, 0.0);
+    if (pl[k]) std::copy(pl[k], pl[k] + cnt, c->s.bnd_planes[b][k].begin());
+  }
+  return 0;
+}
 int32_t orc_shift_window(orc_ctx* c, double x_grid_min_local, double x_min_local, double x_max_local, double x_min,
                          double x_max) {
   if (!c || !c->s.grid_set) return EB200_E_STATE;

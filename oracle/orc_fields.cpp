@@ -376,8 +376,41 @@ void bfield_bcs(State& s, bool mpi_only) {
 
 // laser.f90:509-973 outflow_bcs_{x,y,z}_{min,max} (1D epoch1d/src/laser.f90:303,
 // 2D epoch2d/src/laser.f90:411).  The six routines are cyclic permutations of one
-// another: normal axis a, tangential t1=a+1, t2=a+2.  External boundary fields
-// (ex_x_min ... from the deck's `fields` block) are zero here.
+// another: normal axis a, tangential t1=a+1, t2=a+2.  The boundary planes ex_x_min ... (the fields the run started
+// with, setup_field_boundaries) enter as in laser.f90:536,559-572.
+
+// index of grid point c[] in a plane normal to axis a (other axes incl. ghosts, lower axis fastest)
+static inline size_t plane_index(const State& s, int a, const int* c) {
+  const int lo = a == 0 ? 1 : 0, hi = a == 2 ? 1 : 2;
+  const size_t ext_lo = (size_t)(s.n[lo] + 2 * s.ngd[lo]);
+  return (size_t)(c[lo] + s.ngd[lo] - 1) + ext_lo * (size_t)(c[hi] + s.ngd[hi] - 1);
+}
+
+// housekeeping/setup.F90:426-510: e?_x_min = the field at nx0 (tangential E, normal B) or the mean of the
+// planes nx0 and nx0 - 1 (normal E, tangential B); nx0 = 1 / nx, or one beyond the laser plane of a cpml_laser side
+void setup_field_boundaries(State& s) {
+  for (int b = 0; b < 2 * s.ndims; ++b) {
+    const int a = b / 2;
+    const bool is_max = b & 1;
+    int n0 = is_max ? s.n[a] : 1;
+    if (s.bc_field[b] == BC_CPML_LASER) n0 = is_max ? s.cpml_laser_idx[b] + 1 : s.cpml_laser_idx[b] - 1;
+    const int lo = a == 0 ? 1 : 0, hi = a == 2 ? 1 : 2;
+    const size_t cnt = (size_t)(s.n[lo] + 2 * s.ngd[lo]) * (size_t)(s.n[hi] + 2 * s.ngd[hi]);
+    for (int k = 0; k < 6; ++k) s.bnd_planes[b][k].assign(cnt, 0.0);
+    for (int q = 1 - s.ngd[hi]; q <= s.n[hi] + s.ngd[hi]; ++q)
+      for (int p = 1 - s.ngd[lo]; p <= s.n[lo] + s.ngd[lo]; ++p) {
+        int c[3]; c[a] = n0; c[lo] = p; c[hi] = q;
+        const int64_t i = s.idx(c[0], c[1], c[2]);
+        const size_t l = plane_index(s, a, c);
+        for (int k = 0; k < 3; ++k) {
+          const double* E = s.f[EX + k].data(); const double* B = s.f[BX + k].data();
+          s.bnd_planes[b][EX + k][l] = k == a ? 0.5 * (E[i] + E[i - s.st[a]]) : E[i];
+          s.bnd_planes[b][BX + k][l] = k == a ? B[i] : 0.5 * (B[i] + B[i - s.st[a]]);
+        }
+      }
+  }
+}
+
 static void outflow_bcs(State& s, int boundary) {
   const int a = boundary / 2, t1 = (a + 1) % 3, t2 = (a + 2) % 3;
   const bool is_max = boundary & 1;
@@ -418,23 +451,28 @@ static void outflow_bcs(State& s, int boundary) {
           }
         }
       }
+      const bool have = !s.bnd_planes[boundary][0].empty();
+      const size_t pl = have ? plane_index(s, a, c) : 0;
+      const double PBa = have ? s.bnd_planes[boundary][BX + a][pl] : 0.0;
+      const double PE1 = have ? s.bnd_planes[boundary][EX + t1][pl] : 0.0, PE2 = have ? s.bnd_planes[boundary][EX + t2][pl] : 0.0;
+      const double PB1 = have ? s.bnd_planes[boundary][BX + t1][pl] : 0.0, PB2 = have ? s.bnd_planes[boundary][BX + t2][pl] : 0.0;
       if (!is_max) {
-        Ba[i - sa] = 0.0;  // bx(laserpos-1) = bx_x_min
-        double v2 = 4.0 * source1 + 2.0 * (0.0 + C * 0.0) - 2.0 * E1[i];
+        Ba[i - sa] = PBa;  // bx(laserpos-1) = bx_x_min
+        double v2 = 4.0 * source1 + 2.0 * (PE1 + C * PB2) - 2.0 * E1[i];
         if (t2 < s.ndims) v2 = v2 - l2 * (Ba[i] - Ba[i - s.st[t2]]);
         v2 = v2 + dt_eps * J1[i] + diff * B2[i];
         B2[i - sa] = sum * v2;
-        double v1 = -4.0 * source2 - 2.0 * (0.0 - C * 0.0) + 2.0 * E2[i];
+        double v1 = -4.0 * source2 - 2.0 * (PE2 - C * PB1) + 2.0 * E2[i];
         if (t1 < s.ndims) v1 = v1 - l1 * (Ba[i] - Ba[i - s.st[t1]]);
         v1 = v1 - dt_eps * J2[i] + diff * B1[i];
         B1[i - sa] = sum * v1;
       } else {
-        Ba[i + sa] = 0.0;  // bx(laserpos+1) = bx_x_max
-        double v2 = -4.0 * source1 - 2.0 * (0.0 - C * 0.0) + 2.0 * E1[i];
+        Ba[i + sa] = PBa;  // bx(laserpos+1) = bx_x_max
+        double v2 = -4.0 * source1 - 2.0 * (PE1 - C * PB2) + 2.0 * E1[i];
         if (t2 < s.ndims) v2 = v2 + l2 * (Ba[i] - Ba[i - s.st[t2]]);
         v2 = v2 - dt_eps * J1[i] + diff * B2[i - sa];
         B2[i] = sum * v2;
-        double v1 = 4.0 * source2 + 2.0 * (0.0 + C * 0.0) - 2.0 * E2[i];
+        double v1 = 4.0 * source2 + 2.0 * (PE2 + C * PB1) - 2.0 * E2[i];
         if (t1 < s.ndims) v1 = v1 + l1 * (Ba[i] - Ba[i - s.st[t1]]);
         v1 = v1 + dt_eps * J2[i] + diff * B1[i - sa];
         B1[i] = sum * v1;

@@ -97,6 +97,9 @@ struct State {
   int cpml_laser_idx[6] = {1, 1, 1, 1, 1, 1};
   std::vector<double> cpml_psi[3][4];
   std::vector<double> win_planes[6];   // moving window: e*_x_max, b*_x_max (setup.F90:425-470)
+  // setup_field_boundaries (setup.F90:426-510): per boundary the planes ex..bz over the other axes incl. ghosts
+  // (x fastest in (lower axis, higher axis) order); empty = zero
+  std::vector<double> bnd_planes[6][6];
   // half-step scalars (fields.f90:821-830)
   double hdt = 0, hdtd[3] = {0, 0, 0}, cn[3] = {0, 0, 0}, fac = 0;
   std::vector<double> f[NFIELD];
@@ -134,6 +137,7 @@ void dist_fn(const State& s, int ispecies, int curdims, const int32_t* direction
 void efield_bcs(State& s);
 void bfield_bcs(State& s, bool mpi_only);
 void bfield_final_bcs(State& s);
+void setup_field_boundaries(State& s);
 void update_eb_fields_half(State& s);
 void update_eb_fields_final(State& s);
 void current_finish(State& s);
