@@ -201,8 +201,16 @@ int32_t redistribute(eb200_ctx* c, const int32_t* old_cell_min, const int32_t* o
   cudaStreamSynchronize(c->stream);
   cudaFree(sbuf); cudaFree(rbuf); cudaFree(old_f);
   if (old_psi) cudaFree(old_psi);
-  // the boundary planes of setup_field_boundaries belong to the old slicing: the host hands them over again
-  for (int b = 0; b < 6; ++b) if (c->bnd_planes[b]) { cudaFree(c->bnd_planes[b]); c->bnd_planes[b] = nullptr; }
+  // the boundary planes of setup_field_boundaries (the reference's host remaps its own copies, balance.F90:847-1010):
+  // a plane whose extents changed belongs to the old slicing and is dropped -- outflow_bcs then refuses to run
+  // until the host has handed it over again (set_boundary_fields)
+  for (int b = 0; b < 2 * c->ndims; ++b) {
+    if (!c->bnd_planes[b]) continue;
+    const int a = b / 2;
+    if (og.total / (og.n[a] + 2 * og.ngd[a]) == g.total / (g.n[a] + 2 * g.ngd[a]) &&
+        og.n[(a + 1) % 3] == g.n[(a + 1) % 3] && og.n[(a + 2) % 3] == g.n[(a + 2) % 3]) continue;
+    cudaFree(c->bnd_planes[b]); c->bnd_planes[b] = nullptr; c->bnd_dropped[b] = true;
+  }
   if (err) return err;
   EB_CUDA(c, cudaGetLastError());
   // do_field_mpi_with_lengths on every remapped array (remap_field :1371-1374)

@@ -79,6 +79,31 @@ __global__ void k_unpack(LineP p, Arr3 A, int c0, const double* buf, int add) {
   }
 }
 
+// both sides in one launch (blockIdx.z = side): side 0 uses (c0a, bufa), side 1 (c0b, bufb); on = which sides exist
+__global__ void k_pack2(LineP p, Arr3 A, int c0a, int c0b, double* bufa, double* bufb) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= p.nlines) return;
+  const double* a = A.a[blockIdx.y];
+  const long long b = line_base(p, t);
+  const int c0 = blockIdx.z ? c0b : c0a;
+  double* o = (blockIdx.z ? bufb : bufa) + (long long)blockIdx.y * p.ng * p.nlines;
+  for (int i = 1; i <= p.ng; ++i) o[(long long)(i - 1) * p.nlines + t] = a[AT(b, c0 + i)];
+}
+__global__ void k_unpack2(LineP p, Arr3 A, int c0a, int c0b, const double* bufa, const double* bufb, int add, int on_a, int on_b) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= p.nlines) return;
+  if (blockIdx.z ? !on_b : !on_a) return;
+  double* a = A.a[blockIdx.y];
+  const long long b = line_base(p, t);
+  const int c0 = blockIdx.z ? c0b : c0a;
+  const double* o = (blockIdx.z ? bufb : bufa) + (long long)blockIdx.y * p.ng * p.nlines;
+  for (int i = 1; i <= p.ng; ++i) {
+    const double v = o[(long long)(i - 1) * p.nlines + t];
+    if (add) a[AT(b, c0 + i)] += v; else a[AT(b, c0 + i)] = v;
+  }
+}
+static inline dim3 line_grid2(const LineP& p, int ncomp) { dim3 g = line_grid(p, ncomp); g.z = 2; return g; }
+
 static int32_t ensure_halo(eb200_ctx* c, size_t doubles) {
   if (c->halo_bytes >= doubles * sizeof(double)) return 0;
   if (c->halo_send) cudaFree(c->halo_send);
@@ -116,17 +141,15 @@ static int32_t field_bc_arrays(eb200_ctx* c, Arr3 A, int ncomp) {
       c->launches++;
     } else {
       const size_t cnt = (size_t)ncomp * p.ng * p.nlines;
-      EB_TRY(ensure_halo(c, cnt));
-      const int lo = c->nbr_lo[ax], hi = c->nbr_hi[ax];
-      // send A(1:ng) to the low neighbour, receive A(nn+1:nn+ng) from the high one
-      k_pack<<<line_grid(p, ncomp), 128, 0, c->stream>>>(p, A, 0, c->halo_send);
-      EB_TRY(comm_sendrecv(c, c->halo_send, fill_min ? lo : -1, c->halo_recv, fill_max ? hi : -1, cnt));
-      if (fill_max && hi >= 0) k_unpack<<<line_grid(p, ncomp), 128, 0, c->stream>>>(p, A, p.nn, c->halo_recv, 0);
-      // send A(nn+1-ng:nn) to the high neighbour, receive A(1-ng:0) from the low one
-      k_pack<<<line_grid(p, ncomp), 128, 0, c->stream>>>(p, A, p.nn - p.ng, c->halo_send);
-      EB_TRY(comm_sendrecv(c, c->halo_send, fill_max ? hi : -1, c->halo_recv, fill_min ? lo : -1, cnt));
-      if (fill_min && lo >= 0) k_unpack<<<line_grid(p, ncomp), 128, 0, c->stream>>>(p, A, -p.ng, c->halo_recv, 0);
-      c->launches += 4;
+      EB_TRY(ensure_halo(c, 2 * cnt));
+      const int lo = fill_min ? c->nbr_lo[ax] : -1, hi = fill_max ? c->nbr_hi[ax] : -1;
+      // A(1:ng) goes to the low neighbour and A(nn+1-ng:nn) to the high one; A(nn+1:nn+ng) comes from the high
+      // neighbour and A(1-ng:0) from the low one: one pack, ONE exchange (both directions, all components), one unpack
+      double *s_lo = c->halo_send, *s_hi = c->halo_send + cnt, *r_hi = c->halo_recv, *r_lo = c->halo_recv + cnt;
+      k_pack2<<<line_grid2(p, ncomp), 128, 0, c->stream>>>(p, A, 0, p.nn - p.ng, s_lo, s_hi);
+      EB_TRY(comm_exchange2(c, s_lo, lo, cnt, s_hi, hi, cnt, r_hi, hi, cnt, r_lo, lo, cnt));
+      k_unpack2<<<line_grid2(p, ncomp), 128, 0, c->stream>>>(p, A, p.nn, -p.ng, r_hi, r_lo, 0, hi >= 0, lo >= 0);
+      c->launches += 2;
     }
   }
   EB_CUDA(c, cudaGetLastError());
@@ -327,6 +350,8 @@ static int32_t outflow_bcs(eb200_ctx* c, int b) {
       p.profile[p.nl] = L.profile; p.phase[p.nl] = L.phase;
       p.nl++;
     }
+  if (c->bnd_dropped[b])
+    return fail(c, EB200_E_STATE, "the boundary planes of this side were dropped by redistribute: call set_boundary_fields");
   p.planes = c->bnd_planes[b];
   p.ext_lo = g.n[p.lo_axis] + 2 * g.ngd[p.lo_axis];
   p.plane_cnt = g.total / (g.n[p.a] + 2 * g.ngd[p.a]);
@@ -363,6 +388,7 @@ int32_t setup_field_boundaries(eb200_ctx* c) {
     if (c->bc_field[b] == EB200_BC_CPML_LASER) n0 = is_max ? c->cpml_laser_idx[b] + 1 : c->cpml_laser_idx[b] - 1;
     const long long cnt = g.total / (g.n[a] + 2 * g.ngd[a]);
     if (!c->bnd_planes[b]) EB_CUDA(c, cudaMalloc(&c->bnd_planes[b], 6 * cnt * sizeof(double)));
+    c->bnd_dropped[b] = false;
     k_setup_bnd<<<(unsigned)((cnt + 127) / 128), 128, 0, c->stream>>>(c->g, c->f, a, n0, c->bnd_planes[b], cnt);
     c->launches++;
   }
@@ -374,6 +400,7 @@ int32_t set_boundary_fields(eb200_ctx* c, int b, const double* const planes[6]) 
   const int a = b / 2;
   const size_t cnt = (size_t)(g.total / (g.n[a] + 2 * g.ngd[a]));
   if (!c->bnd_planes[b]) EB_CUDA(c, cudaMalloc(&c->bnd_planes[b], 6 * cnt * sizeof(double)));
+  c->bnd_dropped[b] = false;
   EB_CUDA(c, cudaMemsetAsync(c->bnd_planes[b], 0, 6 * cnt * sizeof(double), c->stream));
   for (int k = 0; k < 6; ++k)
     if (planes[k])
@@ -447,16 +474,18 @@ bool bc_mixed(const eb200_ctx* c) {
 
 // processor_summation_bcs (boundary.F90:1123-1144) on one array.  bc6: the species form
 // (current_bcs(species) with mixed per-species boundaries): that species' codes, ghosts cleared afterwards.
-int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir, const int* bc6) {
+// processor_summation_bcs for ncomp arrays at once (flip[k] = the wall-normal axis whose reflection flips the sign of array k)
+static int32_t summation_bcs_n(eb200_ctx* c, Arr3 A, int ncomp, const int* flip, const int* bc6) {
   auto bc_allspecies = [bc6](const eb200_ctx* cc, int b) { return bc6 ? bc6[b] : bc_allspecies_of(cc, b); };
-  Arr3 A; A.a[0] = A.a[1] = A.a[2] = arr;
   for (int ax = 0; ax < c->ndims; ++ax) {
     const bool rmin = c->min_bnd[ax] && bc_allspecies(c, 2 * ax) == EB200_BC_REFLECT;
     const bool rmax = c->max_bnd[ax] && bc_allspecies(c, 2 * ax + 1) == EB200_BC_REFLECT;
     if (!rmin && !rmax) continue;
     const LineP p = line_params(c, ax);
-    k_reflect_sum<<<line_grid(p, 1), 128, 0, c->stream>>>(p, arr, rmin, rmax, flip_dir == ax);
-    c->launches++;
+    for (int k = 0; k < ncomp; ++k) {
+      k_reflect_sum<<<line_grid(p, 1), 128, 0, c->stream>>>(p, A.a[k], rmin, rmax, flip[k] == ax);
+      c->launches++;
+    }
   }
   for (int ax = 0; ax < c->ndims; ++ax) {
     const LineP p = line_params(c, ax);
@@ -464,31 +493,34 @@ int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir, const int* bc6) {
     const bool has_lo = !(c->min_bnd[ax] && bc_allspecies(c, 2 * ax) != EB200_BC_PERIODIC);
     const bool has_hi = !(c->max_bnd[ax] && bc_allspecies(c, 2 * ax + 1) != EB200_BC_PERIODIC);
     if (c->nprocdir[ax] == 1) {
-      if (has_lo && has_hi) { k_periodic_sum<<<line_grid(p, 1), 128, 0, c->stream>>>(p, arr); c->launches++; }
+      if (has_lo && has_hi)
+        for (int k = 0; k < ncomp; ++k) { k_periodic_sum<<<line_grid(p, 1), 128, 0, c->stream>>>(p, A.a[k]); c->launches++; }
     } else {
-      const size_t cnt = (size_t)p.ng * p.nlines;
-      EB_TRY(ensure_halo(c, cnt));
+      const size_t cnt = (size_t)ncomp * p.ng * p.nlines;
+      EB_TRY(ensure_halo(c, 2 * cnt));
       const int lo = has_lo ? c->nbr_lo[ax] : -1, hi = has_hi ? c->nbr_hi[ax] : -1;
-      // send A(nn+1:nn+ng) to +1, receive from -1, add into A(1:ng)
-      k_pack<<<line_grid(p, 1), 128, 0, c->stream>>>(p, A, p.nn, c->halo_send);
-      EB_TRY(comm_sendrecv(c, c->halo_send, hi, c->halo_recv, lo, cnt));
-      if (lo >= 0) k_unpack<<<line_grid(p, 1), 128, 0, c->stream>>>(p, A, 0, c->halo_recv, 1);
-      // send A(1-ng:0) to -1, receive from +1, add into A(nn+1-ng:nn)
-      k_pack<<<line_grid(p, 1), 128, 0, c->stream>>>(p, A, -p.ng, c->halo_send);
-      EB_TRY(comm_sendrecv(c, c->halo_send, lo, c->halo_recv, hi, cnt));
-      if (hi >= 0) k_unpack<<<line_grid(p, 1), 128, 0, c->stream>>>(p, A, p.nn - p.ng, c->halo_recv, 1);
-      c->launches += 4;
+      // the ghost slab A(nn+1:nn+ng) goes to +1 and A(1-ng:0) to -1; what comes from -1 is added into A(1:ng), what
+      // comes from +1 into A(nn+1-ng:nn) (boundary.F90:976-989): one exchange for both directions and all arrays
+      double *s_hi = c->halo_send, *s_lo = c->halo_send + cnt, *r_lo = c->halo_recv, *r_hi = c->halo_recv + cnt;
+      k_pack2<<<line_grid2(p, ncomp), 128, 0, c->stream>>>(p, A, p.nn, -p.ng, s_hi, s_lo);
+      EB_TRY(comm_exchange2(c, s_hi, hi, cnt, s_lo, lo, cnt, r_lo, lo, cnt, r_hi, hi, cnt));
+      k_unpack2<<<line_grid2(p, ncomp), 128, 0, c->stream>>>(p, A, 0, p.nn - p.ng, r_lo, r_hi, 1, lo >= 0, hi >= 0);
+      c->launches += 2;
     }
   }
   if (bc6) {
     for (int ax = 0; ax < c->ndims; ++ax) {
       const LineP p = line_params(c, ax);
-      k_clear_ghost_lines<<<line_grid(p, 1), 128, 0, c->stream>>>(p, arr);
-      c->launches++;
+      for (int k = 0; k < ncomp; ++k) { k_clear_ghost_lines<<<line_grid(p, 1), 128, 0, c->stream>>>(p, A.a[k]); c->launches++; }
     }
   }
   EB_CUDA(c, cudaGetLastError());
   return 0;
+}
+int32_t summation_bcs(eb200_ctx* c, double* arr, int flip_dir, const int* bc6) {
+  Arr3 A; A.a[0] = A.a[1] = A.a[2] = arr;
+  const int flip[3] = {flip_dir, flip_dir, flip_dir};
+  return summation_bcs_n(c, A, 1, flip, bc6);
 }
 
 // ---- smooth_current (current_smooth.F90:49-151, the strided compensated binomial filter) ----
@@ -570,9 +602,9 @@ int32_t current_finish(eb200_ctx* c) {
   {
     ScopedPhase ph(c, "halo");
     if (!bc_mixed(c)) {       // (mixed: done species by species inside push_particles, boundary.F90:1130-1136)
-      EB_TRY(summation_bcs(c, c->f.f[JX], 0));
-      EB_TRY(summation_bcs(c, c->f.f[JY], 1));
-      EB_TRY(summation_bcs(c, c->f.f[JZ], 2));
+      Arr3 J; J.a[0] = c->f.f[JX]; J.a[1] = c->f.f[JY]; J.a[2] = c->f.f[JZ];
+      const int flip[3] = {0, 1, 2};
+      EB_TRY(summation_bcs_n(c, J, 3, flip, nullptr));
     }
   }
   EB_TRY(field_bc(c, JX, 3));

@@ -38,6 +38,9 @@ static void free_species(SpeciesD& sp) {
   if (sp.probes.buf) cudaFree(sp.probes.buf);
   if (sp.probes.count) cudaFree(sp.probes.count);
   sp.probes = ProbeSet();
+  if (sp.h_mig) cudaFreeHost(sp.h_mig);
+  if (sp.d_mig) cudaFree(sp.d_mig);
+  sp.h_mig = sp.d_mig = nullptr;
   if (sp.far) cudaFree(sp.far);
   sp.far = nullptr; sp.far_cap = 0;
   if (sp.dest) cudaFree(sp.dest);
@@ -479,8 +482,11 @@ int32_t eb200_download_probe(eb200_ctx* c, int32_t isp, int32_t iprobe, int64_t 
                       [src](size_t o, size_t) { return (const void*)(src + o); }));
     EB_CUDA(c, cudaStreamSynchronize(c->stream));
   }
-  if (n_out) *n_out = (int64_t)n;
+  if (n_out) *n_out = (int64_t)kept;          // rows a caller can fetch: never more than the device list holds
   if (clear) EB_CUDA(c, cudaMemsetAsync(ps.count + iprobe, 0, sizeof(unsigned long long), c->stream));
+  if ((long long)n > ps.cap)
+    return fail(c, EB200_E_NOMEM, "probe list overflowed: " + std::to_string(n) + " particles sampled, " + std::to_string(kept) +
+                                  " kept (raise option probe_capacity)");
   return 0;
 }
 int32_t eb200_dist_fn(eb200_ctx* c, int32_t ispecies, int32_t curdims, const int32_t direction[3], const double ranges[6],
@@ -579,7 +585,6 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
   // the arrays are next (re)allocated.  "auto" = need / 8, "0" = off (permute inside the sort)
   if (k == "defer_window") { c->defer_window = v == "auto" ? -1 : atoll(value); return 0; }
   if (k == "deterministic_deposit") { c->deterministic = atoi(value) != 0; return 0; }
-  if (k == "sort_every") { c->sort_every = atoi(value) < 1 ? 1 : atoi(value); return 0; }
   if (k == "timers") { c->timers_on = atoi(value) != 0; return 0; }
   if (k == "reserve") {   // "<species>:<particles>": allocate particle storage once, exactly (no regrow copies)
     const size_t colon = v.find(':');

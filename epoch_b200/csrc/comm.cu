@@ -106,6 +106,23 @@ int32_t comm_sendrecv_v(eb200_ctx* c, const double* send, int dst, size_t nsend,
   return 0;
 }
 
+int32_t comm_exchange2(eb200_ctx* c, const double* a, int da, size_t na, const double* b, int db, size_t nb,
+                       double* ra, int sa, size_t nra, double* rb, int sb, size_t nrb) {
+  if (da < 0 && db < 0 && sa < 0 && sb < 0) return 0;
+  if (!c->nccl) return fail(c, EB200_E_STATE, "NCCL communicator not initialised");
+  Nccl* l = c->nccl;
+  // (sends and receives between one pair of ranks match in issue order: a's partner is ra of the neighbour)
+  ncclResult_t r = l->GroupStart();
+  if (r == 0 && da >= 0) r = l->Send(a, na, ncclFloat64, da, l->comm, c->stream);
+  if (r == 0 && db >= 0) r = l->Send(b, nb, ncclFloat64, db, l->comm, c->stream);
+  if (r == 0 && sa >= 0) r = l->Recv(ra, nra, ncclFloat64, sa, l->comm, c->stream);
+  if (r == 0 && sb >= 0) r = l->Recv(rb, nrb, ncclFloat64, sb, l->comm, c->stream);
+  ncclResult_t r2 = l->GroupEnd();
+  if (r != 0 || r2 != 0)
+    return fail(c, EB200_E_NCCL, std::string("nccl exchange: ") + (l->GetErrorString ? l->GetErrorString(r ? r : r2) : "error"));
+  return 0;
+}
+
 // every rank sends cnt_s[r] doubles at send + off_s[r] to rank r and receives cnt_r[r] doubles at
 // recv + off_r[r] from it, in one NCCL group (balance.F90's MPI_ALLTOALLW of redistribute_field_*);
 // the part a rank keeps is a device-to-device copy

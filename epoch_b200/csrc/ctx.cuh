@@ -96,6 +96,12 @@ struct SpeciesD {
   uint32_t* d_tile_start = nullptr; // first particle of every tile (+1 entry), device and pinned host copy
   uint32_t* h_tile_start = nullptr;
   long long tile_cap = 0;
+  // migration mailboxes (particles.cu): capacity in particles of the links [axis][to lo, to hi, from hi, from lo],
+  // the wanted counts of the last exchange (pinned copy, valid after the next synchronise) and whether they are unread
+  long long mig_cap[3][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}};
+  unsigned long long* h_mig = nullptr;
+  unsigned long long* d_mig = nullptr;
+  bool mig_pending[3] = {false, false, false};
   bool sorted = false;      // keys/cell_start valid for the current positions ...
   bool was_ordered = false; // the slots are in (an older) cell order: a re-sort moves particles by about a tile
   double sort_dt = 0.0;     // ... and for this time step (the key is the cell after the half drift)
@@ -153,6 +159,7 @@ struct eb200_ctx {
   double* cpml_psi = nullptr;       // 12 arrays of g.total doubles (allocated when a CPML side exists)
   double* win_planes = nullptr;     // moving window: e*_x_max, b*_x_max planes (6 x y-z extent with ghosts)
   double* bnd_planes[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // setup_field_boundaries: per boundary 6 planes (ex..bz)
+  bool bnd_dropped[6] = {false, false, false, false, false, false};   // ... dropped by redistribute, not handed over again yet
   double* fbase = nullptr;     // 9 * total doubles
   eb::FieldP f;
   std::vector<eb::SpeciesD> species;
@@ -201,7 +208,6 @@ struct eb200_ctx {
   int fuse_keys = 1;            // option fuse_keys: push kernel emits the next sort keys (single rank)
   long long defer_window = -1;  // option defer_window: head room in slots of the deferred permute (-1 auto, 0 off)
   long long n_deferred = 0, n_permuted = 0;   // sorts that deferred / physically permuted (timer "deferred_sorts")
-  int sort_every = 1;
   bool timers_on = false;
   std::map<std::string, eb::PhaseTimer> timers;
   std::map<std::string, std::pair<cudaEvent_t, long long>> open_marks;
@@ -269,6 +275,9 @@ void comm_destroy(eb200_ctx* c);
 // recv_hi comes from nbr_hi (first call), etc.  Null neighbours are skipped.
 int32_t comm_sendrecv(eb200_ctx* c, const double* send, int dst, double* recv, int src, size_t count);
 int32_t comm_sendrecv_v(eb200_ctx* c, const double* send, int dst, size_t nsend, double* recv, int src, size_t nrecv);
+// both directions of an axis in ONE group: send a to rank da and b to rank db, receive ra from rank sa and rb from sb
+int32_t comm_exchange2(eb200_ctx* c, const double* a, int da, size_t na, const double* b, int db, size_t nb,
+                       double* ra, int sa, size_t nra, double* rb, int sb, size_t nrb);
 int32_t comm_alltoallv(eb200_ctx* c, const double* send, const size_t* off_s, const size_t* cnt_s, double* recv,
                        const size_t* off_r, const size_t* cnt_r);
 // balance.cu / particles.cu: the new owner of a position (get_particle_processor, balance.F90:2673-2746):

@@ -624,18 +624,32 @@ __global__ void k_particle_bc(BcP b, long long n, double* __restrict__ pos, doub
     if (xbd != 0) atomicAdd(counters + (xbd < 0 ? 0 : 1), 1ULL);
   }
 }
-// pack flagged particles into the per-side AoS send buffers and free their slots
-__global__ void k_pack_leavers(long long n, int nd, const double* x, const double* y, const double* z,
+// Migration messages are fixed-capacity mailboxes: [packed count, wanted count, cap x nvar doubles].  The
+// capacity of a directed link is agreed without talking: both ends grow it by the same rule from the count the
+// sender WANTED to send (it travels in the header), read a step late at the sort's synchronise.  So particle_bcs
+// needs no host round trip of its own, and a rank that sees more leavers than a mailbox holds keeps the rest one
+// more step (they sit in its ghost cells: gather and deposit still reach valid cells) instead of failing.
+constexpr int MIG_HDR = 2;
+
+// pack flagged particles into the per-side mailboxes and free their slots; a leaver beyond the capacity stays
+// (its periodic shift, applied by k_particle_bc, is taken back)
+__global__ void k_pack_leavers(long long n, int nd, int ax, double* x, double* y, double* z,
                                const double* px, const double* py, const double* pz, const double* w,
                                uint32_t* key, const uint32_t* flag, unsigned long long* cursors,
-                               double* send_lo, double* send_hi, uint32_t* count = nullptr, uint32_t invalid_bucket = 0,
-                               long long n_counted = 0) {
+                               double* send_lo, double* send_hi, long long cap_lo, long long cap_hi, double undo_lo,
+                               double undo_hi, uint32_t* count = nullptr, uint32_t invalid_bucket = 0,
+                               long long n_counted = 0, int hdr = MIG_HDR) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint32_t f = flag[i];
   if (f == 0) return;
   const unsigned long long slot = atomicAdd(cursors + (f == 1 ? 3 : 4), 1ULL);
-  double* q = (f == 1 ? send_lo : send_hi) + slot * (nd + 4);
+  if (slot >= (unsigned long long)(f == 1 ? cap_lo : cap_hi)) {
+    double* pa = ax == 0 ? x : (ax == 1 ? y : z);
+    pa[i] -= f == 1 ? undo_lo : undo_hi;
+    return;
+  }
+  double* q = (f == 1 ? send_lo : send_hi) + hdr + slot * (nd + 4);
   q[0] = x[i];
   if (nd >= 2) q[1] = y[i];
   if (nd >= 3) q[2] = z[i];
@@ -645,18 +659,25 @@ __global__ void k_pack_leavers(long long n, int nd, const double* x, const doubl
   key[i] = KEY_INVALID;
 }
 
-// the same from the slot lists the push kernel made (fused migration): blockIdx.y = side; a leaver through a
-// global periodic boundary is shifted to the other end (boundary.F90:1390-1461) as it is packed
-__global__ void k_pack_list(const uint32_t* __restrict__ list_lo, const uint32_t* __restrict__ list_hi, long long nlo,
-                            long long nhi, int nd, int ax, double shift_lo, double shift_hi, const double* x,
+// the same from the slot lists the push kernel made (fused migration): blockIdx.y = side; the counts are read on
+// the device (counters[0..1]); a leaver through a global periodic boundary is shifted to the other end
+// (boundary.F90:1390-1461) as it is packed
+__global__ void k_pack_list(const uint32_t* __restrict__ list_lo, const uint32_t* __restrict__ list_hi,
+                            const unsigned long long* __restrict__ counters, long long list_cap, long long cap_lo,
+                            long long cap_hi, int nd, int ax, double shift_lo, double shift_hi, const double* x,
                             const double* y, const double* z, const double* px, const double* py, const double* pz,
                             const double* w, uint32_t* key, double* send_lo, double* send_hi, uint32_t* count,
                             uint32_t invalid_bucket) {
   const int side = blockIdx.y;
   const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= (side == 0 ? nlo : nhi)) return;
+  const long long wanted = (long long)counters[side];
+  long long m = wanted < list_cap ? wanted : list_cap;
+  m = m < (side == 0 ? cap_lo : cap_hi) ? m : (side == 0 ? cap_lo : cap_hi);
+  double* buf = side == 0 ? send_lo : send_hi;
+  if (j == 0) { buf[0] = (double)m; buf[1] = (double)wanted; }
+  if (j >= m) return;
   const uint32_t i = (side == 0 ? list_lo : list_hi)[j];
-  double* q = (side == 0 ? send_lo : send_hi) + j * (nd + 4);
+  double* q = buf + MIG_HDR + j * (nd + 4);
   q[0] = x[i];
   if (nd >= 2) q[1] = y[i];
   if (nd >= 3) q[2] = z[i];
@@ -665,6 +686,35 @@ __global__ void k_pack_list(const uint32_t* __restrict__ list_lo, const uint32_t
   atomicSub(count + key[i], 1u); atomicAdd(count + invalid_bucket, 1u);
   key[i] = KEY_INVALID;
 }
+// headers of the mailboxes filled by k_pack_leavers (counters[0..1] = wanted, cursors clamp to the capacity)
+__global__ void k_mig_header(const unsigned long long* counters, double* send_lo, double* send_hi, long long cap_lo, long long cap_hi) {
+  const long long w0 = (long long)counters[0], w1 = (long long)counters[1];
+  send_lo[0] = (double)(w0 < cap_lo ? w0 : cap_lo); send_lo[1] = (double)w0;
+  send_hi[0] = (double)(w1 < cap_hi ? w1 : cap_hi); send_hi[1] = (double)w1;
+}
+// arrivals of one mailbox -> slots [off, off + cap): the first `packed` are particles, the rest dead slots
+__global__ void k_unpack_mailbox(const double* __restrict__ box, int nd, long long cap, long long off,
+                                 double* x, double* y, double* z, double* px, double* py, double* pz, double* w,
+                                 uint32_t* key) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cap) return;
+  const long long n = (long long)box[0];
+  if (i >= n) { key[off + i] = KEY_INVALID; return; }
+  const double* q = box + MIG_HDR + i * (nd + 4);
+  x[off + i] = q[0];
+  if (nd >= 2) y[off + i] = q[1];
+  if (nd >= 3) z[off + i] = q[2];
+  px[off + i] = q[nd]; py[off + i] = q[nd + 1]; pz[off + i] = q[nd + 2];
+  w[off + i] = q[nd + 3];
+  key[off + i] = 0;
+}
+// what both ends of the four links learn this step: wanted counts out (lo, hi) and in (from hi, from lo)
+__global__ void k_mig_info(const unsigned long long* counters, const double* recv_hi, const double* recv_lo, int has_hi,
+                           int has_lo, unsigned long long* info) {
+  info[0] = counters[0]; info[1] = counters[1];
+  info[2] = has_hi ? (unsigned long long)recv_hi[1] : 0ULL;
+  info[3] = has_lo ? (unsigned long long)recv_lo[1] : 0ULL;
+}
 
 static int32_t read_counters(eb200_ctx* c, int n) {
   EB_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
@@ -672,92 +722,97 @@ static int32_t read_counters(eb200_ctx* c, int n) {
   return 0;
 }
 
+static long long grow_cap(long long cap, unsigned long long wanted) {
+  long long need = 2 * (long long)wanted;
+  while (cap < need) cap *= 2;
+  return cap;
+}
+
 // applies particle_bcs to slots [0, n_slots) of one species; returns the new slot
 // count (arrivals are appended) and whether the live count may have changed
 // n_counted > 0: the push kernel wrote keys + histogram for the slots [0, n_counted) (fused keys)
 // list_axis >= 0: the push kernel has listed the leavers of that axis (c->mig_list, counts in d_counters[0..1])
+// No host synchronisation: counts stay on the device, the mailboxes have agreed capacities (see above); the
+// appended slots [n_slots, n_slots + capacities) hold the arrivals and dead slots, which the sort drops.
 static int32_t species_bcs(eb200_ctx* c, SpeciesD& sp, long long& n_slots, bool& changed, long long n_counted = 0,
                            int list_axis = -1) {
   const int nvar = c->ndims + 4;
   for (int ax = 0; ax < c->ndims; ++ax) {
     const BcP b = make_bc(c, sp, ax);
     if (!b.multi) continue;        // axes that are not decomposed are handled inside the sort's key pass
-    const bool open_here = (b.min_bnd && b.bc_min == EB200_BC_OPEN) || (b.max_bnd && b.bc_max == EB200_BC_OPEN);
-    bool lists = ax == list_axis;
-    if (lists) {
-      EB_TRY(read_counters(c, 2));
-      const long long most = (long long)std::max(c->h_counters[0], c->h_counters[1]);
-      if (most > c->mig_list_cap) { c->mig_list_want = 4 * most; lists = false; }   // too many: find them the usual way
+    changed = true;
+    const bool lists = ax == list_axis;
+    const int lo = c->nbr_lo[ax], hi = c->nbr_hi[ax];
+    // capacities of the four links: grown from what was wanted last time (read at the sort's synchronise since)
+    if (!sp.h_mig) {
+      EB_CUDA(c, cudaMallocHost(&sp.h_mig, 12 * sizeof(unsigned long long)));
+      EB_CUDA(c, cudaMalloc(&sp.d_mig, 12 * sizeof(unsigned long long)));
+      for (int k = 0; k < 12; ++k) sp.h_mig[k] = 0;
     }
-    if (!lists && (n_slots > 0 || b.multi)) {
-      if (b.multi || open_here) EB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
+    for (int k = 0; k < 4; ++k) {
+      if (sp.mig_cap[ax][k] < c->mig_min_particles) sp.mig_cap[ax][k] = c->mig_min_particles;
+      if (sp.mig_pending[ax]) sp.mig_cap[ax][k] = grow_cap(sp.mig_cap[ax][k], sp.h_mig[4 * ax + k]);
+    }
+    if (sp.mig_pending[ax] && lists) {
+      const long long most = (long long)std::max(sp.h_mig[4 * ax], sp.h_mig[4 * ax + 1]);
+      if (2 * most > c->mig_list_cap) c->mig_list_want = 4 * most;     // (grown before the next push)
+    }
+    sp.mig_pending[ax] = false;
+    const long long cap_lo = sp.mig_cap[ax][0], cap_hi = sp.mig_cap[ax][1], cap_fhi = sp.mig_cap[ax][2], cap_flo = sp.mig_cap[ax][3];
+    const long long cap_max = std::max(std::max(cap_lo, cap_hi), std::max(cap_fhi, cap_flo));
+    EB_TRY(ensure_stage(c, std::max<long long>(MIG_HDR + cap_max * nvar, 1 << 16)));
+    const double undo_lo = b.min_bnd && b.bc_min == EB200_BC_PERIODIC ? b.shift : 0.0;
+    const double undo_hi = b.max_bnd && b.bc_max == EB200_BC_PERIODIC ? -b.shift : 0.0;
+    if (lists) {
+      const dim3 gl((unsigned)((std::max(cap_lo, cap_hi) + 255) / 256), 2);
+      k_pack_list<<<gl, 256, 0, c->stream>>>(c->mig_list[0], c->mig_list[1], c->d_counters, c->mig_list_cap, cap_lo, cap_hi,
+          c->ndims, ax, undo_lo, undo_hi, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6],
+          sp.key, c->mig_send[0], c->mig_send[1], c->cell_count, (uint32_t)c->g.ncell_ext);
+      c->launches++;
+    } else {
+      EB_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
       if (n_slots > 0) {
         k_particle_bc<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(b, n_slots, sp.a[ax], sp.a[3 + ax],
             sp.key, sp.dest, c->d_counters);
-        c->launches++;
+        k_pack_leavers<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(n_slots, c->ndims, ax, sp.a[0], sp.a[1], sp.a[2],
+            sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key, sp.dest, c->d_counters, c->mig_send[0], c->mig_send[1], cap_lo, cap_hi,
+            undo_lo, undo_hi, n_counted > 0 ? c->cell_count : nullptr, (uint32_t)c->g.ncell_ext, n_counted);
+        c->launches += 2;
       }
-    }
-    if (open_here) changed = true;
-    if (!b.multi) continue;
-    changed = true;
-    if (!lists) EB_TRY(read_counters(c, 3));
-    const long long nlo = (long long)c->h_counters[0], nhi = (long long)c->h_counters[1];
-    EB_TRY(ensure_stage(c, std::max<long long>(std::max<long long>(4 * std::max(nlo, nhi), c->mig_min_particles) * nvar, 1 << 16)));
-    if (lists && nlo + nhi > 0) {
-      const dim3 gl((unsigned)((std::max(nlo, nhi) + 255) / 256), 2);
-      k_pack_list<<<gl, 256, 0, c->stream>>>(c->mig_list[0], c->mig_list[1], nlo, nhi, c->ndims, ax,
-          b.min_bnd ? b.shift : 0.0, b.max_bnd ? -b.shift : 0.0, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6],
-          sp.key, c->mig_send[0], c->mig_send[1], c->cell_count, (uint32_t)c->g.ncell_ext);
-      c->launches++;
-    } else if (nlo + nhi > 0) {
-      k_pack_leavers<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(n_slots, c->ndims, sp.a[0], sp.a[1], sp.a[2],
-          sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key, sp.dest, c->d_counters, c->mig_send[0], c->mig_send[1],
-          n_counted > 0 ? c->cell_count : nullptr, (uint32_t)c->g.ncell_ext, n_counted);
+      k_mig_header<<<1, 1, 0, c->stream>>>(c->d_counters, c->mig_send[0], c->mig_send[1], cap_lo, cap_hi);
       c->launches++;
     }
-    // exchange counts (as doubles, exact below 2^53), then payloads; low side first.
-    // A particle leaves through a physical boundary only if that boundary is periodic
-    // (xbd is reset to 0 otherwise), so the wrap-around neighbours are always valid.
-    const int lo = c->nbr_lo[ax], hi = c->nbr_hi[ax];
-    double* cnt = c->d_red;     // [0] my->lo, [1] my->hi, [2] from hi, [3] from lo
-    const double hc[2] = {(double)nlo, (double)nhi};
-    EB_CUDA(c, cudaMemcpyAsync(cnt, hc, 2 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-    EB_CUDA(c, cudaMemsetAsync(cnt + 2, 0, 2 * sizeof(double), c->stream));
-    EB_TRY(comm_sendrecv(c, cnt + 0, lo, cnt + 2, hi, 1));
-    EB_TRY(comm_sendrecv(c, cnt + 1, hi, cnt + 3, lo, 1));
-    EB_CUDA(c, cudaMemcpyAsync(c->h_red, cnt, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-    EB_CUDA(c, cudaStreamSynchronize(c->stream));
-    const long long from_hi = (long long)c->h_red[2], from_lo = (long long)c->h_red[3];
-    // receive buffers are sized after the counts are known (send buffers were sized
-    // before packing and are separate allocations, so growing here would lose them)
-    if (std::max(from_hi, from_lo) * nvar > c->mig_cap)
-      return fail(c, EB200_E_NOMEM, "migration receive buffer too small; raise option mig_capacity");
-    // lo-bound leavers travel to `lo`; what arrives from `hi` are hi's lo-bound leavers
-    EB_TRY(comm_sendrecv_v(c, c->mig_send[0], nlo > 0 ? lo : -1, (size_t)nlo * nvar,
-                           c->mig_recv[0], from_hi > 0 ? hi : -1, (size_t)from_hi * nvar));
-    EB_TRY(comm_sendrecv_v(c, c->mig_send[1], nhi > 0 ? hi : -1, (size_t)nhi * nvar,
-                           c->mig_recv[1], from_lo > 0 ? lo : -1, (size_t)from_lo * nvar));
-    const long long arrivals = from_hi + from_lo;
-    if (arrivals > 0) {
+    // one exchange for both directions.  A particle leaves through a physical boundary only if that boundary is
+    // periodic (xbd is reset to 0 otherwise), so the wrap-around neighbours are always valid.  lo-bound leavers
+    // travel to `lo`; what arrives from `hi` are hi's lo-bound leavers.
+    EB_TRY(comm_exchange2(c, c->mig_send[0], lo, (size_t)(MIG_HDR + cap_lo * nvar), c->mig_send[1], hi, (size_t)(MIG_HDR + cap_hi * nvar),
+                          c->mig_recv[0], hi, (size_t)(MIG_HDR + cap_fhi * nvar), c->mig_recv[1], lo, (size_t)(MIG_HDR + cap_flo * nvar)));
+    const long long add = (hi >= 0 ? cap_fhi : 0) + (lo >= 0 ? cap_flo : 0);
+    if (add > 0) {
       const long long keep_n = sp.n;
       sp.n = n_slots;                       // regrow copies [0, sp.n)
-      EB_TRY(species_reserve(c, sp, n_slots + arrivals));
+      EB_TRY(species_reserve(c, sp, n_slots + add));
       sp.n = keep_n;
       // appended; the deferred permute takes slots this far from their sorted place through its side buffer
       long long at = n_slots;
-      if (from_hi > 0) {
-        k_unpack_aos<<<(unsigned)((from_hi + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[0], c->ndims, from_hi, at,
+      if (hi >= 0) {
+        k_unpack_mailbox<<<(unsigned)((cap_fhi + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[0], c->ndims, cap_fhi, at,
             sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
-        at += from_hi; c->launches++;
+        at += cap_fhi; c->launches++;
       }
-      if (from_lo > 0) {
-        k_unpack_aos<<<(unsigned)((from_lo + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[1], c->ndims, from_lo, at,
+      if (lo >= 0) {
+        k_unpack_mailbox<<<(unsigned)((cap_flo + 255) / 256), 256, 0, c->stream>>>(c->mig_recv[1], c->ndims, cap_flo, at,
             sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key);
         c->launches++;
       }
-      n_slots += arrivals;
+      n_slots += add;
     }
+    k_mig_info<<<1, 1, 0, c->stream>>>(c->d_counters, c->mig_recv[0], c->mig_recv[1], hi >= 0, lo >= 0, sp.d_mig + 4 * ax);
+    c->launches++;
+    EB_CUDA(c, cudaMemcpyAsync(sp.h_mig + 4 * ax, sp.d_mig + 4 * ax, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    sp.mig_pending[ax] = true;             // (valid after the next synchronise: the sort's)
   }
+  // open boundaries of the axes that are not decomposed are applied by the key pass of the sort
   EB_CUDA(c, cudaGetLastError());
   return 0;
 }
@@ -812,8 +867,9 @@ int32_t redistribute_particles(eb200_ctx* c, const OwnerP& own, std::vector<long
         EB_TRY(read_counters(c, 2));
         const long long total = (long long)c->h_counters[0], left = (long long)c->h_counters[1], nsend = total - left;
         if (nsend > 0) {
-          k_pack_leavers<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(n_slots, c->ndims, sp.a[0], sp.a[1], sp.a[2],
-              sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key, sp.dest, c->d_counters, c->mig_send[0], c->mig_send[1]);
+          k_pack_leavers<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(n_slots, c->ndims, 0, sp.a[0], sp.a[1], sp.a[2],
+              sp.a[3], sp.a[4], sp.a[5], sp.a[6], sp.key, sp.dest, c->d_counters, c->mig_send[0], c->mig_send[1], 1LL << 62, 1LL << 62,
+              0.0, 0.0, nullptr, 0, 0, 0);
           c->launches++;
         }
         double* cnt = c->d_red;            // [0] sent now, [1] still to come -> [2], [3] from src

@@ -161,8 +161,11 @@ __device__ __forceinline__ void box3(double* acc, const double (*g)[NW], const d
 // column e = bx & ~1 and the NW weights are shifted by the parity of bx inside a vector of 2 * NP weights
 // (zero in the unused slot), so a row costs NP loads instead of NW.  Same value as gather_tile: the extra term is
 // an exact zero at either end of the sum.
+// MEASURED SLOWER (512^3: push 140 -> 166 ms, profiles/r02_variants_512.txt): the shared-memory data stage delivers
+// 128 B per wavefront whatever the access width -- an LDS.128 of a warp costs 4 wavefronts, an LDS.64 two, broadcast
+// or not (ncu: 4.19 wavefronts per shared load) -- so pairing saves no wavefronts and adds 54 DFMA.  Kept as an option.
 #ifndef EB_PAIR
-#define EB_PAIR 1
+#define EB_PAIR 0
 #endif
 template <int SHAPE>
 struct PairW {
@@ -852,8 +855,10 @@ constexpr int SUB = 2;           // a deposit CTA owns 1/SUB of a tile, split al
 // holds exactly two cells of each of the 16 shared-memory bank classes (8-byte words): the cells of a class are
 // ranked by count and warp w takes ranks 2w and 2w + 1 of every class.  Available when the sub-tile's cells fall
 // evenly into the classes (3D triangle, 2D triangle / bspline3).
+// MEASURED WITHOUT EFFECT (512^3: deposit 92.24 -> 92.23 ms, profiles/r02_variants_512.txt): a CTA still runs as long as
+// its fullest cell and with two CTAs per SM the issue slots the lighter warps give up are not what limits it.  Option.
 #ifndef EB_BALANCE
-#define EB_BALANCE 1
+#define EB_BALANCE 0
 #endif
 template <int ND, int SHAPE>
 constexpr bool uniform_bank_classes() {

@@ -173,8 +173,10 @@ class Simulation:
         any_open = any(b in (BC["simple_laser"], BC["simple_outflow"]) for b in bcs)
         if any_open:
             dt = min(dt, solver)
-        if ms == -1:                           # custom stencil: the deck gives dt (setup.F90:734-746)
+        if ms == -1:                           # custom stencil: the deck gives dt (setup.F90:734-746) ...
             dt = self.stencil["dt"]
+            if self.dt_multiplier < 1.0:       # ... and a multiplier below one would detune it (:735-746: warns, resets)
+                self.dt_multiplier = 1.0
         # set_plasma_frequency_dt (setup.F90:640-696; 1D :514-563)
         min_dt = 1000000.0
         k_max = 2.0 * PI / d[0]
@@ -471,6 +473,11 @@ class Simulation:
         self._setup_lasers()
         if getattr(self, "window", None) is not None:
             self.ctx.set_window_fields(None)
+        # the planes of setup_field_boundaries: EPOCH's host remaps its own copies (balance.F90:847-1010); this mirror
+        # keeps none, so re-sliced planes are handed over as zeros (decks with initial fields at an open boundary
+        # AND load balancing need the Fortran host)
+        for b in range(2 * nd):
+            self.ctx.set_boundary_fields(b + 1, None)
         return True
 
     # -- moving window (housekeeping/window.F90) ---------------------------------

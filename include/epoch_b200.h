@@ -308,8 +308,10 @@ int32_t EB200_NAME(dist_fn)(EB200_CTX*, int32_t ispecies, int32_t curdims, const
  * iprobe = 0..7; point/normal have ndims components.  A species with probes is pushed by the general kernel. */
 int32_t EB200_NAME(set_probe)(EB200_CTX*, int32_t ispecies, int32_t iprobe, const double* point, const double* normal,
                               double ek_min, double ek_max);
-/* n_out: particles sampled since the last clear (those beyond option "probe_capacity", default 262144, are counted
- * but not kept); copies min(n, capacity) of them (partlist wire format) when packed != NULL; clear != 0 empties the list */
+/* n_out: particles held in the probe's device list since the last clear (at most option "probe_capacity", default
+ * 262144); copies min(n_out, capacity) of them (partlist wire format) when packed != NULL; clear != 0 empties the
+ * list.  If more particles crossed than the list holds, the kept ones are still copied and the call returns
+ * EB200_E_NOMEM (last_error says how many were sampled). */
 int32_t EB200_NAME(download_probe)(EB200_CTX*, int32_t ispecies, int32_t iprobe, int64_t capacity, double* packed,
                                    int32_t nvar, int64_t* n_out, int32_t clear);
 /* options (key, value as strings):

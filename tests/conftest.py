@@ -8,6 +8,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
+def pytest_addoption(parser):
+    parser.addoption("--ref-dump", action="store", default=os.environ.get("EB200_REF_DUMP"),
+                     help="directory of reference dumps made by tools/ref_build/build_and_run.sh (EPOCH's own output)")
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 

@@ -55,3 +55,28 @@ def match_particles(A, B):
 def relerr(a, b):
     s = max(np.max(np.abs(b)), 1e-300)
     return float(np.max(np.abs(a - b)) / s)
+
+
+# ---- the reference's own particle load (oracle/orc_loader.cpp: KISS + Box-Muller + auto_load) ----
+def reference_load(oracle_abi, sim_oracle, loads, seed=7842432):
+    """auto_load (helper.F90:89-163) on an ORACLE-backed Simulation: random_init(seed + rank) as
+    set_initial_values does (setup.F90:505-510), then, species by species, positions, weights
+    and momenta from the global generator.  `loads` = [(ppc, density, (Tx, Ty, Tz), (dpx, dpy, dpz)), ...]
+    per species.  Returns the packed particle arrays (wire format) per species."""
+    import ctypes as C
+    lib = oracle_abi.lib
+    lib.orc_random_init.argtypes = [C.c_int32]
+    lib.orc_load_uniform.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_double, C.POINTER(C.c_double),
+                                     C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    lib.orc_load_uniform.restype = C.c_int32
+    assert sim_oracle.ctx.abi is oracle_abi
+    lib.orc_random_init(int(seed + sim_oracle.rank))
+    out = []
+    for isp, (ppc, density, temp, drift) in enumerate(loads):
+        n = C.c_int64(0)
+        t3 = (C.c_double * 3)(*temp)
+        d3 = (C.c_double * 3)(*drift)
+        rc = lib.orc_load_uniform(sim_oracle.ctx._ctx, isp, int(ppc), float(density), t3, d3, C.byref(n))
+        assert rc == 0, rc
+        out.append(sim_oracle.ctx.download_particles(isp))
+    return out
