@@ -17,8 +17,12 @@ library's stream, max over ranks) with the state resident in HBM; `e2e` = the sa
 through the C ABI from HOST buffers: upload of all particles and fields, K steps,
 download of all particles and fields, wall clock.
 
-N > 1 (torchrun): weak scaling, one 512^3 slab per GPU stacked along z, NCCL
-send/recv of field halos, current ghost sums and migrating particles.
+N > 1 (torchrun): the line printed is STRONG scaling -- the same global 512^3 box cut into N slabs
+of 512 x 512 x 512/N along z (`"scaling": "strong"`, e2e on that same deck) -- and a key `weak` holds
+the device-timed run with one 512^3 slab per GPU stacked along z (--scaling weak prints that one as
+the line instead).  NCCL send/recv of field halos, current ghost sums and migrating particles.
+Every line carries `parity_check`: global particle count, total-energy drift and the Gauss-law
+residual (max over ranks), taken outside the timed region; a failed check makes the run exit 3.
 
 `--impl reference` times the CPU restatement of the reference (oracle/, built -O3)
 on all host cores, one independent periodic box per process.
@@ -77,7 +81,7 @@ def fill_particles(out, sim, seed, nthreads, k_begin=0, k_end=None):
 
     def work(k0, k1):
         for k in range(k0, k1):
-            rng = np.random.default_rng([seed, sim.rank, k])
+            rng = np.random.default_rng([seed, sim.cell_min[2] - 1 + k])     # by GLOBAL plane: the same load however the box is cut
             P = out[(k - k_begin) * per_plane:(k - k_begin + 1) * per_plane]
             u = rng.random((per_plane, 3))
             u -= 0.5
@@ -185,14 +189,15 @@ def run_reference(args):
     cores = host_cores()
     cells = args.cpu_cells
     rate, s_per_step = cpu_arm(cores, cells, args.steps, args.warmup)
+    ref_scaling = "strong" if (args.gpus > 1 and args.scaling != "weak") else "weak"
     sample = (f"{cores} independent periodic boxes of {cells}^3 cells x {PPC} ppc "
               f"({cores * cells ** 3 * PPC} particles), full step, {args.steps} steps after {args.warmup} warm-up")
     line = {
         "impl": "reference", "metric": "particle-steps/s (push+deposit, full PIC step)", "value": rate,
         "unit": "particle-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": s_per_step * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": s_per_step * 1e3, "higher_is_better": True, "scaling": ref_scaling, "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, args.gpus),
+        "config": workload_config(args, args.gpus, ref_scaling),
         "cpu_baseline": {"value": rate, "unit": "particle-steps/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": "particle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "CPU restatement of the reference (oracle/, g++ -O3 -march=x86-64-v3, no FMA contraction); "
@@ -201,13 +206,19 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, n_gpus):
+def workload_config(args, n_gpus, scaling="weak"):
     c = args.cells
-    return {"workload": f"epoch3d uniform thermal plasma {c}x{c}x{c * n_gpus} cells x {PPC} ppc electrons, periodic, "
-                        f"{SHAPE} shape, fp64 (BASELINE.json configs[2]; {c}^3 per GPU, slabs along z)",
-            "cells_per_gpu": [c, c, c], "ppc": PPC, "particles_per_gpu": c ** 3 * PPC,
+    if scaling == "strong" and n_gpus > 1:
+        glob, per = (c, c, c), (c, c, c // n_gpus)
+        what = f"global {c}^3 cut into {n_gpus} slabs of {c}x{c}x{c // n_gpus} along z (strong scaling)"
+    else:
+        glob, per = (c, c, c * n_gpus), (c, c, c)
+        what = f"{c}^3 per GPU, slabs along z" + (" (weak scaling)" if n_gpus > 1 else "")
+    return {"workload": f"epoch3d uniform thermal plasma {glob[0]}x{glob[1]}x{glob[2]} cells x {PPC} ppc electrons, periodic, "
+                        f"{SHAPE} shape, fp64 (BASELINE.json configs[2]; {what})",
+            "cells_per_gpu": list(per), "ppc": PPC, "particles_per_gpu": per[0] * per[1] * per[2] * PPC,
             "density_m3": DENSITY, "temperature_keV": 1.0, "dx_over_debye": 0.5, "dt_over_cfl": 0.95,
-            "l2_policy": "inputs larger than L2 (particle arrays %.1f GB per GPU)" % (c ** 3 * PPC * 56 / 1e9),
+            "l2_policy": "inputs larger than L2 (particle arrays %.1f GB per GPU)" % (per[0] * per[1] * per[2] * PPC * 56 / 1e9),
             "parallelism": f"domain decomposition 1x1x{n_gpus} (slab along z)"}
 
 
@@ -235,7 +246,6 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the product library has no CPU path")
     torch.cuda.set_device(local)
     abi = _abi.product()
-    nccl_id = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -250,129 +260,25 @@ def run_ours(args):
             buf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
         dist.broadcast(buf, 0)
         return bytes(buf.cpu().numpy().tobytes())
-    nccl_id = fresh_nccl_id()
 
     def barrier():
         if world > 1:
             dist.barrier()
 
-    def max_over_ranks(x):
+    def reduce_ranks(x, op="max"):
         if world == 1:
             return x
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op={"max": dist.ReduceOp.MAX, "sum": dist.ReduceOp.SUM, "min": dist.ReduceOp.MIN}[op])
         return float(t.item())
 
-    c = args.cells
-    cells_global = (c, c, c * world)
-    n_part = c ** 3 * PPC
-    t_setup = time.perf_counter()
-    sim = make_sim(abi, cells_global, rank, world, nccl_id, device=local)
-    # deferred permute: head room between the two states of the particle arrays (7 % of the species:
-    # a quarter for the displacements -- one layer of tiles -- and three quarters for the particles of a launch)
-    sim.ctx.set_option("defer_window", max(n_part // 14, min(n_part // 2, 1 << 24)))
-    for kv in args.opt:                       # tuning experiments: --opt push_kernel=tiled
-        k, v = kv.split("=", 1)
-        sim.ctx.set_option(k, v)
-    sim.ctx.set_option("reserve", f"0:{n_part + n_part // 64 if world > 1 else n_part}")
-    sim.ctx.set_option("timers", 1)
-    # host copy of this rank's particle load (also the e2e leg's host buffer) -- if the host
-    # has the memory for one per rank; else the load is generated and uploaded in slabs and
-    # the e2e leg (which needs the whole state in host buffers) is skipped
     import psutil
     local_world = int(os.environ.get("LOCAL_WORLD_SIZE", str(world)))
-    # (the host buffers are page-locked: keep a good part of the host's memory unpinned)
-    host_budget = 0.70 * psutil.virtual_memory().available / max(1, local_world)
-    if args.host_gb is not None:
-        host_budget = args.host_gb * 1e9
-    full_host = n_part * 56 * 1.04 < host_budget
     gen_threads = max(1, host_cores() // max(1, local_world))
-    if full_host:
-        host_all = sim.ctx.host_empty((n_part + (n_part // 64 if world > 1 else 0), 7))   # room for migrated-in particles
-        host = host_all[:n_part]
-        fill_particles(host, sim, args.seed, gen_threads)
-        t_gen = time.perf_counter() - t_setup
-        sim.ctx.upload_particles(0, host)
-    else:
-        per_plane = c * c * PPC
-        planes = max(1, min(c, int(host_budget / (per_plane * 56 * (1 + 1 / 64)))))
-        host_all = sim.ctx.host_empty((planes * per_plane + planes * per_plane // 64, 7))
-        host = host_all[:planes * per_plane]
-        t_gen = 0.0
-        for k0 in range(0, c, planes):
-            k1 = min(c, k0 + planes)
-            tg = time.perf_counter()
-            fill_particles(host, sim, args.seed, gen_threads, k0, k1)
-            t_gen += time.perf_counter() - tg
-            sim.ctx.upload_particles(0, host[:(k1 - k0) * per_plane], append=k0 > 0)
-    sim.ctx.sync()
-    t_up = time.perf_counter() - t_setup - t_gen
-
-    for _ in range(args.warmup):
-        sim.step_once()
-    sim.ctx.sync()
-    for ph in ("push", "push_kernel", "push_A", "push_B", "sort", "fields", "halo", "bcs", "step"):
-        sim.ctx.timer(ph, reset=True)
-    l0 = sim.ctx.timer("launches")[1]
-    clocks = ClockSampler(local)
-    barrier(); torch.cuda.synchronize()
-    if rank == 0:
-        clocks.start()
-    sim.ctx.mark("step", 1)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        sim.step_once()
-    sim.ctx.mark("step", 0)
-    sim.ctx.sync()
-    wall = time.perf_counter() - t0
-    barrier(); torch.cuda.synchronize()
-    clk = clocks.stop() if rank == 0 else None
-    dev_ms = sim.ctx.timer("step")[0]
-    launches = sim.ctx.timer("launches")[1] - l0
-    ms = max_over_ranks(dev_ms)
-    phases = {ph: sim.ctx.timer(ph) for ph in ("push", "push_kernel", "push_A", "push_B", "sort", "fields", "halo", "bcs")}
-    sorts = {"deferred_to_next_push": sim.ctx.timer("deferred_sorts")[1], "permuted_in_sort": sim.ctx.timer("permuted_sorts")[1]}
-    n_live = sim.ctx.particle_count(0)
-    value = n_part * world * args.steps / (ms * 1e-3)
-
-    # roofline of the dominant kernel (push + deposit): algorithmic bytes per launch
-    # = 104 B per particle (read x,y,z,px,py,pz,w; write x,y,z,px,py,pz) + 72 B per
-    # cell (read 6 field components, write 3 current components)   [SURVEY 8d]
     peaks, how = measured_peaks()
-    pk_ms, pk_launch = phases["push_kernel"]
-    roof = None
-    if pk_launch > 0 and pk_ms > 0:
-        n_launch = args.steps      # one species => one push launch per step
-        alg_bytes = 104.0 * n_live + 72.0 * c ** 3
-        ach = alg_bytes / (pk_ms / n_launch * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "k_push_split + k_deposit_split (one push+deposit pass over all slabs = one 'launch')", "achieved": ach, "peak": peaks["hbm_gbs"],
-                "unit": "GB/s", "frac": ach / peaks["hbm_gbs"], "traffic": None, "peak_source": how,
-                "ms_per_launch": pk_ms / n_launch, "algorithmic_bytes_per_launch": alg_bytes,
-                "particle_steps_per_s_kernel_only": n_live / (pk_ms / n_launch * 1e-3),
-                "share_of_step": pk_ms / dev_ms}
-        tr = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tr):
-            try:
-                roof["traffic"] = json.load(open(tr)).get("push_bytes_per_particle", None)
-                if roof["traffic"] is not None:       # ncu DRAM bytes per particle (profiles/) x particles of a pass
-                    roof["traffic"] = roof["traffic"] * n_live
-                    roof["traffic_source"] = "profiles/traffic.json (ncu --set full dram bytes per particle, 128^3 capture)"
-            except Exception:
-                pass
-    fields_ms, fields_l = phases["fields"]
-    field_line = None
-    if fields_l > 0:
-        cells = (c + 1) ** 3
-        fb = (2 * 96.0 + 2 * 72.0) * cells * args.steps      # 2 E + 2 B half-steps per step
-        field_line = {"cell_updates_per_s": 4 * cells * args.steps / (fields_ms * 1e-3),
-                      "achieved_gbs": fb / (fields_ms * 1e-3) / 1e9,
-                      "frac_of_hbm": fb / (fields_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
-    sim_d, sim_gml, sim_ng = tuple(sim.d), tuple(sim.grid_min_local), sim.ctx.ng
-    pinned_host = bool(getattr(sim.ctx, "pinned_host", False))
-    sim.ctx.close()
-    del sim
+    c = args.cells
 
-    def sim_host_empty(shape):
+    def sim_host_empty(pinned_host, shape):
         """page-locked float64 array (no context needed), ordinary memory if that fails"""
         import ctypes
         n = int(np.prod(shape))
@@ -384,84 +290,269 @@ def run_ours(args):
         weakref.finalize(buf, abi.host_free, p.value)
         return np.frombuffer(buf, dtype=np.float64).reshape(shape)
 
-    # e2e: same metric through the C ABI from host buffers (upload, K steps, download)
-    e2e = None
-    e2e_note = None
-    if not args.no_e2e:
-        cells_e2e, n_e2e = cells_global, n_part
-        if not full_host:
-            # the host cannot hold this rank's whole state: the e2e leg runs the same deck on the
-            # z extent whose particles fit the host buffer (said in e2e.what)
-            import types
-            cells_e2e, n_e2e = (c, c, planes * world), planes * per_plane
-            geo = types.SimpleNamespace(n_local=(c, c, planes), d=sim_d, rank=rank,
-                                        grid_min_local=(sim_gml[0], sim_gml[1], sim_gml[2] - rank * (c - planes) * sim_d[2]))
-            fill_particles(host, geo, args.seed, gen_threads)
-            e2e_note = (f"host memory holds {planes} of the {c} z planes per rank: this leg runs "
-                        f"{c}x{c}x{planes} cells per GPU (the device-timed value is on the full {c}^3)")
-        nccl_id2 = fresh_nccl_id()
-        # host-side field buffers of the e2e leg (page-locked like the particle buffer): six zero input
-        # arrays, nine output arrays
-        shp_e2e = tuple(reversed([n + 2 * sim_ng for n in (cells_e2e[0], cells_e2e[1], cells_e2e[2] // world)]))
-        fzero = sim_host_empty(shp_e2e)
-        fzero[...] = 0.0
-        fout = {k: sim_host_empty(shp_e2e) for k in ("ex", "ey", "ez", "bx", "by", "bz", "jx", "jy", "jz")}
-        for a in fout.values():
-            a[...] = 0.0          # touch the pages before the clock starts
-        barrier(); torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        sim2 = make_sim(abi, cells_e2e, rank, world, nccl_id2, device=local)
-        sim2.ctx.set_option("defer_window", max(n_e2e // 14, min(n_e2e // 2, 1 << 24)))
-        for kv in args.opt:
+    def set_options(sim, n_part):
+        # deferred permute: head room between the two states of the particle arrays (7 % of the species:
+        # a quarter for the displacements -- one layer of tiles -- and three quarters for the particles of a launch)
+        sim.ctx.set_option("defer_window", max(n_part // 14, min(n_part // 2, 1 << 24)))
+        for kv in args.opt:                       # tuning experiments: --opt push_kernel=tiled
             k, v = kv.split("=", 1)
-            sim2.ctx.set_option(k, v)
-        sim2.ctx.set_option("reserve", f"0:{n_e2e + n_e2e // 64 if world > 1 else n_e2e}")
-        shp = sim2.ctx._np_shape()
-        sim2.ctx.upload_fields(ex=fzero, ey=fzero, ez=fzero, bx=fzero, by=fzero, bz=fzero)
-        t1 = time.perf_counter()
-        sim2.ctx.upload_particles(0, host)
-        t2 = time.perf_counter()
-        t2a = t2
-        for i in range(args.steps):
-            sim2.step_once()
-            if i == 0:            # the first step carries the initial sort and the one-time allocations
-                sim2.ctx.sync()
-                t2a = time.perf_counter()
-        sim2.ctx.sync()
-        t3 = time.perf_counter()
-        got = sim2.ctx.download_particles(0, out=host_all)
-        fld = sim2.ctx.download_fields(out=fout)
-        sim2.ctx.sync()
-        t4 = time.perf_counter()
-        t_e2e = max_over_ranks(t4 - t0)
-        h2d = host.nbytes + 6 * fzero.nbytes
-        d2h = got.nbytes + 9 * fzero.nbytes
-        e2e = {"value": n_e2e * world * args.steps / t_e2e, "unit": "particle-steps/s",
-               "h2d_bytes_per_step": h2d * world / args.steps, "d2h_bytes_per_step": d2h * world / args.steps,
-               "seconds": t_e2e, "steps_per_residency": args.steps,
-               "seconds_split": {"create_alloc_upload_fields": t1 - t0, "upload_particles": t2 - t1,
-                                 "first_step": t2a - t2, "other_steps": t3 - t2a, "download": t4 - t3},
-               "h2d_gbs": host.nbytes / (t2 - t1) / 1e9, "d2h_gbs": (got.nbytes + 9 * fzero.nbytes) / (t4 - t3) / 1e9,
-               "host_buffers": "page-locked (eb200_host_alloc)" if pinned_host else "pageable (staged through the library's pinned ring)",
-               "what": "eb200_create + upload_fields + upload_particles from host buffers + K full steps + "
-                       "download_particles + download_fields into host buffers "
-                       "+ sync, wall clock; the state lives on the device between steps, so the copies are "
-                       "amortised over K steps" + ("; " + e2e_note if e2e_note else "")}
-        del fld
-        sim2.ctx.close()
+            sim.ctx.set_option(k, v)
+        sim.ctx.set_option("reserve", f"0:{n_part + max(n_part // 64, 1 << 18) if world > 1 else n_part}")
+
+    def measure(cells_global, mode, want_e2e):
+        """device-timed K steps (+ the e2e leg) of the deck on `cells_global`, slabs along z"""
+        nz_local = cells_global[2] // world
+        n_part = cells_global[0] * cells_global[1] * nz_local * PPC
+        per_plane = cells_global[0] * cells_global[1] * PPC
+        t_setup = time.perf_counter()
+        sim = make_sim(abi, cells_global, rank, world, fresh_nccl_id(), device=local)
+        set_options(sim, n_part)
+        sim.ctx.set_option("timers", 1)
+        # host copy of this rank's particle load (also the e2e leg's host buffer) -- if the host
+        # has the memory for one per rank; else the load is generated and uploaded in slabs and
+        # the e2e leg (which needs the whole state in host buffers) is skipped
+        # (the host buffers are page-locked: keep a good part of the host's memory unpinned)
+        host_budget = 0.70 * psutil.virtual_memory().available / max(1, local_world)
+        if args.host_gb is not None:
+            host_budget = args.host_gb * 1e9
+        full_host = n_part * 56 * 1.04 < host_budget
+        spare = max(n_part // 64, 1 << 18) if world > 1 else 0
+        if full_host:
+            host_all = sim.ctx.host_empty((n_part + spare, 7))   # room for migrated-in particles
+            host = host_all[:n_part]
+            fill_particles(host, sim, args.seed, gen_threads)
+            t_gen = time.perf_counter() - t_setup
+            sim.ctx.upload_particles(0, host)
+        else:
+            planes = max(1, min(nz_local, int(host_budget / (per_plane * 56 * (1 + 1 / 64)))))
+            host_all = sim.ctx.host_empty((planes * per_plane + planes * per_plane // 64, 7))
+            host = host_all[:planes * per_plane]
+            t_gen = 0.0
+            for k0 in range(0, nz_local, planes):
+                k1 = min(nz_local, k0 + planes)
+                tg = time.perf_counter()
+                fill_particles(host, sim, args.seed, gen_threads, k0, k1)
+                t_gen += time.perf_counter() - tg
+                sim.ctx.upload_particles(0, host[:(k1 - k0) * per_plane], append=k0 > 0)
+        sim.ctx.sync()
+        t_up = time.perf_counter() - t_setup - t_gen
+
+        # parity check, outside the timed region: the Gauss-law residual is captured at the first half step
+        # (E at t + dt/2, particles at x(t): div E - rho(x + half drift)/eps0 is invariant under the Esirkepov
+        # deposit), energy and particle count are taken before the warm-up
+        def capture(s_):
+            s_.ctx.set_option("capture_charge_reference", "1")
+        check = {}
+        i_cap = min(1, args.warmup - 1)      # (second warm-up step: the spare array of the first sort has been given back)
+        for i in range(args.warmup):
+            sim.step_once(after_half=capture if (i == i_cap and not args.no_check) else None)
+            if i == i_cap and not args.no_check:
+                fe0, pe0 = sim.ctx.energy()
+                check["e0"] = (reduce_ranks(fe0, "sum"), reduce_ranks(sum(pe0), "sum"))
+        sim.ctx.sync()
+        for ph in ("push", "push_kernel", "push_A", "push_B", "sort", "fields", "halo", "bcs", "step"):
+            sim.ctx.timer(ph, reset=True)
+        l0 = sim.ctx.timer("launches")[1]
+        clocks = ClockSampler(local)
+        barrier(); torch.cuda.synchronize()
+        if rank == 0:
+            clocks.start()
+        sim.ctx.mark("step", 1)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            sim.step_once()
+        sim.ctx.mark("step", 0)
+        sim.ctx.sync()
+        wall = time.perf_counter() - t0
+        barrier(); torch.cuda.synchronize()
+        clk = clocks.stop() if rank == 0 else None
+        dev_ms = sim.ctx.timer("step")[0]
+        launches = sim.ctx.timer("launches")[1] - l0
+        ms = reduce_ranks(dev_ms)
+        phases = {ph: sim.ctx.timer(ph) for ph in ("push", "push_kernel", "push_A", "push_B", "sort", "fields", "halo", "bcs")}
+        phases_max = {ph: reduce_ranks(v[0]) / args.steps for ph, v in phases.items()}
+        sorts = {"deferred_to_next_push": sim.ctx.timer("deferred_sorts")[1], "permuted_in_sort": sim.ctx.timer("permuted_sorts")[1]}
+        n_live = sim.ctx.particle_count(0)
+        n_global = int(round(reduce_ranks(float(n_live), "sum")))
+        n_expected = cells_global[0] * cells_global[1] * cells_global[2] * PPC
+        value = n_expected * args.steps / (ms * 1e-3)
+        parity = None
+        if not args.no_check:
+            res = {}
+
+            def residual(s_):
+                res["r"] = s_.ctx.charge_residual()
+            sim.step_once(after_half=residual)       # one more (untimed) step: residual at its half step
+            fe1, pe1 = sim.ctx.energy()
+            e1 = (reduce_ranks(fe1, "sum"), reduce_ranks(sum(pe1), "sum"))
+            r_max, rho_max = reduce_ranks(res["r"][0]), reduce_ranks(res["r"][1])
+            e0 = check["e0"]
+            drift = (e1[0] + e1[1]) / (e0[0] + e0[1]) - 1.0
+            n_after = int(round(reduce_ranks(float(sim.ctx.particle_count(0)), "sum")))
+            parity = {"particles": n_after, "particles_expected": n_expected,
+                      "energy_field_J": e1[0], "energy_kinetic_J": e1[1],
+                      "energy_total_drift_rel": drift, "steps_between_energy_samples": args.warmup - 1 - i_cap + args.steps + 1,
+                      "charge_residual_max": r_max, "rho_over_eps0_max": rho_max,
+                      "charge_residual_rel": r_max / max(rho_max, 1e-300),
+                      "what": "global particle count (periodic box: conserved exactly), total energy drift over the run, "
+                              "max |div E - rho/eps0| against its value at the first step (exact charge conservation "
+                              "of the Esirkepov deposit); sums / maxima over all ranks"}
+            parity["ok"] = bool(n_after == n_expected and abs(drift) < 1e-2 and parity["charge_residual_rel"] < 1e-9)
+
+        # roofline of the dominant kernel pair (push + deposit): algorithmic bytes per launch
+        # = 104 B per particle (read x,y,z,px,py,pz,w; write x,y,z,px,py,pz) + 72 B per
+        # cell (read 6 field components, write 3 current components)   [SURVEY 8d]
+        pk_ms, pk_launch = phases["push_kernel"]
+        roof = None
+        if pk_launch > 0 and pk_ms > 0:
+            n_launch = args.steps      # one species => one push launch per step
+            ncell_local = cells_global[0] * cells_global[1] * nz_local
+            alg_bytes = 104.0 * n_live + 72.0 * ncell_local
+            t_launch = pk_ms / n_launch * 1e-3
+            ach = alg_bytes / t_launch / 1e9
+            roof = {"bound": "hbm", "kernel": "k_push_split + k_deposit_split (one push+deposit pass over all slabs = one 'launch')", "achieved": ach, "peak": peaks["hbm_gbs"],
+                    "unit": "GB/s", "frac": ach / peaks["hbm_gbs"], "traffic": None, "peak_source": how,
+                    "ms_per_launch": pk_ms / n_launch, "algorithmic_bytes_per_launch": alg_bytes,
+                    "particle_steps_per_s_kernel_only": n_live / t_launch,
+                    "share_of_step": pk_ms / dev_ms}
+            tr = os.path.join(ROOT, "profiles", "traffic.json")
+            if os.path.exists(tr):
+                try:
+                    tj = json.load(open(tr))
+                    if tj.get("push_bytes_per_particle") is not None:       # ncu DRAM bytes per particle (profiles/) x particles of a pass
+                        roof["traffic"] = tj["push_bytes_per_particle"] * n_live
+                        roof["traffic_source"] = tj.get("source", "profiles/traffic.json (ncu --set full dram bytes per particle)")
+                        roof["frac_of_hbm_with_measured_traffic"] = roof["traffic"] / t_launch / 1e9 / peaks["hbm_gbs"]
+                    # the pair is not HBM bound: the fp64 pipe and the shared-memory data stage are busier.  Their fractions
+                    # come from the ncu capture (instructions / wavefronts per particle) x the live particle rate.
+                    if tj.get("fp64_inst_per_particle") is not None:
+                        dfma_peak = tj.get("dfma_peak_per_s", 17.245e12)      # measured: 34.49 TFLOP/s DFMA (profiles/r01_microbench_b200.txt)
+                        roof["fp64"] = {"achieved_inst_per_s": tj["fp64_inst_per_particle"] * n_live / t_launch,
+                                        "peak_inst_per_s": dfma_peak,
+                                        "frac": tj["fp64_inst_per_particle"] * n_live / t_launch / dfma_peak,
+                                        "ncu_sm__pipe_fp64_cycles_active_pct": tj.get("ncu_fp64_pipe_pct")}
+                    if tj.get("lsu_wavefronts_per_particle") is not None:
+                        wf_peak = 148 * tj.get("sm_clock_hz", 1.93e9)         # one shared-memory / L1 data-stage wavefront per clock per SM
+                        roof["l1_data_stage"] = {"frac": tj["lsu_wavefronts_per_particle"] * n_live / t_launch / wf_peak,
+                                                 "ncu_l1tex__data_pipe_lsu_wavefronts_pct": tj.get("ncu_l1_wavefront_pct")}
+                    fr = {"hbm": roof.get("frac_of_hbm_with_measured_traffic", roof["frac"]),
+                          "fp64": roof.get("fp64", {}).get("frac", 0.0), "l1": roof.get("l1_data_stage", {}).get("frac", 0.0)}
+                    roof["binding"] = max(fr, key=fr.get)
+                    roof["bound"] = "hbm" if roof["binding"] == "hbm" else roof["binding"]
+                except Exception:
+                    pass
+        fields_ms, fields_l = phases["fields"]
+        field_line = None
+        if fields_l > 0:
+            cells = (cells_global[0] + 1) * (cells_global[1] + 1) * (nz_local + 1)
+            fb = (2 * 96.0 + 2 * 72.0) * cells * args.steps      # 2 E + 2 B half-steps per step
+            field_line = {"cell_updates_per_s": 4 * cells * args.steps / (fields_ms * 1e-3),
+                          "achieved_gbs": fb / (fields_ms * 1e-3) / 1e9,
+                          "frac_of_hbm": fb / (fields_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+        sim_ng = sim.ctx.ng
+        pinned_host = bool(getattr(sim.ctx, "pinned_host", False))
+        sim.ctx.close()
+        del sim
+
+        # e2e: same metric through the C ABI from host buffers (upload, K steps, download)
+        def e2e_leg(steps):
+            if not full_host:
+                return None
+            shp = tuple(reversed([n + 2 * sim_ng for n in (cells_global[0], cells_global[1], nz_local)]))
+            fzero = sim_host_empty(pinned_host, shp)
+            fzero[...] = 0.0
+            fout = {k: sim_host_empty(pinned_host, shp) for k in ("ex", "ey", "ez", "bx", "by", "bz", "jx", "jy", "jz")}
+            for a in fout.values():
+                a[...] = 0.0          # touch the pages before the clock starts
+            nid = fresh_nccl_id()
+            barrier(); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            sim2 = make_sim(abi, cells_global, rank, world, nid, device=local)
+            set_options(sim2, n_part)
+            sim2.ctx.upload_fields(ex=fzero, ey=fzero, ez=fzero, bx=fzero, by=fzero, bz=fzero)
+            t1 = time.perf_counter()
+            sim2.ctx.upload_particles(0, host)
+            t2 = time.perf_counter()
+            t2a = t2
+            for i in range(steps):
+                sim2.step_once()
+                if i == 0:            # the first step carries the initial sort and the one-time allocations
+                    sim2.ctx.sync()
+                    t2a = time.perf_counter()
+            sim2.ctx.sync()
+            t3 = time.perf_counter()
+            got = sim2.ctx.download_particles(0, out=host_all)
+            fld = sim2.ctx.download_fields(out=fout)
+            sim2.ctx.sync()
+            t4 = time.perf_counter()
+            t_e2e = reduce_ranks(t4 - t0)
+            h2d = host.nbytes + 6 * fzero.nbytes
+            d2h = got.nbytes + 9 * fzero.nbytes
+            out = {"value": n_expected * steps / t_e2e, "unit": "particle-steps/s",
+                   "h2d_bytes_per_step": h2d * world / steps, "d2h_bytes_per_step": d2h * world / steps,
+                   "seconds": t_e2e, "steps_per_residency": steps,
+                   "seconds_split": {"create_alloc_upload_fields": t1 - t0, "upload_particles": t2 - t1,
+                                     "first_step": t2a - t2, "other_steps": t3 - t2a, "download": t4 - t3},
+                   "h2d_gbs": host.nbytes / (t2 - t1) / 1e9, "d2h_gbs": (got.nbytes + 9 * fzero.nbytes) / (t4 - t3) / 1e9,
+                   "host_buffers": "page-locked (eb200_host_alloc)" if pinned_host else "pageable (staged through the library's pinned ring)",
+                   "what": "eb200_create + upload_fields + upload_particles from host buffers + K full steps + "
+                           "download_particles + download_fields into host buffers + sync, wall clock, max over ranks, "
+                           "on the SAME deck and size as `value`; the state lives on the device between steps, so the "
+                           "copies are amortised over K steps"}
+            del fld
+            sim2.ctx.close()
+            return out
+        e2e = None
+        if want_e2e and not args.no_e2e:
+            e2e = e2e_leg(args.steps)
+            if e2e is None:
+                e2e = {"value": None, "unmeasured": "the host cannot hold this rank's particle state in page-locked buffers "
+                                                    f"({n_part * 56 / 1e9:.0f} GB per rank, {local_world} ranks on this host)"}
+            elif args.e2e_long > 0 and world == 1:
+                lg = e2e_leg(args.e2e_long)     # the same with more steps per residency: the copies amortise
+                e2e["longer_residency"] = {k: lg[k] for k in ("value", "seconds", "steps_per_residency", "seconds_split")}
+        return {
+            "value": value, "ms_per_step": ms / args.steps, "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roof, "fields": field_line, "parity_check": parity,
+            "phases_ms_per_step": {k: v[0] / args.steps for k, v in phases.items()},
+            "phases_ms_per_step_max_over_ranks": phases_max,
+            "sorts_whole_run": sorts, "wall_ms_per_step": wall * 1e3 / args.steps,
+            "setup_seconds": {"generate_host": t_gen, "upload": t_up},
+            "cells_global": list(cells_global), "cells_per_gpu": [cells_global[0], cells_global[1], nz_local],
+            "particles_global": n_expected, "scaling": mode,
+        }
+
+    scaling = args.scaling
+    if scaling == "auto":
+        scaling = "strong" if world > 1 else "weak"
+    if world > 1 and c % world != 0:
+        raise SystemExit("--cells must be a multiple of the number of GPUs for the strong-scaling mode")
+    main_res = measure((c, c, c) if scaling == "strong" else (c, c, c * world), scaling, True)
+    other = None
+    if world > 1 and args.scaling == "auto" and not args.one_mode:
+        # the other mode as an extra key (device-timed only): weak = one 512^3 slab per GPU
+        other = measure((c, c, c * world), "weak", False)
     if rank != 0:
+        if main_res["parity_check"] is not None and not main_res["parity_check"]["ok"]:
+            sys.exit(3)
         return
     line = {
-        "metric": "particle-steps/s (push+deposit, full PIC step)", "value": value, "unit": "particle-steps/s",
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args, world), "clocks": clk, "e2e": e2e, "gpu_launches": int(launches),
-        "roofline": roof, "fields": field_line,
-        "phases_ms_per_step": {k: v[0] / args.steps for k, v in phases.items()},
-        "sorts_whole_run": sorts,
-        "wall_ms_per_step": wall * 1e3 / args.steps,
-        "setup_seconds": {"generate_host": t_gen, "upload": t_up},
+        "metric": "particle-steps/s (push+deposit, full PIC step)", "value": main_res["value"], "unit": "particle-steps/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": main_res["ms_per_step"],
+        "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args, world, scaling), "clocks": main_res["clocks"], "e2e": main_res["e2e"],
+        "gpu_launches": main_res["gpu_launches"], "roofline": main_res["roofline"], "fields": main_res["fields"],
+        "parity_check": main_res["parity_check"],
+        "phases_ms_per_step": main_res["phases_ms_per_step"],
+        "phases_ms_per_step_max_over_ranks": main_res["phases_ms_per_step_max_over_ranks"],
+        "sorts_whole_run": main_res["sorts_whole_run"], "wall_ms_per_step": main_res["wall_ms_per_step"],
+        "setup_seconds": main_res["setup_seconds"],
     }
+    if other is not None:
+        line["weak"] = {k: other[k] for k in ("value", "ms_per_step", "cells_global", "cells_per_gpu", "particles_global",
+                                              "phases_ms_per_step_max_over_ranks", "parity_check", "gpu_launches")}
+        line["weak"]["what"] = (f"the same deck with one {c}^3 slab per GPU stacked along z (weak scaling), device-timed; "
+                                "efficiency = weak.value / (n_gpus x the 1-GPU value)")
     if world == 1 and not args.no_cpu:
         cores = host_cores()
         rate, s_per = cpu_arm(cores, args.cpu_cells, 3, 1)
@@ -469,6 +560,8 @@ def run_ours(args):
                                 "sample": f"{cores} independent periodic boxes of {args.cpu_cells}^3 cells x {PPC} ppc, "
                                           f"full step, 3 steps after 1 warm-up ({s_per:.2f} s/step)"}
     print(json.dumps(line), flush=True)
+    if main_res["parity_check"] is not None and not main_res["parity_check"]["ok"]:
+        sys.exit(3)
 
 
 def main():
@@ -481,6 +574,12 @@ def main():
     ap.add_argument("--cpu-cells", type=int, default=64, help="cells per dimension per CPU process (cpu arm)")
     ap.add_argument("--seed", type=int, default=12345)
     ap.add_argument("--shape", default="triangle", choices=["tophat", "triangle", "bspline3"])
+    ap.add_argument("--scaling", default="auto", choices=["auto", "strong", "weak"],
+                    help="N > 1: strong = the global cells^3 box cut into N slabs (the line printed; auto adds the weak "
+                         "run as an extra key), weak = one cells^3 slab per GPU")
+    ap.add_argument("--one-mode", action="store_true", help="N > 1, --scaling auto: skip the extra weak-scaling run")
+    ap.add_argument("--no-check", action="store_true", help="skip the parity check (particle count, energy drift, Gauss residual)")
+    ap.add_argument("--e2e-long", type=int, default=100, help="steps of the second e2e leg at N = 1 (0 = skip)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--host-gb", type=float, default=None, help="host memory per rank for the particle copy (default: from free memory)")

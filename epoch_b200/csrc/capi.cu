@@ -602,7 +602,10 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
     c->pin_bytes = (size_t)std::max<long long>(atoll(value), 1024);
     return 0;
   }
-  if (k == "mig_capacity") { c->mig_min_particles = atoll(value); return 0; }
+  if (k == "mig_capacity") {      // particles per migration mailbox to start with (the same on every rank)
+    if (atoll(value) < 1) return fail(c, EB200_E_ARG, "mig_capacity must be >= 1");
+    c->mig_min_particles = atoll(value); return 0;
+  }
   return fail(c, EB200_E_ARG, "unknown option " + k);
 }
 

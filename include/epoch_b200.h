@@ -322,7 +322,9 @@ int32_t EB200_NAME(download_probe)(EB200_CTX*, int32_t ispecies, int32_t iprobe,
  *   "reserve"       "<species>:<particles>"  allocate a species' storage once
  *   "deposit_scratch" "<particles>" particles per push/deposit launch (64 B of scratch each)
  *   "fuse_keys" "0|1", "tma" "0|1", "timers" "0|1", "host_threads" "<n>", "pin_bytes" "<bytes>",
- *   "mig_capacity" "<particles>", "capture_charge_reference" "1" */
+ *   "mig_capacity" "<particles>"   first capacity of a migration mailbox (per neighbour and direction; the SAME on every
+ *                                   rank); it doubles by itself when more particles want to cross
+ *   "capture_charge_reference" "1" */
 int32_t EB200_NAME(set_option)(EB200_CTX*, const char* key, const char* value);
 int32_t EB200_NAME(sync)(EB200_CTX*);
 /* milliseconds of device time spent in the named phase since the last call with

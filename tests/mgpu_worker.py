@@ -21,6 +21,7 @@ SHAPE = sys.argv[3] if len(sys.argv) > 3 else "triangle"
 WINDOW = len(sys.argv) > 4 and sys.argv[4] == "window"      # moving window at 0.9 c (x decomposition, open x boundaries)
 CPML = len(sys.argv) > 4 and sys.argv[4] == "cpml"          # CPML layers on the decomposed axis and on x
 BALANCE = len(sys.argv) > 4 and sys.argv[4] == "balance"    # lopsided plasma, re-sliced after 2 steps
+SMALLBOX = len(sys.argv) > 4 and sys.argv[4] == "smallbox"  # migration mailboxes far too small at first: leavers wait, boxes grow
 N = [16, 12, 20]
 CELL = 1e-6
 
@@ -59,6 +60,8 @@ def build(abi, rank, nproc, nccl_id, device):
         kw = dict(bc_field=fbc)
         for s in sp:
             s.bcs = pbc
+    if SMALLBOX:
+        kw["options"] = {"mig_capacity": 16}
     sim = Simulation(3, N, [0.0] * 3, [n * CELL for n in N], shape=SHAPE, species=sp, abi=abi, device=device,
                      rank=rank, nproc=nproc, nprocdir=tuple(nprocdir), nccl_id=nccl_id, **kw)
     rng = np.random.default_rng(11)

@@ -25,6 +25,19 @@ def test_two_ranks_equal_one(axis, shape):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
 
 
+@pytest.mark.parametrize("axis", [0, 2])
+def test_two_ranks_small_mailboxes(axis):
+    """migration mailboxes of 16 particles against hundreds of leavers per step: the surplus waits a step in the
+    ghost cells of the rank it left (gather and deposit still valid there), the boxes grow by the agreed rule --
+    no error, no deadlock, and the run still equals the single-GPU run"""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", str(29651 + axis), os.path.join(ROOT, "tests", "mgpu_worker.py"), str(axis), "6", "triangle", "smallbox"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 def test_two_ranks_moving_window():
     """moving window with the domain cut along x: insertion on the last rank, removal on the first,
     shifted fields exchanged through the halos -- equals the single-GPU run"""
