@@ -148,6 +148,7 @@ int32_t eb200_destroy(eb200_ctx* c) {
                   c->cpml_prof[0], c->cpml_prof[1], c->cpml_prof[2]};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (int b = 0; b < 6; ++b) if (c->bnd_planes[b]) cudaFree(c->bnd_planes[b]);
+  if (c->d_probeset) cudaFree(c->d_probeset);
   free_pinned(c);
   if (c->h_counters) cudaFreeHost(c->h_counters);
   if (c->h_red) cudaFreeHost(c->h_red);

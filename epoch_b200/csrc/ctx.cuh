@@ -197,6 +197,7 @@ struct eb200_ctx {
   alignas(64) unsigned char tmap[128] = {0};
   long long tmap_sig[6] = {0, 0, 0, 0, 0, 0};
   bool tmap_valid = false, tmap_ok = false;
+  void* d_probeset = nullptr;           // device copy of the probe set of the species being pushed (tiled kernels)
   long long probe_capacity = 1 << 18;   // option probe_capacity: sampled particles kept per probe
   int use_tma = 1;              // option tma: 0 = stage the field tile with plain loads
   double* det_tiles = nullptr;                // deterministic deposit: one J tile per deposit CTA of a launch

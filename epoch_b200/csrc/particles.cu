@@ -947,7 +947,7 @@ int32_t push_particles(eb200_ctx* c) {
     {
       ScopedPhase ph(c, "push");
       ScopedPhase pk(c, "push_kernel");     // the kernel(s) alone (roofline figure of bench.py)
-      if ((c->push_kernel == 0 || c->push_kernel == 3) && sp.probes.n == 0) {    // (probes: general kernel)
+      if (c->push_kernel == 0 || c->push_kernel == 3) {
         // single rank: no migration, so the push kernel can apply the particle BCs itself and emit
         // the next sort keys + histogram (saves the sort's pass over the particle arrays)
         std::vector<char> ksbuf(keysink_size());

@@ -368,12 +368,12 @@ __device__ __forceinline__ void load_particle(const PArr& a, long long ip, doubl
 
 // phase 1 for one particle: particles.F90:219-452 (gather stage, Boris, drift, store,
 // extra half drift); leaves the deposit inputs in the record arrays
-template <int ND, int SHAPE, bool GATHER>
+template <int ND, int SHAPE, bool GATHER, bool PROBE = false>
 __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos[3], mom[3], weight */, const PArr& a /* output */,
                                          long long ip, const int* c0,
                                          const double* __restrict__ sF, unsigned long long* counters,
                                          double* rec /* NREC doubles */, int& rec_pack, const GridP* g = nullptr,
-                                         const KeySink* ks = nullptr) {
+                                         const KeySink* ks = nullptr, const ProbeSet* pr = nullptr) {
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW;
   double pos[3] = {0, 0, 0}, px[3] = {0, 0, 0}, ux, uy, uz;
@@ -444,6 +444,31 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
   for (int d = 0; d < ND; ++d) {
     px[d] = px[d] + delta[d];
     posn[d] = px[d] + p.gml[d];
+  }
+  if (PROBE) {
+    // particle probes (particles.F90:567-606): energy window, then the plane crossed along its normal between the
+    // position the push started from and the one it stores (before the particle boundaries are applied)
+    const double part_u2 = ux * ux + uy * uy + uz * uz;
+    const double gamma_rel = sqrt(part_u2 + 1.0);
+    const double probe_energy = part_u2 / (gamma_rel + 1.0) * (C0 * p.part_mc);
+    for (int k = 0; k < pr->n; ++k) {
+      if (!pr->on[k] || !(probe_energy > pr->ek_min[k]) || !(probe_energy < pr->ek_max[k])) continue;
+      double d_init = 0.0, d_final = 0.0;
+#pragma unroll
+      for (int d = 0; d < ND; ++d) {
+        d_init += pr->normal[k][d] * (pr->point[k][d] - in[d]);
+        d_final += pr->normal[k][d] * (pr->point[k][d] - posn[d]);
+      }
+      if (d_final < 0.0 && d_init >= 0.0) {
+        const unsigned long long slot = atomicAdd(pr->count + k, 1ULL);
+        if ((long long)slot < pr->cap) {
+          double* q = pr->buf + ((size_t)k * pr->cap + slot) * (ND + 4);
+#pragma unroll
+          for (int d = 0; d < ND; ++d) q[d] = posn[d];
+          q[ND] = momn[0]; q[ND + 1] = momn[1]; q[ND + 2] = momn[2]; q[ND + 3] = part_weight;
+        }
+      }
+    }
   }
   if (ks != nullptr && ks->on) {
     uint32_t k = ks->nbucket - 1;
@@ -694,12 +719,13 @@ constexpr int RING = EB_RING;    // record slots per thread of the deposit kerne
 
 // GATHER (deferred permute, particles.cu): the particle of sorted index q is read from slot src[q] of the
 // arrays `a` (the pre-sort order) and stored to slot q of `o` (the other state of the same allocations)
-template <int ND, int SHAPE, bool GATHER>
+template <int ND, int SHAPE, bool GATHER, bool PROBE>
 __global__ void __launch_bounds__(NTA, SHAPE == SHAPE_BSPLINE3 ? 2 : EB_MINB_A) k_push_split(GridP g, FieldP F, PushP p, PArr a, PArr o, PArr side,
                                                               const uint32_t* __restrict__ src, uint32_t n_main,
                                                               const uint32_t* __restrict__ cell_start, long long tile0,
                                                               double* __restrict__ scratch, unsigned long long* counters,
-                                                              KeySink ks, const __grid_constant__ CUtensorMap tmap, int use_tma) {
+                                                              KeySink ks, const __grid_constant__ CUtensorMap tmap, int use_tma,
+                                                              const ProbeSet* __restrict__ pr) {
   using T = TL<ND, SHAPE>;
   constexpr int SFM = T::SFM;
   extern __shared__ __align__(128) double smem_a[];
@@ -808,7 +834,7 @@ __global__ void __launch_bounds__(NTA, SHAPE == SHAPE_BSPLINE3 ? 2 : EB_MINB_A) 
     if (act) {
       int pack;
       rec[6] = 0.0;
-      push_one<ND, SHAPE, GATHER>(p, in, o, (long long)q, c0, sF, counters, rec, pack, &g, &ks);
+      push_one<ND, SHAPE, GATHER, PROBE>(p, in, o, (long long)q, c0, sF, counters, rec, pack, &g, &ks, pr);
       rec[7] = __longlong_as_double((long long)pack);
     }
     if (p.zero_current) continue;
@@ -1237,6 +1263,14 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
     side.x[d] = sp.far ? sp.far + (size_t)d * sp.far_cap : nullptr; side.m[d] = sp.far ? sp.far + (size_t)(3 + d) * sp.far_cap : nullptr;
   }
   a.w = sp.a[6]; o.w = sp.base[6] + off_new; side.w = sp.far ? sp.far + (size_t)6 * sp.far_cap : nullptr;
+  // a species with particle probes takes the kernel variant with the crossing test; the probe set sits in device memory
+  const bool probe = sp.probes.n > 0;
+  const ProbeSet* d_probes = nullptr;
+  if (probe) {
+    if (!c->d_probeset) EB_CUDA(c, cudaMalloc(&c->d_probeset, sizeof(ProbeSet)));
+    EB_CUDA(c, cudaMemcpyAsync(c->d_probeset, &sp.probes, sizeof(ProbeSet), cudaMemcpyHostToDevice, c->stream));
+    d_probes = (const ProbeSet*)c->d_probeset;
+  }
   const uint32_t n_main = gather ? (uint32_t)sp.n_old : 0u;
   ks.key = sp.key_base + off_new;
   ensure_tmap(c);
@@ -1287,7 +1321,8 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
     const dim3 ga(nb, (unsigned)((big + PUSH_CHUNK - 1) / PUSH_CHUNK));
 #define L(ND, SH)                                                                                          \
     if (c->ndims == ND && c->shape == SH) {                                                                \
-      auto ka = gather ? k_push_split<ND, SH, true> : k_push_split<ND, SH, false>;                         \
+      auto ka = probe ? (gather ? k_push_split<ND, SH, true, true> : k_push_split<ND, SH, false, true>)    \
+                      : (gather ? k_push_split<ND, SH, true, false> : k_push_split<ND, SH, false, false>);  \
       auto kb = det ? k_deposit_split<ND, SH, true> : k_deposit_split<ND, SH, false>;                      \
       const size_t sa = sizeof(double) * (6 * TL<ND, SH>::FN + (NTA / 32) * (EB_STAGE_HALF ? 128 : 256)) + EB_SMEM_PAD;                                               \
       const size_t sb = sizeof(double) * (det ? 6 : 3) * TL<ND, SH>::JNS + sizeof(int) * (2 * MCAPB + 4)                     \
@@ -1295,7 +1330,7 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
       { ScopedPhase pa(c, "push_A");                                                                       \
-        ka<<<ga, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks, tmap, use_tma); } \
+        ka<<<ga, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks, tmap, use_tma, d_probes); } \
       if (!p.zero_current) { ScopedPhase pb(c, "push_B");                                                  \
         kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch, c->det_tiles); \
         if (det) {                                                                                         \
