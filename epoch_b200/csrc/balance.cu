@@ -132,6 +132,8 @@ int32_t redistribute(eb200_ctx* c, const int32_t* old_cell_min, const int32_t* o
   double* old_f = c->fbase;
   double* old_psi = c->cpml_psi;
   c->fbase = nullptr; c->cpml_psi = nullptr;
+  double* old_bnd[6];        // (set_grid frees every array of the old field shape: the boundary planes are decided on below)
+  for (int b = 0; b < 6; ++b) { old_bnd[b] = c->bnd_planes[b]; c->bnd_planes[b] = nullptr; }
   int32_t nl[3] = {1, 1, 1}, ngm[3] = {1, 1, 1}, ngl[3] = {1, 1, 1};
   double dd[3], gml[3] = {0, 0, 0}, mnl[3] = {0, 0, 0}, mxl[3] = {0, 0, 0}, gmn[3], gmx[3];
   for (int a = 0; a < 3; ++a) {
@@ -143,7 +145,7 @@ int32_t redistribute(eb200_ctx* c, const int32_t* old_cell_min, const int32_t* o
     gml[a] = grid_min_local[a]; mnl[a] = min_local[a]; mxl[a] = max_local[a];
   }
   int32_t rc = eb200_set_grid(c, nl, ngl, ngm, dd, gml, mnl, mxl, gmn, gmx, c->cpml_thickness);
-  if (rc != 0) { cudaFree(old_f); if (old_psi) cudaFree(old_psi); return rc; }
+  if (rc != 0) { cudaFree(old_f); if (old_psi) cudaFree(old_psi); for (int b = 0; b < 6; ++b) if (old_bnd[b]) cudaFree(old_bnd[b]); return rc; }
   const GridP& g = c->g;
   const int npsi = old_psi ? 12 : 0;
   if (npsi) {
@@ -204,12 +206,11 @@ int32_t redistribute(eb200_ctx* c, const int32_t* old_cell_min, const int32_t* o
   // the boundary planes of setup_field_boundaries (the reference's host remaps its own copies, balance.F90:847-1010):
   // a plane whose extents changed belongs to the old slicing and is dropped -- outflow_bcs then refuses to run
   // until the host has handed it over again (set_boundary_fields)
-  for (int b = 0; b < 2 * c->ndims; ++b) {
-    if (!c->bnd_planes[b]) continue;
+  for (int b = 0; b < 6; ++b) {
+    if (!old_bnd[b]) continue;
     const int a = b / 2;
-    if (og.total / (og.n[a] + 2 * og.ngd[a]) == g.total / (g.n[a] + 2 * g.ngd[a]) &&
-        og.n[(a + 1) % 3] == g.n[(a + 1) % 3] && og.n[(a + 2) % 3] == g.n[(a + 2) % 3]) continue;
-    cudaFree(c->bnd_planes[b]); c->bnd_planes[b] = nullptr; c->bnd_dropped[b] = true;
+    if (og.n[(a + 1) % 3] == g.n[(a + 1) % 3] && og.n[(a + 2) % 3] == g.n[(a + 2) % 3]) { c->bnd_planes[b] = old_bnd[b]; continue; }
+    cudaFree(old_bnd[b]); c->bnd_dropped[b] = true;
   }
   if (err) return err;
   EB_CUDA(c, cudaGetLastError());

@@ -504,7 +504,15 @@ static int32_t summation_bcs_n(eb200_ctx* c, Arr3 A, int ncomp, const int* flip,
       double *s_hi = c->halo_send, *s_lo = c->halo_send + cnt, *r_lo = c->halo_recv, *r_hi = c->halo_recv + cnt;
       k_pack2<<<line_grid2(p, ncomp), 128, 0, c->stream>>>(p, A, p.nn, -p.ng, s_hi, s_lo);
       EB_TRY(comm_exchange2(c, s_hi, hi, cnt, s_lo, lo, cnt, r_lo, lo, cnt, r_hi, hi, cnt));
-      k_unpack2<<<line_grid2(p, ncomp), 128, 0, c->stream>>>(p, A, 0, p.nn - p.ng, r_lo, r_hi, 1, lo >= 0, hi >= 0);
+      if (p.nn >= 2 * p.ng) {
+        k_unpack2<<<line_grid2(p, ncomp), 128, 0, c->stream>>>(p, A, 0, p.nn - p.ng, r_lo, r_hi, 1, lo >= 0, hi >= 0);
+      } else {
+        // a sub-domain thinner than two ghost widths: A(1:ng) and A(nn+1-ng:nn) overlap, so the two additions
+        // must not run side by side -- one after the other, in the reference's order (boundary.F90:976-989)
+        k_unpack2<<<line_grid2(p, ncomp), 128, 0, c->stream>>>(p, A, 0, p.nn - p.ng, r_lo, r_hi, 1, lo >= 0, 0);
+        k_unpack2<<<line_grid2(p, ncomp), 128, 0, c->stream>>>(p, A, 0, p.nn - p.ng, r_lo, r_hi, 1, 0, hi >= 0);
+        c->launches++;
+      }
       c->launches += 2;
     }
   }

@@ -451,6 +451,7 @@ class Simulation:
         if new_mins == self.cell_mins and new_maxs == self.cell_maxs:
             return False
         old_mins, old_maxs = self.cell_mins, self.cell_maxs
+        old_n_local = list(self.n_local)
         self.cell_mins, self.cell_maxs = new_mins, new_maxs
         self.cell_min = [new_mins[d][self.coords[d]] for d in range(nd)]
         self.cell_max = [new_maxs[d][self.coords[d]] for d in range(nd)]
@@ -477,7 +478,9 @@ class Simulation:
         # keeps none, so re-sliced planes are handed over as zeros (decks with initial fields at an open boundary
         # AND load balancing need the Fortran host)
         for b in range(2 * nd):
-            self.ctx.set_boundary_fields(b + 1, None)
+            others = [a for a in range(nd) if a != b // 2]
+            if any(old_n_local[a] != self.n_local[a] for a in others):     # (planes of unchanged extent stay on the device)
+                self.ctx.set_boundary_fields(b + 1, None)
         return True
 
     # -- moving window (housekeeping/window.F90) ---------------------------------

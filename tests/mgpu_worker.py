@@ -62,6 +62,8 @@ def build(abi, rank, nproc, nccl_id, device):
             s.bcs = pbc
     if SMALLBOX:
         kw["options"] = {"mig_capacity": 16}
+    if os.environ.get("MGPU_OPTS"):          # bisecting aid: library options "k=v,k=v"
+        kw.setdefault("options", {}).update(dict(kv.split("=", 1) for kv in os.environ["MGPU_OPTS"].split(",")))
     sim = Simulation(3, N, [0.0] * 3, [n * CELL for n in N], shape=SHAPE, species=sp, abi=abi, device=device,
                      rank=rank, nproc=nproc, nprocdir=tuple(nprocdir), nccl_id=nccl_id, **kw)
     rng = np.random.default_rng(11)
@@ -120,9 +122,32 @@ def main():
         dist.all_reduce(t)
         return t.cpu().numpy()
     for it in range(STEPS):
-        if BALANCE and it == 2:
+        if BALANCE and it == 2 and not os.environ.get("MGPU_NO_REBALANCE"):
             before = [sim.ctx.particle_count(i) for i in range(2)]
+
+            def snapshot():
+                """global interior fields (assembled on rank 0) and the particle set"""
+                ng_ = sim.ctx.ng
+                f_ = sim.ctx.download_fields()
+                loc = {k: v[ng_:-ng_, ng_:-ng_, ng_:-ng_].copy() for k, v in f_.items()}
+                pp = [sim.ctx.download_particles(i) for i in range(2)]
+                got = [None] * world
+                dist.all_gather_object(got, (list(sim.cell_min), list(sim.cell_max), loc, pp))
+                full = {k: np.zeros((N[2], N[1], N[0])) for k in loc}
+                for (cmin, cmax, loc_r, _) in got:
+                    sl = tuple(slice(cmin[d] - 1, cmax[d]) for d in (2, 1, 0))
+                    for k in loc_r:
+                        full[k][sl] = loc_r[k]
+                parts = [np.concatenate([g_[3][i] for g_ in got]) for i in range(2)]
+                parts = [P_[np.argsort(P_[:, 6])] for P_ in parts]
+                return full, parts
+            snap0 = snapshot()
             changed = sim.balance_workload(allreduce)
+            snap1 = snapshot()
+            for k in snap0[0]:
+                assert np.array_equal(snap0[0][k], snap1[0][k]), "re-slicing changed the interior of " + k
+            for i in range(2):
+                assert np.array_equal(snap0[1][i], snap1[1][i]), "re-slicing changed the particles of species %d" % i
             after = [sim.ctx.particle_count(i) for i in range(2)]
             tot = allreduce(np.array([sum(before), sum(after), max(sum(after), 0)], dtype=np.int64))
             mx = torch.tensor([sum(before), sum(after)], device="cuda")
