@@ -51,6 +51,7 @@ SIGNATURES = {
     "bfield_final_bcs": (i32, [c_ctx_p]),
     "energy": (i32, [c_ctx_p, pf64, pf64]),
     "charge_residual": (i32, [c_ctx_p, pf64, pf64]),
+    "charge_residual_static": (i32, [c_ctx_p, pf64, pf64]),
     "calc_derived": (i32, [c_ctx_p, i32, i32, i32, pf64]),
     "set_probe": (i32, [c_ctx_p, i32, i32, pf64, pf64, f64, f64]),
     "download_probe": (i32, [c_ctx_p, i32, i32, C.c_int64, pf64, i32, pi64, i32]),

@@ -314,6 +314,12 @@ class PicContext:
         self._ck(self.abi.charge_residual(self._ctx, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def charge_residual_static(self):
+        """charge_residual on the library's static device scratch: no allocation (operators' addition)"""
+        a, b = C.c_double(), C.c_double()
+        self._ck(self.abi.charge_residual_static(self._ctx, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     # -- load balancing (housekeeping/balance.F90) ---------------------------------
     def get_load(self, grid_min_global, n_global):
         """this rank's load_x, load_y, load_z of part_load_func (before the ALLREDUCE)"""

@@ -569,6 +569,13 @@ int32_t eb200_charge_residual(eb200_ctx* c, double* max_res, double* max_rho) {
   return charge_residual(c, max_res, max_rho, false);
 }
 
+// no counterpart in the reference (see include/epoch_b200.h)
+int32_t eb200_charge_residual_static(eb200_ctx* c, double* max_res, double* max_rho) {
+  CHECK_CTX(c); NEED_GRID(c); NEED_DT(c);
+  if (bc_mixed(c)) return fail(c, EB200_E_UNSUPPORTED, "charge_residual with mixed per-species particle boundaries");
+  return charge_residual_static(c, max_res, max_rho);
+}
+
 int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
   CHECK_CTX(c);
   if (!key || !value) return fail(c, EB200_E_ARG, "null");

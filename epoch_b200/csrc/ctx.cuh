@@ -303,5 +303,7 @@ int32_t settle_particles(eb200_ctx* c);                // ... for every species
 // reduce.cu
 int32_t energy(eb200_ctx* c, double* fe, double* per_species);
 int32_t charge_residual(eb200_ctx* c, double* max_res, double* max_rho, bool capture);
+int32_t charge_residual_static(eb200_ctx* c, double* max_res, double* max_rho);   // no allocation: file-scope device scratch
+long long charge_residual_static_max();
 
 }  // namespace eb

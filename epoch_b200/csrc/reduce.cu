@@ -188,4 +188,81 @@ int32_t charge_residual(eb200_ctx* c, double* max_res, double* max_rho, bool cap
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// charge_residual without any allocation (eb200_charge_residual_static; no counterpart in the
+// reference, added for callers that may not call cudaMalloc:
+// CUDA graph capture, tight serving loops).  The rho scratch of charge_residual -- one double per
+// grid point incl. ghosts, cudaMalloc'ed lazily there -- is this file-scope device array instead:
+// STATIC_RHO_MAX doubles = 16 MiB, held by every GPU that loads the library until exit.
+// All calls, from every context on a device, share the array; it keeps the last call's contents, so
+// it is cleared at the start of every call, and calls that overlap on the GPU (two contexts = two
+// streams) race.  In host code the array's NAME is a host-side stand-in, not a device address: the
+// address is fetched once per device, with that device current, by cudaGetSymbolAddress.
+// ---------------------------------------------------------------------------------------------
+constexpr long long STATIC_RHO_MAX = 1LL << 21;              // grid points incl. ghosts (2 097 152: e.g. 118^3 cells, triangle)
+static __device__ __align__(256) double g_static_rho[STATIC_RHO_MAX];
+constexpr int STATIC_MAX_DEVICES = 64;
+static double* g_static_rho_addr[STATIC_MAX_DEVICES] = {nullptr};
+
+long long charge_residual_static_max() { return STATIC_RHO_MAX; }
+
+static int32_t static_rho_address(eb200_ctx* c, double** out) {
+  int dev = -1;
+  EB_CUDA(c, cudaGetDevice(&dev));                            // (CHECK_CTX has made the context's device current)
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES) return fail(c, EB200_E_UNSUPPORTED, "charge_residual_static: device ordinal beyond 63");
+  if (!g_static_rho_addr[dev]) {
+    double* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_static_rho);
+    if (e != cudaSuccess || !ptr) {
+      cudaGetLastError();
+      return fail(c, EB200_E_CUDA, std::string("cudaGetSymbolAddress(g_static_rho): ") + cudaGetErrorString(e));
+    }
+    g_static_rho_addr[dev] = ptr;
+  }
+  *out = g_static_rho_addr[dev];
+  return 0;
+}
+
+// the body of charge_residual (mode 0 / 2: plain, or minus the captured reference) on the static scratch;
+// calls no cudaMalloc / cudaFree: d_red, h_red exist since create, the single-rank ghost sums are kernels only
+int32_t charge_residual_static(eb200_ctx* c, double* max_res, double* max_rho) {
+  const GridP& g = c->g;
+  if (g.total > STATIC_RHO_MAX)
+    return fail(c, EB200_E_ARG, "charge_residual_static: grid of " + std::to_string(g.total) + " points (ghosts included) exceeds the static scratch of " +
+                                std::to_string(STATIC_RHO_MAX) + " points; use charge_residual");
+  if (c->nproc > 1)
+    return fail(c, EB200_E_UNSUPPORTED, "charge_residual_static: single-rank contexts only (the multi-rank ghost sum sizes its halo buffers on demand)");
+  EB_TRY(settle_particles(c));          // (a pending deferred permute is finished by copy kernels inside the particle arrays: no allocation)
+  double* rho = nullptr;
+  EB_TRY(static_rho_address(c, &rho));
+  EB_CUDA(c, cudaMemsetAsync(rho, 0, (size_t)g.total * sizeof(double), c->stream));     // the array keeps the last call's contents
+  double idvol = 1.0;
+  for (int d = 0; d < c->ndims; ++d) idvol /= g.d[d];
+  for (SpeciesD& sp : c->species) {
+    if (!sp.defined || sp.n == 0) continue;
+    PushP p;
+    p.n = sp.n;
+    for (int d = 0; d < 3; ++d) { p.idx[d] = 1.0 / g.d[d]; p.gml[d] = g.gml[d]; }
+    p.dtco2 = C0 * (c->dt / 2.0);
+    p.ipart_mc = 1.0 / (C0 * sp.mass);
+    const unsigned grid = (unsigned)((sp.n + 127) / 128);
+#define L(ND, SH)                                                                                  \
+    if (c->ndims == ND && c->shape == SH)                                                          \
+      k_rho<ND, SH><<<grid, 128, 0, c->stream>>>(g, p, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], \
+                                                  sp.a[5], sp.a[6], sp.charge * idvol, rho);
+    L(1, 0) L(1, 1) L(1, 2) L(2, 0) L(2, 1) L(2, 2) L(3, 0) L(3, 1) L(3, 2)
+#undef L
+    c->launches++;
+  }
+  EB_TRY(summation_bcs(c, rho, -1));
+  EB_CUDA(c, cudaMemsetAsync(c->d_red, 0, 2 * sizeof(double), c->stream));
+  k_residual<<<148 * 4, 256, 0, c->stream>>>(g, c->f, rho, c->res_ref, c->res_ref ? 2 : 0, c->d_red);
+  c->launches++;
+  EB_CUDA(c, cudaMemcpyAsync(c->h_red, c->d_red, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (max_res) *max_res = c->h_red[0];
+  if (max_rho) *max_rho = c->h_red[1];
+  return 0;
+}
+
 }  // namespace eb

@@ -233,6 +233,15 @@ int32_t EB200_NAME(energy)(EB200_CTX*, double* field_energy,
  * with the normalised weights of calc_charge_density (calc_df.F90:439-519). */
 int32_t EB200_NAME(charge_residual)(EB200_CTX*, double* max_abs_residual,
                                     double* max_abs_rho_over_eps0);
+/* charge_residual_static: NO COUNTERPART IN THE REFERENCE -- added for callers
+ * that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs
+ * (the context's fields and particles) and outputs as charge_residual, but the charge-density scratch is a
+ * file-scope static __device__ array of the library instead of a lazily cudaMalloc'ed one, and the call allocates
+ * and frees nothing.  Limits: grids of at most 2 097 152 points including ghost cells (16 MiB, held by every GPU
+ * that loads the library until exit; e.g. 118^3 cells with the triangle shape) -- larger grids are rejected with
+ * EB200_E_ARG; single-rank contexts only (EB200_E_UNSUPPORTED otherwise).  Every call on a device shares the
+ * array: it is cleared at the start of each call, and calls that overlap on the GPU (two contexts) race. */
+int32_t EB200_NAME(charge_residual_static)(EB200_CTX*, double* max_abs_residual, double* max_abs_rho_over_eps0);
 /* Load balancing (housekeeping/balance.F90).  The decision -- balance_workload :107-319 and
  * calculate_breaks :2526-2669, a few hundred integers -- stays on the host; the device supplies
  * its input and carries the result out.

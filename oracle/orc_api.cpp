@@ -331,6 +331,9 @@ int32_t orc_charge_residual(orc_ctx* c, double* max_res, double* max_rho) {
   charge_residual(c->s, max_res, max_rho, false);
   return 0;
 }
+// (the CUDA library's no-allocation variant has nothing to vary on the CPU: the same routine under the second name,
+//  so that one binding table serves both libraries)
+int32_t orc_charge_residual_static(orc_ctx* c, double* max_res, double* max_rho) { return orc_charge_residual(c, max_res, max_rho); }
 // part_load_func (balance.F90:2468-2495) for this (single) rank
 int32_t orc_get_load(orc_ctx* c, const double grid_min_global[3], int64_t* load_x, int64_t* load_y, int64_t* load_z) {
   if (!c || !c->s.grid_set) return EB200_E_STATE;
