@@ -71,7 +71,8 @@ int32_t eb200_create(eb200_ctx** out, int32_t ndims, int32_t shape, int32_t devi
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0)
     return fail(nullptr, EB200_E_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e) + " (this library has no CPU path)");
-  if (device < 0 || device >= ndev) return fail(nullptr, EB200_E_ARG, "bad device ordinal");
+  if (device < 0) device = (-(device + 1)) % ndev;      // -(local_rank + 1): the library wraps the node-local rank onto the devices present
+  if (device >= ndev) return fail(nullptr, EB200_E_ARG, "bad device ordinal");
   eb200_ctx* c = new (std::nothrow) eb200_ctx();
   if (!c) return fail(nullptr, EB200_E_NOMEM, "host allocation failed");
   c->ndims = ndims; c->shape = shape; c->device = device; c->rank = rank; c->nproc = nproc < 1 ? 1 : nproc;

@@ -35,6 +35,12 @@ namespace {
 #ifndef EB_MINB_A
 #define EB_MINB_A 4
 #endif
+#ifndef EB_C0_SMEM
+#define EB_C0_SMEM 1
+#endif
+#ifndef EB_SUB
+#define EB_SUB 2                 // a deposit CTA owns 1/EB_SUB of a tile, split along the slowest tile axis
+#endif
 template <int ND, int SHAPE>
 struct TL {
   static constexpr int NW = Sh<SHAPE>::NW, SFM = Sh<SHAPE>::SFMIN;
@@ -59,7 +65,7 @@ struct TL {
   static constexpr int JX = TX + NW + 1, JY = ND >= 2 ? TY + NW + 1 : 1, JZ = ND >= 3 ? TZ + NW + 1 : 1;
   static constexpr int JN = JX * JY * JZ;
   // ... of a deposit CTA's sub-tile (half a tile along the slowest axis)
-  static constexpr int JNS = ND == 3 ? JX * JY * (TZ / 2 + NW + 1) : JX * (TY / 2 + NW + 1);
+  static constexpr int JNS = ND == 3 ? JX * JY * (TZ / EB_SUB + NW + 1) : JX * (TY / EB_SUB + NW + 1);
   // register accumulators per component.  3D: the last box slot along the running-sum axis is
   // left out -- the sum has returned to zero there (rounding residue) unless the particle moved
   // up a cell, and then the slot is deposited by a work item (mover_item3, m == A, dcell = +1)
@@ -368,9 +374,9 @@ __device__ __forceinline__ void load_particle(const PArr& a, long long ip, doubl
 
 // phase 1 for one particle: particles.F90:219-452 (gather stage, Boris, drift, store,
 // extra half drift); leaves the deposit inputs in the record arrays
-template <int ND, int SHAPE, bool GATHER, bool PROBE = false>
+template <int ND, int SHAPE, bool GATHER, bool PROBE = false, class C0P = const int*>
 __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos[3], mom[3], weight */, const PArr& a /* output */,
-                                         long long ip, const int* c0,
+                                         long long ip, C0P c0,
                                          const double* __restrict__ sF, unsigned long long* counters,
                                          double* rec /* NREC doubles */, int& rec_pack, const GridP* g = nullptr,
                                          const KeySink* ks = nullptr, const ProbeSet* pr = nullptr) {
@@ -399,6 +405,9 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
     if ((unsigned)l1[d] >= (unsigned)td) { bad = true; l1[d] = l1[d] < 0 ? 0 : td - 1; l2[d] = l1[d]; }
   }
   if (bad) atomicAdd(counters + 8, 1ULL);   // key and push disagree on the cell: must never happen
+  // tile-local cell of the record; from here on the cell at t + dt/2 is carried by `lc` alone (the cell shift at the
+  // end is taken relative to the tile origin too), which frees the three cell1 registers for the gather
+  const int lc = (l1[2] * T::TY + l1[1]) * T::TX + l1[0];
   // region index of weight slot i: g-type l1 + 1 + i, h-type l2 + 1 + i
   const int gx = l1[0] + 1, gy = l1[1] + 1, gz = l1[2] + 1, hx = l2[0] + 1, hy = l2[1] + 1, hz = l2[2] + 1;
   double ex_part, ey_part, ez_part, bx_part, by_part, bz_part;
@@ -516,7 +525,8 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
     px[d] = px[d] + delta[d];
     double f3;
     const int cell3 = cell_round(cell_coord<SHAPE>(px[d], p.idx[d]), f3);
-    int dc = cell3 - cell1[d];
+    const int ld = d == 0 ? lc % T::TX : (d == 1 ? (lc / T::TX) % T::TY : lc / (T::TX * T::TY));
+    int dc = (cell3 - c0[d]) - ld;
     dc = dc < -1 ? -1 : (dc > 1 ? 1 : dc);          // |dcell| <= 1 by the CFL condition (particles.F90:506-507)
     pack |= (dc + 1) << (2 * d);
     rec[d] = f1[d];
@@ -524,7 +534,6 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
   }
   rec[2 * ND] = part_weight;
   if (ND == 2) rec[2 * ND + 1] = part_vz;
-  const int lc = (l1[2] * T::TY + l1[1]) * T::TX + l1[0];
   rec_pack = pack | (lc << 8);
   return true;
 }
@@ -752,6 +761,14 @@ __global__ void __launch_bounds__(NTA, SHAPE == SHAPE_BSPLINE3 ? 2 : EB_MINB_A) 
     c0[d] = d < ND ? (1 - KM) + tc[d] * tile_dim(ND, d) : 1;
     org[d] = d < ND ? c0[d] + SFM - 1 : 1;
   }
+#if EB_C0_SMEM
+  // the tile origin lives in shared memory and is re-read per particle: as three loop-invariant registers it pushed
+  // the loop over the 128-register budget and ptxas answered with a local-memory spill whose reload (LDL, long
+  // scoreboard) sat at the top of every iteration -- 14 % of the kernel's stall samples in the round-1 capture
+  __shared__ int s_c0[4];
+  if (tid == 0) { s_c0[0] = c0[0]; s_c0[1] = c0[1]; s_c0[2] = c0[2]; }
+  // (both staging branches below pass a __syncthreads before the particle loop)
+#endif
   const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&mbar);
   if (use_tma) {
     // E,B of the tile + gather halo: ONE bulk tensor copy (TMA) of the box [FZ][6 components][FY][FX] out of the
@@ -834,7 +851,11 @@ __global__ void __launch_bounds__(NTA, SHAPE == SHAPE_BSPLINE3 ? 2 : EB_MINB_A) 
     if (act) {
       int pack;
       rec[6] = 0.0;
+#if EB_C0_SMEM
+      push_one<ND, SHAPE, GATHER, PROBE, const volatile int*>(p, in, o, (long long)q, s_c0, sF, counters, rec, pack, &g, &ks, pr);
+#else
       push_one<ND, SHAPE, GATHER, PROBE>(p, in, o, (long long)q, c0, sF, counters, rec, pack, &g, &ks, pr);
+#endif
       rec[7] = __longlong_as_double((long long)pack);
     }
     if (p.zero_current) continue;
@@ -873,7 +894,7 @@ __global__ void __launch_bounds__(NTA, SHAPE == SHAPE_BSPLINE3 ? 2 : EB_MINB_A) 
   }
 }
 
-constexpr int SUB = 2;           // a deposit CTA owns 1/SUB of a tile, split along the slowest tile axis
+constexpr int SUB = EB_SUB;      // a deposit CTA owns 1/SUB of a tile, split along the slowest tile axis
 
 // Lane balance of the deposit kernel (EB_BALANCE): a thread owns one cell and a warp runs as long as its fullest
 // cell, so the cells are dealt to the warps by particle count.  Any permutation of cells over threads keeps the

@@ -13,7 +13,28 @@
 ! wrote them.  A step with no dump / balance / window does no transfer at all.
 !
 ! This file cannot be compiled in the authoring image (no Fortran compiler); it is
-! written against the reference's module variables by name and is reviewed, not built.
+! written against the reference's module variables by name and is reviewed, not built
+! (UNVERIFIED: wherever a gfortran exists, `gfortran -cpp -DEPOCH_NDIMS=3 -fsyntax-only -I<epoch3d/obj>`
+! against the reference's module files is the first check to run).
+!
+! One source for epoch1d / epoch2d / epoch3d: compile with -DEPOCH_NDIMS=1|2|3 (default 3).  The C ABI
+! always takes three-element vectors; the macros below fill the axes a lower-dimensional code does not have.
+#ifndef EPOCH_NDIMS
+#define EPOCH_NDIMS 3
+#endif
+#if EPOCH_NDIMS == 1
+#define I3(a, b, c) [a, 1, 1]
+#define R3(a, b, c, fill) [a, fill, fill]
+#define GHOST_DIMS DIMENSION(1-ng:)
+#elif EPOCH_NDIMS == 2
+#define I3(a, b, c) [a, b, 1]
+#define R3(a, b, c, fill) [a, b, fill]
+#define GHOST_DIMS DIMENSION(1-ng:,1-ng:)
+#else
+#define I3(a, b, c) [a, b, c]
+#define R3(a, b, c, fill) [a, b, c]
+#define GHOST_DIMS DIMENSION(1-ng:,1-ng:,1-ng:)
+#endif
 MODULE epoch_b200_hooks
 
   USE, INTRINSIC :: ISO_C_BINDING
@@ -54,14 +75,31 @@ CONTAINS
   SUBROUTINE gpu_attach
     ! after mpi_initialise (mpi_routines.F90:393-593), setup_boundaries and set_dt
     CHARACTER(KIND=C_CHAR), TARGET :: id(128)
-    INTEGER(C_INT32_T) :: nprocdir(3), crd(3), ndev, ispecies, bcp(6)
-    INTEGER :: ierr
+    INTEGER(C_INT32_T) :: nprocdir(3), crd(3), ispecies, bcp(6)
+    INTEGER :: ierr, node_comm, local_rank
+    REAL(num) :: species_weight
     IF (rank == 0) CALL gpu_check(eb200_nccl_unique_id(id))
     CALL MPI_BCAST(id, 128, MPI_CHARACTER, 0, comm, ierr)
-    nprocdir = [nprocx, nprocy, nprocz]
-    crd = [x_coords, y_coords, z_coords]
-    ndev = 8                                         ! GPUs per node: one rank per GPU
-    CALL gpu_check(eb200_create(gpu, c_ndims, gpu_shape, MOD(rank, ndev), rank, nproc, nprocdir, crd, C_LOC(id)))
+    nprocdir = 1
+    crd = 0
+    nprocdir(1) = nprocx
+    crd(1) = x_coords
+#if EPOCH_NDIMS >= 2
+    nprocdir(2) = nprocy
+    crd(2) = y_coords
+#endif
+#if EPOCH_NDIMS >= 3
+    nprocdir(3) = nprocz
+    crd(3) = z_coords
+#endif
+    ! one rank per GPU: the device follows the rank's position among the ranks of ITS node, whatever the rank
+    ! layout and however many GPUs the node has.  device = -(local_rank + 1) asks the library for
+    ! MOD(local_rank, cudaGetDeviceCount) (include/epoch_b200.h, eb200_create)
+    CALL MPI_COMM_SPLIT_TYPE(comm, MPI_COMM_TYPE_SHARED, rank, MPI_INFO_NULL, node_comm, ierr)
+    CALL MPI_COMM_RANK(node_comm, local_rank, ierr)
+    CALL MPI_COMM_FREE(node_comm, ierr)
+    CALL gpu_check(eb200_create(gpu, c_ndims, gpu_shape, INT(-(local_rank + 1), C_INT32_T), rank, nproc, nprocdir, crd, &
+        C_LOC(id)))
     CALL gpu_set_grid
     CALL gpu_check(eb200_set_field_bcs(gpu, INT(bc_field, C_INT32_T)))
     IF (cpml_boundaries) CALL gpu_set_cpml
@@ -79,9 +117,15 @@ CONTAINS
     END IF
     CALL gpu_resend_lasers
     DO ispecies = 1, n_species
-      bcp = INT(species_list(ispecies)%bc_particle, C_INT32_T)
+      bcp = 0
+      bcp(1:2*c_ndims) = INT(species_list(ispecies)%bc_particle(1:2*c_ndims), C_INT32_T)
+#ifdef PER_SPECIES_WEIGHT
+      species_weight = species_list(ispecies)%weight
+#else
+      species_weight = 0.0_num        ! the weight travels with every particle (shared_data.F90:91-137)
+#endif
       CALL gpu_check(eb200_set_species(gpu, ispecies - 1, species_list(ispecies)%charge, &
-          species_list(ispecies)%mass, species_list(ispecies)%weight, &
+          species_list(ispecies)%mass, species_weight, &
           MERGE(1, 0, species_list(ispecies)%immobile), MERGE(1, 0, species_list(ispecies)%zero_current), &
           MERGE(1, 0, species_list(ispecies)%species_type == c_species_id_photon), bcp))
     END DO
@@ -90,11 +134,11 @@ CONTAINS
 
   SUBROUTINE gpu_set_grid
     ! call again after balance_workload / moving_window changed the local grid
-    CALL gpu_check(eb200_set_grid(gpu, [nx, ny, nz], [nx_global, ny_global, nz_global], &
-        [nx_global_min, ny_global_min, nz_global_min], [dx, dy, dz], &
-        [x_grid_min_local, y_grid_min_local, z_grid_min_local], &
-        [x_min_local, y_min_local, z_min_local], [x_max_local, y_max_local, z_max_local], &
-        [x_min, y_min, z_min], [x_max, y_max, z_max], cpml_thickness))
+    CALL gpu_check(eb200_set_grid(gpu, I3(nx, ny, nz), I3(nx_global, ny_global, nz_global), &
+        I3(nx_global_min, ny_global_min, nz_global_min), R3(dx, dy, dz, 1.0_num), &
+        R3(x_grid_min_local, y_grid_min_local, z_grid_min_local, 0.0_num), &
+        R3(x_min_local, y_min_local, z_min_local, 0.0_num), R3(x_max_local, y_max_local, z_max_local, 0.0_num), &
+        R3(x_min, y_min, z_min, 0.0_num), R3(x_max, y_max, z_max, 0.0_num), cpml_thickness))
   END SUBROUTINE gpu_set_grid
 
   SUBROUTINE gpu_set_cpml
@@ -106,16 +150,20 @@ CONTAINS
     IF (add_laser(c_bd_x_max)) lmax = cpml_x_max_laser_idx
     CALL gpu_check(eb200_set_cpml(gpu, 0, cpml_kappa_ex, cpml_kappa_bx, cpml_sigma_ex, cpml_sigma_bx, &
         cpml_a_ex, cpml_a_bx, cpml_x_min_start, cpml_x_min_end, cpml_x_max_start, cpml_x_max_end, lmin, lmax))
+#if EPOCH_NDIMS >= 2
     lmin = -1; lmax = -1
     IF (add_laser(c_bd_y_min)) lmin = cpml_y_min_laser_idx
     IF (add_laser(c_bd_y_max)) lmax = cpml_y_max_laser_idx
     CALL gpu_check(eb200_set_cpml(gpu, 1, cpml_kappa_ey, cpml_kappa_by, cpml_sigma_ey, cpml_sigma_by, &
         cpml_a_ey, cpml_a_by, cpml_y_min_start, cpml_y_min_end, cpml_y_max_start, cpml_y_max_end, lmin, lmax))
+#endif
+#if EPOCH_NDIMS >= 3
     lmin = -1; lmax = -1
     IF (add_laser(c_bd_z_min)) lmin = cpml_z_min_laser_idx
     IF (add_laser(c_bd_z_max)) lmax = cpml_z_max_laser_idx
     CALL gpu_check(eb200_set_cpml(gpu, 2, cpml_kappa_ez, cpml_kappa_bz, cpml_sigma_ez, cpml_sigma_bz, &
         cpml_a_ez, cpml_a_bz, cpml_z_min_start, cpml_z_min_end, cpml_z_max_start, cpml_z_max_end, lmin, lmax))
+#endif
   END SUBROUTINE gpu_set_cpml
 
   SUBROUTINE gpu_sync_to_device
@@ -228,14 +276,30 @@ CONTAINS
   ! ---- load balancing (housekeeping/balance.F90) ----
   ! part_load_func (:2468): the device counts this rank's particles per global cell; get_load's
   ! MPI_ALLREDUCE and push_per_field weighting (:2446-2460) stay as they are.
+#if EPOCH_NDIMS == 3
   SUBROUTINE part_load_func(load_x, load_y, load_z)
     INTEGER(i8), DIMENSION(1-ng:), INTENT(OUT) :: load_x, load_y, load_z
     CALL gpu_check(eb200_get_load(gpu, [x_grid_min, y_grid_min, z_grid_min], load_x, load_y, load_z))
   END SUBROUTINE part_load_func
+#elif EPOCH_NDIMS == 2
+  SUBROUTINE part_load_func(load_x, load_y)       ! epoch2d/src/housekeeping/balance.F90: two histograms
+    INTEGER(i8), DIMENSION(1-ng:), INTENT(OUT) :: load_x, load_y
+    INTEGER(i8), TARGET :: unused(1)
+    CALL gpu_check(eb200_get_load(gpu, [x_grid_min, y_grid_min, 0.0_num], load_x, load_y, unused))
+  END SUBROUTINE part_load_func
+#else
+  SUBROUTINE part_load_func(load_x)               ! epoch1d: one histogram
+    INTEGER(i8), DIMENSION(1-ng:), INTENT(OUT) :: load_x
+    INTEGER(i8), TARGET :: unused(1)
+    CALL gpu_check(eb200_get_load(gpu, [x_grid_min, 0.0_num, 0.0_num], load_x, unused, unused))
+  END SUBROUTINE part_load_func
+#endif
 
   ! redistribute_domain (:411-472): called by balance_workload after calculate_breaks filled
   ! new_cell_*_min/max and after the new local grid scalars were set (setup_grid_x etc. with the
   ! new nx_global_min); fields, psi arrays and particles move on the device, rank to rank.
+  ! (3D argument list; the 2D / 1D callers pass 0 / 1 for the axes they do not have, as I3 / R3 do above)
+#if EPOCH_NDIMS == 3
   SUBROUTINE gpu_redistribute_domain(x_grid_min_local_new, y_grid_min_local_new, z_grid_min_local_new, &
       mins_new, maxs_new)
     REAL(num), INTENT(IN) :: x_grid_min_local_new, y_grid_min_local_new, z_grid_min_local_new
@@ -252,13 +316,14 @@ CONTAINS
     CALL gpu_resend_lasers
     host_stale = .TRUE.
   END SUBROUTINE gpu_redistribute_domain
+#endif
 
   ! ---- derived grid variables for output_routines (io/calc_df.F90) ----
   ! e.g. calc_number_density(array, ispecies) becomes
   !   CALL gpu_calc_derived(EB200_DF_NUMBER_DENSITY, array, ispecies)
   SUBROUTINE gpu_calc_derived(kind, data_array, current_species, direction)
     INTEGER, INTENT(IN) :: kind, current_species
-    REAL(num), DIMENSION(1-ng:,1-ng:,1-ng:), INTENT(OUT) :: data_array
+    REAL(num), GHOST_DIMS, INTENT(OUT) :: data_array
     INTEGER, INTENT(IN), OPTIONAL :: direction
     INTEGER :: dir
     dir = 0

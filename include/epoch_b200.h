@@ -77,7 +77,9 @@ enum {
  * 393-593) and setup_communicator (:274-389).  nprocdir/coords describe the
  * Cartesian process grid (x,y,z); nccl_unique_id is 128 bytes obtained from
  * eb200_nccl_unique_id() on rank 0 and broadcast by the host (MPI_BCAST); it may
- * be NULL when nproc == 1. */
+ * be NULL when nproc == 1.  device_ordinal >= 0 names the CUDA device; a negative value -(r + 1) hands over the
+ * rank's position r among the ranks of its node (MPI_COMM_TYPE_SHARED) and the library takes device
+ * r mod cudaGetDeviceCount, so the host needs no knowledge of the node's GPU count. */
 int32_t EB200_NAME(create)(EB200_CTX** out, int32_t ndims, int32_t shape,
                            int32_t device_ordinal, int32_t rank, int32_t nproc,
                            const int32_t nprocdir[3], const int32_t coords[3],
