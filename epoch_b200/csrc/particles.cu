@@ -230,38 +230,64 @@ __global__ void k_permute(const double* __restrict__ src, double* __restrict__ d
 // arrival, ...) is copied to the species' side buffer instead -- src = n + index there; far_count counts
 // them (beyond far_cap they stay in place and the host falls back to a permute).
 struct Attr7 { const double* a[7]; };
-__global__ void k_src(const uint32_t* __restrict__ key, long long n, const uint32_t* __restrict__ start,
+// A warp takes SRC_U consecutive groups of 32 slots and keeps their memory round trips in flight together (the key
+// loads, then one cursor atomic per (group, key) and the start[] loads side by side, then the stores): with one
+// group per warp the three dependent round trips left the kernel latency bound at 1.8 TB/s of DRAM traffic
+// (ncu, 512^3: 20.4 GB in 11.2 ms, profiles/r02_dram_512_summary.txt).
+#ifndef EB_SRC_U
+#define EB_SRC_U 4
+#endif
+constexpr int SRC_U = EB_SRC_U;
+__global__ void __launch_bounds__(256) k_src(const uint32_t* __restrict__ key, long long n, const uint32_t* __restrict__ start,
                       uint32_t* cursor, uint32_t* src, uint32_t nbucket, unsigned long long* far_count,
                       Attr7 at, double* __restrict__ far, long long far_cap, long long limit) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool act = i < n;
-  const unsigned am = __ballot_sync(0xffffffffu, act);
-  if (!act) return;
-  uint32_t k = key[i];
-  const bool live = k != KEY_INVALID;
-  if (!live) k = nbucket - 1;
-  const unsigned peers = __match_any_sync(am, k);
   const int lane = threadIdx.x & 31;
-  const int leader = __ffs(peers) - 1;
-  uint32_t base = 0;
-  if (lane == leader) base = atomicAdd(cursor + k, (uint32_t)__popc(peers));
-  base = __shfl_sync(peers, base, leader);
-  const uint32_t d = start[k] + base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
-  if (live) {
-    uint32_t s = (uint32_t)i;
-    const long long df = (long long)d - i;
-    if (df > limit || -df > limit) {
-      // (an unordered load displaces everything: once the buffer is full nobody queues at the counter any more;
-      //  a count >= far_cap tells the host to permute at once)
-      const unsigned long long slot = *far_count < (unsigned long long)far_cap ? atomicAdd(far_count, 1ULL) : (unsigned long long)far_cap;
-      if ((long long)slot < far_cap) {
+  const long long wbase = (((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * (32LL * SRC_U);
+  if (wbase >= n) return;
+  uint32_t k[SRC_U], st[SRC_U], base[SRC_U];
+  unsigned peers[SRC_U];
+  bool live[SRC_U];
 #pragma unroll
-        for (int a = 0; a < 7; ++a)
-          if (at.a[a]) far[(size_t)a * far_cap + slot] = at.a[a][i];
-        s = (uint32_t)(n + (long long)slot);
-      }
+  for (int u = 0; u < SRC_U; ++u) {
+    const long long i = wbase + u * 32 + lane;
+    k[u] = i < n ? key[i] : KEY_INVALID;
+  }
+#pragma unroll
+  for (int u = 0; u < SRC_U; ++u) {
+    const long long i = wbase + u * 32 + lane;
+    const bool act = i < n;
+    const unsigned am = __ballot_sync(0xffffffffu, act);
+    live[u] = act && k[u] != KEY_INVALID;
+    if (!live[u]) k[u] = nbucket - 1;
+    peers[u] = 0; base[u] = 0; st[u] = 0;
+    if (act) {
+      peers[u] = __match_any_sync(am, k[u]);
+      if (lane == __ffs(peers[u]) - 1) base[u] = atomicAdd(cursor + k[u], (uint32_t)__popc(peers[u]));
+      st[u] = start[k[u]];
     }
-    src[d] = s;
+  }
+#pragma unroll
+  for (int u = 0; u < SRC_U; ++u) {
+    const long long i = wbase + u * 32 + lane;
+    if (i >= n) continue;
+    const uint32_t b = __shfl_sync(peers[u], base[u], __ffs(peers[u]) - 1);
+    const uint32_t d = st[u] + b + (uint32_t)__popc(peers[u] & ((1u << lane) - 1u));
+    if (live[u]) {
+      uint32_t s = (uint32_t)i;
+      const long long df = (long long)d - i;
+      if (df > limit || -df > limit) {
+        // (an unordered load displaces everything: once the buffer is full nobody queues at the counter any more;
+        //  a count >= far_cap tells the host to permute at once)
+        const unsigned long long slot = *far_count < (unsigned long long)far_cap ? atomicAdd(far_count, 1ULL) : (unsigned long long)far_cap;
+        if ((long long)slot < far_cap) {
+#pragma unroll
+          for (int a = 0; a < 7; ++a)
+            if (at.a[a]) far[(size_t)a * far_cap + slot] = at.a[a][i];
+          s = (uint32_t)(n + (long long)slot);
+        }
+      }
+      src[d] = s;
+    }
   }
 }
 // dst[i] = from[src[i]] for i in [i0, i1); src >= n_main points into the side buffer
@@ -490,7 +516,7 @@ int32_t sort_species(eb200_ctx* c, SpeciesD& sp, long long n_slots, bool keys_re
     const long long limit = deferrable ? W / 4 : (1LL << 62);
     sp.disp_fwd = sp.disp_bwd = deferrable ? limit : W;
     EB_CUDA(c, cudaMemsetAsync(c->d_counters + 12, 0, sizeof(unsigned long long), c->stream));
-    k_src<<<gp, B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket, c->d_counters + 12,
+    k_src<<<(unsigned)((n_slots + (long long)B * SRC_U - 1) / ((long long)B * SRC_U)), B, 0, c->stream>>>(sp.key, n_slots, sp.cell_start, c->cell_count, sp.dest, nbucket, c->d_counters + 12,
                                    at, sp.far, sp.far_cap, limit);
     EB_CUDA(c, cudaMemcpyAsync(c->h_counters + 12, c->d_counters + 12, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     if (c->deterministic) {

@@ -82,6 +82,7 @@ int32_t set_window_planes(eb200_ctx* c, const double* const planes[6]) {
 }
 
 int32_t shift_window(eb200_ctx* c, double grid_min_local, double min_local, double max_local, double gmin, double gmax) {
+  ScopedPhase ph(c, "window");
   GridP& g = c->g;
   // setup_grid_x
   g.gml[0] = grid_min_local; g.min_local[0] = min_local; g.max_local[0] = max_local;
