@@ -53,6 +53,7 @@ SIGNATURES = {
     "charge_residual": (i32, [c_ctx_p, pf64, pf64]),
     "charge_residual_static": (i32, [c_ctx_p, pf64, pf64]),
     "calc_derived": (i32, [c_ctx_p, i32, i32, i32, pf64]),
+    "set_thermal_boundary": (i32, [c_ctx_p, i32, i32, pf64, i64]),
     "set_probe": (i32, [c_ctx_p, i32, i32, pf64, pf64, f64, f64]),
     "download_probe": (i32, [c_ctx_p, i32, i32, C.c_int64, pf64, i32, pi64, i32]),
     "dist_fn": (i32, [c_ctx_p, i32, i32, pi32, pf64, pi32, pf64, pf64, pi32, pf64]),

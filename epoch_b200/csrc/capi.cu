@@ -43,6 +43,7 @@ static void free_species(SpeciesD& sp) {
   sp.h_mig = sp.d_mig = nullptr;
   if (sp.far) cudaFree(sp.far);
   sp.far = nullptr; sp.far_cap = 0;
+  for (int b = 0; b < 6; ++b) { if (sp.ext_temp[b]) cudaFree(sp.ext_temp[b]); sp.ext_temp[b] = nullptr; }
   if (sp.dest) cudaFree(sp.dest);
   if (sp.d_tile_start) cudaFree(sp.d_tile_start);
   if (sp.h_tile_start) cudaFreeHost(sp.h_tile_start);
@@ -154,6 +155,8 @@ int32_t eb200_destroy(eb200_ctx* c) {
   if (c->h_counters) cudaFreeHost(c->h_counters);
   if (c->h_red) cudaFreeHost(c->h_red);
   for (auto& kv : c->timers) for (auto& ev : kv.second.ev) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
+  for (int k = 0; k < 2; ++k) { if (c->ev_push[k]) cudaEventDestroy(c->ev_push[k]); if (c->ev_dep[k]) cudaEventDestroy(c->ev_dep[k]); }
+  if (c->stream2) cudaStreamDestroy(c->stream2);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
   return 0;
@@ -334,9 +337,10 @@ int32_t eb200_set_species(eb200_ctx* c, int32_t isp, double charge, double mass,
     // setup_particle_boundary, boundary.F90:98-140
     if (bc == EB200_BC_OTHER || bc == EB200_BC_CONDUCT) bc = EB200_BC_REFLECT;
     if (bc == EB200_BC_SIMPLE_LASER || bc == EB200_BC_SIMPLE_OUTFLOW || bc == EB200_BC_CPML_LASER || bc == EB200_BC_CPML_OUTFLOW) bc = EB200_BC_OPEN;
-    if (bc == EB200_BC_THERMAL || bc == EB200_BC_HEAT_BATH)
-      return fail(c, EB200_E_UNSUPPORTED, "thermal / heat-bath particle boundaries need the host RNG and stay on the host");
-    if (bc != EB200_BC_PERIODIC && bc != EB200_BC_REFLECT && bc != EB200_BC_OPEN) return fail(c, EB200_E_ARG, "unrecognised particle boundary code");
+    // heat_bath = open boundary + a boundary injector (setup_domain_dependent_boundaries, boundary.F90:75-93); injectors stay on the host
+    if (bc == EB200_BC_HEAT_BATH) bc = EB200_BC_OPEN;
+    if (bc != EB200_BC_PERIODIC && bc != EB200_BC_REFLECT && bc != EB200_BC_OPEN && bc != EB200_BC_THERMAL)
+      return fail(c, EB200_E_ARG, "unrecognised particle boundary code");
     bcs[i] = bc;
   }
   for (int d = 0; d < c->ndims; ++d)
@@ -450,6 +454,21 @@ int32_t eb200_calc_derived(eb200_ctx* c, int32_t kind, int32_t ispecies, int32_t
   return calc_derived(c, kind, ispecies, direction, out);
 }
 
+int32_t eb200_set_thermal_boundary(eb200_ctx* c, int32_t isp, int32_t boundary, const double* ext_temp, int64_t seed) {
+  CHECK_CTX(c); NEED_GRID(c);
+  if (isp < 0 || (size_t)isp >= c->species.size() || !c->species[isp].defined) return fail(c, EB200_E_ARG, "species not set");
+  if (boundary < 1 || boundary > 2 * c->ndims || !ext_temp) return fail(c, EB200_E_ARG, "set_thermal_boundary: bad boundary / null table");
+  SpeciesD& sp = c->species[isp];
+  const int d = (boundary - 1) / 2;
+  size_t plane = 1;
+  for (int a = 0; a < c->ndims; ++a) if (a != d) plane *= (size_t)(c->g.n[a] + 2 * c->ng);
+  EB_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (sp.ext_temp[boundary - 1]) { cudaFree(sp.ext_temp[boundary - 1]); sp.ext_temp[boundary - 1] = nullptr; }
+  EB_CUDA(c, cudaMalloc(&sp.ext_temp[boundary - 1], 3 * plane * sizeof(double)));
+  EB_CUDA(c, cudaMemcpy(sp.ext_temp[boundary - 1], ext_temp, 3 * plane * sizeof(double), cudaMemcpyHostToDevice));
+  sp.thermal_seed = (unsigned long long)seed;
+  return 0;
+}
 int32_t eb200_set_probe(eb200_ctx* c, int32_t isp, int32_t iprobe, const double* point, const double* normal, double ek_min,
                         double ek_max) {
   CHECK_CTX(c);
@@ -603,6 +622,7 @@ int32_t eb200_set_option(eb200_ctx* c, const char* key, const char* value) {
     if (isp < 0 || (size_t)isp >= c->species.size() || !c->species[isp].defined || n < 0) return fail(c, EB200_E_ARG, "reserve: bad species or count");
     return species_reserve(c, c->species[isp], n, true);
   }
+  if (k == "push_overlap") { c->push_overlap = atoi(value) != 0; return 0; }
   if (k == "deposit_scratch") { c->rec_scratch_max = atoll(value) < 1024 ? 1024 : atoll(value); return 0; }
   if (k == "probe_capacity") { c->probe_capacity = std::max<long long>(atoll(value), 16); return 0; }
   if (k == "host_threads") { c->host_threads = atoi(value); return 0; }

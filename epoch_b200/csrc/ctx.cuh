@@ -102,6 +102,9 @@ struct SpeciesD {
   unsigned long long* h_mig = nullptr;
   unsigned long long* d_mig = nullptr;
   bool mig_pending[3] = {false, false, false};
+  // thermal particle boundaries: ext_temp_<face> on the device (set_thermal_boundary), generator key and call counter
+  double* ext_temp[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  unsigned long long thermal_seed = 0, thermal_calls = 0;
   bool sorted = false;      // keys/cell_start valid for the current positions ...
   bool was_ordered = false; // the slots are in (an older) cell order: a re-sort moves particles by about a tile
   double sort_dt = 0.0;     // ... and for this time step (the key is the cell after the half drift)
@@ -203,6 +206,11 @@ struct eb200_ctx {
   double* det_tiles = nullptr;                // deterministic deposit: one J tile per deposit CTA of a launch
   size_t det_tiles_cap = 0;                   // ... capacity in doubles
   long long rec_scratch_max = 1LL << 27;      // option deposit_scratch (particles per slab, 64 B each)
+  // option push_overlap: the deposit of slab s runs on a second stream beside the push of slab s + 1 (the record
+  // scratch is used as two halves); measured, see DESIGN.md section 8
+  bool push_overlap = false;
+  cudaStream_t stream2 = nullptr;
+  cudaEvent_t ev_push[2] = {nullptr, nullptr}, ev_dep[2] = {nullptr, nullptr};
   // options
   int push_kernel = 0;          // 0 auto, 1 baseline (global atomics), 3 tiled (push + deposit kernels)
   int deterministic = 0;

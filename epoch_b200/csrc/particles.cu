@@ -650,6 +650,145 @@ __global__ void k_particle_bc(BcP b, long long n, double* __restrict__ pos, doub
     if (xbd != 0) atomicAdd(counters + (xbd < 0 ? 0 : 1), 1ULL);
   }
 }
+// ---- thermal particle boundaries (boundary.F90:1405-1461 for x_min, the five other faces alike) ----------------
+// A particle beyond the OUTER edge of a thermal face is re-emitted: temperature from ext_temp at its transverse
+// position (triangle weighting, always), momenta drawn in the order x, y, z (normal component from the flux
+// distribution heading inwards: SQRT(N1^2 + N2^2) of two normal deviates; the others normal), position mirrored at
+// the outer edge.  Runs before the other particle boundaries of the step.  The reference handles a particle's axes
+// in turn, so a particle that also wraps / reflects on an EARLIER axis in the same step is seen here with that
+// position taken into account (a local copy; the wrap itself is stored by the regular pass).  The deviates come
+// from a counter-based generator keyed by (seed, call, slot): the reference's is one sequential host stream whose
+// draws depend on the list order, so the distributions agree, not the numbers.
+struct ThermalP {
+  int nd, ng, on[6], ext[3], wrap_min[3], wrap_max[3], refl_min[3], refl_max[3];
+  double edge[6], gml[3], d[3], min_local[3], max_local[3], gmin[3], gmax[3], shift[3], sigma2;   // sigma2 = kB * mass
+  const double* temp[6];
+  unsigned long long seed, call;
+};
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {      // splitmix64 finaliser
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  return z ^ (z >> 31);
+}
+__device__ __forceinline__ double u01(unsigned long long key, unsigned long long ctr) {   // uniform in (0, 1)
+  const unsigned long long r = mix64(key + ctr * 0x9E3779B97F4A7C15ULL);
+  return ((double)(r >> 11) + 0.5) * (1.0 / 9007199254740992.0);
+}
+__global__ void k_thermal_bc(ThermalP t, long long n, double* x, double* y, double* z, double* px, double* py, double* pz,
+                             const uint32_t* __restrict__ key, unsigned long long* counters) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || key[i] == KEY_INVALID) return;
+  double q[3] = {x[i], t.nd >= 2 ? y[i] : 0.0, t.nd >= 3 ? z[i] : 0.0};
+  double mom[3];
+  bool hit = false;
+  const unsigned long long kbase = mix64(t.seed ^ mix64(t.call * 0xD1B54A32D192ED03ULL + (unsigned long long)i));
+  unsigned long long ctr = 0;
+  for (int d = 0; d < t.nd; ++d) {
+    const double part_pos = q[d];
+    for (int side = 0; side < 2; ++side) {
+      const int b = 2 * d + side;
+      if (!t.on[b]) {
+        // the position an earlier axis leaves behind for the later ones (periodic wrap / reflection; not stored here)
+        if (side == 0 && part_pos < t.min_local[d]) { if (t.wrap_min[d]) q[d] = part_pos + t.shift[d]; else if (t.refl_min[d]) q[d] = 2.0 * t.gmin[d] - part_pos; }
+        if (side == 1 && part_pos >= t.max_local[d]) { if (t.wrap_max[d]) q[d] = part_pos - t.shift[d]; else if (t.refl_max[d]) q[d] = 2.0 * t.gmax[d] - part_pos; }
+        continue;
+      }
+      if (side == 0 ? !(part_pos < t.edge[b]) : !(part_pos >= t.edge[b])) continue;
+      int ta[2], nt = 0;
+      for (int a = 0; a < t.nd; ++a) if (a != d) ta[nt++] = a;
+      int cell[2] = {1, 1};
+      double g[2][3] = {{0.0, 1.0, 0.0}, {0.0, 1.0, 0.0}};
+      for (int k = 0; k < nt; ++k) {
+        const int a = ta[k];
+        const double cell_r = __ddiv_rn(__dsub_rn(q[a], t.gml[a]), t.d[a]);
+        const int c0 = (int)floor(__dadd_rn(cell_r, 0.5));
+        const double cf = __dsub_rn((double)c0, cell_r);
+        cell[k] = c0 + 1;
+        const double cf2 = __dmul_rn(cf, cf);
+        g[k][0] = 0.5 * (0.25 + cf2 + cf);
+        g[k][1] = 0.75 - cf2;
+        g[k][2] = 0.5 * (0.25 + cf2 - cf);
+      }
+      const long long e1 = nt >= 1 ? t.ext[ta[0]] : 1, e2 = nt >= 2 ? t.ext[ta[1]] : 1;
+      const double* et = t.temp[b];
+      double temp[3];
+      for (int c = 0; c < 3; ++c) {
+        temp[c] = 0.0;
+        if (nt == 0) { temp[c] = et[c]; continue; }
+        for (int i2 = (nt >= 2 ? -1 : 0); i2 <= (nt >= 2 ? 1 : 0); ++i2)
+          for (int i1 = -1; i1 <= 1; ++i1) {
+            long long j1 = cell[0] + i1 - (1 - t.ng), j2 = nt >= 2 ? cell[1] + i2 - (1 - t.ng) : 0;
+            j1 = j1 < 0 ? 0 : (j1 >= e1 ? e1 - 1 : j1);        // (memory safety for a particle far outside the transverse range)
+            j2 = j2 < 0 ? 0 : (j2 >= e2 ? e2 - 1 : j2);
+            const double w2 = nt >= 2 ? g[1][i2 + 1] : 1.0;
+            temp[c] = temp[c] + g[0][i1 + 1] * w2 * et[((long long)c * e2 + j2) * e1 + j1];
+          }
+      }
+      // four normal deviates (two Box-Muller pairs): the normal component takes two, the others one each
+      double nrm[4];
+      for (int k = 0; k < 2; ++k) {
+        const double u1 = u01(kbase, ctr++), u2 = u01(kbase, ctr++);
+        const double r = sqrt(-2.0 * log(u1));
+        double sn, cs;
+        sincospi(2.0 * u2, &sn, &cs);
+        nrm[2 * k] = r * cs; nrm[2 * k + 1] = r * sn;
+      }
+      int used = 0;
+      for (int c = 0; c < 3; ++c) {
+        const double stdev = sqrt(temp[c] * t.sigma2);
+        if (c == d) {
+          const double m1 = nrm[used] * stdev, m2 = nrm[used + 1] * stdev;
+          used += 2;
+          mom[c] = (side == 0 ? 1.0 : -1.0) * sqrt(m1 * m1 + m2 * m2);
+        } else {
+          mom[c] = nrm[used++] * stdev;
+        }
+      }
+      q[d] = 2.0 * t.edge[b] - part_pos;
+      hit = true;
+      double* pa = d == 0 ? x : (d == 1 ? y : z);
+      pa[i] = q[d];
+      atomicAdd(counters + 9, 1ULL);
+      break;      // (mirrored at the min edge: it cannot be beyond the max edge too)
+    }
+  }
+  if (hit) { px[i] = mom[0]; py[i] = mom[1]; pz[i] = mom[2]; }
+}
+
+// re-emission at this rank's thermal faces, before the other particle boundaries of the step
+static int32_t thermal_bcs(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
+  ThermalP t{};
+  bool any = false;
+  for (int d = 0; d < c->ndims; ++d) {
+    const BcP b = make_bc(c, sp, d);
+    for (int side = 0; side < 2; ++side) {
+      const int f = 2 * d + side;
+      const bool at_face = side == 0 ? b.min_bnd : b.max_bnd;
+      const bool cpml = side == 0 ? b.cpml_min : b.cpml_max;
+      t.on[f] = at_face && !cpml && sp.bc[f] == EB200_BC_THERMAL;
+      if (t.on[f] && !sp.ext_temp[f]) return fail(c, EB200_E_STATE, "thermal particle boundary without set_thermal_boundary");
+      t.edge[f] = side == 0 ? b.min_outer : b.max_outer;
+      t.temp[f] = sp.ext_temp[f];
+      any = any || t.on[f];
+    }
+    t.gml[d] = c->g.gml[d]; t.d[d] = c->g.d[d]; t.ext[d] = c->g.n[d] + 2 * c->ng;
+    t.min_local[d] = b.min_local; t.max_local[d] = b.max_local; t.gmin[d] = b.gmin; t.gmax[d] = b.gmax; t.shift[d] = b.shift;
+    t.wrap_min[d] = b.min_bnd && !b.cpml_min && b.bc_min == EB200_BC_PERIODIC; t.wrap_max[d] = b.max_bnd && !b.cpml_max && b.bc_max == EB200_BC_PERIODIC;
+    t.refl_min[d] = b.min_bnd && !b.cpml_min && b.bc_min == EB200_BC_REFLECT; t.refl_max[d] = b.max_bnd && !b.cpml_max && b.bc_max == EB200_BC_REFLECT;
+  }
+  if (!any || n_slots <= 0) return 0;
+  t.nd = c->ndims; t.ng = c->ng; t.sigma2 = KB * sp.mass; t.seed = sp.thermal_seed; t.call = sp.thermal_calls++;
+  k_thermal_bc<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(t, n_slots, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5],
+                                                                       sp.key, c->d_counters);
+  c->launches++;
+  EB_CUDA(c, cudaGetLastError());
+  return 0;
+}
+static bool has_thermal(const eb200_ctx* c, const SpeciesD& sp) {
+  for (int f = 0; f < 2 * c->ndims; ++f) if (sp.bc[f] == EB200_BC_THERMAL) return true;
+  return false;
+}
+
 // Migration messages are fixed-capacity mailboxes: [packed count, wanted count, cap x nvar doubles].  The
 // capacity of a directed link is agreed without talking: both ends grow it by the same rule from the count the
 // sender WANTED to send (it travels in the header), read a step late at the sort's synchronise.  So particle_bcs
@@ -940,6 +1079,7 @@ int32_t particle_bcs(eb200_ctx* c) {
     bool changed = false;
     {
       ScopedPhase ph(c, "bcs");
+      if (has_thermal(c, sp)) { EB_TRY(settle_species(c, sp)); EB_TRY(thermal_bcs(c, sp, n_slots)); }
       EB_TRY(species_bcs(c, sp, n_slots, changed));
     }
     EB_TRY(sort_species(c, sp, n_slots, false, sp.was_ordered && c->ndims >= 2 && (c->push_kernel == 0 || c->push_kernel == 3)));
@@ -981,7 +1121,7 @@ int32_t push_particles(eb200_ctx* c) {
         // Several ranks: the same, when the decomposed axes are periodic for the particles (nothing but
         // migration happens there): leavers give their count back when they are packed, arrivals are keyed
         // and counted by a pass over the arrivals alone.
-        bool fusable = c->fuse_keys != 0;
+        bool fusable = c->fuse_keys != 0 && !has_thermal(c, sp);     // (thermal faces re-emit before the keys are made)
         for (int d = 0; d < c->ndims; ++d)
           if (c->nprocdir[d] > 1 && (sp.bc[2 * d] != EB200_BC_PERIODIC || sp.bc[2 * d + 1] != EB200_BC_PERIODIC)) fusable = false;
         if (fusable) {
@@ -1062,6 +1202,7 @@ int32_t push_particles(eb200_ctx* c) {
     bool changed = false;
     {
       ScopedPhase ph(c, "bcs");
+      if (has_thermal(c, sp)) EB_TRY(thermal_bcs(c, sp, n_slots));
       EB_TRY(species_bcs(c, sp, n_slots, changed));
     }
     EB_TRY(sort_species(c, sp, n_slots, false, tiled[is] != 0));

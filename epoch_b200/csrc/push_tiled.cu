@@ -1312,9 +1312,19 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
     EB_CUDA(c, cudaMalloc(&c->rec_scratch, (size_t)want * 8 * sizeof(double)));
     c->rec_scratch_cap = want;
   }
-  const long long cap = c->rec_scratch_cap < room ? c->rec_scratch_cap : room;
   // deterministic mode: one J tile per deposit CTA (1 GB of them at most per launch)
   const bool det = c->deterministic && !p.zero_current;
+  // option push_overlap: two halves of the scratch, the deposit of a slab on a second stream beside the next slab's push
+  const bool overlap = c->push_overlap && !det && !p.zero_current && c->rec_scratch_cap / 2 >= biggest;
+  if (overlap && !c->stream2) {
+    EB_CUDA(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; ++k) {
+      EB_CUDA(c, cudaEventCreateWithFlags(&c->ev_push[k], cudaEventDisableTiming));
+      EB_CUDA(c, cudaEventCreateWithFlags(&c->ev_dep[k], cudaEventDisableTiming));
+    }
+  }
+  const long long scratch_slab = overlap ? c->rec_scratch_cap / 2 : c->rec_scratch_cap;
+  const long long cap = scratch_slab < room ? scratch_slab : room;
   const int jn3[3] = {TL<3, 0>::JN, TL<3, 1>::JN, TL<3, 2>::JN}, jn2[3] = {TL<2, 0>::JN, TL<2, 1>::JN, TL<2, 2>::JN};
   const size_t tile_doubles = 3 * (size_t)(c->ndims == 3 ? jn3[c->shape] : jn2[c->shape]);   // >= the sub-tile's
   const long long max_tiles = det ? std::max<long long>(1, (long long)(((size_t)1 << 30) / (tile_doubles * 8 * SUB))) : (1LL << 62);
@@ -1340,6 +1350,9 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
     long long big = 1;
     for (long long t = t0; t < t1; ++t) big = std::max<long long>(big, (long long)(ts[t + 1] - ts[t]));
     const dim3 ga(nb, (unsigned)((big + PUSH_CHUNK - 1) / PUSH_CHUNK));
+    double* const scr = c->rec_scratch + (overlap ? (size_t)(is & 1) * (size_t)scratch_slab * 8 : 0);
+    cudaStream_t sdep = overlap ? c->stream2 : c->stream;
+    if (overlap && is >= 2) EB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_dep[is & 1], 0));   // the half is free again
 #define L(ND, SH)                                                                                          \
     if (c->ndims == ND && c->shape == SH) {                                                                \
       auto ka = probe ? (gather ? k_push_split<ND, SH, true, true> : k_push_split<ND, SH, false, true>)    \
@@ -1351,9 +1364,11 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
       EB_CUDA(c, cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sa));          \
       EB_CUDA(c, cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sb));          \
       { ScopedPhase pa(c, "push_A");                                                                       \
-        ka<<<ga, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, c->rec_scratch, c->d_counters, ks, tmap, use_tma, d_probes); } \
-      if (!p.zero_current) { ScopedPhase pb(c, "push_B");                                                  \
-        kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, c->stream>>>(c->g, c->f, p, sp.cell_start, t0, c->rec_scratch, c->det_tiles); \
+        ka<<<ga, NTA, sa, c->stream>>>(c->g, c->f, p, a, o, side, sp.dest, n_main, sp.cell_start, t0, scr, c->d_counters, ks, tmap, use_tma, d_probes); } \
+      if (overlap) { cudaEventRecord(c->ev_push[is & 1], c->stream); cudaStreamWaitEvent(sdep, c->ev_push[is & 1], 0); } \
+      if (!p.zero_current) { ScopedPhase pb(c, "push_B");   /* (push_overlap: issued on the second stream, not timed here) */ \
+        kb<<<nb * SUB, TL<ND, SH>::CPT / SUB, sb, sdep>>>(c->g, c->f, p, sp.cell_start, t0, scr, c->det_tiles); \
+        if (overlap) cudaEventRecord(c->ev_dep[is & 1], sdep);                                             \
         if (det) {                                                                                         \
           /* planes of the slowest axis that the tiles [t0, t1) can reach */                              \
           const long long per_layer = ND == 3 ? (long long)c->g.ntile[0] * c->g.ntile[1] : c->g.ntile[0];  \
@@ -1374,6 +1389,8 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
 #undef L
     c->launches += p.zero_current ? 1 : 2;
   }
+  if (overlap)      // join: everything after the push waits for the last deposits
+    for (size_t k = 0; k < std::min<size_t>(2, slabs.size()); ++k) EB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_dep[k], 0));
   EB_CUDA(c, cudaGetLastError());
   if (gather) { set_view(sp, off_new); sp.deferred = false; }
   *handled = true;

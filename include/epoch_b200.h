@@ -325,6 +325,20 @@ int32_t EB200_NAME(set_probe)(EB200_CTX*, int32_t ispecies, int32_t iprobe, cons
  * EB200_E_NOMEM (last_error says how many were sampled). */
 int32_t EB200_NAME(download_probe)(EB200_CTX*, int32_t ispecies, int32_t iprobe, int64_t capacity, double* packed,
                                    int32_t nvar, int64_t* n_out, int32_t clear);
+/* Thermal particle boundaries (c_bc_thermal; particle_bcs, boundary.F90:1405-1461 and the five other faces): a
+ * particle of the species that passes the OUTER edge of boundary `boundary` (1..6 = x_min .. z_max) is re-emitted --
+ * temperature interpolated from ext_temp (triangle weighting at its transverse position), momenta drawn in the order
+ * x, y, z (normal component: flux_momentum_from_temperature heading inwards, the others momentum_from_temperature,
+ * particle_temperature.F90:396-469, drift 0), position mirrored at the outer edge.  ext_temp is the species'
+ * ext_temp_<face> array as the reference allocates it (mpi_routines.F90:561-584): transverse extents 1-ng:n+ng,
+ * first transverse axis fastest, then the 3 temperature components (1D: 3 numbers).  Must be called (again after a
+ * re-slice) before the first push of a species whose set_species lists EB200_BC_THERMAL on that face.  `seed` keys
+ * the device's counter-based generator (one independent stream per re-emitted particle and call; the reference's
+ * generator is one sequential host stream whose draws depend on the list order, so only the distributions agree).
+ * EB200_BC_HEAT_BATH is accepted by set_species as EB200_BC_OPEN: setup_domain_dependent_boundaries (boundary.F90:
+ * 75-93) turns it into an open boundary plus a boundary injector, and injectors stay on the host. */
+int32_t EB200_NAME(set_thermal_boundary)(EB200_CTX*, int32_t ispecies, int32_t boundary, const double* ext_temp,
+                                         int64_t seed);
 /* options (key, value as strings):
  *   "deterministic_deposit" "0|1"   run-to-run bitwise reproducible currents (tiled kernels: 2D/3D)
  *   "push_kernel"   "auto|baseline|tiled"

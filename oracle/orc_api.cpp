@@ -205,8 +205,8 @@ int32_t orc_set_species(orc_ctx* c, int32_t isp, double charge, double mass, dou
     // setup_particle_boundary, boundary.F90:98-140
     if (bc == BC_OTHER || bc == BC_CONDUCT) bc = BC_REFLECT;
     if (bc == BC_SIMPLE_LASER || bc == BC_SIMPLE_OUTFLOW || bc == BC_CPML_LASER || bc == BC_CPML_OUTFLOW) bc = BC_OPEN;
-    if (bc == BC_THERMAL || bc == BC_HEAT_BATH) return fail(c, EB200_E_UNSUPPORTED, "thermal particle BCs not supported");
-    if (bc != BC_PERIODIC && bc != BC_REFLECT && bc != BC_OPEN) return fail(c, EB200_E_ARG, "bad particle BC");
+    if (bc == BC_HEAT_BATH) bc = BC_OPEN;      // setup_domain_dependent_boundaries, boundary.F90:75-93 (the injector stays on the host)
+    if (bc != BC_PERIODIC && bc != BC_REFLECT && bc != BC_OPEN && bc != BC_THERMAL) return fail(c, EB200_E_ARG, "bad particle BC");
     sp.bc[i] = bc;
   }
   return 0;
@@ -305,10 +305,17 @@ int32_t orc_set_laser_step(orc_ctx* c, int32_t boundary, int32_t id, double t_en
   return fail(c, EB200_E_ARG, "laser id not set");
 }
 
+static bool thermal_tables_missing(const State& s) {
+  for (const Species& sp : s.species)
+    for (int b = 0; sp.defined && b < 2 * s.ndims; ++b)
+      if (sp.bc[b] == BC_THERMAL && sp.ext_temp[b].empty()) return true;
+  return false;
+}
 #define HOT(name, call)                                                         \
   int32_t orc_##name(orc_ctx* c) {                                              \
     if (!c || !c->s.grid_set) return fail(c, EB200_E_STATE, "grid not set");    \
     if (c->s.dt <= 0) return fail(c, EB200_E_STATE, "dt not set");              \
+    if (thermal_tables_missing(c->s)) return fail(c, EB200_E_STATE, "thermal boundary without set_thermal_boundary"); \
     call(c->s);                                                                 \
     return 0;                                                                   \
   }
@@ -373,6 +380,18 @@ int32_t orc_calc_derived(orc_ctx* c, int32_t kind, int32_t ispecies, int32_t dir
   const bool need_dir = kind == 2 || kind == 3 || kind == 9 || kind == 10;
   if (ad > 3 || (need_dir && ad == 0) || (direction < 0 && kind != 2)) return EB200_E_ARG;
   calc_derived(c->s, kind, ispecies, direction, out);
+  return 0;
+}
+int32_t orc_set_thermal_boundary(orc_ctx* c, int32_t isp, int32_t boundary, const double* ext_temp, int64_t seed) {
+  if (!c || !c->s.grid_set) return EB200_E_STATE;
+  State& s = c->s;
+  if (isp < 0 || isp >= (int32_t)s.species.size() || !s.species[isp].defined || !ext_temp) return EB200_E_ARG;
+  if (boundary < 1 || boundary > 2 * s.ndims) return EB200_E_ARG;
+  const int d = (boundary - 1) / 2;
+  size_t plane = 1;
+  for (int a = 0; a < s.ndims; ++a) if (a != d) plane *= (size_t)(s.n[a] + 2 * s.ng);
+  s.species[isp].ext_temp[boundary - 1].assign(ext_temp, ext_temp + 3 * plane);
+  (void)seed;      // the oracle draws from the reference's own sequential generator (orc_random_init)
   return 0;
 }
 int32_t orc_set_probe(orc_ctx* c, int32_t isp, int32_t iprobe, const double* point, const double* normal, double ek_min,

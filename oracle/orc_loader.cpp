@@ -77,6 +77,9 @@ static double box_muller(Rng& s, double stdev, double mu) {
   return rand1 * w * stdev + mu;
 }
 
+double global_random() { return kiss(g_rng); }
+double global_random_box_muller(double stdev, double mu) { return box_muller(g_rng, stdev, mu); }
+
 // particle_to_grid.inc: nearest cell (1-based) and normalised weights of one axis
 static int to_grid(const State& s, int d, double pos, double* g) {
   double cr = (pos - s.grid_min_local[d]) / s.d[d];

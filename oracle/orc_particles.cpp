@@ -337,6 +337,58 @@ void push_particles(State& s) {
   particle_bcs(s);
 }
 
+// momentum_from_temperature / flux_momentum_from_temperature with drift = 0 (particle_temperature.F90:396-469)
+static double momentum_from_temperature(double mass, double temperature) {
+  const double stdev = std::sqrt(temperature * KB * mass);
+  return global_random_box_muller(stdev, 0.0);
+}
+static double flux_momentum_from_temperature(double mass, double temperature, double direction) {
+  // drift == 0: Rayleigh distributed, Z = SQRT(X**2 + Y**2) of two normal deviates
+  const double mom1 = momentum_from_temperature(mass, temperature);
+  const double mom2 = momentum_from_temperature(mass, temperature);
+  return direction * std::sqrt(mom1 * mom1 + mom2 * mom2);
+}
+
+// Thermal boundary (boundary.F90:1405-1461 for x_min, the five others alike): the temperature at the particle's
+// transverse position (always the triangle weighting), new momenta drawn in the order x, y, z -- the normal
+// component from the flux distribution, heading back in -- and the position mirrored at the outer edge.
+static void thermal_reemit(State& s, Species& sp, size_t ip, int d, int side, double edge, double part_pos) {
+  const int nd = s.ndims;
+  int t[2], nt = 0;
+  for (int a = 0; a < nd; ++a) if (a != d) t[nt++] = a;
+  int cell[2] = {1, 1};
+  double g[2][3] = {{0.0, 1.0, 0.0}, {0.0, 1.0, 0.0}};
+  for (int k = 0; k < nt; ++k) {
+    const int a = t[k];
+    const double cell_r = (sp.pos[a][ip] - s.grid_min_local[a]) / s.d[a];
+    const int c0 = (int)std::floor(cell_r + 0.5);
+    const double cell_frac = (double)c0 - cell_r;
+    cell[k] = c0 + 1;
+    const double cf2 = cell_frac * cell_frac;
+    g[k][0] = 0.5 * (0.25 + cf2 + cell_frac);
+    g[k][1] = 0.75 - cf2;
+    g[k][2] = 0.5 * (0.25 + cf2 - cell_frac);
+  }
+  const std::vector<double>& et = sp.ext_temp[2 * d + side];
+  const int64_t e1 = nt >= 1 ? s.n[t[0]] + 2 * s.ng : 1, e2 = nt >= 2 ? s.n[t[1]] + 2 * s.ng : 1;
+  double temp[3];
+  for (int i = 0; i < 3; ++i) {
+    temp[i] = 0.0;
+    if (nt == 0) { temp[i] = et[i]; continue; }
+    for (int i2 = (nt >= 2 ? -1 : 0); i2 <= (nt >= 2 ? 1 : 0); ++i2)
+      for (int i1 = -1; i1 <= 1; ++i1) {
+        const int64_t j1 = cell[0] + i1 - (1 - s.ng), j2 = nt >= 2 ? cell[1] + i2 - (1 - s.ng) : 0;
+        const double w2 = nt >= 2 ? g[1][i2 + 1] : 1.0;
+        temp[i] = temp[i] + g[0][i1 + 1] * w2 * et[((int64_t)i * e2 + j2) * e1 + j1];
+      }
+  }
+  const double direction = side == 0 ? 1.0 : -1.0;      // -REAL(sgn, num)
+  for (int i = 0; i < 3; ++i)
+    sp.p[i][ip] = i == d ? flux_momentum_from_temperature(sp.mass, temp[i], direction)
+                         : momentum_from_temperature(sp.mass, temp[i]);
+  sp.pos[d][ip] = 2.0 * edge - part_pos;
+}
+
 // boundary.F90:1316-1972 (single rank: a particle that leaves through a periodic
 // face wraps by the domain length; reflect mirrors; anything else is "open" and
 // the particle is removed once beyond x_min_outer / x_max_outer).
@@ -368,7 +420,10 @@ void particle_bcs(State& s) {
             } else if (bc == BC_PERIODIC) {
               sp.pos[d][ip] = part_pos - (-1.0) * shift;
             }
-            if (part_pos < min_outer && bc != BC_PERIODIC) out_of_bounds = true;
+            if (part_pos < min_outer && bc != BC_PERIODIC) {
+              if (bc == BC_THERMAL) thermal_reemit(s, sp, ip, d, 0, min_outer, part_pos);
+              else out_of_bounds = true;
+            }
           }
         }
         if (cpml_max) {
@@ -382,7 +437,10 @@ void particle_bcs(State& s) {
             } else if (bc == BC_PERIODIC) {
               sp.pos[d][ip] = part_pos - shift;
             }
-            if (part_pos >= max_outer && bc != BC_PERIODIC) out_of_bounds = true;
+            if (part_pos >= max_outer && bc != BC_PERIODIC) {
+              if (bc == BC_THERMAL) thermal_reemit(s, sp, ip, d, 1, max_outer, part_pos);
+              else out_of_bounds = true;
+            }
           }
         }
       }

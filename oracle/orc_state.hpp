@@ -53,8 +53,14 @@ struct Species {
   // particle probes (shared_data.F90:392-404) and their sampled particles (packed pos, p(3), weight)
   struct Probe { bool on = false; double point[3] = {0, 0, 0}, normal[3] = {0, 0, 0}, ek_min = 0, ek_max = 0; std::vector<double> sampled; };
   Probe probes[8];
+  // thermal particle boundaries: ext_temp_{x,y,z}_{min,max}(transverse extents incl. ghosts, 3), mpi_routines.F90:561-584
+  std::vector<double> ext_temp[6];
   size_t count() const { return w.size(); }
 };
+
+// global_random of the reference (orc_loader.cpp: KISS + polar Box-Muller, random_generator.f90:45-173)
+double global_random();
+double global_random_box_muller(double stdev, double mu);
 
 struct State {
   int ndims = 3, shape = 1;
