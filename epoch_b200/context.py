@@ -189,6 +189,12 @@ class PicContext:
                                              self.nvar, C.byref(got)))
         return out[:got.value]
 
+    def set_thermal_boundary(self, isp, boundary, ext_temp, seed=0):
+        """ext_temp_<face> of species isp (boundary 1..6 = x_min .. z_max; mpi_routines.F90:561-584): array shaped
+        (3, n_t2 + 2 ng, n_t1 + 2 ng) -- the Fortran ext_temp(1-ng:n_t1+ng, 1-ng:n_t2+ng, 3) in C order; 1D: (3,)"""
+        a = np.ascontiguousarray(ext_temp, dtype=np.float64)
+        self._ck(self.abi.set_thermal_boundary(self._ctx, isp, int(boundary), a.ctypes.data_as(C.POINTER(C.c_double)), int(seed)))
+
     def set_probe(self, isp, iprobe, point, normal, ek_min=0.0, ek_max=1e300):
         """particle probe (shared_data.F90:392-404) iprobe = 0..7 of species isp"""
         self._ck(self.abi.set_probe(self._ctx, isp, iprobe, _f64(_pad3(point, 0.0)), _f64(_pad3(normal, 0.0)), ek_min, ek_max))

@@ -661,9 +661,11 @@ int32_t eb200_timer(eb200_ctx* c, const char* phase, int32_t reset, double* ms, 
     if (reset) { c->n_deferred = 0; c->n_permuted = 0; }
     return 0;
   }
-  if (k == "cell_mismatch") {   // particles whose sort key and push disagreed on the cell (must stay 0)
+  if (k == "cell_mismatch" || k == "thermal_reemitted") {
+    // particles whose sort key and push disagreed on the cell (must stay 0) / particles re-emitted by thermal walls so far
     unsigned long long v = 0;
-    EB_CUDA(c, cudaMemcpy(&v, c->d_counters + 8, sizeof(v), cudaMemcpyDeviceToHost));
+    EB_CUDA(c, cudaStreamSynchronize(c->stream));
+    EB_CUDA(c, cudaMemcpy(&v, c->d_counters + (k == "cell_mismatch" ? 8 : 9), sizeof(v), cudaMemcpyDeviceToHost));
     if (ms) *ms = 0;
     if (launches) *launches = (int64_t)v;
     return 0;

@@ -15,6 +15,7 @@ namespace eb {
 constexpr double PI = 3.141592653589793238462643383279503;
 constexpr double C0 = 2.99792458e8;
 constexpr double EPS0 = 8.854187817620389850536563031710750e-12;
+constexpr double KB = 1.3806488e-23;          // constants.F90 (kb)
 
 enum { EX = 0, EY, EZ, BX, BY, BZ, JX, JY, JZ, NFIELD };
 enum { SHAPE_TOPHAT = 0, SHAPE_TRIANGLE = 1, SHAPE_BSPLINE3 = 2 };

@@ -16,7 +16,6 @@ namespace eb {
 
 namespace {
 
-constexpr double KB = 1.3806488e-23;
 constexpr double C_TINY = 2.2250738585072014e-308;   // TINY(1.0_num), constants.F90:29
 constexpr double PI_ = 3.141592653589793238462643383279503;
 constexpr double MU0 = 4.e-7 * PI_;

@@ -128,9 +128,35 @@ CONTAINS
           species_list(ispecies)%mass, species_weight, &
           MERGE(1, 0, species_list(ispecies)%immobile), MERGE(1, 0, species_list(ispecies)%zero_current), &
           MERGE(1, 0, species_list(ispecies)%species_type == c_species_id_photon), bcp))
+      CALL gpu_send_thermal(ispecies)
     END DO
     device_stale = .TRUE.
   END SUBROUTINE gpu_attach
+
+  SUBROUTINE gpu_send_thermal(ispecies)
+    ! ext_temp_<face> of a species with thermal particle boundaries (mpi_routines.F90:561-584; filled by
+    ! helper.F90:42-57); again after balance_workload re-sliced them (balance.F90:1170-1260).  The device draws
+    ! from its own counter-based generator, keyed here by the rank so that ranks differ.
+    INTEGER, INTENT(IN) :: ispecies
+    INTEGER(C_INT64_T) :: seed
+    seed = 7842432_C_INT64_T + INT(rank, C_INT64_T)
+    IF (species_list(ispecies)%bc_particle(c_bd_x_min) == c_bc_thermal) CALL gpu_check(eb200_set_thermal_boundary( &
+        gpu, ispecies - 1, c_bd_x_min, species_list(ispecies)%ext_temp_x_min, seed))
+    IF (species_list(ispecies)%bc_particle(c_bd_x_max) == c_bc_thermal) CALL gpu_check(eb200_set_thermal_boundary( &
+        gpu, ispecies - 1, c_bd_x_max, species_list(ispecies)%ext_temp_x_max, seed))
+#if EPOCH_NDIMS >= 2
+    IF (species_list(ispecies)%bc_particle(c_bd_y_min) == c_bc_thermal) CALL gpu_check(eb200_set_thermal_boundary( &
+        gpu, ispecies - 1, c_bd_y_min, species_list(ispecies)%ext_temp_y_min, seed))
+    IF (species_list(ispecies)%bc_particle(c_bd_y_max) == c_bc_thermal) CALL gpu_check(eb200_set_thermal_boundary( &
+        gpu, ispecies - 1, c_bd_y_max, species_list(ispecies)%ext_temp_y_max, seed))
+#endif
+#if EPOCH_NDIMS >= 3
+    IF (species_list(ispecies)%bc_particle(c_bd_z_min) == c_bc_thermal) CALL gpu_check(eb200_set_thermal_boundary( &
+        gpu, ispecies - 1, c_bd_z_min, species_list(ispecies)%ext_temp_z_min, seed))
+    IF (species_list(ispecies)%bc_particle(c_bd_z_max) == c_bc_thermal) CALL gpu_check(eb200_set_thermal_boundary( &
+        gpu, ispecies - 1, c_bd_z_max, species_list(ispecies)%ext_temp_z_max, seed))
+#endif
+  END SUBROUTINE gpu_send_thermal
 
   SUBROUTINE gpu_set_grid
     ! call again after balance_workload / moving_window changed the local grid

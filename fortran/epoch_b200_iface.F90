@@ -26,6 +26,14 @@ MODULE epoch_b200_iface
       IMPORT :: C_INT32_T, C_PTR
       TYPE(C_PTR), VALUE :: p
     END FUNCTION eb200_host_free
+    INTEGER(C_INT32_T) FUNCTION eb200_set_thermal_boundary(ctx, ispecies, boundary, ext_temp, seed) &
+        BIND(C, NAME='eb200_set_thermal_boundary')
+      IMPORT
+      TYPE(C_PTR), VALUE :: ctx
+      INTEGER(C_INT32_T), VALUE :: ispecies, boundary
+      REAL(C_DOUBLE), INTENT(IN) :: ext_temp(*)
+      INTEGER(C_INT64_T), VALUE :: seed
+    END FUNCTION eb200_set_thermal_boundary
     INTEGER(C_INT32_T) FUNCTION eb200_set_probe(ctx, ispecies, iprobe, point, normal, ek_min, ek_max) &
         BIND(C, NAME='eb200_set_probe')
       IMPORT :: C_INT32_T, C_DOUBLE, C_PTR
