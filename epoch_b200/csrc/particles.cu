@@ -41,7 +41,7 @@ static int32_t regrow(eb200_ctx* c, T*& base, const T* view, long long old_n, lo
 int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need, bool exact) {
   if (sp.base[6] && need + sp.win + 2 * sp.gap <= sp.cap) return 0;
   EB_TRY(settle_species(c, sp));
-  const bool tiled = c->ndims >= 2 && c->push_kernel != 1;
+  const bool tiled = c->push_kernel != 1;
   long long win = !tiled ? 0 : (c->defer_window >= 0 ? c->defer_window : std::max<long long>(need / 8, 1 << 16));
   const long long gap = 0;      // (slots kept free below the low state: none needed, arrivals are appended)
   const long long body = exact ? std::max<long long>(need, 1024) : std::max<long long>(need + need / 32 + 1024, 4096);
@@ -1082,7 +1082,7 @@ int32_t particle_bcs(eb200_ctx* c) {
       if (has_thermal(c, sp)) { EB_TRY(settle_species(c, sp)); EB_TRY(thermal_bcs(c, sp, n_slots)); }
       EB_TRY(species_bcs(c, sp, n_slots, changed));
     }
-    EB_TRY(sort_species(c, sp, n_slots, false, sp.was_ordered && c->ndims >= 2 && (c->push_kernel == 0 || c->push_kernel == 3)));
+    EB_TRY(sort_species(c, sp, n_slots, false, sp.was_ordered && (c->push_kernel == 0 || c->push_kernel == 3)));
   }
   return 0;
 }
@@ -1105,7 +1105,7 @@ int32_t push_particles(eb200_ctx* c) {
     // (a re-sort after a window shift or a dt change moves particles by about a tile: the permute can be
     //  left to the push like any other; an unordered load overflows the side buffer and is permuted at once)
     if (!sp.sorted || sp.sort_dt != c->dt)
-      EB_TRY(sort_species(c, sp, sp.n, false, sp.was_ordered && c->ndims >= 2 && (c->push_kernel == 0 || c->push_kernel == 3)));
+      EB_TRY(sort_species(c, sp, sp.n, false, sp.was_ordered && (c->push_kernel == 0 || c->push_kernel == 3)));
     if (sp.n == 0) { sp.deferred = false; continue; }
     PushP p = make_push_params(c, sp, sp.n);
     bool handled = false, fused_keys = false;
@@ -1158,7 +1158,7 @@ int32_t push_particles(eb200_ctx* c) {
       }
       if (!handled) {
         if (c->deterministic)
-          return fail(c, EB200_E_UNSUPPORTED, "deterministic_deposit needs the tiled kernels (2D/3D)");
+          return fail(c, EB200_E_UNSUPPORTED, "deterministic_deposit needs the tiled kernels (option push_kernel)");
         EB_TRY(settle_species(c, sp));
         EB_TRY(launch_push_baseline(c, sp, p));
       }
@@ -1184,7 +1184,7 @@ int32_t push_particles(eb200_ctx* c) {
 #define LK(ND, SH)                                                                               \
           if (c->ndims == ND && c->shape == SH)                                                  \
             k_keys<ND, SH><<<ga, 256, 0, c->stream>>>(c->g, pk2, bc, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5], sp.key, c->cell_count, nbucket, n_counted);
-          LK(2, 0) LK(2, 1) LK(2, 2) LK(3, 0) LK(3, 1) LK(3, 2)
+          LK(1, 0) LK(1, 1) LK(1, 2) LK(2, 0) LK(2, 1) LK(2, 2) LK(3, 0) LK(3, 1) LK(3, 2)
 #undef LK
           c->launches++;
         }

@@ -65,11 +65,11 @@ struct TL {
   static constexpr int JX = TX + NW + 1, JY = ND >= 2 ? TY + NW + 1 : 1, JZ = ND >= 3 ? TZ + NW + 1 : 1;
   static constexpr int JN = JX * JY * JZ;
   // ... of a deposit CTA's sub-tile (half a tile along the slowest axis)
-  static constexpr int JNS = ND == 3 ? JX * JY * (TZ / EB_SUB + NW + 1) : JX * (TY / EB_SUB + NW + 1);
+  static constexpr int JNS = ND == 3 ? JX * JY * (TZ / EB_SUB + NW + 1) : (ND == 2 ? JX * (TY / EB_SUB + NW + 1) : TX / EB_SUB + NW + 1);
   // register accumulators per component.  3D: the last box slot along the running-sum axis is
   // left out -- the sum has returned to zero there (rounding residue) unless the particle moved
   // up a cell, and then the slot is deposited by a work item (mover_item3, m == A, dcell = +1)
-  static constexpr int NACC = ND == 3 ? (NW - 1) * NW * NW : NW * NW;
+  static constexpr int NACC = ND == 3 ? (NW - 1) * NW * NW : (ND == 2 ? NW * NW : NW);
 };
 
 // deposit record: doubles f1[ND], f3[ND], weight[, v_z] and an int = packed cell shift
@@ -432,7 +432,7 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
 
   boris(ux, uy, uz, ex_part, ey_part, ez_part, bx_part, by_part, bz_part, p.cmratio, p.ccmratio);
 
-  double delta[3] = {0, 0, 0}, part_vz = 0.0;
+  double delta[3] = {0, 0, 0}, part_vy = 0.0, part_vz = 0.0;
 #ifdef EB_EXACT_DIV
   const double gamma_rel = sqrt(ux * ux + uy * uy + uz * uz + 1.0);
   const double igamma3 = 1.0 / gamma_rel;
@@ -442,11 +442,16 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
   if (ND == 3) {
     const double root = p.dtco2 * igamma3;
     delta[0] = ux * root; delta[1] = uy * root; delta[2] = uz * root;
-  } else {
+  } else if (ND == 2) {
     const double igamma = igamma3;
     const double root = p.dtco2 * igamma;
     delta[0] = ux * root; delta[1] = uy * root;
     part_vz = uz * C0 * igamma;
+  } else {          // epoch1d/src/particles.F90:330-340
+    const double root = C0 * igamma3;
+    delta[0] = ux * root * p.dto2;
+    part_vy = uy * root;
+    part_vz = uz * root;
   }
   double posn[3] = {0, 0, 0}, momn[3] = {p.part_mc * ux, p.part_mc * uy, p.part_mc * uz};
 #pragma unroll
@@ -534,6 +539,7 @@ __device__ __forceinline__ bool push_one(const PushP& p, const double* in /* pos
   }
   rec[2 * ND] = part_weight;
   if (ND == 2) rec[2 * ND + 1] = part_vz;
+  if (ND == 1) { rec[3] = part_vy; rec[4] = part_vz; }
   rec_pack = pack | (lc << 8);
   return true;
 }
@@ -576,7 +582,8 @@ __device__ __forceinline__ void mover_overflow(const PushP& p, const R& rec, dou
   const double third = 1.0 / 3.0;
   int nov;
   if (ND == 3) nov = ov[0] * wd[1] * wd[2] + NW * ov[1] * wd[2] + NW * NW * ov[2];
-  else nov = ov[0] * wd[1] + NW * ov[1];
+  else if (ND == 2) nov = ov[0] * wd[1] + NW * ov[1];
+  else nov = ov[0];
   for (int it = lane; it < 3 * nov; it += 32) {
     const int comp = it / nov;
     int q = it - comp * nov;
@@ -586,10 +593,12 @@ __device__ __forceinline__ void mover_overflow(const PushP& p, const R& rec, dou
       if (q < n0) { t[0] = tov[0]; t[1] = tlo[1] + q % wd[1]; t[2] = tlo[2] + q / wd[1]; }
       else if (q < n0 + n1) { q -= n0; t[0] = 1 + q % NW; t[1] = tov[1]; t[2] = tlo[2] + q / NW; }
       else { q -= n0 + n1; t[0] = 1 + q % NW; t[1] = 1 + (q / NW) % NW; t[2] = tov[2]; }
-    } else {
+    } else if (ND == 2) {
       const int n0 = ov[0] * wd[1];
       if (q < n0) { t[0] = tov[0]; t[1] = tlo[1] + q; }
       else { q -= n0; t[0] = 1 + q; t[1] = tov[1]; }
+    } else {
+      t[0] = tov[0];
     }
     double gv[ND], hv[ND], cv[ND];
 #pragma unroll
@@ -607,12 +616,17 @@ __device__ __forceinline__ void mover_overflow(const PushP& p, const R& rec, dou
       const double hQ = Q == 0 ? hv[0] : (Q == 1 ? hv[1] : hv[2]);
       const double fc = A == 0 ? p.fc[0] : (A == 1 ? p.fc[1] : p.fc[2]);
       val = -(fc * w * p.q) * gA * (gP * (gQ + 0.5 * hQ) + hP * (third * hQ + 0.5 * gQ));
-    } else {
+    } else if (ND == 2) {
       const double xf1 = gv[0] + 0.5 * hv[0];
-      const double yf1 = gv[1] + 0.5 * hv[1], yf2 = third * hv[1] + 0.5 * gv[1];
+      const double yf1 = gv[ND - 1] + 0.5 * hv[ND - 1], yf2 = third * hv[ND - 1] + 0.5 * gv[ND - 1];
       if (comp == 0) val = -(p.fc[0] * w * p.q) * cv[0] * yf1;
-      else if (comp == 1) val = -(p.fc[1] * w * p.q) * cv[1] * xf1;
+      else if (comp == 1) val = -(p.fc[1] * w * p.q) * cv[ND - 1] * xf1;
       else val = (p.fc[2] * w * p.q * rec.get(2 * ND + 1)) * (gv[0] * yf1 + hv[0] * yf2);
+    } else {
+      // epoch1d/src/particles.F90:437-457: jx is the running sum, jy / jz carry the velocity
+      const double xf1 = gv[0] + 0.5 * hv[0];
+      if (comp == 0) val = -(p.fc[0] * w * p.q) * cv[0];
+      else val = (p.fc[1] * w * p.q * rec.get(comp == 1 ? 3 : 4)) * xf1;
     }
     const int idx = ((ND >= 3 ? (l[2] + t[2]) : 0) * T::JY + (ND >= 2 ? (l[1] + t[1]) : 0)) * T::JX + l[0] + t[0];
     ovf_add<FX>(sJ + comp * jn + idx, val, fx);
@@ -640,6 +654,21 @@ __device__ __forceinline__ void deposit_box(const PushP& p, const R& rec, int co
     if (ALL || comp == 0) box3<0, NW>(acc, gw, hb, hlo, -(p.fc[0] * wq));
     if (ALL || comp == 1) box3<1, NW>(acc + (ALL ? NA : 0), gw, hb, hlo, -(p.fc[1] * wq));
     if (ALL || comp == 2) box3<2, NW>(acc + (ALL ? 2 * NA : 0), gw, hb, hlo, -(p.fc[2] * wq));
+  } else if (ND == 1) {
+    // epoch1d/src/particles.F90:437-457
+    if (ALL || comp == 0) {
+      double c = hlo[0];
+#pragma unroll
+      for (int i = 0; i < NW; ++i) { c += hb[0][i]; acc[i] += -(p.fc[0] * wq) * c; }
+    }
+#pragma unroll
+    for (int k = 1; k < 3; ++k) {
+      if (!(ALL || comp == k)) continue;
+      double* ak = acc + (ALL ? k * NA : 0);
+      const double fj = p.fc[1] * wq * rec.get(2 + k);      // fcy * q * part_vy | part_vz
+#pragma unroll
+      for (int i = 0; i < NW; ++i) ak[i] += fj * (gw[0][i] + 0.5 * hb[0][i]);
+    }
   } else {
     const double third = 1.0 / 3.0;
     if (ALL || comp == 0) {          // Jx = -fjx * cumsum_x(hx) * (gy + hy/2)
@@ -649,15 +678,15 @@ __device__ __forceinline__ void deposit_box(const PushP& p, const R& rec, int co
         c += hb[0][i];
         const double ca = -(p.fc[0] * wq) * c;
 #pragma unroll
-        for (int j = 0; j < NW; ++j) acc[j * NW + i] += ca * (gw[1][j] + 0.5 * hb[1][j]);
+        for (int j = 0; j < NW; ++j) acc[j * NW + i] += ca * (gw[ND - 1][j] + 0.5 * hb[ND - 1][j]);
       }
     }
     if (ALL || comp == 1) {          // Jy = -fjy * cumsum_y(hy) * (gx + hx/2)
       double* ay = acc + (ALL ? NA : 0);
-      double c = hlo[1];
+      double c = hlo[ND - 1];
 #pragma unroll
       for (int j = 0; j < NW; ++j) {
-        c += hb[1][j];
+        c += hb[ND - 1][j];
         const double ca = -(p.fc[1] * wq) * c;
 #pragma unroll
         for (int i = 0; i < NW; ++i) ay[j * NW + i] += ca * (gw[0][i] + 0.5 * hb[0][i]);
@@ -668,7 +697,7 @@ __device__ __forceinline__ void deposit_box(const PushP& p, const R& rec, int co
       const double fjz = p.fc[2] * wq * rec.get(2 * ND + 1);
 #pragma unroll
       for (int j = 0; j < NW; ++j) {
-        const double yf1 = gw[1][j] + 0.5 * hb[1][j], yf2 = third * hb[1][j] + 0.5 * gw[1][j];
+        const double yf1 = gw[ND - 1][j] + 0.5 * hb[ND - 1][j], yf2 = third * hb[ND - 1][j] + 0.5 * gw[ND - 1][j];
 #pragma unroll
         for (int i = 0; i < NW; ++i) az[j * NW + i] += fjz * (gw[0][i] * yf1 + hb[0][i] * yf2);
       }
@@ -940,7 +969,7 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   constexpr int NW = T::NW, SFM = T::SFM, NA = T::NACC, NTB = T::CPT / SUB;
   constexpr int SA = ND - 1;                                   // split axis
   constexpr int TS = tile_dim(ND, SA) / SUB;                   // cells of the sub-tile along it
-  constexpr int JXs = T::JX, JYs = ND == 3 ? T::JY : TS + NW + 1, JZs = ND == 3 ? TS + NW + 1 : 1;
+  constexpr int JXs = ND == 1 ? TS + NW + 1 : T::JX, JYs = ND == 3 ? T::JY : (ND == 2 ? TS + NW + 1 : 1), JZs = ND == 3 ? TS + NW + 1 : 1;
   constexpr int JNs = JXs * JYs * JZs;
   extern __shared__ double smem[];
   double* sJ = smem;                          // [3][JNs] (DET: + [3][JNs] fixed-point overflow sums)
@@ -975,6 +1004,7 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
     const double wm = __longlong_as_double((long long)*reinterpret_cast<unsigned long long*>(sCnt + 2));
     double fcm = fmax(fabs(p.fc[0]), fabs(p.fc[1]));
     fcm = fmax(fcm, fabs(p.fc[2]) * (ND == 2 ? C0 : 1.0));
+    if (ND == 1) fcm = fmax(fabs(p.fc[0]), fabs(p.fc[1]) * C0);
     const double S = fmax(wm * fabs(p.q) * fcm, 1e-300);
     int ex;
     frexp(S, &ex);                                  // S < 2^ex
@@ -1049,10 +1079,10 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
     slot = slot == RING - 1 ? 0 : slot + 1;
     deposit_box<ND, SHAPE, !ONEC>(p, RecR{cur}, pass, acc);
     const int pack = (int)__double_as_longlong(cur[7]);
-    if (pass == 0 && (pack & 0xff) != (ND == 3 ? 0x15 : 0x5)) {
+    if (pass == 0 && (pack & 0xff) != (ND == 3 ? 0x15 : (ND == 2 ? 0x5 : 0x1))) {
       const RecG rec{scratch + (size_t)(q - base) * 8};
       const int r = (int)(q - pb);
-      if (ND == 2) {
+      if (ND <= 2) {
         const int slot = atomicAdd(sCnt, 1);
         if (slot < MCAPB) sM[2 * slot] = r;
         else for (int ln = 0; ln < 32; ++ln) mover_overflow<ND, SHAPE, RecG, DET>(p, rec, sJ, ln, JNs, sub * TS, fx);   // list full
@@ -1076,8 +1106,12 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
   // planes and share a step.
   constexpr bool ZPAIR = ND == 3 && TS == 2 && NW == 3;
   auto box_step = [&](int dx, int dy, int dz) {
-    const int off = (l[0] + 1 + dx) + (l[1] + 1 + dy) * JXs + (ND == 3 ? (l[2] + 1 + dz) * JXs * JYs : 0);
-    if (ND == 3) {
+    const int off = (l[0] + 1 + dx) + (ND >= 2 ? (l[1] + 1 + dy) * JXs : 0) + (ND == 3 ? (l[2] + 1 + dz) * JXs * JYs : 0);
+    if (ND == 1) {
+      sJ[off] += acc[dx];
+      sJ[JNs + off] += acc[NA + dx];
+      sJ[2 * JNs + off] += acc[2 * NA + dx];
+    } else if (ND == 3) {
       // component A: acc[(o[Q] * NW + o[P]) * (NW - 1) + o[A]], P = A + 1, Q = A + 2, o[A] < NW - 1
       if ((!ONEC || pass == 0) && dx < NW - 1) sJ[off] += acc[(dz * NW + dy) * (NW - 1) + dx];
       if ((!ONEC || pass == 1) && dy < NW - 1) sJ[JNs + off] += acc[(ONEC ? 0 : NA) + (dx * NW + dz) * (NW - 1) + dy];
@@ -1091,7 +1125,7 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
 #pragma unroll
   for (int dz = 0; dz < (ND == 3 ? (ZPAIR ? 2 : NW) : 1); ++dz)
 #pragma unroll
-    for (int dy = 0; dy < NW; ++dy)
+    for (int dy = 0; dy < (ND >= 2 ? NW : 1); ++dy)
 #pragma unroll
       for (int dx = 0; dx < NW; ++dx) {
         box_step(dx, dy, dz);
@@ -1121,7 +1155,16 @@ __global__ void __launch_bounds__(TL<ND, SHAPE>::CPT / SUB, EB_MINB_B) k_deposit
       out[i] = sJ[i] + (double)__double_as_longlong(sJ[3 * JNs + i]) * unit;
     return;
   }
-  // tile J -> HBM (RED.ADD.F64: tile halos overlap): thread per (component, y, z) row, walking x
+  // tile J -> HBM (RED.ADD.F64: tile halos overlap): thread per (component, y, z) row, walking x (1D: thread per value)
+  if (ND == 1) {
+    for (int i = tid; i < 3 * JXs; i += NTB) {
+      const int cj = i / JXs, jx = i - cj * JXs;
+      const int X = org[0] + jx;
+      const double v = sJ[cj * JNs + jx];
+      if (v != 0.0 && X >= 1 - g.ngd[0] && X <= g.n[0] + g.ngd[0]) atomicAdd(F.f[JX + cj] + g.idx(X, 1, 1), v);
+    }
+    return;
+  }
   for (int row = tid; row < 3 * JYs * JZs; row += NTB) {
     const int cj = row / (JYs * JZs), r = row - cj * (JYs * JZs);
     const int jy = r % JYs, jz = r / JYs;
@@ -1149,16 +1192,17 @@ __global__ void k_reduce_tiles(GridP g, FieldP F, const uint32_t* __restrict__ c
   using T = TL<ND, SHAPE>;
   constexpr int NW = T::NW, SFM = T::SFM, NTB = T::CPT / SUB, SA = ND - 1;
   constexpr int TS = tile_dim(ND, SA) / SUB;
-  constexpr int JXs = T::JX, JYs = ND == 3 ? T::JY : TS + NW + 1, JZs = ND == 3 ? TS + NW + 1 : 1;
+  constexpr int JXs = ND == 1 ? TS + NW + 1 : T::JX, JYs = ND == 3 ? T::JY : (ND == 2 ? TS + NW + 1 : 1), JZs = ND == 3 ? TS + NW + 1 : 1;
   constexpr int JNs = JXs * JYs * JZs;
   const int ex = g.n[0] + 2 * g.ngd[0], ey = ND >= 2 ? g.n[1] + 2 * g.ngd[1] : 1;
   const long long planes = (long long)(hi - lo + 1);
-  const long long per_plane = ND == 3 ? (long long)ex * ey : ex;
+  const long long per_plane = ND == 3 ? (long long)ex * ey : (ND == 2 ? ex : 1);
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= planes * per_plane) return;
   int X[3] = {1, 1, 1};
-  X[0] = 1 - g.ngd[0] + (int)(i % ex);
-  if (ND == 3) { X[1] = 1 - g.ngd[1] + (int)((i / ex) % ey); X[2] = lo + (int)(i / per_plane); }
+  X[0] = ND == 1 ? lo + (int)i : 1 - g.ngd[0] + (int)(i % ex);
+  if (ND == 1) {
+  } else if (ND == 3) { X[1] = 1 - g.ngd[1] + (int)((i / ex) % ey); X[2] = lo + (int)(i / per_plane); }
   else X[1] = lo + (int)(i / per_plane);
   // candidate (sub-)tile ranges per axis: origin(u) = b0 + u * stride <= X <= origin(u) + extent - 1
   int u_lo[3] = {0, 0, 0}, u_hi[3] = {0, 0, 0};
@@ -1266,7 +1310,7 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
   *handled = false;
   KeySink ks;
   if (keysink) ks = *(const KeySink*)keysink; else { ks.on = 0; ks.count = nullptr; ks.nbucket = 0; ks.mig_axis = -1; }
-  if (c->ndims < 2 || !sp.sorted || !sp.h_tile_start) return 0;
+  if (!sp.sorted || !sp.h_tile_start) return 0;
   // deferred permute: read the pre-sort order through src, write the sorted order into the other state
   const bool gather = sp.deferred;
   bool fwd = true;
@@ -1326,7 +1370,8 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
   const long long scratch_slab = overlap ? c->rec_scratch_cap / 2 : c->rec_scratch_cap;
   const long long cap = scratch_slab < room ? scratch_slab : room;
   const int jn3[3] = {TL<3, 0>::JN, TL<3, 1>::JN, TL<3, 2>::JN}, jn2[3] = {TL<2, 0>::JN, TL<2, 1>::JN, TL<2, 2>::JN};
-  const size_t tile_doubles = 3 * (size_t)(c->ndims == 3 ? jn3[c->shape] : jn2[c->shape]);   // >= the sub-tile's
+  const int jn1[3] = {TL<1, 0>::JN, TL<1, 1>::JN, TL<1, 2>::JN};
+  const size_t tile_doubles = 3 * (size_t)(c->ndims == 3 ? jn3[c->shape] : (c->ndims == 2 ? jn2[c->shape] : jn1[c->shape]));   // >= the sub-tile's
   const long long max_tiles = det ? std::max<long long>(1, (long long)(((size_t)1 << 30) / (tile_doubles * 8 * SUB))) : (1LL << 62);
   if (det && c->det_tiles_cap < (size_t)std::min<long long>(max_tiles, ntiles) * SUB * tile_doubles) {
     if (c->det_tiles) { EB_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(c->det_tiles); }
@@ -1371,13 +1416,13 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
         if (overlap) cudaEventRecord(c->ev_dep[is & 1], sdep);                                             \
         if (det) {                                                                                         \
           /* planes of the slowest axis that the tiles [t0, t1) can reach */                              \
-          const long long per_layer = ND == 3 ? (long long)c->g.ntile[0] * c->g.ntile[1] : c->g.ntile[0];  \
+          const long long per_layer = ND == 3 ? (long long)c->g.ntile[0] * c->g.ntile[1] : (ND == 2 ? c->g.ntile[0] : 1);  \
           const int TDS = tile_dim(ND, ND - 1);                                                            \
           int lo = (1 - KM) + (int)(t0 / per_layer) * TDS + TL<ND, SH>::SFM - 1;                           \
           int hi = (1 - KM) + (int)((t1 - 1) / per_layer) * TDS + TL<ND, SH>::SFM - 1 + TDS + TL<ND, SH>::NW; \
           lo = std::max(lo, 1 - c->g.ngd[ND - 1]); hi = std::min(hi, c->g.n[ND - 1] + c->g.ngd[ND - 1]);   \
           if (hi >= lo) {                                                                                  \
-            const long long cells = (long long)(hi - lo + 1) * (c->g.n[0] + 2 * c->g.ngd[0]) *             \
+            const long long cells = (long long)(hi - lo + 1) * (ND >= 2 ? c->g.n[0] + 2 * c->g.ngd[0] : 1) * \
                                     (ND == 3 ? (c->g.n[1] + 2 * c->g.ngd[1]) : 1);                         \
             k_reduce_tiles<ND, SH><<<(unsigned)((cells + 255) / 256), 256, 0, c->stream>>>(c->g, c->f, sp.cell_start, t0, t1, \
                                                                                            c->det_tiles, lo, hi);           \
@@ -1385,7 +1430,7 @@ int32_t launch_push_split(eb200_ctx* c, SpeciesD& sp, const PushP& p, bool* hand
           }                                                                                                \
         } }                                                                                                \
     }
-    L(2, 0) L(2, 1) L(2, 2) L(3, 0) L(3, 1) L(3, 2)
+    L(1, 0) L(1, 1) L(1, 2) L(2, 0) L(2, 1) L(2, 2) L(3, 0) L(3, 1) L(3, 2)
 #undef L
     c->launches += p.zero_current ? 1 : 2;
   }

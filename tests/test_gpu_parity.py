@@ -228,9 +228,18 @@ def test_error_behaviour(product_abi):
     with pytest.raises(EpochError):
         c.set_field_bcs(["cpml_laser", "periodic", "periodic", "periodic"])
     with pytest.raises(EpochError):
-        c.set_species(0, -Q0, M0, bcs=["thermal", "thermal", "periodic", "periodic"])
+        c.set_species(0, -Q0, M0, bcs=["dump", "dump", "periodic", "periodic"])      # not a particle boundary
     with pytest.raises(EpochError):
-        c.upload_particles(0, np.zeros((1, 6)))   # species not defined
+        c.set_species(0, -Q0, M0, bcs=["periodic", "reflect", "periodic", "periodic"])   # periodic on one side only
+    with pytest.raises(EpochError):
+        c.upload_particles(1, np.zeros((1, 6)))   # species not defined
+    # a thermal wall without its temperature table is refused when the particles reach it
+    c.set_species(0, -Q0, M0, bcs=["thermal", "thermal", "periodic", "periodic"])
+    c.set_field_bcs(["clamp", "clamp", "periodic", "periodic"])
+    c.set_time(1e-16, 0.0, 0)
+    c.upload_particles(0, np.array([[4e-6, 4e-6, 0.0, 0.0, 0.0, 1.0]]))
+    with pytest.raises(EpochError, match="thermal"):
+        c.particle_bcs()
 
 
 # ---- extended-stencil Maxwell solvers (fields.f90:53-179, :655-732) -----------------------------
@@ -433,7 +442,9 @@ def test_redistribute_single_rank_identity(product_abi, oracle_abi):
     (2, "triangle", "periodic", [32, 64], 6000, True), (2, "tophat", "reflect", [32, 64], 7000, True),
     (3, "triangle", "open", [16, 8, 48], 8000, True), (3, "triangle", "periodic", [16, 8, 48], 600, False),
     (3, "triangle", "periodic", [16, 8, 48], "auto", True), (3, "triangle", "periodic", [16, 8, 48], 0, False),
-    (3, "bspline3", "periodic", [16, 8, 48], 9000, True), (2, "bspline3", "open", [32, 64], 7000, True)])
+    (3, "bspline3", "periodic", [16, 8, 48], 9000, True), (2, "bspline3", "open", [32, 64], 7000, True),
+    (1, "triangle", "periodic", [1500], 5000, True), (1, "tophat", "reflect", [1500], 5000, True),
+    (1, "bspline3", "open", [1500], 5000, True)])
 def test_deferred_permute(product_abi, oracle_abi, ndims, shape, pbc, n, window, expect):
     """The sort leaves its permute to the next push (gather through src, write into the other state of the
     arrays).  A window far smaller than the species forces many launches per step in both directions and,
@@ -462,12 +473,14 @@ def test_deferred_permute(product_abi, oracle_abi, ndims, shape, pbc, n, window,
 @pytest.mark.gpu
 @pytest.mark.parametrize("ndims,shape,pbc,window", [(3, "triangle", "periodic", "auto"), (3, "tophat", "reflect", 0),
                                                     (2, "triangle", "periodic", "auto"), (2, "tophat", "open", 4000),
-                                                    (3, "bspline3", "periodic", "auto"), (2, "bspline3", "reflect", "auto")])
+                                                    (3, "bspline3", "periodic", "auto"), (2, "bspline3", "reflect", "auto"),
+                                                    (1, "triangle", "periodic", "auto"), (1, "tophat", "open", 3000),
+                                                    (1, "bspline3", "reflect", "auto")])
 def test_deterministic_deposit(product_abi, oracle_abi, ndims, shape, pbc, window):
     """option deterministic_deposit: two runs of the same deck give bitwise identical currents, fields and
     particle arrays (canonical order inside a cell, fixed-point overflow sums, ordered sum of the tile
     halos), and they still equal the oracle within the usual tolerance."""
-    n = [24, 16, 12] if ndims == 3 else [40, 48]
+    n = [24, 16, 12] if ndims == 3 else ([40, 48] if ndims == 2 else [1200])
     bcs = [pbc] * (2 * ndims)
     fbc = ["periodic" if pbc == "periodic" else "clamp"] * (2 * ndims)
     opts = {"deterministic_deposit": 1, "defer_window": window, "deposit_scratch": 4096}
@@ -486,16 +499,16 @@ def test_deterministic_deposit(product_abi, oracle_abi, ndims, shape, pbc, windo
         assert np.array_equal(a.ctx.download_particles(isp), b.ctx.download_particles(isp))
     compare_fields(a, o, ALL9, tol=1e-10)
     compare_particles(a, o, tol=1e-10)
-    # not on the general kernel (1D)
+    # not on the general kernel
     if ndims == 3:
-        s = make_plasma(product_abi, 1, "triangle", [32], seed=1, ppc=2, options={"deterministic_deposit": 1})
+        s = make_plasma(product_abi, 1, "triangle", [32], seed=1, ppc=2, options={"deterministic_deposit": 1, "push_kernel": "baseline"})
         with pytest.raises(Exception):
             s.step_once()
 
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("ndims,shape,n,ppc", [(2, "triangle", [32, 32], 70), (3, "triangle", [8, 8, 8], 70),
-                                               (2, "bspline3", [16, 32], 80)])
+                                               (2, "bspline3", [16, 32], 80), (1, "triangle", [600], 90)])
 def test_dense_tiles(product_abi, oracle_abi, ndims, shape, n, ppc):
     """tiles with more than PUSH_CHUNK (16384) particles are pushed by several CTAs; dense cells overflow the
     deposit's work-item list (inline path): same answers as the oracle"""
