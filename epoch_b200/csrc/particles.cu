@@ -42,7 +42,19 @@ int32_t species_reserve(eb200_ctx* c, SpeciesD& sp, long long need, bool exact) 
   if (sp.base[6] && need + sp.win + 2 * sp.gap <= sp.cap) return 0;
   EB_TRY(settle_species(c, sp));
   const bool tiled = c->push_kernel != 1;
-  long long win = !tiled ? 0 : (c->defer_window >= 0 ? c->defer_window : std::max<long long>(need / 8, 1 << 16));
+  // "auto" head room of the deferred permute: an eighth of the species, and at least 4.5 layers of tiles along the
+  // slowest axis -- a particle that crosses a tile boundary along that axis moves by one layer of tiles in the sorted
+  // order and the displacement limit is a quarter of the window (on a thin z slab of a big x-y face, the strong-
+  // scaling cut, a layer is a large part of the species: 512 x 512 x 64 cells at 16 ppc = 16.7 M of 268 M particles)
+  long long win_auto = std::max<long long>(need / 8, 1 << 16);
+  if (c->grid_set && c->g.ncell_ext > 0) {
+    const GridP& g = c->g;
+    const double cells = (double)g.n[0] * g.n[1] * g.n[2];
+    const double layer = (double)g.ncell_ext / (double)std::max(1, g.ntile[c->ndims - 1]) * ((double)need / std::max(cells, 1.0));
+    win_auto = std::max<long long>(win_auto, (long long)(4.5 * layer));
+    win_auto = std::min<long long>(win_auto, std::max<long long>(need, 1 << 16));
+  }
+  long long win = !tiled ? 0 : (c->defer_window >= 0 ? c->defer_window : win_auto);
   const long long gap = 0;      // (slots kept free below the low state: none needed, arrivals are appended)
   const long long body = exact ? std::max<long long>(need, 1024) : std::max<long long>(need + need / 32 + 1024, 4096);
   const long long ncap = body + win + 2 * gap;
