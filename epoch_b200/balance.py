@@ -1,6 +1,7 @@
-"""Host side of the dynamic load balancer: the decision logic of
-housekeeping/balance.F90 restated (it works on a few hundred integers and stays on the
-host in the integration as well); the device side is eb200_get_load / eb200_redistribute.
+"""HARNESS, not product: the decision logic of housekeeping/balance.F90 restated so that the Python
+driver mirror, the tests and tools/ can drive eb200_get_load / eb200_redistribute the way
+balance_workload does.  In the integration this logic stays in the Fortran host (it works on a few
+hundred integers) and nothing in the CUDA library depends on this file.
 
 calculate_breaks follows balance.F90:2526-2669 statement by statement, including the way
 load_max / load_min carry over between the perturbation sweeps."""
