@@ -15,7 +15,8 @@ particle_bcs + re-sort), current_finish, update_eb_fields_final -- all of it ins
 the timed region.  `value` = particles x steps / device time (CUDA events on the
 library's stream, max over ranks) with the state resident in HBM; `e2e` = the same
 through the C ABI from HOST buffers: upload of all particles and fields, K steps,
-download of all particles and fields, wall clock.
+download of all particles and fields, wall clock (the context with its NCCL
+communicator is created before the clock starts and timed apart).
 
 N > 1 (torchrun): the line printed is STRONG scaling -- the same global 512^3 box cut into N slabs
 of 512 x 512 x 512/N along z (`"scaling": "strong"`, e2e on that same deck) -- and a key `weak` holds
