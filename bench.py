@@ -356,10 +356,16 @@ def run_ours(args):
             host_all = sim.ctx.host_empty((planes * per_plane + planes * per_plane // 64, 7))
             host = host_all[:planes * per_plane]
             t_gen = 0.0
+            # (the extra weak-scaling run of an N > 1 invocation generates its first chunk of planes and uploads
+            #  z-shifted copies of it for the others: the same uniform / Maxwellian statistics, minutes less numpy)
+            replicate = mode == "weak" and not want_e2e
             for k0 in range(0, nz_local, planes):
                 k1 = min(nz_local, k0 + planes)
                 tg = time.perf_counter()
-                fill_particles(host, sim, args.seed, gen_threads, k0, k1)
+                if k0 == 0 or not replicate or k1 - k0 != planes:
+                    fill_particles(host, sim, args.seed, gen_threads, k0, k1)
+                else:
+                    host[:, 2] += planes * sim.d[2]
                 t_gen += time.perf_counter() - tg
                 sim.ctx.upload_particles(0, host[:(k1 - k0) * per_plane], append=k0 > 0)
         sim.ctx.sync()
