@@ -789,7 +789,9 @@ static int32_t thermal_bcs(eb200_ctx* c, SpeciesD& sp, long long n_slots) {
     t.refl_min[d] = b.min_bnd && !b.cpml_min && b.bc_min == EB200_BC_REFLECT; t.refl_max[d] = b.max_bnd && !b.cpml_max && b.bc_max == EB200_BC_REFLECT;
   }
   if (!any || n_slots <= 0) return 0;
-  t.nd = c->ndims; t.ng = c->ng; t.sigma2 = KB * sp.mass; t.seed = sp.thermal_seed; t.call = sp.thermal_calls++;
+  // (the rank enters the key: ranks handed the same seed must not draw the same deviates for the same slot and call)
+  t.nd = c->ndims; t.ng = c->ng; t.sigma2 = KB * sp.mass;
+  t.seed = sp.thermal_seed ^ ((unsigned long long)c->rank * 0xA0761D6478BD642FULL); t.call = sp.thermal_calls++;
   k_thermal_bc<<<(unsigned)((n_slots + 255) / 256), 256, 0, c->stream>>>(t, n_slots, sp.a[0], sp.a[1], sp.a[2], sp.a[3], sp.a[4], sp.a[5],
                                                                        sp.key, c->d_counters);
   c->launches++;
