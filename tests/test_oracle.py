@@ -277,3 +277,86 @@ def test_filter_passes_strides_and_correction(oracle_abi):
     b = s0.ctx.download_fields(["jx", "jy", "jz"])
     for k, v in zip(("jx", "jy", "jz"), (0.25, -1.5, 3.0)):
         assert np.array_equal(a[k], b[k] - v)
+
+
+# ---- the Yee staggering of the gather (include/*/e_part.inc, b_part.inc): linear fields ---------------------
+# B-spline weights reproduce linear functions exactly, so a field component that is a linear function of position,
+# sampled at ITS OWN Yee locations (ex at x + dx/2; ey at y + dy/2; ez at z + dz/2; bx at y + dy/2, z + dz/2; by at
+# x + dx/2, z + dz/2; bz at x + dx/2, y + dy/2 -- the locations the curl stencils of fields.f90:192-310 imply), must be
+# gathered exactly at any particle position.  A gather that read a component with the wrong stagger would be off by
+# half a cell times the gradient.
+STAGGER = {"ex": (1, 0, 0), "ey": (0, 1, 0), "ez": (0, 0, 1), "bx": (0, 1, 1), "by": (1, 0, 1), "bz": (1, 1, 0)}
+GRAD = {"ex": (0.31, -0.23, 0.17), "ey": (-0.11, 0.29, 0.37), "ez": (0.41, 0.13, -0.19),
+        "bx": (0.27, 0.33, -0.21), "by": (-0.35, 0.15, 0.25), "bz": (0.19, -0.39, 0.23)}
+
+
+def linear_field(sim, comp, amp):
+    """array incl. ghosts of amp * (1 + grad . r / L) sampled at the component's Yee locations"""
+    nd, ng = sim.ndims, sim.ctx.ng
+    coords = []
+    for d in range(nd):
+        i = np.arange(sim.n_local[d] + 2 * ng)
+        coords.append(sim.grid_min_local[d] + (i - ng + 0.5 * STAGGER[comp][d]) * sim.d[d])
+    grids = np.meshgrid(*coords[::-1], indexing="ij")[::-1]        # grids[d] has the array's C-order shape
+    f = np.ones(grids[0].shape)
+    for d in range(nd):
+        f = f + GRAD[comp][d] * grids[d] / sim.length[d]
+    return amp * f
+
+
+def linear_value(sim, comp, amp, pos):
+    v = np.ones(len(pos))
+    for d in range(sim.ndims):
+        v = v + GRAD[comp][d] * pos[:, d] / sim.length[d]
+    return amp * v
+
+
+def check_linear_gather(abi, ndims, shape, tol=2e-12):
+    n = [14, 12, 10][:ndims]
+    cell = 1.0e-3
+    sp = SpeciesSpec("electron", -Q0, M0)
+    rng = np.random.default_rng(17)
+    npart = 200
+    for comp in STAGGER:
+        sim = Simulation(ndims, n, [0.0] * ndims, [cell * x for x in n], shape=shape, species=[sp], abi=abi)
+        amp = 1.0e3 if comp[0] == "e" else 2.0e-2
+        sim.ctx.upload_fields(**{comp: linear_field(sim, comp, amp)})
+        P = np.zeros((npart, ndims + 4))
+        for d in range(ndims):
+            P[:, d] = rng.uniform(3.0 * cell, (n[d] - 3.0) * cell, npart)
+        P[:, ndims + 3] = 1.0 + np.arange(npart) * 1e-3
+        a = "xyz".index(comp[1])
+        b, c = (a + 1) % 3, (a + 2) % 3
+        u0 = 0.02
+        if comp[0] == "b":
+            P[:, ndims + b] = u0 * M0 * C
+        sim.ctx.upload_particles(0, P)
+        sim.ctx.set_time(sim.dt, 0.0, 0)
+        sim.ctx.push_particles()
+        Q = sim.ctx.download_particles(0)
+        P, Q = P[np.argsort(P[:, -1])], Q[np.argsort(Q[:, -1])]
+        if comp[0] == "e":
+            # u = 0, B = 0: p(t + dt) = q E(x) dt, gathered at x itself (no half drift without momentum)
+            got = Q[:, ndims + a] / (-Q0 * sim.dt)
+            want = linear_value(sim, comp, amp, P[:, :ndims])
+            assert np.max(np.abs(Q[:, ndims + b])) == 0.0 and np.max(np.abs(Q[:, ndims + c])) == 0.0
+        else:
+            # E = 0: the Boris rotation about axis a by -2 atan(tau), tau = q B dt / (2 gamma m), B gathered at x + v dt/2
+            gamma = math.sqrt(1.0 + u0 ** 2)
+            xh = P[:, :ndims].copy()
+            if b < ndims:
+                xh[:, b] += (u0 * C / gamma) * sim.dt / 2.0
+            ang = np.arctan2(Q[:, ndims + c], Q[:, ndims + b])
+            got = np.tan(-ang / 2.0) * (2.0 * gamma * M0) / (-Q0 * sim.dt)
+            want = linear_value(sim, comp, amp, xh)
+            assert np.max(np.abs(np.hypot(Q[:, ndims + b], Q[:, ndims + c]) / (u0 * M0 * C) - 1.0)) < 1e-13
+        err = np.max(np.abs(got / want - 1.0))
+        half_cell = 0.5 * max(abs(GRAD[comp][d]) / n[d] for d in range(ndims))     # what a wrong stagger would cost
+        assert err < tol and tol < 1e-6 * half_cell, (comp, err)
+        sim.ctx.close()
+
+
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_gather_staggering_linear_fields(oracle_abi, ndims, shape):
+    check_linear_gather(oracle_abi, ndims, shape)
