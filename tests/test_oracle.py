@@ -360,3 +360,67 @@ def check_linear_gather(abi, ndims, shape, tol=2e-12):
 @pytest.mark.parametrize("shape", SHAPE_NAMES)
 def test_gather_staggering_linear_fields(oracle_abi, ndims, shape):
     check_linear_gather(oracle_abi, ndims, shape)
+
+
+# ---- particle_bcs (boundary.F90:1316-1972): what any correct restatement must do, checked on placed particles ----
+def check_particle_bcs(abi, ndims):
+    """periodic: wrapped by the box length; reflect: mirrored at the boundary with the normal momentum reversed, removed
+    beyond the outer edge (x_min - dx * ((1 + png) / 2), :1336-1338, :1404, :1455-1458); open: kept in the ghost strip,
+    removed beyond the outer edge; the min side tests <, the max side >= (:1390, :1478)"""
+    n = [10, 8, 6][:ndims]
+    cell = 1.0e-6
+    L = [cell * x for x in n]
+    shift = 2.0 * cell                     # triangle: png = 3 -> (1 + 3) / 2 = 2 cells
+    for pbc in ("periodic", "reflect", "open"):
+        fbc = ["periodic" if pbc == "periodic" else "clamp"] * (2 * ndims)
+        sp = SpeciesSpec("electron", -Q0, M0, bcs=[pbc] * (2 * ndims))
+        sim = Simulation(ndims, n, [0.0] * ndims, L, shape="triangle", species=[sp], abi=abi, bc_field=fbc)
+        rows, expect = [], []
+        mid = [0.37 * x for x in L]
+        w = [1.0]
+
+        def put(pos, mom, exp):
+            rows.append(list(pos) + list(mom) + [w[0]])
+            expect.append(None if exp is None else list(exp[0]) + list(exp[1]) + [w[0]])
+            w[0] += 1.0
+        for d in range(ndims):
+            lo, hi = sim.min_local[d], sim.max_local[d]          # what the tests are made against (x_min_local, x_max_local)
+            gmin, gmax = sim.mins[d], sim.maxs[d]                # what reflection and wrap are made with (x_min, x_max)
+            bs = sim.d[d] * float((1 + 3) // 2)
+            wrap = gmax - gmin
+            for x in (lo - 0.4 * cell, lo - shift - 0.3 * cell, hi + 0.4 * cell, hi + shift + 0.3 * cell, hi, lo,
+                      np.nextafter(lo, -1.0), np.nextafter(hi, -1.0)):
+                pos = list(mid); pos[d] = x
+                mom = [1e-24, -2e-24, 3e-24]
+                beyond = x < gmin - bs or x >= gmax + bs
+                below, above = x < lo, x >= hi
+                if pbc == "periodic":
+                    q = list(pos); q[d] = x + wrap if below else (x - wrap if above else x)
+                    put(pos, mom, (q, mom))
+                elif pbc == "reflect":
+                    if beyond:
+                        put(pos, mom, None)
+                    elif below or above:
+                        q = list(pos); q[d] = 2.0 * (gmin if below else gmax) - x
+                        m2 = list(mom); m2[d] = -m2[d]
+                        put(pos, mom, (q, m2))
+                    else:
+                        put(pos, mom, (pos, mom))
+                else:
+                    put(pos, mom, None if beyond else (pos, mom))
+        P = np.array(rows)
+        sim.ctx.upload_particles(0, P)
+        sim.ctx.set_time(sim.dt, 0.0, 0)
+        sim.ctx.particle_bcs()
+        Q = sim.ctx.download_particles(0)
+        want = np.array([e for e in expect if e is not None])
+        assert len(Q) == len(want), (pbc, len(Q), len(want))
+        Q, want = Q[np.argsort(Q[:, -1])], want[np.argsort(want[:, -1])]
+        assert np.array_equal(Q[:, ndims:], want[:, ndims:]), pbc
+        assert np.array_equal(Q[:, :ndims], want[:, :ndims]), pbc
+        sim.ctx.close()
+
+
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+def test_particle_bcs_known_answers(oracle_abi, ndims):
+    check_particle_bcs(oracle_abi, ndims)
