@@ -424,3 +424,42 @@ def check_particle_bcs(abi, ndims):
 @pytest.mark.parametrize("ndims", [1, 2, 3])
 def test_particle_bcs_known_answers(oracle_abi, ndims):
     check_particle_bcs(oracle_abi, ndims)
+
+
+# ---- the deposit's normalisation, also for the components charge conservation does not see --------------------
+def check_total_current(abi, ndims, shape, tol=1e-12):
+    """Sum over the grid of J dV = sum over particles of q w v (v from the momentum the push leaves): for the components
+    along existing axes this follows from continuity, for the ignorable ones (jy, jz in 1D; jz in 2D:
+    `fjy = fcy * part_q * part_vy`, epoch1d/src/particles.F90:431-433; epoch2d `fjz`) it is the only pin on
+    their factor and sign."""
+    n = [12, 10, 8][:ndims]
+    cell = 2.0e-6
+    sp = [SpeciesSpec("electron", -Q0, M0), SpeciesSpec("proton", Q0, 1836.2 * M0)]
+    sim = Simulation(ndims, n, [0.0] * ndims, [cell * x for x in n], shape=shape, species=sp, abi=abi)
+    rng = np.random.default_rng(29)
+    want = np.zeros(3)
+    for isp, s in enumerate(sp):
+        m = 40
+        P = np.zeros((m, ndims + 4))
+        for d in range(ndims):
+            P[:, d] = rng.uniform(sim.min_local[d], sim.max_local[d], m)
+        u = rng.normal(0.0, 0.8, (m, 3))
+        P[:, ndims:ndims + 3] = u * s.mass * C
+        P[:, ndims + 3] = rng.uniform(0.5, 1.5, m) * 1e10
+        sim.ctx.upload_particles(isp, P)
+        gamma = np.sqrt(1.0 + np.sum(u * u, axis=1))
+        want += s.charge * np.sum(P[:, ndims + 3, None] * (u * C / gamma[:, None]), axis=0)
+    sim.ctx.set_time(sim.dt, 0.0, 0)
+    sim.ctx.push_particles()                      # E = B = 0: the momenta stay as loaded
+    j = sim.ctx.download_fields(("jx", "jy", "jz"))
+    dv = float(np.prod(sim.d))
+    got = np.array([j[k].sum() * dv for k in ("jx", "jy", "jz")])
+    scale = np.max(np.abs(want))
+    assert np.max(np.abs(got - want)) < tol * scale, (got, want)
+    sim.ctx.close()
+
+
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_total_current_equals_sum_q_w_v(oracle_abi, ndims, shape):
+    check_total_current(oracle_abi, ndims, shape)
