@@ -463,3 +463,43 @@ def check_total_current(abi, ndims, shape, tol=1e-12):
 @pytest.mark.parametrize("shape", SHAPE_NAMES)
 def test_total_current_equals_sum_q_w_v(oracle_abi, ndims, shape):
     check_total_current(oracle_abi, ndims, shape)
+
+
+# ---- the shape weights themselves (include/{tophat,triangle,bspline3}/gx.inc, hx_dcell.inc): polynomial moments -----
+# The interpolation weights of a particle shape of order n (tophat 1, triangle 2, bspline3 4) are a cardinal B-spline:
+# sum_i w_i (x_i - x)^k equals the spline's k-th central moment for k <= n -- 0, (n+1)/12, 0, 3 ((n+1)/12)^2 - (n+1)/120 --
+# whatever the particle's position.  With k = 0 .. n that fixes all n + 1 weights, so gathering the monomials pins the
+# transcribed weight formulas against spline theory, for the cell-centred (g) and the staggered (h) set.
+def check_weight_moments(abi, shape, tol=5e-12):
+    order = {"tophat": 1, "triangle": 2, "bspline3": 4}[shape]
+    var = (order + 1) / 12.0
+    mu = [1.0, 0.0, var, 0.0, 3.0 * var * var - (order + 1) / 120.0]
+    n, cell = 24, 1.0e-3
+    sp = SpeciesSpec("electron", -Q0, M0)
+    rng = np.random.default_rng(41)
+    for comp, stag in (("ey", 0.0), ("ex", 0.5)):             # 1D: ey is gathered with gx, ex with hx
+        for k in range(order + 1):
+            sim = Simulation(1, [n], [0.0], [n * cell], shape=shape, species=[sp], abi=abi)
+            ng = sim.ctx.ng
+            xc = 0.5 * n * cell
+            X = (sim.grid_min_local[0] + (np.arange(n + 2 * ng) - ng + stag) * cell - xc) / cell     # node positions in cells
+            sim.ctx.upload_fields(**{comp: 1.0e3 * X ** k})
+            m = 300
+            P = np.zeros((m, 5))
+            P[:, 0] = rng.uniform(8.0 * cell, (n - 8.0) * cell, m)
+            P[:, 4] = 1.0 + np.arange(m) * 1e-3
+            sim.ctx.upload_particles(0, P)
+            sim.ctx.set_time(sim.dt, 0.0, 0)
+            sim.ctx.push_particles()
+            Q = sim.ctx.download_particles(0)
+            P, Q = P[np.argsort(P[:, -1])], Q[np.argsort(Q[:, -1])]
+            got = Q[:, 1 + "xyz".index(comp[1])] / (-Q0 * sim.dt) / 1.0e3
+            xp = (P[:, 0] - xc) / cell
+            want = sum(math.comb(k, j) * xp ** (k - j) * mu[j] for j in range(k + 1))
+            assert np.max(np.abs(got - want)) < tol * max(1.0, np.max(np.abs(want))), (shape, comp, k)
+            sim.ctx.close()
+
+
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_shape_weights_reproduce_spline_moments(oracle_abi, shape):
+    check_weight_moments(oracle_abi, shape)
