@@ -503,3 +503,137 @@ def check_weight_moments(abi, shape, tol=5e-12):
 @pytest.mark.parametrize("shape", SHAPE_NAMES)
 def test_shape_weights_reproduce_spline_moments(oracle_abi, shape):
     check_weight_moments(oracle_abi, shape)
+
+
+# ---- the deposit against the published scheme (Esirkepov, Comput. Phys. Commun. 135 (2001) 144), written from the paper ----
+def bspline(order, d):
+    """cardinal B-spline of the given order (1 linear, 2 quadratic, 4 quartic) at distance d (in cells) from its centre"""
+    a = np.abs(d)
+    if order == 1:
+        return np.where(a < 1.0, 1.0 - a, 0.0)
+    if order == 2:
+        return np.where(a <= 0.5, 0.75 - a * a, np.where(a < 1.5, 0.5 * (1.5 - a) ** 2, 0.0))
+    return np.where(a <= 0.5, 115.0 / 192.0 - 5.0 * a * a / 8.0 + a ** 4 / 4.0,
+                    np.where(a <= 1.5, (55.0 + 20.0 * a - 120.0 * a * a + 80.0 * a ** 3 - 16.0 * a ** 4) / 96.0,
+                             np.where(a < 2.5, (5.0 - 2.0 * a) ** 4 / 384.0, 0.0)))
+
+
+def esirkepov_textbook(sim, order, P, charge, mass):
+    """J of free-streaming particles (E = B = 0) by the paper's formulas: form factors S0 at x(t + dt/2), S1 at
+    x(t + 3dt/2), DS = S1 - S0, the density decomposition W, and the running sum along each existing axis."""
+    nd, ng, dt = sim.ndims, sim.ctx.ng, sim.dt
+    shp = sim.ctx._np_shape()
+    J = [np.zeros(shp) for _ in range(3)]
+    ext = [sim.n_local[d] + 2 * ng for d in range(nd)]
+    nodes = [sim.grid_min_local[d] + (np.arange(ext[d]) - ng) * sim.d[d] for d in range(nd)]
+    dv = float(np.prod(sim.d))
+    for row in P:
+        u = row[nd:nd + 3] / (mass * C)
+        v = u * C / math.sqrt(1.0 + float(u @ u))
+        qw = charge * row[nd + 3]
+        S0, DS = [], []
+        for d in range(nd):
+            x0 = row[d] + v[d] * dt / 2.0
+            x1 = row[d] + 3.0 * v[d] * dt / 2.0
+            s0 = bspline(order, (nodes[d] - x0) / sim.d[d])
+            s1 = bspline(order, (nodes[d] - x1) / sim.d[d])
+            S0.append(s0); DS.append(s1 - s0)
+        if nd == 1:
+            J[0] += -(qw / dt) * np.cumsum(DS[0])
+            for c in (1, 2):
+                J[c] += qw * v[c] / sim.d[0] * (S0[0] + 0.5 * DS[0])
+        elif nd == 2:
+            sx, sy, dx_, dy_ = S0[0][None, :], S0[1][:, None], DS[0][None, :], DS[1][:, None]     # arrays are [y][x]
+            J[0] += -(qw / (dt * sim.d[1])) * np.cumsum(dx_ * (sy + 0.5 * dy_), axis=1)
+            J[1] += -(qw / (dt * sim.d[0])) * np.cumsum(dy_ * (sx + 0.5 * dx_), axis=0)
+            J[2] += qw * v[2] / dv * (sx * sy + 0.5 * dx_ * sy + 0.5 * sx * dy_ + dx_ * dy_ / 3.0)
+        else:
+            s = [S0[0][None, None, :], S0[1][None, :, None], S0[2][:, None, None]]               # arrays are [z][y][x]
+            g = [DS[0][None, None, :], DS[1][None, :, None], DS[2][:, None, None]]
+            for a_, axis in ((0, 2), (1, 1), (2, 0)):
+                b_, c_ = (a_ + 1) % 3, (a_ + 2) % 3
+                W = g[a_] * (s[b_] * s[c_] + 0.5 * g[b_] * s[c_] + 0.5 * s[b_] * g[c_] + g[b_] * g[c_] / 3.0)
+                J[a_] += -(qw * sim.d[a_] / (dt * dv)) * np.cumsum(W, axis=axis)
+    return J
+
+
+def check_deposit_against_paper(abi, ndims, shape, tol=2e-12):
+    order = {"tophat": 1, "triangle": 2, "bspline3": 4}[shape]
+    n = [14, 12, 10][:ndims]
+    cell = 1.5e-6
+    sp = SpeciesSpec("positron", Q0, M0)
+    sim = Simulation(ndims, n, [0.0] * ndims, [cell * x for x in n], shape=shape, species=[sp], abi=abi)
+    rng = np.random.default_rng(53)
+    m = 60
+    P = np.zeros((m, ndims + 4))
+    for d in range(ndims):
+        P[:, d] = rng.uniform(sim.min_local[d], sim.max_local[d], m)          # anywhere, also next to the boundary
+    P[:, ndims:ndims + 3] = rng.normal(0.0, 1.5, (m, 3)) * M0 * C             # relativistic: many cell crossings
+    P[:, ndims + 3] = rng.uniform(0.5, 1.5, m) * 1e12
+    sim.ctx.upload_particles(0, P)
+    sim.ctx.set_time(sim.dt, 0.0, 0)
+    want = esirkepov_textbook(sim, order, P, Q0, M0)
+    sim.ctx.push_particles()
+    got = sim.ctx.download_fields(("jx", "jy", "jz"))
+    for c, k in enumerate(("jx", "jy", "jz")):
+        scale = max(np.max(np.abs(want[c])), 1e-300)
+        assert np.max(np.abs(got[k] - want[c])) < tol * scale, (k, np.max(np.abs(got[k] - want[c])) / scale)
+    sim.ctx.close()
+
+
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_deposit_equals_published_esirkepov(oracle_abi, ndims, shape):
+    check_deposit_against_paper(oracle_abi, ndims, shape)
+
+
+# ---- the push against the textbook Boris scheme (Birdsall & Langdon 4-3, relativistic form), uniform E and B ----------
+def check_push_against_textbook(abi, ndims, shape, tol=5e-14):
+    """u- = u + (q dt / 2 m c) E;  t = (q dt / 2 m) B / gamma(u-);  u' = u- + u- x t;  u+ = u- + u' x 2 t / (1 + t^2);
+    u(t + dt) = u+ + (q dt / 2 m c) E;  x(t + dt) = x + (v(t) + v(t + dt)) dt / 2 -- written from the textbook; the reference
+    applies the rotation as one closed-form matrix (particles.F90:347-394)."""
+    n = [10, 8, 6][:ndims]
+    cell = 1.0e-3
+    sp = SpeciesSpec("electron", -Q0, M0)
+    sim = Simulation(ndims, n, [0.0] * ndims, [cell * x for x in n], shape=shape, species=[sp], abi=abi)
+    shp = sim.ctx._np_shape()
+    E = np.array([3.0e5, -2.0e5, 4.0e5])
+    B = np.array([0.02, 0.05, -0.03])
+    sim.ctx.upload_fields(**{k: np.full(shp, v) for k, v in zip(("ex", "ey", "ez", "bx", "by", "bz"), list(E) + list(B))})
+    rng = np.random.default_rng(61)
+    m = 100
+    P = np.zeros((m, ndims + 4))
+    for d in range(ndims):
+        P[:, d] = rng.uniform(3.0 * cell, (n[d] - 3.0) * cell, m)
+    u = rng.normal(0.0, 1.0, (m, 3))
+    P[:, ndims:ndims + 3] = u * M0 * C
+    P[:, ndims + 3] = 1.0 + np.arange(m) * 1e-3
+    sim.ctx.upload_particles(0, P)
+    sim.ctx.set_time(sim.dt, 0.0, 0)
+    sim.ctx.push_particles()
+    Q = sim.ctx.download_particles(0)
+    P, Q = P[np.argsort(P[:, -1])], Q[np.argsort(Q[:, -1])]
+    u = P[:, ndims:ndims + 3] / (M0 * C)
+    q, dt = -Q0, sim.dt
+    um = u + (q * dt / (2.0 * M0 * C)) * E
+    gm = np.sqrt(1.0 + np.sum(um * um, axis=1))[:, None]
+    t = (q * dt / (2.0 * M0)) * B / gm
+    up = um + np.cross(um, t)
+    upl = um + np.cross(up, 2.0 * t / (1.0 + np.sum(t * t, axis=1))[:, None])
+    un = upl + (q * dt / (2.0 * M0 * C)) * E
+    got_u = Q[:, ndims:ndims + 3] / (M0 * C)
+    assert np.max(np.abs(got_u - un)) < tol * np.max(np.abs(un))
+    v0 = u * C / np.sqrt(1.0 + np.sum(u * u, axis=1))[:, None]
+    v1 = un * C / np.sqrt(1.0 + np.sum(un * un, axis=1))[:, None]
+    xn = P[:, :ndims] + 0.5 * dt * (v0 + v1)[:, :ndims]
+    L = np.array([cell * x for x in n])
+    dx = np.abs(Q[:, :ndims] - xn)
+    dx = np.minimum(dx, np.abs(L - dx))                    # (a particle may have wrapped)
+    assert np.max(dx / L) < 1e-13
+    sim.ctx.close()
+
+
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_push_equals_textbook_boris(oracle_abi, ndims, shape):
+    check_push_against_textbook(oracle_abi, ndims, shape)
