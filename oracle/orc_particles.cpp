@@ -3,6 +3,14 @@
 // shape include files epochNd/src/include/{tophat,triangle,bspline3}/*.inc, in the
 // reference's operation order, plus particle_bcs
 // (boundary.F90:1316-1972) and the diagnostics formulas of io/calc_df.F90.
+//
+// PARITY UNPINNED BY THE REFERENCE: EPOCH's own tests hold no particle-dependent number and EPOCH cannot be built
+// here (Fortran + MPI + the missing SDF submodule), so nothing in this file has been compared with reference output
+// (tools/ref_build/ is the recipe that would do it).  What pins it instead, stage by stage (tests/test_oracle.py,
+// DESIGN.md section 5): the gather's Yee staggering by exact reproduction of linear fields, the shape weights by the
+// B-spline central moments, the rotation by the textbook Boris form, the position update, the deposit by Esirkepov's
+// scheme written from the paper, particle_bcs by placed particles, the whole by exact charge conservation and the
+// reference's two-stream deck (growth rates, Langmuir frequency, energy bound).
 #include "orc_state.hpp"
 #include <algorithm>
 
