@@ -340,10 +340,13 @@ int32_t EB200_NAME(download_probe)(EB200_CTX*, int32_t ispecies, int32_t iprobe,
 int32_t EB200_NAME(set_thermal_boundary)(EB200_CTX*, int32_t ispecies, int32_t boundary, const double* ext_temp,
                                          int64_t seed);
 /* options (key, value as strings):
- *   "deterministic_deposit" "0|1"   run-to-run bitwise reproducible currents (tiled kernels: 2D/3D)
- *   "push_kernel"   "auto|baseline|tiled"
+ *   "deterministic_deposit" "0|1"   run-to-run bitwise reproducible currents (tiled kernels: 1D/2D/3D)
+ *   "push_kernel"   "auto|baseline|tiled"   auto / tiled: the tiled push + deposit kernels (1D/2D/3D); baseline: the
+ *                                   general kernel with one global RED per deposited value (debugging)
  *   "defer_window"  "auto|<slots>"  head room of the deferred permute (0: permute inside the sort); takes effect
- *                                   when the particle arrays are next allocated ("reserve", upload)
+ *                                   when the particle arrays are next allocated ("reserve", upload); auto = an eighth of
+ *                                   the species and at least 4.5 layers of tiles along the slowest axis
+ *   "push_overlap"  "0|1"           deposit of a slab on a second stream beside the next slab's push (measured: no gain)
  *   "reserve"       "<species>:<particles>"  allocate a species' storage once
  *   "deposit_scratch" "<particles>" particles per push/deposit launch (64 B of scratch each)
  *   "fuse_keys" "0|1", "tma" "0|1", "timers" "0|1", "host_threads" "<n>", "pin_bytes" "<bytes>",
@@ -353,7 +356,9 @@ int32_t EB200_NAME(set_thermal_boundary)(EB200_CTX*, int32_t ispecies, int32_t b
 int32_t EB200_NAME(set_option)(EB200_CTX*, const char* key, const char* value);
 int32_t EB200_NAME(sync)(EB200_CTX*);
 /* milliseconds of device time spent in the named phase since the last call with
- * reset != 0 ("push", "sort", "fields", "halo", "bcs"); CUDA-event based. */
+ * reset != 0 ("push", "push_kernel", "push_A", "push_B", "sort", "fields", "halo", "bcs", "window", any name given to
+ * eb200_mark); CUDA-event based.  Counters read through the same call (in *launches): "launches", "deferred_sorts",
+ * "permuted_sorts", "cell_mismatch" (must stay 0), "thermal_reemitted". */
 int32_t EB200_NAME(timer)(EB200_CTX*, const char* phase, int32_t reset, double* ms,
                           int64_t* launches);
 /* user bracket on the context's stream: mark(phase, 1) records a begin event,
