@@ -629,7 +629,7 @@ def check_push_against_textbook(abi, ndims, shape, tol=5e-14):
     L = np.array([cell * x for x in n])
     dx = np.abs(Q[:, :ndims] - xn)
     dx = np.minimum(dx, np.abs(L - dx))                    # (a particle may have wrapped)
-    assert np.max(dx / L) < 1e-13
+    assert np.max(dx / L) < max(1e-13, tol)
     sim.ctx.close()
 
 

@@ -21,3 +21,45 @@ def test_particle_bcs_known_answers_gpu(product_abi, ndims):
     """placed particles through eb200_particle_bcs: wrap, mirror, removal beyond the outer edge, < on the min side and
     >= on the max side -- bit for bit the known answers of tests/test_oracle.py::test_particle_bcs_known_answers"""
     check_particle_bcs(product_abi, ndims)
+
+
+# ---- the published-algorithm pins of tests/test_oracle.py through the CUDA library ----------------------------------------
+# Written after the round's GPU budget was spent: they have NOT run on a GPU yet.  xfail(strict=False) keeps an untested
+# assertion from failing the suite -- a pass shows up as XPASS, a miss as xfail -- until a GPU run has confirmed them.
+# The CUDA path is covered either way: it equals the oracle to 1e-12 on the same stages (tests/test_gpu_parity.py) and the
+# oracle meets these pins on the CPU.
+from test_oracle import (check_deposit_against_paper, check_push_against_textbook, check_weight_moments,  # noqa: E402
+                         check_total_current)
+
+UNRUN = pytest.mark.xfail(reason="added after the GPU budget of round 2 was spent: not yet run on a GPU", strict=False)
+
+
+@pytest.mark.gpu
+@UNRUN
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_deposit_equals_published_esirkepov_gpu(product_abi, ndims, shape):
+    check_deposit_against_paper(product_abi, ndims, shape, tol=1e-10)
+
+
+@pytest.mark.gpu
+@UNRUN
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_push_equals_textbook_boris_gpu(product_abi, ndims, shape):
+    check_push_against_textbook(product_abi, ndims, shape, tol=1e-11)
+
+
+@pytest.mark.gpu
+@UNRUN
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_shape_weights_reproduce_spline_moments_gpu(product_abi, shape):
+    check_weight_moments(product_abi, shape, tol=1e-10)
+
+
+@pytest.mark.gpu
+@UNRUN
+@pytest.mark.parametrize("ndims", [1, 2, 3])
+@pytest.mark.parametrize("shape", SHAPE_NAMES)
+def test_total_current_equals_sum_q_w_v_gpu(product_abi, ndims, shape):
+    check_total_current(product_abi, ndims, shape, tol=1e-9)
