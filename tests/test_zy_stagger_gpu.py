@@ -1,4 +1,5 @@
-"""The Yee staggering of the gather on the CUDA path (tiled kernels, TMA-staged tiles in 2D/3D): linear fields sampled at
+"""Known answers through the CUDA library (collected late; tests/test_zz_no_alloc.py stays last).
+The Yee staggering of the gather on the CUDA path (tiled kernels, TMA-staged tiles in 2D/3D): linear fields sampled at
 each component's own Yee locations must be gathered exactly -- the same check as
 tests/test_oracle.py::test_gather_staggering_linear_fields, through the product library (tolerance 1e-11 of the field
 value; a wrong stagger costs 1e-2)."""
